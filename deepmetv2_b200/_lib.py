@@ -1,0 +1,132 @@
+"""ctypes binding of csrc/libgraphmet.so (the C ABI declared in include/graphmet.h).
+
+There is NO fallback: if the shared library is missing the import of any op raises, telling the
+user how to build it (``python -c 'import __graft_entry__ as g; g.build()'`` or ``make -C
+deepmetv2_b200/csrc``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+SO_PATH = os.path.join(CSRC, "libgraphmet.so")
+HEADER = os.path.join(os.path.dirname(_HERE), "include", "graphmet.h")
+
+GM_OK = 0
+FLAG_CAT_OUT_OF_RANGE = 1
+FLAG_DEGREE_CAPPED = 2
+FLAG_EDGE_OVERFLOW = 4
+FLAG_EVENT_TOO_LARGE = 8
+MAX_CONV_DEPTH = 4
+AGGR = {"max": 0, "add": 1, "mean": 2}
+PRECISION = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3}
+
+_vp, _i, _ll, _f, _d, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double, C.c_size_t
+
+
+class GmBatchNorm(C.Structure):
+    _fields_ = [("weight", _vp), ("bias", _vp), ("running_mean", _vp), ("running_var", _vp),
+                ("num_batches_tracked", _vp)]
+
+
+class GmParams(C.Structure):
+    _fields_ = [("embed_charge", _vp), ("embed_pdgid", _vp), ("embed_pv", _vp),
+                ("cont_w", _vp), ("cont_b", _vp), ("cat_w", _vp), ("cat_b", _vp),
+                ("enc_w", _vp), ("enc_b", _vp), ("bn_all", GmBatchNorm),
+                ("conv_w", _vp * MAX_CONV_DEPTH), ("conv_b", _vp * MAX_CONV_DEPTH),
+                ("conv_bn", GmBatchNorm * MAX_CONV_DEPTH),
+                ("out1_w", _vp), ("out1_b", _vp), ("out2_w", _vp), ("out2_b", _vp),
+                ("continuous_dim", _i), ("conv_depth", _i)]
+
+
+# name -> (restype, argtypes); must list every symbol include/graphmet.h declares
+SIGNATURES = {
+    "gm_version": (_i, []),
+    "gm_status_string": (C.c_char_p, [_i]),
+    "gm_last_cuda_error": (_i, []),
+    "gm_num_sms": (_i, []),
+    "gm_prepare_etaphi": (_i, [_vp, _i, _i, _vp, _vp]),
+    "gm_batch_to_ptr": (_i, [_vp, _i, _i, _vp, _vp]),
+    "gm_radius_graph_ws_bytes": (_sz, [_i, _i]),
+    "gm_radius_graph_count": (_i, [_vp, _i, _i, _vp, _i, _i, _d, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _vp]),
+    "gm_radius_graph_fill": (_i, [_vp, _i, _i, _vp, _i, _i, _d, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _ll, _vp,
+                                  _vp, _vp]),
+    "gm_csr_ws_bytes": (_sz, [_i, _ll]),
+    "gm_edge_index_to_csr": (_i, [_vp, _ll, _i, _vp, _sz, _vp, _vp, _vp]),
+    "gm_csr_transpose": (_i, [_vp, _vp, _i, _ll, _vp, _sz, _vp, _vp, _vp]),
+    "gm_edgeconv_forward": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "gm_net_ws_bytes": (_sz, [_i, _i, _i]),
+    "gm_net_forward": (_i, [C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f,
+                            _vp, _sz, _vp, _vp, _vp]),
+    "gm_net_bwd_ws_bytes": (_sz, [_i, _i]),
+    "gm_net_backward": (_i, [C.POINTER(GmParams), C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp,
+                             _i, _i, _i, _i, _f, _vp, _sz, _vp, _sz, _vp, _vp, _vp]),
+    "gm_met_loss": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
+    "gm_segment_sum": (_i, [_vp, _vp, _i, _vp, _vp]),
+    "gm_scatter_add": (_i, [_vp, _vp, _ll, _vp, _ll, _vp]),
+    "gm_index_stats": (_i, [_vp, _ll, _vp, _vp]),
+    "gm_resolution": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    "gm_adamw_step": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _f, _vp]),
+}
+
+_lib = None
+
+
+class GraphMETLibraryError(RuntimeError):
+    pass
+
+
+def build(verbose: bool = False) -> str:
+    """Compile csrc/*.cu for sm_100a into csrc/libgraphmet.so (nvcc cross-compiles without a GPU)."""
+    cmd = ["make", "-C", CSRC, "-j", str(os.cpu_count() or 4)]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        print(res.stdout[-4000:])
+        print(res.stderr[-4000:])
+    if res.returncode != 0:
+        raise GraphMETLibraryError("building libgraphmet.so failed")
+    return SO_PATH
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise GraphMETLibraryError(
+                f"{SO_PATH} is missing: build it with `make -C {CSRC}` "
+                "(or __graft_entry__.build()). There is no CPU / PyTorch fallback for this path.")
+        l = C.CDLL(SO_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def check(status: int, what: str = "libgraphmet") -> None:
+    if status != GM_OK:
+        l = lib()
+        msg = l.gm_status_string(status).decode()
+        if status == -4:
+            msg += f" (cudaError {l.gm_last_cuda_error()})"
+        raise GraphMETLibraryError(f"{what}: {msg}")
+
+
+def stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def ptr(t: torch.Tensor | None) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def require_cuda(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise GraphMETLibraryError(
+            f"{name} is on {t.device}: the GraphMET kernels are CUDA (sm_100a) only; there is no CPU fallback")

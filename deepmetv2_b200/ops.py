@@ -1,0 +1,190 @@
+"""Host-side mirror of the three upstream operators the reference's hot path calls, backed by
+libgraphmet.so (CUDA, sm_100a) — same names, argument meaning and return types:
+
+* ``radius_graph``  <- torch_cluster.radius_graph   (train.py:48, evaluate.py:88, plt_weight.py:122)
+* ``scatter_add``   <- torch_scatter.scatter_add     (model/net.py:8,55-56,79-80,132-133)
+* ``build_graph``   the same search without materialising the int64 ``edge_index`` (fused path)
+
+plus ``prepare_inputs`` (train.py:42-46 fused) and ``batch_to_ptr``.
+No CPU path: tensors must live on a CUDA device.
+"""
+from __future__ import annotations
+
+import dataclasses
+
+import torch
+
+from . import _lib
+from ._lib import check, lib, ptr, stream
+
+
+@dataclasses.dataclass
+class GraphCSR:
+    """CSR by target (rows) with ascending sources (cols) + the transposed CSR for the backward."""
+    rowptr: torch.Tensor          # [N+1] int32
+    col: torch.Tensor             # [E]   int32
+    num_nodes: int
+    num_edges: int
+    max_degree: int = -1          # before the cap
+    num_capped: int = 0
+    rowptr_t: torch.Tensor | None = None
+    col_t: torch.Tensor | None = None
+
+    @property
+    def symmetric(self) -> bool:
+        return self.num_capped == 0
+
+    def transposed(self):
+        """(rowptr_t, col_t): the graph by SOURCE. Equal to (rowptr, col) when no node was capped."""
+        if self.symmetric:
+            return self.rowptr, self.col
+        if self.rowptr_t is None:
+            N, E = self.num_nodes, self.num_edges
+            l = lib()
+            ws = torch.empty(l.gm_csr_ws_bytes(N, E), dtype=torch.uint8, device=self.col.device)
+            self.rowptr_t = torch.empty(N + 1, dtype=torch.int32, device=self.col.device)
+            self.col_t = torch.empty(max(E, 1), dtype=torch.int32, device=self.col.device)
+            check(l.gm_csr_transpose(ptr(self.rowptr), ptr(self.col), N, E, ptr(ws), ws.numel(),
+                                     ptr(self.rowptr_t), ptr(self.col_t), stream()), "gm_csr_transpose")
+        return self.rowptr_t, self.col_t
+
+
+class EdgeIndex(torch.Tensor):
+    """The reference-shaped ``LongTensor[2,E]`` returned by :func:`radius_graph`, carrying the int32
+    CSR it was built from so ``GraphMETNetwork.forward`` does not have to re-sort it."""
+    __torch_function__ = torch._C._disabled_torch_function_impl
+
+    @staticmethod
+    def wrap(t: torch.Tensor, csr: GraphCSR) -> "EdgeIndex":
+        e = torch.Tensor._make_subclass(EdgeIndex, t)
+        e._gm_csr = csr
+        return e
+
+
+def batch_to_ptr(batch: torch.Tensor, num_events: int) -> torch.Tensor:
+    """Sorted int64 ``batch`` [N] -> int32 ``ptr`` [B+1] on the device (no sync)."""
+    _lib.require_cuda(batch, "batch")
+    batch = batch.contiguous()
+    assert batch.dtype == torch.int64
+    out = torch.empty(num_events + 1, dtype=torch.int32, device=batch.device)
+    check(lib().gm_batch_to_ptr(ptr(batch), batch.numel(), num_events, ptr(out), stream()), "gm_batch_to_ptr")
+    return out
+
+
+def prepare_inputs(x: torch.Tensor):
+    """train.py:42-46 in one pass: returns (x_cont view, x_cat_f32 view, etaphi[N,2]).
+    phi = atan2f(py, px) is evaluated by the kernel; feed the returned etaphi to an oracle when
+    comparing edge sets (libm/ATen atan2 differ from CUDA's in the last ulp)."""
+    _lib.require_cuda(x, "x")
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1 and x.shape[1] >= 11
+    etaphi = torch.empty(x.shape[0], 2, dtype=torch.float32, device=x.device)
+    check(lib().gm_prepare_etaphi(ptr(x), x.stride(0), x.shape[0], ptr(etaphi), stream()), "gm_prepare_etaphi")
+    return x[:, :8], x[:, 8:11], etaphi
+
+
+def build_graph(pos: torch.Tensor, r: float, ptr_i32: torch.Tensor | None = None, batch: torch.Tensor | None = None,
+                loop: bool = False, max_num_neighbors: int = 32, phi_wrap: bool = False,
+                max_event_nodes: int | None = None, want_edge_index: bool = False,
+                edge_capacity: int | None = None):
+    """Cell-binned radius search. Returns GraphCSR (and the int64 edge_index if asked).
+
+    ``edge_capacity``: when given, no host sync happens (E stays on the device, ``num_edges`` is the
+    capacity and ``col`` is over-allocated); otherwise E is read back once (as torch_cluster does)."""
+    _lib.require_cuda(pos, "x")
+    if pos.dim() == 1:
+        pos = pos[:, None]
+    assert pos.dtype == torch.float32 and pos.stride(1) == 1
+    N, dim = pos.shape
+    if dim > 2:
+        raise NotImplementedError("radius_graph kernels are specialised for 1-D / 2-D (eta, phi) positions")
+    dev = pos.device
+    if ptr_i32 is None:
+        if batch is None:
+            ptr_i32 = torch.tensor([0, N], dtype=torch.int32, device=dev)
+        else:
+            B = int(batch[-1].item()) + 1 if N > 0 else 0   # sorted batch: last element is the max
+            ptr_i32 = batch_to_ptr(batch, B)
+    B = ptr_i32.numel() - 1
+    if max_event_nodes is None:
+        max_event_nodes = int((ptr_i32[1:] - ptr_i32[:-1]).max().item()) if B > 0 else 0
+    l = lib()
+    ws = torch.empty(l.gm_radius_graph_ws_bytes(N, B), dtype=torch.uint8, device=dev)
+    rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+    stats = torch.zeros(4, dtype=torch.int32, device=dev)
+    args = (ptr(pos), pos.stride(0), dim, ptr(ptr_i32), N, B, float(r), int(max_num_neighbors), int(bool(loop)),
+            int(bool(phi_wrap)), int(max_event_nodes), ptr(ws), ws.numel())
+    check(l.gm_radius_graph_count(*args, ptr(rowptr), ptr(stats), stream()), "gm_radius_graph_count")
+    if edge_capacity is None:
+        E, max_deg, capped, _flags = stats.tolist()      # one D2H sync, like torch_cluster's masked_select
+        cap = E
+    else:
+        E, max_deg, capped = int(edge_capacity), -1, 0
+        cap = E
+    col = torch.empty(max(cap, 1), dtype=torch.int32, device=dev)
+    ei = torch.empty(2, cap, dtype=torch.int64, device=dev) if want_edge_index else None
+    check(l.gm_radius_graph_fill(*args, ptr(rowptr), ptr(col), cap, ptr(ei), ptr(stats), stream()),
+          "gm_radius_graph_fill")
+    g = GraphCSR(rowptr, col, N, E, max_deg, capped)
+    g._stats = stats
+    return (g, ei) if want_edge_index else g
+
+
+def radius_graph(x, r, batch=None, loop=False, max_num_neighbors=32, flow="source_to_target", phi_wrap=False):
+    """Drop-in for ``torch_cluster.radius_graph``: LongTensor[2,E], row 0 = source j, row 1 = target i,
+    sorted by (i, j); at most ``max_num_neighbors`` sources per target (lowest indices kept)."""
+    assert flow in ("source_to_target", "target_to_source")
+    g, ei = build_graph(x, r, batch=batch, loop=loop, max_num_neighbors=max_num_neighbors, phi_wrap=phi_wrap,
+                        want_edge_index=True)
+    if flow == "target_to_source":
+        return ei.flip(0)
+    return EdgeIndex.wrap(ei, g)
+
+
+def csr_from_edge_index(edge_index: torch.Tensor, num_nodes: int) -> GraphCSR:
+    """Any int64 [2,E] edge_index -> GraphCSR (device counting sort; symmetric-ness unknown, so the
+    transposed CSR is built on demand for the backward)."""
+    csr = getattr(edge_index, "_gm_csr", None)
+    if csr is not None and csr.num_nodes == num_nodes:
+        return csr
+    _lib.require_cuda(edge_index, "edge_index")
+    assert edge_index.dtype == torch.int64 and edge_index.dim() == 2 and edge_index.shape[0] == 2
+    ei = edge_index.contiguous()
+    E = ei.shape[1]
+    l = lib()
+    ws = torch.empty(l.gm_csr_ws_bytes(num_nodes, E), dtype=torch.uint8, device=ei.device)
+    rowptr = torch.empty(num_nodes + 1, dtype=torch.int32, device=ei.device)
+    col = torch.empty(max(E, 1), dtype=torch.int32, device=ei.device)
+    check(l.gm_edge_index_to_csr(ptr(ei), E, num_nodes, ptr(ws), ws.numel(), ptr(rowptr), ptr(col), stream()),
+          "gm_edge_index_to_csr")
+    return GraphCSR(rowptr, col, num_nodes, E, -1, num_capped=1)   # treat as possibly asymmetric
+
+
+def segment_sum(src: torch.Tensor, ptr_i32: torch.Tensor) -> torch.Tensor:
+    out = torch.empty(ptr_i32.numel() - 1, dtype=torch.float32, device=src.device)
+    check(lib().gm_segment_sum(ptr(src), ptr(ptr_i32), out.numel(), ptr(out), stream()), "gm_segment_sum")
+    return out
+
+
+def scatter_add(src, index, dim=-1, out=None, dim_size=None):
+    """Drop-in for ``torch_scatter.scatter_add`` on 1-D float32 CUDA tensors (what model/net.py uses).
+    A sorted index (PyG ``batch``) takes the deterministic segmented path; anything else the atomic one.
+    Not differentiable — the differentiable MET reduction is ``loss_fn`` / ``met_from_weights``."""
+    _lib.require_cuda(src, "src")
+    if src.dim() != 1 or index.dim() != 1 or dim not in (-1, 0):
+        raise NotImplementedError("scatter_add kernels cover the 1-D case used by the GraphMET path")
+    src = src.detach().contiguous().float()
+    index = index.contiguous()
+    l = lib()
+    stats = torch.empty(2, dtype=torch.int64, device=src.device)
+    check(l.gm_index_stats(ptr(index), index.numel(), ptr(stats), stream()), "gm_index_stats")
+    mx, is_sorted = stats.tolist()
+    if out is not None:
+        dim_size = out.numel()
+    elif dim_size is None:
+        dim_size = mx + 1
+    if is_sorted and out is None:
+        return segment_sum(src, batch_to_ptr(index, dim_size))
+    if out is None:
+        out = torch.zeros(dim_size, dtype=torch.float32, device=src.device)
+    check(l.gm_scatter_add(ptr(src), ptr(index), src.numel(), ptr(out), dim_size, stream()), "gm_scatter_add")
+    return out

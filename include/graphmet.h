@@ -1,0 +1,225 @@
+/*
+ * graphmet.h — C ABI of libgraphmet.so: the B200 (sm_100a) implementation of the
+ * DeepMETv2 GraphMETNetwork hot path.
+ *
+ * Every entry point is `extern "C"`, takes plain device pointers / sizes / a
+ * cudaStream_t (passed as void*), returns an int status (GM_OK == 0, < 0 on error),
+ * never throws, never allocates device memory and never synchronises unless stated.
+ * The caller (the Python host in deepmetv2_b200/, or any other FFI) owns all
+ * buffers.  All kernels are launched on `stream`.
+ *
+ * Each function cites the reference call it replaces (paths are into the upstream
+ * repository DeepMETv2/DeepMETv2).
+ *
+ * Layouts (fp32 unless stated):
+ *   x        [N,11]  PF candidates: pX,pY,pT,eta,d0,dz,mass,puppiWeight | pdgId,charge,fromPV
+ *                    (model/data_loader.py:70-77)
+ *   ptr      [B+1]   int32 event boundaries into the node axis (batch is sorted)
+ *   rowptr   [N+1]   int32 CSR by TARGET node; col[E] int32 = SOURCE node, ascending per row
+ *   emb      [N,32]  node embeddings, row-major, hidden_dim = 32 (model/net.py:41-43)
+ */
+#ifndef GRAPHMET_H_
+#define GRAPHMET_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GM_VERSION 100
+
+/* status codes */
+#define GM_OK 0
+#define GM_ERR_INVALID_ARGUMENT (-1)
+#define GM_ERR_CAPACITY (-2)      /* caller-provided buffer too small */
+#define GM_ERR_UNSUPPORTED (-3)   /* shape outside what the kernels are specialised for */
+#define GM_ERR_CUDA (-4)          /* a CUDA runtime call / launch failed; see gm_last_cuda_error */
+
+/* device-side error flag bits (written with atomicOr into an int the caller provides) */
+#define GM_FLAG_CAT_OUT_OF_RANGE 1   /* embedding index outside its table (reference: IndexError) */
+#define GM_FLAG_DEGREE_CAPPED 2      /* some node hit max_num_neighbors: CSR is not symmetric */
+#define GM_FLAG_EDGE_OVERFLOW 4      /* E exceeded the capacity given to gm_radius_graph_fill */
+#define GM_FLAG_EVENT_TOO_LARGE 8     /* an event has more nodes than max_event_nodes promised */
+
+#define GM_HIDDEN 32
+#define GM_NUM_PARAM_TENSORS 23
+#define GM_NUM_PARAM_FLOATS 6641     /* for continuous_dim = 8, conv_depth = 2 */
+#define GM_MAX_CONV_DEPTH 4
+
+/* aggregation of EdgeConv (torch_geometric default for EdgeConv is max) */
+#define GM_AGGR_MAX 0
+#define GM_AGGR_ADD 1
+#define GM_AGGR_MEAN 2
+
+/* arithmetic of the per-edge contraction */
+#define GM_PREC_FP32 0      /* CUDA-core fp32 FFMA2 (parity mode) */
+#define GM_PREC_TF32 1      /* tcgen05 kind::tf32 */
+#define GM_PREC_BF16 2      /* tcgen05 kind::f16 (bf16 operands, fp32 accumulate in TMEM) */
+#define GM_PREC_TF32X3 3    /* tcgen05 3xTF32 split (fp32-accurate) */
+
+int gm_version(void);
+const char *gm_status_string(int status);
+int gm_last_cuda_error(void);          /* cudaError_t of the last failing runtime call */
+int gm_num_sms(void);                  /* of the current device (cached) */
+
+/* ---------------------------------------------------------------------------------
+ * Parameters: the reference's 23 trainable tensors in construction order
+ * (model/graph_met_network.py:15-45; state_dict names in comments) + BN buffers.
+ * Gradients use the same struct with the buffers being written.
+ * --------------------------------------------------------------------------------- */
+typedef struct GmBatchNorm {
+    float *weight;               /* [32]  gamma */
+    float *bias;                 /* [32]  beta */
+    float *running_mean;         /* [32]  (NULL in a gradient struct) */
+    float *running_var;          /* [32] */
+    int64_t *num_batches_tracked;/* [1]   may be NULL */
+} GmBatchNorm;
+
+typedef struct GmParams {
+    float *embed_charge;         /* [3,8]   graphnet.embed_charge.weight */
+    float *embed_pdgid;          /* [7,8]   graphnet.embed_pdgid.weight */
+    float *embed_pv;             /* [8,8]   graphnet.embed_pv.weight */
+    float *cont_w, *cont_b;      /* [16,CD],[16]  graphnet.embed_continuous.0.{weight,bias} */
+    float *cat_w, *cat_b;        /* [16,24],[16]  graphnet.embed_categorical.0.{weight,bias} */
+    float *enc_w, *enc_b;        /* [32,32],[32]  graphnet.encode_all.0.{weight,bias} */
+    GmBatchNorm bn_all;          /*               graphnet.bn_all.* */
+    float *conv_w[GM_MAX_CONV_DEPTH]; /* [32,64]  graphnet.conv_continuous.l.0.nn.0.weight */
+    float *conv_b[GM_MAX_CONV_DEPTH]; /* [32]     graphnet.conv_continuous.l.0.nn.0.bias */
+    GmBatchNorm conv_bn[GM_MAX_CONV_DEPTH]; /*    graphnet.conv_continuous.l.1.* */
+    float *out1_w, *out1_b;      /* [16,32],[16]  graphnet.output.0.{weight,bias} */
+    float *out2_w, *out2_b;      /* [1,16],[1]    graphnet.output.2.{weight,bias} */
+    int continuous_dim;          /* CD (8; 7 for the reference's "remove puppi" variant) */
+    int conv_depth;              /* 2 for model/net.py Net */
+} GmParams;
+
+/* ---------------------------------------------------------------------------------
+ * a1. Input preparation — replaces train.py:42-46 / evaluate.py:83-86
+ *     (phi = atan2(py,px); etaphi = cat[eta, phi]).  etaphi_out [N,2].
+ * --------------------------------------------------------------------------------- */
+int gm_prepare_etaphi(const float *x, int x_stride, int N, float *etaphi_out, void *stream);
+
+/* batch[N] (sorted int64, PyG collation) -> ptr[B+1] int32. Replaces the scatter_add+cumsum
+ * prologue inside torch_cluster.radius (called from train.py:48). */
+int gm_batch_to_ptr(const int64_t *batch, int N, int B, int *ptr_out, void *stream);
+
+/* ---------------------------------------------------------------------------------
+ * a2. Radius graph — replaces torch_cluster.radius_graph(etaphi, r, batch, loop,
+ *     max_num_neighbors) at train.py:48, evaluate.py:88, plt_weight.py:122.
+ *     Cell-binned per-event search; result is bit-identical to the brute force:
+ *     edge (j -> i) iff fmaf(dphi,dphi, deta*deta) < (float)(r*r), same event; per target
+ *     at most max_num_neighbors sources, lowest source indices first; sorted (i, j).
+ *     Two-call protocol: _count fills rowptr (rowptr[N] = E stays on the device; read it
+ *     back, or pass an upper bound as capacity), _fill writes col and, optionally, the
+ *     reference's int64 edge_index[2,E] (row 0 = source, row 1 = target).
+ *     pos: [N, pos_stride] floats with (eta, phi) in columns 0,1 (dim==1: column 0 only).
+ *     stats_out (optional, int[4]): {E, max degree before cap, #capped nodes, flags}.
+ * --------------------------------------------------------------------------------- */
+size_t gm_radius_graph_ws_bytes(int N, int B);
+int gm_radius_graph_count(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B,
+                          double r, int max_num_neighbors, int loop, int phi_wrap,
+                          int max_event_nodes, void *ws, size_t ws_bytes,
+                          int *rowptr_out, int *stats_out, void *stream);
+int gm_radius_graph_fill(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B,
+                         double r, int max_num_neighbors, int loop, int phi_wrap,
+                         int max_event_nodes, void *ws, size_t ws_bytes,
+                         const int *rowptr, int *col_out, long long col_capacity,
+                         int64_t *edge_index64_out /* [2, col_capacity] or NULL */,
+                         int *stats_out, void *stream);
+
+/* Any int64 edge_index[2,E] (e.g. one not produced by this library) -> CSR by target.
+ * Device counting sort, sources ascending per row (stable). Needs ws of gm_csr_ws_bytes. */
+size_t gm_csr_ws_bytes(int N, long long E);
+int gm_edge_index_to_csr(const int64_t *edge_index, long long E, int N, void *ws, size_t ws_bytes,
+                         int *rowptr_out, int *col_out, void *stream);
+
+/* ---------------------------------------------------------------------------------
+ * Whole-network forward — replaces Net.forward / GraphMETNetwork.forward
+ * (model/net.py:45-47, model/graph_met_network.py:47-69) given the CSR graph.
+ *
+ *   x_cont / x_cont_stride : continuous features, row stride in floats (train.py:42 passes the
+ *                            strided view data.x[:, :8], stride 11)
+ *   x_cat_i64              : [N,3] int64 (train.py:44)  — or NULL and
+ *   x_cat_f32 / stride     : the float columns 8..10 of data.x (fused path, no int64 copy)
+ *   training               : 1 = batch statistics + running-stat update (model.train()),
+ *                            0 = running statistics (model.eval())
+ *   save_for_backward      : 1 = also keep the arg-max sources (ws must then be sized with save=1)
+ *   apply_sigmoid          : 1 = Net.forward (model/net.py:47), 0 = GraphMETNetwork.forward
+ *   ws                     : gm_net_ws_bytes(N, depth, save_for_backward) bytes; holds every intermediate the
+ *                            backward needs and must stay untouched until gm_net_backward ran
+ *   out                    : [N]
+ *   err_flags              : int[1], OR-ed with GM_FLAG_* (never cleared by the library)
+ * --------------------------------------------------------------------------------- */
+size_t gm_net_ws_bytes(int N, int conv_depth, int save_for_backward);
+int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride,
+                   const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride,
+                   const int *rowptr, const int *col, int N,
+                   int training, int save_for_backward, int apply_sigmoid, int aggr, int precision,
+                   float momentum, float eps,
+                   void *ws, size_t ws_bytes, float *out, int *err_flags, void *stream);
+
+/* a5 alone — replaces torch_geometric.nn.EdgeConv(nn=Linear(64,32), aggr).forward(x, edge_index)
+ * (model/graph_met_network.py:38,65): out_i = aggr_j W.[x_i ; x_j - x_i] + b over the CSR row of i.
+ * arg_out (optional, [N,32] int32): arg-max source per (target, channel) for aggr = max. */
+int gm_edgeconv_forward(const float *x, const int *rowptr, const int *col, int N, const float *W,
+                        const float *b, int aggr, int precision, float *out, int *arg_out, void *stream);
+
+/* Backward of gm_net_forward (replaces loss.backward() through the model, train.py:51).
+ * grad_out [N] = dL/d out.  Every tensor of `grads` (same layout as GmParams; BN running
+ * buffers ignored) is OVERWRITTEN with the gradient.  Deterministic: no atomics; every
+ * reduction runs in a fixed order.  The forward must have been run with save_for_backward.
+ * (rowptr_t, col_t) is the CSR of the TRANSPOSED graph (by source); for a symmetric graph
+ * (no node hit the max_num_neighbors cap) pass (rowptr, col) again.
+ * Only aggr = max has a backward so far. */
+size_t gm_net_bwd_ws_bytes(int N, int conv_depth);
+int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
+                    const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride,
+                    const int *rowptr, const int *col, const int *rowptr_t, const int *col_t, int N,
+                    int training, int apply_sigmoid, int aggr, float eps,
+                    const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
+                    const float *out, const float *grad_out, void *stream);
+
+/* CSR (by target) -> CSR of the transposed graph (by source), targets ascending per row.
+ * ws: gm_csr_ws_bytes(N, E). Needed by the backward only when GM_FLAG_DEGREE_CAPPED was raised. */
+int gm_csr_transpose(const int *rowptr, const int *col, int N, long long E, void *ws, size_t ws_bytes,
+                     int *rowptr_t_out, int *col_t_out, void *stream);
+
+/* ---------------------------------------------------------------------------------
+ * a7. loss_fn — replaces model/net.py:49-62 (two torch_scatter.scatter_add + mean).
+ *     px = pred[:,0], py = pred[:,1]; MET_e = sum_{n in e} w_n*(px,py);
+ *     loss = 0.5 * mean_e((METx+ty0)^2 + (METy+ty1)^2).  Segmented per-event reduction in a
+ *     fixed order (deterministic).  met_out [B,2]; loss_out [1];
+ *     grad_w_out (optional) [N] = d loss / d w (so loss.backward() needs no second pass).
+ * --------------------------------------------------------------------------------- */
+int gm_met_loss(const float *w, const float *pred, int pred_stride, const float *truth,
+                int truth_stride, const int *ptr, int N, int B, float *met_out, float *loss_out,
+                float *grad_w_out, void *stream);
+
+/* scatter_add(src, index) for a SORTED index given as ptr (model/net.py:55-56, :132-133). */
+int gm_segment_sum(const float *src, const int *ptr, int B, float *out, void *stream);
+/* torch_scatter.scatter_add for an arbitrary int64 index (atomicAdd; out must be pre-zeroed /
+ * pre-filled by the caller). stats_out int64[2] = {max index (-1 if empty), 1 if sorted}. */
+int gm_scatter_add(const float *src, const int64_t *index, long long n, float *out, long long dim_size,
+                   void *stream);
+int gm_index_stats(const int64_t *index, long long n, int64_t *stats_out, void *stream);
+
+/* a8. resolution metric — replaces model/net.py:92-157 on the device: for each of K MET
+ *     flavours (MET = -sum w p first, then truth column pairs (2,3),(4,5),(6,7),(8,9)) writes
+ *     u_perp, u_par, response: out [K,3,B]; qt_out [B]. K = 3 if truth has <= 6 columns else 5. */
+int gm_resolution(const float *met /*[B,2]*/, const float *truth, int truth_stride, int truth_cols,
+                  int B, float *out, float *qt_out, void *stream);
+
+/* ---------------------------------------------------------------------------------
+ * a9. Optimiser — replaces torch.optim.AdamW.step (train.py:52,75): one fused kernel over a
+ *     flat fp32 buffer. grad_scale multiplies the gradient first (1/world_size after a SUM
+ *     allreduce). step is the 1-based step count AFTER this update.
+ * --------------------------------------------------------------------------------- */
+int gm_adamw_step(float *params, const float *grads, float *exp_avg, float *exp_avg_sq, int n,
+                  float lr, float beta1, float beta2, float eps, float weight_decay,
+                  int step, float grad_scale, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRAPHMET_H_ */

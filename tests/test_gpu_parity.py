@@ -1,0 +1,334 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via the reference-shaped Python surface) against
+the oracle restatement and the committed golden fixtures.  Run on the B200 box: pytest -m gpu."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN_CASES, golden_state_dict, load_golden
+from deepmetv2_b200 import ops, synth
+from deepmetv2_b200.model import net as gnet
+from oracle import graphmet_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+# fp32 tolerances from BASELINE.json north_star
+W_RTOL = 1e-4       # per-candidate weights, relative
+MET_RTOL = 1e-3     # per-event MET px/py, relative
+GRAD_RTOL = 1e-3    # gradients, relative to the tensor's max-abs
+
+
+def _rel(a, b, floor=1e-30):
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))
+
+
+def _norm_err(a, b):
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-12))
+
+
+# ----------------------------------------------------------------------------------------------- radius graph
+def _check_graph(etaphi, batch, r=0.4, loop=True, cap=255, wrap=False):
+    want = O.radius_graph(etaphi, r, batch, loop=loop, max_num_neighbors=cap, phi_wrap=wrap)
+    got = ops.radius_graph(etaphi.to(DEV), r, None if batch is None else batch.to(DEV), loop=loop,
+                           max_num_neighbors=cap, phi_wrap=wrap)
+    assert got.dtype == torch.int64 and got.shape[0] == 2
+    assert torch.equal(got.cpu(), want), (got.shape, want.shape)
+    rowptr_w, col_w = O.radius_graph_csr(etaphi, r, batch, loop, cap, wrap)
+    csr = got._gm_csr
+    assert torch.equal(csr.rowptr.cpu().long(), rowptr_w)
+    assert torch.equal(csr.col[:csr.num_edges].cpu().long(), col_w)
+    return got
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_radius_graph_matches_golden(name):
+    g = load_golden(name)
+    ei = ops.radius_graph(torch.from_numpy(g["etaphi"]).to(DEV), 0.4, torch.from_numpy(g["batch"]).to(DEV),
+                          loop=True, max_num_neighbors=255)
+    assert np.array_equal(ei.cpu().numpy(), g["edge_index"].astype(np.int64))
+
+
+@pytest.mark.parametrize("shape,sizes", [("dytt", [300, 0, 1, 420, 2]), ("dytt", None), ("highpu", None), ("tiny", None)])
+@pytest.mark.parametrize("loop", [True, False])
+def test_radius_graph_exact_vs_bruteforce(shape, sizes, loop):
+    n_ev = len(sizes) if sizes else 3
+    b = synth.make_batch(n_ev, shape, seed=21, sizes=sizes)
+    etaphi = O.prepare_inputs(b.x)[2]
+    _check_graph(etaphi, b.batch, loop=loop)
+    _check_graph(etaphi, b.batch, loop=loop, wrap=True)
+
+
+def test_radius_graph_cap_and_duplicates():
+    n = 700
+    pos = torch.zeros(n, 2)
+    pos[:, 0] = torch.linspace(0, 0.05, n)
+    pos[100:140] = pos[100]                       # exact duplicates
+    for cap in (255, 32, 1):
+        for loop in (True, False):
+            ei = _check_graph(pos, None, cap=cap, loop=loop)
+            assert ei._gm_csr.num_capped > 0 and not ei._gm_csr.symmetric
+    # two events, one dense and capped, one sparse
+    batch = torch.cat([torch.zeros(400, dtype=torch.long), torch.ones(300, dtype=torch.long)])
+    pos2 = pos.clone(); pos2[400:, 1] = torch.linspace(-3, 3, 300)
+    _check_graph(pos2, batch, cap=255)
+
+
+def test_radius_graph_phi_boundary_and_single_event():
+    pos = torch.tensor([[0.0, 0.0], [0.4, 0.0], [0.39999, 0.0], [0.0, 3.1], [0.0, -3.1], [5.0, 3.14], [5.0, -3.14]])
+    ei = _check_graph(pos, None)
+    pairs = set(map(tuple, ei.cpu().t().tolist()))
+    assert (3, 4) not in pairs and (2, 0) in pairs and (1, 0) not in pairs
+    eiw = _check_graph(pos, None, wrap=True)
+    assert (3, 4) in set(map(tuple, eiw.cpu().t().tolist()))
+    _check_graph(torch.zeros(0, 2), None)
+    _check_graph(torch.randn(1, 2), None)
+    _check_graph(torch.randn(1000, 2) * 0.2, None, r=0.05)          # r much smaller than extent
+    _check_graph(torch.randn(500, 2) * 0.01, None, r=0.4)           # everything in one cell
+
+
+def test_edge_index_to_csr_roundtrip():
+    b = synth.make_batch(2, "dytt", seed=4, sizes=[250, 300])
+    ei = O.radius_graph(O.prepare_inputs(b.x)[2], 0.4, b.batch, loop=True, max_num_neighbors=255)
+    perm = torch.randperm(ei.shape[1], generator=torch.Generator().manual_seed(0))
+    csr = ops.csr_from_edge_index(ei[:, perm].contiguous().to(DEV), b.x.shape[0])
+    rowptr, col = O.radius_graph_csr(O.prepare_inputs(b.x)[2], 0.4, b.batch, True, 255)
+    assert torch.equal(csr.rowptr.cpu().long(), rowptr) and torch.equal(csr.col.cpu().long()[:col.numel()], col)
+    rt, ct = csr.transposed()       # symmetric graph: transposed == itself
+    assert torch.equal(rt.cpu().long(), rowptr) and torch.equal(ct.cpu().long()[:col.numel()], col)
+
+
+def test_prepare_inputs_and_batch_to_ptr():
+    b = synth.make_batch(4, "dytt", seed=8, sizes=[100, 0, 50, 7])
+    x = b.x.to(DEV)
+    x_cont, x_cat, etaphi = ops.prepare_inputs(x)
+    ref = O.prepare_inputs(b.x)[2]
+    assert torch.equal(etaphi[:, 0].cpu(), ref[:, 0])
+    assert torch.allclose(etaphi[:, 1].cpu(), ref[:, 1], atol=5e-7, rtol=0)
+    assert torch.equal(ops.batch_to_ptr(b.batch.to(DEV), 4).cpu(), b.ptr)
+    assert torch.equal(ops.batch_to_ptr(b.batch.to(DEV), 6).cpu()[-2:], torch.tensor([157, 157], dtype=torch.int32))
+
+
+# ----------------------------------------------------------------------------------------------- model
+def _models(g):
+    sd = golden_state_dict(g)
+    ours = gnet.Net(8, 3)
+    ours.load_state_dict(sd, strict=True)
+    ref = O.Net(8, 3)
+    ref.load_state_dict(sd, strict=True)
+    return ours.to(DEV), ref
+
+
+def _gpu_inputs(g):
+    x = torch.from_numpy(g["x"]).to(DEV)
+    y = torch.from_numpy(g["y"]).to(DEV)
+    b = torch.from_numpy(g["batch"]).to(DEV)
+    return x, y, b
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_eval_forward_matches_reference_fixture(name):
+    """evaluate.py:83-103 through our drop-in surface vs the reference's own outputs."""
+    g = load_golden(name)
+    ours, _ = _models(g)
+    ours.eval()
+    x, y, b = _gpu_inputs(g)
+    x_cont = x[:, :8]
+    x_cat = x[:, 8:].long()
+    etaphi = torch.from_numpy(g["etaphi"]).to(DEV)
+    edge_index = ops.radius_graph(etaphi, r=0.4, batch=b, loop=True, max_num_neighbors=255)
+    w = ours(x_cont, x_cat, edge_index, b)
+    assert w.shape == (x.shape[0],)
+    assert _rel(w.cpu().numpy(), g["eval_weights"]) < W_RTOL
+    loss = gnet.loss_fn(w, x, y, b)
+    assert loss.dim() == 0
+    assert abs(loss.item() - float(g["eval_loss"])) <= MET_RTOL * abs(float(g["eval_loss"]))
+    res, qT = gnet.metrics["resolution"](w, x, y, b)
+    assert isinstance(qT, np.ndarray) and np.allclose(qT, g["eval_qT"], rtol=1e-5)
+    for k in res:
+        for i, nm in enumerate(("u_perp", "u_par", "R")):
+            want = g[f"eval_res::{k}::{nm}"]
+            assert np.allclose(res[k][i], want, rtol=2e-3, atol=2e-3 * np.abs(want).max()), (k, nm)
+    upl = gnet.u_perp_par_loss(w, x, y, b)
+    assert abs(upl.item() - float(g["eval_u_perp_par_loss"])) <= 2e-3 * abs(float(g["eval_u_perp_par_loss"]))
+    # per-event MET px/py within 1e-3 relative of the oracle's (scaled by the event's |MET|)
+    met = gnet.met_from_weights(w, x, b, y.shape[0]).cpu().numpy()
+    bw = torch.from_numpy(g["batch"])
+    wref = torch.from_numpy(g["eval_weights"]); xr = torch.from_numpy(g["x"])
+    met_ref = torch.stack((O.scatter_add(wref * xr[:, 0], bw), O.scatter_add(wref * xr[:, 1], bw)), 1).numpy()
+    scale = np.linalg.norm(met_ref, axis=1, keepdims=True)
+    assert np.max(np.abs(met - met_ref) / scale) < MET_RTOL
+    # fused float-categorical path (no int64 copy) gives the same result bit-for-bit
+    w2 = ours(x_cont, x[:, 8:11], edge_index, b)
+    assert torch.equal(w, w2)
+    # a foreign (non-annotated) edge_index goes through the device CSR sort and gives the same result
+    w3 = ours(x_cont, x_cat, edge_index.clone(), b)
+    assert torch.equal(w, w3)
+
+
+@pytest.mark.parametrize("name", [c for c in GOLDEN_CASES if not c.startswith("c1")])
+def test_train_step_gradients_match_reference_fixture(name):
+    """train.py:35,49-51 — forward in train mode, loss, backward: all 23 gradients + BN running stats."""
+    g = load_golden(name)
+    ours, _ = _models(g)
+    ours.train()
+    x, y, b = _gpu_inputs(g)
+    edge_index = ops.radius_graph(torch.from_numpy(g["etaphi"]).to(DEV), r=0.4, batch=b, loop=True,
+                                  max_num_neighbors=255)
+    w = ours(x[:, :8], x[:, 8:].long(), edge_index, b)
+    loss = gnet.loss_fn(w, x, y, b)
+    loss.backward()
+    assert _rel(w.detach().cpu().numpy(), g["train_weights"]) < W_RTOL
+    assert abs(loss.item() - float(g["train_loss"])) <= MET_RTOL * abs(float(g["train_loss"]))
+    for k, p in ours.named_parameters():
+        want = g["grad::" + k]
+        assert p.grad is not None, k
+        assert _norm_err(p.grad.cpu().numpy(), want) < GRAD_RTOL, (k, _norm_err(p.grad.cpu().numpy(), want))
+    for k, v in ours.state_dict().items():
+        if "running" in k:
+            assert np.allclose(v.cpu().numpy(), g["sd_after::" + k], rtol=1e-5, atol=1e-6), k
+        if "num_batches" in k:
+            assert int(v) == int(g["sd_after::" + k]), k
+
+
+def test_run_to_run_determinism_and_event_permutation():
+    g = load_golden("small_init")
+    ours, _ = _models(g)
+    x, y, b = _gpu_inputs(g)
+    etaphi = torch.from_numpy(g["etaphi"]).to(DEV)
+    grads = []
+    for _ in range(3):
+        ours.train(); ours.zero_grad()
+        ei = ops.radius_graph(etaphi, 0.4, b, loop=True, max_num_neighbors=255)
+        w = ours(x[:, :8], x[:, 8:].long(), ei, b)
+        gnet.loss_fn(w, x, y, b).backward()
+        grads.append(torch.cat([p.grad.flatten() for p in ours.parameters()] + [w.detach()]).clone())
+    assert torch.equal(grads[0], grads[1]) and torch.equal(grads[0], grads[2])
+    # eval mode: permuting the events of a batch permutes the outputs
+    ours.eval()
+    ptr = g["ptr"]
+    order = [2, 0, 1]
+    idx = torch.cat([torch.arange(ptr[e], ptr[e + 1]) for e in order]).to(DEV)
+    xb = x[idx]
+    bb = torch.repeat_interleave(torch.arange(3), torch.tensor([int(ptr[e + 1] - ptr[e]) for e in order])).to(DEV)
+    with torch.no_grad():
+        w_a = ours(x[:, :8], x[:, 8:].long(), ops.radius_graph(etaphi, 0.4, b, True, 255), b)
+        w_b = ours(xb[:, :8], xb[:, 8:].long(), ops.radius_graph(etaphi[idx], 0.4, bb, True, 255), bb)
+    assert torch.allclose(w_a[idx], w_b, rtol=1e-5, atol=1e-7)
+
+
+def test_capped_graph_backward_uses_transposed_csr():
+    """Degree cap breaks symmetry: gradients must still match oracle autograd."""
+    torch.manual_seed(3)
+    b = synth.make_batch(2, "dytt", seed=31, sizes=[260, 240])
+    x = b.x.clone()
+    x[:, 3] *= 0.05                                    # squeeze eta: dense neighbourhoods
+    etaphi = O.prepare_inputs(x)[2]
+    ei_ref = O.radius_graph(etaphi, 0.4, b.batch, loop=True, max_num_neighbors=16)
+    ref = O.Net(8, 3); ours = gnet.Net(8, 3); ours.load_state_dict(ref.state_dict()); ours.to(DEV)
+    ref.train(); ours.train()
+    w_ref = ref(*O.prepare_inputs(x)[:2], ei_ref, b.batch)
+    O.loss_fn(w_ref, x, b.y, b.batch).backward()
+    xg, yg, bg = x.to(DEV), b.y.to(DEV), b.batch.to(DEV)
+    ei = ops.radius_graph(etaphi.to(DEV), 0.4, bg, loop=True, max_num_neighbors=16)
+    assert not ei._gm_csr.symmetric and torch.equal(ei.cpu(), ei_ref)
+    w = ours(xg[:, :8], xg[:, 8:].long(), ei, bg)
+    gnet.loss_fn(w, xg, yg, bg).backward()
+    assert _rel(w.detach().cpu().numpy(), w_ref.detach().numpy()) < W_RTOL
+    for (k, p), (_, q) in zip(ours.named_parameters(), ref.named_parameters()):
+        assert _norm_err(p.grad.cpu().numpy(), q.grad.numpy()) < GRAD_RTOL, k
+
+
+def test_c2_sized_batch_properties():
+    """BASELINE configs[1] size (32 DY/TT events): oracle forward parity + size-independent properties."""
+    b = synth.make_batch(32, "dytt", seed=1002)
+    g = b.to(DEV)
+    x_cont, x_cat, etaphi = ops.prepare_inputs(g.x)
+    graph, ei = ops.build_graph(etaphi, 0.4, ptr_i32=g.ptr, loop=True, max_num_neighbors=255, want_edge_index=True)
+    # sortedness / self loops / in-event / symmetry
+    key = ei[1] * g.x.shape[0] + ei[0]
+    assert bool((key[1:] > key[:-1]).all())
+    assert int((ei[0] == ei[1]).sum()) == g.x.shape[0]
+    assert torch.equal(g.batch[ei[0]], g.batch[ei[1]])
+    rev = torch.sort(ei[0] * g.x.shape[0] + ei[1]).values
+    assert torch.equal(rev, key)
+    want = O.radius_graph(etaphi.cpu(), 0.4, b.batch, loop=True, max_num_neighbors=255)
+    assert torch.equal(ei.cpu(), want)
+    torch.manual_seed(0)
+    ref = O.Net(8, 3); ours = gnet.Net(8, 3); ours.load_state_dict(ref.state_dict()); ours.to(DEV)
+    ref.eval(); ours.eval()
+    with torch.no_grad():
+        w = ours(x_cont, x_cat, graph, g.batch)
+        w_ref = ref(*O.prepare_inputs(b.x)[:2], want, b.batch)
+    assert _rel(w.cpu().numpy(), w_ref.numpy()) < W_RTOL
+    assert abs(gnet.loss_fn(w, g.x, g.y, g.batch).item() - O.loss_fn(w_ref, b.x, b.y, b.batch).item()) < \
+        MET_RTOL * O.loss_fn(w_ref, b.x, b.y, b.batch).item()
+
+
+def test_edgeconv_standalone_aggregations():
+    b = synth.make_batch(2, "dytt", seed=5, sizes=[200, 180])
+    ei = O.radius_graph(O.prepare_inputs(b.x)[2], 0.4, b.batch, loop=True, max_num_neighbors=255)
+    torch.manual_seed(1)
+    x = torch.randn(380, 32)
+    from deepmetv2_b200.model.graph_met_network import EdgeConv
+    for aggr in ("max", "add", "mean"):
+        lin = torch.nn.Sequential(torch.nn.Linear(64, 32))
+        want = O.EdgeConv(lin, aggr)(x, ei).detach()
+        conv = EdgeConv(torch.nn.Sequential(torch.nn.Linear(64, 32)), aggr).to(DEV)
+        conv.nn.load_state_dict(lin.state_dict())
+        with torch.no_grad():
+            got = conv(x.to(DEV), ei.to(DEV)).cpu()
+        assert torch.allclose(got, want, rtol=1e-4, atol=2e-5), aggr
+
+
+def test_scatter_add_and_loss_fn_gradient():
+    src = torch.randn(1000, device=DEV)
+    idx_sorted = torch.sort(torch.randint(0, 7, (1000,), device=DEV)).values
+    want = torch.zeros(int(idx_sorted.max()) + 1, device=DEV).scatter_add_(0, idx_sorted, src)
+    assert torch.allclose(ops.scatter_add(src, idx_sorted), want, rtol=1e-5, atol=1e-5)
+    idx = torch.randint(0, 9, (1000,), device=DEV)
+    want = torch.zeros(12, device=DEV).scatter_add_(0, idx, src)
+    assert torch.allclose(ops.scatter_add(src, idx, dim_size=12), want, rtol=1e-5, atol=1e-5)
+    # loss_fn gradient vs oracle autograd
+    b = synth.make_batch(3, "tiny", seed=2)
+    w = torch.rand(b.x.shape[0], requires_grad=True)
+    O.loss_fn(w, b.x, b.y, b.batch).backward()
+    wg = w.detach().to(DEV).requires_grad_(True)
+    loss = gnet.loss_fn(wg, b.x.to(DEV), b.y.to(DEV), b.batch.to(DEV))
+    loss.backward()
+    assert torch.allclose(wg.grad.cpu(), w.grad, rtol=1e-5, atol=1e-6)
+
+
+def test_adamw_matches_torch():
+    from deepmetv2_b200._lib import check, lib, ptr, stream
+    torch.manual_seed(0)
+    p = torch.randn(6641, device=DEV); p_ref = p.clone().requires_grad_(True)
+    opt = torch.optim.AdamW([p_ref], lr=1e-3)
+    m = torch.zeros_like(p); v = torch.zeros_like(p)
+    for step in range(1, 4):
+        gr = torch.randn(6641, device=DEV)
+        p_ref.grad = gr.clone()
+        opt.step()
+        check(lib().gm_adamw_step(ptr(p), ptr(gr), ptr(m), ptr(v), 6641, 1e-3, 0.9, 0.999, 1e-8, 0.01, step, 1.0,
+                                  stream()))
+    assert torch.allclose(p, p_ref.detach(), rtol=1e-5, atol=1e-7)
+
+
+def test_out_of_range_category_raises_indexerror():
+    g = load_golden("tiny_init")
+    ours, _ = _models(g)
+    ours.eval()
+    x, y, b = _gpu_inputs(g)
+    x = x.clone(); x[0, 10] = 9.0                       # fromPV outside its 8-row table
+    ei = ops.radius_graph(torch.from_numpy(g["etaphi"]).to(DEV), 0.4, b, True, 255)
+    ours(x[:, :8], x[:, 8:].long(), ei, b)
+    with pytest.raises(IndexError):
+        ours.graphnet.check_errors()
+
+
+def test_cpu_tensors_fail_loudly():
+    m = gnet.Net(8, 3)
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(4, 8), torch.zeros(4, 3, dtype=torch.long), torch.zeros(2, 0, dtype=torch.long),
+          torch.zeros(4, dtype=torch.long))
