@@ -83,6 +83,8 @@ def radius_graph_csr(x, r, batch=None, loop=False, max_num_neighbors=32, phi_wra
         assert bool((b[1:] >= b[:-1]).all()), "batch must be sorted"
         ptr = batch_to_ptr(b)
     B = ptr.numel() - 1
+    if N == 0:
+        return torch.zeros(1, dtype=torch.int64), torch.empty(0, dtype=torch.int64)
     lib = _radius_lib()
     rowptr = torch.zeros(N + 1, dtype=torch.int64)
     E = lib.oracle_radius_graph(pos.data_ptr(), dim, ptr.data_ptr(), B, float(r),

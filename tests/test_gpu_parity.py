@@ -23,9 +23,26 @@ def _rel(a, b, floor=1e-30):
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))
 
 
-def _norm_err(a, b):
+def _norm_err(a, b, floor=1e-12):
     a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
-    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-12))
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), floor))
+
+
+def _check_grads(named_ours, ref_grads):
+    """Every gradient within GRAD_RTOL of its tensor's max-abs.  An EdgeConv bias feeds a train-mode
+    BatchNorm, so its true gradient is identically 0 and both sides hold rounding noise: it is compared
+    on the scale of the same layer's weight gradient instead."""
+    worst = {}
+    for k, p in named_ours:
+        want = ref_grads[k]
+        floor = 1e-12
+        if k.endswith("nn.0.bias"):
+            floor = float(np.max(np.abs(ref_grads[k.replace("nn.0.bias", "nn.0.weight")])))
+        assert p.grad is not None, k
+        worst[k] = _norm_err(p.grad.cpu().numpy(), want, floor)
+    bad = {k: v for k, v in worst.items() if not v < GRAD_RTOL}
+    assert not bad, bad
+    return worst
 
 
 # ----------------------------------------------------------------------------------------------- radius graph
@@ -138,9 +155,9 @@ def test_eval_forward_matches_reference_fixture(name):
     x_cat = x[:, 8:].long()
     etaphi = torch.from_numpy(g["etaphi"]).to(DEV)
     edge_index = ops.radius_graph(etaphi, r=0.4, batch=b, loop=True, max_num_neighbors=255)
-    w = ours(x_cont, x_cat, edge_index, b)
-    assert w.shape == (x.shape[0],)
-    assert _rel(w.cpu().numpy(), g["eval_weights"]) < W_RTOL
+    w = ours(x_cont, x_cat, edge_index, b)        # autograd stays enabled, as in evaluate.py:71-100
+    assert w.shape == (x.shape[0],) and w.requires_grad
+    assert _rel(w.detach().cpu().numpy(), g["eval_weights"]) < W_RTOL
     loss = gnet.loss_fn(w, x, y, b)
     assert loss.dim() == 0
     assert abs(loss.item() - float(g["eval_loss"])) <= MET_RTOL * abs(float(g["eval_loss"]))
@@ -154,6 +171,7 @@ def test_eval_forward_matches_reference_fixture(name):
     assert abs(upl.item() - float(g["eval_u_perp_par_loss"])) <= 2e-3 * abs(float(g["eval_u_perp_par_loss"]))
     # per-event MET px/py within 1e-3 relative of the oracle's (scaled by the event's |MET|)
     met = gnet.met_from_weights(w, x, b, y.shape[0]).cpu().numpy()
+    w = w.detach()
     bw = torch.from_numpy(g["batch"])
     wref = torch.from_numpy(g["eval_weights"]); xr = torch.from_numpy(g["x"])
     met_ref = torch.stack((O.scatter_add(wref * xr[:, 0], bw), O.scatter_add(wref * xr[:, 1], bw)), 1).numpy()
@@ -181,10 +199,7 @@ def test_train_step_gradients_match_reference_fixture(name):
     loss.backward()
     assert _rel(w.detach().cpu().numpy(), g["train_weights"]) < W_RTOL
     assert abs(loss.item() - float(g["train_loss"])) <= MET_RTOL * abs(float(g["train_loss"]))
-    for k, p in ours.named_parameters():
-        want = g["grad::" + k]
-        assert p.grad is not None, k
-        assert _norm_err(p.grad.cpu().numpy(), want) < GRAD_RTOL, (k, _norm_err(p.grad.cpu().numpy(), want))
+    _check_grads(ours.named_parameters(), {k: g["grad::" + k] for k, _ in ours.named_parameters()})
     for k, v in ours.state_dict().items():
         if "running" in k:
             assert np.allclose(v.cpu().numpy(), g["sd_after::" + k], rtol=1e-5, atol=1e-6), k
@@ -236,8 +251,7 @@ def test_capped_graph_backward_uses_transposed_csr():
     w = ours(xg[:, :8], xg[:, 8:].long(), ei, bg)
     gnet.loss_fn(w, xg, yg, bg).backward()
     assert _rel(w.detach().cpu().numpy(), w_ref.detach().numpy()) < W_RTOL
-    for (k, p), (_, q) in zip(ours.named_parameters(), ref.named_parameters()):
-        assert _norm_err(p.grad.cpu().numpy(), q.grad.numpy()) < GRAD_RTOL, k
+    _check_grads(ours.named_parameters(), {k: q.grad.numpy() for k, q in ref.named_parameters()})
 
 
 def test_c2_sized_batch_properties():
