@@ -1,0 +1,359 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the GraphMETNetwork hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c5]
+
+A "step" is one pass of the hot path over one batch of synthetic events:
+  c2 (default, BASELINE.json configs[1]): TRAINING step (radius graph + forward + loss + backward +
+      AdamW) on 32 DY/TT-shaped events (~1.7k PF candidates each), fp32.
+  c3: high-pile-up INFERENCE (graph + forward + MET/loss) on 256 events of ~5k candidates.
+  c5: training on 32 high-pile-up events per GPU (the data-parallel config).
+Multi-GPU: one process per GPU (torchrun), events sharded by rank (weak scaling: every rank gets its own
+batch of the same shape), the only collective is the NCCL all-reduce of the 26.6 KB flat gradient.
+Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+WORKLOADS = {
+    #        events/GPU, shape,    mode,    human name
+    "c2": (32, "dytt", "train", "GraphMETNetwork training step, batch 32 synthetic DY/TT events (~1.7k cands), fp32"),
+    "c3": (256, "highpu", "eval", "GraphMETNetwork inference, batch 256 high-pile-up events (~5k cands), r=0.4"),
+    "c5": (32, "highpu", "train", "GraphMETNetwork training step, 32 high-pile-up events (~5k cands) per GPU"),
+}
+N_ROTATE = 4   # distinct pre-generated batches cycled through the steps
+
+
+def _peaks():
+    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"hbm_gbs": float(p["hbm_gbs"]), "bf16_tflops": float(p["bf16_tflops"]),
+                "bf16_tflops_sustained": float(p.get("bf16_tflops_sustained", p["bf16_tflops"])),
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0,
+            "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [s.strip() for s in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_batches(workload: str, rank: int):
+    from deepmetv2_b200 import synth
+    n_ev, shape, _, _ = WORKLOADS[workload]
+    cfg = int(workload[1:])
+    return [synth.make_batch(n_ev, shape, seed=1000 * cfg + 100 * rank + i) for i in range(N_ROTATE)]
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def cpu_train_or_eval_step(model, opt, batch, mode):
+    """The reference path on host cores: train.py:40-55 / evaluate.py:81-100 restated (oracle)."""
+    from oracle import graphmet_oracle as O
+    x_cont, x_cat, etaphi = O.prepare_inputs(batch.x)
+    ei = O.radius_graph(etaphi, r=0.4, batch=batch.batch, loop=True, max_num_neighbors=255)
+    if mode == "train":
+        opt.zero_grad()
+        w = model(x_cont, x_cat, ei, batch.batch)
+        loss = O.loss_fn(w, batch.x, batch.y, batch.batch)
+        loss.backward()
+        opt.step()
+    else:
+        w = model(x_cont, x_cat, ei, batch.batch)       # evaluate.py keeps autograd enabled
+        loss = O.loss_fn(w, batch.x, batch.y, batch.batch)
+    return float(loss.item()), ei.shape[1]
+
+
+def cpu_sample(batch, workload):
+    """Bounded sample of the workload for the CPU arm: whole batch for c2, 8 events for the 5k-cand ones."""
+    from deepmetv2_b200.synth import EventBatch
+    n_ev = {"c2": 32, "c3": 8, "c5": 8}[workload]
+    n_ev = min(n_ev, batch.num_graphs)
+    n = int(batch.ptr[n_ev])
+    return EventBatch(batch.x[:n], batch.y[:n_ev], batch.batch[:n], batch.ptr[:n_ev + 1]), n_ev
+
+
+def run_cpu_arm(workload, steps, warmup):
+    from oracle import graphmet_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    torch.manual_seed(0)
+    _, _, mode, _ = WORKLOADS[workload]
+    model = O.Net(8, 3)
+    model.train() if mode == "train" else model.eval()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3)
+    samples = [cpu_sample(b, workload) for b in make_batches(workload, 0)]
+    for i in range(warmup):
+        cpu_train_or_eval_step(model, opt, samples[i % N_ROTATE][0], mode)
+    t0 = time.perf_counter()
+    ev = 0
+    for i in range(steps):
+        s, n_ev = samples[i % N_ROTATE]
+        cpu_train_or_eval_step(model, opt, s, mode)
+        ev += n_ev
+    dt = time.perf_counter() - t0
+    return ev / dt, dt / max(steps, 1) * 1e3, samples[0][1], torch.get_num_threads()
+
+
+# ------------------------------------------------------------------------------------------------ main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "bf16", "tf32x3"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    n_ev, shape, mode, human = WORKLOADS[args.workload]
+    metric = "training events/sec" if mode == "train" else "inference events/sec"
+
+    if args.impl == "reference":
+        # The reference's genuine PyG/torch_cluster implementation is unavailable on this box (packages
+        # absent); this arm times the oracle restatement of its CPU path on the host cores (kind "port").
+        if rank != 0:
+            return
+        value, ms, n_s, threads = run_cpu_arm(args.workload, args.steps, args.warmup)
+        sample = f"{n_s} of {n_ev} events of the {args.workload} batch per step"
+        print(json.dumps({
+            "impl": "reference", "metric": metric, "value": value, "unit": "events/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": human, "events_per_step": n_s},
+            "cpu_baseline": {"value": value, "unit": "events/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "events/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }))
+        return
+
+    from deepmetv2_b200 import _lib
+    from deepmetv2_b200.model import net as gnet
+    from deepmetv2_b200.trainer import GraphMETTrainer
+
+    assert torch.cuda.is_available(), "bench.py --impl ours needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    pg = None
+    if world > 1:
+        torch.distributed.init_process_group("nccl", device_id=dev)
+        pg = torch.distributed.group.WORLD
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    l = _lib.lib()
+    torch.manual_seed(0)
+    model = gnet.Net(8, 3).to(dev)
+    model.graphnet.edge_precision = args.precision
+    trainer = GraphMETTrainer(model, lr=1e-3, process_group=pg)
+    host = [b.pin_memory() for b in make_batches(args.workload, rank)]
+    devb = [b.to(dev) for b in host]
+    men = [int((b.ptr[1:] - b.ptr[:-1]).max()) for b in host]
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def one_step(i):
+        k = i % N_ROTATE
+        if mode == "train":
+            return trainer.train_step(devb[k], men[k])
+        return trainer.eval_step(devb[k], men[k])[1]
+
+    def one_step_e2e(i):
+        k = i % N_ROTATE
+        if mode == "train":
+            return trainer.train_step_from_host(host[k], men[k])
+        x = host[k].x.to(dev, non_blocking=True); y = host[k].y.to(dev, non_blocking=True)
+        p = host[k].ptr.to(dev, non_blocking=True)
+        from deepmetv2_b200.synth import EventBatch
+        _, loss, _ = trainer.eval_step(EventBatch(x, y, None, p), men[k])
+        return float(loss.item())
+
+    # ---------------- device-resident arm (value) ----------------
+    for i in range(args.warmup):
+        one_step(i)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l.gm_timing_enable(1)
+    for s in range(8):                   # clear the timer slots
+        t_ms, t_n = ctypes.c_float(), ctypes.c_int()
+        l.gm_timing_read(s, ctypes.byref(t_ms), ctypes.byref(t_n))
+    l.gm_launch_count(1)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.zero_()                    # L2 flush between timed iterations (outside the event pair)
+        ev[i][0].record()
+        one_step(i)
+        ev[i][1].record()
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = l.gm_launch_count(0)
+    l.gm_timing_enable(0)
+    total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    total_ms = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+    value = n_ev * world * args.steps / (total_ms / 1e3)
+
+    timers = {}
+    for name, slot in _lib.TIMERS.items():
+        t_ms, t_n = ctypes.c_float(), ctypes.c_int()
+        l.gm_timing_read(slot, ctypes.byref(t_ms), ctypes.byref(t_n))
+        if t_n.value:
+            timers[name] = (t_ms.value, t_n.value)
+
+    # graph statistics of the rotating batches (for the algorithmic flops / bytes)
+    Es, Ns = [], []
+    for k in range(N_ROTATE):
+        one_step(k)
+        st = trainer.graph_stats()
+        Es.append(st[0]); Ns.append(devb[k].x.shape[0])
+    E_avg, N_avg = sum(Es) / len(Es), sum(Ns) / len(Ns)
+    max_deg, capped = st[1], st[2]
+
+    # ---------------- end-to-end arm (host buffers, H2D + D2H inside the timed region) ----------------
+    for i in range(3):
+        one_step_e2e(i)
+    barrier()
+    e2e_t = 0.0
+    for i in range(args.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        one_step_e2e(i)                  # ends with the loss on the host (stream sync inside)
+        e2e_t += time.perf_counter() - t0
+    t = torch.tensor([e2e_t], dtype=torch.float64, device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    e2e_value = n_ev * world * args.steps / float(t.item())
+    h2d = int(sum(b.x.numel() * 4 + b.y.numel() * 4 + b.ptr.numel() * 4 for b in host) / len(host))
+
+    if rank != 0:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+        return
+
+    peaks = _peaks()
+    # dominant kernel: the per-edge contraction of EdgeConv (4096 flop per edge per layer)
+    ec_ms, ec_n = timers.get("edgeconv_fwd", (0.0, 0))
+    roofline = None
+    if ec_n:
+        dur = ec_ms / ec_n * 1e-3
+        achieved = 4096.0 * E_avg / dur / 1e12
+        peak = peaks["bf16_tflops_sustained"]
+        roofline = {"kernel": "edgeconv_fwd (" + args.precision + ")", "bound": "tensor", "achieved": achieved,
+                    "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                    "avg_launch_us": dur * 1e6, "launches_timed": ec_n,
+                    "algorithmic_flops_per_launch": 4096.0 * E_avg, "peak_source": peaks["source"],
+                    "gather_GBps_L2": E_avg * 128.0 / dur / 1e9}
+    # algorithmic HBM bytes per kernel family per launch (DESIGN.md "kernels")
+    alg_bytes = {"radius_graph": 12 * N_avg + 4 * E_avg, "encode_fwd": 172 * N_avg, "head_fwd": 132 * N_avg,
+                 "scatter_s_bwd": 260 * N_avg + 4 * E_avg, "conv_node_bwd": 640 * N_avg, "encode_bwd": 300 * N_avg}
+    kernels = {}
+    for name, (ms, n) in timers.items():
+        d = {"avg_us": ms / n * 1e3, "regions": n, "share_of_step": ms / total_ms}
+        if name in alg_bytes:
+            d["hbm_GBps"] = alg_bytes[name] / (ms / n * 1e-3) / 1e9
+            d["hbm_frac"] = d["hbm_GBps"] / peaks["hbm_gbs"]
+        kernels[name] = d
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        v, ms, n_s, threads = run_cpu_arm(args.workload, 2, 1)
+        cpu = {"value": v, "unit": "events/s", "cores": threads, "kind": "port",
+               "sample": f"2 steps of {n_s} of the {n_ev} events of the {args.workload} batch "
+                         f"(oracle restatement of the PyG CPU path; genuine PyG unavailable on this box)",
+               "ms_per_step": ms}
+
+    out = {
+        "metric": metric, "value": value, "unit": "events/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else args.precision, "data": "synthetic",
+        "config": {"workload": human, "events_per_gpu": n_ev, "nodes_per_step": N_avg, "edges_per_step": E_avg,
+                   "max_degree": max_deg, "capped_nodes": capped, "edge_precision": args.precision,
+                   "l2": "flushed between timed iterations (256 MiB memset)", "rotating_batches": N_ROTATE,
+                   "parallelism": f"dp{world}" if world > 1 else "single"},
+        "edges_per_sec": E_avg * world * args.steps / (total_ms / 1e3),
+        "wall_ms_per_step_incl_flush": wall / args.steps * 1e3,
+        "gpu_launches": int(launches), "gpu_launches_per_step": launches / args.steps,
+        "clocks": clocks, "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu,
+        "e2e": {"value": e2e_value, "unit": "events/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                "api": "GraphMETTrainer.train_step_from_host" if mode == "train" else "GraphMETTrainer.eval_step",
+                "timing": "host wall clock per step (includes H2D, all kernels, loss D2H, stream sync)"},
+    }
+    print(json.dumps(out))
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -25,6 +25,8 @@ FLAG_EVENT_TOO_LARGE = 8
 MAX_CONV_DEPTH = 4
 AGGR = {"max": 0, "add": 1, "mean": 2}
 PRECISION = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3}
+TIMERS = {"radius_graph": 0, "encode_fwd": 1, "edgeconv_fwd": 2, "head_fwd": 3, "scatter_s_bwd": 4,
+          "conv_node_bwd": 5, "encode_bwd": 6, "bn": 7}
 
 _vp, _i, _ll, _f, _d, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double, C.c_size_t
 
@@ -50,6 +52,9 @@ SIGNATURES = {
     "gm_status_string": (C.c_char_p, [_i]),
     "gm_last_cuda_error": (_i, []),
     "gm_num_sms": (_i, []),
+    "gm_launch_count": (_ll, [_i]),
+    "gm_timing_enable": (_i, [_i]),
+    "gm_timing_read": (_i, [_i, _vp, _vp]),
     "gm_prepare_etaphi": (_i, [_vp, _i, _i, _vp, _vp]),
     "gm_batch_to_ptr": (_i, [_vp, _i, _i, _vp, _vp]),
     "gm_radius_graph_ws_bytes": (_sz, [_i, _i]),
@@ -58,13 +63,13 @@ SIGNATURES = {
                                   _vp, _vp]),
     "gm_csr_ws_bytes": (_sz, [_i, _ll]),
     "gm_edge_index_to_csr": (_i, [_vp, _ll, _i, _vp, _sz, _vp, _vp, _vp]),
-    "gm_csr_transpose": (_i, [_vp, _vp, _i, _ll, _vp, _sz, _vp, _vp, _vp]),
+    "gm_csr_transpose": (_i, [_vp, _vp, _i, _ll, _vp, _sz, _vp, _vp, _vp, _vp]),
     "gm_edgeconv_forward": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "gm_net_ws_bytes": (_sz, [_i, _i, _i]),
     "gm_net_forward": (_i, [C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f,
                             _vp, _sz, _vp, _vp, _vp]),
     "gm_net_bwd_ws_bytes": (_sz, [_i, _i]),
-    "gm_net_backward": (_i, [C.POINTER(GmParams), C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp,
+    "gm_net_backward": (_i, [C.POINTER(GmParams), C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp,
                              _i, _i, _i, _i, _f, _vp, _sz, _vp, _sz, _vp, _vp, _vp]),
     "gm_met_loss": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "gm_segment_sum": (_i, [_vp, _vp, _i, _vp, _vp]),

@@ -11,6 +11,7 @@ constexpr int H = GM_HIDDEN;       // hidden_dim of model/net.py:41-43
 constexpr int WARP = 32;
 
 extern int g_last_cuda_error;
+extern long long g_launch_count;      // kernels launched by this library (gm_launch_count)
 
 inline int cuda_fail(cudaError_t e) {
     g_last_cuda_error = (int)e;
@@ -23,7 +24,11 @@ inline int cuda_fail(cudaError_t e) {
         if (_e != cudaSuccess) return ::gm::cuda_fail(_e);  \
     } while (0)
 
-#define GM_LAUNCH_CHECK() GM_CUDA_TRY(cudaGetLastError())
+#define GM_LAUNCH_CHECK()                  \
+    do {                                   \
+        ++::gm::g_launch_count;            \
+        GM_CUDA_TRY(cudaGetLastError());   \
+    } while (0)
 
 #define GM_TRY(expr)                 \
     do {                             \
@@ -32,6 +37,15 @@ inline int cuda_fail(cudaError_t e) {
     } while (0)
 
 int num_sms();
+
+// Optional per-kernel-family CUDA-event timing on the launching stream (gm_timing_enable / gm_timing_read).
+struct TimedRegion {
+    int slot;
+    cudaStream_t st;
+    bool on;
+    TimedRegion(int slot, cudaStream_t st);
+    ~TimedRegion();
+};
 
 inline cudaStream_t as_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
 

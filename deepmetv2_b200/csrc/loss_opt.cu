@@ -1,10 +1,41 @@
 // a7/a8/a9: per-event MET reduction + loss (model/net.py:49-62), resolution metric (model/net.py:92-157),
 // fused flat AdamW (train.py:52,75), plus library-wide helpers and the generic edge_index -> CSR sort.
+#include <vector>
+
 #include "common.cuh"
 
 namespace gm {
 
 int g_last_cuda_error = 0;
+long long g_launch_count = 0;
+
+namespace {
+struct TimerSlot {
+    std::vector<cudaEvent_t> beg, end;
+    size_t used = 0;
+};
+TimerSlot g_timers[GM_NUM_TIMERS];
+bool g_timing_on = false;
+}  // namespace
+
+TimedRegion::TimedRegion(int slot_, cudaStream_t st_) : slot(slot_), st(st_), on(g_timing_on) {
+    if (!on) return;
+    TimerSlot &t = g_timers[slot];
+    if (t.used == t.beg.size()) {
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        t.beg.push_back(a);
+        t.end.push_back(b);
+    }
+    cudaEventRecord(t.beg[t.used], st);
+}
+TimedRegion::~TimedRegion() {
+    if (!on) return;
+    TimerSlot &t = g_timers[slot];
+    cudaEventRecord(t.end[t.used], st);
+    ++t.used;
+}
 
 int num_sms() {
     static int cached = 0;
@@ -152,7 +183,8 @@ __global__ void __launch_bounds__(256) k_fill_unsorted(const long long *__restri
 }
 // warp per row: rank sort by source (ties are identical values, so their relative order is immaterial)
 __global__ void __launch_bounds__(256) k_sort_rows(const int *__restrict__ rowptr, int N, const int *__restrict__ tmp,
-                                                   int *__restrict__ col) {
+                                                   int *__restrict__ col, const int *__restrict__ gate) {
+    if (gate && *gate == 0) return;
     const int lane = threadIdx.x & 31;
     const int warps = (gridDim.x * blockDim.x) >> 5;
     for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < N; i += warps) {
@@ -171,7 +203,8 @@ __global__ void __launch_bounds__(256) k_sort_rows(const int *__restrict__ rowpt
 
 // transposed CSR: histogram of sources, warp per target row
 __global__ void __launch_bounds__(256) k_count_sources(const int *__restrict__ rowptr, const int *__restrict__ col, int N,
-                                                       int *__restrict__ deg_t) {
+                                                       int *__restrict__ deg_t, const int *__restrict__ gate) {
+    if (gate && *gate == 0) return;
     const int lane = threadIdx.x & 31;
     const int warps = (gridDim.x * blockDim.x) >> 5;
     for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < N; i += warps)
@@ -179,7 +212,8 @@ __global__ void __launch_bounds__(256) k_count_sources(const int *__restrict__ r
 }
 __global__ void __launch_bounds__(256) k_fill_transposed(const int *__restrict__ rowptr, const int *__restrict__ col, int N,
                                                          const int *__restrict__ rowptr_t, int *__restrict__ cursor,
-                                                         int *__restrict__ tmp) {
+                                                         int *__restrict__ tmp, const int *__restrict__ gate) {
+    if (gate && *gate == 0) return;
     const int lane = threadIdx.x & 31;
     const int warps = (gridDim.x * blockDim.x) >> 5;
     for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < N; i += warps)
@@ -231,6 +265,30 @@ extern "C" {
 int gm_version(void) { return GM_VERSION; }
 int gm_last_cuda_error(void) { return g_last_cuda_error; }
 int gm_num_sms(void) { return num_sms(); }
+long long gm_launch_count(int reset) {
+    long long v = g_launch_count;
+    if (reset) g_launch_count = 0;
+    return v;
+}
+int gm_timing_enable(int on) {
+    g_timing_on = on != 0;
+    return GM_OK;
+}
+int gm_timing_read(int slot, float *total_ms_out, int *regions_out) {
+    if (slot < 0 || slot >= GM_NUM_TIMERS || !total_ms_out || !regions_out) return GM_ERR_INVALID_ARGUMENT;
+    TimerSlot &t = g_timers[slot];
+    float total = 0.f;
+    for (size_t k = 0; k < t.used; ++k) {
+        GM_CUDA_TRY(cudaEventSynchronize(t.end[k]));
+        float ms = 0.f;
+        GM_CUDA_TRY(cudaEventElapsedTime(&ms, t.beg[k], t.end[k]));
+        total += ms;
+    }
+    *total_ms_out = total;
+    *regions_out = (int)t.used;
+    t.used = 0;
+    return GM_OK;
+}
 
 const char *gm_status_string(int status) {
     switch (status) {
@@ -311,14 +369,14 @@ int gm_edge_index_to_csr(const int64_t *edge_index, long long E, int N, void *ws
         GM_TRY(exclusive_scan_inplace(rowptr_out, N + 1, w.tiles, nullptr, st));
         k_fill_unsorted<<<g, 256, 0, st>>>((const long long *)edge_index, E, N, rowptr_out, w.cursor, w.tmp);
         GM_LAUNCH_CHECK();
-        k_sort_rows<<<persistent_grid(((long long)N * 32 + 255) / 256, 8), 256, 0, st>>>(rowptr_out, N, w.tmp, col_out);
+        k_sort_rows<<<persistent_grid(((long long)N * 32 + 255) / 256, 8), 256, 0, st>>>(rowptr_out, N, w.tmp, col_out, nullptr);
         GM_LAUNCH_CHECK();
     }
     return GM_OK;
 }
 
 int gm_csr_transpose(const int *rowptr, const int *col, int N, long long E, void *ws, size_t ws_bytes,
-                     int *rowptr_t_out, int *col_t_out, void *stream) {
+                     int *rowptr_t_out, int *col_t_out, const int *only_if_flag, void *stream) {
     if (N < 0 || E < 0 || !ws || !rowptr_t_out || (N > 0 && !rowptr) || (E > 0 && (!col || !col_t_out)))
         return GM_ERR_INVALID_ARGUMENT;
     if (ws_bytes < csr_ws_layout(N, E, nullptr, nullptr)) return GM_ERR_CAPACITY;
@@ -329,12 +387,12 @@ int gm_csr_transpose(const int *rowptr, const int *col, int N, long long E, void
     GM_CUDA_TRY(cudaMemsetAsync(w.cursor, 0, (size_t)(N + 1) * sizeof(int), st));
     if (N > 0 && E > 0) {
         const int g = persistent_grid(((long long)N * 32 + 255) / 256, 8);
-        k_count_sources<<<g, 256, 0, st>>>(rowptr, col, N, rowptr_t_out);
+        k_count_sources<<<g, 256, 0, st>>>(rowptr, col, N, rowptr_t_out, only_if_flag);
         GM_LAUNCH_CHECK();
         GM_TRY(exclusive_scan_inplace(rowptr_t_out, N + 1, w.tiles, nullptr, st));
-        k_fill_transposed<<<g, 256, 0, st>>>(rowptr, col, N, rowptr_t_out, w.cursor, w.tmp);
+        k_fill_transposed<<<g, 256, 0, st>>>(rowptr, col, N, rowptr_t_out, w.cursor, w.tmp, only_if_flag);
         GM_LAUNCH_CHECK();
-        k_sort_rows<<<g, 256, 0, st>>>(rowptr_t_out, N, w.tmp, col_t_out);
+        k_sort_rows<<<g, 256, 0, st>>>(rowptr_t_out, N, w.tmp, col_t_out, only_if_flag);
         GM_LAUNCH_CHECK();
     }
     return GM_OK;

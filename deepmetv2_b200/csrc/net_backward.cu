@@ -277,8 +277,12 @@ __global__ void __launch_bounds__(BNB_THREADS) k_bn_bwd_apply(const float4 *__re
 // S[j][c] = sum over targets i that list j as a source of [arg(i,c) == j] * DC[i][c].
 // Warp per source j, lane = channel; the DC load is predicated on the match so only live sectors move.
 __global__ void __launch_bounds__(256) k_scatter_s(const float *__restrict__ DC, const int *__restrict__ arg,
-                                                   const int *__restrict__ rowptr_t, const int *__restrict__ col_t, int N,
-                                                   float *__restrict__ S) {
+                                                   const int *__restrict__ rowptr_s, const int *__restrict__ col_s,
+                                                   const int *__restrict__ rowptr_tt, const int *__restrict__ col_tt,
+                                                   const int *__restrict__ use_t, int N, float *__restrict__ S) {
+    const bool tr = use_t ? (*use_t != 0) : true;
+    const int *__restrict__ rowptr_t = tr ? rowptr_tt : rowptr_s;
+    const int *__restrict__ col_t = tr ? col_tt : col_s;
     const int lane = threadIdx.x & 31;
     const int warps = (gridDim.x * blockDim.x) >> 5;
     for (int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; j < N; j += warps) {
@@ -537,10 +541,10 @@ size_t gm_net_bwd_ws_bytes(int N, int conv_depth) {
 
 int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
                     const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride, const int *rowptr,
-                    const int *col, const int *rowptr_t, const int *col_t, int N, int training, int apply_sigmoid,
-                    int aggr, float eps, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
+                    const int *col, const int *rowptr_t, const int *col_t, const int *use_transposed_flag, int N,
+                    int training, int apply_sigmoid, int aggr, float eps, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
                     const float *out, const float *grad_out, void *stream) {
-    (void)eps; (void)rowptr; (void)col;
+    (void)eps;
     GM_TRY(check_params(p));
     if (!grads || N < 0 || !fwd_ws || !bwd_ws) return GM_ERR_INVALID_ARGUMENT;
     if (aggr != GM_AGGR_MAX) return GM_ERR_UNSUPPORTED;
@@ -576,11 +580,18 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
     for (int l = depth - 1; l >= 0; --l) {
         const float *stat = f.bnstat + (size_t)(l + 1) * BNSTAT_STRIDE;
         GM_TRY(bn_backward(w.G, f.conv[l], stat, N, training, grads->conv_bn[l].weight, grads->conv_bn[l].bias, w.DC, w, st));
-        k_scatter_s<<<persistent_grid(((long long)N * 32 + 255) / 256, 8), 256, 0, st>>>(w.DC, f.arg[l], rowptr_t, col_t, N, w.S);
-        GM_LAUNCH_CHECK();
+        {
+            TimedRegion tr(GM_TIMER_SCATTER_S_BWD, st);
+            k_scatter_s<<<persistent_grid(((long long)N * 32 + 255) / 256, 8), 256, 0, st>>>(
+                w.DC, f.arg[l], rowptr, col, rowptr_t, col_t, use_transposed_flag, N, w.S);
+            GM_LAUNCH_CHECK();
+        }
         GM_CUDA_TRY(cudaFuncSetAttribute(k_conv_bwd_node, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CONV_BWD_SMEM));
-        k_conv_bwd_node<<<ngrid, NODE_TILE, CONV_BWD_SMEM, st>>>(f.emb[l], w.DC, w.S, N, p->conv_w[l], w.G, w.gpart);
-        GM_LAUNCH_CHECK();
+        {
+            TimedRegion tr(GM_TIMER_CONV_NODE_BWD, st);
+            k_conv_bwd_node<<<ngrid, NODE_TILE, CONV_BWD_SMEM, st>>>(f.emb[l], w.DC, w.S, N, p->conv_w[l], w.G, w.gpart);
+            GM_LAUNCH_CHECK();
+        }
         Segs s{};
         s.n = 3;
         s.s[0] = Seg{grads->conv_w[l], CONV_IN, 0, H, H, H};
@@ -598,8 +609,11 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
     ea.e_chrg = p->embed_charge; ea.e_pdg = p->embed_pdgid; ea.e_pv = p->embed_pv;
     ea.enc = f.enc; ea.DA = w.DC; ea.gpart = w.gpart;
     GM_CUDA_TRY(cudaFuncSetAttribute(k_encode_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ENC_BWD_SMEM));
-    k_encode_bwd<<<ngrid, NODE_TILE, ENC_BWD_SMEM, st>>>(ea);
-    GM_LAUNCH_CHECK();
+    {
+        TimedRegion tr(GM_TIMER_ENCODE_BWD, st);
+        k_encode_bwd<<<ngrid, NODE_TILE, ENC_BWD_SMEM, st>>>(ea);
+        GM_LAUNCH_CHECK();
+    }
     {
         const int CD = p->continuous_dim;
         Segs s{};

@@ -421,6 +421,7 @@ int gm_edgeconv_forward(const float *x, const int *rowptr, const int *col, int N
     if (N < 0 || (N > 0 && (!x || !rowptr || !W || !b || !out))) return GM_ERR_INVALID_ARGUMENT;
     if (N == 0) return GM_OK;
     int n_part = 0;
+    TimedRegion tr(GM_TIMER_EDGECONV_FWD, as_stream(stream));
     return edgeconv_forward(x, rowptr, col, N, W, b, aggr, precision, out, arg_out, nullptr, &n_part, as_stream(stream));
 }
 
@@ -458,8 +459,11 @@ int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, co
     ea.partials = training ? w.partials : nullptr;
     ea.err_flags = err_flags;
     const int enc_grid = persistent_grid(tiles, 4);
-    k_encode<<<enc_grid, NODE_TILE, 0, st>>>(ea);
-    GM_LAUNCH_CHECK();
+    {
+        TimedRegion tr(GM_TIMER_ENCODE_FWD, st);
+        k_encode<<<enc_grid, NODE_TILE, 0, st>>>(ea);
+        GM_LAUNCH_CHECK();
+    }
 
     k_bn_finalize<<<1, 1024, 0, st>>>(w.partials, enc_grid, p->bn_all, momentum, eps, training, w.bnstat);
     GM_LAUNCH_CHECK();
@@ -470,8 +474,12 @@ int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, co
 
     for (int l = 0; l < depth; ++l) {
         int n_part = 0;
-        GM_TRY(edgeconv_forward(w.emb[l], rowptr, col, N, p->conv_w[l], p->conv_b[l], aggr, precision, w.conv[l],
-                                save_for_backward ? w.arg[l] : nullptr, training ? w.partials : nullptr, &n_part, st));
+        {
+            TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
+            GM_TRY(edgeconv_forward(w.emb[l], rowptr, col, N, p->conv_w[l], p->conv_b[l], aggr, precision, w.conv[l],
+                                    save_for_backward ? w.arg[l] : nullptr, training ? w.partials : nullptr, &n_part,
+                                    st));
+        }
         float *stat = w.bnstat + (size_t)(l + 1) * BNSTAT_STRIDE;
         k_bn_finalize<<<1, 1024, 0, st>>>(w.partials, n_part, p->conv_bn[l], momentum, eps, training, stat);
         GM_LAUNCH_CHECK();
@@ -479,9 +487,12 @@ int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, co
                                             (float4 *)w.emb[l + 1], n4);
         GM_LAUNCH_CHECK();
     }
-    k_head<<<persistent_grid(tiles, 4), NODE_TILE, 0, st>>>(w.emb[depth], N, p->out1_w, p->out1_b, p->out2_w,
-                                                            p->out2_b, apply_sigmoid, out);
-    GM_LAUNCH_CHECK();
+    {
+        TimedRegion tr(GM_TIMER_HEAD_FWD, st);
+        k_head<<<persistent_grid(tiles, 4), NODE_TILE, 0, st>>>(w.emb[depth], N, p->out1_w, p->out1_b, p->out2_w,
+                                                                p->out2_b, apply_sigmoid, out);
+        GM_LAUNCH_CHECK();
+    }
     return GM_OK;
 }
 

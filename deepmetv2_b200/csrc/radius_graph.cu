@@ -483,6 +483,7 @@ int gm_radius_graph_count(const float *pos, int pos_stride, int dim, const int *
     cudaStream_t st = as_stream(stream);
     Workspace w;
     ws_layout(N, B, (char *)ws, &w);
+    TimedRegion tr(GM_TIMER_RADIUS_GRAPH, st);
     GM_TRY(run_common(pos, pos_stride, dim, ptr, N, B, r, phi_wrap, w, st));
     const float rf = (float)r, r2 = (float)(r * r);  // r*r in double, then fp32
     if (N > 0) {
@@ -508,6 +509,7 @@ int gm_radius_graph_fill(const float *pos, int pos_stride, int dim, const int *p
     cudaStream_t st = as_stream(stream);
     Workspace w;
     ws_layout(N, B, (char *)ws, &w);  // sorted points / cell starts were left there by _count
+    TimedRegion tr(GM_TIMER_RADIUS_GRAPH, st);
     const int mask_words = (max_event_nodes + 31) / 32 + 1;
     int threads = 256;
     while (threads > 32 && (size_t)(threads / 32) * mask_words * 4 > 200 * 1024) threads >>= 1;

@@ -45,7 +45,7 @@ class GraphCSR:
             self.rowptr_t = torch.empty(N + 1, dtype=torch.int32, device=self.col.device)
             self.col_t = torch.empty(max(E, 1), dtype=torch.int32, device=self.col.device)
             check(l.gm_csr_transpose(ptr(self.rowptr), ptr(self.col), N, E, ptr(ws), ws.numel(),
-                                     ptr(self.rowptr_t), ptr(self.col_t), stream()), "gm_csr_transpose")
+                                     ptr(self.rowptr_t), ptr(self.col_t), None, stream()), "gm_csr_transpose")
         return self.rowptr_t, self.col_t
 
 

@@ -1,0 +1,200 @@
+"""Fused, sync-free training / inference step for GraphMETNetwork (the body of train.py:39-55 and
+evaluate.py:81-100 of the reference as ONE call).
+
+``GraphMETTrainer.train_step(batch)`` enqueues, on the current stream and without any host sync:
+    etaphi prep -> radius graph (count, scan, fill; E stays on the device) -> [transposed CSR iff capped]
+    -> fused forward (train-mode BN) -> per-event MET + loss (+ dL/dw) -> fused backward into a flat
+    gradient buffer -> [NCCL all-reduce of the 26.6 KB buffer] -> fused flat AdamW.
+Parameters stay the module's ``nn.Parameter``s (re-pointed at one flat fp32 buffer), so
+``state_dict()`` / checkpoints are unchanged; optimizer state converts to and from the
+``torch.optim.AdamW`` layout the reference's checkpoints store (``optim_dict``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import AGGR, PRECISION, check, lib, ptr, stream
+from .synth import EventBatch
+
+
+class GraphMETTrainer:
+    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, r=0.4,
+                 max_num_neighbors=255, loop=True, phi_wrap=False, process_group=None, device=None):
+        self.model = model
+        self.net = model.graphnet if hasattr(model, "graphnet") else model
+        self.apply_sigmoid = hasattr(model, "graphnet")       # Net applies the sigmoid, GraphMETNetwork does not
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self.r, self.max_nn, self.loop, self.phi_wrap = r, max_num_neighbors, loop, phi_wrap
+        self.pg = process_group
+        self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
+        self.step_count = 0
+        params = list(self.net.parameters())
+        dev = device or params[0].device
+        if dev.type != "cuda":
+            raise _lib.GraphMETLibraryError("GraphMETTrainer needs the model on a CUDA device (no CPU fallback)")
+        self.device = dev
+        n = sum(p.numel() for p in params)
+        self.flat = torch.empty(n, dtype=torch.float32, device=dev)
+        self.flat_grad = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
+        self._views, self._gviews, off = [], [], 0
+        for p in params:
+            k = p.numel()
+            self.flat[off:off + k].copy_(p.data.reshape(-1))
+            p.data = self.flat[off:off + k].view_as(p)        # parameters now alias the flat buffer
+            self._views.append(p.data)
+            self._gviews.append(self.flat_grad[off:off + k].view_as(p))
+            off += k
+        self._P = self.net._param_struct()
+        self._G = self.net._param_struct(grad_views=self._gviews)
+        self._cap_nodes = self._cap_events = self._cap_edges = -1
+        self.flags = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self._host_loss = torch.zeros((), dtype=torch.float32).pin_memory()
+
+    # ------------------------------------------------------------------------------------------ buffers
+    def _reserve(self, N: int, B: int, max_event_nodes: int):
+        E = N * min(self.max_nn + (0 if self.loop else 1), max(max_event_nodes, 1))
+        if N <= self._cap_nodes and B <= self._cap_events and E <= self._cap_edges:
+            return
+        N, B, E = max(N, self._cap_nodes), max(B, self._cap_events), max(E, self._cap_edges)
+        l, dev, depth = lib(), self.device, len(self.net.conv_continuous)
+        u8 = lambda nbytes: torch.empty(int(nbytes), dtype=torch.uint8, device=dev)  # noqa: E731
+        self.etaphi = torch.empty(N, 2, dtype=torch.float32, device=dev)
+        self.rg_ws = u8(l.gm_radius_graph_ws_bytes(N, B))
+        self.rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+        self.col = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
+        self.rowptr_t = torch.empty(N + 1, dtype=torch.int32, device=dev)
+        self.col_t = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
+        self.csr_ws = u8(l.gm_csr_ws_bytes(N, E))
+        self.stats = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.fwd_ws = u8(l.gm_net_ws_bytes(N, depth, 1))
+        self.bwd_ws = u8(l.gm_net_bwd_ws_bytes(N, depth))
+        self.weights = torch.empty(N, dtype=torch.float32, device=dev)
+        self.grad_w = torch.empty(N, dtype=torch.float32, device=dev)
+        self.met = torch.empty(B, 2, dtype=torch.float32, device=dev)
+        self._cap_nodes, self._cap_events, self._cap_edges = N, B, E
+
+    # ------------------------------------------------------------------------------------------ pieces
+    def _graph(self, x, ptr_i32, N, B, max_event_nodes, need_transpose):
+        l, st = lib(), stream()
+        check(l.gm_prepare_etaphi(ptr(x), x.stride(0), N, ptr(self.etaphi), st), "gm_prepare_etaphi")
+        args = (ptr(self.etaphi), 2, 2, ptr(ptr_i32), N, B, float(self.r), int(self.max_nn), int(self.loop),
+                int(self.phi_wrap), int(max_event_nodes), ptr(self.rg_ws), self.rg_ws.numel())
+        check(l.gm_radius_graph_count(*args, ptr(self.rowptr), ptr(self.stats), st), "gm_radius_graph_count")
+        check(l.gm_radius_graph_fill(*args, ptr(self.rowptr), ptr(self.col), self._cap_edges, None,
+                                     ptr(self.stats), st), "gm_radius_graph_fill")
+        if need_transpose:   # kernels are no-ops unless some node hit the cap (decided on the device)
+            check(l.gm_csr_transpose(ptr(self.rowptr), ptr(self.col), N, self._cap_edges, ptr(self.csr_ws),
+                                     self.csr_ws.numel(), ptr(self.rowptr_t), ptr(self.col_t),
+                                     self.stats.data_ptr() + 8, st), "gm_csr_transpose")
+
+    def _forward(self, x, N, training, save):
+        net = self.net
+        check(lib().gm_net_forward(C.byref(self._P), ptr(x), x.stride(0), None, x.data_ptr() + 8 * 4, x.stride(0),
+                                   ptr(self.rowptr), ptr(self.col), N, int(training), int(save),
+                                   int(self.apply_sigmoid), AGGR[net.aggr], PRECISION[net.edge_precision],
+                                   float(net.bn_all.momentum), float(net.bn_all.eps), ptr(self.fwd_ws),
+                                   self.fwd_ws.numel(), ptr(self.weights), ptr(self.flags), stream()),
+              "gm_net_forward")
+
+    @staticmethod
+    def _sizes(batch: EventBatch, max_event_nodes):
+        N, B = batch.x.shape[0], batch.y.shape[0]
+        if max_event_nodes is None:
+            max_event_nodes = getattr(batch, "max_event_nodes", None)
+        if max_event_nodes is None:
+            max_event_nodes = int((batch.ptr[1:] - batch.ptr[:-1]).max().item()) if B else 0   # syncs; pass it in
+        return N, B, int(max_event_nodes)
+
+    # ------------------------------------------------------------------------------------------ public
+    def train_step(self, batch: EventBatch, max_event_nodes: int | None = None) -> torch.Tensor:
+        """One optimisation step on a device-resident batch. Returns the loss as a 0-dim device tensor
+        (no sync). ``batch.x`` [N,11] f32, ``batch.y`` [B,>=2] f32, ``batch.ptr`` [B+1] i32."""
+        x, y, p = batch.x, batch.y, batch.ptr
+        N, B, men = self._sizes(batch, max_event_nodes)
+        self._reserve(N, B, men)
+        self.net.train()
+        l, st = lib(), stream()
+        self._graph(x, p, N, B, men, need_transpose=True)
+        self._forward(x, N, training=True, save=True)
+        check(l.gm_met_loss(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
+                            ptr(self.met), ptr(self.loss), ptr(self.grad_w), st), "gm_met_loss")
+        net = self.net
+        check(l.gm_net_backward(C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), None, x.data_ptr() + 32,
+                                x.stride(0), ptr(self.rowptr), ptr(self.col), ptr(self.rowptr_t), ptr(self.col_t),
+                                self.stats.data_ptr() + 8, N, 1, int(self.apply_sigmoid), AGGR[net.aggr],
+                                float(net.bn_all.eps), ptr(self.fwd_ws), self.fwd_ws.numel(), ptr(self.bwd_ws),
+                                self.bwd_ws.numel(), ptr(self.weights), ptr(self.grad_w), st), "gm_net_backward")
+        scale = 1.0
+        if self.world > 1:
+            torch.distributed.all_reduce(self.flat_grad, group=self.pg)      # NCCL SUM over NVLink
+            scale = 1.0 / self.world
+        self.step_count += 1
+        check(l.gm_adamw_step(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq),
+                              self.flat.numel(), self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay,
+                              self.step_count, scale, st), "gm_adamw_step")
+        return self.loss
+
+    def train_step_from_host(self, host_batch: EventBatch, max_event_nodes: int | None = None) -> float:
+        """End-to-end step from PINNED host buffers: H2D copies, the step, and the loss read back
+        (what train.py:41,54 do per batch)."""
+        dev = self.device
+        x = host_batch.x.to(dev, non_blocking=True)
+        y = host_batch.y.to(dev, non_blocking=True)
+        p = host_batch.ptr.to(dev, non_blocking=True)
+        men = max_event_nodes if max_event_nodes is not None else \
+            int((host_batch.ptr[1:] - host_batch.ptr[:-1]).max())       # host tensor: no device sync
+        loss = self.train_step(EventBatch(x, y, None, p), men)
+        self._host_loss.copy_(loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(self._host_loss)
+
+    @torch.no_grad()
+    def eval_step(self, batch: EventBatch, max_event_nodes: int | None = None):
+        """evaluate.py:81-100 fused: returns (weights[N] view, loss 0-dim, met[B,2]) on the device."""
+        x, y, p = batch.x, batch.y, batch.ptr
+        N, B, men = self._sizes(batch, max_event_nodes)
+        self._reserve(N, B, men)
+        self.net.eval()
+        self._graph(x, p, N, B, men, need_transpose=False)
+        self._forward(x, N, training=False, save=False)
+        check(lib().gm_met_loss(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
+                                ptr(self.met), ptr(self.loss), None, stream()), "gm_met_loss")
+        return self.weights[:N], self.loss, self.met[:B]
+
+    def graph_stats(self):
+        """(E, max degree before the cap, #capped nodes, flags) of the last batch — synchronises."""
+        return tuple(self.stats.tolist())
+
+    # ------------------------------------------------------------------------------------------ optimizer state
+    def optimizer_state_dict(self):
+        """State in torch.optim.AdamW's layout (what the reference stores as ``optim_dict``)."""
+        state, off = {}, 0
+        for i, v in enumerate(self._views):
+            k = v.numel()
+            state[i] = {"step": torch.tensor(float(self.step_count)),
+                        "exp_avg": self.exp_avg[off:off + k].view_as(v).clone(),
+                        "exp_avg_sq": self.exp_avg_sq[off:off + k].view_as(v).clone()}
+            off += k
+        group = {"lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay,
+                 "amsgrad": False, "params": list(range(len(self._views)))}
+        return {"state": state, "param_groups": [group]}
+
+    def load_optimizer_state_dict(self, sd):
+        g = sd["param_groups"][0]
+        self.lr, self.betas, self.eps = g["lr"], tuple(g["betas"]), g["eps"]
+        self.weight_decay = g["weight_decay"]
+        off = 0
+        for i, v in enumerate(self._views):
+            k = v.numel()
+            st = sd["state"].get(i)
+            if st is not None:
+                self.exp_avg[off:off + k].copy_(st["exp_avg"].reshape(-1))
+                self.exp_avg_sq[off:off + k].copy_(st["exp_avg_sq"].reshape(-1))
+                self.step_count = int(st["step"])
+            off += k

@@ -63,6 +63,22 @@ int gm_version(void);
 const char *gm_status_string(int status);
 int gm_last_cuda_error(void);          /* cudaError_t of the last failing runtime call */
 int gm_num_sms(void);                  /* of the current device (cached) */
+long long gm_launch_count(int reset);  /* kernels this library launched since the last reset */
+
+/* Optional CUDA-event timing of kernel families on the launching stream (used by bench.py for the
+ * live roofline figure). gm_timing_read synchronises on the recorded events, returns the summed
+ * milliseconds and the number of timed regions of `slot`, and clears the slot. */
+#define GM_TIMER_RADIUS_GRAPH 0
+#define GM_TIMER_ENCODE_FWD 1
+#define GM_TIMER_EDGECONV_FWD 2
+#define GM_TIMER_HEAD_FWD 3
+#define GM_TIMER_SCATTER_S_BWD 4
+#define GM_TIMER_CONV_NODE_BWD 5
+#define GM_TIMER_ENCODE_BWD 6
+#define GM_TIMER_BN 7
+#define GM_NUM_TIMERS 8
+int gm_timing_enable(int on);
+int gm_timing_read(int slot, float *total_ms_out, int *regions_out);
 
 /* ---------------------------------------------------------------------------------
  * Parameters: the reference's 23 trainable tensors in construction order
@@ -170,20 +186,25 @@ int gm_edgeconv_forward(const float *x, const int *rowptr, const int *col, int N
  * buffers ignored) is OVERWRITTEN with the gradient.  Deterministic: no atomics; every
  * reduction runs in a fixed order.  The forward must have been run with save_for_backward.
  * (rowptr_t, col_t) is the CSR of the TRANSPOSED graph (by source); for a symmetric graph
- * (no node hit the max_num_neighbors cap) pass (rowptr, col) again.
+ * (no node hit the max_num_neighbors cap) pass (rowptr, col) again.  use_transposed_flag (device
+ * int, may be NULL): when given, the kernels use (rowptr_t, col_t) only if *flag != 0 and (rowptr, col)
+ * otherwise — lets a sync-free caller decide on the device (pass stats+2 of gm_radius_graph_count).
  * Only aggr = max has a backward so far. */
 size_t gm_net_bwd_ws_bytes(int N, int conv_depth);
 int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
                     const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride,
-                    const int *rowptr, const int *col, const int *rowptr_t, const int *col_t, int N,
+                    const int *rowptr, const int *col, const int *rowptr_t, const int *col_t,
+                    const int *use_transposed_flag, int N,
                     int training, int apply_sigmoid, int aggr, float eps,
                     const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
                     const float *out, const float *grad_out, void *stream);
 
 /* CSR (by target) -> CSR of the transposed graph (by source), targets ascending per row.
- * ws: gm_csr_ws_bytes(N, E). Needed by the backward only when GM_FLAG_DEGREE_CAPPED was raised. */
+ * ws: gm_csr_ws_bytes(N, E). Needed by the backward only when GM_FLAG_DEGREE_CAPPED was raised;
+ * with only_if_flag the kernels are no-ops unless *only_if_flag != 0 (E is then a capacity). */
 int gm_csr_transpose(const int *rowptr, const int *col, int N, long long E, void *ws, size_t ws_bytes,
-                     int *rowptr_t_out, int *col_t_out, void *stream);
+                     int *rowptr_t_out, int *col_t_out, const int *only_if_flag /* device int or NULL */,
+                     void *stream);
 
 /* ---------------------------------------------------------------------------------
  * a7. loss_fn — replaces model/net.py:49-62 (two torch_scatter.scatter_add + mean).
