@@ -127,6 +127,8 @@ __device__ __forceinline__ void dense_smem(const float *__restrict__ W, const fl
             for (int k = 0; k < IN; ++k) acc = fmaf(W[o * IN + k], x[k], acc);
         }
         y[o] = acc;
+        // keep ptxas from hoisting every weight load of the unrolled product to the top (register spills)
+        if ((o & 3) == 3) asm volatile("" ::: "memory");
     }
 }
 
@@ -152,6 +154,7 @@ __device__ __forceinline__ void dense_t_smem(const float *__restrict__ W, const 
 #pragma unroll
             for (int k = 0; k < IN; ++k) y[k] = fmaf(W[o * IN + k], g[o], y[k]);
         }
+        if ((o & 3) == 3) asm volatile("" ::: "memory");
     }
 }
 

@@ -137,22 +137,43 @@ struct ColSum {
 };
 
 struct Seg { float *dst; int dst_ld, off, rows, src_ld, cols; };
-struct Segs { int n; Seg s[8]; };
+struct Segs { int n; Seg s[10]; };
 
-// dst[r*dst_ld + c] = sum_b part[b][off + r*src_ld + c]   (b ascending: fixed order)
+// dst[r*dst_ld + c] = sum_b part[b][off + r*src_ld + c].  grid = (chunks of 32 outputs, segments);
+// thread (c = t%32, g = t/32): lanes read 32 consecutive outputs (coalesced), the 8 groups split the
+// CTA-partial axis (b = g, g+8, ...) and are folded in a fixed order => deterministic.
 __global__ void __launch_bounds__(256) k_reduce_partials(const float *__restrict__ part, int nblk, int stride, Segs segs) {
-    for (int si = 0; si < segs.n; ++si) {
-        const Seg sg = segs.s[si];
-        if (!sg.dst) continue;
-        const int total = sg.rows * sg.cols;
-        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-            const int r = i / sg.cols, c = i - r * sg.cols;
-            const float *p = part + sg.off + r * sg.src_ld + c;
-            float acc = 0.f;
-            for (int b = 0; b < nblk; ++b) acc += p[(size_t)b * stride];
-            sg.dst[r * sg.dst_ld + c] = acc;
-        }
+    __shared__ float sm[8][32];
+    const Seg sg = segs.s[blockIdx.y];
+    const int total = sg.rows * sg.cols;
+    const int i = blockIdx.x * 32 + (threadIdx.x & 31);
+    if (!sg.dst || blockIdx.x * 32 >= total) return;
+    const int g = threadIdx.x >> 5;
+    float acc = 0.f;
+    int r = 0, c = 0;
+    if (i < total) {
+        r = i / sg.cols; c = i - r * sg.cols;
+        const float *p = part + sg.off + r * sg.src_ld + c;
+#pragma unroll 4
+        for (int b = g; b < nblk; b += 8) acc += p[(size_t)b * stride];
     }
+    sm[g][threadIdx.x & 31] = acc;
+    __syncthreads();
+    if (g == 0 && i < total) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += sm[k][threadIdx.x];
+        sg.dst[r * sg.dst_ld + c] = t;
+    }
+}
+
+int launch_reduce(const float *part, int nblk, const Segs &segs, cudaStream_t st) {
+    int max_total = 0;
+    for (int k = 0; k < segs.n; ++k) max_total = max(max_total, segs.s[k].rows * segs.s[k].cols);
+    dim3 grid((max_total + 31) / 32, segs.n);
+    k_reduce_partials<<<grid, 256, 0, st>>>(part, nblk, GP_STRIDE, segs);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
 }
 
 // ----------------------------------------------------------------------------------------- head backward
@@ -573,8 +594,7 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
         s.s[1] = Seg{grads->out1_b, 16, 512, 1, 16, 16};
         s.s[2] = Seg{grads->out2_w, 16, 528, 1, 16, 16};
         s.s[3] = Seg{grads->out2_b, 1, 544, 1, 1, 1};
-        k_reduce_partials<<<4, 256, 0, st>>>(w.gpart, ngrid, GP_STRIDE, s);
-        GM_LAUNCH_CHECK();
+        GM_TRY(launch_reduce(w.gpart, ngrid, s, st));
     }
     // ---- EdgeConv layers, last to first
     for (int l = depth - 1; l >= 0; --l) {
@@ -597,8 +617,7 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
         s.s[0] = Seg{grads->conv_w[l], CONV_IN, 0, H, H, H};
         s.s[1] = Seg{grads->conv_w[l] ? grads->conv_w[l] + H : nullptr, CONV_IN, 1024, H, H, H};
         s.s[2] = Seg{grads->conv_b[l], H, 2048, 1, H, H};
-        k_reduce_partials<<<8, 256, 0, st>>>(w.gpart, ngrid, GP_STRIDE, s);
-        GM_LAUNCH_CHECK();
+        GM_TRY(launch_reduce(w.gpart, ngrid, s, st));
     }
     // ---- bn_all + encoder
     GM_TRY(bn_backward(w.G, f.enc, f.bnstat, N, training, grads->bn_all.weight, grads->bn_all.bias, w.DC, w, st));
@@ -617,7 +636,7 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
     {
         const int CD = p->continuous_dim;
         Segs s{};
-        s.n = 8;
+        s.n = 9;
         s.s[0] = Seg{grads->enc_w, H, 0, H, H, H};
         s.s[1] = Seg{grads->enc_b, H, 1024, 1, H, H};
         s.s[2] = Seg{grads->cont_w, CD, 1056, 16, 8, CD};
@@ -626,13 +645,8 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
         s.s[5] = Seg{grads->cat_b, 16, 1584, 1, 16, 16};
         s.s[6] = Seg{grads->embed_charge, 8, 1600, 3, 8, 8};
         s.s[7] = Seg{grads->embed_pdgid, 8, 1624, 7, 8, 8};
-        k_reduce_partials<<<8, 256, 0, st>>>(w.gpart, ngrid, GP_STRIDE, s);
-        GM_LAUNCH_CHECK();
-        Segs s2{};
-        s2.n = 1;
-        s2.s[0] = Seg{grads->embed_pv, 8, 1680, 8, 8, 8};
-        k_reduce_partials<<<1, 256, 0, st>>>(w.gpart, ngrid, GP_STRIDE, s2);
-        GM_LAUNCH_CHECK();
+        s.s[8] = Seg{grads->embed_pv, 8, 1680, 8, 8, 8};
+        GM_TRY(launch_reduce(w.gpart, ngrid, s, st));
     }
     return GM_OK;
 }

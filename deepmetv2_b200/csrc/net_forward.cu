@@ -188,6 +188,7 @@ __global__ void __launch_bounds__(1024) k_bn_finalize(const float *__restrict__ 
     const int c = threadIdx.x & 31, s = threadIdx.x >> 5;
     if (training) {
         Moments m{0.f, 0.f, 0.f};
+#pragma unroll 4
         for (int b = s; b < n_partials; b += 32) {
             const float *p = partials + (size_t)b * MOM_STRIDE;
             m = moments_combine(m, Moments{p[c], p[H + c], p[2 * H + c]});
