@@ -51,8 +51,9 @@ def test_trainer_matches_dropin_loop_and_oracle():
     for (k, pa), (_, pb), (_, pr) in zip(a.named_parameters(), b.named_parameters(), ref.named_parameters()):
         if k.endswith("nn.0.bias"):
             # an EdgeConv bias feeds a train-mode BatchNorm: its gradient is pure rounding noise and AdamW
-            # turns noise of any size into +-lr steps, so two correct implementations differ by <= steps*lr
-            assert torch.allclose(pa, pb, rtol=0, atol=3.1e-3) and torch.allclose(pb.cpu(), pr, rtol=0, atol=3.1e-3), k
+            # turns noise of any size into +-lr steps: each implementation random-walks by <= steps*lr, so two
+            # correct implementations differ by <= 2*steps*lr (3 steps, lr 1e-3)
+            assert torch.allclose(pa, pb, rtol=0, atol=6.2e-3) and torch.allclose(pb.cpu(), pr, rtol=0, atol=6.2e-3), k
             continue
         assert torch.allclose(pa, pb, rtol=1e-4, atol=1e-6), k
         assert torch.allclose(pb.cpu(), pr, rtol=2e-3, atol=2e-5), k
