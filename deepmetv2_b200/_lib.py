@@ -24,9 +24,9 @@ FLAG_EDGE_OVERFLOW = 4
 FLAG_EVENT_TOO_LARGE = 8
 MAX_CONV_DEPTH = 4
 AGGR = {"max": 0, "add": 1, "mean": 2}
-PRECISION = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3}
+PRECISION = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3, "fp32_direct": 4}
 TIMERS = {"radius_graph": 0, "encode_fwd": 1, "edgeconv_fwd": 2, "head_fwd": 3, "scatter_s_bwd": 4,
-          "conv_node_bwd": 5, "encode_bwd": 6, "bn": 7}
+          "conv_node_bwd": 5, "encode_bwd": 6, "bn": 7, "node_prep": 8, "head_bwd": 9}
 
 _vp, _i, _ll, _f, _d, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double, C.c_size_t
 
@@ -64,13 +64,14 @@ SIGNATURES = {
     "gm_csr_ws_bytes": (_sz, [_i, _ll]),
     "gm_edge_index_to_csr": (_i, [_vp, _ll, _i, _vp, _sz, _vp, _vp, _vp]),
     "gm_csr_transpose": (_i, [_vp, _vp, _i, _ll, _vp, _sz, _vp, _vp, _vp, _vp]),
-    "gm_edgeconv_forward": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "gm_edgeconv_ws_bytes": (_sz, [_i]),
+    "gm_edgeconv_forward": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _sz, _vp, _vp, _vp]),
     "gm_net_ws_bytes": (_sz, [_i, _i, _i]),
-    "gm_net_forward": (_i, [C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f,
+    "gm_net_forward": (_i, [C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _f,
                             _vp, _sz, _vp, _vp, _vp]),
     "gm_net_bwd_ws_bytes": (_sz, [_i, _i]),
     "gm_net_backward": (_i, [C.POINTER(GmParams), C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp,
-                             _i, _i, _i, _i, _f, _vp, _sz, _vp, _sz, _vp, _vp, _vp]),
+                             _i, _vp, _i, _i, _i, _f, _vp, _sz, _vp, _sz, _vp, _vp, _vp]),
     "gm_met_loss": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "gm_segment_sum": (_i, [_vp, _vp, _i, _vp, _vp]),
     "gm_scatter_add": (_i, [_vp, _vp, _ll, _vp, _ll, _vp]),

@@ -1,14 +1,20 @@
 // Backward of the GraphMETNetwork hot path (what loss.backward() runs through autograd in the
 // reference, train.py:51): hand-written, atomics-free, fixed-order (bit-deterministic) kernels.
 //
-//   k_head_bwd        : d(out) -> d(emb_L), partial dW/db of output.{0,2}
-//   k_bn_bwd_reduce   : per-channel sum(G), sum(G*xhat)                     (BatchNorm backward, pass 1)
-//   k_bn_bwd_apply    : d(conv) = gamma*invstd*(G - mean(G) - xhat*mean(G*xhat)); writes d gamma, d beta
+//   k_head_bwd        : d(out) -> G = d(emb_L), partial dW/db of output.{0,2}, BatchNorm sums of the last layer
 //   k_scatter_s       : S[j][c] = sum_{i: argmax_src(i,c) == j} d(conv)[i][c]  as a GATHER over the
-//                       transposed CSR (max-aggregation routes each (target,channel) gradient to one edge)
-//   k_conv_bwd_node   : G += (W1-W2)^T d(conv) + W2^T S ; partial dW1 = dconv (x) x, dW2 = (S-dconv) (x) x
-//   k_encode_bwd      : BN_all'd gradient -> encode_all / embed_continuous / embed_categorical / 3 tables
-//   k_reduce_partials : fixed-order sum of the per-CTA partials into the caller's gradient tensors
+//                       transposed CSR (max-aggregation routes each (target,channel) gradient to one edge);
+//                       d(conv) = BatchNorm backward of G, evaluated on the fly for the matching entries only
+//   k_conv_bwd_node   : G += (W1-W2)^T d(conv) + W2^T S ; partial dW1 = dconv (x) x, dW2 = (S-dconv) (x) x ;
+//                       BatchNorm sums of the layer below
+//   k_encode_bwd      : BN_all backward on the fly -> encode_all / embed_continuous / embed_categorical / 3 tables
+//   k_reduce_partials : ONE launch: fixed-order sum of every stage's per-CTA partials into the gradient tensors
+//
+// BatchNorm backward needs sum(G) and sum(G*xhat) over all nodes before any node can be finished.  The
+// kernel that PRODUCES G accumulates per-CTA partial sums and its last CTA (ticket counter, nobody waits)
+// folds them in a fixed order into bnsum (and d gamma / d beta), so the consumer kernels apply
+//     d(conv) = gamma*invstd * (G - mean(G) - xhat * mean(G*xhat))
+// while they load G: no separate BatchNorm-backward pass, no extra launch.
 //
 // Parameter-gradient GEMMs (dW = sum_n a_n (x) b_n) are split-K over node tiles: every CTA keeps 4x4
 // register blocks of the outer product for its tiles, the per-CTA results are summed in CTA order.
@@ -19,13 +25,15 @@ namespace {
 
 constexpr int GLD = 36;                 // float4-aligned padded tile row (conflict-free LDS.128 row-per-thread)
 constexpr int GP_STRIDE = 2112;         // floats per CTA in the parameter-gradient partial buffer
-constexpr int BNB_THREADS = 256;
 constexpr int MAX_BWD_CTAS = 148 * 2;
+constexpr int MAX_STAGES = GM_MAX_CONV_DEPTH + 2;   // head, conv layers, encoder
 
 struct BwdWs {
-    float *G, *DC, *S;                  // [N,32] each
+    float *G, *S;                       // [N,32] each
+    float *bnsum;                       // [depth+1][64]  sum(G)[32], sum(G*xhat)[32] per BatchNorm
     float *bnpart;                      // [MAX_BWD_CTAS][64]
-    float *gpart;                       // [MAX_BWD_CTAS][GP_STRIDE]
+    float *gpart;                       // [MAX_STAGES][MAX_BWD_CTAS][GP_STRIDE]
+    int *counters;                      // [NUM_COUNTERS]
 };
 
 size_t bwd_ws_layout(int N, char *base, BwdWs *w) {
@@ -33,11 +41,12 @@ size_t bwd_ws_layout(int N, char *base, BwdWs *w) {
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return base ? base + o : nullptr; };
     const size_t nodes = (size_t)(N > 0 ? N : 1);
     BwdWs t;
-    t.G = (float *)take(nodes * H * sizeof(float));
-    t.DC = (float *)take(nodes * H * sizeof(float));
-    t.S = (float *)take(nodes * H * sizeof(float));
+    t.counters = (int *)take(NUM_COUNTERS * sizeof(int));
+    t.bnsum = (float *)take((size_t)(GM_MAX_CONV_DEPTH + 1) * 64 * sizeof(float));
     t.bnpart = (float *)take((size_t)MAX_BWD_CTAS * 64 * sizeof(float));
-    t.gpart = (float *)take((size_t)MAX_BWD_CTAS * GP_STRIDE * sizeof(float));
+    t.gpart = (float *)take((size_t)MAX_STAGES * MAX_BWD_CTAS * GP_STRIDE * sizeof(float));
+    t.G = (float *)take(nodes * H * sizeof(float));
+    t.S = (float *)take(nodes * H * sizeof(float));
     if (w) *w = t;
     return off;
 }
@@ -136,13 +145,14 @@ struct ColSum {
     }
 };
 
-struct Seg { float *dst; int dst_ld, off, rows, src_ld, cols; };
-struct Segs { int n; Seg s[10]; };
+struct Seg { const float *part; float *dst; int dst_ld, off, rows, src_ld, cols, nblk; };
+constexpr int MAX_SEGS = 4 + 3 * GM_MAX_CONV_DEPTH + 9;
+struct Segs { int n; Seg s[MAX_SEGS]; };
 
 // dst[r*dst_ld + c] = sum_b part[b][off + r*src_ld + c].  grid = (chunks of 32 outputs, segments);
 // thread (c = t%32, g = t/32): lanes read 32 consecutive outputs (coalesced), the 8 groups split the
 // CTA-partial axis (b = g, g+8, ...) and are folded in a fixed order => deterministic.
-__global__ void __launch_bounds__(256) k_reduce_partials(const float *__restrict__ part, int nblk, int stride, Segs segs) {
+__global__ void __launch_bounds__(256) k_reduce_partials(Segs segs) {
     __shared__ float sm[8][32];
     const Seg sg = segs.s[blockIdx.y];
     const int total = sg.rows * sg.cols;
@@ -153,9 +163,9 @@ __global__ void __launch_bounds__(256) k_reduce_partials(const float *__restrict
     int r = 0, c = 0;
     if (i < total) {
         r = i / sg.cols; c = i - r * sg.cols;
-        const float *p = part + sg.off + r * sg.src_ld + c;
+        const float *p = sg.part + sg.off + r * sg.src_ld + c;
 #pragma unroll 4
-        for (int b = g; b < nblk; b += 8) acc += p[(size_t)b * stride];
+        for (int b = g; b < sg.nblk; b += 8) acc += p[(size_t)b * GP_STRIDE];
     }
     sm[g][threadIdx.x & 31] = acc;
     __syncthreads();
@@ -167,43 +177,102 @@ __global__ void __launch_bounds__(256) k_reduce_partials(const float *__restrict
     }
 }
 
-int launch_reduce(const float *part, int nblk, const Segs &segs, cudaStream_t st) {
-    int max_total = 0;
-    for (int k = 0; k < segs.n; ++k) max_total = max(max_total, segs.s[k].rows * segs.s[k].cols);
-    dim3 grid((max_total + 31) / 32, segs.n);
-    k_reduce_partials<<<grid, 256, 0, st>>>(part, nblk, GP_STRIDE, segs);
-    GM_LAUNCH_CHECK();
-    return GM_OK;
+// ----------------------------------------------------------------------------------------- BatchNorm-backward plumbing
+// What a consumer needs to turn G into d(raw) for one BatchNorm: per channel
+//     d(raw) = scale * (G - c1 - (raw - mean) * invstd * c2),  c1 = sum(G)/N, c2 = sum(G*xhat)/N  (train)
+//                                                              c1 = c2 = 0                        (eval)
+struct BnBwd {
+    const float *stat;      // mean[32], scale[32], invstd[32], beta[32]   (forward)
+    const float *sum;       // sum(G)[32], sum(G*xhat)[32]                 (from the producer's last CTA)
+    float inv_n;            // 1/N in train mode, 0 in eval mode
+};
+// Producer side: where the per-CTA partial sums go and what the last CTA writes.
+struct BnSumOut {
+    const float *raw;       // [N,32] pre-BatchNorm activations of the BatchNorm being differentiated
+    const float *stat;
+    float *part;            // [grid][64]
+    float *sum;             // [64]
+    float *dgamma, *dbeta;  // gradient tensors (may be NULL)
+    int *counter;
+};
+
+// smem coefficient table for BnBwd: [5][32] = mean, invstd, scale, c1, c2
+__device__ __forceinline__ void bn_bwd_coeffs(const BnBwd &b, float *s_coef) {
+    const int t = threadIdx.x;
+    if (t < H) {
+        s_coef[t] = b.stat[t];
+        s_coef[H + t] = b.stat[2 * H + t];
+        s_coef[2 * H + t] = b.stat[H + t];
+        s_coef[3 * H + t] = b.sum[t] * b.inv_n;
+        s_coef[4 * H + t] = b.sum[H + t] * b.inv_n;
+    }
+}
+__device__ __forceinline__ float bn_bwd_one(const float *s_coef, int c, float g, float raw) {
+    const float xhat = (raw - s_coef[c]) * s_coef[H + c];
+    return s_coef[2 * H + c] * (g - s_coef[3 * H + c] - xhat * s_coef[4 * H + c]);
+}
+
+// Last CTA: fold the per-CTA (sum G, sum G*xhat) partials in a fixed order.  blockDim.x == NODE_TILE: 16 lane
+// groups of 8 lanes (two float4 = 8 of the 64 sums each) stream CTAs g, g+16, ... with independent loads,
+// then 64 threads fold the 16 group results in group order.  scratch >= 1024 floats.
+__device__ __forceinline__ void bn_sums_finalize(const BnSumOut &o, float *scratch) {
+    const int t = threadIdx.x, sub = t & 7, grp = t >> 3;
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+#pragma unroll 4
+    for (int b = grp; b < (int)gridDim.x; b += NODE_TILE / 8) {
+        const float4 *p = reinterpret_cast<const float4 *>(o.part + (size_t)b * 64) + 2 * sub;
+        const float4 u = __ldcg(p), v = __ldcg(p + 1);
+        a0.x += u.x; a0.y += u.y; a0.z += u.z; a0.w += u.w;
+        a1.x += v.x; a1.y += v.y; a1.z += v.z; a1.w += v.w;
+    }
+    float *d = scratch + grp * 64 + 8 * sub;
+    d[0] = a0.x; d[1] = a0.y; d[2] = a0.z; d[3] = a0.w; d[4] = a1.x; d[5] = a1.y; d[6] = a1.z; d[7] = a1.w;
+    __syncthreads();
+    if (t < 64) {
+        float tot = 0.f;
+#pragma unroll
+        for (int g = 0; g < NODE_TILE / 8; ++g) tot += scratch[g * 64 + t];
+        o.sum[t] = tot;
+        if (t < 32) { if (o.dbeta) o.dbeta[t] = tot; }
+        else if (o.dgamma) o.dgamma[t - 32] = tot;
+    }
+    __syncthreads();
 }
 
 // ----------------------------------------------------------------------------------------- head backward
 // partial layout: dW1[16][32] @0, db1[16] @512, dW2[16] @528, db2 @544
 __global__ void __launch_bounds__(NODE_TILE, 2)
-k_head_bwd(const float *__restrict__ emb, const float *__restrict__ out, const float *__restrict__ grad_out, int N,
-           const float *__restrict__ w1, const float *__restrict__ b1, const float *__restrict__ w2,
-           int apply_sigmoid, float *__restrict__ G, float *__restrict__ gpart) {
+k_head_bwd(const float *__restrict__ emb, const float *__restrict__ out, const float *__restrict__ grad_out,
+           const int *__restrict__ perm, int N, const float *__restrict__ w1, const float *__restrict__ b1,
+           const float *__restrict__ w2, int apply_sigmoid, float *__restrict__ G, float *__restrict__ gpart,
+           BnSumOut bo) {
     __shared__ __align__(16) float s_w1[16 * H];
     __shared__ float s_b1[16];
     __shared__ float s_w2[16];
-    __shared__ __align__(16) float tA[NODE_TILE * GLD];   // dh[0:16] | go*hact[16:32] | go at [32]
-    __shared__ __align__(16) float tB[NODE_TILE * GLD];   // emb row
-    __shared__ float scratch[16 * H];
+    __shared__ float s_mean[H], s_inv[H];
+    __shared__ __align__(16) float tA[NODE_TILE * GLD];   // dh[0:16] | go*hact[16:32] | go at [32]   then  G row
+    __shared__ __align__(16) float tB[NODE_TILE * GLD];   // emb row                                   then  G*xhat row
+    __shared__ __align__(16) float scratch[1024];
     const int t = threadIdx.x;
     for (int i = t; i < 16 * H; i += NODE_TILE) s_w1[i] = w1[i];
     if (t < 16) { s_b1[t] = b1[t]; s_w2[t] = w2[t]; }
+    if (t < H) { s_mean[t] = bo.stat[t]; s_inv[t] = bo.stat[2 * H + t]; }
     __syncthreads();
     Outer<16, H> oW1; oW1.zero();
     ColSum<GLD> cs; cs.zero();   // columns 0..15 = db1, 16..31 = dW2, 32 = db2
+    ColSum<H> sg, sgx; sg.zero(); sgx.zero();
     const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
     for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const int node0 = tile * NODE_TILE, rows = min(NODE_TILE, N - node0);
+        float gx[H];
         if (t < rows) {
             const int n = node0 + t;
-            float xr[H], hdn[16], dh[16], gx[H];
+            const int src = perm ? perm[n] : n;
+            float xr[H], hdn[16], dh[16];
             load_row32(emb + (size_t)n * H, xr);
             dense_smem<H, 16>(s_w1, s_b1, xr, hdn);
-            const float w = out[n];
-            const float go = grad_out[n] * (apply_sigmoid ? w * (1.f - w) : 1.f);
+            const float w = out[src];
+            const float go = grad_out[src] * (apply_sigmoid ? w * (1.f - w) : 1.f);
             float *ra = tA + t * GLD;
 #pragma unroll
             for (int k = 0; k < 16; ++k) {
@@ -221,142 +290,129 @@ k_head_bwd(const float *__restrict__ emb, const float *__restrict__ out, const f
         oW1.accumulate(tA, GLD, tB, GLD, rows);
         cs.accumulate(tA, GLD, rows);
         __syncthreads();
+        if (t < rows) {   // BatchNorm sums of the layer below: G and G * xhat
+            float raw[H];
+            load_row32(bo.raw + (size_t)(node0 + t) * H, raw);
+            store_row<H>(tA + t * GLD, gx);
+#pragma unroll
+            for (int k = 0; k < H; ++k) raw[k] = gx[k] * ((raw[k] - s_mean[k]) * s_inv[k]);
+            store_row<H>(tB + t * GLD, raw);
+        }
+        __syncthreads();
+        sg.accumulate(tA, GLD, rows);
+        sgx.accumulate(tB, GLD, rows);
+        __syncthreads();
     }
     float *dst = gpart + (size_t)blockIdx.x * GP_STRIDE;
     oW1.flush(scratch, dst);
     cs.flush(scratch, dst + 512, 33);
-}
-
-// ----------------------------------------------------------------------------------------- BatchNorm backward
-// stat: mean[32], scale[32] (= gamma*invstd), invstd[32], beta[32]
-__global__ void __launch_bounds__(BNB_THREADS) k_bn_bwd_reduce(const float4 *__restrict__ G, const float4 *__restrict__ raw,
-                                                               const float *__restrict__ stat, size_t n4,
-                                                               float *__restrict__ part) {
-    __shared__ float sm[BNB_THREADS][9];
-    const int t = threadIdx.x;
-    const int c = (t & 7) * 4;   // gridDim.x*blockDim.x is a multiple of 8 => a thread keeps its channels
-    float mean[4], inv[4], sg[4] = {0.f, 0.f, 0.f, 0.f}, sgx[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { mean[k] = stat[c + k]; inv[k] = stat[2 * H + c + k]; }
-    for (size_t i = (size_t)blockIdx.x * BNB_THREADS + t; i < n4; i += (size_t)gridDim.x * BNB_THREADS) {
-        const float4 g = G[i], r = raw[i];
-        sg[0] += g.x; sgx[0] = fmaf(g.x, (r.x - mean[0]) * inv[0], sgx[0]);
-        sg[1] += g.y; sgx[1] = fmaf(g.y, (r.y - mean[1]) * inv[1], sgx[1]);
-        sg[2] += g.z; sgx[2] = fmaf(g.z, (r.z - mean[2]) * inv[2], sgx[2]);
-        sg[3] += g.w; sgx[3] = fmaf(g.w, (r.w - mean[3]) * inv[3], sgx[3]);
-    }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { sm[t][k] = sg[k]; sm[t][4 + k] = sgx[k]; }
-    __syncthreads();
-    if (t < 64) {  // t<32: sum G of channel t ; t>=32: sum G*xhat of channel t-32
-        const int ch = t & 31, which = t >> 5;
-        const int lane8 = ch >> 2, sub = ch & 3;
-        float acc = 0.f;
-        for (int k = lane8; k < BNB_THREADS; k += 8) acc += sm[k][which * 4 + sub];
-        part[(size_t)blockIdx.x * 64 + t] = acc;
-    }
-}
-
-__global__ void __launch_bounds__(BNB_THREADS) k_bn_bwd_apply(const float4 *__restrict__ G, const float4 *__restrict__ raw,
-                                                              const float *__restrict__ stat, const float *__restrict__ part,
-                                                              int nblk, int N, int training, float *__restrict__ dgamma,
-                                                              float *__restrict__ dbeta, float4 *__restrict__ DC, size_t n4) {
-    __shared__ float s_sum[64];
-    __shared__ float s_stat[BNSTAT_STRIDE];
-    const int t = threadIdx.x;
-    if (t < 64) {
-        float acc = 0.f;
-        for (int b = 0; b < nblk; ++b) acc += part[(size_t)b * 64 + t];
-        s_sum[t] = acc;
-        if (blockIdx.x == 0) {
-            if (t < 32) { if (dbeta) dbeta[t] = acc; }
-            else if (dgamma) dgamma[t - 32] = acc;
-        }
-    }
-    if (t < BNSTAT_STRIDE) s_stat[t] = stat[t];
-    __syncthreads();
-    const float inv_n = training ? 1.f / (float)N : 0.f;
-    const int c = (t & 7) * 4;
-    float mean[4], inv[4], scale[4], c1[4], c2[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        mean[k] = s_stat[c + k]; scale[k] = s_stat[H + c + k]; inv[k] = s_stat[2 * H + c + k];
-        c1[k] = s_sum[c + k] * inv_n; c2[k] = s_sum[32 + c + k] * inv_n;
-    }
-    for (size_t i = (size_t)blockIdx.x * BNB_THREADS + t; i < n4; i += (size_t)gridDim.x * BNB_THREADS) {
-        const float4 g = G[i], r = raw[i];
-        float4 o;
-        o.x = scale[0] * (g.x - c1[0] - (r.x - mean[0]) * inv[0] * c2[0]);
-        o.y = scale[1] * (g.y - c1[1] - (r.y - mean[1]) * inv[1] * c2[1]);
-        o.z = scale[2] * (g.z - c1[2] - (r.z - mean[2]) * inv[2] * c2[2]);
-        o.w = scale[3] * (g.w - c1[3] - (r.w - mean[3]) * inv[3] * c2[3]);
-        DC[i] = o;
-    }
+    float *bp = bo.part + (size_t)blockIdx.x * 64;
+    sg.flush(scratch, bp, H);
+    sgx.flush(scratch, bp + H, H);
+    if (last_cta_done(bo.counter)) bn_sums_finalize(bo, scratch);
 }
 
 // ----------------------------------------------------------------------------------------- max-aggregation routing
-// S[j][c] = sum over targets i that list j as a source of [arg(i,c) == j] * DC[i][c].
-// Warp per source j, lane = channel; the DC load is predicated on the match so only live sectors move.
-__global__ void __launch_bounds__(256) k_scatter_s(const float *__restrict__ DC, const int *__restrict__ arg,
-                                                   const int *__restrict__ rowptr_s, const int *__restrict__ col_s,
-                                                   const int *__restrict__ rowptr_tt, const int *__restrict__ col_tt,
-                                                   const int *__restrict__ use_t, int N, float *__restrict__ S) {
+// S[j][c] = sum over targets i that list j as a source of [arg(i,c) == j] * d(conv)[i][c].
+// Warp per source j; an arg row (128 B) is read by 8 lanes as int4, so one load covers FOUR targets; G and
+// raw are only touched where a channel matches (N*32 matches in total).  The four lane groups are folded
+// with a fixed pairing => deterministic.
+__global__ void __launch_bounds__(256) k_scatter_s(const float *__restrict__ G, const float *__restrict__ raw, BnBwd bn,
+                                                   const int *__restrict__ arg, const int *__restrict__ rowptr_s,
+                                                   const int *__restrict__ col_s, const int *__restrict__ rowptr_tt,
+                                                   const int *__restrict__ col_tt, const int *__restrict__ use_t, int N,
+                                                   float *__restrict__ S) {
+    __shared__ float s_coef[5 * H];
+    bn_bwd_coeffs(bn, s_coef);
+    __syncthreads();
     const bool tr = use_t ? (*use_t != 0) : true;
     const int *__restrict__ rowptr_t = tr ? rowptr_tt : rowptr_s;
     const int *__restrict__ col_t = tr ? col_tt : col_s;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
     const int warps = (gridDim.x * blockDim.x) >> 5;
+    const int4 *__restrict__ arg4 = reinterpret_cast<const int4 *>(arg);
+    const float4 *__restrict__ G4 = reinterpret_cast<const float4 *>(G);
+    const float4 *__restrict__ R4 = reinterpret_cast<const float4 *>(raw);
+    const int c0 = 4 * sub;
     for (int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; j < N; j += warps) {
-        const int beg = rowptr_t[j], end = rowptr_t[j + 1];
-        float s = 0.f;
+        const int beg = __ldg(rowptr_t + j), end = __ldg(rowptr_t + j + 1);
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int e0 = beg; e0 < end; e0 += 32) {
-            const int il = (e0 + lane < end) ? col_t[e0 + lane] : -1;
             const int nb = min(32, end - e0);
-            for (int e = 0; e < nb; e += 4) {
-                int i[4], a[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    i[u] = __shfl_sync(0xffffffffu, il, (e + u) & 31);
-                    a[u] = (e + u < nb) ? arg[(size_t)i[u] * H + lane] : -1;
+            const int il = lane < nb ? __ldg(col_t + e0 + lane) : -1;
+#pragma unroll 2
+            for (int k = 0; k < nb; k += 8) {
+                const int ia = __shfl_sync(0xffffffffu, il, k + grp);
+                const int ib = __shfl_sync(0xffffffffu, il, (k + 4 + grp) & 31);
+                const bool va = k + grp < nb, vb = k + 4 + grp < nb;
+                int4 aa = make_int4(-1, -1, -1, -1), ab = aa;
+                if (va) aa = __ldg(arg4 + (size_t)ia * (H / 4) + sub);
+                if (vb) ab = __ldg(arg4 + (size_t)ib * (H / 4) + sub);
+                if (aa.x == j || aa.y == j || aa.z == j || aa.w == j) {
+                    const float4 g = __ldg(G4 + (size_t)ia * (H / 4) + sub), r = __ldg(R4 + (size_t)ia * (H / 4) + sub);
+                    if (aa.x == j) s.x += bn_bwd_one(s_coef, c0 + 0, g.x, r.x);
+                    if (aa.y == j) s.y += bn_bwd_one(s_coef, c0 + 1, g.y, r.y);
+                    if (aa.z == j) s.z += bn_bwd_one(s_coef, c0 + 2, g.z, r.z);
+                    if (aa.w == j) s.w += bn_bwd_one(s_coef, c0 + 3, g.w, r.w);
                 }
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    if (a[u] == j) s += DC[(size_t)i[u] * H + lane];
+                if (ab.x == j || ab.y == j || ab.z == j || ab.w == j) {
+                    const float4 g = __ldg(G4 + (size_t)ib * (H / 4) + sub), r = __ldg(R4 + (size_t)ib * (H / 4) + sub);
+                    if (ab.x == j) s.x += bn_bwd_one(s_coef, c0 + 0, g.x, r.x);
+                    if (ab.y == j) s.y += bn_bwd_one(s_coef, c0 + 1, g.y, r.y);
+                    if (ab.z == j) s.z += bn_bwd_one(s_coef, c0 + 2, g.z, r.z);
+                    if (ab.w == j) s.w += bn_bwd_one(s_coef, c0 + 3, g.w, r.w);
+                }
             }
         }
-        S[(size_t)j * H + lane] = s;
+#pragma unroll
+        for (int off = 8; off <= 16; off <<= 1) {
+            const float ox = __shfl_xor_sync(0xffffffffu, s.x, off), oy = __shfl_xor_sync(0xffffffffu, s.y, off);
+            const float oz = __shfl_xor_sync(0xffffffffu, s.z, off), ow = __shfl_xor_sync(0xffffffffu, s.w, off);
+            const bool lo = (lane & off) == 0;
+            s.x = lo ? s.x + ox : ox + s.x; s.y = lo ? s.y + oy : oy + s.y;
+            s.z = lo ? s.z + oz : oz + s.z; s.w = lo ? s.w + ow : ow + s.w;
+        }
+        if (grp == 0) reinterpret_cast<float4 *>(S)[(size_t)j * (H / 4) + sub] = s;
     }
 }
 
 // ----------------------------------------------------------------------------------------- EdgeConv node-level backward
 // partial layout: dW1[32][32] @0, dW2[32][32] @1024, db[32] @2048
 __global__ void __launch_bounds__(NODE_TILE, 2)
-k_conv_bwd_node(const float *__restrict__ x, const float *__restrict__ DC, const float *__restrict__ S, int N,
-                const float *__restrict__ W, float *__restrict__ G, float *__restrict__ gpart) {
+k_conv_bwd_node(const float *__restrict__ x, const float *__restrict__ raw, BnBwd bn, const float *__restrict__ S, int N,
+                const float *__restrict__ W, float *__restrict__ G, float *__restrict__ gpart, BnSumOut bo) {
     extern __shared__ __align__(16) float smem[];
     float *s_wd = smem;                  // W1 - W2, [c][k]
     float *s_w2 = s_wd + H * H;
-    float *tA = s_w2 + H * H;
-    float *tB = tA + NODE_TILE * GLD;
-    float *tC = tB + NODE_TILE * GLD;
+    float *tA = s_w2 + H * H;            // d(conv)            then  G_new
+    float *tB = tA + NODE_TILE * GLD;    // x                  then  G_new * xhat(below)
+    float *tC = tB + NODE_TILE * GLD;    // S - d(conv)
+    float *s_coef = tC + NODE_TILE * GLD;   // [5][32]
+    float *s_mean = s_coef + 5 * H;      // BatchNorm below: mean, invstd
+    float *s_inv = s_mean + H;
     const int t = threadIdx.x;
     for (int i = t; i < H * H; i += NODE_TILE) {
         const int c = i >> 5, k = i & 31;
         const float a = W[c * CONV_IN + k], b = W[c * CONV_IN + H + k];
         s_wd[i] = a - b; s_w2[i] = b;
     }
+    bn_bwd_coeffs(bn, s_coef);
+    if (t < H) { s_mean[t] = bo.stat[t]; s_inv[t] = bo.stat[2 * H + t]; }
     __syncthreads();
     Outer<H, H> o1, o2; o1.zero(); o2.zero();
-    ColSum<H> cb; cb.zero();
+    ColSum<H> cb, sg, sgx; cb.zero(); sg.zero(); sgx.zero();
     const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
     for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const int node0 = tile * NODE_TILE, rows = min(NODE_TILE, N - node0);
+        float g[H];
         if (t < rows) {
             const size_t n = (size_t)(node0 + t) * H;
-            float dc[H], s[H], tmp[H], g[H];
-            load_row32(DC + n, dc);
-            load_row32(S + n, s);
+            float dc[H], s[H], tmp[H];
             load_row32(G + n, g);
+            load_row32(raw + n, tmp);
+#pragma unroll
+            for (int k = 0; k < H; ++k) dc[k] = bn_bwd_one(s_coef, k, g[k], tmp[k]);
+            load_row32(S + n, s);
             dense_t_smem<H, H>(s_wd, dc, tmp);
 #pragma unroll
             for (int k = 0; k < H; ++k) g[k] += tmp[k];
@@ -376,11 +432,27 @@ k_conv_bwd_node(const float *__restrict__ x, const float *__restrict__ DC, const
         o2.accumulate(tC, GLD, tB, GLD, rows);
         cb.accumulate(tA, GLD, rows);
         __syncthreads();
+        if (t < rows) {   // BatchNorm sums of the layer below (bn_all for layer 0)
+            float rb[H];
+            load_row32(bo.raw + (size_t)(node0 + t) * H, rb);
+            store_row<H>(tA + t * GLD, g);
+#pragma unroll
+            for (int k = 0; k < H; ++k) rb[k] = g[k] * ((rb[k] - s_mean[k]) * s_inv[k]);
+            store_row<H>(tB + t * GLD, rb);
+        }
+        __syncthreads();
+        sg.accumulate(tA, GLD, rows);
+        sgx.accumulate(tB, GLD, rows);
+        __syncthreads();
     }
     float *dst = gpart + (size_t)blockIdx.x * GP_STRIDE;
     o1.flush(tA, dst);
     o2.flush(tA, dst + 1024);
     cb.flush(tA, dst + 2048, H);
+    float *bp = bo.part + (size_t)blockIdx.x * 64;
+    sg.flush(tA, bp, H);
+    sgx.flush(tA, bp + H, H);
+    if (last_cta_done(bo.counter)) bn_sums_finalize(bo, tA);
 }
 
 // ----------------------------------------------------------------------------------------- encoder backward
@@ -390,10 +462,12 @@ struct EncBwdArgs {
     const float *x_cont; int x_cont_stride;
     const long long *x_cat_i64;
     const float *x_cat_f32; int x_cat_stride;
+    const int *perm;
     int N, CD;
     const float *cont_w, *cont_b, *cat_w, *enc_w, *lut, *e_chrg, *e_pdg, *e_pv;
-    const float *enc;      // [N,32] forward ELU(encode_all) output
-    const float *DA;       // [N,32] gradient w.r.t. enc (after BN_all backward)
+    const float *enc;      // [N,32] forward ELU(encode_all) output (pre-BatchNorm)
+    const float *G;        // [N,32] gradient w.r.t. emb_0 = bn_all(enc)
+    BnBwd bn;
     float *gpart;
 };
 
@@ -409,6 +483,7 @@ __global__ void __launch_bounds__(NODE_TILE, 2) k_encode_bwd(EncBwdArgs a) {
     float *tB = tA + NODE_TILE * GLD;            // NODE_TILE*GLD
     float *scratch = tB + NODE_TILE * GLD;       // 1024
     int *s_idx = reinterpret_cast<int *>(scratch + 1024);  // NODE_TILE
+    float *s_coef = reinterpret_cast<float *>(s_idx + NODE_TILE);   // 160
     const int t = threadIdx.x;
     for (int i = t; i < H * H; i += NODE_TILE) s_enc_w[i] = a.enc_w[i];
     for (int i = t; i < 128; i += NODE_TILE) { int o = i >> 3, k = i & 7; s_cont_w[i] = k < a.CD ? a.cont_w[o * a.CD + k] : 0.f; }
@@ -417,6 +492,7 @@ __global__ void __launch_bounds__(NODE_TILE, 2) k_encode_bwd(EncBwdArgs a) {
     for (int i = t; i < LUT_ROWS * 16; i += NODE_TILE) s_lut[i] = a.lut[i];
     for (int i = t; i < 144; i += NODE_TILE)
         s_tab[i] = i < 24 ? a.e_chrg[i] : (i < 80 ? a.e_pdg[i - 24] : a.e_pv[i - 80]);
+    bn_bwd_coeffs(a.bn, s_coef);
     __syncthreads();
 
     Outer<H, H> oA; oA.zero();
@@ -434,12 +510,13 @@ __global__ void __launch_bounds__(NODE_TILE, 2) k_encode_bwd(EncBwdArgs a) {
         int ic = 0, ip = 0, iv = 0;
         if (t < rows) {
             const size_t n = node0 + t;
-            const float *row = a.x_cont + n * a.x_cont_stride;
+            const size_t src = a.perm ? (size_t)a.perm[n] : n;
+            const float *row = a.x_cont + src * a.x_cont_stride;
 #pragma unroll
             for (int k = 0; k < 8; ++k) xc[k] = k < a.CD ? row[k] : 0.f;
             long long c0, c1, c2;
-            if (a.x_cat_i64) { const long long *cr = a.x_cat_i64 + n * 3; c0 = cr[0]; c1 = cr[1]; c2 = cr[2]; }
-            else { const float *cr = a.x_cat_f32 + n * a.x_cat_stride; c0 = (long long)cr[0]; c1 = (long long)cr[1]; c2 = (long long)cr[2]; }
+            if (a.x_cat_i64) { const long long *cr = a.x_cat_i64 + src * 3; c0 = cr[0]; c1 = cr[1]; c2 = cr[2]; }
+            else { const float *cr = a.x_cat_f32 + src * a.x_cat_stride; c0 = (long long)cr[0]; c1 = (long long)cr[1]; c2 = (long long)cr[2]; }
             long long lc = c1 + 1, lp = pdg_remap(c0), lv = c2;   // clamp exactly like the forward
             ic = (int)(lc < 0 ? 0 : (lc > 2 ? 2 : lc));
             ip = (int)(lp < 0 ? 0 : (lp > 6 ? 6 : lp));
@@ -452,9 +529,9 @@ __global__ void __launch_bounds__(NODE_TILE, 2) k_encode_bwd(EncBwdArgs a) {
 #pragma unroll
             for (int k = 0; k < 16; ++k) { hact[k] = elu(h0[k]); u[16 + k] = hact[k]; }
             load_row32(a.enc + n * H, a0);
-            load_row32(a.DA + n * H, dz);
+            load_row32(a.G + n * H, dz);
 #pragma unroll
-            for (int k = 0; k < H; ++k) dz[k] *= elu_grad_from_out(a0[k]);
+            for (int k = 0; k < H; ++k) dz[k] = bn_bwd_one(s_coef, k, dz[k], a0[k]) * elu_grad_from_out(a0[k]);
             store_row<H>(tA + t * GLD, dz);
             store_row<H>(tB + t * GLD, u);
             dense_t_smem<H, H>(s_enc_w, dz, du);
@@ -529,21 +606,9 @@ __global__ void __launch_bounds__(NODE_TILE, 2) k_encode_bwd(EncBwdArgs a) {
     }
 }
 
-constexpr size_t CONV_BWD_SMEM = (size_t)(2 * H * H + 3 * NODE_TILE * GLD) * 4;
-constexpr size_t ENC_BWD_SMEM = (size_t)(H * H + 128 + 16 + 384 + LUT_ROWS * 16 + 144 + 2 * NODE_TILE * GLD + 1024 + NODE_TILE) * 4;
-
-int bn_backward(const float *G, const float *raw, const float *stat, int N, int training, float *dgamma, float *dbeta,
-                float *DC, const BwdWs &w, cudaStream_t st) {
-    const size_t n4 = (size_t)N * (H / 4);
-    const int grid = persistent_grid((long long)((n4 + BNB_THREADS - 1) / BNB_THREADS), 2);
-    k_bn_bwd_reduce<<<grid, BNB_THREADS, 0, st>>>((const float4 *)G, (const float4 *)raw, stat, n4, w.bnpart);
-    GM_LAUNCH_CHECK();
-    const int grid2 = persistent_grid((long long)((n4 + BNB_THREADS - 1) / BNB_THREADS), 8);
-    k_bn_bwd_apply<<<grid2, BNB_THREADS, 0, st>>>((const float4 *)G, (const float4 *)raw, stat, w.bnpart, grid, N,
-                                                  training, dgamma, dbeta, (float4 *)DC, n4);
-    GM_LAUNCH_CHECK();
-    return GM_OK;
-}
+constexpr size_t CONV_BWD_SMEM = (size_t)(2 * H * H + 3 * NODE_TILE * GLD + 5 * H + 2 * H) * 4;
+constexpr size_t ENC_BWD_SMEM =
+    (size_t)(H * H + 128 + 16 + 384 + LUT_ROWS * 16 + 144 + 2 * NODE_TILE * GLD + 1024 + NODE_TILE + 5 * H) * 4;
 
 }  // namespace
 
@@ -563,8 +628,9 @@ size_t gm_net_bwd_ws_bytes(int N, int conv_depth) {
 int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
                     const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride, const int *rowptr,
                     const int *col, const int *rowptr_t, const int *col_t, const int *use_transposed_flag, int N,
-                    int training, int apply_sigmoid, int aggr, float eps, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
-                    const float *out, const float *grad_out, void *stream) {
+                    const int *node_perm, int training, int apply_sigmoid, int aggr, float eps, const void *fwd_ws,
+                    size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes, const float *out, const float *grad_out,
+                    void *stream) {
     (void)eps;
     GM_TRY(check_params(p));
     if (!grads || N < 0 || !fwd_ws || !bwd_ws) return GM_ERR_INVALID_ARGUMENT;
@@ -582,71 +648,93 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
     bwd_ws_layout(N, (char *)bwd_ws, &w);
     const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
     const int ngrid = persistent_grid(tiles, 2);
+    const float inv_n = training ? 1.f / (float)N : 0.f;
+    GM_CUDA_TRY(cudaMemsetAsync(w.counters, 0, NUM_COUNTERS * sizeof(int), st));
 
-    // ---- head
-    k_head_bwd<<<ngrid, NODE_TILE, 0, st>>>(f.emb[depth], out, grad_out, N, p->out1_w, p->out1_b, p->out2_w,
-                                            apply_sigmoid, w.G, w.gpart);
-    GM_LAUNCH_CHECK();
+    auto gpart = [&](int stage) { return w.gpart + (size_t)stage * MAX_BWD_CTAS * GP_STRIDE; };
+    // BatchNorm index b: 0 = bn_all (raw = enc), l+1 = conv_bn[l] (raw = conv[l])
+    auto bn_raw = [&](int b) { return b == 0 ? (const float *)f.enc : (const float *)f.conv[b - 1]; };
+    auto bn_stat = [&](int b) { return (const float *)(f.bnstat + (size_t)b * BNSTAT_STRIDE); };
+    auto bn_sum = [&](int b) { return w.bnsum + (size_t)b * 64; };
+    auto bn_grads = [&](int b) -> const GmBatchNorm & { return b == 0 ? grads->bn_all : grads->conv_bn[b - 1]; };
+    auto sum_out = [&](int b) {
+        return BnSumOut{bn_raw(b), bn_stat(b), w.bnpart, bn_sum(b), bn_grads(b).weight, bn_grads(b).bias,
+                        w.counters + b};
+    };
+    auto bn_in = [&](int b) { return BnBwd{bn_stat(b), bn_sum(b), inv_n}; };
+
+    Segs segs{};
+    auto add_seg = [&](int stage, float *dst, int dst_ld, int off, int rows, int src_ld, int cols) {
+        if (dst) segs.s[segs.n++] = Seg{gpart(stage), dst, dst_ld, off, rows, src_ld, cols, ngrid};
+    };
+
+    // ---- head (stage 0); also produces the BatchNorm sums of the topmost BatchNorm (index depth)
     {
-        Segs s{};
-        s.n = 4;
-        s.s[0] = Seg{grads->out1_w, H, 0, 16, H, H};
-        s.s[1] = Seg{grads->out1_b, 16, 512, 1, 16, 16};
-        s.s[2] = Seg{grads->out2_w, 16, 528, 1, 16, 16};
-        s.s[3] = Seg{grads->out2_b, 1, 544, 1, 1, 1};
-        GM_TRY(launch_reduce(w.gpart, ngrid, s, st));
-    }
-    // ---- EdgeConv layers, last to first
-    for (int l = depth - 1; l >= 0; --l) {
-        const float *stat = f.bnstat + (size_t)(l + 1) * BNSTAT_STRIDE;
-        GM_TRY(bn_backward(w.G, f.conv[l], stat, N, training, grads->conv_bn[l].weight, grads->conv_bn[l].bias, w.DC, w, st));
-        {
-            TimedRegion tr(GM_TIMER_SCATTER_S_BWD, st);
-            k_scatter_s<<<persistent_grid(((long long)N * 32 + 255) / 256, 8), 256, 0, st>>>(
-                w.DC, f.arg[l], rowptr, col, rowptr_t, col_t, use_transposed_flag, N, w.S);
-            GM_LAUNCH_CHECK();
-        }
-        GM_CUDA_TRY(cudaFuncSetAttribute(k_conv_bwd_node, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CONV_BWD_SMEM));
-        {
-            TimedRegion tr(GM_TIMER_CONV_NODE_BWD, st);
-            k_conv_bwd_node<<<ngrid, NODE_TILE, CONV_BWD_SMEM, st>>>(f.emb[l], w.DC, w.S, N, p->conv_w[l], w.G, w.gpart);
-            GM_LAUNCH_CHECK();
-        }
-        Segs s{};
-        s.n = 3;
-        s.s[0] = Seg{grads->conv_w[l], CONV_IN, 0, H, H, H};
-        s.s[1] = Seg{grads->conv_w[l] ? grads->conv_w[l] + H : nullptr, CONV_IN, 1024, H, H, H};
-        s.s[2] = Seg{grads->conv_b[l], H, 2048, 1, H, H};
-        GM_TRY(launch_reduce(w.gpart, ngrid, s, st));
-    }
-    // ---- bn_all + encoder
-    GM_TRY(bn_backward(w.G, f.enc, f.bnstat, N, training, grads->bn_all.weight, grads->bn_all.bias, w.DC, w, st));
-    EncBwdArgs ea{};
-    ea.x_cont = x_cont; ea.x_cont_stride = x_cont_stride; ea.x_cat_i64 = (const long long *)x_cat_i64;
-    ea.x_cat_f32 = x_cat_f32; ea.x_cat_stride = x_cat_stride; ea.N = N; ea.CD = p->continuous_dim;
-    ea.cont_w = p->cont_w; ea.cont_b = p->cont_b; ea.cat_w = p->cat_w; ea.enc_w = p->enc_w; ea.lut = f.lut;
-    ea.e_chrg = p->embed_charge; ea.e_pdg = p->embed_pdgid; ea.e_pv = p->embed_pv;
-    ea.enc = f.enc; ea.DA = w.DC; ea.gpart = w.gpart;
-    GM_CUDA_TRY(cudaFuncSetAttribute(k_encode_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ENC_BWD_SMEM));
-    {
-        TimedRegion tr(GM_TIMER_ENCODE_BWD, st);
-        k_encode_bwd<<<ngrid, NODE_TILE, ENC_BWD_SMEM, st>>>(ea);
+        TimedRegion tr(GM_TIMER_HEAD_BWD, st);
+        k_head_bwd<<<ngrid, NODE_TILE, 0, st>>>(f.emb[depth], out, grad_out, node_perm, N, p->out1_w, p->out1_b,
+                                                p->out2_w, apply_sigmoid, w.G, gpart(0), sum_out(depth));
         GM_LAUNCH_CHECK();
     }
+    add_seg(0, grads->out1_w, H, 0, 16, H, H);
+    add_seg(0, grads->out1_b, 16, 512, 1, 16, 16);
+    add_seg(0, grads->out2_w, 16, 528, 1, 16, 16);
+    add_seg(0, grads->out2_b, 1, 544, 1, 1, 1);
+
+    // ---- EdgeConv layers, last to first
+    GM_CUDA_TRY(cudaFuncSetAttribute(k_conv_bwd_node, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CONV_BWD_SMEM));
+    for (int l = depth - 1; l >= 0; --l) {
+        const int stage = depth - l;
+        {
+            TimedRegion tr(GM_TIMER_SCATTER_S_BWD, st);
+            k_scatter_s<<<persistent_grid(((long long)N * 32 + 255) / 256, 4), 256, 0, st>>>(
+                w.G, f.conv[l], bn_in(l + 1), f.arg[l], rowptr, col, rowptr_t, col_t, use_transposed_flag, N, w.S);
+            GM_LAUNCH_CHECK();
+        }
+        {
+            TimedRegion tr(GM_TIMER_CONV_NODE_BWD, st);
+            k_conv_bwd_node<<<ngrid, NODE_TILE, CONV_BWD_SMEM, st>>>(f.emb[l], f.conv[l], bn_in(l + 1), w.S, N,
+                                                                     p->conv_w[l], w.G, gpart(stage), sum_out(l));
+            GM_LAUNCH_CHECK();
+        }
+        add_seg(stage, grads->conv_w[l], CONV_IN, 0, H, H, H);
+        add_seg(stage, grads->conv_w[l] ? grads->conv_w[l] + H : nullptr, CONV_IN, 1024, H, H, H);
+        add_seg(stage, grads->conv_b[l], H, 2048, 1, H, H);
+    }
+    // ---- bn_all + encoder (stage depth+1)
     {
+        const int stage = depth + 1;
+        EncBwdArgs ea{};
+        ea.x_cont = x_cont; ea.x_cont_stride = x_cont_stride; ea.x_cat_i64 = (const long long *)x_cat_i64;
+        ea.x_cat_f32 = x_cat_f32; ea.x_cat_stride = x_cat_stride; ea.perm = node_perm; ea.N = N;
+        ea.CD = p->continuous_dim;
+        ea.cont_w = p->cont_w; ea.cont_b = p->cont_b; ea.cat_w = p->cat_w; ea.enc_w = p->enc_w; ea.lut = f.lut;
+        ea.e_chrg = p->embed_charge; ea.e_pdg = p->embed_pdgid; ea.e_pv = p->embed_pv;
+        ea.enc = f.enc; ea.G = w.G; ea.bn = bn_in(0); ea.gpart = gpart(stage);
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_encode_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ENC_BWD_SMEM));
+        {
+            TimedRegion tr(GM_TIMER_ENCODE_BWD, st);
+            k_encode_bwd<<<ngrid, NODE_TILE, ENC_BWD_SMEM, st>>>(ea);
+            GM_LAUNCH_CHECK();
+        }
         const int CD = p->continuous_dim;
-        Segs s{};
-        s.n = 9;
-        s.s[0] = Seg{grads->enc_w, H, 0, H, H, H};
-        s.s[1] = Seg{grads->enc_b, H, 1024, 1, H, H};
-        s.s[2] = Seg{grads->cont_w, CD, 1056, 16, 8, CD};
-        s.s[3] = Seg{grads->cont_b, 16, 1184, 1, 16, 16};
-        s.s[4] = Seg{grads->cat_w, 24, 1200, 16, 24, 24};
-        s.s[5] = Seg{grads->cat_b, 16, 1584, 1, 16, 16};
-        s.s[6] = Seg{grads->embed_charge, 8, 1600, 3, 8, 8};
-        s.s[7] = Seg{grads->embed_pdgid, 8, 1624, 7, 8, 8};
-        s.s[8] = Seg{grads->embed_pv, 8, 1680, 8, 8, 8};
-        GM_TRY(launch_reduce(w.gpart, ngrid, s, st));
+        add_seg(stage, grads->enc_w, H, 0, H, H, H);
+        add_seg(stage, grads->enc_b, H, 1024, 1, H, H);
+        add_seg(stage, grads->cont_w, CD, 1056, 16, 8, CD);
+        add_seg(stage, grads->cont_b, 16, 1184, 1, 16, 16);
+        add_seg(stage, grads->cat_w, 24, 1200, 16, 24, 24);
+        add_seg(stage, grads->cat_b, 16, 1584, 1, 16, 16);
+        add_seg(stage, grads->embed_charge, 8, 1600, 3, 8, 8);
+        add_seg(stage, grads->embed_pdgid, 8, 1624, 7, 8, 8);
+        add_seg(stage, grads->embed_pv, 8, 1680, 8, 8, 8);
+    }
+    {
+        int max_total = 0;
+        for (int k = 0; k < segs.n; ++k) max_total = max(max_total, segs.s[k].rows * segs.s[k].cols);
+        if (segs.n > 0) {
+            dim3 grid((max_total + 31) / 32, segs.n);
+            k_reduce_partials<<<grid, 256, 0, st>>>(segs);
+            GM_LAUNCH_CHECK();
+        }
     }
     return GM_OK;
 }

@@ -1,10 +1,12 @@
 // Forward of the GraphMETNetwork hot path (model/graph_met_network.py:47-69, model/net.py:45-47):
 //   k_build_lut   : the 168-entry categorical table ELU(Linear_24->16(cat[E_chrg,E_pdg,E_pv]))
 //   k_encode      : fused embeddings + continuous encoder + encode_all (+ BatchNorm moments)   [a3,a4]
-//   k_bn_finalize : deterministic combination of per-CTA moments, running-stat update        [K4]
-//   k_bn_apply    : emb = (resid +) (raw - mean) * gamma*invstd + beta
-//   k_edgeconv_simt: fp32 EdgeConv, warp per target, FFMA2 edge contraction, segmented max     [a5]
-//   k_head        : Linear_32->16 + ELU + Linear_16->1 (+ sigmoid)                              [a6]
+//   k_node_prep   : emb_l = (resid +) BN(raw) ; Y = W2 emb_l ; P = (W1-W2) emb_l + b            [K4 + a5, node side]
+//   k_edge_aggr   : out_i = P_i + max_j Y_j over the CSR row (segmented, atomics-free) + BN moments [a5, edge side]
+//   k_edgeconv_simt: fp32 EdgeConv with the per-edge contraction W2 (x_j - x_i) spelled out (cross-check variant)
+//   k_head        : emb_L = resid + BN(raw) ; Linear_32->16 + ELU + Linear_16->1 (+ sigmoid)    [a6]
+// BatchNorm statistics (train mode) are combined by the LAST CTA of the producing kernel in a fixed order
+// (bn_finalize_cta): no separate launch, no CTA ever waits on another, bit-deterministic.
 #include "net_layout.cuh"
 
 namespace gm {
@@ -16,8 +18,22 @@ int edgeconv_tc_forward(const float *x, const int *rowptr, const int *col, int N
 namespace {
 
 // ------------------------------------------------------------------------------------------ LUT
-__global__ void __launch_bounds__(256) k_build_lut(GmParams p, float *__restrict__ lut) {
+__global__ void __launch_bounds__(256) k_build_lut(GmParams p, float *__restrict__ lut, int *__restrict__ counters,
+                                                   float *__restrict__ bnstat, int training, float eps) {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < NUM_COUNTERS) counters[idx] = 0;
+    if (!training && blockIdx.x == 0) {      // eval mode: BatchNorm is a fixed affine of the running statistics
+        for (int k = threadIdx.x; k < (p.conv_depth + 1) * H; k += blockDim.x) {
+            const int l = k >> 5, c = k & 31;
+            const GmBatchNorm &bn = l == 0 ? p.bn_all : p.conv_bn[l - 1];
+            const float invstd = 1.0f / sqrtf(bn.running_var[c] + eps);
+            float *stat = bnstat + (size_t)l * BNSTAT_STRIDE;
+            stat[c] = bn.running_mean[c];
+            stat[H + c] = bn.weight[c] * invstd;
+            stat[2 * H + c] = invstd;
+            stat[3 * H + c] = bn.bias[c];
+        }
+    }
     if (idx >= LUT_ROWS * 16) return;
     const int o = idx & 15, combo = idx >> 4;
     const int pv = combo & 7, pdg = (combo >> 3) % 7, ch = (combo >> 3) / 7;
@@ -62,24 +78,18 @@ __device__ __forceinline__ void store_tile(const float *tile, float *__restrict_
     }
 }
 
-__device__ __forceinline__ void load_tile(float *tile, const float *__restrict__ in, int node0, int rows) {
-    for (int idx = threadIdx.x; idx < rows * (H / 4); idx += blockDim.x) {
-        int r = idx >> 3, c4 = (idx & 7) * 4;
-        float4 v = reinterpret_cast<const float4 *>(in + (size_t)(node0 + r) * H)[idx & 7];
-        float *d = tile + r * TILE_LD + c4;
-        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-    }
-}
-
 // ------------------------------------------------------------------------------------------ encoder
 struct EncodeArgs {
     const float *x_cont; int x_cont_stride;
     const long long *x_cat_i64;
     const float *x_cat_f32; int x_cat_stride;
-    int N, CD, flat;          // flat: x_cont/x_cat_f32 are columns of one [N, stride] matrix (stride <= 16)
+    const int *perm;          // internal position -> input row (NULL = identity)
+    int N, CD, flat;          // flat: x_cont/x_cat_f32 are columns of one [N, stride] matrix (stride <= 16), no perm
     const float *cont_w, *cont_b, *enc_w, *enc_b, *lut;
     float *enc_out;           // [N,32]
-    float *partials;          // [grid][3][32] or NULL
+    float *partials;          // [grid][3][32] or NULL (eval mode)
+    int *counter;             // last-CTA ticket (train mode)
+    GmBatchNorm bn; float momentum, eps; float *stat;
     int *err_flags;
 };
 
@@ -102,7 +112,7 @@ __global__ void __launch_bounds__(NODE_TILE) k_encode(EncodeArgs a) {
     __shared__ __align__(16) float s_lut[LUT_ROWS * 16];
     __shared__ __align__(16) float s_x[NODE_TILE * 16];
     __shared__ float s_tile[NODE_TILE * TILE_LD];
-    __shared__ float s_red[NODE_TILE / 32][3][H];
+    __shared__ float s_red[NODE_TILE / 8][3][H];   // tile_moments uses 4 slices, the last-CTA finalize all 16
 
     const int t = threadIdx.x;
     for (int i = t; i < 16 * 8; i += NODE_TILE) {
@@ -136,14 +146,15 @@ __global__ void __launch_bounds__(NODE_TILE) k_encode(EncodeArgs a) {
                 c0 = (long long)row[cat_off]; c1 = (long long)row[cat_off + 1]; c2 = (long long)row[cat_off + 2];
             }
         } else if (t < rows) {
-            const float *row = a.x_cont + (size_t)(node0 + t) * a.x_cont_stride;
+            const size_t n = a.perm ? (size_t)a.perm[node0 + t] : (size_t)(node0 + t);
+            const float *row = a.x_cont + n * a.x_cont_stride;
 #pragma unroll
             for (int k = 0; k < 8; ++k) xc[k] = k < a.CD ? row[k] : 0.f;
             if (a.x_cat_i64) {
-                const long long *cr = a.x_cat_i64 + (size_t)(node0 + t) * 3;
+                const long long *cr = a.x_cat_i64 + n * 3;
                 c0 = cr[0]; c1 = cr[1]; c2 = cr[2];
             } else {
-                const float *cr = a.x_cat_f32 + (size_t)(node0 + t) * a.x_cat_stride;
+                const float *cr = a.x_cat_f32 + n * a.x_cat_stride;
                 c0 = (long long)cr[0]; c1 = (long long)cr[1]; c2 = (long long)cr[2];
             }
         }
@@ -170,72 +181,230 @@ __global__ void __launch_bounds__(NODE_TILE) k_encode(EncodeArgs a) {
         if (a.partials) tile_moments(s_tile, rows, s_red, run);
         else __syncthreads();
     }
-    if (a.partials && t < 32) {
-        float *dst = a.partials + (size_t)blockIdx.x * MOM_STRIDE;
-        dst[t] = run.n; dst[H + t] = run.mean; dst[2 * H + t] = run.m2;
-    }
     if (err) atomicOr(a.err_flags, GM_FLAG_CAT_OUT_OF_RANGE);
-}
-
-// ------------------------------------------------------------------------------------------ BatchNorm
-// One CTA of 1024 threads: thread (c = t%32, s = t/32) folds partial CTAs s, s+32, ... then the 32
-// slices are folded in order.  Fixed order => bit-deterministic.  ATen semantics:
-// biased variance for normalisation, unbiased for running_var, momentum update, counter += 1.
-__global__ void __launch_bounds__(1024) k_bn_finalize(const float *__restrict__ partials, int n_partials,
-                                                      GmBatchNorm bn, float momentum, float eps, int training,
-                                                      float *__restrict__ stat) {
-    __shared__ float red[32][3][H];
-    const int c = threadIdx.x & 31, s = threadIdx.x >> 5;
-    if (training) {
-        Moments m{0.f, 0.f, 0.f};
-#pragma unroll 4
-        for (int b = s; b < n_partials; b += 32) {
-            const float *p = partials + (size_t)b * MOM_STRIDE;
-            m = moments_combine(m, Moments{p[c], p[H + c], p[2 * H + c]});
+    if (a.partials) {
+        if (t < 32) {
+            float *dst = a.partials + (size_t)blockIdx.x * MOM_STRIDE;
+            dst[t] = run.n; dst[H + t] = run.mean; dst[2 * H + t] = run.m2;
         }
-        red[s][0][c] = m.n; red[s][1][c] = m.mean; red[s][2][c] = m.m2;
-        __syncthreads();
-        if (s == 0) {
-            Moments tot{0.f, 0.f, 0.f};
-            for (int k = 0; k < 32; ++k) tot = moments_combine(tot, Moments{red[k][0][c], red[k][1][c], red[k][2][c]});
-            const float var = tot.n > 0.f ? tot.m2 / tot.n : 0.f;
-            const float invstd = 1.0f / sqrtf(var + eps);
-            stat[c] = tot.mean;
-            stat[H + c] = bn.weight[c] * invstd;
-            stat[2 * H + c] = invstd;
-            stat[3 * H + c] = bn.bias[c];
-            if (bn.running_mean) {
-                const float unbiased = tot.n > 1.f ? tot.m2 / (tot.n - 1.f) : var;
-                bn.running_mean[c] = (1.f - momentum) * bn.running_mean[c] + momentum * tot.mean;
-                bn.running_var[c] = (1.f - momentum) * bn.running_var[c] + momentum * unbiased;
-            }
-            if (c == 0 && bn.num_batches_tracked) *bn.num_batches_tracked += 1;
-        }
-    } else if (s == 0) {
-        const float invstd = 1.0f / sqrtf(bn.running_var[c] + eps);
-        stat[c] = bn.running_mean[c];
-        stat[H + c] = bn.weight[c] * invstd;
-        stat[2 * H + c] = invstd;
-        stat[3 * H + c] = bn.bias[c];
+        if (last_cta_done(a.counter))
+            bn_finalize_cta(a.partials, gridDim.x, a.bn, a.momentum, a.eps, a.stat, s_red);
     }
 }
 
-__global__ void __launch_bounds__(256) k_bn_apply(const float4 *__restrict__ raw, const float4 *__restrict__ resid,
-                                                  const float *__restrict__ stat, float4 *__restrict__ out,
-                                                  size_t n4) {
+// ------------------------------------------------------------------------------------------ BatchNorm (TC path only)
+// Stand-alone finalize for producers that do not carry the last-CTA epilogue (the tcgen05 EdgeConv kernel).
+__global__ void __launch_bounds__(256) k_bn_finalize(const float *__restrict__ partials, int n_partials,
+                                                     GmBatchNorm bn, float momentum, float eps,
+                                                     float *__restrict__ stat) {
+    __shared__ float red[32][3][H];
+    bn_finalize_cta(partials, n_partials, bn, momentum, eps, stat, red);
+}
+
+// ------------------------------------------------------------------------------------------ EdgeConv, node side
+// The single-Linear edge MLP of the reference (model/graph_met_network.py:34-38) splits exactly:
+//     W [x_i ; x_j - x_i] + b  =  (W1 - W2) x_i + b  +  W2 x_j   =  P_i + Y_j ,
+// so max_j / sum_j only ever touch Y_j.  This kernel materialises, in ONE pass over the nodes,
+//     emb = (resid +) BN(raw)      the layer input (previous BatchNorm + residual folded in, K4)
+//     Y   = W2 emb                 what the edge side gathers
+//     P   = (W1 - W2) emb + b      the per-target term
+// Thread per node, weights broadcast from shared memory, coalesced tile loads/stores.
+template <bool WRITE_YP>
+__global__ void __launch_bounds__(NODE_TILE)
+k_node_prep(const float *__restrict__ raw, const float *__restrict__ resid, const float *__restrict__ stat,
+            const float *__restrict__ W, const float *__restrict__ bias, int N, float *__restrict__ emb_out,
+            float *__restrict__ Y, float *__restrict__ P) {
+    __shared__ __align__(16) float s_wd[H * H];     // W1 - W2, [c][k]
+    __shared__ __align__(16) float s_w2[H * H];
+    __shared__ float s_b[H], s_zero[H];
     __shared__ float s_stat[BNSTAT_STRIDE];
-    if (threadIdx.x < BNSTAT_STRIDE) s_stat[threadIdx.x] = stat[threadIdx.x];
+    __shared__ float s_tile[NODE_TILE * TILE_LD];
+    const int t = threadIdx.x;
+    if (WRITE_YP) {
+        for (int i = t; i < H * H; i += NODE_TILE) {
+            const int c = i >> 5, k = i & 31;
+            const float w1 = W[c * CONV_IN + k], w2 = W[c * CONV_IN + H + k];
+            s_wd[i] = w1 - w2; s_w2[i] = w2;
+        }
+        if (t < H) { s_b[t] = bias[t]; s_zero[t] = 0.f; }
+    }
+    if (stat && t < BNSTAT_STRIDE) s_stat[t] = stat[t];
     __syncthreads();
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
-        const int c = (int)(i & 7) * 4;
-        float4 v = raw[i];
-        float4 r = resid ? resid[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 o;
-        o.x = r.x + fmaf(v.x - s_stat[c + 0], s_stat[H + c + 0], s_stat[3 * H + c + 0]);
-        o.y = r.y + fmaf(v.y - s_stat[c + 1], s_stat[H + c + 1], s_stat[3 * H + c + 1]);
-        o.z = r.z + fmaf(v.z - s_stat[c + 2], s_stat[H + c + 2], s_stat[3 * H + c + 2]);
-        o.w = r.w + fmaf(v.w - s_stat[c + 3], s_stat[H + c + 3], s_stat[3 * H + c + 3]);
-        out[i] = o;
+    const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const int node0 = tile * NODE_TILE, rows = min(NODE_TILE, N - node0);
+        // coalesced load with the BatchNorm affine + residual applied on the fly; emb is stored right away
+        for (int idx = t; idx < rows * (H / 4); idx += NODE_TILE) {
+            const int r = idx >> 3, c4 = (idx & 7) * 4;
+            const size_t g = (size_t)(node0 + r) * (H / 4) + (idx & 7);
+            float4 v = reinterpret_cast<const float4 *>(raw)[g];
+            if (stat) {
+                v.x = fmaf(v.x - s_stat[c4 + 0], s_stat[H + c4 + 0], s_stat[3 * H + c4 + 0]);
+                v.y = fmaf(v.y - s_stat[c4 + 1], s_stat[H + c4 + 1], s_stat[3 * H + c4 + 1]);
+                v.z = fmaf(v.z - s_stat[c4 + 2], s_stat[H + c4 + 2], s_stat[3 * H + c4 + 2]);
+                v.w = fmaf(v.w - s_stat[c4 + 3], s_stat[H + c4 + 3], s_stat[3 * H + c4 + 3]);
+            }
+            if (resid) {
+                const float4 q = reinterpret_cast<const float4 *>(resid)[g];
+                v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
+            }
+            if (emb_out) reinterpret_cast<float4 *>(emb_out)[g] = v;
+            float *d = s_tile + r * TILE_LD + c4;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        }
+        __syncthreads();
+        if (WRITE_YP) {
+            float x[H], y[H];
+            if (t < rows) {
+#pragma unroll
+                for (int k = 0; k < H; ++k) x[k] = s_tile[t * TILE_LD + k];
+                dense_smem<H, H>(s_w2, s_zero, x, y);
+#pragma unroll
+                for (int k = 0; k < H; ++k) s_tile[t * TILE_LD + k] = y[k];
+            }
+            __syncthreads();
+            store_tile(s_tile, Y, node0, rows);
+            __syncthreads();
+            if (t < rows) {
+                dense_smem<H, H>(s_wd, s_b, x, y);
+#pragma unroll
+                for (int k = 0; k < H; ++k) s_tile[t * TILE_LD + k] = y[k];
+            }
+            __syncthreads();
+            store_tile(s_tile, P, node0, rows);
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------ EdgeConv, edge side
+// out_i = P_i + max_{j in N(i)} Y_j   (add: deg*P_i + sum_j Y_j ; mean: P_i + mean_j Y_j)
+// Warp per target.  A 128-byte Y row is read by 8 lanes as float4, so one LDG.128 moves FOUR source rows and
+// every lane keeps a running max / arg-max (or sum) of 4 channels over the edges of its lane group; two
+// loads are in flight per lane.  The four groups are folded with two xor-shuffles.  Rows are read in CSR
+// order (ascending source) and ties go to the lower source index, so the result does not depend on the
+// thread mapping: a segmented, fixed-order, atomics-free reduction.  BatchNorm moments of the output ride
+// along (Welford per warp, Chan-combined in a fixed order) and the last CTA finalises them.
+constexpr int EA_WARPS = 8;
+
+struct AggrTail {                 // BatchNorm epilogue of the EdgeConv output (train mode); partials == NULL otherwise
+    float *partials; int *counter; GmBatchNorm bn; float momentum, eps; float *stat;
+};
+
+__device__ __forceinline__ void amax4(float4 &best, int4 &barg, const float4 v, const int j) {
+    if (v.x > best.x) { best.x = v.x; barg.x = j; }
+    if (v.y > best.y) { best.y = v.y; barg.y = j; }
+    if (v.z > best.z) { best.z = v.z; barg.z = j; }
+    if (v.w > best.w) { best.w = v.w; barg.w = j; }
+}
+__device__ __forceinline__ void amax_merge(float &best, int &barg, const float ob, const int oa) {
+    // other group's candidate wins when larger, or equal with a lower source index (oa < 0: no candidate)
+    if (oa >= 0 && (barg < 0 || ob > best || (ob == best && oa < barg))) { best = ob; barg = oa; }
+}
+
+template <int AGGR, bool ARG>
+__global__ void __launch_bounds__(EA_WARPS * 32)
+k_edge_aggr(const float *__restrict__ Y, const float *__restrict__ P, const int *__restrict__ rowptr,
+            const int *__restrict__ col, int N, float *__restrict__ out, int *__restrict__ arg, AggrTail tail) {
+    __shared__ float s_red[EA_WARPS * 4][3][H];   // per-warp moments (EA_WARPS rows), then the finalize's lane groups
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane & 7, grp = lane >> 3;
+    const float4 *__restrict__ Y4 = reinterpret_cast<const float4 *>(Y);
+    const float NEG = -INFINITY;
+    Moments run[4] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
+    for (int i = blockIdx.x * EA_WARPS + warp; i < N; i += gridDim.x * EA_WARPS) {
+        const int beg = __ldg(rowptr + i), end = __ldg(rowptr + i + 1);
+        float4 acc = AGGR == GM_AGGR_MAX ? make_float4(NEG, NEG, NEG, NEG) : make_float4(0.f, 0.f, 0.f, 0.f);
+        int4 barg = make_int4(-1, -1, -1, -1);
+        for (int e0 = beg; e0 < end; e0 += 32) {
+            const int nb = min(32, end - e0);
+            const int jl = lane < nb ? __ldg(col + e0 + lane) : -1;
+#pragma unroll 2
+            for (int k = 0; k < nb; k += 8) {
+                const int ja = __shfl_sync(0xffffffffu, jl, k + grp);
+                const int jb = __shfl_sync(0xffffffffu, jl, (k + 4 + grp) & 31);
+                const bool va = k + grp < nb, vb = k + 4 + grp < nb;
+                float4 a, b;
+                if (AGGR == GM_AGGR_MAX) { a = make_float4(NEG, NEG, NEG, NEG); b = a; }
+                else { a = make_float4(0.f, 0.f, 0.f, 0.f); b = a; }
+                if (va) a = __ldg(Y4 + (size_t)ja * (H / 4) + sub);
+                if (vb) b = __ldg(Y4 + (size_t)jb * (H / 4) + sub);
+                if (AGGR == GM_AGGR_MAX && ARG) {
+                    if (va) amax4(acc, barg, a, ja);
+                    if (vb) amax4(acc, barg, b, jb);
+                } else if (AGGR == GM_AGGR_MAX) {
+                    acc.x = fmaxf(acc.x, fmaxf(a.x, b.x)); acc.y = fmaxf(acc.y, fmaxf(a.y, b.y));
+                    acc.z = fmaxf(acc.z, fmaxf(a.z, b.z)); acc.w = fmaxf(acc.w, fmaxf(a.w, b.w));
+                } else {
+                    acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+                    acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
+                }
+            }
+        }
+#pragma unroll
+        for (int off = 8; off <= 16; off <<= 1) {
+            const float ox = __shfl_xor_sync(0xffffffffu, acc.x, off), oy = __shfl_xor_sync(0xffffffffu, acc.y, off);
+            const float oz = __shfl_xor_sync(0xffffffffu, acc.z, off), ow = __shfl_xor_sync(0xffffffffu, acc.w, off);
+            if (AGGR == GM_AGGR_MAX && !ARG) {
+                acc.x = fmaxf(acc.x, ox); acc.y = fmaxf(acc.y, oy); acc.z = fmaxf(acc.z, oz); acc.w = fmaxf(acc.w, ow);
+            } else if (AGGR == GM_AGGR_MAX) {
+                const int ax = __shfl_xor_sync(0xffffffffu, barg.x, off), ay = __shfl_xor_sync(0xffffffffu, barg.y, off);
+                const int az = __shfl_xor_sync(0xffffffffu, barg.z, off), aw = __shfl_xor_sync(0xffffffffu, barg.w, off);
+                amax_merge(acc.x, barg.x, ox, ax); amax_merge(acc.y, barg.y, oy, ay);
+                amax_merge(acc.z, barg.z, oz, az); amax_merge(acc.w, barg.w, ow, aw);
+            } else {
+                // fixed pairing: (g0+g1)+(g2+g3) evaluated identically in every lane group
+                const bool lo = (lane & off) == 0;
+                acc.x = lo ? acc.x + ox : ox + acc.x; acc.y = lo ? acc.y + oy : oy + acc.y;
+                acc.z = lo ? acc.z + oz : oz + acc.z; acc.w = lo ? acc.w + ow : ow + acc.w;
+            }
+        }
+        if (grp == 0) {
+            const int deg = end - beg;
+            const float4 p = __ldg(reinterpret_cast<const float4 *>(P) + (size_t)i * (H / 4) + sub);
+            float4 o;
+            if (deg == 0) o = make_float4(0.f, 0.f, 0.f, 0.f);                       // PyG: empty rows aggregate to 0
+            else if (AGGR == GM_AGGR_MAX) o = make_float4(p.x + acc.x, p.y + acc.y, p.z + acc.z, p.w + acc.w);
+            else if (AGGR == GM_AGGR_ADD) {
+                const float d = (float)deg;
+                o = make_float4(fmaf(d, p.x, acc.x), fmaf(d, p.y, acc.y), fmaf(d, p.z, acc.z), fmaf(d, p.w, acc.w));
+            } else {
+                const float inv = 1.f / (float)deg;
+                o = make_float4(fmaf(acc.x, inv, p.x), fmaf(acc.y, inv, p.y), fmaf(acc.z, inv, p.z), fmaf(acc.w, inv, p.w));
+            }
+            reinterpret_cast<float4 *>(out)[(size_t)i * (H / 4) + sub] = o;
+            if (ARG) reinterpret_cast<int4 *>(arg)[(size_t)i * (H / 4) + sub] = barg;
+            if (tail.partials) {
+                const float ov[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    run[q].n += 1.f;
+                    const float dl = ov[q] - run[q].mean;
+                    run[q].mean += dl / run[q].n;
+                    run[q].m2 = fmaf(dl, ov[q] - run[q].mean, run[q].m2);
+                }
+            }
+        }
+    }
+    if (tail.partials) {
+        if (grp == 0) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                s_red[warp][0][4 * sub + q] = run[q].n; s_red[warp][1][4 * sub + q] = run[q].mean;
+                s_red[warp][2][4 * sub + q] = run[q].m2;
+            }
+        }
+        __syncthreads();
+        if (warp == 0) {
+            Moments tot{0.f, 0.f, 0.f};
+#pragma unroll
+            for (int k = 0; k < EA_WARPS; ++k)
+                tot = moments_combine(tot, Moments{s_red[k][0][lane], s_red[k][1][lane], s_red[k][2][lane]});
+            float *dst = tail.partials + (size_t)blockIdx.x * MOM_STRIDE;
+            dst[lane] = tot.n; dst[H + lane] = tot.mean; dst[2 * H + lane] = tot.m2;
+        }
+        if (last_cta_done(tail.counter))
+            bn_finalize_cta(tail.partials, gridDim.x, tail.bn, tail.momentum, tail.eps, tail.stat, s_red);
     }
 }
 
@@ -343,24 +512,47 @@ k_edgeconv_simt(const float *__restrict__ x, const int *__restrict__ rowptr, con
 }
 
 // ------------------------------------------------------------------------------------------ head
-__global__ void __launch_bounds__(NODE_TILE) k_head(const float *__restrict__ emb, int N, const float *__restrict__ w1,
-                                                   const float *__restrict__ b1, const float *__restrict__ w2,
-                                                   const float *__restrict__ b2, int apply_sigmoid,
-                                                   float *__restrict__ out) {
+// emb_L = (resid +) BN(raw) folded into the load (K4), then Linear_32->16 + ELU + Linear_16->1 (+ sigmoid).
+// emb_out (optional) keeps emb_L for the backward; out is written at perm[n] (NULL = identity).
+__global__ void __launch_bounds__(NODE_TILE) k_head(const float *__restrict__ raw, const float *__restrict__ resid,
+                                                   const float *__restrict__ stat, int N,
+                                                   const float *__restrict__ w1, const float *__restrict__ b1,
+                                                   const float *__restrict__ w2, const float *__restrict__ b2,
+                                                   int apply_sigmoid, const int *__restrict__ perm,
+                                                   float *__restrict__ emb_out, float *__restrict__ out) {
     __shared__ __align__(16) float s_w1[16 * H];
     __shared__ float s_b1[16];
     __shared__ __align__(16) float s_w2[16];
     __shared__ float s_b2[1];
+    __shared__ float s_stat[BNSTAT_STRIDE];
     __shared__ float s_tile[NODE_TILE * TILE_LD];
     const int t = threadIdx.x;
     for (int i = t; i < 16 * H; i += NODE_TILE) s_w1[i] = w1[i];
     if (t < 16) { s_b1[t] = b1[t]; s_w2[t] = w2[t]; }
     if (t == 0) s_b2[0] = b2[0];
+    if (stat && t < BNSTAT_STRIDE) s_stat[t] = stat[t];
     __syncthreads();
     const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
     for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const int node0 = tile * NODE_TILE, rows = min(NODE_TILE, N - node0);
-        load_tile(s_tile, emb, node0, rows);
+        for (int idx = t; idx < rows * (H / 4); idx += NODE_TILE) {
+            const int r = idx >> 3, c4 = (idx & 7) * 4;
+            const size_t g = (size_t)(node0 + r) * (H / 4) + (idx & 7);
+            float4 v = reinterpret_cast<const float4 *>(raw)[g];
+            if (stat) {
+                v.x = fmaf(v.x - s_stat[c4 + 0], s_stat[H + c4 + 0], s_stat[3 * H + c4 + 0]);
+                v.y = fmaf(v.y - s_stat[c4 + 1], s_stat[H + c4 + 1], s_stat[3 * H + c4 + 1]);
+                v.z = fmaf(v.z - s_stat[c4 + 2], s_stat[H + c4 + 2], s_stat[3 * H + c4 + 2]);
+                v.w = fmaf(v.w - s_stat[c4 + 3], s_stat[H + c4 + 3], s_stat[3 * H + c4 + 3]);
+            }
+            if (resid) {
+                const float4 q = reinterpret_cast<const float4 *>(resid)[g];
+                v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
+            }
+            if (emb_out) reinterpret_cast<float4 *>(emb_out)[g] = v;
+            float *d = s_tile + r * TILE_LD + c4;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        }
         __syncthreads();
         if (t < rows) {
             float xr[H], hdn[16], hact[16], o[1];
@@ -370,7 +562,8 @@ __global__ void __launch_bounds__(NODE_TILE) k_head(const float *__restrict__ em
 #pragma unroll
             for (int k = 0; k < 16; ++k) hact[k] = elu(hdn[k]);
             dense_smem<16, 1>(s_w2, s_b2, hact, o);
-            out[node0 + t] = apply_sigmoid ? sigmoidf(o[0]) : o[0];
+            const int dst = perm ? perm[node0 + t] : node0 + t;
+            out[dst] = apply_sigmoid ? sigmoidf(o[0]) : o[0];
         }
         __syncthreads();
     }
@@ -389,12 +582,31 @@ int launch_edgeconv_simt(const float *x, const int *rowptr, const int *col, int 
     return GM_OK;
 }
 
-}  // namespace
+template <int AGGR>
+int launch_edge_aggr(const float *Y, const float *P, const int *rowptr, const int *col, int N, float *out, int *arg,
+                     const AggrTail &tail, cudaStream_t st) {
+    const int grid = persistent_grid((N + EA_WARPS - 1) / EA_WARPS, 4);   // 48-64 registers: 4 CTAs of 256 fit an SM
+    if (arg) k_edge_aggr<AGGR, true><<<grid, EA_WARPS * 32, 0, st>>>(Y, P, rowptr, col, N, out, arg, tail);
+    else k_edge_aggr<AGGR, false><<<grid, EA_WARPS * 32, 0, st>>>(Y, P, rowptr, col, N, out, arg, tail);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
 
-int edgeconv_forward(const float *x, const int *rowptr, const int *col, int N, const float *W, const float *b,
-                     int aggr, int precision, float *out, int *arg, float *partials, int *n_partials,
-                     cudaStream_t st) {
-    if (precision != GM_PREC_FP32)
+int edge_aggr(int aggr, const float *Y, const float *P, const int *rowptr, const int *col, int N, float *out, int *arg,
+              const AggrTail &tail, cudaStream_t st) {
+    switch (aggr) {
+        case GM_AGGR_MAX: return launch_edge_aggr<GM_AGGR_MAX>(Y, P, rowptr, col, N, out, arg, tail, st);
+        case GM_AGGR_ADD: return launch_edge_aggr<GM_AGGR_ADD>(Y, P, rowptr, col, N, out, arg, tail, st);
+        case GM_AGGR_MEAN: return launch_edge_aggr<GM_AGGR_MEAN>(Y, P, rowptr, col, N, out, arg, tail, st);
+    }
+    return GM_ERR_INVALID_ARGUMENT;
+}
+
+// direct per-edge contraction: fp32 CUDA cores (GM_PREC_FP32_DIRECT) or tcgen05 (tf32 / bf16)
+int edgeconv_direct(const float *x, const int *rowptr, const int *col, int N, const float *W, const float *b,
+                    int aggr, int precision, float *out, int *arg, float *partials, int *n_partials,
+                    cudaStream_t st) {
+    if (precision != GM_PREC_FP32_DIRECT)
         return edgeconv_tc_forward(x, rowptr, col, N, W, b, aggr, precision, out, arg, partials, n_partials, st);
     switch (aggr) {
         case GM_AGGR_MAX: return launch_edgeconv_simt<GM_AGGR_MAX>(x, rowptr, col, N, W, b, out, arg, partials, n_partials, st);
@@ -403,6 +615,11 @@ int edgeconv_forward(const float *x, const int *rowptr, const int *col, int N, c
     }
     return GM_ERR_INVALID_ARGUMENT;
 }
+
+int node_grid(int N) { return persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 4); }
+int encode_grid(int N) { return persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 2); }   // 214 registers: 2 CTAs/SM
+
+}  // namespace
 
 int check_params(const GmParams *p) {
     if (!p) return GM_ERR_INVALID_ARGUMENT;
@@ -417,13 +634,29 @@ using namespace gm;
 
 extern "C" {
 
+size_t gm_edgeconv_ws_bytes(int N) { return 2 * align_up((size_t)(N > 0 ? N : 1) * H * sizeof(float), 256); }
+
 int gm_edgeconv_forward(const float *x, const int *rowptr, const int *col, int N, const float *W, const float *b,
-                        int aggr, int precision, float *out, int *arg_out, void *stream) {
+                        int aggr, int precision, void *ws, size_t ws_bytes, float *out, int *arg_out, void *stream) {
     if (N < 0 || (N > 0 && (!x || !rowptr || !W || !b || !out))) return GM_ERR_INVALID_ARGUMENT;
     if (N == 0) return GM_OK;
-    int n_part = 0;
-    TimedRegion tr(GM_TIMER_EDGECONV_FWD, as_stream(stream));
-    return edgeconv_forward(x, rowptr, col, N, W, b, aggr, precision, out, arg_out, nullptr, &n_part, as_stream(stream));
+    cudaStream_t st = as_stream(stream);
+    if (precision != GM_PREC_FP32) {
+        int n_part = 0;
+        TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
+        return edgeconv_direct(x, rowptr, col, N, W, b, aggr, precision, out, arg_out, nullptr, &n_part, st);
+    }
+    if (!ws) return GM_ERR_INVALID_ARGUMENT;
+    if (ws_bytes < gm_edgeconv_ws_bytes(N)) return GM_ERR_CAPACITY;
+    float *Y = (float *)ws;
+    float *P = (float *)((char *)ws + gm_edgeconv_ws_bytes(N) / 2);
+    {
+        TimedRegion tr(GM_TIMER_NODE_PREP, st);
+        k_node_prep<true><<<node_grid(N), NODE_TILE, 0, st>>>(x, nullptr, nullptr, W, b, N, nullptr, Y, P);
+        GM_LAUNCH_CHECK();
+    }
+    TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
+    return edge_aggr(aggr, Y, P, rowptr, col, N, out, arg_out, AggrTail{}, st);
 }
 
 size_t gm_net_ws_bytes(int N, int conv_depth, int save_for_backward) {
@@ -431,9 +664,10 @@ size_t gm_net_ws_bytes(int N, int conv_depth, int save_for_backward) {
 }
 
 int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, const int64_t *x_cat_i64,
-                   const float *x_cat_f32, int x_cat_stride, const int *rowptr, const int *col, int N, int training,
-                   int save_for_backward, int apply_sigmoid, int aggr, int precision, float momentum, float eps, void *ws, size_t ws_bytes,
-                   float *out, int *err_flags, void *stream) {
+                   const float *x_cat_f32, int x_cat_stride, const int *rowptr, const int *col, int N,
+                   const int *node_perm, int training, int save_for_backward, int apply_sigmoid, int aggr,
+                   int precision, float momentum, float eps, void *ws, size_t ws_bytes, float *out, int *err_flags,
+                   void *stream) {
     GM_TRY(check_params(p));
     if (N < 0 || !ws || !err_flags) return GM_ERR_INVALID_ARGUMENT;
     if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || !rowptr || !out)) return GM_ERR_INVALID_ARGUMENT;
@@ -443,55 +677,74 @@ int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, co
     NetWs w;
     net_ws_layout(N, p->conv_depth, save_for_backward, (char *)ws, &w);
     const int depth = p->conv_depth;
-    const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
+    const int ngrid = node_grid(N);
 
-    k_build_lut<<<(LUT_ROWS * 16 + 255) / 256, 256, 0, st>>>(*p, w.lut);
+    k_build_lut<<<(LUT_ROWS * 16 + 255) / 256, 256, 0, st>>>(*p, w.lut, w.counters, w.bnstat, training, eps);
     GM_LAUNCH_CHECK();
 
     EncodeArgs ea{};
     ea.x_cont = x_cont; ea.x_cont_stride = x_cont_stride;
     ea.x_cat_i64 = (const long long *)x_cat_i64;
     ea.x_cat_f32 = x_cat_f32; ea.x_cat_stride = x_cat_stride;
+    ea.perm = node_perm;
     ea.N = N; ea.CD = p->continuous_dim;
-    ea.flat = (!x_cat_i64 && x_cat_f32 && x_cat_stride == x_cont_stride && x_cont_stride <= 16 &&
+    ea.flat = (!node_perm && !x_cat_i64 && x_cat_f32 && x_cat_stride == x_cont_stride && x_cont_stride <= 16 &&
                x_cat_f32 >= x_cont && (x_cat_f32 - x_cont) + 3 <= x_cont_stride) ? 1 : 0;
     ea.cont_w = p->cont_w; ea.cont_b = p->cont_b; ea.enc_w = p->enc_w; ea.enc_b = p->enc_b; ea.lut = w.lut;
     ea.enc_out = w.enc;
     ea.partials = training ? w.partials : nullptr;
+    ea.counter = w.counters + 0;
+    ea.bn = p->bn_all; ea.momentum = momentum; ea.eps = eps; ea.stat = w.bnstat;
     ea.err_flags = err_flags;
-    const int enc_grid = persistent_grid(tiles, 4);
     {
         TimedRegion tr(GM_TIMER_ENCODE_FWD, st);
-        k_encode<<<enc_grid, NODE_TILE, 0, st>>>(ea);
+        k_encode<<<encode_grid(N), NODE_TILE, 0, st>>>(ea);
         GM_LAUNCH_CHECK();
     }
-
-    k_bn_finalize<<<1, 1024, 0, st>>>(w.partials, enc_grid, p->bn_all, momentum, eps, training, w.bnstat);
-    GM_LAUNCH_CHECK();
-    const size_t n4 = (size_t)N * (H / 4);
-    const int ew_grid = persistent_grid((long long)((n4 + 255) / 256), 8);
-    k_bn_apply<<<ew_grid, 256, 0, st>>>((const float4 *)w.enc, nullptr, w.bnstat, (float4 *)w.emb[0], n4);
-    GM_LAUNCH_CHECK();
 
     for (int l = 0; l < depth; ++l) {
-        int n_part = 0;
-        {
+        const float *raw = l == 0 ? w.enc : w.conv[l - 1];
+        const float *resid = l == 0 ? nullptr : w.emb[l - 1];
+        const float *stat_in = w.bnstat + (size_t)l * BNSTAT_STRIDE;
+        float *stat_out = w.bnstat + (size_t)(l + 1) * BNSTAT_STRIDE;
+        int *arg = save_for_backward ? w.arg[l] : nullptr;
+        if (precision == GM_PREC_FP32) {
+            {
+                TimedRegion tr(GM_TIMER_NODE_PREP, st);
+                k_node_prep<true><<<ngrid, NODE_TILE, 0, st>>>(raw, resid, stat_in, p->conv_w[l], p->conv_b[l], N,
+                                                               w.emb[l], w.Y, w.P);
+                GM_LAUNCH_CHECK();
+            }
+            AggrTail tail{};
+            if (training) tail = AggrTail{w.partials, w.counters + 1 + l, p->conv_bn[l], momentum, eps, stat_out};
             TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
-            GM_TRY(edgeconv_forward(w.emb[l], rowptr, col, N, p->conv_w[l], p->conv_b[l], aggr, precision, w.conv[l],
-                                    save_for_backward ? w.arg[l] : nullptr, training ? w.partials : nullptr, &n_part,
-                                    st));
+            GM_TRY(edge_aggr(aggr, w.Y, w.P, rowptr, col, N, w.conv[l], arg, tail, st));
+        } else {
+            {
+                TimedRegion tr(GM_TIMER_NODE_PREP, st);
+                k_node_prep<false><<<ngrid, NODE_TILE, 0, st>>>(raw, resid, stat_in, nullptr, nullptr, N, w.emb[l],
+                                                                nullptr, nullptr);
+                GM_LAUNCH_CHECK();
+            }
+            int n_part = 0;
+            {
+                TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
+                GM_TRY(edgeconv_direct(w.emb[l], rowptr, col, N, p->conv_w[l], p->conv_b[l], aggr, precision,
+                                       w.conv[l], arg, training ? w.partials : nullptr, &n_part, st));
+            }
+            if (training) {
+                k_bn_finalize<<<1, 256, 0, st>>>(w.partials, n_part, p->conv_bn[l], momentum, eps, stat_out);
+                GM_LAUNCH_CHECK();
+            }
         }
-        float *stat = w.bnstat + (size_t)(l + 1) * BNSTAT_STRIDE;
-        k_bn_finalize<<<1, 1024, 0, st>>>(w.partials, n_part, p->conv_bn[l], momentum, eps, training, stat);
-        GM_LAUNCH_CHECK();
-        k_bn_apply<<<ew_grid, 256, 0, st>>>((const float4 *)w.conv[l], (const float4 *)w.emb[l], stat,
-                                            (float4 *)w.emb[l + 1], n4);
-        GM_LAUNCH_CHECK();
     }
     {
+        const float *raw = depth == 0 ? w.enc : w.conv[depth - 1];
+        const float *resid = depth == 0 ? nullptr : w.emb[depth - 1];
         TimedRegion tr(GM_TIMER_HEAD_FWD, st);
-        k_head<<<persistent_grid(tiles, 4), NODE_TILE, 0, st>>>(w.emb[depth], N, p->out1_w, p->out1_b, p->out2_w,
-                                                                p->out2_b, apply_sigmoid, out);
+        k_head<<<ngrid, NODE_TILE, 0, st>>>(raw, resid, w.bnstat + (size_t)depth * BNSTAT_STRIDE, N, p->out1_w,
+                                            p->out1_b, p->out2_w, p->out2_b, apply_sigmoid, node_perm,
+                                            save_for_backward ? w.emb[depth] : nullptr, out);
         GM_LAUNCH_CHECK();
     }
     return GM_OK;

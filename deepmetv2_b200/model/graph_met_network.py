@@ -42,9 +42,11 @@ class EdgeConv(nn.Module):
         csr = edge_index if isinstance(edge_index, ops.GraphCSR) else ops.csr_from_edge_index(edge_index, x.shape[0])
         x = x.contiguous().float()
         out = torch.empty_like(x)
-        check(lib().gm_edgeconv_forward(ptr(x), ptr(csr.rowptr), ptr(csr.col), x.shape[0], ptr(lin.weight),
-                                        ptr(lin.bias), AGGR[self.aggr], PRECISION[self.precision], ptr(out), None,
-                                        stream()), "gm_edgeconv_forward")
+        l = lib()
+        ws = torch.empty(l.gm_edgeconv_ws_bytes(x.shape[0]), dtype=torch.uint8, device=x.device)
+        check(l.gm_edgeconv_forward(ptr(x), ptr(csr.rowptr), ptr(csr.col), x.shape[0], ptr(lin.weight),
+                                    ptr(lin.bias), AGGR[self.aggr], PRECISION[self.precision], ptr(ws), ws.numel(),
+                                    ptr(out), None, stream()), "gm_edgeconv_forward")
         return out
 
 
@@ -76,7 +78,7 @@ class _GraphMETFunction(torch.autograd.Function):
         training = bool(net.training)
         check(l.gm_net_forward(C.byref(P), ptr(x_cont), x_cont.stride(0), ptr(cat_i64), ptr(cat_f32),
                                0 if cat_f32 is None else cat_f32.stride(0), ptr(csr.rowptr), ptr(csr.col), N,
-                               int(training), int(save), int(apply_sigmoid), AGGR[net.aggr],
+                               None, int(training), int(save), int(apply_sigmoid), AGGR[net.aggr],
                                PRECISION[net.edge_precision], float(net.bn_all.momentum), float(net.bn_all.eps),
                                ptr(ws), ws.numel(), ptr(out), ptr(net._err_flags(dev)), stream()), "gm_net_forward")
         ctx.net, ctx.csr, ctx.ws, ctx.saved_save = net, csr, ws, save
@@ -109,7 +111,7 @@ class _GraphMETFunction(torch.autograd.Function):
         grad_out = grad_out.contiguous().float()
         check(l.gm_net_backward(C.byref(P), C.byref(G), ptr(ctx.x_cont), ctx.x_cont.stride(0), ptr(cat_i64),
                                 ptr(cat_f32), 0 if cat_f32 is None else cat_f32.stride(0), ptr(csr.rowptr),
-                                ptr(csr.col), ptr(rowptr_t), ptr(col_t), None, N, int(ctx.training),
+                                ptr(csr.col), ptr(rowptr_t), ptr(col_t), None, N, None, int(ctx.training),
                                 int(ctx.apply_sigmoid), AGGR[net.aggr], float(net.bn_all.eps), ptr(ctx.ws),
                                 ctx.ws.numel(), ptr(bws), bws.numel(), ptr(ctx.out), ptr(grad_out), stream()),
               "gm_net_backward")

@@ -96,7 +96,7 @@ class GraphMETTrainer:
     def _forward(self, x, N, training, save):
         net = self.net
         check(lib().gm_net_forward(C.byref(self._P), ptr(x), x.stride(0), None, x.data_ptr() + 8 * 4, x.stride(0),
-                                   ptr(self.rowptr), ptr(self.col), N, int(training), int(save),
+                                   ptr(self.rowptr), ptr(self.col), N, None, int(training), int(save),
                                    int(self.apply_sigmoid), AGGR[net.aggr], PRECISION[net.edge_precision],
                                    float(net.bn_all.momentum), float(net.bn_all.eps), ptr(self.fwd_ws),
                                    self.fwd_ws.numel(), ptr(self.weights), ptr(self.flags), stream()),
@@ -127,7 +127,7 @@ class GraphMETTrainer:
         net = self.net
         check(l.gm_net_backward(C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), None, x.data_ptr() + 32,
                                 x.stride(0), ptr(self.rowptr), ptr(self.col), ptr(self.rowptr_t), ptr(self.col_t),
-                                self.stats.data_ptr() + 8, N, 1, int(self.apply_sigmoid), AGGR[net.aggr],
+                                self.stats.data_ptr() + 8, N, None, 1, int(self.apply_sigmoid), AGGR[net.aggr],
                                 float(net.bn_all.eps), ptr(self.fwd_ws), self.fwd_ws.numel(), ptr(self.bwd_ws),
                                 self.bwd_ws.numel(), ptr(self.weights), ptr(self.grad_w), st), "gm_net_backward")
         scale = 1.0

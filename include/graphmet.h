@@ -54,10 +54,11 @@ extern "C" {
 #define GM_AGGR_MEAN 2
 
 /* arithmetic of the per-edge contraction */
-#define GM_PREC_FP32 0      /* CUDA-core fp32 FFMA2 (parity mode) */
+#define GM_PREC_FP32 0      /* fp32 CUDA cores, factored form P_i + aggr_j Y_j (parity mode, default) */
 #define GM_PREC_TF32 1      /* tcgen05 kind::tf32 */
 #define GM_PREC_BF16 2      /* tcgen05 kind::f16 (bf16 operands, fp32 accumulate in TMEM) */
-#define GM_PREC_TF32X3 3    /* tcgen05 3xTF32 split (fp32-accurate) */
+#define GM_PREC_TF32X3 3    /* reserved: tcgen05 3xTF32 split (returns GM_ERR_UNSUPPORTED) */
+#define GM_PREC_FP32_DIRECT 4 /* fp32 CUDA cores, per-edge contraction W2 (x_j - x_i) spelled out (cross-check) */
 
 int gm_version(void);
 const char *gm_status_string(int status);
@@ -76,7 +77,9 @@ long long gm_launch_count(int reset);  /* kernels this library launched since th
 #define GM_TIMER_CONV_NODE_BWD 5
 #define GM_TIMER_ENCODE_BWD 6
 #define GM_TIMER_BN 7
-#define GM_NUM_TIMERS 8
+#define GM_TIMER_NODE_PREP 8
+#define GM_TIMER_HEAD_BWD 9
+#define GM_NUM_TIMERS 10
 int gm_timing_enable(int on);
 int gm_timing_read(int slot, float *total_ms_out, int *regions_out);
 
@@ -162,6 +165,11 @@ int gm_edge_index_to_csr(const int64_t *edge_index, long long E, int N, void *ws
  *                            0 = running statistics (model.eval())
  *   save_for_backward      : 1 = also keep the arg-max sources (ws must then be sized with save=1)
  *   apply_sigmoid          : 1 = Net.forward (model/net.py:47), 0 = GraphMETNetwork.forward
+ *   node_perm              : int32 [N] or NULL.  When given, the network runs in an INTERNAL node order:
+ *                            internal row s is input row node_perm[s]; rowptr/col index internal rows
+ *                            (the cell-sorted CSR of gm_radius_graph_*), x_* rows are read at node_perm[s]
+ *                            and out is written at node_perm[s], i.e. inputs and outputs stay in the
+ *                            caller's order.  NULL = identity.
  *   ws                     : gm_net_ws_bytes(N, depth, save_for_backward) bytes; holds every intermediate the
  *                            backward needs and must stay untouched until gm_net_backward ran
  *   out                    : [N]
@@ -170,16 +178,19 @@ int gm_edge_index_to_csr(const int64_t *edge_index, long long E, int N, void *ws
 size_t gm_net_ws_bytes(int N, int conv_depth, int save_for_backward);
 int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride,
                    const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride,
-                   const int *rowptr, const int *col, int N,
+                   const int *rowptr, const int *col, int N, const int *node_perm,
                    int training, int save_for_backward, int apply_sigmoid, int aggr, int precision,
                    float momentum, float eps,
                    void *ws, size_t ws_bytes, float *out, int *err_flags, void *stream);
 
 /* a5 alone — replaces torch_geometric.nn.EdgeConv(nn=Linear(64,32), aggr).forward(x, edge_index)
  * (model/graph_met_network.py:38,65): out_i = aggr_j W.[x_i ; x_j - x_i] + b over the CSR row of i.
+ * ws: gm_edgeconv_ws_bytes(N) bytes of scratch (Y = W2 x and P = (W1-W2) x + b; GM_PREC_FP32 only).
  * arg_out (optional, [N,32] int32): arg-max source per (target, channel) for aggr = max. */
+size_t gm_edgeconv_ws_bytes(int N);
 int gm_edgeconv_forward(const float *x, const int *rowptr, const int *col, int N, const float *W,
-                        const float *b, int aggr, int precision, float *out, int *arg_out, void *stream);
+                        const float *b, int aggr, int precision, void *ws, size_t ws_bytes, float *out,
+                        int *arg_out, void *stream);
 
 /* Backward of gm_net_forward (replaces loss.backward() through the model, train.py:51).
  * grad_out [N] = dL/d out.  Every tensor of `grads` (same layout as GmParams; BN running
@@ -194,7 +205,7 @@ size_t gm_net_bwd_ws_bytes(int N, int conv_depth);
 int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
                     const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride,
                     const int *rowptr, const int *col, const int *rowptr_t, const int *col_t,
-                    const int *use_transposed_flag, int N,
+                    const int *use_transposed_flag, int N, const int *node_perm,
                     int training, int apply_sigmoid, int aggr, float eps,
                     const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
                     const float *out, const float *grad_out, void *stream);

@@ -334,5 +334,34 @@ def forward_step(model, x, y, batch, edge_index=None, r=0.4, max_num_neighbors=2
     return w, loss, edge_index
 
 
+def ambiguous_argmax_pairs(net: "Net", x, edge_index, batch, ulps: float = 4.0) -> int:
+    """Number of (target, channel) pairs, over all EdgeConv layers, whose two largest messages lie within
+    ``ulps`` fp32 ulps of the layer's message scale, evaluated by an fp64 twin of ``net`` (train mode).
+    For such pairs the arg-max — hence where max-aggregation routes the gradient — is decided by fp32
+    rounding order, so two correct fp32 implementations (upstream PyG included) may legitimately differ:
+    the EdgeConv analogue of the radius-graph margin check."""
+    import copy
+    m = copy.deepcopy(net).double()
+    m.train()
+    with torch.no_grad():
+        xd = x.double()
+        _, inter = m.graphnet(xd[:, :8], x[:, 8:].long(), edge_index, batch, return_intermediates=True)
+        j, i = edge_index[0], edge_index[1]
+        count = 0
+        for l, co_conv in enumerate(m.graphnet.conv_continuous):
+            emb = inter[f"emb{l}"]
+            msg = co_conv[0].nn(torch.cat([emb[i], emb[j] - emb[i]], dim=1))
+            N, C = emb.shape[0], msg.shape[1]
+            idx = i.view(-1, 1).expand(-1, C)
+            top1 = msg.new_full((N, C), -torch.inf).scatter_reduce(0, idx, msg, "amax", include_self=True)
+            rest = msg.masked_fill(msg == top1[i], -torch.inf)
+            top2 = msg.new_full((N, C), -torch.inf).scatter_reduce(0, idx, rest, "amax", include_self=True)
+            tol = ulps * float(np.spacing(np.float32(msg.abs().max().item())))
+            count += int(((top1 - top2 <= tol) & torch.isfinite(top2)).sum())
+            # exact ties between distinct edges also count
+            count += int((msg == top1[i]).sum()) - int(torch.isfinite(top1).sum())
+    return count
+
+
 def num_threads_used():
     return torch.get_num_threads()

@@ -28,7 +28,7 @@ def _norm_err(a, b, floor=1e-12):
     return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), floor))
 
 
-def _check_grads(named_ours, ref_grads):
+def _check_grads(named_ours, ref_grads, rtol=GRAD_RTOL):
     """Every gradient within GRAD_RTOL of its tensor's max-abs.  An EdgeConv bias feeds a train-mode
     BatchNorm, so its true gradient is identically 0 and both sides hold rounding noise: it is compared
     on the scale of the same layer's weight gradient instead."""
@@ -40,9 +40,20 @@ def _check_grads(named_ours, ref_grads):
             floor = float(np.max(np.abs(ref_grads[k.replace("nn.0.bias", "nn.0.weight")])))
         assert p.grad is not None, k
         worst[k] = _norm_err(p.grad.cpu().numpy(), want, floor)
-    bad = {k: v for k, v in worst.items() if not v < GRAD_RTOL}
+    bad = {k: v for k, v in worst.items() if not v < rtol}
     assert not bad, bad
     return worst
+
+
+def _grad_rtol(ref_model, g):
+    """GRAD_RTOL, unless the fixture holds (target, channel) pairs whose two best messages are closer than
+    fp32 can resolve (O.ambiguous_argmax_pairs): which source then receives the max-aggregation gradient is
+    decided by rounding order, in upstream PyG as much as here, and each such pair can move a gradient by up
+    to |d conv| * |x_j1 - x_j2|.  Those fixtures (a handful of pairs at most) are held to 5e-3 instead."""
+    n_amb = O.ambiguous_argmax_pairs(ref_model, torch.from_numpy(g["x"]),
+                                     torch.from_numpy(g["edge_index"].astype(np.int64)), torch.from_numpy(g["batch"]))
+    assert n_amb < 10, n_amb
+    return GRAD_RTOL if n_amb == 0 else 5 * GRAD_RTOL
 
 
 # ----------------------------------------------------------------------------------------------- radius graph
@@ -189,7 +200,7 @@ def test_eval_forward_matches_reference_fixture(name):
 def test_train_step_gradients_match_reference_fixture(name):
     """train.py:35,49-51 — forward in train mode, loss, backward: all 23 gradients + BN running stats."""
     g = load_golden(name)
-    ours, _ = _models(g)
+    ours, ref = _models(g)
     ours.train()
     x, y, b = _gpu_inputs(g)
     edge_index = ops.radius_graph(torch.from_numpy(g["etaphi"]).to(DEV), r=0.4, batch=b, loop=True,
@@ -199,7 +210,8 @@ def test_train_step_gradients_match_reference_fixture(name):
     loss.backward()
     assert _rel(w.detach().cpu().numpy(), g["train_weights"]) < W_RTOL
     assert abs(loss.item() - float(g["train_loss"])) <= MET_RTOL * abs(float(g["train_loss"]))
-    _check_grads(ours.named_parameters(), {k: g["grad::" + k] for k, _ in ours.named_parameters()})
+    _check_grads(ours.named_parameters(), {k: g["grad::" + k] for k, _ in ours.named_parameters()},
+                 rtol=_grad_rtol(ref, g))
     for k, v in ours.state_dict().items():
         if "running" in k:
             assert np.allclose(v.cpu().numpy(), g["sd_after::" + k], rtol=1e-5, atol=1e-6), k
@@ -291,9 +303,11 @@ def test_edgeconv_standalone_aggregations():
         want = O.EdgeConv(lin, aggr)(x, ei).detach()
         conv = EdgeConv(torch.nn.Sequential(torch.nn.Linear(64, 32)), aggr).to(DEV)
         conv.nn.load_state_dict(lin.state_dict())
-        with torch.no_grad():
-            got = conv(x.to(DEV), ei.to(DEV)).cpu()
-        assert torch.allclose(got, want, rtol=1e-4, atol=2e-5), aggr
+        for prec in ("fp32", "fp32_direct"):     # factored P_i + aggr_j Y_j  vs  per-edge W2 (x_j - x_i)
+            conv.precision = prec
+            with torch.no_grad():
+                got = conv(x.to(DEV), ei.to(DEV)).cpu()
+            assert torch.allclose(got, want, rtol=1e-4, atol=2e-5), (aggr, prec)
 
 
 def test_scatter_add_and_loss_fn_gradient():
