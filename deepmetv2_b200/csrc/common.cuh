@@ -59,6 +59,17 @@ inline int persistent_grid(long long work_ctas, int ctas_per_sm) {
     return (int)(work_ctas < cap ? work_ctas : cap);
 }
 
+// Resident CTAs per SM of a kernel at a launch configuration (occupancy query; falls back to `fallback`).
+template <typename K>
+inline int resident_ctas(K kernel, int threads, size_t smem, int fallback) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smem) != cudaSuccess || n < 1) {
+        cudaGetLastError();
+        n = fallback;
+    }
+    return n;
+}
+
 // ----------------------------------------------------------------------------- device
 __device__ __forceinline__ float elu(float v) { return v > 0.f ? v : expm1f(v); }
 // derivative of ELU expressed through its OUTPUT a = elu(z): z>0 -> 1, else a + 1

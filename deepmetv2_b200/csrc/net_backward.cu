@@ -314,9 +314,33 @@ k_head_bwd(const float *__restrict__ emb, const float *__restrict__ out, const f
 
 // ----------------------------------------------------------------------------------------- max-aggregation routing
 // S[j][c] = sum over targets i that list j as a source of [arg(i,c) == j] * d(conv)[i][c].
-// Warp per source j; an arg row (128 B) is read by 8 lanes as int4, so one load covers FOUR targets; G and
-// raw are only touched where a channel matches (N*32 matches in total).  The four lane groups are folded
-// with a fixed pairing => deterministic.
+// Warp per source j, half-warp per arg row (int2 per lane), up to 16 loads (32 targets) in flight per lane,
+// next row prefetched; G and
+// raw are only touched where a channel matches (N*32 matches in total).  Targets are visited in CSR order
+// and the two halves are folded as (half 0) + (half 1) => fixed summation order.
+// Matching (target, channel) entries are sparse (32 per source on average): the G / raw loads are PREDICATED,
+// not branched, so all of a batch's loads are issued back to back (one more round trip, not one per match).
+__device__ __forceinline__ void scatter_consume(float2 &s, const int2 (&a)[8], const int (&i)[8], int j, int sub,
+                                                const float *s_coef, const float2 *__restrict__ G2,
+                                                const float2 *__restrict__ R2) {
+    float2 g[8], r[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        g[u] = make_float2(0.f, 0.f); r[u] = g[u];
+        if (a[u].x == j || a[u].y == j) {          // j >= 0 never equals the -1 filler
+            g[u] = __ldg(G2 + (size_t)i[u] * (H / 2) + sub);
+            r[u] = __ldg(R2 + (size_t)i[u] * (H / 2) + sub);
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const float dx = bn_bwd_one(s_coef, 2 * sub + 0, g[u].x, r[u].x);
+        const float dy = bn_bwd_one(s_coef, 2 * sub + 1, g[u].y, r[u].y);
+        s.x += a[u].x == j ? dx : 0.f;
+        s.y += a[u].y == j ? dy : 0.f;
+    }
+}
+
 __global__ void __launch_bounds__(256) k_scatter_s(const float *__restrict__ G, const float *__restrict__ raw, BnBwd bn,
                                                    const int *__restrict__ arg, const int *__restrict__ rowptr_s,
                                                    const int *__restrict__ col_s, const int *__restrict__ rowptr_tt,
@@ -328,51 +352,47 @@ __global__ void __launch_bounds__(256) k_scatter_s(const float *__restrict__ G, 
     const bool tr = use_t ? (*use_t != 0) : true;
     const int *__restrict__ rowptr_t = tr ? rowptr_tt : rowptr_s;
     const int *__restrict__ col_t = tr ? col_tt : col_s;
-    const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
-    const int warps = (gridDim.x * blockDim.x) >> 5;
-    const int4 *__restrict__ arg4 = reinterpret_cast<const int4 *>(arg);
-    const float4 *__restrict__ G4 = reinterpret_cast<const float4 *>(G);
-    const float4 *__restrict__ R4 = reinterpret_cast<const float4 *>(raw);
-    const int c0 = 4 * sub;
-    for (int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; j < N; j += warps) {
-        const int beg = __ldg(rowptr_t + j), end = __ldg(rowptr_t + j + 1);
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int lane = threadIdx.x & 31, sub = lane & 15, half = lane >> 4;
+    const int stride = (gridDim.x * blockDim.x) >> 5;
+    const int2 *__restrict__ arg2 = reinterpret_cast<const int2 *>(arg);
+    const float2 *__restrict__ G2 = reinterpret_cast<const float2 *>(G);
+    const float2 *__restrict__ R2 = reinterpret_cast<const float2 *>(raw);
+    const int2 NONE = make_int2(-1, -1);
+    int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int beg = 0, end = 0, il = -1;
+    if (j < N) {
+        beg = __ldg(rowptr_t + j); end = __ldg(rowptr_t + j + 1);
+        il = lane < end - beg ? __ldg(col_t + beg + lane) : -1;
+    }
+    while (j < N) {
+        const int jn = j + stride;
+        int nbeg = 0, nend = 0, inext = -1;
+        if (jn < N) { nbeg = __ldg(rowptr_t + jn); nend = __ldg(rowptr_t + jn + 1); }
+        float2 s = make_float2(0.f, 0.f);
         for (int e0 = beg; e0 < end; e0 += 32) {
             const int nb = min(32, end - e0);
-            const int il = lane < nb ? __ldg(col_t + e0 + lane) : -1;
-#pragma unroll 2
-            for (int k = 0; k < nb; k += 8) {
-                const int ia = __shfl_sync(0xffffffffu, il, k + grp);
-                const int ib = __shfl_sync(0xffffffffu, il, (k + 4 + grp) & 31);
-                const bool va = k + grp < nb, vb = k + 4 + grp < nb;
-                int4 aa = make_int4(-1, -1, -1, -1), ab = aa;
-                if (va) aa = __ldg(arg4 + (size_t)ia * (H / 4) + sub);
-                if (vb) ab = __ldg(arg4 + (size_t)ib * (H / 4) + sub);
-                if (aa.x == j || aa.y == j || aa.z == j || aa.w == j) {
-                    const float4 g = __ldg(G4 + (size_t)ia * (H / 4) + sub), r = __ldg(R4 + (size_t)ia * (H / 4) + sub);
-                    if (aa.x == j) s.x += bn_bwd_one(s_coef, c0 + 0, g.x, r.x);
-                    if (aa.y == j) s.y += bn_bwd_one(s_coef, c0 + 1, g.y, r.y);
-                    if (aa.z == j) s.z += bn_bwd_one(s_coef, c0 + 2, g.z, r.z);
-                    if (aa.w == j) s.w += bn_bwd_one(s_coef, c0 + 3, g.w, r.w);
-                }
-                if (ab.x == j || ab.y == j || ab.z == j || ab.w == j) {
-                    const float4 g = __ldg(G4 + (size_t)ib * (H / 4) + sub), r = __ldg(R4 + (size_t)ib * (H / 4) + sub);
-                    if (ab.x == j) s.x += bn_bwd_one(s_coef, c0 + 0, g.x, r.x);
-                    if (ab.y == j) s.y += bn_bwd_one(s_coef, c0 + 1, g.y, r.y);
-                    if (ab.z == j) s.z += bn_bwd_one(s_coef, c0 + 2, g.z, r.z);
-                    if (ab.w == j) s.w += bn_bwd_one(s_coef, c0 + 3, g.w, r.w);
-                }
-            }
-        }
+            if (e0 > beg) il = lane < nb ? __ldg(col_t + e0 + lane) : -1;
+            int ia[8], ib[8];
+            int2 aa[8], ab[8];
 #pragma unroll
-        for (int off = 8; off <= 16; off <<= 1) {
-            const float ox = __shfl_xor_sync(0xffffffffu, s.x, off), oy = __shfl_xor_sync(0xffffffffu, s.y, off);
-            const float oz = __shfl_xor_sync(0xffffffffu, s.z, off), ow = __shfl_xor_sync(0xffffffffu, s.w, off);
-            const bool lo = (lane & off) == 0;
-            s.x = lo ? s.x + ox : ox + s.x; s.y = lo ? s.y + oy : oy + s.y;
-            s.z = lo ? s.z + oz : oz + s.z; s.w = lo ? s.w + ow : ow + s.w;
+            for (int u = 0; u < 8; ++u) ia[u] = __shfl_sync(0xffffffffu, il, 2 * u + half);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) aa[u] = (2 * u + half < nb) ? __ldg(arg2 + (size_t)ia[u] * (H / 2) + sub) : NONE;
+            if (nb > 16) {
+#pragma unroll
+                for (int u = 0; u < 8; ++u) ib[u] = __shfl_sync(0xffffffffu, il, 16 + 2 * u + half);
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    ab[u] = (16 + 2 * u + half < nb) ? __ldg(arg2 + (size_t)ib[u] * (H / 2) + sub) : NONE;
+            }
+            if (e0 == beg && jn < N) inext = lane < nend - nbeg ? __ldg(col_t + nbeg + lane) : -1;
+            scatter_consume(s, aa, ia, j, sub, s_coef, G2, R2);
+            if (nb > 16) scatter_consume(s, ab, ib, j, sub, s_coef, G2, R2);
         }
-        if (grp == 0) reinterpret_cast<float4 *>(S)[(size_t)j * (H / 4) + sub] = s;
+        if (end == beg && jn < N) inext = lane < nend - nbeg ? __ldg(col_t + nbeg + lane) : -1;
+        const float ox = __shfl_xor_sync(0xffffffffu, s.x, 16), oy = __shfl_xor_sync(0xffffffffu, s.y, 16);
+        if (half == 0) reinterpret_cast<float2 *>(S)[(size_t)j * (H / 2) + sub] = make_float2(s.x + ox, s.y + oy);
+        j = jn; beg = nbeg; end = nend; il = inext;
     }
 }
 
@@ -686,7 +706,9 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
         const int stage = depth - l;
         {
             TimedRegion tr(GM_TIMER_SCATTER_S_BWD, st);
-            k_scatter_s<<<persistent_grid(((long long)N * 32 + 255) / 256, 4), 256, 0, st>>>(
+            static int occ = 0;
+            if (!occ) occ = resident_ctas(k_scatter_s, 256, 0, 3);
+            k_scatter_s<<<persistent_grid(((long long)N * 32 + 255) / 256, occ), 256, 0, st>>>(
                 w.G, f.conv[l], bn_in(l + 1), f.arg[l], rowptr, col, rowptr_t, col_t, use_transposed_flag, N, w.S);
             GM_LAUNCH_CHECK();
         }

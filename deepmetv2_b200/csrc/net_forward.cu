@@ -279,27 +279,35 @@ k_node_prep(const float *__restrict__ raw, const float *__restrict__ resid, cons
 
 // ------------------------------------------------------------------------------------------ EdgeConv, edge side
 // out_i = P_i + max_{j in N(i)} Y_j   (add: deg*P_i + sum_j Y_j ; mean: P_i + mean_j Y_j)
-// Warp per target.  A 128-byte Y row is read by 8 lanes as float4, so one LDG.128 moves FOUR source rows and
-// every lane keeps a running max / arg-max (or sum) of 4 channels over the edges of its lane group; two
-// loads are in flight per lane.  The four groups are folded with two xor-shuffles.  Rows are read in CSR
-// order (ascending source) and ties go to the lower source index, so the result does not depend on the
-// thread mapping: a segmented, fixed-order, atomics-free reduction.  BatchNorm moments of the output ride
-// along (Welford per warp, Chan-combined in a fixed order) and the last CTA finalises them.
+// Warp per target, HALF-WARP per source row: a 128-byte Y row is read by 16 lanes as float2, so one LDG.64
+// of the warp moves two source rows and every lane keeps the running max / arg-max (or sum) of 2 channels
+// over the edges of its half; up to 16 loads (32 edges) are in flight per lane and the next target's row
+// bounds / sources are prefetched while the current one is reduced.  The per-target epilogue is one
+// xor-16 exchange.  Rows are read in CSR order (ascending source) with a strict '>' and the halves are
+// merged with "lowest source index wins", so ties are broken exactly like a sequential scan: a segmented,
+// fixed-order, atomics-free reduction.  BatchNorm moments of the output ride along as shifted sums
+// (shift = the warp's first output, so nothing cancels) and the last CTA finalises them.
+// [profiles/r01_ncu_edge_aggr.txt: the float4 / 8-lanes-per-row variant spent 48% of its instructions in
+//  the per-target epilogue at the DY/TT degree of ~27; this layout cuts the epilogue to one exchange.]
 constexpr int EA_WARPS = 8;
 
 struct AggrTail {                 // BatchNorm epilogue of the EdgeConv output (train mode); partials == NULL otherwise
     float *partials; int *counter; GmBatchNorm bn; float momentum, eps; float *stat;
 };
 
-__device__ __forceinline__ void amax4(float4 &best, int4 &barg, const float4 v, const int j) {
-    if (v.x > best.x) { best.x = v.x; barg.x = j; }
-    if (v.y > best.y) { best.y = v.y; barg.y = j; }
-    if (v.z > best.z) { best.z = v.z; barg.z = j; }
-    if (v.w > best.w) { best.w = v.w; barg.w = j; }
-}
-__device__ __forceinline__ void amax_merge(float &best, int &barg, const float ob, const int oa) {
-    // other group's candidate wins when larger, or equal with a lower source index (oa < 0: no candidate)
-    if (oa >= 0 && (barg < 0 || ob > best || (ob == best && oa < barg))) { best = ob; barg = oa; }
+template <int AGGR, bool ARG>
+__device__ __forceinline__ void aggr_consume(float2 &acc, int2 &barg, const float2 (&v)[8], const int (&j)[8]) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        if (AGGR == GM_AGGR_MAX && ARG) {
+            if (v[u].x > acc.x) { acc.x = v[u].x; barg.x = j[u]; }
+            if (v[u].y > acc.y) { acc.y = v[u].y; barg.y = j[u]; }
+        } else if (AGGR == GM_AGGR_MAX) {
+            acc.x = fmaxf(acc.x, v[u].x); acc.y = fmaxf(acc.y, v[u].y);
+        } else {
+            acc.x += v[u].x; acc.y += v[u].y;
+        }
+    }
 }
 
 template <int AGGR, bool ARG>
@@ -308,91 +316,96 @@ k_edge_aggr(const float *__restrict__ Y, const float *__restrict__ P, const int 
             const int *__restrict__ col, int N, float *__restrict__ out, int *__restrict__ arg, AggrTail tail) {
     __shared__ float s_red[EA_WARPS * 4][3][H];   // per-warp moments (EA_WARPS rows), then the finalize's lane groups
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int sub = lane & 7, grp = lane >> 3;
-    const float4 *__restrict__ Y4 = reinterpret_cast<const float4 *>(Y);
+    const int sub = lane & 15, half = lane >> 4;
+    const float2 *__restrict__ Y2 = reinterpret_cast<const float2 *>(Y);
     const float NEG = -INFINITY;
-    Moments run[4] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
-    for (int i = blockIdx.x * EA_WARPS + warp; i < N; i += gridDim.x * EA_WARPS) {
-        const int beg = __ldg(rowptr + i), end = __ldg(rowptr + i + 1);
-        float4 acc = AGGR == GM_AGGR_MAX ? make_float4(NEG, NEG, NEG, NEG) : make_float4(0.f, 0.f, 0.f, 0.f);
-        int4 barg = make_int4(-1, -1, -1, -1);
+    const float2 IDENT = AGGR == GM_AGGR_MAX ? make_float2(NEG, NEG) : make_float2(0.f, 0.f);
+    // shifted sums for the BatchNorm moments of this warp's outputs (lanes of half 0; 2 channels each)
+    float cnt = 0.f;
+    float2 shift = make_float2(0.f, 0.f), s1 = shift, s2 = shift;
+    const int stride = gridDim.x * EA_WARPS;
+    int i = blockIdx.x * EA_WARPS + warp;
+    // software pipeline over targets: row bounds and the first 32 sources of the NEXT target are fetched
+    // while the current one is reduced
+    int beg = 0, end = 0, jl = -1;
+    if (i < N) {
+        beg = __ldg(rowptr + i); end = __ldg(rowptr + i + 1);
+        jl = lane < end - beg ? __ldg(col + beg + lane) : -1;
+    }
+    while (i < N) {
+        const int inext = i + stride;
+        int nbeg = 0, nend = 0, jnext = -1;
+        if (inext < N) { nbeg = __ldg(rowptr + inext); nend = __ldg(rowptr + inext + 1); }
+        float2 p = make_float2(0.f, 0.f);
+        if (half == 0) p = __ldg(reinterpret_cast<const float2 *>(P) + (size_t)i * (H / 2) + sub);
+        float2 acc = IDENT;
+        int2 barg = make_int2(-1, -1);
         for (int e0 = beg; e0 < end; e0 += 32) {
             const int nb = min(32, end - e0);
-            const int jl = lane < nb ? __ldg(col + e0 + lane) : -1;
-#pragma unroll 2
-            for (int k = 0; k < nb; k += 8) {
-                const int ja = __shfl_sync(0xffffffffu, jl, k + grp);
-                const int jb = __shfl_sync(0xffffffffu, jl, (k + 4 + grp) & 31);
-                const bool va = k + grp < nb, vb = k + 4 + grp < nb;
-                float4 a, b;
-                if (AGGR == GM_AGGR_MAX) { a = make_float4(NEG, NEG, NEG, NEG); b = a; }
-                else { a = make_float4(0.f, 0.f, 0.f, 0.f); b = a; }
-                if (va) a = __ldg(Y4 + (size_t)ja * (H / 4) + sub);
-                if (vb) b = __ldg(Y4 + (size_t)jb * (H / 4) + sub);
-                if (AGGR == GM_AGGR_MAX && ARG) {
-                    if (va) amax4(acc, barg, a, ja);
-                    if (vb) amax4(acc, barg, b, jb);
-                } else if (AGGR == GM_AGGR_MAX) {
-                    acc.x = fmaxf(acc.x, fmaxf(a.x, b.x)); acc.y = fmaxf(acc.y, fmaxf(a.y, b.y));
-                    acc.z = fmaxf(acc.z, fmaxf(a.z, b.z)); acc.w = fmaxf(acc.w, fmaxf(a.w, b.w));
-                } else {
-                    acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
-                    acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
-                }
-            }
-        }
+            if (e0 > beg) jl = lane < nb ? __ldg(col + e0 + lane) : -1;
+            // up to 16 row loads in flight per lane (edge 2u + half of this 32-edge chunk)
+            int ja[8], jb[8];
+            float2 va[8], vb[8];
 #pragma unroll
-        for (int off = 8; off <= 16; off <<= 1) {
-            const float ox = __shfl_xor_sync(0xffffffffu, acc.x, off), oy = __shfl_xor_sync(0xffffffffu, acc.y, off);
-            const float oz = __shfl_xor_sync(0xffffffffu, acc.z, off), ow = __shfl_xor_sync(0xffffffffu, acc.w, off);
-            if (AGGR == GM_AGGR_MAX && !ARG) {
-                acc.x = fmaxf(acc.x, ox); acc.y = fmaxf(acc.y, oy); acc.z = fmaxf(acc.z, oz); acc.w = fmaxf(acc.w, ow);
-            } else if (AGGR == GM_AGGR_MAX) {
-                const int ax = __shfl_xor_sync(0xffffffffu, barg.x, off), ay = __shfl_xor_sync(0xffffffffu, barg.y, off);
-                const int az = __shfl_xor_sync(0xffffffffu, barg.z, off), aw = __shfl_xor_sync(0xffffffffu, barg.w, off);
-                amax_merge(acc.x, barg.x, ox, ax); amax_merge(acc.y, barg.y, oy, ay);
-                amax_merge(acc.z, barg.z, oz, az); amax_merge(acc.w, barg.w, ow, aw);
-            } else {
-                // fixed pairing: (g0+g1)+(g2+g3) evaluated identically in every lane group
-                const bool lo = (lane & off) == 0;
-                acc.x = lo ? acc.x + ox : ox + acc.x; acc.y = lo ? acc.y + oy : oy + acc.y;
-                acc.z = lo ? acc.z + oz : oz + acc.z; acc.w = lo ? acc.w + ow : ow + acc.w;
+            for (int u = 0; u < 8; ++u) ja[u] = __shfl_sync(0xffffffffu, jl, 2 * u + half);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) va[u] = (2 * u + half < nb) ? __ldg(Y2 + (size_t)ja[u] * (H / 2) + sub) : IDENT;
+            if (nb > 16) {
+#pragma unroll
+                for (int u = 0; u < 8; ++u) jb[u] = __shfl_sync(0xffffffffu, jl, 16 + 2 * u + half);
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    vb[u] = (16 + 2 * u + half < nb) ? __ldg(Y2 + (size_t)jb[u] * (H / 2) + sub) : IDENT;
             }
+            if (e0 == beg && inext < N) jnext = lane < nend - nbeg ? __ldg(col + nbeg + lane) : -1;
+            aggr_consume<AGGR, ARG>(acc, barg, va, ja);
+            if (nb > 16) aggr_consume<AGGR, ARG>(acc, barg, vb, jb);
         }
-        if (grp == 0) {
+        if (end == beg && inext < N) jnext = lane < nend - nbeg ? __ldg(col + nbeg + lane) : -1;
+        // fold the two halves
+        const float ox = __shfl_xor_sync(0xffffffffu, acc.x, 16), oy = __shfl_xor_sync(0xffffffffu, acc.y, 16);
+        if (AGGR == GM_AGGR_MAX) {
+            const float mx = fmaxf(acc.x, ox), my = fmaxf(acc.y, oy);
+            if (ARG) {   // lowest source index among the halves that hold the maximum
+                const int cx = acc.x == mx ? barg.x : 0x7fffffff, cy = acc.y == my ? barg.y : 0x7fffffff;
+                barg.x = min(cx, __shfl_xor_sync(0xffffffffu, cx, 16));
+                barg.y = min(cy, __shfl_xor_sync(0xffffffffu, cy, 16));
+            }
+            acc.x = mx; acc.y = my;
+        } else {   // (half 0) + (half 1), evaluated identically in both halves
+            acc.x = half == 0 ? acc.x + ox : ox + acc.x;
+            acc.y = half == 0 ? acc.y + oy : oy + acc.y;
+        }
+        if (half == 0) {
             const int deg = end - beg;
-            const float4 p = __ldg(reinterpret_cast<const float4 *>(P) + (size_t)i * (H / 4) + sub);
-            float4 o;
-            if (deg == 0) o = make_float4(0.f, 0.f, 0.f, 0.f);                       // PyG: empty rows aggregate to 0
-            else if (AGGR == GM_AGGR_MAX) o = make_float4(p.x + acc.x, p.y + acc.y, p.z + acc.z, p.w + acc.w);
-            else if (AGGR == GM_AGGR_ADD) {
-                const float d = (float)deg;
-                o = make_float4(fmaf(d, p.x, acc.x), fmaf(d, p.y, acc.y), fmaf(d, p.z, acc.z), fmaf(d, p.w, acc.w));
-            } else {
+            float2 o;
+            if (deg == 0) o = make_float2(0.f, 0.f);                                  // PyG: empty rows aggregate to 0
+            else if (AGGR == GM_AGGR_MAX) o = make_float2(p.x + acc.x, p.y + acc.y);
+            else if (AGGR == GM_AGGR_ADD) o = make_float2(fmaf((float)deg, p.x, acc.x), fmaf((float)deg, p.y, acc.y));
+            else {
                 const float inv = 1.f / (float)deg;
-                o = make_float4(fmaf(acc.x, inv, p.x), fmaf(acc.y, inv, p.y), fmaf(acc.z, inv, p.z), fmaf(acc.w, inv, p.w));
+                o = make_float2(fmaf(acc.x, inv, p.x), fmaf(acc.y, inv, p.y));
             }
-            reinterpret_cast<float4 *>(out)[(size_t)i * (H / 4) + sub] = o;
-            if (ARG) reinterpret_cast<int4 *>(arg)[(size_t)i * (H / 4) + sub] = barg;
+            reinterpret_cast<float2 *>(out)[(size_t)i * (H / 2) + sub] = o;
+            if (ARG) reinterpret_cast<int2 *>(arg)[(size_t)i * (H / 2) + sub] = barg;
             if (tail.partials) {
-                const float ov[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    run[q].n += 1.f;
-                    const float dl = ov[q] - run[q].mean;
-                    run[q].mean += dl / run[q].n;
-                    run[q].m2 = fmaf(dl, ov[q] - run[q].mean, run[q].m2);
-                }
+                if (cnt == 0.f) shift = o;
+                cnt += 1.f;
+                const float dx = o.x - shift.x, dy = o.y - shift.y;
+                s1.x += dx; s1.y += dy;
+                s2.x = fmaf(dx, dx, s2.x); s2.y = fmaf(dy, dy, s2.y);
             }
         }
+        i = inext; beg = nbeg; end = nend; jl = jnext;
     }
     if (tail.partials) {
-        if (grp == 0) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                s_red[warp][0][4 * sub + q] = run[q].n; s_red[warp][1][4 * sub + q] = run[q].mean;
-                s_red[warp][2][4 * sub + q] = run[q].m2;
-            }
+        if (half == 0) {   // shifted sums -> (n, mean, M2)
+            const float rn = cnt > 0.f ? 1.f / cnt : 0.f;
+            s_red[warp][0][2 * sub] = cnt;     s_red[warp][0][2 * sub + 1] = cnt;
+            s_red[warp][1][2 * sub] = fmaf(s1.x, rn, shift.x);
+            s_red[warp][1][2 * sub + 1] = fmaf(s1.y, rn, shift.y);
+            s_red[warp][2][2 * sub] = fmaxf(s2.x - s1.x * s1.x * rn, 0.f);
+            s_red[warp][2][2 * sub + 1] = fmaxf(s2.y - s1.y * s1.y * rn, 0.f);
         }
         __syncthreads();
         if (warp == 0) {
@@ -585,7 +598,11 @@ int launch_edgeconv_simt(const float *x, const int *rowptr, const int *col, int 
 template <int AGGR>
 int launch_edge_aggr(const float *Y, const float *P, const int *rowptr, const int *col, int N, float *out, int *arg,
                      const AggrTail &tail, cudaStream_t st) {
-    const int grid = persistent_grid((N + EA_WARPS - 1) / EA_WARPS, 4);   // 48-64 registers: 4 CTAs of 256 fit an SM
+    // one resident wave: the grid is (#SM x resident CTAs of this instantiation), found by an occupancy query
+    static int occ[2] = {0, 0};
+    if (!occ[0]) occ[0] = resident_ctas(k_edge_aggr<AGGR, false>, EA_WARPS * 32, 0, 2);
+    if (!occ[1]) occ[1] = resident_ctas(k_edge_aggr<AGGR, true>, EA_WARPS * 32, 0, 2);
+    const int grid = persistent_grid((N + EA_WARPS - 1) / EA_WARPS, min(occ[arg ? 1 : 0], MAX_PARTIAL_CTAS / 148));
     if (arg) k_edge_aggr<AGGR, true><<<grid, EA_WARPS * 32, 0, st>>>(Y, P, rowptr, col, N, out, arg, tail);
     else k_edge_aggr<AGGR, false><<<grid, EA_WARPS * 32, 0, st>>>(Y, P, rowptr, col, N, out, arg, tail);
     GM_LAUNCH_CHECK();
@@ -617,7 +634,7 @@ int edgeconv_direct(const float *x, const int *rowptr, const int *col, int N, co
 }
 
 int node_grid(int N) { return persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 4); }
-int encode_grid(int N) { return persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 2); }   // 214 registers: 2 CTAs/SM
+int encode_grid(int N) { return persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 4); }
 
 }  // namespace
 
