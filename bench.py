@@ -162,6 +162,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "bf16", "tf32x3"])
+    ap.add_argument("--graph", default="implicit", choices=["implicit", "csr"],
+                    help="implicit: cell-staged EdgeConv, no edge list (default; fp32 only). csr: explicit edge list")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -210,7 +212,8 @@ def main():
     torch.manual_seed(0)
     model = gnet.Net(8, 3).to(dev)
     model.graphnet.edge_precision = args.precision
-    trainer = GraphMETTrainer(model, lr=1e-3, process_group=pg)
+    trainer = GraphMETTrainer(model, lr=1e-3, process_group=pg, graph=args.graph)
+    graph_mode = "implicit" if trainer._implicit() else "csr"
     host = [b.pin_memory() for b in make_batches(args.workload, rank)]
     devb = [b.to(dev) for b in host]
     men = [int((b.ptr[1:] - b.ptr[:-1]).max()) for b in host]
@@ -271,14 +274,18 @@ def main():
         if t_n.value:
             timers[name] = (t_ms.value, t_n.value)
 
-    # graph statistics of the rotating batches (for the algorithmic flops / bytes)
-    Es, Ns = [], []
+    # graph statistics of the rotating batches (for the algorithmic flops / bytes), from the explicit radius graph
+    # — outside every timed region; the implicit path never counts its edges
+    from deepmetv2_b200 import ops
+    Es, Ns, max_deg, capped = [], [], 0, 0
     for k in range(N_ROTATE):
-        one_step(k)
-        st = trainer.graph_stats()
-        Es.append(st[0]); Ns.append(devb[k].x.shape[0])
+        _, _, etaphi = ops.prepare_inputs(devb[k].x)
+        g = ops.build_graph(etaphi, 0.4, ptr_i32=devb[k].ptr, loop=True, max_num_neighbors=255)
+        Es.append(g.num_edges); Ns.append(devb[k].x.shape[0])
+        max_deg, capped = max(max_deg, g.max_degree), capped + g.num_capped
+        del g
     E_avg, N_avg = sum(Es) / len(Es), sum(Ns) / len(Ns)
-    max_deg, capped = st[1], st[2]
+    torch.cuda.empty_cache()
 
     # ---------------- end-to-end arm (host buffers, H2D + D2H inside the timed region) ----------------
     for i in range(3):
@@ -339,7 +346,7 @@ def main():
         "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else args.precision, "data": "synthetic",
         "config": {"workload": human, "events_per_gpu": n_ev, "nodes_per_step": N_avg, "edges_per_step": E_avg,
-                   "max_degree": max_deg, "capped_nodes": capped, "edge_precision": args.precision,
+                   "max_degree": max_deg, "capped_nodes": capped, "edge_precision": args.precision, "graph": graph_mode,
                    "l2": "flushed between timed iterations (256 MiB memset)", "rotating_batches": N_ROTATE,
                    "parallelism": f"dp{world}" if world > 1 else "single"},
         "edges_per_sec": E_avg * world * args.steps / (total_ms / 1e3),

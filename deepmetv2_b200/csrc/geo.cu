@@ -1,0 +1,621 @@
+// Cell-staged EdgeConv with an IMPLICIT radius graph (the fused path of GraphMETTrainer).
+//
+// The edge list of radius_graph(etaphi, r, batch, loop, max_num_neighbors) (train.py:48) is never written: nodes run
+// in INTERNAL order (event, cell, original index), every neighbour of a node lies in the <= 3 contiguous runs that
+// cover the 3x3 cells around it, and the kernels below stage those runs ONCE per block of 32 consecutive nodes into
+// shared memory with TMA bulk copies (cp.async.bulk + mbarrier) and re-evaluate the edge predicate of geo_layout.cuh
+// there.  Against the CSR kernels (k_edge_aggr / k_scatter_s) this removes the col[] traffic (4E bytes written, read
+// 3x), fetches each 128-byte row from L2 once per block instead of once per edge, and needs no transposed CSR for
+// the backward, capped graph or not.
+//
+//   gm_geo_build        : bin -> deterministic order inside cells -> node_perm -> cap thresholds (dense cells only)
+//   k_geo_aggr          : out_i = P_i + max_{j in N(i)} Y_j  (+ arg-max, + BatchNorm moments)              [a5 fwd]
+//   k_geo_scatter       : S_j = sum_{i : arg(i,c) == j} d conv_i[c], BatchNorm backward on the fly          [a5 bwd]
+// All reductions run in a fixed order (internal node order): bit-deterministic, no float atomics.
+#include "geo_layout.cuh"
+#include "net_layout.cuh"
+
+namespace gm {
+namespace {
+
+constexpr int GEO_TPI = 32;          // nodes per work item (one warp-width of consecutive internal nodes)
+constexpr int GEO_THREADS = 128;     // backward kernel: 4 warps
+constexpr int GEO_WARPS = GEO_THREADS / 32;
+constexpr int AG_THREADS = 256;      // forward kernel: 8 warps, AG_TPW targets of the item each
+constexpr int AG_WARPS = AG_THREADS / 32;
+constexpr int AG_TPW = GEO_TPI / AG_WARPS;
+constexpr int AG_CH = 128;           // staged neighbourhood rows per pipeline stage
+constexpr int AG_STAGES = 2;
+constexpr int AG_LIST = AG_CH + 8;   // per-warp hit list (uint16 row indices), padded to a multiple of 4
+constexpr unsigned GEO_SPIN_LIMIT = 1u << 24;
+
+// ------------------------------------------------------------------------------------------ PTX: mbarrier + TMA bulk copy
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {   // bounded: a bug must trap, not hang
+#pragma unroll 1
+    for (unsigned it = 0; it < GEO_SPIN_LIMIT; ++it)
+        if (mbar_try_wait(bar, parity)) return;
+    __trap();
+}
+// global -> shared bulk copy through the TMA unit; bytes % 16 == 0, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------ build
+__global__ void k_geo_meta(GeoMeta *m, float r, float r2, int dim, int phi_wrap, int loop, int cap_eff, int N, int B,
+                           int *stats) {
+    if (threadIdx.x == 0) {
+        *m = GeoMeta{r, r2, dim, phi_wrap, loop, cap_eff, N, B};
+        stats[0] = -1;                                   // E is never counted on this path
+    }
+}
+
+// The counting-sort scatter (k_cell_fill) places the points of a cell in atomic (arbitrary) order.  Internal order
+// must be reproducible run to run (it fixes every summation order downstream), so each point is re-ranked inside its
+// cell by original index: thread per slot, O(cell population) compares against L1/L2-resident neighbours.
+__global__ void __launch_bounds__(256) k_cell_rank(const float4 *__restrict__ tmp, const int *__restrict__ ptr, int N,
+                                                   int B, const int *__restrict__ cell_start,
+                                                   float4 *__restrict__ pts, int *__restrict__ perm) {
+    for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < N; s += gridDim.x * blockDim.x) {
+        const int e = find_event(ptr, B, s);
+        const float4 t = tmp[s];
+        const int idx = __float_as_int(t.z), cell = __float_as_int(t.w);
+        const int *cs = cell_start + (size_t)e * (CMAX + 1);
+        const int lo = __ldg(cs + cell), hi = __ldg(cs + cell + 1);
+        int rank = 0;
+        for (int k = lo; k < hi; ++k) rank += __float_as_int(tmp[k].z) < idx;
+        pts[lo + rank] = t;
+        perm[lo + rank] = __ldg(ptr + e) + idx;
+    }
+}
+
+// thr[s] for the targets that can exceed the cap at all (3x3 neighbourhood population > cap): hits are marked in a
+// per-warp shared bitmask indexed by the event-local ORIGINAL index, the cap-th set bit is the last admissible source.
+__global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, int N, int B, const GeoMeta *__restrict__ meta,
+                                                 const int *__restrict__ bbox, const int *__restrict__ cell_start,
+                                                 const float4 *__restrict__ pts, int mask_words, int *__restrict__ thr,
+                                                 int *__restrict__ stats) {
+    extern __shared__ unsigned int smask[];
+    const GeoMeta m = *meta;
+    const CellGrid g = make_grid(bbox, m.r, m.dim, m.phi_wrap);
+    const int lane = threadIdx.x & 31;
+    unsigned int *mask = smask + (size_t)(threadIdx.x >> 5) * mask_words;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    int local_max = 0, local_capped = 0;
+    for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < N; s += warps) {
+        const int e = find_event(ptr, B, s);
+        const int base = __ldg(ptr + e), n_e = __ldg(ptr + e + 1) - base;
+        const float4 t = pts[s];
+        const int cell = __float_as_int(t.w);
+        const int ce = cell / g.g1, cp = cell - ce * g.g1;
+        int rlo[6], rhi[6];
+        const int nr = nbhd_runs(g, cell_start + (size_t)e * (CMAX + 1), ce, cp, cp, m.phi_wrap, rlo, rhi);
+        int C = 0;
+        for (int q = 0; q < nr; ++q) C += rhi[q] - rlo[q];
+        if (C <= m.cap_eff) continue;                      // cannot be capped: thr stays INT_MAX-like
+        const int words = (n_e + 31) >> 5;
+        if (words > mask_words) {                          // host promised a smaller max_event_nodes
+            if (lane == 0) atomicOr(stats + 3, GM_FLAG_EVENT_TOO_LARGE);
+            continue;
+        }
+        for (int w = lane; w < words; w += 32) mask[w] = 0u;
+        __syncwarp();
+        for (int q = 0; q < nr; ++q)
+            for (int k = rlo[q] + lane; k < rhi[q]; k += 32) {
+                const float4 c = pts[k];
+                if (dist2(t.x, t.y, c.x, c.y, m.dim, m.phi_wrap) < m.r2) {
+                    const int cl = __float_as_int(c.z);
+                    atomicOr(mask + (cl >> 5), 1u << (cl & 31));
+                }
+            }
+        __syncwarp();
+        int found = 0x7fffffff, seen = 0;
+        for (int w0 = 0; w0 < words; w0 += 32) {
+            const unsigned int word = (w0 + lane < words) ? mask[w0 + lane] : 0u;
+            int tot;
+            const int before = seen + warp_excl_scan_int(__popc(word), lane, tot);
+            if (before < m.cap_eff && before + __popc(word) >= m.cap_eff) {   // the cap-th hit (1-based) is in this word
+                unsigned int v = word;
+                for (int k = m.cap_eff - before - 1; k > 0; --k) v &= v - 1;
+                found = ((w0 + lane) << 5) + __ffs(v) - 1;
+            }
+            seen += tot;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) found = min(found, __shfl_xor_sync(0xffffffffu, found, o));
+        if (lane == 0) {
+            local_max = max(local_max, seen);
+            if (seen > m.cap_eff) { thr[s] = found; ++local_capped; }
+        }
+        __syncwarp();
+    }
+    if (lane == 0) {
+        if (local_max) atomicMax(stats + 1, local_max);
+        if (local_capped) { atomicAdd(stats + 2, local_capped); atomicOr(stats + 3, GM_FLAG_DEGREE_CAPPED); }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ staging machinery
+// A work item = GEO_TPI consecutive internal nodes.  It is cut into SEGMENTS of equal (event, eta-row); the
+// neighbourhood of a segment whose nodes sit in phi cells cpa..cpb is the <= 6 runs of nbhd_runs, flattened into
+// "virtual rows" 0..C-1 and staged AG_CH (forward) / SC_CH (backward) rows at a time.
+struct SegStage {
+    int nr;            // runs
+    int rlo[6];        // first internal node of run q
+    int voff[7];       // first virtual row of run q; voff[nr] = C
+};
+
+struct GeoView {       // device pointers of a built GeoWs (passed by value)
+    const GeoMeta *meta;
+    const int *bbox, *cell_start, *ptr, *thr;
+    const float4 *pts;
+};
+
+// forward kernel: [stage]{ (AG_CH + 1) rows x 128 B (last row: identity), AG_CH points x 16 B }
+constexpr size_t AG_STAGE_BYTES = (size_t)(AG_CH + 1) * 128 + (size_t)AG_CH * 16;
+constexpr size_t AG_OFF_PTS = (size_t)(AG_CH + 1) * 128;                   // inside a stage
+constexpr size_t AG_LISTS = AG_STAGES * AG_STAGE_BYTES;                    // AG_WARPS x AG_LIST x u16
+constexpr size_t AG_ITEM = AG_LISTS + (size_t)AG_WARPS * AG_LIST * 2;      // heads, e[32], cell[32]
+constexpr size_t AG_SEG = AG_ITEM + 66 * 4;                                // SegStage
+constexpr size_t AG_BAR = (AG_SEG + sizeof(SegStage) + 7) / 8 * 8;
+constexpr size_t AG_TOTAL = AG_BAR + 8 * AG_STAGES;
+static_assert(AG_STAGE_BYTES % 128 == 0 && AG_LISTS % 8 == 0 && (AG_LIST * 2) % 8 == 0, "staging alignment");
+static_assert(AG_STAGES * AG_STAGE_BYTES >= (size_t)(AG_THREADS / 8) * 3 * H * 4, "BatchNorm scratch aliases the stages");
+
+// warp 0: find the (event, eta-row) segments of the item's nodes
+__device__ __forceinline__ void item_segments(const GeoView &v, const CellGrid &g, int B, int n0, int cnt, int lane,
+                                              int *s_item) {
+    const int node = n0 + lane;
+    const bool valid = lane < cnt;
+    const int e = valid ? find_event(v.ptr, B, node) : -1;
+    const int cell = valid ? __float_as_int(v.pts[node].w) : 0;
+    const int key = valid ? ((e << 5) | (cell / g.g1)) : -1;
+    const int prev = __shfl_up_sync(0xffffffffu, key, 1);
+    const unsigned heads = __ballot_sync(0xffffffffu, valid && (lane == 0 || key != prev));
+    s_item[1 + lane] = e;
+    s_item[33 + lane] = cell;
+    if (lane == 0) s_item[0] = (int)heads;
+}
+
+// thread 0: runs of the segment [a, b) of the item
+__device__ __forceinline__ void segment_runs(const GeoView &v, const CellGrid &g, int phi_wrap, const int *s_item, int a,
+                                             int b, SegStage *seg) {
+    const int e = s_item[1 + a], ca = s_item[33 + a], cb = s_item[33 + b - 1];
+    const int ce = ca / g.g1;
+    int rlo[6], rhi[6];
+    const int nr = nbhd_runs(g, v.cell_start + (size_t)e * (CMAX + 1), ce, ca - ce * g.g1, cb - ce * g.g1, phi_wrap,
+                             rlo, rhi);
+    int off = 0, n = 0;
+    for (int q = 0; q < nr; ++q) {
+        if (rhi[q] <= rlo[q]) continue;
+        seg->rlo[n] = rlo[q]; seg->voff[n] = off; off += rhi[q] - rlo[q]; ++n;
+    }
+    seg->voff[n] = off;
+    seg->nr = n;
+}
+
+// thread 0: issue the TMA bulk copies of chunk k (virtual rows k*AG_CH ...) into one pipeline stage:
+// points + one 128-byte row array
+__device__ __forceinline__ void issue_chunk(const SegStage *seg, int k, const float4 *__restrict__ pts,
+                                            const void *__restrict__ rows128, uint32_t s_stage, uint32_t bar) {
+    const int c0 = k * AG_CH, c1 = min(seg->voff[seg->nr], c0 + AG_CH);
+    mbar_expect_tx(bar, (uint32_t)(c1 - c0) * (128u + 16u));
+    for (int q = 0; q < seg->nr; ++q) {
+        const int lo = max(seg->voff[q], c0), hi = min(seg->voff[q + 1], c1);
+        if (lo >= hi) continue;
+        const size_t node = (size_t)(seg->rlo[q] + (lo - seg->voff[q]));
+        const uint32_t n = (uint32_t)(hi - lo), row = (uint32_t)(lo - c0);
+        bulk_g2s(s_stage + (uint32_t)AG_OFF_PTS + row * 16u, pts + node, n * 16u, bar);
+        bulk_g2s(s_stage + row * 128u, reinterpret_cast<const char *>(rows128) + node * 128, n * 128u, bar);
+    }
+}
+
+__device__ __forceinline__ int node_of_row(const SegStage *seg, int k, int row) {
+    const int vr = k * AG_CH + row;
+    int q = 0;
+    while (q + 1 < seg->nr && vr >= seg->voff[q + 1]) ++q;
+    return seg->rlo[q] + (vr - seg->voff[q]);
+}
+
+// Hit list of one target against the staged chunk: rows whose point passes the edge predicate of geo_layout.cuh, in
+// staged order, padded with 4 x the identity row.  th = cap threshold of the target, excl = local index to exclude
+// (the target itself when loop == 0, -1 otherwise).  Returns the hit count.
+__device__ __forceinline__ int build_hit_list(const float4 *s_pts, int rows, float px, float py, int th, int excl,
+                                              const GeoMeta &m, int lane, unsigned short *list) {
+    int nh = 0;
+    for (int base = 0; base < rows; base += 32) {
+        const int c = base + lane;
+        bool hit = false;
+        if (c < rows) {
+            const float4 q = s_pts[c];
+            const int cl = __float_as_int(q.z);
+            hit = dist2(px, py, q.x, q.y, m.dim, m.phi_wrap) < m.r2 && cl <= th && cl != excl;
+        }
+        const unsigned mk = __ballot_sync(0xffffffffu, hit);
+        if (hit) list[nh + __popc(mk & ((1u << lane) - 1u))] = (unsigned short)c;
+        nh += __popc(mk);
+    }
+    if (lane < 4) list[nh + lane] = (unsigned short)AG_CH;
+    __syncwarp();
+    return nh;
+}
+
+// ------------------------------------------------------------------------------------------ forward: aggregate
+// out_i = P_i + max_{j in N(i)} Y_j (add / mean alike).  8 warps; a warp owns AG_TPW targets of the item and keeps
+// their running max / arg-max in REGISTERS while the neighbourhood streams through a 2-stage TMA pipeline of AG_CH
+// rows (points + Y rows): thread 0 refills a stage as soon as the CTA has consumed it, so copies overlap the
+// reduction.  Per (target, chunk): lanes test 32 candidate points at a time and compact the hits (ballot + popc)
+// into a per-warp list, then lane = channel walks the list 4 rows at a time out of shared memory.
+template <int AGGR, bool ARG>
+__global__ void __launch_bounds__(AG_THREADS, 3)
+k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, int N, float *__restrict__ out,
+           int *__restrict__ arg, AggrTail tail) {
+    extern __shared__ __align__(128) unsigned char gs[];
+    int *s_item = reinterpret_cast<int *>(gs + AG_ITEM);
+    SegStage *seg = reinterpret_cast<SegStage *>(gs + AG_SEG);
+    const uint32_t bar0 = smem_u32(gs + AG_BAR);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned short *list = reinterpret_cast<unsigned short *>(gs + AG_LISTS) + warp * AG_LIST;
+
+    const GeoMeta m = *v.meta;
+    const CellGrid g = make_grid(v.bbox, m.r, m.dim, m.phi_wrap);
+    const float IDENT = AGGR == GM_AGGR_MAX ? -INFINITY : 0.f;
+    if (tid == 0) {
+        for (int s = 0; s < AG_STAGES; ++s) mbar_init(bar0 + 8u * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp < AG_STAGES) reinterpret_cast<float *>(gs + warp * AG_STAGE_BYTES)[AG_CH * 32 + lane] = IDENT;
+    __syncthreads();
+
+    uint32_t phases = 0u;                                   // bit s = parity of pipeline stage s
+    float cnt = 0.f, shift = 0.f, s1 = 0.f, s2 = 0.f;      // BatchNorm moments of this warp's outputs (lane = channel)
+    const int n_items = (N + GEO_TPI - 1) / GEO_TPI;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int n0 = item * GEO_TPI, icnt = min(GEO_TPI, N - n0);
+        if (warp == 0) item_segments(v, g, m.B, n0, icnt, lane, s_item);
+        __syncthreads();
+        unsigned heads = (unsigned)s_item[0];
+        while (heads) {
+            const int a = __ffs(heads) - 1;
+            heads &= heads - 1;
+            const int b = heads ? __ffs(heads) - 1 : icnt;
+            if (tid == 0) {
+                segment_runs(v, g, m.phi_wrap, s_item, a, b, seg);
+                const int nck = (seg->voff[seg->nr] + AG_CH - 1) / AG_CH;
+                for (int k = 0; k < min(nck, AG_STAGES); ++k)
+                    issue_chunk(seg, k, v.pts, Y, smem_u32(gs + k * AG_STAGE_BYTES), bar0 + 8u * k);
+            }
+            // this warp's targets of the segment: a + warp, a + warp + 8, ...
+            float px[AG_TPW], py[AG_TPW], acc[AG_TPW];
+            int th[AG_TPW], excl[AG_TPW], barg[AG_TPW], deg[AG_TPW];
+#pragma unroll
+            for (int u = 0; u < AG_TPW; ++u) {
+                const int t = a + warp + u * AG_WARPS;
+                acc[u] = IDENT; barg[u] = -1; deg[u] = 0; px[u] = 0.f; py[u] = 0.f; th[u] = 0; excl[u] = -1;
+                if (t < b) {
+                    const float4 pt = __ldg(v.pts + n0 + t);
+                    px[u] = pt.x; py[u] = pt.y;
+                    th[u] = __ldg(v.thr + n0 + t);
+                    excl[u] = m.loop ? -1 : __float_as_int(pt.z);
+                }
+            }
+            __syncthreads();
+            const int C = seg->voff[seg->nr];
+            const int nchunks = (C + AG_CH - 1) / AG_CH;
+            for (int k = 0; k < nchunks; ++k) {
+                const int st = k & 1;
+                const int rows = min(AG_CH, C - k * AG_CH);
+                const float *s_rows = reinterpret_cast<const float *>(gs + st * AG_STAGE_BYTES);
+                const float4 *s_pts = reinterpret_cast<const float4 *>(gs + st * AG_STAGE_BYTES + AG_OFF_PTS);
+                mbar_wait(bar0 + 8u * st, (phases >> st) & 1u);
+                phases ^= 1u << st;
+#pragma unroll
+                for (int u = 0; u < AG_TPW; ++u) {
+                    if (a + warp + u * AG_WARPS >= b) continue;                 // warp-uniform
+                    const int nh = build_hit_list(s_pts, rows, px[u], py[u], th[u], excl[u], m, lane, list);
+                    deg[u] += nh;
+                    float ac = acc[u];
+                    int brow = -1;
+                    for (int k4 = 0; k4 < nh; k4 += 4) {
+                        const uint2 rr = *reinterpret_cast<const uint2 *>(list + k4);
+                        const int r0 = rr.x & 0xffff, r1 = rr.x >> 16, r2 = rr.y & 0xffff, r3 = rr.y >> 16;
+                        const float v0 = s_rows[r0 * 32 + lane], v1 = s_rows[r1 * 32 + lane];
+                        const float v2 = s_rows[r2 * 32 + lane], v3 = s_rows[r3 * 32 + lane];
+                        if (AGGR == GM_AGGR_MAX && ARG) {
+                            if (v0 > ac) { ac = v0; brow = r0; }
+                            if (v1 > ac) { ac = v1; brow = r1; }
+                            if (v2 > ac) { ac = v2; brow = r2; }
+                            if (v3 > ac) { ac = v3; brow = r3; }
+                        } else if (AGGR == GM_AGGR_MAX) {
+                            ac = fmaxf(fmaxf(ac, v0), fmaxf(v1, fmaxf(v2, v3)));
+                        } else {
+                            ac += v0; ac += v1; ac += v2; ac += v3;
+                        }
+                    }
+                    acc[u] = ac;
+                    if (ARG && brow >= 0) barg[u] = node_of_row(seg, k, brow);
+                    __syncwarp();                                   // the hit list is reused by the next target
+                }
+                __syncthreads();                                    // stage st fully consumed
+                if (tid == 0 && k + AG_STAGES < nchunks)
+                    issue_chunk(seg, k + AG_STAGES, v.pts, Y, smem_u32(gs + st * AG_STAGE_BYTES), bar0 + 8u * st);
+            }
+#pragma unroll
+            for (int u = 0; u < AG_TPW; ++u) {
+                const int t = a + warp + u * AG_WARPS;
+                if (t >= b) continue;
+                const size_t node = (size_t)(n0 + t);
+                const float p = __ldg(P + node * H + lane);
+                float o;
+                if (deg[u] == 0) o = 0.f;                                  // PyG: empty rows aggregate to 0
+                else if (AGGR == GM_AGGR_MAX) o = p + acc[u];
+                else if (AGGR == GM_AGGR_ADD) o = fmaf((float)deg[u], p, acc[u]);
+                else o = fmaf(acc[u], 1.f / (float)deg[u], p);
+                out[node * H + lane] = o;
+                if (ARG) arg[node * H + lane] = barg[u];
+                if (tail.partials) {
+                    if (cnt == 0.f) shift = o;
+                    cnt += 1.f;
+                    const float d = o - shift;
+                    s1 += d;
+                    s2 = fmaf(d, d, s2);
+                }
+            }
+        }
+    }
+    if (tail.partials) {
+        float(*s_red)[3][H] = reinterpret_cast<float(*)[3][H]>(gs);      // aliases the (now idle) pipeline stages
+        __syncthreads();
+        const float rn = cnt > 0.f ? 1.f / cnt : 0.f;
+        s_red[warp][0][lane] = cnt;
+        s_red[warp][1][lane] = fmaf(s1, rn, shift);
+        s_red[warp][2][lane] = fmaxf(s2 - s1 * s1 * rn, 0.f);
+        __syncthreads();
+        if (warp == 0) {
+            Moments tot{0.f, 0.f, 0.f};
+#pragma unroll
+            for (int k = 0; k < AG_WARPS; ++k)
+                tot = moments_combine(tot, Moments{s_red[k][0][lane], s_red[k][1][lane], s_red[k][2][lane]});
+            float *dst = tail.partials + (size_t)blockIdx.x * MOM_STRIDE;
+            dst[lane] = tot.n; dst[H + lane] = tot.mean; dst[2 * H + lane] = tot.m2;
+        }
+        if (last_cta_done(tail.counter))
+            bn_finalize_cta(tail.partials, gridDim.x, tail.bn, tail.momentum, tail.eps, tail.stat, s_red);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ backward: route to sources
+// S[j][c] = sum over targets i with arg(i,c) == j of d conv_i[c]   (max-aggregation sends each (target, channel)
+// gradient to ONE edge; d conv = BatchNorm backward of G, evaluated on the fly).
+// Work item = 32 consecutive SOURCES.  Every target that can point at them lies in their cell neighbourhood, whose
+// arg / G / raw rows are streamed through shared memory by TMA (2-stage pipeline).  Each warp walks staged target
+// rows; lane c looks at arg(i,c) and, if that source belongs to the item, adds d conv_i[c] into ITS column of a
+// per-warp [32 sources][32 channels] accumulator — a lane owns its column, so there are no conflicts and no atomics.
+// No distance test, no cap threshold, no transposed graph: arg == j already says the edge exists.  The four warp
+// accumulators are folded in warp order and rows are walked in staged (= internal node) order: bit-deterministic.
+constexpr int SC_CH = 64;                      // staged target rows per pipeline stage
+constexpr int SC_STAGES = 2;
+constexpr size_t SC_ROWS = 0;                                                  // [stage][arg | G | raw][SC_CH][32] x 4 B
+constexpr size_t SC_STAGE_BYTES = (size_t)3 * SC_CH * 128;
+constexpr size_t SC_ACC = SC_ROWS + SC_STAGES * SC_STAGE_BYTES;                // [GEO_WARPS][32][32] f32
+constexpr size_t SC_COEF = SC_ACC + (size_t)GEO_WARPS * 32 * 32 * 4;           // [5][32] f32
+constexpr size_t SC_ITEM = SC_COEF + 5 * 32 * 4;
+constexpr size_t SC_SEG = SC_ITEM + 66 * 4;
+constexpr size_t SC_BAR = (SC_SEG + sizeof(SegStage) + 7) / 8 * 8;
+constexpr size_t SC_TOTAL = SC_BAR + 8 * SC_STAGES;
+
+// thread 0: TMA bulk copies of chunk k of the segment: three 128-byte row arrays
+__device__ __forceinline__ void issue_chunk3(const SegStage *seg, int k, const void *__restrict__ a0,
+                                             const void *__restrict__ a1, const void *__restrict__ a2, uint32_t s_dst,
+                                             uint32_t bar) {
+    const int c0 = k * SC_CH, c1 = min(seg->voff[seg->nr], c0 + SC_CH);
+    mbar_expect_tx(bar, (uint32_t)(c1 - c0) * 384u);
+    for (int q = 0; q < seg->nr; ++q) {
+        const int lo = max(seg->voff[q], c0), hi = min(seg->voff[q + 1], c1);
+        if (lo >= hi) continue;
+        const size_t off = (size_t)(seg->rlo[q] + (lo - seg->voff[q])) * 128;
+        const uint32_t n = (uint32_t)(hi - lo) * 128u, row = (uint32_t)(lo - c0) * 128u;
+        bulk_g2s(s_dst + row, reinterpret_cast<const char *>(a0) + off, n, bar);
+        bulk_g2s(s_dst + SC_CH * 128u + row, reinterpret_cast<const char *>(a1) + off, n, bar);
+        bulk_g2s(s_dst + 2u * SC_CH * 128u + row, reinterpret_cast<const char *>(a2) + off, n, bar);
+    }
+}
+
+__global__ void __launch_bounds__(GEO_THREADS)
+k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd bn, const int *__restrict__ arg,
+              GeoView v, int N, float *__restrict__ S) {
+    extern __shared__ __align__(128) unsigned char gs[];
+    float(*s_acc)[32][32] = reinterpret_cast<float(*)[32][32]>(gs + SC_ACC);
+    float *s_coef = reinterpret_cast<float *>(gs + SC_COEF);
+    int *s_item = reinterpret_cast<int *>(gs + SC_ITEM);
+    SegStage *seg = reinterpret_cast<SegStage *>(gs + SC_SEG);
+    const uint32_t bar0 = smem_u32(gs + SC_BAR);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    const GeoMeta m = *v.meta;
+    const CellGrid g = make_grid(v.bbox, m.r, m.dim, m.phi_wrap);
+    if (tid == 0) {
+        for (int s = 0; s < SC_STAGES; ++s) mbar_init(bar0 + 8u * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    bn_bwd_coeffs(bn, s_coef);
+    for (int i = lane; i < 32 * 32; i += 32) (&s_acc[warp][0][0])[i] = 0.f;
+    __syncthreads();
+    const float c_mean = s_coef[lane], c_inv = s_coef[H + lane], c_scale = s_coef[2 * H + lane];
+    const float c_1 = s_coef[3 * H + lane], c_2 = s_coef[4 * H + lane];
+
+    uint32_t phases = 0u;                                   // bit s = parity of pipeline stage s
+    const int n_items = (N + GEO_TPI - 1) / GEO_TPI;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int n0 = item * GEO_TPI, icnt = min(GEO_TPI, N - n0);
+        if (warp == 0) item_segments(v, g, m.B, n0, icnt, lane, s_item);
+        __syncthreads();
+        unsigned heads = (unsigned)s_item[0];
+        while (heads) {
+            const int a = __ffs(heads) - 1;
+            heads &= heads - 1;
+            const int b = heads ? __ffs(heads) - 1 : icnt;
+            if (tid == 0) {
+                segment_runs(v, g, m.phi_wrap, s_item, a, b, seg);
+                const int nck = (seg->voff[seg->nr] + SC_CH - 1) / SC_CH;
+                for (int k = 0; k < min(nck, SC_STAGES); ++k)
+                    issue_chunk3(seg, k, arg, G, raw, smem_u32(gs + SC_ROWS + k * SC_STAGE_BYTES), bar0 + 8u * k);
+            }
+            __syncthreads();
+            const int C = seg->voff[seg->nr];
+            const int nchunks = (C + SC_CH - 1) / SC_CH;
+            const unsigned first = (unsigned)(n0 + a), span = (unsigned)(b - a);
+            for (int k = 0; k < nchunks; ++k) {
+                const int st = k & 1;
+                const int rows = min(SC_CH, C - k * SC_CH);
+                const int *s_arg = reinterpret_cast<const int *>(gs + SC_ROWS + st * SC_STAGE_BYTES);
+                const float *s_G = reinterpret_cast<const float *>(s_arg + SC_CH * 32);
+                const float *s_R = s_G + SC_CH * 32;
+                mbar_wait(bar0 + 8u * st, (phases >> st) & 1u);
+                phases ^= 1u << st;
+#pragma unroll 2
+                for (int r = warp; r < rows; r += GEO_WARPS) {
+                    const unsigned rel = (unsigned)s_arg[r * 32 + lane] - first;
+                    if (rel < span) {                                      // this lane's arg-max source is in the item
+                        const float xhat = (s_R[r * 32 + lane] - c_mean) * c_inv;
+                        const float d = c_scale * (s_G[r * 32 + lane] - c_1 - xhat * c_2);
+                        s_acc[warp][a + rel][lane] += d;
+                    }
+                }
+                __syncthreads();                                           // stage st fully consumed
+                if (tid == 0 && k + SC_STAGES < nchunks)
+                    issue_chunk3(seg, k + SC_STAGES, arg, G, raw, smem_u32(gs + SC_ROWS + st * SC_STAGE_BYTES),
+                                 bar0 + 8u * st);
+            }
+            // fold the warp accumulators of this segment's sources in warp order, write S, clear for the next use
+            for (int idx = tid; idx < (b - a) * 32; idx += GEO_THREADS) {
+                const int t = a + (idx >> 5), c = idx & 31;
+                float tot = 0.f;
+#pragma unroll
+                for (int w = 0; w < GEO_WARPS; ++w) { tot += s_acc[w][t][c]; s_acc[w][t][c] = 0.f; }
+                S[(size_t)(n0 + t) * H + c] = tot;
+            }
+            __syncthreads();
+        }
+    }
+}
+
+GeoView view_of(const void *geo_ws, int N, int B) {
+    GeoWs w;
+    geo_ws_layout(N, B, (char *)geo_ws, &w);
+    return GeoView{w.meta, w.bbox, w.cell_start, w.ptr, w.thr, w.pts};
+}
+
+// ------------------------------------------------------------------------------------------ launchers
+template <int AGGR>
+int launch_geo_aggr(const float *Y, const float *P, const GeoView &v, int N, float *out, int *arg,
+                    const AggrTail &tail, cudaStream_t st) {
+    static int occ[2] = {0, 0};
+    const int which = arg ? 1 : 0;
+    if (!occ[which]) {
+        if (arg) {
+            GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_aggr<AGGR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AG_TOTAL));
+            occ[1] = resident_ctas(k_geo_aggr<AGGR, true>, AG_THREADS, AG_TOTAL, 3);
+        } else {
+            GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_aggr<AGGR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AG_TOTAL));
+            occ[0] = resident_ctas(k_geo_aggr<AGGR, false>, AG_THREADS, AG_TOTAL, 3);
+        }
+    }
+    const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, min(occ[which], MAX_PARTIAL_CTAS / 148));
+    if (arg) k_geo_aggr<AGGR, true><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, tail);
+    else k_geo_aggr<AGGR, false><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, tail);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+}  // namespace
+
+int geo_edge_aggr(int aggr, const float *Y, const float *P, const void *geo_ws, int N, int B, float *out, int *arg,
+                  const AggrTail &tail, cudaStream_t st) {
+    if (!geo_ws || B < 1) return GM_ERR_INVALID_ARGUMENT;
+    const GeoView v = view_of(geo_ws, N, B);
+    switch (aggr) {
+        case GM_AGGR_MAX: return launch_geo_aggr<GM_AGGR_MAX>(Y, P, v, N, out, arg, tail, st);
+        case GM_AGGR_ADD: return launch_geo_aggr<GM_AGGR_ADD>(Y, P, v, N, out, arg, tail, st);
+        case GM_AGGR_MEAN: return launch_geo_aggr<GM_AGGR_MEAN>(Y, P, v, N, out, arg, tail, st);
+    }
+    return GM_ERR_INVALID_ARGUMENT;
+}
+
+int geo_scatter_s(const float *G, const float *raw, const BnBwd &bn, const int *arg, const void *geo_ws, int N, int B,
+                  float *S, cudaStream_t st) {
+    if (!geo_ws || B < 1) return GM_ERR_INVALID_ARGUMENT;
+    const GeoView v = view_of(geo_ws, N, B);
+    static int occ = 0;
+    if (!occ) {
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SC_TOTAL));
+        occ = resident_ctas(k_geo_scatter, GEO_THREADS, SC_TOTAL, 3);
+    }
+    const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, occ);
+    k_geo_scatter<<<grid, GEO_THREADS, SC_TOTAL, st>>>(G, raw, bn, arg, v, N, S);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+}  // namespace gm
+
+using namespace gm;
+
+extern "C" {
+
+size_t gm_geo_ws_bytes(int N, int B) { return geo_ws_layout(N < 0 ? 0 : N, B < 0 ? 0 : B, nullptr, nullptr); }
+
+int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B, double r,
+                 int max_num_neighbors, int loop, int phi_wrap, int max_event_nodes, void *ws, size_t ws_bytes,
+                 int *node_perm_out, int *stats_out, void *stream) {
+    if (N < 0 || B < 1 || !ptr || !ws || (N > 0 && (!pos || !node_perm_out))) return GM_ERR_INVALID_ARGUMENT;
+    if (!(r > 0.0) || max_num_neighbors < 1 || max_event_nodes < 0) return GM_ERR_INVALID_ARGUMENT;
+    if (dim < 1 || dim > 2) return GM_ERR_UNSUPPORTED;
+    if (ws_bytes < geo_ws_layout(N, B, nullptr, nullptr)) return GM_ERR_CAPACITY;
+    cudaStream_t st = as_stream(stream);
+    GeoWs w;
+    geo_ws_layout(N, B, (char *)ws, &w);
+    TimedRegion tr(GM_TIMER_RADIUS_GRAPH, st);
+    const float rf = (float)r, r2 = (float)(r * r);          // r*r in double, then fp32
+    const int cap_eff = loop ? max_num_neighbors : max_num_neighbors + 1;
+    GM_TRY(bin_points(pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt, w.cell_start, w.tmp, w.stats, st));
+    k_geo_meta<<<1, 32, 0, st>>>(w.meta, rf, r2, dim, phi_wrap, loop, cap_eff, N, B, w.stats);
+    GM_LAUNCH_CHECK();
+    GM_CUDA_TRY(cudaMemcpyAsync(w.ptr, ptr, (size_t)(B + 1) * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    if (N > 0) {
+        k_cell_rank<<<persistent_grid((N + 255) / 256, 8), 256, 0, st>>>(w.tmp, ptr, N, B, w.cell_start, w.pts, node_perm_out);
+        GM_LAUNCH_CHECK();
+        GM_CUDA_TRY(cudaMemsetAsync(w.thr, 0x7f, (size_t)N * sizeof(int), st));    // 0x7f7f7f7f: "not capped"
+        const int mask_words = (max_event_nodes + 31) / 32 + 1;
+        int threads = 256;
+        while (threads > 32 && (size_t)(threads / 32) * mask_words * 4 > 200 * 1024) threads >>= 1;
+        const size_t smem = (size_t)(threads / 32) * mask_words * 4;
+        if (smem > 200 * 1024) return GM_ERR_UNSUPPORTED;
+        if (smem > 48 * 1024)
+            GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_cap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int grid = persistent_grid(((long long)N * 32 + threads - 1) / threads, 2048 / threads);
+        k_geo_cap<<<grid, threads, smem, st>>>(ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts, mask_words, w.thr, w.stats);
+        GM_LAUNCH_CHECK();
+    }
+    if (stats_out) GM_CUDA_TRY(cudaMemcpyAsync(stats_out, w.stats, 4 * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    return GM_OK;
+}
+
+}  // extern "C"

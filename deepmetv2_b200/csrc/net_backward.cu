@@ -18,6 +18,7 @@
 //
 // Parameter-gradient GEMMs (dW = sum_n a_n (x) b_n) are split-K over node tiles: every CTA keeps 4x4
 // register blocks of the outer product for its tiles, the per-CTA results are summed in CTA order.
+#include "geo_layout.cuh"
 #include "net_layout.cuh"
 
 namespace gm {
@@ -175,41 +176,6 @@ __global__ void __launch_bounds__(256) k_reduce_partials(Segs segs) {
         for (int k = 0; k < 8; ++k) t += sm[k][threadIdx.x];
         sg.dst[r * sg.dst_ld + c] = t;
     }
-}
-
-// ----------------------------------------------------------------------------------------- BatchNorm-backward plumbing
-// What a consumer needs to turn G into d(raw) for one BatchNorm: per channel
-//     d(raw) = scale * (G - c1 - (raw - mean) * invstd * c2),  c1 = sum(G)/N, c2 = sum(G*xhat)/N  (train)
-//                                                              c1 = c2 = 0                        (eval)
-struct BnBwd {
-    const float *stat;      // mean[32], scale[32], invstd[32], beta[32]   (forward)
-    const float *sum;       // sum(G)[32], sum(G*xhat)[32]                 (from the producer's last CTA)
-    float inv_n;            // 1/N in train mode, 0 in eval mode
-};
-// Producer side: where the per-CTA partial sums go and what the last CTA writes.
-struct BnSumOut {
-    const float *raw;       // [N,32] pre-BatchNorm activations of the BatchNorm being differentiated
-    const float *stat;
-    float *part;            // [grid][64]
-    float *sum;             // [64]
-    float *dgamma, *dbeta;  // gradient tensors (may be NULL)
-    int *counter;
-};
-
-// smem coefficient table for BnBwd: [5][32] = mean, invstd, scale, c1, c2
-__device__ __forceinline__ void bn_bwd_coeffs(const BnBwd &b, float *s_coef) {
-    const int t = threadIdx.x;
-    if (t < H) {
-        s_coef[t] = b.stat[t];
-        s_coef[H + t] = b.stat[2 * H + t];
-        s_coef[2 * H + t] = b.stat[H + t];
-        s_coef[3 * H + t] = b.sum[t] * b.inv_n;
-        s_coef[4 * H + t] = b.sum[H + t] * b.inv_n;
-    }
-}
-__device__ __forceinline__ float bn_bwd_one(const float *s_coef, int c, float g, float raw) {
-    const float xhat = (raw - s_coef[c]) * s_coef[H + c];
-    return s_coef[2 * H + c] * (g - s_coef[3 * H + c] - xhat * s_coef[4 * H + c]);
 }
 
 // Last CTA: fold the per-CTA (sum G, sum G*xhat) partials in a fixed order.  blockDim.x == NODE_TILE: 16 lane
@@ -645,17 +611,19 @@ size_t gm_net_bwd_ws_bytes(int N, int conv_depth) {
     return bwd_ws_layout(N < 0 ? 0 : N, nullptr, nullptr);
 }
 
-int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
-                    const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride, const int *rowptr,
-                    const int *col, const int *rowptr_t, const int *col_t, const int *use_transposed_flag, int N,
-                    const int *node_perm, int training, int apply_sigmoid, int aggr, float eps, const void *fwd_ws,
-                    size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes, const float *out, const float *grad_out,
-                    void *stream) {
-    (void)eps;
+}  // extern "C"
+
+// Shared body of gm_net_backward (explicit CSR) and gm_net_backward_geo (implicit radius graph: geo_ws != NULL).
+static int net_backward_impl(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
+                             const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride, const int *rowptr,
+                             const int *col, const int *rowptr_t, const int *col_t, const int *use_transposed_flag,
+                             const void *geo_ws, int B, int N, const int *node_perm, int training, int apply_sigmoid,
+                             int aggr, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
+                             const float *out, const float *grad_out, void *stream) {
     GM_TRY(check_params(p));
     if (!grads || N < 0 || !fwd_ws || !bwd_ws) return GM_ERR_INVALID_ARGUMENT;
     if (aggr != GM_AGGR_MAX) return GM_ERR_UNSUPPORTED;
-    if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || !rowptr_t || !col_t || !out || !grad_out))
+    if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || (!geo_ws && (!rowptr_t || !col_t)) || !out || !grad_out))
         return GM_ERR_INVALID_ARGUMENT;
     const int depth = p->conv_depth;
     if (fwd_ws_bytes < net_ws_layout(N, depth, 1, nullptr, nullptr)) return GM_ERR_CAPACITY;
@@ -706,11 +674,15 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
         const int stage = depth - l;
         {
             TimedRegion tr(GM_TIMER_SCATTER_S_BWD, st);
-            static int occ = 0;
-            if (!occ) occ = resident_ctas(k_scatter_s, 256, 0, 3);
-            k_scatter_s<<<persistent_grid(((long long)N * 32 + 255) / 256, occ), 256, 0, st>>>(
-                w.G, f.conv[l], bn_in(l + 1), f.arg[l], rowptr, col, rowptr_t, col_t, use_transposed_flag, N, w.S);
-            GM_LAUNCH_CHECK();
+            if (geo_ws) {
+                GM_TRY(geo_scatter_s(w.G, f.conv[l], bn_in(l + 1), f.arg[l], geo_ws, N, B, w.S, st));
+            } else {
+                static int occ = 0;
+                if (!occ) occ = resident_ctas(k_scatter_s, 256, 0, 3);
+                k_scatter_s<<<persistent_grid(((long long)N * 32 + 255) / 256, occ), 256, 0, st>>>(
+                    w.G, f.conv[l], bn_in(l + 1), f.arg[l], rowptr, col, rowptr_t, col_t, use_transposed_flag, N, w.S);
+                GM_LAUNCH_CHECK();
+            }
         }
         {
             TimedRegion tr(GM_TIMER_CONV_NODE_BWD, st);
@@ -759,6 +731,31 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
         }
     }
     return GM_OK;
+}
+
+extern "C" {
+
+int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
+                    const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride, const int *rowptr,
+                    const int *col, const int *rowptr_t, const int *col_t, const int *use_transposed_flag, int N,
+                    const int *node_perm, int training, int apply_sigmoid, int aggr, float eps, const void *fwd_ws,
+                    size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes, const float *out, const float *grad_out,
+                    void *stream) {
+    (void)eps;
+    return net_backward_impl(p, grads, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, rowptr, col, rowptr_t,
+                             col_t, use_transposed_flag, nullptr, 0, N, node_perm, training, apply_sigmoid, aggr, fwd_ws,
+                             fwd_ws_bytes, bwd_ws, bwd_ws_bytes, out, grad_out, stream);
+}
+
+int gm_net_backward_geo(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
+                        const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride, const void *geo_ws, int N,
+                        int B, const int *node_perm, int training, int apply_sigmoid, int aggr, const void *fwd_ws,
+                        size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes, const float *out,
+                        const float *grad_out, void *stream) {
+    if (!geo_ws || B < 1 || !node_perm) return GM_ERR_INVALID_ARGUMENT;
+    return net_backward_impl(p, grads, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, nullptr, nullptr,
+                             nullptr, nullptr, nullptr, geo_ws, B, N, node_perm, training, apply_sigmoid, aggr, fwd_ws,
+                             fwd_ws_bytes, bwd_ws, bwd_ws_bytes, out, grad_out, stream);
 }
 
 }  // extern "C"

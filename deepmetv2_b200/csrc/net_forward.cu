@@ -7,6 +7,7 @@
 //   k_head        : emb_L = resid + BN(raw) ; Linear_32->16 + ELU + Linear_16->1 (+ sigmoid)    [a6]
 // BatchNorm statistics (train mode) are combined by the LAST CTA of the producing kernel in a fixed order
 // (bn_finalize_cta): no separate launch, no CTA ever waits on another, bit-deterministic.
+#include "geo_layout.cuh"
 #include "net_layout.cuh"
 
 namespace gm {
@@ -291,9 +292,6 @@ k_node_prep(const float *__restrict__ raw, const float *__restrict__ resid, cons
 //  the per-target epilogue at the DY/TT degree of ~27; this layout cuts the epilogue to one exchange.]
 constexpr int EA_WARPS = 8;
 
-struct AggrTail {                 // BatchNorm epilogue of the EdgeConv output (train mode); partials == NULL otherwise
-    float *partials; int *counter; GmBatchNorm bn; float momentum, eps; float *stat;
-};
 
 template <int AGGR, bool ARG>
 __device__ __forceinline__ void aggr_consume(float2 &acc, int2 &barg, const float2 (&v)[8], const int (&j)[8]) {
@@ -680,14 +678,18 @@ size_t gm_net_ws_bytes(int N, int conv_depth, int save_for_backward) {
     return net_ws_layout(N < 0 ? 0 : N, conv_depth, save_for_backward, nullptr, nullptr);
 }
 
-int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, const int64_t *x_cat_i64,
-                   const float *x_cat_f32, int x_cat_stride, const int *rowptr, const int *col, int N,
-                   const int *node_perm, int training, int save_for_backward, int apply_sigmoid, int aggr,
-                   int precision, float momentum, float eps, void *ws, size_t ws_bytes, float *out, int *err_flags,
-                   void *stream) {
+}  // extern "C"
+
+// Shared body of gm_net_forward (explicit CSR) and gm_net_forward_geo (implicit radius graph: geo_ws != NULL).
+static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_stride, const int64_t *x_cat_i64,
+                            const float *x_cat_f32, int x_cat_stride, const int *rowptr, const int *col,
+                            const void *geo_ws, int B, int N, const int *node_perm, int training,
+                            int save_for_backward, int apply_sigmoid, int aggr, int precision, float momentum,
+                            float eps, void *ws, size_t ws_bytes, float *out, int *err_flags, void *stream) {
     GM_TRY(check_params(p));
     if (N < 0 || !ws || !err_flags) return GM_ERR_INVALID_ARGUMENT;
-    if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || !rowptr || !out)) return GM_ERR_INVALID_ARGUMENT;
+    if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || (!rowptr && !geo_ws) || !out)) return GM_ERR_INVALID_ARGUMENT;
+    if (geo_ws && (precision != GM_PREC_FP32 || !node_perm)) return GM_ERR_UNSUPPORTED;
     if (ws_bytes < net_ws_layout(N, p->conv_depth, save_for_backward, nullptr, nullptr)) return GM_ERR_CAPACITY;
     if (N == 0) return GM_OK;
     cudaStream_t st = as_stream(stream);
@@ -735,7 +737,8 @@ int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, co
             AggrTail tail{};
             if (training) tail = AggrTail{w.partials, w.counters + 1 + l, p->conv_bn[l], momentum, eps, stat_out};
             TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
-            GM_TRY(edge_aggr(aggr, w.Y, w.P, rowptr, col, N, w.conv[l], arg, tail, st));
+            if (geo_ws) GM_TRY(geo_edge_aggr(aggr, w.Y, w.P, geo_ws, N, B, w.conv[l], arg, tail, st));
+            else GM_TRY(edge_aggr(aggr, w.Y, w.P, rowptr, col, N, w.conv[l], arg, tail, st));
         } else {
             {
                 TimedRegion tr(GM_TIMER_NODE_PREP, st);
@@ -765,6 +768,46 @@ int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, co
         GM_LAUNCH_CHECK();
     }
     return GM_OK;
+}
+
+extern "C" {
+
+int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, const int64_t *x_cat_i64,
+                   const float *x_cat_f32, int x_cat_stride, const int *rowptr, const int *col, int N,
+                   const int *node_perm, int training, int save_for_backward, int apply_sigmoid, int aggr,
+                   int precision, float momentum, float eps, void *ws, size_t ws_bytes, float *out, int *err_flags,
+                   void *stream) {
+    return net_forward_impl(p, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, rowptr, col, nullptr, 0, N,
+                            node_perm, training, save_for_backward, apply_sigmoid, aggr, precision, momentum, eps, ws,
+                            ws_bytes, out, err_flags, stream);
+}
+
+int gm_net_forward_geo(const GmParams *p, const float *x_cont, int x_cont_stride, const int64_t *x_cat_i64,
+                       const float *x_cat_f32, int x_cat_stride, const void *geo_ws, int N, int B,
+                       const int *node_perm, int training, int save_for_backward, int apply_sigmoid, int aggr,
+                       float momentum, float eps, void *ws, size_t ws_bytes, float *out, int *err_flags,
+                       void *stream) {
+    if (!geo_ws || B < 1) return GM_ERR_INVALID_ARGUMENT;
+    return net_forward_impl(p, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, nullptr, nullptr, geo_ws, B, N,
+                            node_perm, training, save_for_backward, apply_sigmoid, aggr, GM_PREC_FP32, momentum, eps,
+                            ws, ws_bytes, out, err_flags, stream);
+}
+
+int gm_edgeconv_forward_geo(const float *x, const void *geo_ws, int N, int B, const float *W, const float *b, int aggr,
+                            void *ws, size_t ws_bytes, float *out, int *arg_out, void *stream) {
+    if (N < 0 || B < 1 || !geo_ws || (N > 0 && (!x || !W || !b || !out || !ws))) return GM_ERR_INVALID_ARGUMENT;
+    if (N == 0) return GM_OK;
+    if (ws_bytes < gm_edgeconv_ws_bytes(N)) return GM_ERR_CAPACITY;
+    cudaStream_t st = as_stream(stream);
+    float *Y = (float *)ws;
+    float *P = (float *)((char *)ws + gm_edgeconv_ws_bytes(N) / 2);
+    {
+        TimedRegion tr(GM_TIMER_NODE_PREP, st);
+        k_node_prep<true><<<node_grid(N), NODE_TILE, 0, st>>>(x, nullptr, nullptr, W, b, N, nullptr, Y, P);
+        GM_LAUNCH_CHECK();
+    }
+    TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
+    return geo_edge_aggr(aggr, Y, P, geo_ws, N, B, out, arg_out, AggrTail{}, st);
 }
 
 }  // extern "C"

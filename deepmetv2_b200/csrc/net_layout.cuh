@@ -116,4 +116,44 @@ __device__ __forceinline__ void bn_finalize_cta(const float *__restrict__ partia
     __syncthreads();
 }
 
+struct AggrTail {   // BatchNorm epilogue of the EdgeConv output (train mode); partials == NULL otherwise
+    float *partials; int *counter; GmBatchNorm bn; float momentum, eps; float *stat;
+};
+
+// ----------------------------------------------------------------------------------------- BatchNorm-backward plumbing
+// What a consumer needs to turn G into d(raw) for one BatchNorm: per channel
+//     d(raw) = scale * (G - c1 - (raw - mean) * invstd * c2),  c1 = sum(G)/N, c2 = sum(G*xhat)/N  (train)
+//                                                              c1 = c2 = 0                        (eval)
+struct BnBwd {
+    const float *stat;      // mean[32], scale[32], invstd[32], beta[32]   (forward)
+    const float *sum;       // sum(G)[32], sum(G*xhat)[32]                 (from the producer's last CTA)
+    float inv_n;            // 1/N in train mode, 0 in eval mode
+};
+// Producer side: where the per-CTA partial sums go and what the last CTA writes.
+struct BnSumOut {
+    const float *raw;       // [N,32] pre-BatchNorm activations of the BatchNorm being differentiated
+    const float *stat;
+    float *part;            // [grid][64]
+    float *sum;             // [64]
+    float *dgamma, *dbeta;  // gradient tensors (may be NULL)
+    int *counter;
+};
+
+// smem coefficient table for BnBwd: [5][32] = mean, invstd, scale, c1, c2
+__device__ __forceinline__ void bn_bwd_coeffs(const BnBwd &b, float *s_coef) {
+    const int t = threadIdx.x;
+    if (t < H) {
+        s_coef[t] = b.stat[t];
+        s_coef[H + t] = b.stat[2 * H + t];
+        s_coef[2 * H + t] = b.stat[H + t];
+        s_coef[3 * H + t] = b.sum[t] * b.inv_n;
+        s_coef[4 * H + t] = b.sum[H + t] * b.inv_n;
+    }
+}
+__device__ __forceinline__ float bn_bwd_one(const float *s_coef, int c, float g, float raw) {
+    const float xhat = (raw - s_coef[c]) * s_coef[H + c];
+    return s_coef[2 * H + c] * (g - s_coef[3 * H + c] - xhat * s_coef[4 * H + c]);
+}
+
+
 }  // namespace gm

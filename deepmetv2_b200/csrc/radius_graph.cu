@@ -10,19 +10,14 @@
 // index and then emits the set bits in order: the row comes out sorted by source index and the
 // max_num_neighbors cap keeps the LOWEST indices, exactly like the reference's sequential scan,
 // without any sort and independent of the (atomic, hence arbitrary) order inside a cell.
-#include "common.cuh"
+#include "geo_layout.cuh"
 
 namespace gm {
 namespace {
 
-constexpr int GMAX = 32;                 // cells per dimension (<=)
-constexpr int CMAX = GMAX * GMAX;        // cells per event (<=)
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
-constexpr float CELL_SLACK = 1.0005f;    // cell edge >= r * slack  => hits are always in adjacent cells
-constexpr float PI_F = 3.14159265358979323846f;
-constexpr float TWO_PI_F = 6.28318530717958647692f;
 
 struct Workspace {
     int *bbox;        // [4] ordered-int min0,max0,min1,max1
@@ -48,79 +43,6 @@ size_t ws_layout(int N, int B, char *base, Workspace *w) {
     int *stats = (int *)take(4 * sizeof(int));
     if (w) *w = Workspace{bbox, cnt, start, sorted, tot, stats};
     return off;
-}
-
-__device__ __forceinline__ int float_to_ordered(float f) {
-    int i = __float_as_int(f);
-    return i >= 0 ? i : i ^ 0x7fffffff;
-}
-__device__ __forceinline__ float ordered_to_float(int i) {
-    return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff);
-}
-
-struct CellGrid {
-    float min0, min1, inv0, inv1;
-    int g0, g1;
-};
-
-// Same deterministic function of (bbox, r) in every kernel.
-__device__ __forceinline__ CellGrid make_grid(const int *__restrict__ bbox, float r, int dim, int phi_wrap) {
-    CellGrid g;
-    const float cs = r * CELL_SLACK;
-    float lo0 = ordered_to_float(bbox[0]), hi0 = ordered_to_float(bbox[1]);
-    float ext0 = hi0 - lo0;
-    if (!(ext0 > 0.f) || !isfinite(ext0)) { lo0 = isfinite(lo0) ? lo0 : 0.f; ext0 = 0.f; }
-    int n0 = (int)fminf((float)GMAX, floorf(ext0 / cs));
-    g.g0 = n0 < 1 ? 1 : n0;
-    g.min0 = lo0;
-    g.inv0 = ext0 > 0.f ? (float)g.g0 / ext0 : 0.f;
-    if (dim < 2) {
-        g.g1 = 1; g.min1 = 0.f; g.inv1 = 0.f;
-    } else if (phi_wrap) {
-        int n1 = (int)fminf((float)GMAX, floorf(TWO_PI_F / cs));
-        g.g1 = n1 < 1 ? 1 : n1;
-        g.min1 = -PI_F;
-        g.inv1 = (float)g.g1 / TWO_PI_F;
-    } else {
-        float lo1 = ordered_to_float(bbox[2]), hi1 = ordered_to_float(bbox[3]);
-        float ext1 = hi1 - lo1;
-        if (!(ext1 > 0.f) || !isfinite(ext1)) { lo1 = isfinite(lo1) ? lo1 : 0.f; ext1 = 0.f; }
-        int n1 = (int)fminf((float)GMAX, floorf(ext1 / cs));
-        g.g1 = n1 < 1 ? 1 : n1;
-        g.min1 = lo1;
-        g.inv1 = ext1 > 0.f ? (float)g.g1 / ext1 : 0.f;
-    }
-    return g;
-}
-
-__device__ __forceinline__ int cell_coord(float v, float lo, float inv, int g) {
-    if (!isfinite(v)) return 0;
-    int c = (int)floorf((v - lo) * inv);
-    return c < 0 ? 0 : (c >= g ? g - 1 : c);
-}
-
-__device__ __forceinline__ int find_event(const int *__restrict__ ptr, int B, int node) {
-    int lo = 0, hi = B;  // largest e with ptr[e] <= node
-    while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (__ldg(ptr + mid) <= node) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-
-__device__ __forceinline__ float dist2(float e0, float p0, float e1, float p1, int dim, int phi_wrap) {
-    // reference arithmetic: dist = fmaf(dphi, dphi, deta*deta), fp32
-    float de = e1 - e0;
-    float acc = __fmul_rn(de, de);
-    if (dim >= 2) {
-        float dp = p1 - p0;
-        if (phi_wrap) {
-            if (dp > PI_F) dp -= TWO_PI_F;
-            else if (dp < -PI_F) dp += TWO_PI_F;
-        }
-        acc = __fmaf_rn(dp, dp, acc);
-    }
-    return acc;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -455,6 +377,12 @@ int check_args(const float *pos, int dim, const int *ptr, int N, int B, double r
 }
 
 }  // namespace
+
+int bin_points(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B, float r, int phi_wrap,
+               int *bbox, int *cell_cnt, int *cell_start, float4 *sorted, int *stats, cudaStream_t st) {
+    Workspace w{bbox, cell_cnt, cell_start, sorted, nullptr, stats};
+    return run_common(pos, pos_stride, dim, ptr, N, B, (double)r, phi_wrap, w, st);
+}
 
 int exclusive_scan_inplace(int *data, int n, int *tile_totals, int *total_out, cudaStream_t st) {
     if (n <= 0) return GM_OK;

@@ -129,6 +129,62 @@ def build_graph(pos: torch.Tensor, r: float, ptr_i32: torch.Tensor | None = None
     return (g, ei) if want_edge_index else g
 
 
+@dataclasses.dataclass
+class GeoGraph:
+    """The radius graph kept implicit (``gm_geo_build``): cell-binned points in internal node order plus the
+    per-node cap threshold, inside one opaque device workspace.  ``perm[s]`` = input row of internal row s."""
+    ws: torch.Tensor              # uint8 [gm_geo_ws_bytes(N, B)]
+    perm: torch.Tensor            # [N] int32
+    stats: torch.Tensor           # [4] int32: -1, max degree seen among cap candidates, #capped, flags
+    num_nodes: int
+    num_events: int
+
+
+def build_geo(pos: torch.Tensor, r: float, ptr_i32: torch.Tensor, loop: bool = False, max_num_neighbors: int = 32,
+              phi_wrap: bool = False, max_event_nodes: int | None = None, out: "GeoGraph | None" = None) -> GeoGraph:
+    """Same arguments and edge set as :func:`build_graph`, but no edge list is written (no host sync at all when
+    ``max_event_nodes`` is given).  Pass a previous ``out`` of sufficient size to reuse its buffers."""
+    _lib.require_cuda(pos, "x")
+    if pos.dim() == 1:
+        pos = pos[:, None]
+    assert pos.dtype == torch.float32 and pos.stride(1) == 1
+    N, dim = pos.shape
+    if dim > 2:
+        raise NotImplementedError("radius_graph kernels are specialised for 1-D / 2-D (eta, phi) positions")
+    B = ptr_i32.numel() - 1
+    if max_event_nodes is None:
+        max_event_nodes = int((ptr_i32[1:] - ptr_i32[:-1]).max().item()) if B > 0 else 0
+    l, dev = lib(), pos.device
+    need = l.gm_geo_ws_bytes(N, B)
+    if out is not None and out.ws.numel() >= need and out.perm.numel() >= N and out.num_events == B \
+            and out.num_nodes == N:
+        g = out
+    else:
+        g = GeoGraph(torch.empty(need, dtype=torch.uint8, device=dev),
+                     torch.empty(max(N, 1), dtype=torch.int32, device=dev),
+                     torch.zeros(4, dtype=torch.int32, device=dev), N, B)
+    check(l.gm_geo_build(ptr(pos), pos.stride(0), dim, ptr(ptr_i32), N, B, float(r), int(max_num_neighbors),
+                         int(bool(loop)), int(bool(phi_wrap)), int(max_event_nodes), ptr(g.ws), g.ws.numel(),
+                         ptr(g.perm), ptr(g.stats), stream()), "gm_geo_build")
+    return g
+
+
+def edgeconv_geo(x_internal: torch.Tensor, geo: GeoGraph, weight: torch.Tensor, bias: torch.Tensor, aggr: str = "max",
+                 want_arg: bool = False):
+    """EdgeConv(Linear(64, 32), aggr) over the implicit graph; ``x_internal`` [N,32] is in internal node order
+    (``x[geo.perm]``) and so are the outputs."""
+    _lib.require_cuda(x_internal, "x")
+    x = x_internal.contiguous().float()
+    N = x.shape[0]
+    l = lib()
+    ws = torch.empty(l.gm_edgeconv_ws_bytes(N), dtype=torch.uint8, device=x.device)
+    out = torch.empty_like(x)
+    arg = torch.empty(N, 32, dtype=torch.int32, device=x.device) if want_arg else None
+    check(l.gm_edgeconv_forward_geo(ptr(x), ptr(geo.ws), N, geo.num_events, ptr(weight), ptr(bias), _lib.AGGR[aggr],
+                                    ptr(ws), ws.numel(), ptr(out), ptr(arg), stream()), "gm_edgeconv_forward_geo")
+    return (out, arg) if want_arg else out
+
+
 def radius_graph(x, r, batch=None, loop=False, max_num_neighbors=32, flow="source_to_target", phi_wrap=False):
     """Drop-in for ``torch_cluster.radius_graph``: LongTensor[2,E], row 0 = source j, row 1 = target i,
     sorted by (i, j); at most ``max_num_neighbors`` sources per target (lowest indices kept)."""

@@ -2,9 +2,13 @@
 evaluate.py:81-100 of the reference as ONE call).
 
 ``GraphMETTrainer.train_step(batch)`` enqueues, on the current stream and without any host sync:
-    etaphi prep -> radius graph (count, scan, fill; E stays on the device) -> [transposed CSR iff capped]
-    -> fused forward (train-mode BN) -> per-event MET + loss (+ dL/dw) -> fused backward into a flat
-    gradient buffer -> [NCCL all-reduce of the 26.6 KB buffer] -> fused flat AdamW.
+    etaphi prep -> radius graph -> fused forward (train-mode BN) -> per-event MET + loss (+ dL/dw)
+    -> fused backward into a flat gradient buffer -> [NCCL all-reduce of the 26.6 KB buffer] -> fused flat AdamW.
+The radius graph is, by default, kept IMPLICIT (``graph="implicit"``, ``gm_geo_build``): points are cell-binned,
+the network runs in cell-sorted node order and the EdgeConv kernels re-evaluate the edge predicate on cell
+neighbourhoods staged in shared memory, so no edge list and no transposed graph are ever written.
+``graph="csr"`` is the explicit path (count, scan, fill; E stays on the device; transposed CSR iff capped) and
+the only one that supports the tcgen05 ``edge_precision`` variants.
 Parameters stay the module's ``nn.Parameter``s (re-pointed at one flat fp32 buffer), so
 ``state_dict()`` / checkpoints are unchanged; optimizer state converts to and from the
 ``torch.optim.AdamW`` layout the reference's checkpoints store (``optim_dict``).
@@ -22,12 +26,16 @@ from .synth import EventBatch
 
 class GraphMETTrainer:
     def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, r=0.4,
-                 max_num_neighbors=255, loop=True, phi_wrap=False, process_group=None, device=None):
+                 max_num_neighbors=255, loop=True, phi_wrap=False, process_group=None, device=None,
+                 graph="implicit"):
         self.model = model
         self.net = model.graphnet if hasattr(model, "graphnet") else model
         self.apply_sigmoid = hasattr(model, "graphnet")       # Net applies the sigmoid, GraphMETNetwork does not
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
         self.r, self.max_nn, self.loop, self.phi_wrap = r, max_num_neighbors, loop, phi_wrap
+        if graph not in ("implicit", "csr"):
+            raise ValueError("graph must be 'implicit' or 'csr'")
+        self.graph = graph
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.step_count = 0
@@ -52,37 +60,52 @@ class GraphMETTrainer:
         self._P = self.net._param_struct()
         self._G = self.net._param_struct(grad_views=self._gviews)
         self._cap_nodes = self._cap_events = self._cap_edges = -1
+        self._cap_implicit = None
         self.flags = torch.zeros(1, dtype=torch.int32, device=dev)
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
         self._host_loss = torch.zeros((), dtype=torch.float32).pin_memory()
 
     # ------------------------------------------------------------------------------------------ buffers
+    def _implicit(self) -> bool:
+        return self.graph == "implicit" and self.net.edge_precision == "fp32"
+
     def _reserve(self, N: int, B: int, max_event_nodes: int):
-        E = N * min(self.max_nn + (0 if self.loop else 1), max(max_event_nodes, 1))
-        if N <= self._cap_nodes and B <= self._cap_events and E <= self._cap_edges:
+        implicit = self._implicit()
+        E = 0 if implicit else N * min(self.max_nn + (0 if self.loop else 1), max(max_event_nodes, 1))
+        if N <= self._cap_nodes and B <= self._cap_events and E <= self._cap_edges and \
+                implicit == self._cap_implicit:
             return
         N, B, E = max(N, self._cap_nodes), max(B, self._cap_events), max(E, self._cap_edges)
         l, dev, depth = lib(), self.device, len(self.net.conv_continuous)
         u8 = lambda nbytes: torch.empty(int(nbytes), dtype=torch.uint8, device=dev)  # noqa: E731
         self.etaphi = torch.empty(N, 2, dtype=torch.float32, device=dev)
-        self.rg_ws = u8(l.gm_radius_graph_ws_bytes(N, B))
-        self.rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
-        self.col = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
-        self.rowptr_t = torch.empty(N + 1, dtype=torch.int32, device=dev)
-        self.col_t = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
-        self.csr_ws = u8(l.gm_csr_ws_bytes(N, E))
         self.stats = torch.zeros(4, dtype=torch.int32, device=dev)
+        if implicit:      # no edge list: O(N) state only
+            self.geo_ws = u8(l.gm_geo_ws_bytes(N, B))
+            self.perm = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
+        else:
+            self.rg_ws = u8(l.gm_radius_graph_ws_bytes(N, B))
+            self.rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+            self.col = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
+            self.rowptr_t = torch.empty(N + 1, dtype=torch.int32, device=dev)
+            self.col_t = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
+            self.csr_ws = u8(l.gm_csr_ws_bytes(N, E))
         self.fwd_ws = u8(l.gm_net_ws_bytes(N, depth, 1))
         self.bwd_ws = u8(l.gm_net_bwd_ws_bytes(N, depth))
         self.weights = torch.empty(N, dtype=torch.float32, device=dev)
         self.grad_w = torch.empty(N, dtype=torch.float32, device=dev)
         self.met = torch.empty(B, 2, dtype=torch.float32, device=dev)
-        self._cap_nodes, self._cap_events, self._cap_edges = N, B, E
+        self._cap_nodes, self._cap_events, self._cap_edges, self._cap_implicit = N, B, E, implicit
 
     # ------------------------------------------------------------------------------------------ pieces
     def _graph(self, x, ptr_i32, N, B, max_event_nodes, need_transpose):
         l, st = lib(), stream()
         check(l.gm_prepare_etaphi(ptr(x), x.stride(0), N, ptr(self.etaphi), st), "gm_prepare_etaphi")
+        if self._implicit():
+            check(l.gm_geo_build(ptr(self.etaphi), 2, 2, ptr(ptr_i32), N, B, float(self.r), int(self.max_nn),
+                                 int(self.loop), int(self.phi_wrap), int(max_event_nodes), ptr(self.geo_ws),
+                                 self.geo_ws.numel(), ptr(self.perm), ptr(self.stats), st), "gm_geo_build")
+            return
         args = (ptr(self.etaphi), 2, 2, ptr(ptr_i32), N, B, float(self.r), int(self.max_nn), int(self.loop),
                 int(self.phi_wrap), int(max_event_nodes), ptr(self.rg_ws), self.rg_ws.numel())
         check(l.gm_radius_graph_count(*args, ptr(self.rowptr), ptr(self.stats), st), "gm_radius_graph_count")
@@ -93,14 +116,37 @@ class GraphMETTrainer:
                                      self.csr_ws.numel(), ptr(self.rowptr_t), ptr(self.col_t),
                                      self.stats.data_ptr() + 8, st), "gm_csr_transpose")
 
-    def _forward(self, x, N, training, save):
+    def _forward(self, x, N, B, training, save):
         net = self.net
+        if self._implicit():
+            check(lib().gm_net_forward_geo(C.byref(self._P), ptr(x), x.stride(0), None, x.data_ptr() + 8 * 4,
+                                           x.stride(0), ptr(self.geo_ws), N, B, ptr(self.perm), int(training),
+                                           int(save), int(self.apply_sigmoid), AGGR[net.aggr],
+                                           float(net.bn_all.momentum), float(net.bn_all.eps), ptr(self.fwd_ws),
+                                           self.fwd_ws.numel(), ptr(self.weights), ptr(self.flags), stream()),
+                  "gm_net_forward_geo")
+            return
         check(lib().gm_net_forward(C.byref(self._P), ptr(x), x.stride(0), None, x.data_ptr() + 8 * 4, x.stride(0),
                                    ptr(self.rowptr), ptr(self.col), N, None, int(training), int(save),
                                    int(self.apply_sigmoid), AGGR[net.aggr], PRECISION[net.edge_precision],
                                    float(net.bn_all.momentum), float(net.bn_all.eps), ptr(self.fwd_ws),
                                    self.fwd_ws.numel(), ptr(self.weights), ptr(self.flags), stream()),
               "gm_net_forward")
+
+    def _backward(self, x, N, B):
+        net, l, st = self.net, lib(), stream()
+        if self._implicit():
+            check(l.gm_net_backward_geo(C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), None,
+                                        x.data_ptr() + 32, x.stride(0), ptr(self.geo_ws), N, B, ptr(self.perm), 1,
+                                        int(self.apply_sigmoid), AGGR[net.aggr], ptr(self.fwd_ws), self.fwd_ws.numel(),
+                                        ptr(self.bwd_ws), self.bwd_ws.numel(), ptr(self.weights), ptr(self.grad_w), st),
+                  "gm_net_backward_geo")
+            return
+        check(l.gm_net_backward(C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), None, x.data_ptr() + 32,
+                                x.stride(0), ptr(self.rowptr), ptr(self.col), ptr(self.rowptr_t), ptr(self.col_t),
+                                self.stats.data_ptr() + 8, N, None, 1, int(self.apply_sigmoid), AGGR[net.aggr],
+                                float(net.bn_all.eps), ptr(self.fwd_ws), self.fwd_ws.numel(), ptr(self.bwd_ws),
+                                self.bwd_ws.numel(), ptr(self.weights), ptr(self.grad_w), st), "gm_net_backward")
 
     @staticmethod
     def _sizes(batch: EventBatch, max_event_nodes):
@@ -121,15 +167,10 @@ class GraphMETTrainer:
         self.net.train()
         l, st = lib(), stream()
         self._graph(x, p, N, B, men, need_transpose=True)
-        self._forward(x, N, training=True, save=True)
+        self._forward(x, N, B, training=True, save=True)
         check(l.gm_met_loss(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
                             ptr(self.met), ptr(self.loss), ptr(self.grad_w), st), "gm_met_loss")
-        net = self.net
-        check(l.gm_net_backward(C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), None, x.data_ptr() + 32,
-                                x.stride(0), ptr(self.rowptr), ptr(self.col), ptr(self.rowptr_t), ptr(self.col_t),
-                                self.stats.data_ptr() + 8, N, None, 1, int(self.apply_sigmoid), AGGR[net.aggr],
-                                float(net.bn_all.eps), ptr(self.fwd_ws), self.fwd_ws.numel(), ptr(self.bwd_ws),
-                                self.bwd_ws.numel(), ptr(self.weights), ptr(self.grad_w), st), "gm_net_backward")
+        self._backward(x, N, B)
         scale = 1.0
         if self.world > 1:
             torch.distributed.all_reduce(self.flat_grad, group=self.pg)      # NCCL SUM over NVLink
@@ -162,13 +203,14 @@ class GraphMETTrainer:
         self._reserve(N, B, men)
         self.net.eval()
         self._graph(x, p, N, B, men, need_transpose=False)
-        self._forward(x, N, training=False, save=False)
+        self._forward(x, N, B, training=False, save=False)
         check(lib().gm_met_loss(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
                                 ptr(self.met), ptr(self.loss), None, stream()), "gm_met_loss")
         return self.weights[:N], self.loss, self.met[:B]
 
     def graph_stats(self):
-        """(E, max degree before the cap, #capped nodes, flags) of the last batch — synchronises."""
+        """(E, max degree before the cap, #capped nodes, flags) of the last batch — synchronises.  On the
+        implicit path E is -1 (edges are never counted) and the max degree covers cap candidates only."""
         return tuple(self.stats.tolist())
 
     # ------------------------------------------------------------------------------------------ optimizer state

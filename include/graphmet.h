@@ -210,6 +210,42 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
                     const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
                     const float *out, const float *grad_out, void *stream);
 
+/* ---------------------------------------------------------------------------------
+ * Fused path: the radius graph kept IMPLICIT (no edge list is ever written).
+ *
+ * gm_geo_build replaces the same torch_cluster.radius_graph call (train.py:48, evaluate.py:88) for callers
+ * that only feed the graph to the network: it bins the points into the (eta, phi) cell grid, fixes the
+ * INTERNAL node order (event, cell, original index) and returns it as node_perm_out [N] (internal row s is
+ * input row node_perm[s]), and records per node the max_num_neighbors cap as "largest admissible source
+ * index".  The edge j -> i of the reference graph exists iff same event && dist2 < r*r && index(j) <=
+ * thr[i] && (loop || j != i) -- exactly the edge set of gm_radius_graph_* (tests compare them bit for bit).
+ * gm_net_forward_geo / gm_net_backward_geo / gm_edgeconv_forward_geo are gm_net_forward / gm_net_backward /
+ * gm_edgeconv_forward with (geo_ws, B, node_perm) in place of the CSR: the EdgeConv layers stage each cell
+ * neighbourhood once into shared memory (TMA bulk copies) and evaluate that predicate there; the backward
+ * needs no transposed graph.  fp32 (factored) arithmetic only.  geo_ws (gm_geo_ws_bytes(N, B)) must stay
+ * untouched between the build and the last forward / backward that uses it.
+ * stats_out (optional, int[4]): {-1 (E is not counted), max degree seen among cap candidates, #capped, flags}.
+ * x of gm_edgeconv_forward_geo, and arg_out, are in INTERNAL node order.
+ * --------------------------------------------------------------------------------- */
+size_t gm_geo_ws_bytes(int N, int B);
+int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B, double r,
+                 int max_num_neighbors, int loop, int phi_wrap, int max_event_nodes, void *ws, size_t ws_bytes,
+                 int *node_perm_out, int *stats_out, void *stream);
+int gm_net_forward_geo(const GmParams *p, const float *x_cont, int x_cont_stride,
+                       const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride,
+                       const void *geo_ws, int N, int B, const int *node_perm,
+                       int training, int save_for_backward, int apply_sigmoid, int aggr,
+                       float momentum, float eps,
+                       void *ws, size_t ws_bytes, float *out, int *err_flags, void *stream);
+int gm_net_backward_geo(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
+                        const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride,
+                        const void *geo_ws, int N, int B, const int *node_perm,
+                        int training, int apply_sigmoid, int aggr,
+                        const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
+                        const float *out, const float *grad_out, void *stream);
+int gm_edgeconv_forward_geo(const float *x, const void *geo_ws, int N, int B, const float *W, const float *b,
+                            int aggr, void *ws, size_t ws_bytes, float *out, int *arg_out, void *stream);
+
 /* CSR (by target) -> CSR of the transposed graph (by source), targets ascending per row.
  * ws: gm_csr_ws_bytes(N, E). Needed by the backward only when GM_FLAG_DEGREE_CAPPED was raised;
  * with only_if_flag the kernels are no-ops unless *only_if_flag != 0 (E is then a capacity). */

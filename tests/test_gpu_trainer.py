@@ -28,14 +28,15 @@ def _dropin_step(model, opt, g):
     return loss.item()
 
 
-def test_trainer_matches_dropin_loop_and_oracle():
+@pytest.mark.parametrize("graph", ["implicit", "csr"])
+def test_trainer_matches_dropin_loop_and_oracle(graph):
     torch.manual_seed(0)
     ref = O.Net(8, 3)
     a = gnet.Net(8, 3); a.load_state_dict(ref.state_dict()); a.to(DEV)
     b = gnet.Net(8, 3); b.load_state_dict(ref.state_dict()); b.to(DEV)
     opt_ref = torch.optim.AdamW(ref.parameters(), lr=1e-3)
     opt_a = torch.optim.AdamW(a.parameters(), lr=1e-3)
-    trainer = GraphMETTrainer(b, lr=1e-3)
+    trainer = GraphMETTrainer(b, lr=1e-3, graph=graph)
     ref.train(); a.train()
     for step in range(3):
         batch = synth.make_batch(3, "dytt", seed=50 + step, sizes=[220, 260, 180])
@@ -84,10 +85,11 @@ def test_trainer_matches_dropin_loop_and_oracle():
     assert abs(loss.item() - gnet.loss_fn(w2, g.x, g.y, g.batch).item()) < 1e-6 * abs(loss.item()) + 1e-6
 
 
-def test_trainer_from_host_and_checkpoint_roundtrip(tmp_path):
+@pytest.mark.parametrize("graph", ["implicit", "csr"])
+def test_trainer_from_host_and_checkpoint_roundtrip(tmp_path, graph):
     torch.manual_seed(1)
     m = gnet.Net(8, 3).to(DEV)
-    tr = GraphMETTrainer(m)
+    tr = GraphMETTrainer(m, graph=graph)
     hb = synth.make_batch(2, "dytt", seed=9, sizes=[120, 140]).pin_memory()
     l0 = tr.train_step_from_host(hb)
     l1 = tr.train_step_from_host(hb)
@@ -98,18 +100,20 @@ def test_trainer_from_host_and_checkpoint_roundtrip(tmp_path):
     ck = torch.load(path, weights_only=False)
     m2 = gnet.Net(8, 3).to(DEV)
     m2.load_state_dict(ck["state_dict"])
-    tr2 = GraphMETTrainer(m2)
+    tr2 = GraphMETTrainer(m2, graph=graph)
     tr2.load_optimizer_state_dict(ck["optim_dict"])
     assert tr2.step_count == 2
     assert abs(tr.train_step_from_host(hb) - tr2.train_step_from_host(hb)) < 1e-6 * abs(l0)
 
 
-def test_trainer_capped_graph_uses_device_side_transpose():
-    """Degree cap binds -> asymmetric CSR; the trainer decides on the device to use the transposed CSR."""
+@pytest.mark.parametrize("graph", ["implicit", "csr"])
+def test_trainer_capped_graph(graph):
+    """Degree cap binds -> asymmetric graph.  csr: the trainer decides on the device to use the transposed CSR;
+    implicit: the cap is the per-target source-index threshold and the backward needs no transposed graph."""
     torch.manual_seed(2)
     ref = O.Net(8, 3)
     m = gnet.Net(8, 3); m.load_state_dict(ref.state_dict()); m.to(DEV)
-    tr = GraphMETTrainer(m, max_num_neighbors=16)
+    tr = GraphMETTrainer(m, max_num_neighbors=16, graph=graph)
     b = synth.make_batch(2, "dytt", seed=31, sizes=[260, 240])
     b.x[:, 3] *= 0.05
     b.x[:, 0] = b.x[:, 2] * torch.cos(torch.atan2(b.x[:, 1], b.x[:, 0]))   # keep (px,py) consistent
