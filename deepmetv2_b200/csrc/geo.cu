@@ -24,7 +24,7 @@ constexpr int GEO_WARPS = GEO_THREADS / 32;
 constexpr int AG_THREADS = 256;      // forward kernel: 8 warps, AG_TPW targets of the item each
 constexpr int AG_WARPS = AG_THREADS / 32;
 constexpr int AG_TPW = GEO_TPI / AG_WARPS;
-constexpr int AG_CH = 128;           // staged neighbourhood rows per pipeline stage
+constexpr int AG_CH = 224;           // staged neighbourhood rows per pipeline stage (2 stages x 3 CTAs fit one SM)
 constexpr int AG_STAGES = 2;
 constexpr int AG_LIST = AG_CH + 8;   // per-warp hit list (uint16 row indices), padded to a multiple of 4
 constexpr unsigned GEO_SPIN_LIMIT = 1u << 24;
@@ -115,7 +115,16 @@ __global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, in
             if (lane == 0) atomicOr(stats + 3, GM_FLAG_EVENT_TOO_LARGE);
             continue;
         }
-        for (int w = lane; w < words; w += 32) mask[w] = 0u;
+        int total = 0;                                     // pass 1: count only (most cap candidates stay below it)
+        for (int q = 0; q < nr; ++q)
+            for (int k = rlo[q] + lane; k < rhi[q]; k += 32) {
+                const float4 c = pts[k];
+                total += dist2(t.x, t.y, c.x, c.y, m.dim, m.phi_wrap) < m.r2;
+            }
+        total = warp_sum_int(total);
+        local_max = max(local_max, total);
+        if (total <= m.cap_eff) continue;
+        for (int w = lane; w < words; w += 32) mask[w] = 0u;   // pass 2: mark hits by original index, find the cap-th
         __syncwarp();
         for (int q = 0; q < nr; ++q)
             for (int k = rlo[q] + lane; k < rhi[q]; k += 32) {
@@ -240,16 +249,15 @@ __device__ __forceinline__ int node_of_row(const SegStage *seg, int k, int row) 
 __device__ __forceinline__ int build_hit_list(const float4 *s_pts, int rows, float px, float py, int th, int excl,
                                               const GeoMeta &m, int lane, unsigned short *list) {
     int nh = 0;
+    const unsigned lt = (1u << lane) - 1u;
     for (int base = 0; base < rows; base += 32) {
         const int c = base + lane;
-        bool hit = false;
-        if (c < rows) {
-            const float4 q = s_pts[c];
-            const int cl = __float_as_int(q.z);
-            hit = dist2(px, py, q.x, q.y, m.dim, m.phi_wrap) < m.r2 && cl <= th && cl != excl;
-        }
+        const float4 q = s_pts[c];                          // c < AG_CH always; rows beyond `rows` hold stale points
+        const int cl = __float_as_int(q.z);
+        const bool hit = (dist2(px, py, q.x, q.y, m.dim, m.phi_wrap) < m.r2) & (cl <= th) & (cl != excl) & (c < rows);
         const unsigned mk = __ballot_sync(0xffffffffu, hit);
-        if (hit) list[nh + __popc(mk & ((1u << lane) - 1u))] = (unsigned short)c;
+        unsigned short *slot = list + nh + __popc(mk & lt);   // address formed unconditionally => predicated store
+        if (hit) *slot = (unsigned short)c;
         nh += __popc(mk);
     }
     if (lane < 4) list[nh + lane] = (unsigned short)AG_CH;
