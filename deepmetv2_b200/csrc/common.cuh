@@ -169,6 +169,32 @@ __device__ __forceinline__ void dense_t_smem(const float *__restrict__ W, const 
     }
 }
 
+// Register-blocked tile product for the node-level layers: a CTA of 32*(O/4) threads multiplies a tile of 128 node
+// rows held in shared memory ([128][LD] floats, LD odd so row-per-lane access is conflict-free) by a K x O weight
+// matrix stored K-MAJOR in shared memory (wT[k*O + o], 16-byte aligned).  Thread t owns the 4 x 4 block
+//     nodes  ng, ng+32, ng+64, ng+96  (ng = t / (O/4))    x    outputs 4*og .. 4*og+3  (og = t % (O/4)),
+// so per k it issues 4 scalar LDS (x) + 1 LDS.128 (w) for 16 independent FMAs, and a warp's results are whole
+// contiguous output rows (coalesced float4 stores straight from registers).  acc[i][j] += x[ng+32i][k] * wT[k][4og+j].
+template <int K, int O, int LD>
+__device__ __forceinline__ void tile_gemm(const float *__restrict__ sX, const float *__restrict__ wT, int ng, int og,
+                                          float (&acc)[4][4]) {
+    const float *x0 = sX + ng * LD;
+    const float4 *w4 = reinterpret_cast<const float4 *>(wT) + og;
+#pragma unroll 8
+    for (int k = 0; k < K; ++k) {
+        const float4 w = w4[k * (O / 4)];
+        const float a0 = x0[k], a1 = x0[32 * LD + k], a2 = x0[64 * LD + k], a3 = x0[96 * LD + k];
+        acc[0][0] = fmaf(a0, w.x, acc[0][0]); acc[0][1] = fmaf(a0, w.y, acc[0][1]);
+        acc[0][2] = fmaf(a0, w.z, acc[0][2]); acc[0][3] = fmaf(a0, w.w, acc[0][3]);
+        acc[1][0] = fmaf(a1, w.x, acc[1][0]); acc[1][1] = fmaf(a1, w.y, acc[1][1]);
+        acc[1][2] = fmaf(a1, w.z, acc[1][2]); acc[1][3] = fmaf(a1, w.w, acc[1][3]);
+        acc[2][0] = fmaf(a2, w.x, acc[2][0]); acc[2][1] = fmaf(a2, w.y, acc[2][1]);
+        acc[2][2] = fmaf(a2, w.z, acc[2][2]); acc[2][3] = fmaf(a2, w.w, acc[2][3]);
+        acc[3][0] = fmaf(a3, w.x, acc[3][0]); acc[3][1] = fmaf(a3, w.y, acc[3][1]);
+        acc[3][2] = fmaf(a3, w.z, acc[3][2]); acc[3][3] = fmaf(a3, w.w, acc[3][3]);
+    }
+}
+
 // reference pdg remap: model/graph_met_network.py:52-54 (sequential where-chain over
 // [1,2,11,13,22,130,211]; any other value passes through unchanged)
 __device__ __forceinline__ long long pdg_remap(long long pdg) {

@@ -278,6 +278,73 @@ k_node_prep(const float *__restrict__ raw, const float *__restrict__ resid, cons
     }
 }
 
+// Same layer-input pass on the register-blocked tile product (common.cuh: tile_gemm): 256 threads per 128-node tile,
+// thread = 4 nodes x 4 outputs, weights K-major in shared memory, results stored straight from registers as whole
+// 128-byte rows.  ~64 registers instead of ~100 and 16 independent FMA chains per thread instead of one: the
+// thread-per-node version above ran at 23% of the FMA pipe with 16 warps per SM (profiles/r01c_ncu_node_kernels.txt).
+constexpr int NP_THREADS = 256;
+__global__ void __launch_bounds__(NP_THREADS, 4)
+k_node_prep2(const float *__restrict__ raw, const float *__restrict__ resid, const float *__restrict__ stat,
+             const float *__restrict__ W, const float *__restrict__ bias, int N, float *__restrict__ emb_out,
+             float *__restrict__ Y, float *__restrict__ P) {
+    __shared__ __align__(16) float s_wdT[H * H];    // (W1 - W2)^T : [k][c]
+    __shared__ __align__(16) float s_w2T[H * H];    // W2^T
+    __shared__ __align__(16) float s_b[H];
+    __shared__ float s_stat[BNSTAT_STRIDE];
+    __shared__ float s_x[NODE_TILE * TILE_LD];
+    const int t = threadIdx.x, ng = t >> 3, og = t & 7;
+    for (int i = t; i < H * H; i += NP_THREADS) {
+        const int k = i >> 5, c = i & 31;
+        const float w1 = W[c * CONV_IN + k], w2 = W[c * CONV_IN + H + k];
+        s_wdT[i] = w1 - w2; s_w2T[i] = w2;
+    }
+    if (t < H) s_b[t] = bias[t];
+    if (stat && t < BNSTAT_STRIDE) s_stat[t] = stat[t];
+    __syncthreads();
+    const float4 b4 = reinterpret_cast<const float4 *>(s_b)[og];
+    const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const int node0 = tile * NODE_TILE, rows = min(NODE_TILE, N - node0);
+        for (int idx = t; idx < rows * (H / 4); idx += NP_THREADS) {
+            const int r = idx >> 3, c4 = (idx & 7) * 4;
+            const size_t g = (size_t)(node0 + r) * (H / 4) + (idx & 7);
+            float4 v = reinterpret_cast<const float4 *>(raw)[g];
+            if (stat) {
+                v.x = fmaf(v.x - s_stat[c4 + 0], s_stat[H + c4 + 0], s_stat[3 * H + c4 + 0]);
+                v.y = fmaf(v.y - s_stat[c4 + 1], s_stat[H + c4 + 1], s_stat[3 * H + c4 + 1]);
+                v.z = fmaf(v.z - s_stat[c4 + 2], s_stat[H + c4 + 2], s_stat[3 * H + c4 + 2]);
+                v.w = fmaf(v.w - s_stat[c4 + 3], s_stat[H + c4 + 3], s_stat[3 * H + c4 + 3]);
+            }
+            if (resid) {
+                const float4 q = reinterpret_cast<const float4 *>(resid)[g];
+                v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
+            }
+            if (emb_out) reinterpret_cast<float4 *>(emb_out)[g] = v;
+            float *d = s_x + r * TILE_LD + c4;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        }
+        __syncthreads();
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; acc[i][2] = 0.f; acc[i][3] = 0.f; }
+        tile_gemm<H, H, TILE_LD>(s_x, s_w2T, ng, og, acc);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (ng + 32 * i < rows)
+                reinterpret_cast<float4 *>(Y)[(size_t)(node0 + ng + 32 * i) * (H / 4) + og] =
+                    make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { acc[i][0] = b4.x; acc[i][1] = b4.y; acc[i][2] = b4.z; acc[i][3] = b4.w; }
+        tile_gemm<H, H, TILE_LD>(s_x, s_wdT, ng, og, acc);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (ng + 32 * i < rows)
+                reinterpret_cast<float4 *>(P)[(size_t)(node0 + ng + 32 * i) * (H / 4) + og] =
+                    make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        __syncthreads();
+    }
+}
+
 // ------------------------------------------------------------------------------------------ EdgeConv, edge side
 // out_i = P_i + max_{j in N(i)} Y_j   (add: deg*P_i + sum_j Y_j ; mean: P_i + mean_j Y_j)
 // Warp per target, HALF-WARP per source row: a 128-byte Y row is read by 16 lanes as float2, so one LDG.64
@@ -667,7 +734,7 @@ int gm_edgeconv_forward(const float *x, const int *rowptr, const int *col, int N
     float *P = (float *)((char *)ws + gm_edgeconv_ws_bytes(N) / 2);
     {
         TimedRegion tr(GM_TIMER_NODE_PREP, st);
-        k_node_prep<true><<<node_grid(N), NODE_TILE, 0, st>>>(x, nullptr, nullptr, W, b, N, nullptr, Y, P);
+        k_node_prep2<<<node_grid(N), NP_THREADS, 0, st>>>(x, nullptr, nullptr, W, b, N, nullptr, Y, P);
         GM_LAUNCH_CHECK();
     }
     TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
@@ -730,8 +797,8 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
         if (precision == GM_PREC_FP32) {
             {
                 TimedRegion tr(GM_TIMER_NODE_PREP, st);
-                k_node_prep<true><<<ngrid, NODE_TILE, 0, st>>>(raw, resid, stat_in, p->conv_w[l], p->conv_b[l], N,
-                                                               w.emb[l], w.Y, w.P);
+                k_node_prep2<<<ngrid, NP_THREADS, 0, st>>>(raw, resid, stat_in, p->conv_w[l], p->conv_b[l], N, w.emb[l],
+                                                           w.Y, w.P);
                 GM_LAUNCH_CHECK();
             }
             AggrTail tail{};
@@ -803,7 +870,7 @@ int gm_edgeconv_forward_geo(const float *x, const void *geo_ws, int N, int B, co
     float *P = (float *)((char *)ws + gm_edgeconv_ws_bytes(N) / 2);
     {
         TimedRegion tr(GM_TIMER_NODE_PREP, st);
-        k_node_prep<true><<<node_grid(N), NODE_TILE, 0, st>>>(x, nullptr, nullptr, W, b, N, nullptr, Y, P);
+        k_node_prep2<<<node_grid(N), NP_THREADS, 0, st>>>(x, nullptr, nullptr, W, b, N, nullptr, Y, P);
         GM_LAUNCH_CHECK();
     }
     TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
