@@ -14,7 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-SO_PATH = os.path.join(CSRC, "libgraphmet.so")
+SO_PATH = os.environ.get("GRAPHMET_SO") or os.path.join(CSRC, "libgraphmet.so")   # override: kernel-variant experiments
 HEADER = os.path.join(os.path.dirname(_HERE), "include", "graphmet.h")
 
 GM_OK = 0

@@ -19,15 +19,21 @@ namespace gm {
 namespace {
 
 constexpr int GEO_TPI = 32;          // nodes per work item (one warp-width of consecutive internal nodes)
-constexpr int GEO_THREADS = 128;     // backward kernel: 4 warps
+#ifndef GEO_SC_THREADS
+#define GEO_SC_THREADS 128
+#endif
+#ifndef GEO_SC_CH
+#define GEO_SC_CH 64
+#endif
+constexpr int GEO_THREADS = GEO_SC_THREADS;     // backward kernel: 4 warps
 constexpr int GEO_WARPS = GEO_THREADS / 32;
-constexpr int AG_THREADS = 256;      // forward kernel: 8 warps, AG_TPW targets of the item each
-constexpr int AG_WARPS = AG_THREADS / 32;
-constexpr int AG_TPW = GEO_TPI / AG_WARPS;
+constexpr int AG_CONSUMERS = 8;      // forward kernel: 8 consumer warps (AG_TPW targets of the item each) ...
+constexpr int AG_THREADS = (AG_CONSUMERS + 1) * 32;   // ... + 1 producer warp (segments, descriptors, TMA)
+constexpr int AG_TPW = GEO_TPI / AG_CONSUMERS;
 constexpr int AG_CH = 224;           // staged neighbourhood rows per pipeline stage (2 stages x 3 CTAs fit one SM)
 constexpr int AG_STAGES = 2;
-constexpr int AG_LIST = AG_CH + 8;   // per-warp hit list (uint16 row indices), padded to a multiple of 4
-constexpr unsigned GEO_SPIN_LIMIT = 1u << 24;
+constexpr int AG_LIST = AG_CH + 8;   // per-warp hit list (uint32 byte offsets of staged rows), padded by 8 identity entries
+constexpr unsigned GEO_SPIN_LIMIT = 1u << 20;
 
 // ------------------------------------------------------------------------------------------ PTX: mbarrier + TMA bulk copy
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -37,19 +43,29 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// potentially blocking: the thread is suspended in hardware until the phase completes or ~hint_ns elapse, so waiting
+// warps do not compete for issue slots with the warps that still work
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        : "=r"(ok) : "r"(bar), "r"(parity), "r"(hint_ns) : "memory");
     return ok != 0;
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {   // bounded: a bug must trap, not hang
+// bounded (a bug must trap, not hang); failed polls back off with nanosleep so that waiting warps do not take issue
+// slots from the warps that still work (ncu: 14 % of the executed instructions were try_wait polls without it)
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigned sleep_ns = 128) {
+    if (mbar_try_wait(bar, parity, 1000u)) return;
 #pragma unroll 1
-    for (unsigned it = 0; it < GEO_SPIN_LIMIT; ++it)
-        if (mbar_try_wait(bar, parity)) return;
+    for (unsigned it = 0; it < GEO_SPIN_LIMIT; ++it) {
+        __nanosleep(sleep_ns);
+        if (mbar_try_wait(bar, parity, 1000u)) return;
+    }
     __trap();
 }
 // global -> shared bulk copy through the TMA unit; bytes % 16 == 0, both addresses 16-byte aligned
@@ -175,19 +191,35 @@ struct GeoView {       // device pointers of a built GeoWs (passed by value)
     const GeoMeta *meta;
     const int *bbox, *cell_start, *ptr, *thr;
     const float4 *pts;
+    int *sched;        // [2] dynamic-schedule ticket + finished-CTA count (self-resetting; zeroed by gm_geo_build)
 };
 
-// forward kernel: [stage]{ (AG_CH + 1) rows x 128 B (last row: identity), AG_CH points x 16 B }
-constexpr size_t AG_STAGE_BYTES = (size_t)(AG_CH + 1) * 128 + (size_t)AG_CH * 16;
+// forward kernel: [stage]{ (AG_CH + 1) rows x 128 B (last row: identity), AG_CH points x 16 B, the item's 32 target
+// points x 16 B, their 32 cap thresholds, the chunk descriptor }
+struct ChunkDesc {     // written by the producer into the stage it fills, read by the consumers after the full barrier
+    int flags;         // AG_FIRST / AG_LAST chunk of a segment, AG_END of the CTA's work
+    int n0;            // first node of the item
+    int a, b;          // targets [a, b) of the item form the segment
+    int rows;          // staged rows of this chunk
+    int vbase;         // virtual row of staged row 0
+    int nr;            // runs of the segment's neighbourhood
+    int rlo[6];        // first internal node of run q
+    int voff[7];       // first virtual row of run q; voff[nr] = C
+};
+constexpr int AG_FIRST = 1, AG_LAST = 2, AG_END = 4;
 constexpr size_t AG_OFF_PTS = (size_t)(AG_CH + 1) * 128;                   // inside a stage
-constexpr size_t AG_LISTS = AG_STAGES * AG_STAGE_BYTES;                    // AG_WARPS x AG_LIST x u16
-constexpr size_t AG_ITEM = AG_LISTS + (size_t)AG_WARPS * AG_LIST * 2;      // heads, e[32], cell[32]
-constexpr size_t AG_SEG = AG_ITEM + 66 * 4;                                // SegStage
-constexpr size_t AG_BAR = (AG_SEG + sizeof(SegStage) + 7) / 8 * 8;
-constexpr size_t AG_TOTAL = AG_BAR + 8 * AG_STAGES;
-static_assert(AG_STAGE_BYTES % 128 == 0 && AG_LISTS % 8 == 0 && (AG_LIST * 2) % 8 == 0, "staging alignment");
+constexpr size_t AG_OFF_TGT = AG_OFF_PTS + (size_t)AG_CH * 16;
+constexpr size_t AG_OFF_THR = AG_OFF_TGT + (size_t)GEO_TPI * 16;
+constexpr size_t AG_OFF_DESC = AG_OFF_THR + (size_t)GEO_TPI * 4;
+constexpr size_t AG_STAGE_BYTES = AG_OFF_DESC + 128;
+constexpr size_t AG_LISTS = AG_STAGES * AG_STAGE_BYTES;                    // AG_CONSUMERS x AG_LIST x u32
+constexpr size_t AG_BAR = AG_LISTS + (size_t)AG_CONSUMERS * AG_LIST * 4;   // full[AG_STAGES], empty[AG_STAGES]
+constexpr size_t AG_TOTAL = AG_BAR + 16 * AG_STAGES;
+static_assert(sizeof(ChunkDesc) <= 128, "descriptor slot");
+static_assert(AG_STAGE_BYTES % 128 == 0 && AG_LISTS % 8 == 0 && (AG_LIST * 4) % 16 == 0 && AG_LISTS % 16 == 0 && AG_BAR % 8 == 0, "staging alignment");
 static_assert(AG_STAGES * AG_STAGE_BYTES >= (size_t)(AG_THREADS / 8) * 3 * H * 4, "BatchNorm scratch aliases the stages");
 
+// backward kernel bookkeeping: heads, e[32], cell[32] + SegStage
 // warp 0: find the (event, eta-row) segments of the item's nodes
 __device__ __forceinline__ void item_segments(const GeoView &v, const CellGrid &g, int B, int n0, int cnt, int lane,
                                               int *s_item) {
@@ -220,34 +252,18 @@ __device__ __forceinline__ void segment_runs(const GeoView &v, const CellGrid &g
     seg->nr = n;
 }
 
-// thread 0: issue the TMA bulk copies of chunk k (virtual rows k*AG_CH ...) into one pipeline stage:
-// points + one 128-byte row array
-__device__ __forceinline__ void issue_chunk(const SegStage *seg, int k, const float4 *__restrict__ pts,
-                                            const void *__restrict__ rows128, uint32_t s_stage, uint32_t bar) {
-    const int c0 = k * AG_CH, c1 = min(seg->voff[seg->nr], c0 + AG_CH);
-    mbar_expect_tx(bar, (uint32_t)(c1 - c0) * (128u + 16u));
-    for (int q = 0; q < seg->nr; ++q) {
-        const int lo = max(seg->voff[q], c0), hi = min(seg->voff[q + 1], c1);
-        if (lo >= hi) continue;
-        const size_t node = (size_t)(seg->rlo[q] + (lo - seg->voff[q]));
-        const uint32_t n = (uint32_t)(hi - lo), row = (uint32_t)(lo - c0);
-        bulk_g2s(s_stage + (uint32_t)AG_OFF_PTS + row * 16u, pts + node, n * 16u, bar);
-        bulk_g2s(s_stage + row * 128u, reinterpret_cast<const char *>(rows128) + node * 128, n * 128u, bar);
-    }
-}
-
-__device__ __forceinline__ int node_of_row(const SegStage *seg, int k, int row) {
-    const int vr = k * AG_CH + row;
+__device__ __forceinline__ int node_of_row(const ChunkDesc *d, int row) {
+    const int vr = d->vbase + row;
     int q = 0;
-    while (q + 1 < seg->nr && vr >= seg->voff[q + 1]) ++q;
-    return seg->rlo[q] + (vr - seg->voff[q]);
+    while (q + 1 < d->nr && vr >= d->voff[q + 1]) ++q;
+    return d->rlo[q] + (vr - d->voff[q]);
 }
 
-// Hit list of one target against the staged chunk: rows whose point passes the edge predicate of geo_layout.cuh, in
-// staged order, padded with 4 x the identity row.  th = cap threshold of the target, excl = local index to exclude
-// (the target itself when loop == 0, -1 otherwise).  Returns the hit count.
+// Hit list of one target against the staged chunk: BYTE OFFSETS (row * 128) of the rows whose point passes the edge
+// predicate of geo_layout.cuh, in staged order, padded with 8 x the identity row.  th = cap threshold of the target,
+// excl = local index to exclude (the target itself when loop == 0, -1 otherwise).  Returns the hit count.
 __device__ __forceinline__ int build_hit_list(const float4 *s_pts, int rows, float px, float py, int th, int excl,
-                                              const GeoMeta &m, int lane, unsigned short *list) {
+                                              const GeoMeta &m, int lane, unsigned *list) {
     int nh = 0;
     const unsigned lt = (1u << lane) - 1u;
     for (int base = 0; base < rows; base += 32) {
@@ -256,150 +272,258 @@ __device__ __forceinline__ int build_hit_list(const float4 *s_pts, int rows, flo
         const int cl = __float_as_int(q.z);
         const bool hit = (dist2(px, py, q.x, q.y, m.dim, m.phi_wrap) < m.r2) & (cl <= th) & (cl != excl) & (c < rows);
         const unsigned mk = __ballot_sync(0xffffffffu, hit);
-        unsigned short *slot = list + nh + __popc(mk & lt);   // address formed unconditionally => predicated store
-        if (hit) *slot = (unsigned short)c;
+        unsigned *slot = list + nh + __popc(mk & lt);       // address formed unconditionally => predicated store
+        if (hit) *slot = (unsigned)c << 7;
         nh += __popc(mk);
     }
-    if (lane < 4) list[nh + lane] = (unsigned short)AG_CH;
+    if (lane < 8) list[nh + lane] = (unsigned)AG_CH << 7;
     __syncwarp();
     return nh;
 }
 
+// One target against one staged chunk: hit list, then lane = channel walks the list 4 rows at a time out of shared
+// memory.  The caller must NOT unroll its target loop around this body: the consumer warps run decoupled, and four
+// copies (one per target slot) thrash the instruction cache (ncu: stall_no_instruction 0.2 -> 3.7 per issue); a
+// __noinline__ call, on the other hand, confines ptxas to the scratch registers and serialises the row loads.
+struct TargetResult {
+    float ac;
+    int brow, nh;
+};
+template <int AGGR, bool ARG>
+__device__ __forceinline__ TargetResult aggr_target(const float4 *s_pts, const float *s_rows, int rows, float px, float py,
+                                                 int th, int excl, float ac, float r2, int dim, int phi_wrap, int lane,
+                                                 unsigned *list) {
+    GeoMeta m;
+    m.r2 = r2; m.dim = dim; m.phi_wrap = phi_wrap;
+    const int nh = build_hit_list(s_pts, rows, px, py, th, excl, m, lane, list);
+    const char *col = reinterpret_cast<const char *>(s_rows + lane);       // this lane's channel of staged row 0
+    unsigned boff = 0xffffffffu;                                           // byte offset of the arg-max row
+    for (int k8 = 0; k8 < nh; k8 += 8) {
+        const uint4 ra = *reinterpret_cast<const uint4 *>(list + k8);
+        const uint4 rb = *reinterpret_cast<const uint4 *>(list + k8 + 4);
+        const float v0 = *reinterpret_cast<const float *>(col + ra.x), v1 = *reinterpret_cast<const float *>(col + ra.y);
+        const float v2 = *reinterpret_cast<const float *>(col + ra.z), v3 = *reinterpret_cast<const float *>(col + ra.w);
+        const float v4 = *reinterpret_cast<const float *>(col + rb.x), v5 = *reinterpret_cast<const float *>(col + rb.y);
+        const float v6 = *reinterpret_cast<const float *>(col + rb.z), v7 = *reinterpret_cast<const float *>(col + rb.w);
+        if (AGGR == GM_AGGR_MAX && ARG) {
+            if (v0 > ac) { ac = v0; boff = ra.x; }
+            if (v1 > ac) { ac = v1; boff = ra.y; }
+            if (v2 > ac) { ac = v2; boff = ra.z; }
+            if (v3 > ac) { ac = v3; boff = ra.w; }
+            if (v4 > ac) { ac = v4; boff = rb.x; }
+            if (v5 > ac) { ac = v5; boff = rb.y; }
+            if (v6 > ac) { ac = v6; boff = rb.z; }
+            if (v7 > ac) { ac = v7; boff = rb.w; }
+        } else if (AGGR == GM_AGGR_MAX) {
+            ac = fmaxf(fmaxf(fmaxf(ac, v0), fmaxf(v1, v2)), fmaxf(fmaxf(v3, v4), fmaxf(v5, fmaxf(v6, v7))));
+        } else {
+            ac += v0; ac += v1; ac += v2; ac += v3; ac += v4; ac += v5; ac += v6; ac += v7;
+        }
+    }
+    return TargetResult{ac, boff == 0xffffffffu ? -1 : (int)(boff >> 7), nh};
+}
+
 // ------------------------------------------------------------------------------------------ forward: aggregate
-// out_i = P_i + max_{j in N(i)} Y_j (add / mean alike).  8 warps; a warp owns AG_TPW targets of the item and keeps
-// their running max / arg-max in REGISTERS while the neighbourhood streams through a 2-stage TMA pipeline of AG_CH
-// rows (points + Y rows): thread 0 refills a stage as soon as the CTA has consumed it, so copies overlap the
-// reduction.  Per (target, chunk): lanes test 32 candidate points at a time and compact the hits (ballot + popc)
-// into a per-warp list, then lane = channel walks the list 4 rows at a time out of shared memory.
+// out_i = P_i + max_{j in N(i)} Y_j (add / mean alike), warp-specialised.
+//   producer warp : walks the CTA's items, cuts them into segments, computes the neighbourhood runs and streams the
+//                   neighbourhood (points + Y rows) through a 2-stage ring with TMA bulk copies, AG_CH rows at a time;
+//                   every chunk carries its descriptor and the item's target points / cap thresholds, so consumers never
+//                   touch global memory until they write a finished row.  It runs ahead across segment and item
+//                   boundaries: the pipeline never drains while the CTA has work.
+//   consumer warps: a warp owns AG_TPW targets of the item and keeps their running max / arg-max in REGISTERS.  Per
+//                   (target, chunk): lanes test 32 candidate points at a time and compact the hits (ballot + popc) into
+//                   a per-warp list, then lane = channel walks the list 4 rows at a time out of shared memory.
+// full[s] (1 arrival + TMA bytes) / empty[s] (AG_CONSUMERS arrivals) mbarriers; no CTA-wide barrier in the main loop.
+// Items are scheduled statically (item = blockIdx + k * gridDim) when BatchNorm partials are produced, so the per-CTA
+// moments are bit-reproducible; without them (eval) the producer takes tickets from a self-resetting counter.
 template <int AGGR, bool ARG>
 __global__ void __launch_bounds__(AG_THREADS, 3)
 k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, int N, float *__restrict__ out,
            int *__restrict__ arg, AggrTail tail) {
     extern __shared__ __align__(128) unsigned char gs[];
-    int *s_item = reinterpret_cast<int *>(gs + AG_ITEM);
-    SegStage *seg = reinterpret_cast<SegStage *>(gs + AG_SEG);
-    const uint32_t bar0 = smem_u32(gs + AG_BAR);
+    const uint32_t full0 = smem_u32(gs + AG_BAR), empty0 = full0 + 8u * AG_STAGES;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    unsigned short *list = reinterpret_cast<unsigned short *>(gs + AG_LISTS) + warp * AG_LIST;
 
     const GeoMeta m = *v.meta;
-    const CellGrid g = make_grid(v.bbox, m.r, m.dim, m.phi_wrap);
     const float IDENT = AGGR == GM_AGGR_MAX ? -INFINITY : 0.f;
+#ifdef GEO_FORCE_DYNAMIC
+    const bool dynamic = true;
+#else
+    const bool dynamic = tail.partials == nullptr;
+#endif
     if (tid == 0) {
-        for (int s = 0; s < AG_STAGES; ++s) mbar_init(bar0 + 8u * s, 1);
+        for (int s = 0; s < AG_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, AG_CONSUMERS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp < AG_STAGES) reinterpret_cast<float *>(gs + warp * AG_STAGE_BYTES)[AG_CH * 32 + lane] = IDENT;
     __syncthreads();
 
-    uint32_t phases = 0u;                                   // bit s = parity of pipeline stage s
     float cnt = 0.f, shift = 0.f, s1 = 0.f, s2 = 0.f;      // BatchNorm moments of this warp's outputs (lane = channel)
-    const int n_items = (N + GEO_TPI - 1) / GEO_TPI;
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const int n0 = item * GEO_TPI, icnt = min(GEO_TPI, N - n0);
-        if (warp == 0) item_segments(v, g, m.B, n0, icnt, lane, s_item);
-        __syncthreads();
-        unsigned heads = (unsigned)s_item[0];
-        while (heads) {
-            const int a = __ffs(heads) - 1;
-            heads &= heads - 1;
-            const int b = heads ? __ffs(heads) - 1 : icnt;
-            if (tid == 0) {
-                segment_runs(v, g, m.phi_wrap, s_item, a, b, seg);
-                const int nck = (seg->voff[seg->nr] + AG_CH - 1) / AG_CH;
-                for (int k = 0; k < min(nck, AG_STAGES); ++k)
-                    issue_chunk(seg, k, v.pts, Y, smem_u32(gs + k * AG_STAGE_BYTES), bar0 + 8u * k);
+    if (warp == AG_CONSUMERS) {
+        // ================================================================== producer
+        const CellGrid g = make_grid(v.bbox, m.r, m.dim, m.phi_wrap);
+        const int n_items = (N + GEO_TPI - 1) / GEO_TPI;
+        uint32_t gc = 0;                                    // chunks issued so far; chunk gc lives in stage gc & 1
+        int item = blockIdx.x;
+        for (;;) {
+            if (dynamic) {
+                if (lane == 0) item = atomicAdd(v.sched, 1);
+                item = __shfl_sync(0xffffffffu, item, 0);
             }
-            // this warp's targets of the segment: a + warp, a + warp + 8, ...
-            float px[AG_TPW], py[AG_TPW], acc[AG_TPW];
-            int th[AG_TPW], excl[AG_TPW], barg[AG_TPW], deg[AG_TPW];
+            if (item >= n_items) break;
+            const int n0 = item * GEO_TPI, icnt = min(GEO_TPI, N - n0);
+            const bool valid = lane < icnt;
+            const int e = valid ? find_event(v.ptr, m.B, n0 + lane) : -1;
+            const int cell = valid ? __float_as_int(__ldg(&v.pts[n0 + lane].w)) : 0;
+            const int key = valid ? ((e << 5) | (cell / g.g1)) : -1;
+            const int prev = __shfl_up_sync(0xffffffffu, key, 1);
+            unsigned heads = __ballot_sync(0xffffffffu, valid && (lane == 0 || key != prev));
+            while (heads) {
+                const int a = __ffs(heads) - 1;
+                heads &= heads - 1;
+                const int b = heads ? __ffs(heads) - 1 : icnt;
+                const int ev = __shfl_sync(0xffffffffu, e, a);
+                const int ca = __shfl_sync(0xffffffffu, cell, a), cb = __shfl_sync(0xffffffffu, cell, b - 1);
+                const int ce = ca / g.g1;
+                int rlo[6], rhi[6], voff[7];                // every lane computes the (uniform) runs: broadcast loads
+                const int nr0 = nbhd_runs(g, v.cell_start + (size_t)ev * (CMAX + 1), ce, ca - ce * g.g1, cb - ce * g.g1,
+                                          m.phi_wrap, rlo, rhi);
+                int nr = 0, C = 0;
 #pragma unroll
-            for (int u = 0; u < AG_TPW; ++u) {
-                const int t = a + warp + u * AG_WARPS;
-                acc[u] = IDENT; barg[u] = -1; deg[u] = 0; px[u] = 0.f; py[u] = 0.f; th[u] = 0; excl[u] = -1;
-                if (t < b) {
-                    const float4 pt = __ldg(v.pts + n0 + t);
-                    px[u] = pt.x; py[u] = pt.y;
-                    th[u] = __ldg(v.thr + n0 + t);
-                    excl[u] = m.loop ? -1 : __float_as_int(pt.z);
-                }
-            }
-            __syncthreads();
-            const int C = seg->voff[seg->nr];
-            const int nchunks = (C + AG_CH - 1) / AG_CH;
-            for (int k = 0; k < nchunks; ++k) {
-                const int st = k & 1;
-                const int rows = min(AG_CH, C - k * AG_CH);
-                const float *s_rows = reinterpret_cast<const float *>(gs + st * AG_STAGE_BYTES);
-                const float4 *s_pts = reinterpret_cast<const float4 *>(gs + st * AG_STAGE_BYTES + AG_OFF_PTS);
-                mbar_wait(bar0 + 8u * st, (phases >> st) & 1u);
-                phases ^= 1u << st;
+                for (int q = 0; q < 6; ++q)
+                    if (q < nr0 && rhi[q] > rlo[q]) { rlo[nr] = rlo[q]; voff[nr] = C; C += rhi[q] - rlo[q]; ++nr; }
+                voff[nr] = C;
+                const int nck = (C + AG_CH - 1) / AG_CH;
+                const int crow = min(AG_CH, (((C + nck - 1) / nck) + 31) & ~31);    // even split, multiple of 32
+                for (int k = 0; k < nck; ++k, ++gc) {
+                    const int st = gc & 1;
+                    mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u, 400);        // stage consumed (or never used)
+                    if (lane == 0) {
+                        unsigned char *stage = gs + st * AG_STAGE_BYTES;
+                        const uint32_t s_stage = smem_u32(stage), bar = full0 + 8u * st;
+                        const int c0 = k * crow, c1 = min(C, c0 + crow);
+                        ChunkDesc *d = reinterpret_cast<ChunkDesc *>(stage + AG_OFF_DESC);
+                        d->flags = (k == 0 ? AG_FIRST : 0) | (k == nck - 1 ? AG_LAST : 0);
+                        d->n0 = n0; d->a = a; d->b = b; d->rows = c1 - c0; d->vbase = c0; d->nr = nr;
 #pragma unroll
-                for (int u = 0; u < AG_TPW; ++u) {
-                    if (a + warp + u * AG_WARPS >= b) continue;                 // warp-uniform
-                    const int nh = build_hit_list(s_pts, rows, px[u], py[u], th[u], excl[u], m, lane, list);
-                    deg[u] += nh;
-                    float ac = acc[u];
-                    int brow = -1;
-                    for (int k4 = 0; k4 < nh; k4 += 4) {
-                        const uint2 rr = *reinterpret_cast<const uint2 *>(list + k4);
-                        const int r0 = rr.x & 0xffff, r1 = rr.x >> 16, r2 = rr.y & 0xffff, r3 = rr.y >> 16;
-                        const float v0 = s_rows[r0 * 32 + lane], v1 = s_rows[r1 * 32 + lane];
-                        const float v2 = s_rows[r2 * 32 + lane], v3 = s_rows[r3 * 32 + lane];
-                        if (AGGR == GM_AGGR_MAX && ARG) {
-                            if (v0 > ac) { ac = v0; brow = r0; }
-                            if (v1 > ac) { ac = v1; brow = r1; }
-                            if (v2 > ac) { ac = v2; brow = r2; }
-                            if (v3 > ac) { ac = v3; brow = r3; }
-                        } else if (AGGR == GM_AGGR_MAX) {
-                            ac = fmaxf(fmaxf(ac, v0), fmaxf(v1, fmaxf(v2, v3)));
-                        } else {
-                            ac += v0; ac += v1; ac += v2; ac += v3;
+                        for (int q = 0; q < 6; ++q) { d->rlo[q] = rlo[q]; d->voff[q] = voff[q]; }
+                        d->voff[6] = voff[6];
+                        mbar_expect_tx(bar, (uint32_t)(c1 - c0) * (128u + 16u) + (uint32_t)icnt * 16u + 128u);
+                        bulk_g2s(s_stage + (uint32_t)AG_OFF_TGT, v.pts + n0, (uint32_t)icnt * 16u, bar);
+                        bulk_g2s(s_stage + (uint32_t)AG_OFF_THR, v.thr + n0, 128u, bar);
+#pragma unroll
+                        for (int q = 0; q < 6; ++q) {
+                            if (q >= nr) break;
+                            const int lo = max(voff[q], c0), hi = min(voff[q + 1], c1);
+                            if (lo >= hi) continue;
+                            const size_t node = (size_t)(rlo[q] + (lo - voff[q]));
+                            const uint32_t n = (uint32_t)(hi - lo), row = (uint32_t)(lo - c0);
+                            bulk_g2s(s_stage + (uint32_t)AG_OFF_PTS + row * 16u, v.pts + node, n * 16u, bar);
+                            bulk_g2s(s_stage + row * 128u, Y + node * H, n * 128u, bar);
                         }
                     }
-                    acc[u] = ac;
-                    if (ARG && brow >= 0) barg[u] = node_of_row(seg, k, brow);
-                    __syncwarp();                                   // the hit list is reused by the next target
+                    __syncwarp();
                 }
-                __syncthreads();                                    // stage st fully consumed
-                if (tid == 0 && k + AG_STAGES < nchunks)
-                    issue_chunk(seg, k + AG_STAGES, v.pts, Y, smem_u32(gs + st * AG_STAGE_BYTES), bar0 + 8u * st);
             }
+            item += gridDim.x;
+        }
+        const int st = gc & 1;                              // end-of-work descriptor (no copies)
+        mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u);
+        if (lane == 0) {
+            reinterpret_cast<ChunkDesc *>(gs + st * AG_STAGE_BYTES + AG_OFF_DESC)->flags = AG_END;
+            mbar_arrive(full0 + 8u * st);
+        }
+    } else {
+        // ================================================================== consumers
+        unsigned *list = reinterpret_cast<unsigned *>(gs + AG_LISTS) + warp * AG_LIST;
+        float px[AG_TPW], py[AG_TPW], acc[AG_TPW];
+        int th[AG_TPW], excl[AG_TPW], barg[AG_TPW], deg[AG_TPW];
 #pragma unroll
-            for (int u = 0; u < AG_TPW; ++u) {
-                const int t = a + warp + u * AG_WARPS;
-                if (t >= b) continue;
-                const size_t node = (size_t)(n0 + t);
-                const float p = __ldg(P + node * H + lane);
-                float o;
-                if (deg[u] == 0) o = 0.f;                                  // PyG: empty rows aggregate to 0
-                else if (AGGR == GM_AGGR_MAX) o = p + acc[u];
-                else if (AGGR == GM_AGGR_ADD) o = fmaf((float)deg[u], p, acc[u]);
-                else o = fmaf(acc[u], 1.f / (float)deg[u], p);
-                out[node * H + lane] = o;
-                if (ARG) arg[node * H + lane] = barg[u];
-                if (tail.partials) {
-                    if (cnt == 0.f) shift = o;
-                    cnt += 1.f;
-                    const float d = o - shift;
-                    s1 += d;
-                    s2 = fmaf(d, d, s2);
+        for (int u = 0; u < AG_TPW; ++u) { px[u] = py[u] = 0.f; acc[u] = IDENT; th[u] = 0; excl[u] = -1; barg[u] = -1; deg[u] = 0; }
+        for (uint32_t gc = 0;; ++gc) {
+            const int st = gc & 1;
+            const unsigned char *stage = gs + st * AG_STAGE_BYTES;
+            mbar_wait(full0 + 8u * st, (gc >> 1) & 1u);
+            const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + AG_OFF_DESC);
+            const int flags = d->flags;
+            if (flags & AG_END) break;
+            const int a = d->a, b = d->b, rows = d->rows, n0 = d->n0;
+            const float *s_rows = reinterpret_cast<const float *>(stage);
+            const float4 *s_pts = reinterpret_cast<const float4 *>(stage + AG_OFF_PTS);
+            if (flags & AG_FIRST) {
+                const float4 *s_tgt = reinterpret_cast<const float4 *>(stage + AG_OFF_TGT);
+                const int *s_thr = reinterpret_cast<const int *>(stage + AG_OFF_THR);
+#pragma unroll
+                for (int u = 0; u < AG_TPW; ++u) {
+                    const int t = a + warp + u * AG_CONSUMERS;
+                    acc[u] = IDENT; barg[u] = -1; deg[u] = 0;
+                    if (t < b) {
+                        const float4 pt = s_tgt[t];
+                        px[u] = pt.x; py[u] = pt.y;
+                        th[u] = s_thr[t];
+                        excl[u] = m.loop ? -1 : __float_as_int(pt.z);
+                    }
                 }
             }
+#pragma unroll 1                                                                // one copy of the body: see aggr_target
+            for (int u = 0; u < AG_TPW; ++u) {
+                if (a + warp + u * AG_CONSUMERS >= b) break;                    // warp-uniform
+                const TargetResult tr = aggr_target<AGGR, ARG>(s_pts, s_rows, rows, px[u], py[u], th[u], excl[u], acc[u],
+                                                               m.r2, m.dim, m.phi_wrap, lane, list);
+                deg[u] += tr.nh;
+                acc[u] = tr.ac;
+                const int brow = tr.brow;
+                if (ARG && brow >= 0) barg[u] = node_of_row(d, brow);
+                __syncwarp();                                   // the hit list is reused by the next target
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty0 + 8u * st);       // this warp is done with the stage
+            if (flags & AG_LAST) {
+#pragma unroll
+                for (int u = 0; u < AG_TPW; ++u) {
+                    const int t = a + warp + u * AG_CONSUMERS;
+                    if (t >= b) continue;
+                    const size_t node = (size_t)(n0 + t);
+                    const float p = __ldg(P + node * H + lane);
+                    float o;
+                    if (deg[u] == 0) o = 0.f;                                  // PyG: empty rows aggregate to 0
+                    else if (AGGR == GM_AGGR_MAX) o = p + acc[u];
+                    else if (AGGR == GM_AGGR_ADD) o = fmaf((float)deg[u], p, acc[u]);
+                    else o = fmaf(acc[u], 1.f / (float)deg[u], p);
+                    out[node * H + lane] = o;
+                    if (ARG) arg[node * H + lane] = barg[u];
+                    if (tail.partials) {
+                        if (cnt == 0.f) shift = o;
+                        cnt += 1.f;
+                        const float dd = o - shift;
+                        s1 += dd;
+                        s2 = fmaf(dd, dd, s2);
+                    }
+                }
+            }
+        }
+    }
+    if (dynamic) {                                              // last CTA out re-arms the ticket counter
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            if (atomicAdd(v.sched + 1, 1) == (int)gridDim.x - 1) { v.sched[0] = 0; v.sched[1] = 0; __threadfence(); }
         }
     }
     if (tail.partials) {
         float(*s_red)[3][H] = reinterpret_cast<float(*)[3][H]>(gs);      // aliases the (now idle) pipeline stages
         __syncthreads();
-        const float rn = cnt > 0.f ? 1.f / cnt : 0.f;
-        s_red[warp][0][lane] = cnt;
-        s_red[warp][1][lane] = fmaf(s1, rn, shift);
-        s_red[warp][2][lane] = fmaxf(s2 - s1 * s1 * rn, 0.f);
+        if (warp < AG_CONSUMERS) {
+            const float rn = cnt > 0.f ? 1.f / cnt : 0.f;
+            s_red[warp][0][lane] = cnt;
+            s_red[warp][1][lane] = fmaf(s1, rn, shift);
+            s_red[warp][2][lane] = fmaxf(s2 - s1 * s1 * rn, 0.f);
+        }
         __syncthreads();
         if (warp == 0) {
             Moments tot{0.f, 0.f, 0.f};
 #pragma unroll
-            for (int k = 0; k < AG_WARPS; ++k)
+            for (int k = 0; k < AG_CONSUMERS; ++k)
                 tot = moments_combine(tot, Moments{s_red[k][0][lane], s_red[k][1][lane], s_red[k][2][lane]});
             float *dst = tail.partials + (size_t)blockIdx.x * MOM_STRIDE;
             dst[lane] = tot.n; dst[H + lane] = tot.mean; dst[2 * H + lane] = tot.m2;
@@ -418,7 +542,7 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
 // per-warp [32 sources][32 channels] accumulator — a lane owns its column, so there are no conflicts and no atomics.
 // No distance test, no cap threshold, no transposed graph: arg == j already says the edge exists.  The four warp
 // accumulators are folded in warp order and rows are walked in staged (= internal node) order: bit-deterministic.
-constexpr int SC_CH = 64;                      // staged target rows per pipeline stage
+constexpr int SC_CH = GEO_SC_CH;               // staged target rows per pipeline stage
 constexpr int SC_STAGES = 2;
 constexpr size_t SC_ROWS = 0;                                                  // [stage][arg | G | raw][SC_CH][32] x 4 B
 constexpr size_t SC_STAGE_BYTES = (size_t)3 * SC_CH * 128;
@@ -528,7 +652,7 @@ k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd 
 GeoView view_of(const void *geo_ws, int N, int B) {
     GeoWs w;
     geo_ws_layout(N, B, (char *)geo_ws, &w);
-    return GeoView{w.meta, w.bbox, w.cell_start, w.ptr, w.thr, w.pts};
+    return GeoView{w.meta, w.bbox, w.cell_start, w.ptr, w.thr, w.pts, w.sched};
 }
 
 // ------------------------------------------------------------------------------------------ launchers
@@ -607,6 +731,7 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
     k_geo_meta<<<1, 32, 0, st>>>(w.meta, rf, r2, dim, phi_wrap, loop, cap_eff, N, B, w.stats);
     GM_LAUNCH_CHECK();
     GM_CUDA_TRY(cudaMemcpyAsync(w.ptr, ptr, (size_t)(B + 1) * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    GM_CUDA_TRY(cudaMemsetAsync(w.sched, 0, 2 * sizeof(int), st));
     if (N > 0) {
         k_cell_rank<<<persistent_grid((N + 255) / 256, 8), 256, 0, st>>>(w.tmp, ptr, N, B, w.cell_start, w.pts, node_perm_out);
         GM_LAUNCH_CHECK();
