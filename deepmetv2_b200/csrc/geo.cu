@@ -266,15 +266,23 @@ __device__ __forceinline__ int build_hit_list(const float4 *s_pts, int rows, flo
                                               const GeoMeta &m, int lane, unsigned *list) {
     int nh = 0;
     const unsigned lt = (1u << lane) - 1u;
-    for (int base = 0; base < rows; base += 32) {
-        const int c = base + lane;
-        const float4 q = s_pts[c];                          // c < AG_CH always; rows beyond `rows` hold stale points
-        const int cl = __float_as_int(q.z);
-        const bool hit = (dist2(px, py, q.x, q.y, m.dim, m.phi_wrap) < m.r2) & (cl <= th) & (cl != excl) & (c < rows);
-        const unsigned mk = __ballot_sync(0xffffffffu, hit);
-        unsigned *slot = list + nh + __popc(mk & lt);       // address formed unconditionally => predicated store
-        if (hit) *slot = (unsigned)c << 7;
-        nh += __popc(mk);
+    // 128 candidates per trip, their 4 point loads issued up front: the list stores below may alias the points as
+    // far as the compiler knows, so it cannot hoist the next load over them itself.  Reads past `rows` stay inside
+    // the stage (AG_CH + 32 <= points + target area) and are masked by c < rows.
+    for (int base = 0; base < rows; base += 128) {
+        float4 q[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) q[u] = s_pts[base + 32 * u + lane];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int c = base + 32 * u + lane;
+            const int cl = __float_as_int(q[u].z);
+            const bool hit = (dist2(px, py, q[u].x, q[u].y, m.dim, m.phi_wrap) < m.r2) & (cl <= th) & (cl != excl) & (c < rows);
+            const unsigned mk = __ballot_sync(0xffffffffu, hit);
+            unsigned *slot = list + nh + __popc(mk & lt);   // address formed unconditionally => predicated store
+            if (hit) *slot = (unsigned)c << 7;
+            nh += __popc(mk);
+        }
     }
     if (lane < 8) list[nh + lane] = (unsigned)AG_CH << 7;
     __syncwarp();
@@ -296,15 +304,16 @@ __device__ __forceinline__ TargetResult aggr_target(const float4 *s_pts, const f
     GeoMeta m;
     m.r2 = r2; m.dim = dim; m.phi_wrap = phi_wrap;
     const int nh = build_hit_list(s_pts, rows, px, py, th, excl, m, lane, list);
-    const char *col = reinterpret_cast<const char *>(s_rows + lane);       // this lane's channel of staged row 0
+    const uint32_t col = smem_u32(s_rows + lane);                          // this lane's channel of staged row 0
+    auto lds = [](uint32_t a) { float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; };
     unsigned boff = 0xffffffffu;                                           // byte offset of the arg-max row
     for (int k8 = 0; k8 < nh; k8 += 8) {
         const uint4 ra = *reinterpret_cast<const uint4 *>(list + k8);
         const uint4 rb = *reinterpret_cast<const uint4 *>(list + k8 + 4);
-        const float v0 = *reinterpret_cast<const float *>(col + ra.x), v1 = *reinterpret_cast<const float *>(col + ra.y);
-        const float v2 = *reinterpret_cast<const float *>(col + ra.z), v3 = *reinterpret_cast<const float *>(col + ra.w);
-        const float v4 = *reinterpret_cast<const float *>(col + rb.x), v5 = *reinterpret_cast<const float *>(col + rb.y);
-        const float v6 = *reinterpret_cast<const float *>(col + rb.z), v7 = *reinterpret_cast<const float *>(col + rb.w);
+        const float v0 = lds(col + ra.x), v1 = lds(col + ra.y);
+        const float v2 = lds(col + ra.z), v3 = lds(col + ra.w);
+        const float v4 = lds(col + rb.x), v5 = lds(col + rb.y);
+        const float v6 = lds(col + rb.z), v7 = lds(col + rb.w);
         if (AGGR == GM_AGGR_MAX && ARG) {
             if (v0 > ac) { ac = v0; boff = ra.x; }
             if (v1 > ac) { ac = v1; boff = ra.y; }
