@@ -631,14 +631,21 @@ k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd 
                 const float *s_R = s_G + SC_CH * 32;
                 mbar_wait(bar0 + 8u * st, (phases >> st) & 1u);
                 phases ^= 1u << st;
-#pragma unroll 2
-                for (int r = warp; r < rows; r += GEO_WARPS) {
-                    const unsigned rel = (unsigned)s_arg[r * 32 + lane] - first;
-                    if (rel < span) {                                      // this lane's arg-max source is in the item
-                        const float xhat = (s_R[r * 32 + lane] - c_mean) * c_inv;
-                        const float d = c_scale * (s_G[r * 32 + lane] - c_1 - xhat * c_2);
-                        s_acc[warp][a + rel][lane] += d;
+                // 4 staged rows per trip: their arg / G / raw loads are issued together (unconditionally: shared
+                // memory, no traffic to save), then the <= 4 read-modify-writes of the accumulator run in row order
+                for (int r = warp; r < rows; r += 4 * GEO_WARPS) {
+                    unsigned rel[4];
+                    float dv[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int rr = min(r + u * GEO_WARPS, SC_CH - 1);
+                        rel[u] = (r + u * GEO_WARPS < rows) ? (unsigned)s_arg[rr * 32 + lane] - first : 0xffffffffu;
+                        const float xhat = (s_R[rr * 32 + lane] - c_mean) * c_inv;
+                        dv[u] = c_scale * (s_G[rr * 32 + lane] - c_1 - xhat * c_2);
                     }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (rel[u] < span) s_acc[warp][a + rel[u]][lane] += dv[u];
                 }
                 __syncthreads();                                           // stage st fully consumed
                 if (tid == 0 && k + SC_STAGES < nchunks)
