@@ -193,6 +193,137 @@ __global__ void __launch_bounds__(NODE_TILE) k_encode(EncodeArgs a) {
     }
 }
 
+// Encoder on the register-blocked tile product: 256 threads per 128-node tile.  Threads 0..127 build the node's
+// 32-vector u = [LUT row | ELU(W_c x_cont + b)] (thread per node: 256 flop), then ALL threads run the 32x32 layer
+// (2/3 of the encoder's flops) as tile_gemm (4 nodes x 4 outputs per thread, K-major weights), apply ELU and store
+// whole 128-byte rows from registers.  BatchNorm moments: results go back into the tile, 8 slices of 16 rows.
+constexpr int ENC_THREADS = 256;
+__global__ void __launch_bounds__(ENC_THREADS, 3) k_encode2(EncodeArgs a) {
+    __shared__ __align__(16) float s_cont_w[16 * 8];
+    __shared__ float s_cont_b[16];
+    __shared__ __align__(16) float s_encT[H * H];                // enc_w transposed: [k][o]
+    __shared__ __align__(16) float s_enc_b[H];
+    __shared__ __align__(16) float s_lut[LUT_ROWS * 16];
+    __shared__ __align__(16) float s_x[NODE_TILE * 16];
+    __shared__ float s_tile[NODE_TILE * TILE_LD];
+    __shared__ float s_red[ENC_THREADS / 32][3][H];              // 8 slices for the moments
+    static_assert(NODE_TILE * TILE_LD >= (ENC_THREADS / 8) * 3 * H, "the finalize scratch aliases the tile");
+
+    const int t = threadIdx.x, ng = t >> 3, og = t & 7;
+    for (int i = t; i < 16 * 8; i += ENC_THREADS) {
+        int o = i >> 3, k = i & 7;
+        s_cont_w[i] = k < a.CD ? a.cont_w[o * a.CD + k] : 0.f;
+    }
+    if (t < 16) s_cont_b[t] = a.cont_b[t];
+    for (int i = t; i < H * H; i += ENC_THREADS) s_encT[i] = a.enc_w[(i & 31) * H + (i >> 5)];
+    if (t < H) s_enc_b[t] = a.enc_b[t];
+    for (int i = t; i < LUT_ROWS * 16; i += ENC_THREADS) s_lut[i] = a.lut[i];
+    __syncthreads();
+    const float4 b4 = reinterpret_cast<const float4 *>(s_enc_b)[og];
+
+    Moments run{0.f, 0.f, 0.f};
+    int err = 0;
+    const int tiles = (a.N + NODE_TILE - 1) / NODE_TILE;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const int node0 = tile * NODE_TILE;
+        const int rows = min(NODE_TILE, a.N - node0);
+        float xc[8];
+        long long c0 = 0, c1 = 0, c2 = 0;
+        if (a.flat) {
+            const int S = a.x_cont_stride;
+            const float *src = a.x_cont + (size_t)node0 * S;
+            for (int i = t; i < rows * S; i += ENC_THREADS) s_x[i] = src[i];
+            __syncthreads();
+            if (t < rows) {
+                const float *row = s_x + t * S;
+                const int cat_off = (int)(a.x_cat_f32 - a.x_cont);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) xc[k] = k < a.CD ? row[k] : 0.f;
+                c0 = (long long)row[cat_off]; c1 = (long long)row[cat_off + 1]; c2 = (long long)row[cat_off + 2];
+            }
+        } else if (t < rows) {
+            const size_t n = a.perm ? (size_t)a.perm[node0 + t] : (size_t)(node0 + t);
+            const float *row = a.x_cont + n * a.x_cont_stride;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) xc[k] = k < a.CD ? row[k] : 0.f;
+            if (a.x_cat_i64) {
+                const long long *cr = a.x_cat_i64 + n * 3;
+                c0 = cr[0]; c1 = cr[1]; c2 = cr[2];
+            } else {
+                const float *cr = a.x_cat_f32 + n * a.x_cat_stride;
+                c0 = (long long)cr[0]; c1 = (long long)cr[1]; c2 = (long long)cr[2];
+            }
+        }
+        if (t < rows) {                                           // u = cat[emb_cat, emb_cont] (graph_met_network.py:58)
+            float *u = s_tile + t * TILE_LD;
+            const int combo = cat_combo(c0, c1, c2, &err);
+            const float4 *l4 = reinterpret_cast<const float4 *>(s_lut + combo * 16);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float4 v = l4[k];
+                u[4 * k] = v.x; u[4 * k + 1] = v.y; u[4 * k + 2] = v.z; u[4 * k + 3] = v.w;
+            }
+            float h0[16];
+            dense_smem<8, 16>(s_cont_w, s_cont_b, xc, h0);
+#pragma unroll
+            for (int k = 0; k < 16; ++k) u[16 + k] = elu(h0[k]);
+        } else if (t < NODE_TILE) {                               // rows past the end: keep the product finite
+            float *u = s_tile + t * TILE_LD;
+#pragma unroll
+            for (int k = 0; k < H; ++k) u[k] = 0.f;
+        }
+        __syncthreads();
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { acc[i][0] = b4.x; acc[i][1] = b4.y; acc[i][2] = b4.z; acc[i][3] = b4.w; }
+        tile_gemm<H, H, TILE_LD>(s_tile, s_encT, ng, og, acc);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = elu(acc[i][j]);
+            if (ng + 32 * i < rows)
+                reinterpret_cast<float4 *>(a.enc_out)[(size_t)(node0 + ng + 32 * i) * (H / 4) + og] =
+                    make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        }
+        __syncthreads();                                          // every thread is done reading u
+        if (a.partials) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float *d = s_tile + (ng + 32 * i) * TILE_LD + 4 * og;
+                d[0] = acc[i][0]; d[1] = acc[i][1]; d[2] = acc[i][2]; d[3] = acc[i][3];
+            }
+            __syncthreads();
+            const int c = t & 31, q = t >> 5;                     // slice q: rows 16q .. 16q+15
+            const int r0 = q * 16, r1 = min(rows, r0 + 16);
+            float n = (float)max(r1 - r0, 0), mean = 0.f, m2 = 0.f;
+            if (r1 > r0) {
+                float sum = 0.f;
+                for (int r = r0; r < r1; ++r) sum += s_tile[r * TILE_LD + c];
+                mean = sum / n;
+                for (int r = r0; r < r1; ++r) { float dlt = s_tile[r * TILE_LD + c] - mean; m2 = fmaf(dlt, dlt, m2); }
+            }
+            s_red[q][0][c] = n; s_red[q][1][c] = mean; s_red[q][2][c] = m2;
+            __syncthreads();
+            if (t < 32) {
+#pragma unroll
+                for (int gq = 0; gq < ENC_THREADS / 32; ++gq)
+                    run = moments_combine(run, Moments{s_red[gq][0][c], s_red[gq][1][c], s_red[gq][2][c]});
+            }
+            __syncthreads();
+        }
+    }
+    if (err) atomicOr(a.err_flags, GM_FLAG_CAT_OUT_OF_RANGE);
+    if (a.partials) {
+        if (t < 32) {
+            float *dst = a.partials + (size_t)blockIdx.x * MOM_STRIDE;
+            dst[t] = run.n; dst[H + t] = run.mean; dst[2 * H + t] = run.m2;
+        }
+        if (last_cta_done(a.counter))
+            bn_finalize_cta(a.partials, gridDim.x, a.bn, a.momentum, a.eps, a.stat,
+                            reinterpret_cast<float(*)[3][H]>(s_tile));
+    }
+}
+
 // ------------------------------------------------------------------------------------------ BatchNorm (TC path only)
 // Stand-alone finalize for producers that do not carry the last-CTA epilogue (the tcgen05 EdgeConv kernel).
 __global__ void __launch_bounds__(256) k_bn_finalize(const float *__restrict__ partials, int n_partials,
@@ -784,7 +915,7 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
     ea.err_flags = err_flags;
     {
         TimedRegion tr(GM_TIMER_ENCODE_FWD, st);
-        k_encode<<<encode_grid(N), NODE_TILE, 0, st>>>(ea);
+        k_encode2<<<persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 3), ENC_THREADS, 0, st>>>(ea);
         GM_LAUNCH_CHECK();
     }
 
