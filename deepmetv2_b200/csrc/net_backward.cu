@@ -69,12 +69,12 @@ __device__ __forceinline__ void store_row(float *dst, const float (&v)[NV]) {
 }
 
 // dW[o][i] += sum_rows A[r][o] * B[r][i] ; thread owns one 4x4 block for one group of rows.
-template <int O, int I>
+template <int O, int I, int NT = NODE_TILE>
 struct Outer {
     static constexpr int BO = O / 4, BI = I / 4, BLK = BO * BI;
-    static constexpr int GROUPS = NODE_TILE / BLK;
+    static constexpr int GROUPS = NT / BLK;
     static constexpr int ROWS_PER = (NODE_TILE + GROUPS - 1) / GROUPS;
-    static_assert(O % 4 == 0 && I % 4 == 0 && BLK <= NODE_TILE, "bad outer-product shape");
+    static_assert(O % 4 == 0 && I % 4 == 0 && BLK <= NT, "bad outer-product shape");
     float acc[16];
     __device__ __forceinline__ void zero() {
 #pragma unroll
@@ -101,7 +101,7 @@ struct Outer {
     // fold the row groups in order, write the [O][I] CTA partial; scratch >= O*I floats of smem
     __device__ __forceinline__ void flush(float *scratch, float *__restrict__ dst) {
         const int t = threadIdx.x;
-        for (int i = t; i < O * I; i += NODE_TILE) scratch[i] = 0.f;
+        for (int i = t; i < O * I; i += NT) scratch[i] = 0.f;
         __syncthreads();
         const int g = t / BLK, b = t - g * BLK, bo = b / BI, bi = b - bo * BI;
         for (int gg = 0; gg < GROUPS; ++gg) {
@@ -113,15 +113,15 @@ struct Outer {
             }
             __syncthreads();
         }
-        for (int i = t; i < O * I; i += NODE_TILE) dst[i] = scratch[i];
+        for (int i = t; i < O * I; i += NT) dst[i] = scratch[i];
         __syncthreads();
     }
 };
 
 // column sums of a tile: s[c] += sum_rows T[r][c], c < NC
-template <int NC>
+template <int NC, int NT = NODE_TILE>
 struct ColSum {
-    static constexpr int GROUPS = NODE_TILE / NC;
+    static constexpr int GROUPS = NT / NC;
     static constexpr int ROWS_PER = (NODE_TILE + GROUPS - 1) / GROUPS;
     float acc;
     __device__ __forceinline__ void zero() { acc = 0.f; }
@@ -178,21 +178,23 @@ __global__ void __launch_bounds__(256) k_reduce_partials(Segs segs) {
     }
 }
 
-// Last CTA: fold the per-CTA (sum G, sum G*xhat) partials in a fixed order.  blockDim.x == NODE_TILE: 16 lane
+// Last CTA: fold the per-CTA (sum G, sum G*xhat) partials in a fixed order.  blockDim.x >= NODE_TILE: 16 lane
 // groups of 8 lanes (two float4 = 8 of the 64 sums each) stream CTAs g, g+16, ... with independent loads,
 // then 64 threads fold the 16 group results in group order.  scratch >= 1024 floats.
 __device__ __forceinline__ void bn_sums_finalize(const BnSumOut &o, float *scratch) {
     const int t = threadIdx.x, sub = t & 7, grp = t >> 3;
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
 #pragma unroll 4
-    for (int b = grp; b < (int)gridDim.x; b += NODE_TILE / 8) {
+    for (int b = grp; b < (int)gridDim.x && t < NODE_TILE; b += NODE_TILE / 8) {
         const float4 *p = reinterpret_cast<const float4 *>(o.part + (size_t)b * 64) + 2 * sub;
         const float4 u = __ldcg(p), v = __ldcg(p + 1);
         a0.x += u.x; a0.y += u.y; a0.z += u.z; a0.w += u.w;
         a1.x += v.x; a1.y += v.y; a1.z += v.z; a1.w += v.w;
     }
-    float *d = scratch + grp * 64 + 8 * sub;
-    d[0] = a0.x; d[1] = a0.y; d[2] = a0.z; d[3] = a0.w; d[4] = a1.x; d[5] = a1.y; d[6] = a1.z; d[7] = a1.w;
+    if (t < NODE_TILE) {
+        float *d = scratch + grp * 64 + 8 * sub;
+        d[0] = a0.x; d[1] = a0.y; d[2] = a0.z; d[3] = a0.w; d[4] = a1.x; d[5] = a1.y; d[6] = a1.z; d[7] = a1.w;
+    }
     __syncthreads();
     if (t < 64) {
         float tot = 0.f;
@@ -441,6 +443,114 @@ k_conv_bwd_node(const float *__restrict__ x, const float *__restrict__ raw, BnBw
     if (last_cta_done(bo.counter)) bn_sums_finalize(bo, tA);
 }
 
+// Same stage on the register-blocked tile product (common.cuh): 256 threads per 128-node tile.  Cooperative,
+// coalesced float4 loads build the tiles d(conv) = BatchNorm backward of G, S and x in shared memory; the two
+// 32x32 transposed products run as tile_gemm with the accumulators initialised from G (4 nodes x 4 channels per
+// thread) and the new G leaves from registers as whole 128-byte rows; the parameter-gradient outer products and
+// the BatchNorm sums of the layer below read the same tiles.  [c][k] weights are K-major for the transposed product.
+constexpr int CB_THREADS = 256;
+__global__ void __launch_bounds__(CB_THREADS, 2)
+k_conv_bwd_node2(const float *__restrict__ x, const float *__restrict__ raw, BnBwd bn, const float *__restrict__ S, int N,
+                 const float *__restrict__ W, float *__restrict__ G, float *__restrict__ gpart, BnSumOut bo) {
+    extern __shared__ __align__(16) float smem[];
+    float *s_wd = smem;                  // W1 - W2, [c][k]
+    float *s_w2 = s_wd + H * H;
+    float *tA = s_w2 + H * H;            // d(conv)            then  G_new
+    float *tB = tA + NODE_TILE * GLD;    // x                  then  G_new * xhat(below)
+    float *tC = tB + NODE_TILE * GLD;    // S                  then  S - d(conv)
+    float *s_coef = tC + NODE_TILE * GLD;   // [5][32]
+    float *s_mean = s_coef + 5 * H;      // BatchNorm below: mean, invstd
+    float *s_inv = s_mean + H;
+    const int t = threadIdx.x, ng = t >> 3, og = t & 7;
+    for (int i = t; i < H * H; i += CB_THREADS) {
+        const int c = i >> 5, k = i & 31;
+        const float a = W[c * CONV_IN + k], b = W[c * CONV_IN + H + k];
+        s_wd[i] = a - b; s_w2[i] = b;
+    }
+    bn_bwd_coeffs(bn, s_coef);
+    if (t < H) { s_mean[t] = bo.stat[t]; s_inv[t] = bo.stat[2 * H + t]; }
+    __syncthreads();
+    Outer<H, H, CB_THREADS> o1, o2; o1.zero(); o2.zero();
+    ColSum<H, CB_THREADS> cb, sg, sgx; cb.zero(); sg.zero(); sgx.zero();
+    const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const int node0 = tile * NODE_TILE, rows = min(NODE_TILE, N - node0);
+        const float4 *G4 = reinterpret_cast<const float4 *>(G) + (size_t)node0 * (H / 4);
+        const float4 *R4 = reinterpret_cast<const float4 *>(raw) + (size_t)node0 * (H / 4);
+        const float4 *S4 = reinterpret_cast<const float4 *>(S) + (size_t)node0 * (H / 4);
+        const float4 *X4 = reinterpret_cast<const float4 *>(x) + (size_t)node0 * (H / 4);
+#pragma unroll
+        for (int it = 0; it < NODE_TILE * (H / 4) / CB_THREADS; ++it) {
+            const int idx = it * CB_THREADS + t, r = idx >> 3, c4 = (idx & 7) * 4;
+            float4 dc = make_float4(0.f, 0.f, 0.f, 0.f), sv = dc, xv = dc;
+            if (r < rows) {
+                const float4 g = G4[idx], rw = R4[idx];
+                sv = S4[idx]; xv = X4[idx];
+                dc.x = bn_bwd_one(s_coef, c4 + 0, g.x, rw.x); dc.y = bn_bwd_one(s_coef, c4 + 1, g.y, rw.y);
+                dc.z = bn_bwd_one(s_coef, c4 + 2, g.z, rw.z); dc.w = bn_bwd_one(s_coef, c4 + 3, g.w, rw.w);
+            }
+            *reinterpret_cast<float4 *>(tA + r * GLD + c4) = dc;
+            *reinterpret_cast<float4 *>(tC + r * GLD + c4) = sv;
+            *reinterpret_cast<float4 *>(tB + r * GLD + c4) = xv;
+        }
+        __syncthreads();
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float4 g = ng + 32 * i < rows ? G4[(ng + 32 * i) * (H / 4) + og] : make_float4(0.f, 0.f, 0.f, 0.f);
+            acc[i][0] = g.x; acc[i][1] = g.y; acc[i][2] = g.z; acc[i][3] = g.w;
+        }
+        tile_gemm<H, H, GLD>(tA, s_wd, ng, og, acc);       // += (W1 - W2)^T d(conv)
+        tile_gemm<H, H, GLD>(tC, s_w2, ng, og, acc);       // += W2^T S
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (ng + 32 * i < rows)
+                reinterpret_cast<float4 *>(G)[(size_t)(node0 + ng + 32 * i) * (H / 4) + og] =
+                    make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        __syncthreads();                                   // products done with tA / tC
+#pragma unroll
+        for (int it = 0; it < NODE_TILE * (H / 4) / CB_THREADS; ++it) {
+            const int idx = it * CB_THREADS + t, r = idx >> 3, c4 = (idx & 7) * 4;
+            const float4 dc = *reinterpret_cast<const float4 *>(tA + r * GLD + c4);
+            float4 sv = *reinterpret_cast<const float4 *>(tC + r * GLD + c4);
+            sv.x -= dc.x; sv.y -= dc.y; sv.z -= dc.z; sv.w -= dc.w;
+            *reinterpret_cast<float4 *>(tC + r * GLD + c4) = sv;
+        }
+        __syncthreads();
+        o1.accumulate(tA, GLD, tB, GLD, rows);
+        o2.accumulate(tC, GLD, tB, GLD, rows);
+        cb.accumulate(tA, GLD, rows);
+        __syncthreads();
+        // BatchNorm sums of the layer below (bn_all for layer 0): tiles of G_new and G_new * xhat
+        const float4 *RB4 = reinterpret_cast<const float4 *>(bo.raw) + (size_t)node0 * (H / 4);
+        const float4 m4 = reinterpret_cast<const float4 *>(s_mean)[og], i4 = reinterpret_cast<const float4 *>(s_inv)[og];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = ng + 32 * i;
+            float4 gx = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (r < rows) {
+                const float4 rb = RB4[r * (H / 4) + og];
+                gx.x = acc[i][0] * ((rb.x - m4.x) * i4.x); gx.y = acc[i][1] * ((rb.y - m4.y) * i4.y);
+                gx.z = acc[i][2] * ((rb.z - m4.z) * i4.z); gx.w = acc[i][3] * ((rb.w - m4.w) * i4.w);
+            }
+            *reinterpret_cast<float4 *>(tA + r * GLD + 4 * og) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+            *reinterpret_cast<float4 *>(tB + r * GLD + 4 * og) = gx;
+        }
+        __syncthreads();
+        sg.accumulate(tA, GLD, rows);
+        sgx.accumulate(tB, GLD, rows);
+        __syncthreads();
+    }
+    float *dst = gpart + (size_t)blockIdx.x * GP_STRIDE;
+    o1.flush(tA, dst);
+    o2.flush(tA, dst + 1024);
+    cb.flush(tA, dst + 2048, H);
+    float *bp = bo.part + (size_t)blockIdx.x * 64;
+    sg.flush(tA, bp, H);
+    sgx.flush(tA, bp + H, H);
+    if (last_cta_done(bo.counter)) bn_sums_finalize(bo, tA);
+}
+
 // ----------------------------------------------------------------------------------------- encoder backward
 // partial layout: dWa[32][32] @0, dba[32] @1024, dWc[16][8] @1056, dbc[16] @1184, dWk[16][24] @1200,
 //                 dbk[16] @1584, d(tables)[18][8] @1600 (charge rows 0-2, pdgid 3-9, pv 10-17)
@@ -669,7 +779,7 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
     add_seg(0, grads->out2_b, 1, 544, 1, 1, 1);
 
     // ---- EdgeConv layers, last to first
-    GM_CUDA_TRY(cudaFuncSetAttribute(k_conv_bwd_node, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CONV_BWD_SMEM));
+    GM_CUDA_TRY(cudaFuncSetAttribute(k_conv_bwd_node2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CONV_BWD_SMEM));
     for (int l = depth - 1; l >= 0; --l) {
         const int stage = depth - l;
         {
@@ -686,8 +796,8 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
         }
         {
             TimedRegion tr(GM_TIMER_CONV_NODE_BWD, st);
-            k_conv_bwd_node<<<ngrid, NODE_TILE, CONV_BWD_SMEM, st>>>(f.emb[l], f.conv[l], bn_in(l + 1), w.S, N,
-                                                                     p->conv_w[l], w.G, gpart(stage), sum_out(l));
+            k_conv_bwd_node2<<<ngrid, CB_THREADS, CONV_BWD_SMEM, st>>>(f.emb[l], f.conv[l], bn_in(l + 1), w.S, N,
+                                                                       p->conv_w[l], w.G, gpart(stage), sum_out(l));
             GM_LAUNCH_CHECK();
         }
         add_seg(stage, grads->conv_w[l], CONV_IN, 0, H, H, H);
