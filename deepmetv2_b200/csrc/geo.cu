@@ -102,11 +102,45 @@ __global__ void __launch_bounds__(256) k_cell_rank(const float4 *__restrict__ tm
     }
 }
 
+// Cap pre-filter, thread per node: only a target whose 3x3 neighbourhood holds more than `cap` points can be capped
+// at all.  Those (a few percent outside jet cores) are appended to a list for the warp-per-target kernel below; the
+// order of the list is arbitrary and irrelevant (thr[s] depends on s alone).
+__global__ void __launch_bounds__(256) k_geo_cap_scan(const int *__restrict__ ptr, int N, int B,
+                                                      const GeoMeta *__restrict__ meta, const int *__restrict__ bbox,
+                                                      const int *__restrict__ cell_start, const float4 *__restrict__ pts,
+                                                      int *__restrict__ list, int *__restrict__ count) {
+    const GeoMeta m = *meta;
+    const CellGrid g = make_grid(bbox, m.r, m.dim, m.phi_wrap);
+    const int lane = threadIdx.x & 31;
+    for (int s0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; s0 < N; s0 += gridDim.x * blockDim.x) {
+        const int s = s0 + lane;
+        bool dense = false;
+        if (s < N) {
+            const int e = find_event(ptr, B, s);
+            const int cell = __float_as_int(__ldg(&pts[s].w));
+            const int ce = cell / g.g1, cp = cell - ce * g.g1;
+            int rlo[6], rhi[6];
+            const int nr = nbhd_runs(g, cell_start + (size_t)e * (CMAX + 1), ce, cp, cp, m.phi_wrap, rlo, rhi);
+            int C = 0;
+            for (int q = 0; q < nr; ++q) C += rhi[q] - rlo[q];
+            dense = C > m.cap_eff;
+        }
+        const unsigned mk = __ballot_sync(0xffffffffu, dense);
+        if (mk) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(count, __popc(mk));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (dense) list[base + __popc(mk & ((1u << lane) - 1u))] = s;
+        }
+    }
+}
+
 // thr[s] for the targets that can exceed the cap at all (3x3 neighbourhood population > cap): hits are marked in a
 // per-warp shared bitmask indexed by the event-local ORIGINAL index, the cap-th set bit is the last admissible source.
 __global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, int N, int B, const GeoMeta *__restrict__ meta,
                                                  const int *__restrict__ bbox, const int *__restrict__ cell_start,
                                                  const float4 *__restrict__ pts, int mask_words, int *__restrict__ thr,
+                                                 const int *__restrict__ list, const int *__restrict__ count,
                                                  int *__restrict__ stats) {
     extern __shared__ unsigned int smask[];
     const GeoMeta m = *meta;
@@ -115,7 +149,9 @@ __global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, in
     unsigned int *mask = smask + (size_t)(threadIdx.x >> 5) * mask_words;
     const int warps = (gridDim.x * blockDim.x) >> 5;
     int local_max = 0, local_capped = 0;
-    for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < N; s += warps) {
+    const int n_list = *count;
+    for (int li = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; li < n_list; li += warps) {
+        const int s = list[li];
         const int e = find_event(ptr, B, s);
         const int base = __ldg(ptr + e), n_e = __ldg(ptr + e + 1) - base;
         const float4 t = pts[s];
@@ -191,7 +227,7 @@ struct GeoView {       // device pointers of a built GeoWs (passed by value)
     const GeoMeta *meta;
     const int *bbox, *cell_start, *ptr, *thr;
     const float4 *pts;
-    int *sched;        // [2] dynamic-schedule ticket + finished-CTA count (self-resetting; zeroed by gm_geo_build)
+    int *sched;        // [0..1] dynamic-schedule ticket + finished-CTA count (self-resetting; zeroed by gm_geo_build)
 };
 
 // forward kernel: [stage]{ (AG_CH + 1) rows x 128 B (last row: identity), AG_CH points x 16 B, the item's 32 target
@@ -747,7 +783,7 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
     k_geo_meta<<<1, 32, 0, st>>>(w.meta, rf, r2, dim, phi_wrap, loop, cap_eff, N, B, w.stats);
     GM_LAUNCH_CHECK();
     GM_CUDA_TRY(cudaMemcpyAsync(w.ptr, ptr, (size_t)(B + 1) * sizeof(int), cudaMemcpyDeviceToDevice, st));
-    GM_CUDA_TRY(cudaMemsetAsync(w.sched, 0, 2 * sizeof(int), st));
+    GM_CUDA_TRY(cudaMemsetAsync(w.sched, 0, 4 * sizeof(int), st));
     if (N > 0) {
         k_cell_rank<<<persistent_grid((N + 255) / 256, 8), 256, 0, st>>>(w.tmp, ptr, N, B, w.cell_start, w.pts, node_perm_out);
         GM_LAUNCH_CHECK();
@@ -760,7 +796,12 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
         if (smem > 48 * 1024)
             GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_cap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const int grid = persistent_grid(((long long)N * 32 + threads - 1) / threads, 2048 / threads);
-        k_geo_cap<<<grid, threads, smem, st>>>(ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts, mask_words, w.thr, w.stats);
+        int *cap_list = reinterpret_cast<int *>(w.tmp);          // tmp is dead once k_cell_rank has run
+        k_geo_cap_scan<<<persistent_grid((N + 255) / 256, 8), 256, 0, st>>>(ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts,
+                                                                            cap_list, w.sched + 2);
+        GM_LAUNCH_CHECK();
+        k_geo_cap<<<grid, threads, smem, st>>>(ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts, mask_words, w.thr,
+                                               cap_list, w.sched + 2, w.stats);
         GM_LAUNCH_CHECK();
     }
     if (stats_out) GM_CUDA_TRY(cudaMemcpyAsync(stats_out, w.stats, 4 * sizeof(int), cudaMemcpyDeviceToDevice, st));

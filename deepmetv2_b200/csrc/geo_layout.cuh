@@ -29,7 +29,8 @@ struct GeoWs {
     float4 *pts;          // [N] (eta, phi, local original index bits, cell bits) in internal order
     int *thr;             // [N] internal order
     int *stats;           // [4] E (-1: not counted), max degree seen in dense cells, #capped, flags
-    int *sched;           // [2] ticket / finished-CTA counters of the dynamically scheduled (eval) forward kernel
+    int *sched;           // [4] ticket / finished-CTA counters of the dynamically scheduled (eval) forward kernel,
+                          //     [2] = length of the cap-candidate list
 };
 
 inline size_t geo_ws_layout(int N, int B, char *base, GeoWs *w) {
@@ -44,7 +45,7 @@ inline size_t geo_ws_layout(int N, int B, char *base, GeoWs *w) {
     t.meta = (GeoMeta *)take(sizeof(GeoMeta));
     t.bbox = (int *)take(4 * sizeof(int));
     t.stats = (int *)take(4 * sizeof(int));
-    t.sched = (int *)take(2 * sizeof(int));
+    t.sched = (int *)take(4 * sizeof(int));
     t.ptr = (int *)take((events + 1) * sizeof(int));
     t.cell_cnt = (int *)take(events * CMAX * sizeof(int));
     t.cell_start = (int *)take(events * (CMAX + 1) * sizeof(int));
