@@ -391,11 +391,7 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
 
     const GeoMeta m = *v.meta;
     const float IDENT = AGGR == GM_AGGR_MAX ? -INFINITY : 0.f;
-#ifdef GEO_FORCE_DYNAMIC
-    const bool dynamic = true;
-#else
     const bool dynamic = tail.partials == nullptr;
-#endif
     if (tid == 0) {
         for (int s = 0; s < AG_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, AG_CONSUMERS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -701,6 +697,51 @@ k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd 
     }
 }
 
+// BatchNorm moments of an [N, 32] activation, as a pass of its own: the forward geo kernel takes its items from a
+// ticket counter (dense jet cells cost many times a forward-calorimeter cell: static schedules left the SMs idle
+// 24-37 % of the kernel), so its per-CTA contents depend on the schedule; this kernel reads the freshly written,
+// L2-resident rows with a STATIC assignment (warp w of the grid owns rows w, w + W, ...), which keeps the moments --
+// and with them the whole training step -- bit-reproducible.  Lane = channel, 8 row loads in flight per lane,
+// shifted sums per warp (shift = the warp's first row), Chan combination in warp / CTA order, last CTA finalises.
+constexpr int RM_THREADS = 256;
+__global__ void __launch_bounds__(RM_THREADS) k_row_moments(const float *__restrict__ x, int N, AggrTail tail) {
+    __shared__ float s_red[RM_THREADS / 8][3][H];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int W = (gridDim.x * RM_THREADS) >> 5;
+    float cnt = 0.f, shift = 0.f, s1 = 0.f, s2 = 0.f;
+    for (int r0 = blockIdx.x * (RM_THREADS / 32) + warp; r0 < N; r0 += 8 * W) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int r = r0 + u * W;
+            v[u] = r < N ? __ldcg(x + (size_t)r * H + lane) : 0.f;
+        }
+        if (cnt == 0.f) shift = v[0];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (r0 + u * W < N) {
+                const float d = v[u] - shift;
+                cnt += 1.f; s1 += d; s2 = fmaf(d, d, s2);
+            }
+        }
+    }
+    const float rn = cnt > 0.f ? 1.f / cnt : 0.f;
+    s_red[warp][0][lane] = cnt;
+    s_red[warp][1][lane] = fmaf(s1, rn, shift);
+    s_red[warp][2][lane] = fmaxf(s2 - s1 * s1 * rn, 0.f);
+    __syncthreads();
+    if (warp == 0) {
+        Moments tot{0.f, 0.f, 0.f};
+#pragma unroll
+        for (int k = 0; k < RM_THREADS / 32; ++k)
+            tot = moments_combine(tot, Moments{s_red[k][0][lane], s_red[k][1][lane], s_red[k][2][lane]});
+        float *dst = tail.partials + (size_t)blockIdx.x * MOM_STRIDE;
+        dst[lane] = tot.n; dst[H + lane] = tot.mean; dst[2 * H + lane] = tot.m2;
+    }
+    if (last_cta_done(tail.counter))
+        bn_finalize_cta(tail.partials, gridDim.x, tail.bn, tail.momentum, tail.eps, tail.stat, s_red);
+}
+
 GeoView view_of(const void *geo_ws, int N, int B) {
     GeoWs w;
     geo_ws_layout(N, B, (char *)geo_ws, &w);
@@ -723,9 +764,19 @@ int launch_geo_aggr(const float *Y, const float *P, const GeoView &v, int N, flo
         }
     }
     const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, min(occ[which], MAX_PARTIAL_CTAS / 148));
-    if (arg) k_geo_aggr<AGGR, true><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, tail);
-    else k_geo_aggr<AGGR, false><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, tail);
+    // Train mode, two ways to the BatchNorm moments: with >= 8 items per CTA the ticket schedule wins more than the
+    // extra (L2-resident) pass of k_row_moments costs (c5: 233 -> 212 us); below that the static schedule with the
+    // moments folded into the kernel is faster (c2: 72 vs 80 us).  Both are bit-reproducible.
+    const bool split = tail.partials && (long long)(N + GEO_TPI - 1) / GEO_TPI >= 8LL * grid;
+    const AggrTail in_kernel = split ? AggrTail{} : tail;
+    if (arg) k_geo_aggr<AGGR, true><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, in_kernel);
+    else k_geo_aggr<AGGR, false><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, in_kernel);
     GM_LAUNCH_CHECK();
+    if (split) {
+        const int mgrid = persistent_grid((N + 63) / 64, min(4, MAX_PARTIAL_CTAS / 148));
+        k_row_moments<<<mgrid, RM_THREADS, 0, st>>>(out, N, tail);
+        GM_LAUNCH_CHECK();
+    }
     return GM_OK;
 }
 
