@@ -85,6 +85,39 @@ __global__ void __launch_bounds__(RED_THREADS) k_met(const float *__restrict__ w
     if (threadIdx.x == 0) { met[2 * e] = sx; met[2 * e + 1] = sy; }
 }
 
+// MET + d loss / d w_n = ((METx+tx) px + (METy+ty) py) / B in one launch (training): the CTA of an event has everything d loss / d w needs once its own
+// MET is reduced; the second sweep over the event's rows hits L1/L2.  Same summation order as k_met.
+__global__ void __launch_bounds__(RED_THREADS) k_met_grad(const float *__restrict__ w, const float *__restrict__ pred,
+                                                          int pstride, const int *__restrict__ ptr,
+                                                          const float *__restrict__ truth, int tstride, int B,
+                                                          float *__restrict__ met, float *__restrict__ gw) {
+    __shared__ float sm[RED_THREADS / 32];
+    __shared__ float s_g[2];
+    const int e = blockIdx.x;
+    const int lo = ptr[e], hi = ptr[e + 1];
+    float sx = 0.f, sy = 0.f;
+    for (int n = lo + threadIdx.x; n < hi; n += RED_THREADS) {
+        const float wn = w[n];
+        const float *row = pred + (size_t)n * pstride;
+        sx = fmaf(wn, row[0], sx);
+        sy = fmaf(wn, row[1], sy);
+    }
+    sx = block_sum(sx, sm);
+    sy = block_sum(sy, sm);
+    if (threadIdx.x == 0) {
+        met[2 * e] = sx; met[2 * e + 1] = sy;
+        const float inv_b = 1.0f / (float)B;
+        s_g[0] = (sx + truth[(size_t)e * tstride]) * inv_b;
+        s_g[1] = (sy + truth[(size_t)e * tstride + 1]) * inv_b;
+    }
+    __syncthreads();
+    const float gx = s_g[0], gy = s_g[1];
+    for (int n = lo + threadIdx.x; n < hi; n += RED_THREADS) {
+        const float *row = pred + (size_t)n * pstride;
+        gw[n] = fmaf(gx, row[0], gy * row[1]);
+    }
+}
+
 __global__ void __launch_bounds__(RED_THREADS) k_loss(const float *__restrict__ met, const float *__restrict__ truth,
                                                       int tstride, int B, float *__restrict__ loss) {
     __shared__ float sm[RED_THREADS / 32];
@@ -96,22 +129,6 @@ __global__ void __launch_bounds__(RED_THREADS) k_loss(const float *__restrict__ 
     }
     acc = block_sum(acc, sm);
     if (threadIdx.x == 0) loss[0] = 0.5f * acc / (float)B;
-}
-
-// d loss / d w_n = ((METx+tx) px + (METy+ty) py) / B
-__global__ void __launch_bounds__(RED_THREADS) k_loss_grad_w(const float *__restrict__ met,
-                                                             const float *__restrict__ truth, int tstride,
-                                                             const float *__restrict__ pred, int pstride,
-                                                             const int *__restrict__ ptr, int B,
-                                                             float *__restrict__ gw) {
-    const int e = blockIdx.x;
-    const float inv_b = 1.0f / (float)B;
-    const float gx = (met[2 * e] + truth[(size_t)e * tstride]) * inv_b;
-    const float gy = (met[2 * e + 1] + truth[(size_t)e * tstride + 1]) * inv_b;
-    for (int n = ptr[e] + threadIdx.x; n < ptr[e + 1]; n += RED_THREADS) {
-        const float *row = pred + (size_t)n * pstride;
-        gw[n] = fmaf(gx, row[0], gy * row[1]);
-    }
 }
 
 __global__ void __launch_bounds__(RED_THREADS) k_segment_sum(const float *__restrict__ src, const int *__restrict__ ptr,
@@ -307,14 +324,13 @@ int gm_met_loss(const float *w, const float *pred, int pred_stride, const float 
         return GM_ERR_INVALID_ARGUMENT;
     if (pred_stride < 2 || truth_stride < 2) return GM_ERR_INVALID_ARGUMENT;
     cudaStream_t st = as_stream(stream);
-    k_met<<<B, RED_THREADS, 0, st>>>(w, pred, pred_stride, ptr, met_out);
+    if (grad_w_out && N > 0)
+        k_met_grad<<<B, RED_THREADS, 0, st>>>(w, pred, pred_stride, ptr, truth, truth_stride, B, met_out, grad_w_out);
+    else
+        k_met<<<B, RED_THREADS, 0, st>>>(w, pred, pred_stride, ptr, met_out);
     GM_LAUNCH_CHECK();
     k_loss<<<1, RED_THREADS, 0, st>>>(met_out, truth, truth_stride, B, loss_out);
     GM_LAUNCH_CHECK();
-    if (grad_w_out && N > 0) {
-        k_loss_grad_w<<<B, RED_THREADS, 0, st>>>(met_out, truth, truth_stride, pred, pred_stride, ptr, B, grad_w_out);
-        GM_LAUNCH_CHECK();
-    }
     return GM_OK;
 }
 
