@@ -213,7 +213,7 @@ def main():
     model = gnet.Net(8, 3).to(dev)
     model.graphnet.edge_precision = args.precision
     trainer = GraphMETTrainer(model, lr=1e-3, process_group=pg, graph=args.graph)
-    graph_mode = "implicit" if trainer._implicit() else "csr"
+    graph_mode = "implicit" if trainer._implicit(training=(mode == "train")) else "csr"
     host = [b.pin_memory() for b in make_batches(args.workload, rank)]
     devb = [b.to(dev) for b in host]
     men = [int((b.ptr[1:] - b.ptr[:-1]).max()) for b in host]
@@ -358,7 +358,7 @@ def main():
         dur = ec_ms / ec_n * 1e-3
         achieved = 4096.0 * E_avg / dur / 1e12
         peak = peaks["bf16_tflops_sustained"]
-        roofline = {"kernel": "k_edgeconv_tc (" + args.precision + ")", "bound": "tensor", "achieved": achieved,
+        roofline = {"kernel": ("k_geo_edgeconv_tc (" if implicit else "k_edgeconv_tc (") + args.precision + ")", "bound": "tensor", "achieved": achieved,
                     "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                     "avg_launch_us": dur * 1e6, "launches_timed": ec_n,
                     "algorithmic_flops_per_launch": 4096.0 * E_avg, "peak_source": peaks["source"],

@@ -74,11 +74,11 @@ SIGNATURES = {
                              _i, _vp, _i, _i, _i, _f, _vp, _sz, _vp, _sz, _vp, _vp, _vp]),
     "gm_geo_ws_bytes": (_sz, [_i, _i]),
     "gm_geo_build": (_i, [_vp, _i, _i, _vp, _i, _i, _d, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _vp]),
-    "gm_net_forward_geo": (_i, [C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _f, _f,
+    "gm_net_forward_geo": (_i, [C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _f, _f,
                                 _vp, _sz, _vp, _vp, _vp]),
     "gm_net_backward_geo": (_i, [C.POINTER(GmParams), C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _i, _i, _vp,
                                  _i, _i, _i, _vp, _sz, _vp, _sz, _vp, _vp, _vp]),
-    "gm_edgeconv_forward_geo": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp, _sz, _vp, _vp, _vp]),
+    "gm_edgeconv_forward_geo": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _i, _vp, _sz, _vp, _vp, _vp]),
     "gm_met_loss": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "gm_segment_sum": (_i, [_vp, _vp, _i, _vp, _vp]),
     "gm_scatter_add": (_i, [_vp, _vp, _ll, _vp, _ll, _vp]),

@@ -12,13 +12,11 @@
 //   k_geo_aggr          : out_i = P_i + max_{j in N(i)} Y_j  (+ arg-max, + BatchNorm moments)              [a5 fwd]
 //   k_geo_scatter       : S_j = sum_{i : arg(i,c) == j} d conv_i[c], BatchNorm backward on the fly          [a5 bwd]
 // All reductions run in a fixed order (internal node order): bit-deterministic, no float atomics.
-#include "geo_layout.cuh"
-#include "net_layout.cuh"
+#include "geo_stage.cuh"
 
 namespace gm {
 namespace {
 
-constexpr int GEO_TPI = 32;          // nodes per work item (one warp-width of consecutive internal nodes)
 #ifndef GEO_SC_THREADS
 #define GEO_SC_THREADS 128
 #endif
@@ -31,48 +29,8 @@ constexpr int AG_CONSUMERS = 8;      // forward kernel: 8 consumer warps (AG_TPW
 constexpr int AG_THREADS = (AG_CONSUMERS + 1) * 32;   // ... + 1 producer warp (segments, descriptors, TMA)
 constexpr int AG_TPW = GEO_TPI / AG_CONSUMERS;
 constexpr int AG_CH = 224;           // staged neighbourhood rows per pipeline stage (2 stages x 3 CTAs fit one SM)
-constexpr int AG_STAGES = 2;
 constexpr int AG_LIST = AG_CH + 8;   // per-warp hit list (uint32 byte offsets of staged rows), padded by 8 identity entries
-constexpr unsigned GEO_SPIN_LIMIT = 1u << 20;
-
-// ------------------------------------------------------------------------------------------ PTX: mbarrier + TMA bulk copy
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-// potentially blocking: the thread is suspended in hardware until the phase completes or ~hint_ns elapse, so waiting
-// warps do not compete for issue slots with the warps that still work
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(bar), "r"(parity), "r"(hint_ns) : "memory");
-    return ok != 0;
-}
-// bounded (a bug must trap, not hang); failed polls back off with nanosleep so that waiting warps do not take issue
-// slots from the warps that still work (ncu: 14 % of the executed instructions were try_wait polls without it)
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigned sleep_ns = 128) {
-    if (mbar_try_wait(bar, parity, 1000u)) return;
-#pragma unroll 1
-    for (unsigned it = 0; it < GEO_SPIN_LIMIT; ++it) {
-        __nanosleep(sleep_ns);
-        if (mbar_try_wait(bar, parity, 1000u)) return;
-    }
-    __trap();
-}
-// global -> shared bulk copy through the TMA unit; bytes % 16 == 0, both addresses 16-byte aligned
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
+using AgStage = StageL<AG_CH, false>;
 
 // ------------------------------------------------------------------------------------------ build
 __global__ void k_geo_meta(GeoMeta *m, float r, float r2, int dim, int phi_wrap, int loop, int cap_eff, int N, int B,
@@ -223,35 +181,11 @@ struct SegStage {
     int voff[7];       // first virtual row of run q; voff[nr] = C
 };
 
-struct GeoView {       // device pointers of a built GeoWs (passed by value)
-    const GeoMeta *meta;
-    const int *bbox, *cell_start, *ptr, *thr;
-    const float4 *pts;
-    int *sched;        // [0..1] dynamic-schedule ticket + finished-CTA count (self-resetting; zeroed by gm_geo_build)
-};
-
-// forward kernel: [stage]{ (AG_CH + 1) rows x 128 B (last row: identity), AG_CH points x 16 B, the item's 32 target
-// points x 16 B, their 32 cap thresholds, the chunk descriptor }
-struct ChunkDesc {     // written by the producer into the stage it fills, read by the consumers after the full barrier
-    int flags;         // AG_FIRST / AG_LAST chunk of a segment, AG_END of the CTA's work
-    int n0;            // first node of the item
-    int a, b;          // targets [a, b) of the item form the segment
-    int rows;          // staged rows of this chunk
-    int vbase;         // virtual row of staged row 0
-    int nr;            // runs of the segment's neighbourhood
-    int rlo[6];        // first internal node of run q
-    int voff[7];       // first virtual row of run q; voff[nr] = C
-};
-constexpr int AG_FIRST = 1, AG_LAST = 2, AG_END = 4;
-constexpr size_t AG_OFF_PTS = (size_t)(AG_CH + 1) * 128;                   // inside a stage
-constexpr size_t AG_OFF_TGT = AG_OFF_PTS + (size_t)AG_CH * 16;
-constexpr size_t AG_OFF_THR = AG_OFF_TGT + (size_t)GEO_TPI * 16;
-constexpr size_t AG_OFF_DESC = AG_OFF_THR + (size_t)GEO_TPI * 4;
-constexpr size_t AG_STAGE_BYTES = AG_OFF_DESC + 128;
+constexpr size_t AG_OFF_PTS = AgStage::OFF_PTS, AG_OFF_TGT = AgStage::OFF_TGT, AG_OFF_THR = AgStage::OFF_THR;
+constexpr size_t AG_OFF_DESC = AgStage::OFF_DESC, AG_STAGE_BYTES = AgStage::BYTES;
 constexpr size_t AG_LISTS = AG_STAGES * AG_STAGE_BYTES;                    // AG_CONSUMERS x AG_LIST x u32
 constexpr size_t AG_BAR = AG_LISTS + (size_t)AG_CONSUMERS * AG_LIST * 4;   // full[AG_STAGES], empty[AG_STAGES]
 constexpr size_t AG_TOTAL = AG_BAR + 16 * AG_STAGES;
-static_assert(sizeof(ChunkDesc) <= 128, "descriptor slot");
 static_assert(AG_STAGE_BYTES % 128 == 0 && AG_LISTS % 8 == 0 && (AG_LIST * 4) % 16 == 0 && AG_LISTS % 16 == 0 && AG_BAR % 8 == 0, "staging alignment");
 static_assert(AG_STAGES * AG_STAGE_BYTES >= (size_t)(AG_THREADS / 8) * 3 * H * 4, "BatchNorm scratch aliases the stages");
 
@@ -288,43 +222,6 @@ __device__ __forceinline__ void segment_runs(const GeoView &v, const CellGrid &g
     seg->nr = n;
 }
 
-__device__ __forceinline__ int node_of_row(const ChunkDesc *d, int row) {
-    const int vr = d->vbase + row;
-    int q = 0;
-    while (q + 1 < d->nr && vr >= d->voff[q + 1]) ++q;
-    return d->rlo[q] + (vr - d->voff[q]);
-}
-
-// Hit list of one target against the staged chunk: BYTE OFFSETS (row * 128) of the rows whose point passes the edge
-// predicate of geo_layout.cuh, in staged order, padded with 8 x the identity row.  th = cap threshold of the target,
-// excl = local index to exclude (the target itself when loop == 0, -1 otherwise).  Returns the hit count.
-__device__ __forceinline__ int build_hit_list(const float4 *s_pts, int rows, float px, float py, int th, int excl,
-                                              const GeoMeta &m, int lane, unsigned *list) {
-    int nh = 0;
-    const unsigned lt = (1u << lane) - 1u;
-    // 128 candidates per trip, their 4 point loads issued up front: the list stores below may alias the points as
-    // far as the compiler knows, so it cannot hoist the next load over them itself.  Reads past `rows` stay inside
-    // the stage (AG_CH + 32 <= points + target area) and are masked by c < rows.
-    for (int base = 0; base < rows; base += 128) {
-        float4 q[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) q[u] = s_pts[base + 32 * u + lane];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int c = base + 32 * u + lane;
-            const int cl = __float_as_int(q[u].z);
-            const bool hit = (dist2(px, py, q[u].x, q[u].y, m.dim, m.phi_wrap) < m.r2) & (cl <= th) & (cl != excl) & (c < rows);
-            const unsigned mk = __ballot_sync(0xffffffffu, hit);
-            unsigned *slot = list + nh + __popc(mk & lt);   // address formed unconditionally => predicated store
-            if (hit) *slot = (unsigned)c << 7;
-            nh += __popc(mk);
-        }
-    }
-    if (lane < 8) list[nh + lane] = (unsigned)AG_CH << 7;
-    __syncwarp();
-    return nh;
-}
-
 // One target against one staged chunk: hit list, then lane = channel walks the list 4 rows at a time out of shared
 // memory.  The caller must NOT unroll its target loop around this body: the consumer warps run decoupled, and four
 // copies (one per target slot) thrash the instruction cache (ncu: stall_no_instruction 0.2 -> 3.7 per issue); a
@@ -339,7 +236,7 @@ __device__ __forceinline__ TargetResult aggr_target(const float4 *s_pts, const f
                                                  unsigned *list) {
     GeoMeta m;
     m.r2 = r2; m.dim = dim; m.phi_wrap = phi_wrap;
-    const int nh = build_hit_list(s_pts, rows, px, py, th, excl, m, lane, list);
+    const int nh = build_hit_list<AG_CH>(s_pts, rows, px, py, th, excl, m, lane, list);
     const uint32_t col = smem_u32(s_rows + lane);                          // this lane's channel of staged row 0
     auto lds = [](uint32_t a) { float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; };
     unsigned boff = 0xffffffffu;                                           // byte offset of the arg-max row
@@ -402,78 +299,7 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
     float cnt = 0.f, shift = 0.f, s1 = 0.f, s2 = 0.f;      // BatchNorm moments of this warp's outputs (lane = channel)
     if (warp == AG_CONSUMERS) {
         // ================================================================== producer
-        const CellGrid g = make_grid(v.bbox, m.r, m.dim, m.phi_wrap);
-        const int n_items = (N + GEO_TPI - 1) / GEO_TPI;
-        uint32_t gc = 0;                                    // chunks issued so far; chunk gc lives in stage gc & 1
-        int item = blockIdx.x;
-        for (;;) {
-            if (dynamic) {
-                if (lane == 0) item = atomicAdd(v.sched, 1);
-                item = __shfl_sync(0xffffffffu, item, 0);
-            }
-            if (item >= n_items) break;
-            const int n0 = item * GEO_TPI, icnt = min(GEO_TPI, N - n0);
-            const bool valid = lane < icnt;
-            const int e = valid ? find_event(v.ptr, m.B, n0 + lane) : -1;
-            const int cell = valid ? __float_as_int(__ldg(&v.pts[n0 + lane].w)) : 0;
-            const int key = valid ? ((e << 5) | (cell / g.g1)) : -1;
-            const int prev = __shfl_up_sync(0xffffffffu, key, 1);
-            unsigned heads = __ballot_sync(0xffffffffu, valid && (lane == 0 || key != prev));
-            while (heads) {
-                const int a = __ffs(heads) - 1;
-                heads &= heads - 1;
-                const int b = heads ? __ffs(heads) - 1 : icnt;
-                const int ev = __shfl_sync(0xffffffffu, e, a);
-                const int ca = __shfl_sync(0xffffffffu, cell, a), cb = __shfl_sync(0xffffffffu, cell, b - 1);
-                const int ce = ca / g.g1;
-                int rlo[6], rhi[6], voff[7];                // every lane computes the (uniform) runs: broadcast loads
-                const int nr0 = nbhd_runs(g, v.cell_start + (size_t)ev * (CMAX + 1), ce, ca - ce * g.g1, cb - ce * g.g1,
-                                          m.phi_wrap, rlo, rhi);
-                int nr = 0, C = 0;
-#pragma unroll
-                for (int q = 0; q < 6; ++q)
-                    if (q < nr0 && rhi[q] > rlo[q]) { rlo[nr] = rlo[q]; voff[nr] = C; C += rhi[q] - rlo[q]; ++nr; }
-                voff[nr] = C;
-                const int nck = (C + AG_CH - 1) / AG_CH;
-                const int crow = min(AG_CH, (((C + nck - 1) / nck) + 31) & ~31);    // even split, multiple of 32
-                for (int k = 0; k < nck; ++k, ++gc) {
-                    const int st = gc & 1;
-                    mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u, 400);        // stage consumed (or never used)
-                    if (lane == 0) {
-                        unsigned char *stage = gs + st * AG_STAGE_BYTES;
-                        const uint32_t s_stage = smem_u32(stage), bar = full0 + 8u * st;
-                        const int c0 = k * crow, c1 = min(C, c0 + crow);
-                        ChunkDesc *d = reinterpret_cast<ChunkDesc *>(stage + AG_OFF_DESC);
-                        d->flags = (k == 0 ? AG_FIRST : 0) | (k == nck - 1 ? AG_LAST : 0);
-                        d->n0 = n0; d->a = a; d->b = b; d->rows = c1 - c0; d->vbase = c0; d->nr = nr;
-#pragma unroll
-                        for (int q = 0; q < 6; ++q) { d->rlo[q] = rlo[q]; d->voff[q] = voff[q]; }
-                        d->voff[6] = voff[6];
-                        mbar_expect_tx(bar, (uint32_t)(c1 - c0) * (128u + 16u) + (uint32_t)icnt * 16u + 128u);
-                        bulk_g2s(s_stage + (uint32_t)AG_OFF_TGT, v.pts + n0, (uint32_t)icnt * 16u, bar);
-                        bulk_g2s(s_stage + (uint32_t)AG_OFF_THR, v.thr + n0, 128u, bar);
-#pragma unroll
-                        for (int q = 0; q < 6; ++q) {
-                            if (q >= nr) break;
-                            const int lo = max(voff[q], c0), hi = min(voff[q + 1], c1);
-                            if (lo >= hi) continue;
-                            const size_t node = (size_t)(rlo[q] + (lo - voff[q]));
-                            const uint32_t n = (uint32_t)(hi - lo), row = (uint32_t)(lo - c0);
-                            bulk_g2s(s_stage + (uint32_t)AG_OFF_PTS + row * 16u, v.pts + node, n * 16u, bar);
-                            bulk_g2s(s_stage + row * 128u, Y + node * H, n * 128u, bar);
-                        }
-                    }
-                    __syncwarp();
-                }
-            }
-            item += gridDim.x;
-        }
-        const int st = gc & 1;                              // end-of-work descriptor (no copies)
-        mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u);
-        if (lane == 0) {
-            reinterpret_cast<ChunkDesc *>(gs + st * AG_STAGE_BYTES + AG_OFF_DESC)->flags = AG_END;
-            mbar_arrive(full0 + 8u * st);
-        }
+        geo_produce<AgStage, false>(gs, full0, empty0, v, m, Y, N, dynamic, lane);
     } else {
         // ================================================================== consumers
         unsigned *list = reinterpret_cast<unsigned *>(gs + AG_LISTS) + warp * AG_LIST;
@@ -740,12 +566,6 @@ __global__ void __launch_bounds__(RM_THREADS) k_row_moments(const float *__restr
     }
     if (last_cta_done(tail.counter))
         bn_finalize_cta(tail.partials, gridDim.x, tail.bn, tail.momentum, tail.eps, tail.stat, s_red);
-}
-
-GeoView view_of(const void *geo_ws, int N, int B) {
-    GeoWs w;
-    geo_ws_layout(N, B, (char *)geo_ws, &w);
-    return GeoView{w.meta, w.bbox, w.cell_start, w.ptr, w.thr, w.pts, w.sched};
 }
 
 // ------------------------------------------------------------------------------------------ launchers

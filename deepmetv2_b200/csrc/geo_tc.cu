@@ -1,0 +1,337 @@
+// a5 as a REAL per-edge contraction on the 5th-generation tensor cores, fed from the cell-staged IMPLICIT radius graph
+// (model/graph_met_network.py:34-39,65; PyG EdgeConv: out_i = aggr_j W [x_i ; x_j - x_i] + b).
+//
+//   out_i[c] = P_i[c] + aggr_{j in N(i)} sum_k W2[c,k] * round(x_j[k] - x_i[k])      P = W1 x + b (fp32, node side)
+//
+// Same staging as k_geo_aggr (geo.cu): a producer warp streams the cell neighbourhood of every 32-node work item
+// (points + x rows) through a 2-stage shared-memory ring with TMA bulk copies; no edge list exists.  The consumer
+// warps differ: each one runs ITS OWN tcgen05 pipeline, with no cross-warp synchronisation at all --
+//   * per (target, chunk) it builds the hit list of the edge predicate, then 8 lanes per edge read the staged x_j
+//     row (LDS.128), subtract x_i in fp32, round to bf16 / tf32 and append the row to the warp's private K-major
+//     operand block (32 edge columns, double-buffered);
+//   * the hits of a (target, chunk) are padded to a multiple of 8 columns (max: the last hit again; add / mean: a zero
+//     row), so slot runs start on 8-column groups; when 32 columns are full (blocks run across targets and chunks; a
+//     partial block is flushed at the end of a segment) one lane issues tcgen05.mma  D[128 x 32] = W2r[128 x 32] * block^T  (W2 replicated 4x along M so that
+//     every TMEM lane quarter holds all 32 channels) into the warp's 32 TMEM columns and commits to the warp's
+//     mbarrier; the MMA runs while the warp fills the next block;
+//   * before the next MMA the warp reads its lane quarter back (tcgen05.ld 32x32b.x32: lane = channel, register =
+//     edge column) and folds each 8-column group into the accumulator of the target slot that owns it, in a fixed
+//     order -- no atomics, bit-deterministic.
+// Tensor work per edge: 2*128*32 flop issued for 2*64*32 useful (W2 replication); the pipe needs ~1 clk per edge per
+// SM, TMEM read-back ~2 clk, so the kernel is bound by the shared-memory / issue work of building operand rows.
+#include "geo_stage.cuh"
+#include "tc_ptx.cuh"
+
+namespace gm {
+namespace {
+
+constexpr int GT_CONSUMERS = 4;                       // consumer warps = TMEM lane quarters
+constexpr int GT_THREADS = (GT_CONSUMERS + 1) * 32;   // + 1 producer warp
+constexpr int GT_TPW = GEO_TPI / GT_CONSUMERS;        // target slots per warp and item
+#ifndef GT_CH
+#define GT_CH 160                                     // staged neighbourhood rows per pipeline stage
+#endif
+constexpr int GT_LIST = GT_CH + 8;
+constexpr int GT_BLK = 32;                            // edge columns per MMA block (MMA N)
+constexpr int GT_LBO = 192;                           // bytes between the 16-byte K chunks of an 8-row group: 4 rows x
+                                                      // (4 | 8) chunks of a warp store land on distinct banks
+constexpr int GT_TMEM_COLS = 128;                     // GT_CONSUMERS x GT_BLK
+using GtStage = StageL<GT_CH, true>;
+static_assert(GT_CONSUMERS * GT_BLK == GT_TMEM_COLS && GT_TPW <= 8, "TMEM columns / slot count");
+
+template <int PREC> struct GtCfg;
+template <> struct GtCfg<GM_PREC_TF32> { static constexpr int CHUNKS = 8, KSTEPS = 4, FMT = 2; };   // 4 tf32 per chunk
+template <> struct GtCfg<GM_PREC_BF16> { static constexpr int CHUNKS = 4, KSTEPS = 2, FMT = 1; };   // 8 bf16 per chunk
+
+template <int PREC>
+struct GtSmem {
+    static constexpr int SBO = GtCfg<PREC>::CHUNKS * GT_LBO;          // stride of an 8-row group
+    static constexpr int A_BYTES = (128 / 8) * SBO;
+    static constexpr int B_BYTES = (GT_BLK / 8) * SBO;                // one operand block
+    static constexpr size_t OFF_LISTS = (size_t)AG_STAGES * GtStage::BYTES;
+    static constexpr size_t OFF_A = OFF_LISTS + (size_t)GT_CONSUMERS * GT_LIST * 4;
+    static constexpr size_t OFF_B = OFF_A + A_BYTES;                                   // [warp][2] blocks
+    static constexpr size_t OFF_XI = OFF_B + (size_t)GT_CONSUMERS * 2 * B_BYTES;       // [warp][slot][32] f32: x_i
+    static constexpr size_t OFF_ACC = OFF_XI + (size_t)GT_CONSUMERS * GT_TPW * 128;    // [warp][slot][32] f32
+    static constexpr size_t OFF_SLOT = OFF_ACC + (size_t)GT_CONSUMERS * GT_TPW * 128;  // [warp][slot] (eta, phi, thr, excl)
+    static constexpr size_t OFF_DEG = OFF_SLOT + (size_t)GT_CONSUMERS * GT_TPW * 16;   // [warp][slot] i32
+    static constexpr size_t OFF_GSLOT = OFF_DEG + (size_t)GT_CONSUMERS * GT_TPW * 4;   // [warp][2][4] u8: slot of a group
+    static constexpr size_t OFF_BAR = (OFF_GSLOT + (size_t)GT_CONSUMERS * 8 + 7) / 8 * 8;     // full[2] empty[2] mma[warp]
+    static constexpr size_t OFF_TMEM = OFF_BAR + (size_t)(2 * AG_STAGES + GT_CONSUMERS) * 8;
+    static constexpr size_t TOTAL = OFF_TMEM + 16;
+    static_assert(OFF_A % 128 == 0 && OFF_B % 16 == 0 && OFF_XI % 16 == 0 && OFF_SLOT % 16 == 0, "operand alignment");
+};
+
+// K-major, no-swizzle operand layout: 8-row x 16-byte core matrices; chunk stride LBO, 8-row group stride SBO
+template <int PREC>
+__device__ __forceinline__ uint64_t gt_smem_desc(uint32_t addr) {
+    uint64_t d = (uint64_t)((addr >> 4) & 0x3FFF);
+    d |= (uint64_t)(GT_LBO >> 4) << 16;
+    d |= (uint64_t)(GtSmem<PREC>::SBO >> 4) << 32;
+    d |= 1ull << 46;                          // descriptor version (sm_100)
+    return d;                                 // layout_type = 0 (SWIZZLE_NONE), base_offset = 0
+}
+template <int PREC>
+__device__ __forceinline__ uint32_t gt_instr_desc(int n) {
+    return (1u << 4) | ((uint32_t)GtCfg<PREC>::FMT << 7) | ((uint32_t)GtCfg<PREC>::FMT << 10) |
+           ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);   // F32 accum, K-major A and B, M = 128
+}
+__device__ __forceinline__ void gt_sts64(uint32_t addr, uint32_t a, uint32_t b) {
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ void gt_sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+template <int PREC, int AGGR>
+__global__ void __launch_bounds__(GT_THREADS, 2)
+k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, const float *__restrict__ W, GeoView v,
+                  int N, float *__restrict__ out) {
+    using S = GtSmem<PREC>;
+    using C = GtCfg<PREC>;
+    constexpr bool TF32 = PREC == GM_PREC_TF32;
+    extern __shared__ __align__(128) unsigned char gs[];
+    const uint32_t full0 = smem_u32(gs + S::OFF_BAR), empty0 = full0 + 8u * AG_STAGES, mma0 = empty0 + 8u * AG_STAGES;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const GeoMeta m = *v.meta;
+    const float IDENT = AGGR == GM_AGGR_MAX ? -INFINITY : 0.f;
+
+    // ---- one-time setup: barriers, TMEM, the A operand (W2 replicated 4x along M, rounded to the MMA input type)
+    if (tid == 0) {
+        for (int s = 0; s < AG_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, GT_CONSUMERS); }
+        for (int w = 0; w < GT_CONSUMERS; ++w) mbar_init(mma0 + 8u * w, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tc5_alloc(smem_u32(gs + S::OFF_TMEM), GT_TMEM_COLS);
+    const uint32_t a_base = smem_u32(gs + S::OFF_A);
+    for (int t = tid; t < 128 * C::CHUNKS; t += GT_THREADS) {
+        const int row = t / C::CHUNKS, c = t - row * C::CHUNKS;
+        const float *wrow = W + (row & 31) * CONV_IN + H;
+        const uint32_t addr = a_base + (uint32_t)((row >> 3) * S::SBO + c * GT_LBO + (row & 7) * 16);
+        if constexpr (TF32) {
+            const float4 w0 = *reinterpret_cast<const float4 *>(wrow + 4 * c);
+            gt_sts128(addr, tc5_to_tf32(w0.x), tc5_to_tf32(w0.y), tc5_to_tf32(w0.z), tc5_to_tf32(w0.w));
+        } else {
+            const float4 w0 = *reinterpret_cast<const float4 *>(wrow + 8 * c);
+            const float4 w1 = *reinterpret_cast<const float4 *>(wrow + 8 * c + 4);
+            gt_sts128(addr, tc5_pack_bf16(w0.x, w0.y), tc5_pack_bf16(w0.z, w0.w), tc5_pack_bf16(w1.x, w1.y),
+                      tc5_pack_bf16(w1.z, w1.w));
+        }
+    }
+    tc5_fence_async_smem();
+    tc5_fence_before();
+    __syncthreads();
+    tc5_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<const uint32_t *>(gs + S::OFF_TMEM);
+
+    if (warp == GT_CONSUMERS) {
+        // ================================================================== producer (tickets: no BatchNorm partials here)
+        geo_produce<GtStage, true>(gs, full0, empty0, v, m, X, N, true, lane);
+    } else {
+        // ================================================================== consumers
+        const int w = warp;
+        unsigned *list = reinterpret_cast<unsigned *>(gs + S::OFF_LISTS) + w * GT_LIST;
+        float *s_xi = reinterpret_cast<float *>(gs + S::OFF_XI) + w * GT_TPW * 32;
+        float *s_acc = reinterpret_cast<float *>(gs + S::OFF_ACC) + w * GT_TPW * 32;
+        float4 *s_slot = reinterpret_cast<float4 *>(gs + S::OFF_SLOT) + w * GT_TPW;
+        int *s_deg = reinterpret_cast<int *>(gs + S::OFF_DEG) + w * GT_TPW;
+        unsigned char *s_gslot = gs + S::OFF_GSLOT + w * 8;
+        const uint32_t b_base = smem_u32(gs + S::OFF_B) + (uint32_t)(w * 2 * S::B_BYTES);
+        const uint32_t mbar = mma0 + 8u * w;
+        const uint32_t d_tmem = tmem_base + (uint32_t)(w * GT_BLK);                 // all 128 lanes, this warp's columns
+        const uint32_t ld_tmem = d_tmem + ((uint32_t)((w & 3) * 32) << 16);         // this warp's lane quarter
+        const uint32_t idesc = gt_instr_desc<PREC>(GT_BLK);
+        const int r4 = lane >> 3, c4 = lane & 7;                                    // 8 lanes per edge row, 4 channels per lane
+        const uint32_t lane_off = TF32 ? (uint32_t)(c4 * GT_LBO) : (uint32_t)((c4 >> 1) * GT_LBO + (c4 & 1) * 8);
+        int fill = 0, buf = 0, pending = -1, nv_pending = 0;
+        uint32_t mma_parity = 0;
+
+        // read the finished block back (lane = channel, register = edge column) and fold its columns into the slots
+        auto epilogue = [&]() {
+            mbar_wait(mbar, mma_parity, 32);
+            mma_parity ^= 1u;
+            tc5_fence_after();
+            uint32_t r[32];
+            tc5_ld32(ld_tmem, r);
+            const unsigned slots = *reinterpret_cast<const unsigned *>(s_gslot + pending * 4);
+#pragma unroll
+            for (int g = 0; g < GT_BLK / 8; ++g) {
+                if (g * 8 < nv_pending) {                                           // warp-uniform
+                    float t[8];
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) t[c] = __uint_as_float(r[8 * g + c]);
+                    const float red = AGGR == GM_AGGR_MAX
+                        ? fmaxf(fmaxf(fmaxf(t[0], t[1]), fmaxf(t[2], t[3])), fmaxf(fmaxf(t[4], t[5]), fmaxf(t[6], t[7])))
+                        : ((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]));
+                    float *dst = s_acc + (int)((slots >> (8 * g)) & 0xffu) * 32 + lane;
+                    *dst = AGGR == GM_AGGR_MAX ? fmaxf(*dst, red) : *dst + red;
+                }
+            }
+            tc5_fence_before();
+            pending = -1;
+        };
+        // hand the current block (columns 0..fill-1 valid) to the tensor core
+        auto flush = [&]() {
+            if (pending >= 0) epilogue();                                           // frees the warp's TMEM columns
+            tc5_fence_async_smem();                                                 // operand stores -> async proxy
+            __syncwarp();
+            if (lane == 0) {
+                tc5_fence_after();
+                const uint32_t bs = b_base + (uint32_t)(buf * S::B_BYTES);
+#pragma unroll
+                for (int ks = 0; ks < C::KSTEPS; ++ks)
+                    tc5_mma<TF32>(d_tmem, gt_smem_desc<PREC>(a_base + ks * 2 * GT_LBO),
+                                  gt_smem_desc<PREC>(bs + ks * 2 * GT_LBO), idesc, ks > 0 ? 1u : 0u);
+                tc5_commit(mbar);
+            }
+            __syncwarp();
+            pending = buf; nv_pending = fill; buf ^= 1; fill = 0;
+        };
+
+        for (uint32_t gc = 0;; ++gc) {
+            const int st = gc & 1;
+            const unsigned char *stage = gs + st * GtStage::BYTES;
+            mbar_wait(full0 + 8u * st, (gc >> 1) & 1u);
+            const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + GtStage::OFF_DESC);
+            const int flags = d->flags;
+            if (flags & AG_END) break;
+            const int a = d->a, b = d->b, rows = d->rows, n0 = d->n0;
+            const float4 *s_pts = reinterpret_cast<const float4 *>(stage + GtStage::OFF_PTS);
+            if (flags & AG_FIRST) {
+                const float4 *s_tgt = reinterpret_cast<const float4 *>(stage + GtStage::OFF_TGT);
+                const int *s_thr = reinterpret_cast<const int *>(stage + GtStage::OFF_THR);
+                const float *s_trows = reinterpret_cast<const float *>(stage + GtStage::OFF_TROWS);
+                if (lane < GT_TPW) {
+                    const int t = a + w + lane * GT_CONSUMERS;
+                    if (t < b) {
+                        const float4 pt = s_tgt[t];
+                        s_slot[lane] = make_float4(pt.x, pt.y, __int_as_float(s_thr[t]), m.loop ? __int_as_float(-1) : pt.z);
+                        s_deg[lane] = 0;
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < GT_TPW; ++u) {
+                    const int t = a + w + u * GT_CONSUMERS;
+                    s_acc[u * 32 + lane] = IDENT;
+                    if (t < b) s_xi[u * 32 + lane] = s_trows[t * 32 + lane];
+                }
+                __syncwarp();
+            }
+#pragma unroll 1
+            for (int u = 0; u < GT_TPW; ++u) {
+                if (a + w + u * GT_CONSUMERS >= b) break;                           // warp-uniform
+                const float4 sl = s_slot[u];
+                const int nh = build_hit_list<GT_CH>(s_pts, rows, sl.x, sl.y, __float_as_int(sl.z), __float_as_int(sl.w),
+                                                     m, lane, list);
+                if (lane == 0) s_deg[u] += nh;
+                const float4 xi = *reinterpret_cast<const float4 *>(s_xi + u * 32 + c4 * 4);
+                const int np = (nh + 7) & ~7;                                       // padded to whole 8-column groups
+                int k = 0;
+                while (k < np) {                                                    // warp-uniform
+                    const int n = min(np - k, GT_BLK - fill);                       // a multiple of 8
+                    if (lane < (n >> 3)) s_gslot[buf * 4 + (fill >> 3) + lane] = (unsigned char)u;
+                    const uint32_t bs = b_base + (uint32_t)(buf * S::B_BYTES) + lane_off;
+                    for (int j = r4; j < n; j += 4) {
+                        const int h = k + j;
+                        float4 dv = make_float4(0.f, 0.f, 0.f, 0.f);                // add / mean padding: a zero row
+                        if (AGGR == GM_AGGR_MAX || h < nh) {                        // max padding: the last hit again
+                            const unsigned off = list[min(h, nh - 1)];
+                            const float4 xj = *reinterpret_cast<const float4 *>(stage + off + c4 * 16);
+                            dv = make_float4(xj.x - xi.x, xj.y - xi.y, xj.z - xi.z, xj.w - xi.w);
+                        }
+                        const int col = fill + j;
+                        const uint32_t addr = bs + (uint32_t)((col >> 3) * S::SBO + (col & 7) * 16);
+                        if constexpr (TF32)
+                            gt_sts128(addr, tc5_to_tf32(dv.x), tc5_to_tf32(dv.y), tc5_to_tf32(dv.z), tc5_to_tf32(dv.w));
+                        else
+                            gt_sts64(addr, tc5_pack_bf16(dv.x, dv.y), tc5_pack_bf16(dv.z, dv.w));
+                    }
+                    fill += n; k += n;
+                    if (fill == GT_BLK) flush();
+                }
+                __syncwarp();                                   // the hit list is reused by the next target
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty0 + 8u * st);       // this warp is done with the stage
+            if (flags & AG_LAST) {
+                float p[GT_TPW];
+#pragma unroll
+                for (int u = 0; u < GT_TPW; ++u) {
+                    const int t = a + w + u * GT_CONSUMERS;
+                    p[u] = t < b ? __ldg(P + (size_t)(n0 + t) * H + lane) : 0.f;
+                }
+                if (fill > 0) flush();
+                if (pending >= 0) epilogue();
+                __syncwarp();
+#pragma unroll
+                for (int u = 0; u < GT_TPW; ++u) {
+                    const int t = a + w + u * GT_CONSUMERS;
+                    if (t >= b) continue;
+                    const int deg = s_deg[u];
+                    const float acc = s_acc[u * 32 + lane];
+                    float o;
+                    if (deg == 0) o = 0.f;                                          // PyG: empty rows aggregate to 0
+                    else if (AGGR == GM_AGGR_MAX) o = p[u] + acc;
+                    else if (AGGR == GM_AGGR_ADD) o = fmaf((float)deg, p[u], acc);
+                    else o = fmaf(acc, 1.f / (float)deg, p[u]);
+                    out[(size_t)(n0 + t) * H + lane] = o;
+                }
+                __syncwarp();
+            }
+        }
+    }
+
+    // ---- teardown: TMEM back, last CTA out re-arms the ticket counter
+    tc5_fence_before();
+    __syncthreads();
+    tc5_fence_after();
+    if (warp == 0) tc5_dealloc(tmem_base, GT_TMEM_COLS);
+    if (tid == 0) {
+        __threadfence();
+        if (atomicAdd(v.sched + 1, 1) == (int)gridDim.x - 1) { v.sched[0] = 0; v.sched[1] = 0; __threadfence(); }
+    }
+}
+
+template <int PREC, int AGGR>
+int launch_geo_tc(const float *X, const float *P, const float *W, const GeoView &v, int N, float *out, cudaStream_t st) {
+    static int occ = 0;
+    if (!occ) {
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_edgeconv_tc<PREC, AGGR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)GtSmem<PREC>::TOTAL));
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_edgeconv_tc<PREC, AGGR>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                         (int)cudaSharedmemCarveoutMaxShared));
+        occ = min(resident_ctas(k_geo_edgeconv_tc<PREC, AGGR>, GT_THREADS, GtSmem<PREC>::TOTAL, 1), 512 / GT_TMEM_COLS);
+        // work is taken from a ticket counter, so a CTA that is not resident at once only finds the queue empty:
+        // size the grid by what shared memory allows even if the occupancy query is pessimistic
+        occ = max(occ, min((int)(227 * 1024 / (GtSmem<PREC>::TOTAL + 1024)), 512 / GT_TMEM_COLS));
+    }
+    const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, occ);
+    k_geo_edgeconv_tc<PREC, AGGR><<<grid, GT_THREADS, GtSmem<PREC>::TOTAL, st>>>(X, P, W, v, N, out);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+template <int PREC>
+int dispatch_geo_tc(int aggr, const float *X, const float *P, const float *W, const GeoView &v, int N, float *out,
+                    cudaStream_t st) {
+    switch (aggr) {
+        case GM_AGGR_MAX: return launch_geo_tc<PREC, GM_AGGR_MAX>(X, P, W, v, N, out, st);
+        case GM_AGGR_ADD: return launch_geo_tc<PREC, GM_AGGR_ADD>(X, P, W, v, N, out, st);
+        case GM_AGGR_MEAN: return launch_geo_tc<PREC, GM_AGGR_MEAN>(X, P, W, v, N, out, st);
+    }
+    return GM_ERR_INVALID_ARGUMENT;
+}
+
+}  // namespace
+
+// X: layer input [N,32] in internal order; P = W1 x + b [N,32]; W: the EdgeConv weight [32,64] (W2 = columns 32..63)
+int geo_edgeconv_tc(int aggr, int precision, const float *X, const float *P, const float *W, const void *geo_ws, int N,
+                    int B, float *out, cudaStream_t st) {
+    if (!geo_ws || B < 1) return GM_ERR_INVALID_ARGUMENT;
+    const GeoView v = view_of(geo_ws, N, B);
+    if (precision == GM_PREC_TF32) return dispatch_geo_tc<GM_PREC_TF32>(aggr, X, P, W, v, N, out, st);
+    if (precision == GM_PREC_BF16) return dispatch_geo_tc<GM_PREC_BF16>(aggr, X, P, W, v, N, out, st);
+    return GM_ERR_UNSUPPORTED;
+}
+
+}  // namespace gm

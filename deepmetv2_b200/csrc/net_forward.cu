@@ -417,7 +417,8 @@ constexpr int NP_THREADS = 256;
 __global__ void __launch_bounds__(NP_THREADS, 4)
 k_node_prep2(const float *__restrict__ raw, const float *__restrict__ resid, const float *__restrict__ stat,
              const float *__restrict__ W, const float *__restrict__ bias, int N, float *__restrict__ emb_out,
-             float *__restrict__ Y, float *__restrict__ P) {
+             float *__restrict__ Y, float *__restrict__ P, int direct = 0) {
+    // direct != 0 (per-edge tcgen05 path, geo_tc.cu): P = W1 x + b and no Y (pass Y == NULL)
     __shared__ __align__(16) float s_wdT[H * H];    // (W1 - W2)^T : [k][c]
     __shared__ __align__(16) float s_w2T[H * H];    // W2^T
     __shared__ __align__(16) float s_b[H];
@@ -427,7 +428,7 @@ k_node_prep2(const float *__restrict__ raw, const float *__restrict__ resid, con
     for (int i = t; i < H * H; i += NP_THREADS) {
         const int k = i >> 5, c = i & 31;
         const float w1 = W[c * CONV_IN + k], w2 = W[c * CONV_IN + H + k];
-        s_wdT[i] = w1 - w2; s_w2T[i] = w2;
+        s_wdT[i] = direct ? w1 : w1 - w2; s_w2T[i] = w2;
     }
     if (t < H) s_b[t] = bias[t];
     if (stat && t < BNSTAT_STRIDE) s_stat[t] = stat[t];
@@ -456,14 +457,16 @@ k_node_prep2(const float *__restrict__ raw, const float *__restrict__ resid, con
         }
         __syncthreads();
         float acc[4][4];
+        if (Y) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; acc[i][2] = 0.f; acc[i][3] = 0.f; }
-        tile_gemm<H, H, TILE_LD>(s_x, s_w2T, ng, og, acc);
+            for (int i = 0; i < 4; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; acc[i][2] = 0.f; acc[i][3] = 0.f; }
+            tile_gemm<H, H, TILE_LD>(s_x, s_w2T, ng, og, acc);
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-            if (ng + 32 * i < rows)
-                reinterpret_cast<float4 *>(Y)[(size_t)(node0 + ng + 32 * i) * (H / 4) + og] =
-                    make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+            for (int i = 0; i < 4; ++i)
+                if (ng + 32 * i < rows)
+                    reinterpret_cast<float4 *>(Y)[(size_t)(node0 + ng + 32 * i) * (H / 4) + og] =
+                        make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) { acc[i][0] = b4.x; acc[i][1] = b4.y; acc[i][2] = b4.z; acc[i][3] = b4.w; }
         tile_gemm<H, H, TILE_LD>(s_x, s_wdT, ng, og, acc);
@@ -887,7 +890,11 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
     GM_TRY(check_params(p));
     if (N < 0 || !ws || !err_flags) return GM_ERR_INVALID_ARGUMENT;
     if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || (!rowptr && !geo_ws) || !out)) return GM_ERR_INVALID_ARGUMENT;
-    if (geo_ws && (precision != GM_PREC_FP32 || !node_perm)) return GM_ERR_UNSUPPORTED;
+    if (geo_ws && !node_perm) return GM_ERR_UNSUPPORTED;
+    // per-edge tcgen05 on the implicit graph: forward only (no arg-max, no BatchNorm partials)
+    if (geo_ws && precision != GM_PREC_FP32 &&
+        ((precision != GM_PREC_TF32 && precision != GM_PREC_BF16) || training || save_for_backward))
+        return GM_ERR_UNSUPPORTED;
     if (ws_bytes < net_ws_layout(N, p->conv_depth, save_for_backward, nullptr, nullptr)) return GM_ERR_CAPACITY;
     if (N == 0) return GM_OK;
     cudaStream_t st = as_stream(stream);
@@ -937,6 +944,15 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
             TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
             if (geo_ws) GM_TRY(geo_edge_aggr(aggr, w.Y, w.P, geo_ws, N, B, w.conv[l], arg, tail, st));
             else GM_TRY(edge_aggr(aggr, w.Y, w.P, rowptr, col, N, w.conv[l], arg, tail, st));
+        } else if (geo_ws) {
+            {
+                TimedRegion tr(GM_TIMER_NODE_PREP, st);
+                k_node_prep2<<<ngrid, NP_THREADS, 0, st>>>(raw, resid, stat_in, p->conv_w[l], p->conv_b[l], N, w.emb[l],
+                                                           nullptr, w.P, 1);
+                GM_LAUNCH_CHECK();
+            }
+            TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
+            GM_TRY(geo_edgeconv_tc(aggr, precision, w.emb[l], w.P, p->conv_w[l], geo_ws, N, B, w.conv[l], st));
         } else {
             {
                 TimedRegion tr(GM_TIMER_NODE_PREP, st);
@@ -983,22 +999,32 @@ int gm_net_forward(const GmParams *p, const float *x_cont, int x_cont_stride, co
 int gm_net_forward_geo(const GmParams *p, const float *x_cont, int x_cont_stride, const int64_t *x_cat_i64,
                        const float *x_cat_f32, int x_cat_stride, const void *geo_ws, int N, int B,
                        const int *node_perm, int training, int save_for_backward, int apply_sigmoid, int aggr,
-                       float momentum, float eps, void *ws, size_t ws_bytes, float *out, int *err_flags,
+                       int precision, float momentum, float eps, void *ws, size_t ws_bytes, float *out, int *err_flags,
                        void *stream) {
     if (!geo_ws || B < 1) return GM_ERR_INVALID_ARGUMENT;
     return net_forward_impl(p, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, nullptr, nullptr, geo_ws, B, N,
-                            node_perm, training, save_for_backward, apply_sigmoid, aggr, GM_PREC_FP32, momentum, eps,
+                            node_perm, training, save_for_backward, apply_sigmoid, aggr, precision, momentum, eps,
                             ws, ws_bytes, out, err_flags, stream);
 }
 
 int gm_edgeconv_forward_geo(const float *x, const void *geo_ws, int N, int B, const float *W, const float *b, int aggr,
-                            void *ws, size_t ws_bytes, float *out, int *arg_out, void *stream) {
+                            int precision, void *ws, size_t ws_bytes, float *out, int *arg_out, void *stream) {
     if (N < 0 || B < 1 || !geo_ws || (N > 0 && (!x || !W || !b || !out || !ws))) return GM_ERR_INVALID_ARGUMENT;
     if (N == 0) return GM_OK;
     if (ws_bytes < gm_edgeconv_ws_bytes(N)) return GM_ERR_CAPACITY;
     cudaStream_t st = as_stream(stream);
     float *Y = (float *)ws;
     float *P = (float *)((char *)ws + gm_edgeconv_ws_bytes(N) / 2);
+    if (precision != GM_PREC_FP32) {                    // per-edge tcgen05 contraction: forward only
+        if (arg_out || (precision != GM_PREC_TF32 && precision != GM_PREC_BF16)) return GM_ERR_UNSUPPORTED;
+        {
+            TimedRegion tr(GM_TIMER_NODE_PREP, st);
+            k_node_prep2<<<node_grid(N), NP_THREADS, 0, st>>>(x, nullptr, nullptr, W, b, N, nullptr, nullptr, P, 1);
+            GM_LAUNCH_CHECK();
+        }
+        TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
+        return geo_edgeconv_tc(aggr, precision, x, P, W, geo_ws, N, B, out, st);
+    }
     {
         TimedRegion tr(GM_TIMER_NODE_PREP, st);
         k_node_prep2<<<node_grid(N), NP_THREADS, 0, st>>>(x, nullptr, nullptr, W, b, N, nullptr, Y, P);

@@ -170,9 +170,10 @@ def build_geo(pos: torch.Tensor, r: float, ptr_i32: torch.Tensor, loop: bool = F
 
 
 def edgeconv_geo(x_internal: torch.Tensor, geo: GeoGraph, weight: torch.Tensor, bias: torch.Tensor, aggr: str = "max",
-                 want_arg: bool = False):
+                 want_arg: bool = False, precision: str = "fp32"):
     """EdgeConv(Linear(64, 32), aggr) over the implicit graph; ``x_internal`` [N,32] is in internal node order
-    (``x[geo.perm]``) and so are the outputs."""
+    (``x[geo.perm]``) and so are the outputs.  ``precision`` "tf32" / "bf16" runs the per-edge contraction on
+    tcgen05 (forward only: no ``want_arg``)."""
     _lib.require_cuda(x_internal, "x")
     x = x_internal.contiguous().float()
     N = x.shape[0]
@@ -181,7 +182,7 @@ def edgeconv_geo(x_internal: torch.Tensor, geo: GeoGraph, weight: torch.Tensor, 
     out = torch.empty_like(x)
     arg = torch.empty(N, 32, dtype=torch.int32, device=x.device) if want_arg else None
     check(l.gm_edgeconv_forward_geo(ptr(x), ptr(geo.ws), N, geo.num_events, ptr(weight), ptr(bias), _lib.AGGR[aggr],
-                                    ptr(ws), ws.numel(), ptr(out), ptr(arg), stream()), "gm_edgeconv_forward_geo")
+                                    _lib.PRECISION[precision], ptr(ws), ws.numel(), ptr(out), ptr(arg), stream()), "gm_edgeconv_forward_geo")
     return (out, arg) if want_arg else out
 
 

@@ -8,7 +8,8 @@ The radius graph is, by default, kept IMPLICIT (``graph="implicit"``, ``gm_geo_b
 the network runs in cell-sorted node order and the EdgeConv kernels re-evaluate the edge predicate on cell
 neighbourhoods staged in shared memory, so no edge list and no transposed graph are ever written.
 ``graph="csr"`` is the explicit path (count, scan, fill; E stays on the device; transposed CSR iff capped) and
-the only one that supports the tcgen05 ``edge_precision`` variants.
+the only one that supports the tcgen05 ``edge_precision`` variants in TRAINING; in eval mode tf32 / bf16 run the
+per-edge contraction on the implicit graph too (``csrc/geo_tc.cu``).
 Parameters stay the module's ``nn.Parameter``s (re-pointed at one flat fp32 buffer), so
 ``state_dict()`` / checkpoints are unchanged; optimizer state converts to and from the
 ``torch.optim.AdamW`` layout the reference's checkpoints store (``optim_dict``).
@@ -66,8 +67,13 @@ class GraphMETTrainer:
         self._host_loss = torch.zeros((), dtype=torch.float32).pin_memory()
 
     # ------------------------------------------------------------------------------------------ buffers
-    def _implicit(self) -> bool:
-        return self.graph == "implicit" and self.net.edge_precision == "fp32"
+    def _implicit(self, training: bool | None = None) -> bool:
+        """fp32: always; tf32 / bf16 (per-edge tcgen05 on the implicit graph, csrc/geo_tc.cu): forward only."""
+        if training is None:
+            training = self.net.training
+        if self.graph != "implicit":
+            return False
+        return self.net.edge_precision == "fp32" or (self.net.edge_precision in ("tf32", "bf16") and not training)
 
     def _reserve(self, N: int, B: int, max_event_nodes: int):
         implicit = self._implicit()
@@ -122,7 +128,7 @@ class GraphMETTrainer:
             check(lib().gm_net_forward_geo(C.byref(self._P), ptr(x), x.stride(0), None, x.data_ptr() + 8 * 4,
                                            x.stride(0), ptr(self.geo_ws), N, B, ptr(self.perm), int(training),
                                            int(save), int(self.apply_sigmoid), AGGR[net.aggr],
-                                           float(net.bn_all.momentum), float(net.bn_all.eps), ptr(self.fwd_ws),
+                                           PRECISION[net.edge_precision], float(net.bn_all.momentum), float(net.bn_all.eps), ptr(self.fwd_ws),
                                            self.fwd_ws.numel(), ptr(self.weights), ptr(self.flags), stream()),
                   "gm_net_forward_geo")
             return
@@ -163,8 +169,8 @@ class GraphMETTrainer:
         (no sync). ``batch.x`` [N,11] f32, ``batch.y`` [B,>=2] f32, ``batch.ptr`` [B+1] i32."""
         x, y, p = batch.x, batch.y, batch.ptr
         N, B, men = self._sizes(batch, max_event_nodes)
-        self._reserve(N, B, men)
         self.net.train()
+        self._reserve(N, B, men)
         l, st = lib(), stream()
         self._graph(x, p, N, B, men, need_transpose=True)
         self._forward(x, N, B, training=True, save=True)
@@ -200,8 +206,8 @@ class GraphMETTrainer:
         """evaluate.py:81-100 fused: returns (weights[N] view, loss 0-dim, met[B,2]) on the device."""
         x, y, p = batch.x, batch.y, batch.ptr
         N, B, men = self._sizes(batch, max_event_nodes)
-        self._reserve(N, B, men)
         self.net.eval()
+        self._reserve(N, B, men)
         self._graph(x, p, N, B, men, need_transpose=False)
         self._forward(x, N, B, training=False, save=False)
         check(lib().gm_met_loss(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,

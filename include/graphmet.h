@@ -222,7 +222,9 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
  * gm_net_forward_geo / gm_net_backward_geo / gm_edgeconv_forward_geo are gm_net_forward / gm_net_backward /
  * gm_edgeconv_forward with (geo_ws, B, node_perm) in place of the CSR: the EdgeConv layers stage each cell
  * neighbourhood once into shared memory (TMA bulk copies) and evaluate that predicate there; the backward
- * needs no transposed graph.  fp32 (factored) arithmetic only.  geo_ws (gm_geo_ws_bytes(N, B)) must stay
+ * needs no transposed graph.  precision: GM_PREC_FP32 (factored fp32: forward, backward, arg-max) or, forward
+ * only (training == 0, save_for_backward == 0, arg_out == NULL), GM_PREC_TF32 / GM_PREC_BF16: the per-edge
+ * contraction on tcgen05, every consumer warp driving its own TMEM pipeline (csrc/geo_tc.cu).  geo_ws (gm_geo_ws_bytes(N, B)) must stay
  * untouched between the build and the last forward / backward that uses it.
  * stats_out (optional, int[4]): {-1 (E is not counted), max degree seen among cap candidates, #capped, flags}.
  * x of gm_edgeconv_forward_geo, and arg_out, are in INTERNAL node order.
@@ -234,7 +236,7 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
 int gm_net_forward_geo(const GmParams *p, const float *x_cont, int x_cont_stride,
                        const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride,
                        const void *geo_ws, int N, int B, const int *node_perm,
-                       int training, int save_for_backward, int apply_sigmoid, int aggr,
+                       int training, int save_for_backward, int apply_sigmoid, int aggr, int precision,
                        float momentum, float eps,
                        void *ws, size_t ws_bytes, float *out, int *err_flags, void *stream);
 int gm_net_backward_geo(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
@@ -244,7 +246,8 @@ int gm_net_backward_geo(const GmParams *p, const GmParams *grads, const float *x
                         const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
                         const float *out, const float *grad_out, void *stream);
 int gm_edgeconv_forward_geo(const float *x, const void *geo_ws, int N, int B, const float *W, const float *b,
-                            int aggr, void *ws, size_t ws_bytes, float *out, int *arg_out, void *stream);
+                            int aggr, int precision, void *ws, size_t ws_bytes, float *out, int *arg_out,
+                            void *stream);
 
 /* CSR (by target) -> CSR of the transposed graph (by source), targets ascending per row.
  * ws: gm_csr_ws_bytes(N, E). Needed by the backward only when GM_FLAG_DEGREE_CAPPED was raised;
