@@ -110,7 +110,7 @@ __device__ __forceinline__ int node_of_row(const ChunkDesc *d, int row) {
 template <class SL, bool TROWS>
 __device__ __forceinline__ void geo_produce(unsigned char *gs, uint32_t full0, uint32_t empty0, const GeoView &v,
                                             const GeoMeta &m, const float *__restrict__ rows_src, int N, bool dynamic,
-                                            int lane) {
+                                            int lane, unsigned sleep_ns = 400) {
     const CellGrid g = make_grid(v.bbox, m.r, m.dim, m.phi_wrap);
     const int n_items = (N + GEO_TPI - 1) / GEO_TPI;
     uint32_t gc = 0;                                    // chunks issued so far; chunk gc lives in stage gc & 1
@@ -147,7 +147,7 @@ __device__ __forceinline__ void geo_produce(unsigned char *gs, uint32_t full0, u
             const int crow = min(SL::ROWS, (((C + nck - 1) / nck) + 31) & ~31);    // even split, multiple of 32
             for (int k = 0; k < nck; ++k, ++gc) {
                 const int st = gc & 1;
-                mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u, 400);        // stage consumed (or never used)
+                mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u, sleep_ns);   // stage consumed (or never used)
                 if (lane == 0) {
                     unsigned char *stage = gs + st * SL::BYTES;
                     const uint32_t s_stage = smem_u32(stage), bar = full0 + 8u * st;

@@ -25,26 +25,33 @@
 namespace gm {
 namespace {
 
-constexpr int GT_CONSUMERS = 4;                       // consumer warps = TMEM lane quarters
-constexpr int GT_THREADS = (GT_CONSUMERS + 1) * 32;   // + 1 producer warp
-constexpr int GT_TPW = GEO_TPI / GT_CONSUMERS;        // target slots per warp and item
 #ifndef GT_CH
-#define GT_CH 160                                     // staged neighbourhood rows per pipeline stage
+#define GT_CH 224                                     // staged neighbourhood rows per pipeline stage
+#endif
+#ifndef GT_NC_BF16
+#define GT_NC_BF16 16                                 // consumer warps per CTA (one CTA per SM: 512 TMEM columns)
+#endif
+#ifndef GT_NC_TF32
+#define GT_NC_TF32 8                                  // tf32 operand blocks are twice as large
 #endif
 constexpr int GT_LIST = GT_CH + 8;
 constexpr int GT_BLK = 32;                            // edge columns per MMA block (MMA N)
 constexpr int GT_LBO = 192;                           // bytes between the 16-byte K chunks of an 8-row group: 4 rows x
                                                       // (4 | 8) chunks of a warp store land on distinct banks
-constexpr int GT_TMEM_COLS = 128;                     // GT_CONSUMERS x GT_BLK
 using GtStage = StageL<GT_CH, true>;
-static_assert(GT_CONSUMERS * GT_BLK == GT_TMEM_COLS && GT_TPW <= 8, "TMEM columns / slot count");
 
 template <int PREC> struct GtCfg;
-template <> struct GtCfg<GM_PREC_TF32> { static constexpr int CHUNKS = 8, KSTEPS = 4, FMT = 2; };   // 4 tf32 per chunk
-template <> struct GtCfg<GM_PREC_BF16> { static constexpr int CHUNKS = 4, KSTEPS = 2, FMT = 1; };   // 8 bf16 per chunk
+template <> struct GtCfg<GM_PREC_TF32> { static constexpr int CHUNKS = 8, KSTEPS = 4, FMT = 2, NC = GT_NC_TF32; };   // 4 tf32 per chunk
+template <> struct GtCfg<GM_PREC_BF16> { static constexpr int CHUNKS = 4, KSTEPS = 2, FMT = 1, NC = GT_NC_BF16; };   // 8 bf16 per chunk
+constexpr int gt_tmem_cols(int nc) { return nc * GT_BLK <= 32 ? 32 : nc * GT_BLK <= 64 ? 64 : nc * GT_BLK <= 128 ? 128 : nc * GT_BLK <= 256 ? 256 : 512; }
 
 template <int PREC>
 struct GtSmem {
+    static constexpr int GT_CONSUMERS = GtCfg<PREC>::NC;              // consumer warps (TMEM lane quarter = warp & 3)
+    static constexpr int GT_TPW = GEO_TPI / GT_CONSUMERS;             // target slots per warp and item
+    static constexpr int THREADS = (GT_CONSUMERS + 1) * 32;           // + 1 producer warp
+    static constexpr int TMEM_COLS = gt_tmem_cols(GT_CONSUMERS);
+    static_assert(GT_CONSUMERS * GT_BLK <= 512 && GEO_TPI % GT_CONSUMERS == 0 && GT_TPW <= 8, "TMEM columns / slot count");
     static constexpr int SBO = GtCfg<PREC>::CHUNKS * GT_LBO;          // stride of an 8-row group
     static constexpr int A_BYTES = (128 / 8) * SBO;
     static constexpr int B_BYTES = (GT_BLK / 8) * SBO;                // one operand block
@@ -84,12 +91,13 @@ __device__ __forceinline__ void gt_sts128(uint32_t addr, uint32_t a, uint32_t b,
 }
 
 template <int PREC, int AGGR>
-__global__ void __launch_bounds__(GT_THREADS, 2)
+__global__ void __launch_bounds__(GtSmem<PREC>::THREADS, 1)
 k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, const float *__restrict__ W, GeoView v,
                   int N, float *__restrict__ out) {
     using S = GtSmem<PREC>;
     using C = GtCfg<PREC>;
     constexpr bool TF32 = PREC == GM_PREC_TF32;
+    constexpr int GT_CONSUMERS = S::GT_CONSUMERS, GT_TPW = S::GT_TPW, GT_THREADS = S::THREADS, GT_TMEM_COLS = S::TMEM_COLS;
     extern __shared__ __align__(128) unsigned char gs[];
     const uint32_t full0 = smem_u32(gs + S::OFF_BAR), empty0 = full0 + 8u * AG_STAGES, mma0 = empty0 + 8u * AG_STAGES;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -126,7 +134,7 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
 
     if (warp == GT_CONSUMERS) {
         // ================================================================== producer (tickets: no BatchNorm partials here)
-        geo_produce<GtStage, true>(gs, full0, empty0, v, m, X, N, true, lane);
+        geo_produce<GtStage, true>(gs, full0, empty0, v, m, X, N, true, lane, 1000);
     } else {
         // ================================================================== consumers
         const int w = warp;
@@ -300,13 +308,13 @@ int launch_geo_tc(const float *X, const float *P, const float *W, const GeoView 
                                          (int)GtSmem<PREC>::TOTAL));
         GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_edgeconv_tc<PREC, AGGR>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                          (int)cudaSharedmemCarveoutMaxShared));
-        occ = min(resident_ctas(k_geo_edgeconv_tc<PREC, AGGR>, GT_THREADS, GtSmem<PREC>::TOTAL, 1), 512 / GT_TMEM_COLS);
+        occ = min(resident_ctas(k_geo_edgeconv_tc<PREC, AGGR>, GtSmem<PREC>::THREADS, GtSmem<PREC>::TOTAL, 1), 512 / GtSmem<PREC>::TMEM_COLS);
         // work is taken from a ticket counter, so a CTA that is not resident at once only finds the queue empty:
         // size the grid by what shared memory allows even if the occupancy query is pessimistic
-        occ = max(occ, min((int)(227 * 1024 / (GtSmem<PREC>::TOTAL + 1024)), 512 / GT_TMEM_COLS));
+        occ = max(occ, min((int)(227 * 1024 / (GtSmem<PREC>::TOTAL + 1024)), 512 / GtSmem<PREC>::TMEM_COLS));
     }
     const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, occ);
-    k_geo_edgeconv_tc<PREC, AGGR><<<grid, GT_THREADS, GtSmem<PREC>::TOTAL, st>>>(X, P, W, v, N, out);
+    k_geo_edgeconv_tc<PREC, AGGR><<<grid, GtSmem<PREC>::THREADS, GtSmem<PREC>::TOTAL, st>>>(X, P, W, v, N, out);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
