@@ -107,13 +107,13 @@ __device__ __forceinline__ int node_of_row(const ChunkDesc *d, int row) {
 // with TMA bulk copies, SL::ROWS rows at a time; every chunk carries its descriptor and the item's target points / cap
 // thresholds (and, with TROWS, the item's own rows of `rows_src` on the first chunk of a segment).
 //   full[s]  : 1 arrival + TMA bytes;   empty[s] : one arrival per consumer warp.
-template <class SL, bool TROWS>
+template <class SL, bool TROWS, int NS = AG_STAGES>
 __device__ __forceinline__ void geo_produce(unsigned char *gs, uint32_t full0, uint32_t empty0, const GeoView &v,
                                             const GeoMeta &m, const float *__restrict__ rows_src, int N, bool dynamic,
                                             int lane, unsigned sleep_ns = 400) {
     const CellGrid g = make_grid(v.bbox, m.r, m.dim, m.phi_wrap);
     const int n_items = (N + GEO_TPI - 1) / GEO_TPI;
-    uint32_t gc = 0;                                    // chunks issued so far; chunk gc lives in stage gc & 1
+    uint32_t gc = 0;                                    // chunks issued so far; chunk gc lives in stage gc % NS
     int item = blockIdx.x;
     for (;;) {
         if (dynamic) {
@@ -146,8 +146,8 @@ __device__ __forceinline__ void geo_produce(unsigned char *gs, uint32_t full0, u
             const int nck = (C + SL::ROWS - 1) / SL::ROWS;
             const int crow = min(SL::ROWS, (((C + nck - 1) / nck) + 31) & ~31);    // even split, multiple of 32
             for (int k = 0; k < nck; ++k, ++gc) {
-                const int st = gc & 1;
-                mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u, sleep_ns);   // stage consumed (or never used)
+                const int st = gc % NS;
+                mbar_wait(empty0 + 8u * st, ((gc / NS) & 1u) ^ 1u, sleep_ns);   // stage consumed (or never used)
                 if (lane == 0) {
                     unsigned char *stage = gs + st * SL::BYTES;
                     const uint32_t s_stage = smem_u32(stage), bar = full0 + 8u * st;
@@ -181,8 +181,8 @@ __device__ __forceinline__ void geo_produce(unsigned char *gs, uint32_t full0, u
         }
         item += gridDim.x;
     }
-    const int st = gc & 1;                              // end-of-work descriptor (no copies)
-    mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u);
+    const int st = gc % NS;                             // end-of-work descriptor (no copies)
+    mbar_wait(empty0 + 8u * st, ((gc / NS) & 1u) ^ 1u);
     if (lane == 0) {
         reinterpret_cast<ChunkDesc *>(gs + st * SL::BYTES + SL::OFF_DESC)->flags = AG_END;
         mbar_arrive(full0 + 8u * st);

@@ -26,7 +26,10 @@ namespace gm {
 namespace {
 
 #ifndef GT_CH
-#define GT_CH 224                                     // staged neighbourhood rows per pipeline stage
+#define GT_CH 160                                     // staged neighbourhood rows per pipeline stage
+#endif
+#ifndef GT_STAGES
+#define GT_STAGES 3                                   // 16 consumer warps drain a stage in 2-3 us: one more in flight
 #endif
 #ifndef GT_NC_BF16
 #define GT_NC_BF16 16                                 // consumer warps per CTA (one CTA per SM: 512 TMEM columns)
@@ -55,7 +58,7 @@ struct GtSmem {
     static constexpr int SBO = GtCfg<PREC>::CHUNKS * GT_LBO;          // stride of an 8-row group
     static constexpr int A_BYTES = (128 / 8) * SBO;
     static constexpr int B_BYTES = (GT_BLK / 8) * SBO;                // one operand block
-    static constexpr size_t OFF_LISTS = (size_t)AG_STAGES * GtStage::BYTES;
+    static constexpr size_t OFF_LISTS = (size_t)GT_STAGES * GtStage::BYTES;
     static constexpr size_t OFF_A = OFF_LISTS + (size_t)GT_CONSUMERS * GT_LIST * 4;
     static constexpr size_t OFF_B = OFF_A + A_BYTES;                                   // [warp][2] blocks
     static constexpr size_t OFF_XI = OFF_B + (size_t)GT_CONSUMERS * 2 * B_BYTES;       // [warp][slot][32] f32: x_i
@@ -64,7 +67,7 @@ struct GtSmem {
     static constexpr size_t OFF_DEG = OFF_SLOT + (size_t)GT_CONSUMERS * GT_TPW * 16;   // [warp][slot] i32
     static constexpr size_t OFF_GSLOT = OFF_DEG + (size_t)GT_CONSUMERS * GT_TPW * 4;   // [warp][2][4] u8: slot of a group
     static constexpr size_t OFF_BAR = (OFF_GSLOT + (size_t)GT_CONSUMERS * 8 + 7) / 8 * 8;     // full[2] empty[2] mma[warp]
-    static constexpr size_t OFF_TMEM = OFF_BAR + (size_t)(2 * AG_STAGES + GT_CONSUMERS) * 8;
+    static constexpr size_t OFF_TMEM = OFF_BAR + (size_t)(2 * GT_STAGES + GT_CONSUMERS) * 8;
     static constexpr size_t TOTAL = OFF_TMEM + 16;
     static_assert(OFF_A % 128 == 0 && OFF_B % 16 == 0 && OFF_XI % 16 == 0 && OFF_SLOT % 16 == 0, "operand alignment");
 };
@@ -99,14 +102,14 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
     constexpr bool TF32 = PREC == GM_PREC_TF32;
     constexpr int GT_CONSUMERS = S::GT_CONSUMERS, GT_TPW = S::GT_TPW, GT_THREADS = S::THREADS, GT_TMEM_COLS = S::TMEM_COLS;
     extern __shared__ __align__(128) unsigned char gs[];
-    const uint32_t full0 = smem_u32(gs + S::OFF_BAR), empty0 = full0 + 8u * AG_STAGES, mma0 = empty0 + 8u * AG_STAGES;
+    const uint32_t full0 = smem_u32(gs + S::OFF_BAR), empty0 = full0 + 8u * GT_STAGES, mma0 = empty0 + 8u * GT_STAGES;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const GeoMeta m = *v.meta;
     const float IDENT = AGGR == GM_AGGR_MAX ? -INFINITY : 0.f;
 
     // ---- one-time setup: barriers, TMEM, the A operand (W2 replicated 4x along M, rounded to the MMA input type)
     if (tid == 0) {
-        for (int s = 0; s < AG_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, GT_CONSUMERS); }
+        for (int s = 0; s < GT_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, GT_CONSUMERS); }
         for (int w = 0; w < GT_CONSUMERS; ++w) mbar_init(mma0 + 8u * w, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -134,7 +137,7 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
 
     if (warp == GT_CONSUMERS) {
         // ================================================================== producer (tickets: no BatchNorm partials here)
-        geo_produce<GtStage, true>(gs, full0, empty0, v, m, X, N, true, lane, 1000);
+        geo_produce<GtStage, true, GT_STAGES>(gs, full0, empty0, v, m, X, N, true, lane, 200);
     } else {
         // ================================================================== consumers
         const int w = warp;
@@ -149,6 +152,7 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
         const uint32_t d_tmem = tmem_base + (uint32_t)(w * GT_BLK);                 // all 128 lanes, this warp's columns
         const uint32_t ld_tmem = d_tmem + ((uint32_t)((w & 3) * 32) << 16);         // this warp's lane quarter
         const uint32_t idesc = gt_instr_desc<PREC>(GT_BLK);
+        const uint64_t adesc0 = gt_smem_desc<PREC>(a_base), bdesc0 = gt_smem_desc<PREC>(b_base);
         const int r4 = lane >> 3, c4 = lane & 7;                                    // 8 lanes per edge row, 4 channels per lane
         const uint32_t lane_off = TF32 ? (uint32_t)(c4 * GT_LBO) : (uint32_t)((c4 >> 1) * GT_LBO + (c4 & 1) * 8);
         int fill = 0, buf = 0, pending = -1, nv_pending = 0;
@@ -162,17 +166,24 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
             uint32_t r[32];
             tc5_ld32(ld_tmem, r);
             const unsigned slots = *reinterpret_cast<const unsigned *>(s_gslot + pending * 4);
+            float run = IDENT;                                                      // groups of one slot are merged in registers
 #pragma unroll
             for (int g = 0; g < GT_BLK / 8; ++g) {
                 if (g * 8 < nv_pending) {                                           // warp-uniform
                     float t[8];
 #pragma unroll
                     for (int c = 0; c < 8; ++c) t[c] = __uint_as_float(r[8 * g + c]);
-                    const float red = AGGR == GM_AGGR_MAX
-                        ? fmaxf(fmaxf(fmaxf(t[0], t[1]), fmaxf(t[2], t[3])), fmaxf(fmaxf(t[4], t[5]), fmaxf(t[6], t[7])))
-                        : ((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]));
-                    float *dst = s_acc + (int)((slots >> (8 * g)) & 0xffu) * 32 + lane;
-                    *dst = AGGR == GM_AGGR_MAX ? fmaxf(*dst, red) : *dst + red;
+                    if (AGGR == GM_AGGR_MAX)
+                        run = fmaxf(fmaxf(fmaxf(run, t[0]), fmaxf(t[1], t[2])), fmaxf(fmaxf(t[3], t[4]), fmaxf(t[5], fmaxf(t[6], t[7]))));
+                    else
+                        run += ((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]));
+                    const unsigned sg = (slots >> (8 * g)) & 0xffu;
+                    const bool close = (g + 1) * 8 >= nv_pending || g == GT_BLK / 8 - 1 || ((slots >> (8 * g + 8)) & 0xffu) != sg;
+                    if (close) {                                                    // warp-uniform
+                        float *dst = s_acc + (int)sg * 32 + lane;
+                        *dst = AGGR == GM_AGGR_MAX ? fmaxf(*dst, run) : *dst + run;
+                        run = IDENT;
+                    }
                 }
             }
             tc5_fence_before();
@@ -185,11 +196,11 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
             __syncwarp();
             if (lane == 0) {
                 tc5_fence_after();
-                const uint32_t bs = b_base + (uint32_t)(buf * S::B_BYTES);
+                const uint64_t bdesc = bdesc0 + (uint64_t)((buf * S::B_BYTES) >> 4);   // address field only: no carry out
 #pragma unroll
                 for (int ks = 0; ks < C::KSTEPS; ++ks)
-                    tc5_mma<TF32>(d_tmem, gt_smem_desc<PREC>(a_base + ks * 2 * GT_LBO),
-                                  gt_smem_desc<PREC>(bs + ks * 2 * GT_LBO), idesc, ks > 0 ? 1u : 0u);
+                    tc5_mma<TF32>(d_tmem, adesc0 + (uint64_t)((ks * 2 * GT_LBO) >> 4), bdesc + (uint64_t)((ks * 2 * GT_LBO) >> 4),
+                                  idesc, ks > 0 ? 1u : 0u);
                 tc5_commit(mbar);
             }
             __syncwarp();
@@ -197,9 +208,9 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
         };
 
         for (uint32_t gc = 0;; ++gc) {
-            const int st = gc & 1;
+            const int st = gc % GT_STAGES;
             const unsigned char *stage = gs + st * GtStage::BYTES;
-            mbar_wait(full0 + 8u * st, (gc >> 1) & 1u);
+            mbar_wait(full0 + 8u * st, (gc / GT_STAGES) & 1u);
             const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + GtStage::OFF_DESC);
             const int flags = d->flags;
             if (flags & AG_END) break;
@@ -233,29 +244,41 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
                                                      m, lane, list);
                 if (lane == 0) s_deg[u] += nh;
                 const float4 xi = *reinterpret_cast<const float4 *>(s_xi + u * 32 + c4 * 4);
-                const int np = (nh + 7) & ~7;                                       // padded to whole 8-column groups
-                int k = 0;
-                while (k < np) {                                                    // warp-uniform
-                    const int n = min(np - k, GT_BLK - fill);                       // a multiple of 8
-                    if (lane < (n >> 3)) s_gslot[buf * 4 + (fill >> 3) + lane] = (unsigned char)u;
-                    const uint32_t bs = b_base + (uint32_t)(buf * S::B_BYTES) + lane_off;
-                    for (int j = r4; j < n; j += 4) {
-                        const int h = k + j;
-                        float4 dv = make_float4(0.f, 0.f, 0.f, 0.f);                // add / mean padding: a zero row
-                        if (AGGR == GM_AGGR_MAX || h < nh) {                        // max padding: the last hit again
-                            const unsigned off = list[min(h, nh - 1)];
-                            const float4 xj = *reinterpret_cast<const float4 *>(stage + off + c4 * 16);
-                            dv = make_float4(xj.x - xi.x, xj.y - xi.y, xj.z - xi.z, xj.w - xi.w);
+                if (nh > 0) {
+                    // pad the list to whole 8-column groups: max -> the last hit again; add / mean -> x_i itself (a zero row)
+                    const unsigned pad = AGGR == GM_AGGR_MAX ? list[nh - 1]
+                                                             : (unsigned)(smem_u32(s_xi + u * 32) - smem_u32(stage));
+                    __syncwarp();
+                    if (lane < 8) list[nh + lane] = pad;
+                    __syncwarp();
+                    const uint32_t src = smem_u32(stage) + (uint32_t)(c4 * 16);
+                    const uint32_t dstl = b_base + lane_off + (uint32_t)(r4 * 16);
+                    // one 8-column group per trip, software-pipelined: the rows of group k + 8 and the list entries of
+                    // group k + 16 are in flight while group k is subtracted, rounded and stored
+                    auto lds4 = [](float4 &q, uint32_t a) {
+                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(q.x), "=f"(q.y), "=f"(q.z), "=f"(q.w) : "r"(a));
+                    };
+                    float4 x0, x1;
+                    lds4(x0, src + list[r4]);
+                    lds4(x1, src + list[4 + r4]);
+                    unsigned o0 = list[8 + r4], o1 = list[12 + r4];                 // in bounds (GT_LIST); used only if valid
+                    for (int k = 0; k < nh; k += 8) {
+                        float4 y0 = x0, y1 = x1;
+                        if (k + 8 < nh) { lds4(y0, src + o0); lds4(y1, src + o1); } // warp-uniform
+                        if (k + 16 < nh) { o0 = list[k + 16 + r4]; o1 = list[k + 20 + r4]; }
+                        const uint32_t addr = dstl + (uint32_t)(buf * S::B_BYTES + (fill >> 3) * S::SBO);
+                        if constexpr (TF32) {
+                            gt_sts128(addr, tc5_to_tf32(x0.x - xi.x), tc5_to_tf32(x0.y - xi.y), tc5_to_tf32(x0.z - xi.z), tc5_to_tf32(x0.w - xi.w));
+                            gt_sts128(addr + 64, tc5_to_tf32(x1.x - xi.x), tc5_to_tf32(x1.y - xi.y), tc5_to_tf32(x1.z - xi.z), tc5_to_tf32(x1.w - xi.w));
+                        } else {
+                            gt_sts64(addr, tc5_pack_bf16(x0.x - xi.x, x0.y - xi.y), tc5_pack_bf16(x0.z - xi.z, x0.w - xi.w));
+                            gt_sts64(addr + 64, tc5_pack_bf16(x1.x - xi.x, x1.y - xi.y), tc5_pack_bf16(x1.z - xi.z, x1.w - xi.w));
                         }
-                        const int col = fill + j;
-                        const uint32_t addr = bs + (uint32_t)((col >> 3) * S::SBO + (col & 7) * 16);
-                        if constexpr (TF32)
-                            gt_sts128(addr, tc5_to_tf32(dv.x), tc5_to_tf32(dv.y), tc5_to_tf32(dv.z), tc5_to_tf32(dv.w));
-                        else
-                            gt_sts64(addr, tc5_pack_bf16(dv.x, dv.y), tc5_pack_bf16(dv.z, dv.w));
+                        if (lane == 0) s_gslot[buf * 4 + (fill >> 3)] = (unsigned char)u;
+                        fill += 8;
+                        if (fill == GT_BLK) flush();
+                        x0 = y0; x1 = y1;
                     }
-                    fill += n; k += n;
-                    if (fill == GT_BLK) flush();
                 }
                 __syncwarp();                                   // the hit list is reused by the next target
             }
