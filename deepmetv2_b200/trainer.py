@@ -201,6 +201,39 @@ class GraphMETTrainer:
         torch.cuda.current_stream().synchronize()
         return float(self._host_loss)
 
+    def _epoch_from_host(self, host_batches, depth, step):
+        """Double-buffered H2D (``feeder.HostFeeder``) + loss read-back deferred by ONE step: the 4-byte D2H of step
+        k is enqueued right behind its kernels, but the host waits for it only after step k+1 has been enqueued, so
+        neither the copy engine nor the SMs ever wait for Python."""
+        from .feeder import HostFeeder
+        if not hasattr(self, "_loss_ring"):
+            self._loss_ring = [(torch.zeros((), dtype=torch.float32).pin_memory(), torch.cuda.Event()) for _ in range(2)]
+        losses, pending = [], None
+        for k, b in enumerate(HostFeeder(host_batches, self.device, depth=depth)):
+            loss = step(b)
+            slot, ev = self._loss_ring[k & 1]
+            slot.copy_(loss, non_blocking=True)
+            ev.record()
+            if pending is not None:
+                pending[1].synchronize()
+                losses.append(float(pending[0]))
+            pending = (slot, ev)
+        if pending is not None:
+            pending[1].synchronize()
+            losses.append(float(pending[0]))
+        return losses
+
+    def train_epoch_from_host(self, host_batches, depth: int = 2):
+        """train.py:39-55 over an iterable of PINNED host batches with the H2D copy of batch k+1 overlapped with
+        the step on batch k; the loss of every step is read back like train.py:54 does (one step late).
+        Returns the list of per-step losses."""
+        return self._epoch_from_host(host_batches, depth, lambda b: self.train_step(b, b.max_event_nodes))
+
+    def eval_epoch_from_host(self, host_batches, depth: int = 2):
+        """evaluate.py:71-103 over pinned host batches, fed like :meth:`train_epoch_from_host`.  Returns the
+        per-batch losses (weights / MET of the last batch stay in ``self.weights`` / ``self.met``)."""
+        return self._epoch_from_host(host_batches, depth, lambda b: self.eval_step(b, b.max_event_nodes)[1])
+
     @torch.no_grad()
     def eval_step(self, batch: EventBatch, max_event_nodes: int | None = None):
         """evaluate.py:81-100 fused: returns (weights[N] view, loss 0-dim, met[B,2]) on the device."""

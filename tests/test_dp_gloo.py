@@ -105,3 +105,20 @@ def test_two_rank_gradient_allreduce_matches_manual_average(tmp_path):
     want = (grads[0] + grads[1]) * 0.5
     assert torch.allclose(got[0]["grad"], want, rtol=0, atol=0)
     assert dp.allreduce_sum_(torch.zeros(3)) == 1.0            # outside a group: no-op
+
+
+def test_pack_events_and_shard_round_trip(tmp_path):
+    """Row f3 host logic: per-event tensors -> packed batch (x, y, ptr, batch) -> shard file -> the same batch."""
+    import torch
+    from deepmetv2_b200.feeder import pack_events, save_shard, load_shard
+    torch.manual_seed(0)
+    xs = [torch.randn(n, 11) for n in (5, 0, 3, 7)]
+    ys = [torch.randn(11) for _ in xs]
+    b = pack_events(xs, ys, pin=False)
+    assert b.ptr.tolist() == [0, 5, 5, 8, 15] and b.x.shape == (15, 11) and b.y.shape == (4, 11)
+    assert b.batch.tolist() == [0] * 5 + [2] * 3 + [3] * 7
+    assert torch.equal(b.x[5:8], xs[2]) and torch.equal(b.y[3], ys[3])
+    path = str(tmp_path / "shard.npz")
+    save_shard(path, b)
+    c = load_shard(path, pin=False)
+    assert torch.equal(c.x, b.x) and torch.equal(c.y, b.y) and torch.equal(c.ptr, b.ptr) and torch.equal(c.batch, b.batch)
