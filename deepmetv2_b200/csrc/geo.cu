@@ -12,7 +12,6 @@
 //   k_geo_aggr          : out_i = P_i + max_{j in N(i)} Y_j  (+ arg-max, + BatchNorm moments)              [a5 fwd]
 //   k_geo_scatter       : S_j = sum_{i : arg(i,c) == j} d conv_i[c], BatchNorm backward on the fly          [a5 bwd]
 // All reductions run in a fixed order (internal node order): bit-deterministic, no float atomics.
-#include <cooperative_groups.h>
 #include "geo_stage.cuh"
 
 namespace gm {
@@ -34,12 +33,19 @@ constexpr int AG_LIST = AG_CH + 8;   // per-warp hit list (uint32 byte offsets o
 using AgStage = StageL<AG_CH, false>;
 
 // ------------------------------------------------------------------------------------------ build
-__global__ void k_geo_meta(GeoMeta *m, float r, float r2, int dim, int phi_wrap, int loop, int cap_eff, int N, int B,
-                           int *stats) {
-    if (threadIdx.x == 0) {
+// meta, ticket counters, the workspace's copy of ptr and the "not capped" default of thr in ONE launch (was a kernel,
+// a memcpy node and two memset nodes: at DY/TT sizes the build is launch-latency bound)
+__global__ void __launch_bounds__(256) k_geo_init(GeoMeta *m, float r, float r2, int dim, int phi_wrap, int loop, int cap_eff,
+                                                  int N, int B, const int *__restrict__ ptr, int *__restrict__ ptr_copy,
+                                                  int *__restrict__ sched, int *__restrict__ thr, int *stats) {
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+    if (gtid == 0) {
         *m = GeoMeta{r, r2, dim, phi_wrap, loop, cap_eff, N, B};
         stats[0] = -1;                                   // E is never counted on this path
+        sched[0] = 0; sched[1] = 0; sched[2] = 0; sched[3] = 0;
     }
+    for (int i = gtid; i <= B; i += gsize) ptr_copy[i] = ptr[i];
+    for (int i = gtid; i < N; i += gsize) thr[i] = 0x7f7f7f7f;      // "not capped"
 }
 
 // The counting-sort scatter (k_cell_fill) places the points of a cell in atomic (arbitrary) order.  Internal order
@@ -169,199 +175,6 @@ __global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, in
     if (lane == 0) {
         if (local_max) atomicMax(stats + 1, local_max);
         if (local_capped) { atomicAdd(stats + 2, local_capped); atomicOr(stats + 3, GM_FLAG_DEGREE_CAPPED); }
-    }
-}
-
-// ------------------------------------------------------------------------------------------ build, one launch
-// The whole build as ONE cooperative kernel: at DY/TT sizes the eleven launches above are 3-9 us each and mostly
-// latency (profiles/r01e_launches_c2.csv: 65 us in total for 54k nodes), a grid barrier costs ~1.5 us.  Same
-// arithmetic, same order-independent integer atomics, same deterministic ranking as the separate kernels (which stay
-// as the fallback when the cooperative launch is not possible).
-struct GeoBuildArgs {
-    const float *pos;
-    int pos_stride, dim;
-    const int *ptr;
-    int N, B;
-    float r, r2;
-    int phi_wrap, loop, cap_eff, mask_words;
-    GeoWs w;
-    int *node_perm;
-};
-
-__global__ void __launch_bounds__(256) k_geo_build_fused(GeoBuildArgs a) {
-    namespace cg = cooperative_groups;
-    cg::grid_group grid = cg::this_grid();
-    extern __shared__ unsigned int smask[];
-    __shared__ int s_wtot[8];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int gtid = blockIdx.x * 256 + tid, gsize = gridDim.x * 256;
-    const int N = a.N, B = a.B;
-    // ---- phase 0: constants of this build
-    if (gtid == 0) {
-        a.w.bbox[0] = 0x7fffffff; a.w.bbox[1] = (int)0x80000000;
-        a.w.bbox[2] = 0x7fffffff; a.w.bbox[3] = (int)0x80000000;
-        a.w.stats[0] = -1; a.w.stats[1] = 0; a.w.stats[2] = 0; a.w.stats[3] = 0;     // E is never counted on this path
-        a.w.sched[0] = 0; a.w.sched[1] = 0; a.w.sched[2] = 0; a.w.sched[3] = 0;
-        *a.w.meta = GeoMeta{a.r, a.r2, a.dim, a.phi_wrap, a.loop, a.cap_eff, N, B};
-    }
-    for (int i = gtid; i <= B; i += gsize) a.w.ptr[i] = a.ptr[i];
-    grid.sync();
-    // ---- phase 1: bounding box (ordered-int min / max: order-independent)
-    {
-        int lo0 = 0x7fffffff, hi0 = (int)0x80000000, lo1 = lo0, hi1 = hi0;
-        for (int i = gtid; i < N; i += gsize) {
-            const float p0 = a.pos[(size_t)i * a.pos_stride];
-            if (isfinite(p0)) { const int o = float_to_ordered(p0); lo0 = min(lo0, o); hi0 = max(hi0, o); }
-            if (a.dim >= 2) {
-                const float p1 = a.pos[(size_t)i * a.pos_stride + 1];
-                if (isfinite(p1)) { const int o = float_to_ordered(p1); lo1 = min(lo1, o); hi1 = max(hi1, o); }
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            lo0 = min(lo0, __shfl_xor_sync(0xffffffffu, lo0, o));
-            hi0 = max(hi0, __shfl_xor_sync(0xffffffffu, hi0, o));
-            lo1 = min(lo1, __shfl_xor_sync(0xffffffffu, lo1, o));
-            hi1 = max(hi1, __shfl_xor_sync(0xffffffffu, hi1, o));
-        }
-        if (lane == 0) {
-            atomicMin(a.w.bbox + 0, lo0); atomicMax(a.w.bbox + 1, hi0);
-            atomicMin(a.w.bbox + 2, lo1); atomicMax(a.w.bbox + 3, hi1);
-        }
-    }
-    grid.sync();
-    const CellGrid g = make_grid(a.w.bbox, a.r, a.dim, a.phi_wrap);
-    // ---- phase 2: per-event cell histogram
-    for (int i = gtid; i < N; i += gsize) {
-        const int e = find_event(a.ptr, B, i);
-        const float p0 = a.pos[(size_t)i * a.pos_stride];
-        const float p1 = a.dim >= 2 ? a.pos[(size_t)i * a.pos_stride + 1] : 0.f;
-        const int c = cell_coord(p0, g.min0, g.inv0, g.g0) * g.g1 + cell_coord(p1, g.min1, g.inv1, g.g1);
-        atomicAdd(a.w.cell_cnt + (size_t)e * CMAX + c, 1);
-    }
-    grid.sync();
-    // ---- phase 3: cell_start[e][c] = ptr[e] + exclusive scan of the histogram (CTA per event, 4 cells per thread)
-    for (int e = blockIdx.x; e < B; e += gridDim.x) {
-        const int4 v = reinterpret_cast<const int4 *>(a.w.cell_cnt + (size_t)e * CMAX)[tid];
-        const int sum = v.x + v.y + v.z + v.w;
-        int tot;
-        const int ex = warp_excl_scan_int(sum, lane, tot);
-        if (lane == 31) s_wtot[warp] = tot;
-        __syncthreads();
-        int base = __ldg(a.ptr + e);
-        for (int k = 0; k < warp; ++k) base += s_wtot[k];
-        int *cs = a.w.cell_start + (size_t)e * (CMAX + 1) + 4 * tid;
-        const int s0 = base + ex;
-        cs[0] = s0; cs[1] = s0 + v.x; cs[2] = s0 + v.x + v.y; cs[3] = s0 + v.x + v.y + v.z;
-        if (tid == 255) cs[4] = s0 + sum;
-        __syncthreads();
-    }
-    grid.sync();
-    // ---- phase 4: counting-sort scatter (arbitrary order inside a cell; the histogram is consumed back to zero)
-    for (int i = gtid; i < N; i += gsize) {
-        const int e = find_event(a.ptr, B, i);
-        const float p0 = a.pos[(size_t)i * a.pos_stride];
-        const float p1 = a.dim >= 2 ? a.pos[(size_t)i * a.pos_stride + 1] : 0.f;
-        const int c = cell_coord(p0, g.min0, g.inv0, g.g0) * g.g1 + cell_coord(p1, g.min1, g.inv1, g.g1);
-        const int k = atomicSub(a.w.cell_cnt + (size_t)e * CMAX + c, 1) - 1;
-        const int slot = a.w.cell_start[(size_t)e * (CMAX + 1) + c] + k;
-        a.w.tmp[slot] = make_float4(p0, p1, __int_as_float(i - __ldg(a.ptr + e)), __int_as_float(c));
-    }
-    grid.sync();
-    // ---- phase 5: deterministic rank inside the cell -> pts, node_perm, default thr; cap pre-filter (3x3 population)
-    for (int s0 = gtid & ~31; s0 < N; s0 += gsize) {
-        const int s = s0 + lane;
-        bool dense = false;
-        int dst = 0;
-        if (s < N) {
-            const int e = find_event(a.ptr, B, s);
-            const float4 t = a.w.tmp[s];
-            const int idx = __float_as_int(t.z), cell = __float_as_int(t.w);
-            const int *cs = a.w.cell_start + (size_t)e * (CMAX + 1);
-            const int lo = cs[cell], hi = cs[cell + 1];
-            int rank = 0;
-            for (int k = lo; k < hi; ++k) rank += __float_as_int(a.w.tmp[k].z) < idx;
-            dst = lo + rank;
-            a.w.pts[dst] = t;
-            a.node_perm[dst] = __ldg(a.ptr + e) + idx;
-            a.w.thr[dst] = 0x7f7f7f7f;
-            const int ce = cell / g.g1, cp = cell - ce * g.g1;
-            int rlo[6], rhi[6];
-            const int nr = nbhd_runs(g, cs, ce, cp, cp, a.phi_wrap, rlo, rhi);
-            int C = 0;
-            for (int q = 0; q < nr; ++q) C += rhi[q] - rlo[q];
-            dense = C > a.cap_eff;
-        }
-        const unsigned mk = __ballot_sync(0xffffffffu, dense);
-        if (mk) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(a.w.sched + 2, __popc(mk));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (dense) a.w.cap_list[base + __popc(mk & ((1u << lane) - 1u))] = dst;
-        }
-    }
-    grid.sync();
-    // ---- phase 6: cap thresholds of the listed targets (warp per target; same body as k_geo_cap)
-    {
-        unsigned int *mask = smask + (size_t)warp * a.mask_words;
-        const int warps = gsize >> 5;
-        int local_max = 0, local_capped = 0;
-        const int n_list = a.w.sched[2];
-        for (int li = gtid >> 5; li < n_list; li += warps) {
-            const int s = a.w.cap_list[li];
-            const int e = find_event(a.ptr, B, s);
-            const int n_e = __ldg(a.ptr + e + 1) - __ldg(a.ptr + e);
-            const float4 t = a.w.pts[s];
-            const int cell = __float_as_int(t.w);
-            const int ce = cell / g.g1, cp = cell - ce * g.g1;
-            int rlo[6], rhi[6];
-            const int nr = nbhd_runs(g, a.w.cell_start + (size_t)e * (CMAX + 1), ce, cp, cp, a.phi_wrap, rlo, rhi);
-            const int words = (n_e + 31) >> 5;
-            if (words > a.mask_words) {                        // host promised a smaller max_event_nodes
-                if (lane == 0) atomicOr(a.w.stats + 3, GM_FLAG_EVENT_TOO_LARGE);
-                continue;
-            }
-            int total = 0;                                     // pass 1: count only
-            for (int q = 0; q < nr; ++q)
-                for (int k = rlo[q] + lane; k < rhi[q]; k += 32) {
-                    const float4 c = a.w.pts[k];
-                    total += dist2(t.x, t.y, c.x, c.y, a.dim, a.phi_wrap) < a.r2;
-                }
-            total = warp_sum_int(total);
-            local_max = max(local_max, total);
-            if (total <= a.cap_eff) continue;
-            for (int w = lane; w < words; w += 32) mask[w] = 0u;   // pass 2: mark hits by original index, find the cap-th
-            __syncwarp();
-            for (int q = 0; q < nr; ++q)
-                for (int k = rlo[q] + lane; k < rhi[q]; k += 32) {
-                    const float4 c = a.w.pts[k];
-                    if (dist2(t.x, t.y, c.x, c.y, a.dim, a.phi_wrap) < a.r2) {
-                        const int cl = __float_as_int(c.z);
-                        atomicOr(mask + (cl >> 5), 1u << (cl & 31));
-                    }
-                }
-            __syncwarp();
-            int found = 0x7fffffff, seen = 0;
-            for (int w0 = 0; w0 < words; w0 += 32) {
-                const unsigned int word = (w0 + lane < words) ? mask[w0 + lane] : 0u;
-                int tot;
-                const int before = seen + warp_excl_scan_int(__popc(word), lane, tot);
-                if (before < a.cap_eff && before + __popc(word) >= a.cap_eff) {
-                    unsigned int v = word;
-                    for (int k = a.cap_eff - before - 1; k > 0; --k) v &= v - 1;
-                    found = ((w0 + lane) << 5) + __ffs(v) - 1;
-                }
-                seen += tot;
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) found = min(found, __shfl_xor_sync(0xffffffffu, found, o));
-            if (lane == 0 && seen > a.cap_eff) { a.w.thr[s] = found; ++local_capped; }
-            __syncwarp();
-        }
-        if (lane == 0) {
-            if (local_max) atomicMax(a.w.stats + 1, local_max);
-            if (local_capped) { atomicAdd(a.w.stats + 2, local_capped); atomicOr(a.w.stats + 3, GM_FLAG_DEGREE_CAPPED); }
-        }
     }
 }
 
@@ -844,41 +657,13 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
     TimedRegion tr(GM_TIMER_RADIUS_GRAPH, st);
     const float rf = (float)r, r2 = (float)(r * r);          // r*r in double, then fp32
     const int cap_eff = loop ? max_num_neighbors : max_num_neighbors + 1;
-    if (N > 0) {        // one cooperative launch when the grid fits (it always does on a B200 with default limits)
-        const int mask_words = (max_event_nodes + 31) / 32 + 1;
-        const size_t smem = (size_t)8 * mask_words * 4;
-        static int coop = -1;
-        if (coop < 0) {
-            int dev = 0, ok = 0;
-            cudaGetDevice(&dev);
-            cudaDeviceGetAttribute(&ok, cudaDevAttrCooperativeLaunch, dev);
-            coop = ok ? 1 : 0;
-        }
-        if (coop && smem <= 200 * 1024) {
-            if (smem > 48 * 1024)
-                GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_build_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            int per_sm = 0;
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_geo_build_fused, 256, smem) == cudaSuccess && per_sm > 0) {
-                const int grid = persistent_grid((N + 255) / 256, min(per_sm, 4));
-                GeoBuildArgs a{pos, pos_stride, dim, ptr, N, B, rf, r2, phi_wrap, loop, cap_eff, mask_words, w, node_perm_out};
-                void *params[] = {&a};
-                ++::gm::g_launch_count;
-                GM_CUDA_TRY(cudaLaunchCooperativeKernel((const void *)k_geo_build_fused, dim3(grid), dim3(256), params, smem, st));
-                if (stats_out) GM_CUDA_TRY(cudaMemcpyAsync(stats_out, w.stats, 4 * sizeof(int), cudaMemcpyDeviceToDevice, st));
-                return GM_OK;
-            }
-            cudaGetLastError();
-        }
-    }
     GM_TRY(bin_points(pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt, w.cell_start, w.tmp, w.stats, st));
-    k_geo_meta<<<1, 32, 0, st>>>(w.meta, rf, r2, dim, phi_wrap, loop, cap_eff, N, B, w.stats);
+    k_geo_init<<<persistent_grid((N + 255) / 256, 4), 256, 0, st>>>(w.meta, rf, r2, dim, phi_wrap, loop, cap_eff, N, B, ptr, w.ptr,
+                                                                    w.sched, w.thr, w.stats);
     GM_LAUNCH_CHECK();
-    GM_CUDA_TRY(cudaMemcpyAsync(w.ptr, ptr, (size_t)(B + 1) * sizeof(int), cudaMemcpyDeviceToDevice, st));
-    GM_CUDA_TRY(cudaMemsetAsync(w.sched, 0, 4 * sizeof(int), st));
     if (N > 0) {
         k_cell_rank<<<persistent_grid((N + 255) / 256, 8), 256, 0, st>>>(w.tmp, ptr, N, B, w.cell_start, w.pts, node_perm_out);
         GM_LAUNCH_CHECK();
-        GM_CUDA_TRY(cudaMemsetAsync(w.thr, 0x7f, (size_t)N * sizeof(int), st));    // 0x7f7f7f7f: "not capped"
         const int mask_words = (max_event_nodes + 31) / 32 + 1;
         int threads = 256;
         while (threads > 32 && (size_t)(threads / 32) * mask_words * 4 > 200 * 1024) threads >>= 1;
@@ -887,7 +672,7 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
         if (smem > 48 * 1024)
             GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_cap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const int grid = persistent_grid(((long long)N * 32 + threads - 1) / threads, 2048 / threads);
-        int *cap_list = w.cap_list;
+        int *cap_list = reinterpret_cast<int *>(w.tmp);          // tmp is dead once k_cell_rank has run
         k_geo_cap_scan<<<persistent_grid((N + 255) / 256, 8), 256, 0, st>>>(ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts,
                                                                             cap_list, w.sched + 2);
         GM_LAUNCH_CHECK();

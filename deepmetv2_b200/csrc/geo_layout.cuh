@@ -31,7 +31,6 @@ struct GeoWs {
     int *stats;           // [4] E (-1: not counted), max degree seen in dense cells, #capped, flags
     int *sched;           // [4] ticket / finished-CTA counters of the dynamically scheduled (eval) forward kernel,
                           //     [2] = length of the cap-candidate list
-    int *cap_list;        // [N] internal indices of the targets whose 3x3 population exceeds the cap (unordered)
 };
 
 inline size_t geo_ws_layout(int N, int B, char *base, GeoWs *w) {
@@ -53,7 +52,6 @@ inline size_t geo_ws_layout(int N, int B, char *base, GeoWs *w) {
     t.tmp = (float4 *)take(nodes * sizeof(float4));
     t.pts = (float4 *)take(nodes * sizeof(float4));
     t.thr = (int *)take(nodes * sizeof(int));
-    t.cap_list = (int *)take(nodes * sizeof(int));
     if (w) *w = t;
     return off;
 }
