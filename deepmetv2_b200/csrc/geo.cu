@@ -56,12 +56,13 @@ __global__ void __launch_bounds__(256) k_cell_rank(const float4 *__restrict__ tm
                                                    float4 *__restrict__ pts, int *__restrict__ perm) {
     for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < N; s += gridDim.x * blockDim.x) {
         const int e = find_event(ptr, B, s);
-        const float4 t = tmp[s];
+        float4 t = tmp[s];
         const int idx = __float_as_int(t.z), cell = __float_as_int(t.w);
         const int *cs = cell_start + (size_t)e * (CMAX + 1);
         const int lo = __ldg(cs + cell), hi = __ldg(cs + cell + 1);
         int rank = 0;
         for (int k = lo; k < hi; ++k) rank += __float_as_int(tmp[k].z) < idx;
+        t.w = __int_as_float(cell | (e << 10));
         pts[lo + rank] = t;
         perm[lo + rank] = __ldg(ptr + e) + idx;
     }
@@ -81,8 +82,8 @@ __global__ void __launch_bounds__(256) k_geo_cap_scan(const int *__restrict__ pt
         const int s = s0 + lane;
         bool dense = false;
         if (s < N) {
-            const int e = find_event(ptr, B, s);
-            const int cell = __float_as_int(__ldg(&pts[s].w));
+            const float pw = __ldg(&pts[s].w);
+            const int e = pts_event(pw), cell = pts_cell(pw);
             const int ce = cell / g.g1, cp = cell - ce * g.g1;
             int rlo[6], rhi[6];
             const int nr = nbhd_runs(g, cell_start + (size_t)e * (CMAX + 1), ce, cp, cp, m.phi_wrap, rlo, rhi);
@@ -117,10 +118,9 @@ __global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, in
     const int n_list = *count;
     for (int li = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; li < n_list; li += warps) {
         const int s = list[li];
-        const int e = find_event(ptr, B, s);
-        const int base = __ldg(ptr + e), n_e = __ldg(ptr + e + 1) - base;
         const float4 t = pts[s];
-        const int cell = __float_as_int(t.w);
+        const int e = pts_event(t.w), cell = pts_cell(t.w);
+        const int base = __ldg(ptr + e), n_e = __ldg(ptr + e + 1) - base;
         const int ce = cell / g.g1, cp = cell - ce * g.g1;
         int rlo[6], rhi[6];
         const int nr = nbhd_runs(g, cell_start + (size_t)e * (CMAX + 1), ce, cp, cp, m.phi_wrap, rlo, rhi);
@@ -202,8 +202,9 @@ __device__ __forceinline__ void item_segments(const GeoView &v, const CellGrid &
                                               int *s_item) {
     const int node = n0 + lane;
     const bool valid = lane < cnt;
-    const int e = valid ? find_event(v.ptr, B, node) : -1;
-    const int cell = valid ? __float_as_int(v.pts[node].w) : 0;
+    const float pw = valid ? __ldg(&v.pts[node].w) : 0.f;
+    const int e = valid ? pts_event(pw) : -1;
+    const int cell = pts_cell(pw);
     const int key = valid ? ((e << 5) | (cell / g.g1)) : -1;
     const int prev = __shfl_up_sync(0xffffffffu, key, 1);
     const unsigned heads = __ballot_sync(0xffffffffu, valid && (lane == 0 || key != prev));
@@ -649,7 +650,7 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
                  int *node_perm_out, int *stats_out, void *stream) {
     if (N < 0 || B < 1 || !ptr || !ws || (N > 0 && (!pos || !node_perm_out))) return GM_ERR_INVALID_ARGUMENT;
     if (!(r > 0.0) || max_num_neighbors < 1 || max_event_nodes < 0) return GM_ERR_INVALID_ARGUMENT;
-    if (dim < 1 || dim > 2) return GM_ERR_UNSUPPORTED;
+    if (dim < 1 || dim > 2 || B >= GEO_MAX_EVENTS) return GM_ERR_UNSUPPORTED;
     if (ws_bytes < geo_ws_layout(N, B, nullptr, nullptr)) return GM_ERR_CAPACITY;
     cudaStream_t st = as_stream(stream);
     GeoWs w;

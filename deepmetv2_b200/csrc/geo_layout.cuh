@@ -26,12 +26,19 @@ struct GeoWs {
     int *cell_cnt;        // [B*CMAX]   (left at zero after a build)
     int *cell_start;      // [B*(CMAX+1)] start of every cell in internal order (absolute node index)
     float4 *tmp;          // [N] points grouped by (event, cell), arbitrary order inside a cell
-    float4 *pts;          // [N] (eta, phi, local original index bits, cell bits) in internal order
+    float4 *pts;          // [N] (eta, phi, local original index bits, event << 10 | cell) in internal order
     int *thr;             // [N] internal order
     int *stats;           // [4] E (-1: not counted), max degree seen in dense cells, #capped, flags
     int *sched;           // [4] ticket / finished-CTA counters of the dynamically scheduled (eval) forward kernel,
                           //     [2] = length of the cap-candidate list
 };
+
+// pts[].w carries the node's cell (10 bits: CMAX = 1024) and its event, so the staging warps get both from the one
+// load they do anyway instead of a 6-deep dependent binary search over ptr[] per work item (B < 2^21)
+static_assert(CMAX == 1024, "pts.w packing");
+constexpr int GEO_MAX_EVENTS = 1 << 21;
+__device__ __forceinline__ int pts_cell(float w) { return __float_as_int(w) & (CMAX - 1); }
+__device__ __forceinline__ int pts_event(float w) { return (int)((unsigned)__float_as_int(w) >> 10); }
 
 inline size_t geo_ws_layout(int N, int B, char *base, GeoWs *w) {
     size_t off = 0;

@@ -123,8 +123,9 @@ __device__ __forceinline__ void geo_produce(unsigned char *gs, uint32_t full0, u
         if (item >= n_items) break;
         const int n0 = item * GEO_TPI, icnt = min(GEO_TPI, N - n0);
         const bool valid = lane < icnt;
-        const int e = valid ? find_event(v.ptr, m.B, n0 + lane) : -1;
-        const int cell = valid ? __float_as_int(__ldg(&v.pts[n0 + lane].w)) : 0;
+        const float pw = valid ? __ldg(&v.pts[n0 + lane].w) : 0.f;         // event << 10 | cell
+        const int e = valid ? pts_event(pw) : -1;
+        const int cell = pts_cell(pw);
         const int key = valid ? ((e << 5) | (cell / g.g1)) : -1;
         const int prev = __shfl_up_sync(0xffffffffu, key, 1);
         unsigned heads = __ballot_sync(0xffffffffu, valid && (lane == 0 || key != prev));
