@@ -372,7 +372,9 @@ def main():
         achieved = 4096.0 * E_avg / dur / 1e12
         peak = peaks["bf16_tflops_sustained"]
         roofline = {"kernel": ("k_geo_edgeconv_tc (" if implicit else "k_edgeconv_tc (") + args.precision + ")", "bound": "tensor", "achieved": achieved,
-                    "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                    "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                    "traffic": traffic_db.get(args.workload, {}).get(
+                        ("k_geo_edgeconv_tc (" if implicit else "k_edgeconv_tc (") + args.precision + ")"),
                     "avg_launch_us": dur * 1e6, "launches_timed": ec_n,
                     "algorithmic_flops_per_launch": 4096.0 * E_avg, "peak_source": peaks["source"],
                     "share_of_step": ec_ms / total_ms}

@@ -29,7 +29,7 @@ constexpr int AG_CONSUMERS = 8;      // forward kernel: 8 consumer warps (AG_TPW
 constexpr int AG_THREADS = (AG_CONSUMERS + 1) * 32;   // ... + 1 producer warp (segments, descriptors, TMA)
 constexpr int AG_TPW = GEO_TPI / AG_CONSUMERS;
 constexpr int AG_CH = 224;           // staged neighbourhood rows per pipeline stage (2 stages x 3 CTAs fit one SM)
-constexpr int AG_LIST = AG_CH + 8;   // per-warp hit list (uint32 byte offsets of staged rows), padded by 8 identity entries
+constexpr int AG_LIST = AG_CH + 16;  // per-warp hit list (uint32 byte offsets of staged rows), padded by 16 identity entries
 using AgStage = StageL<AG_CH, false>;
 
 // ------------------------------------------------------------------------------------------ build
@@ -273,6 +273,44 @@ __device__ __forceinline__ TargetResult aggr_target(const float4 *s_pts, const f
     return TargetResult{ac, boff == 0xffffffffu ? -1 : (int)(boff >> 7), nh};
 }
 
+// The same reduction with QUARTER-WARP rows (inference: no arg-max, no BatchNorm moments): 8 lanes read one staged row
+// as LDS.128, lane = 4 channels, the 4 lane groups take 4 consecutive list entries each, so one trip covers 16 hits
+// with 1 list load + 4 row loads + 8 three-input max instead of 16 row loads + 16 max.  Every lane group keeps its own
+// partial over the chunks of a segment; the groups are folded once per target (2 shuffles per channel).
+template <int AGGR>
+__device__ __forceinline__ float4 aggr_rows_q4(const float *s_rows, const unsigned *list, int nh, float4 ac, int lane) {
+    const uint32_t base = smem_u32(s_rows) + (uint32_t)((lane & 7) * 16);
+    const unsigned *mine = list + 4 * (lane >> 3);
+    auto lds4 = [](uint32_t a) {
+        float4 q;
+        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(q.x), "=f"(q.y), "=f"(q.z), "=f"(q.w) : "r"(a));
+        return q;
+    };
+    for (int k = 0; k < nh; k += 16) {
+        const uint4 o = *reinterpret_cast<const uint4 *>(mine + k);
+        const float4 r0 = lds4(base + o.x), r1 = lds4(base + o.y), r2 = lds4(base + o.z), r3 = lds4(base + o.w);
+        if (AGGR == GM_AGGR_MAX) {
+            ac.x = fmaxf(fmaxf(fmaxf(ac.x, r0.x), r1.x), fmaxf(r2.x, r3.x));
+            ac.y = fmaxf(fmaxf(fmaxf(ac.y, r0.y), r1.y), fmaxf(r2.y, r3.y));
+            ac.z = fmaxf(fmaxf(fmaxf(ac.z, r0.z), r1.z), fmaxf(r2.z, r3.z));
+            ac.w = fmaxf(fmaxf(fmaxf(ac.w, r0.w), r1.w), fmaxf(r2.w, r3.w));
+        } else {
+            ac.x += (r0.x + r1.x) + (r2.x + r3.x);
+            ac.y += (r0.y + r1.y) + (r2.y + r3.y);
+            ac.z += (r0.z + r1.z) + (r2.z + r3.z);
+            ac.w += (r0.w + r1.w) + (r2.w + r3.w);
+        }
+    }
+    return ac;
+}
+template <int AGGR>
+__device__ __forceinline__ float fold_groups(float v) {             // over the 4 lane groups (lanes l, l^8, l^16, l^24)
+    const float a = __shfl_xor_sync(0xffffffffu, v, 8);
+    v = AGGR == GM_AGGR_MAX ? fmaxf(v, a) : v + a;
+    const float b = __shfl_xor_sync(0xffffffffu, v, 16);
+    return AGGR == GM_AGGR_MAX ? fmaxf(v, b) : v + b;
+}
+
 // ------------------------------------------------------------------------------------------ forward: aggregate
 // out_i = P_i + max_{j in N(i)} Y_j (add / mean alike), warp-specialised.
 //   producer warp : walks the CTA's items, cuts them into segments, computes the neighbourhood runs and streams the
@@ -286,7 +324,7 @@ __device__ __forceinline__ TargetResult aggr_target(const float4 *s_pts, const f
 // full[s] (1 arrival + TMA bytes) / empty[s] (AG_CONSUMERS arrivals) mbarriers; no CTA-wide barrier in the main loop.
 // Items are scheduled statically (item = blockIdx + k * gridDim) when BatchNorm partials are produced, so the per-CTA
 // moments are bit-reproducible; without them (eval) the producer takes tickets from a self-resetting counter.
-template <int AGGR, bool ARG>
+template <int AGGR, bool ARG, bool Q4 = false>
 __global__ void __launch_bounds__(AG_THREADS, 3)
 k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, int N, float *__restrict__ out,
            int *__restrict__ arg, AggrTail tail) {
@@ -308,13 +346,19 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
     if (warp == AG_CONSUMERS) {
         // ================================================================== producer
         geo_produce<AgStage, false>(gs, full0, empty0, v, m, Y, N, dynamic, lane);
-    } else {
-        // ================================================================== consumers
+    } else if constexpr (Q4) {
+        // ================================================================== consumers, quarter-warp rows (inference)
+        // Per-slot state lives in REGISTERS, not in a dynamically indexed (= local-memory) array: lane u holds the
+        // point / cap threshold / degree of target slot u (fetched with one shuffle each), and the four running
+        // accumulators are four scalars selected by a warp-uniform branch.  After a (target, chunk) the four lane
+        // groups are folded and lane (g, c4) keeps channel 4 * c4 + g.
+        static_assert(AG_TPW == 4, "one scalar accumulator per target slot");
         unsigned *list = reinterpret_cast<unsigned *>(gs + AG_LISTS) + warp * AG_LIST;
-        float px[AG_TPW], py[AG_TPW], acc[AG_TPW];
-        int th[AG_TPW], excl[AG_TPW], barg[AG_TPW], deg[AG_TPW];
-#pragma unroll
-        for (int u = 0; u < AG_TPW; ++u) { px[u] = py[u] = 0.f; acc[u] = IDENT; th[u] = 0; excl[u] = -1; barg[u] = -1; deg[u] = 0; }
+        const int grp = lane >> 3, c4 = lane & 7, ch = 4 * c4 + grp;
+        float px_l = 0.f, py_l = 0.f, acc0 = IDENT, acc1 = IDENT, acc2 = IDENT, acc3 = IDENT;
+        int th_l = 0, excl_l = -1, deg_l = 0;
+        GeoMeta mm;
+        mm.r2 = m.r2; mm.dim = m.dim; mm.phi_wrap = m.phi_wrap;
         for (uint32_t gc = 0;; ++gc) {
             const int st = gc & 1;
             const unsigned char *stage = gs + st * AG_STAGE_BYTES;
@@ -326,29 +370,36 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
             const float *s_rows = reinterpret_cast<const float *>(stage);
             const float4 *s_pts = reinterpret_cast<const float4 *>(stage + AG_OFF_PTS);
             if (flags & AG_FIRST) {
-                const float4 *s_tgt = reinterpret_cast<const float4 *>(stage + AG_OFF_TGT);
-                const int *s_thr = reinterpret_cast<const int *>(stage + AG_OFF_THR);
-#pragma unroll
-                for (int u = 0; u < AG_TPW; ++u) {
-                    const int t = a + warp + u * AG_CONSUMERS;
-                    acc[u] = IDENT; barg[u] = -1; deg[u] = 0;
-                    if (t < b) {
-                        const float4 pt = s_tgt[t];
-                        px[u] = pt.x; py[u] = pt.y;
-                        th[u] = s_thr[t];
-                        excl[u] = m.loop ? -1 : __float_as_int(pt.z);
-                    }
+                acc0 = acc1 = acc2 = acc3 = IDENT;
+                deg_l = 0;
+                const int t = a + warp + lane * AG_CONSUMERS;                   // lanes 0..3: slot = lane
+                if (lane < AG_TPW && t < b) {
+                    const float4 pt = reinterpret_cast<const float4 *>(stage + AG_OFF_TGT)[t];
+                    px_l = pt.x; py_l = pt.y;
+                    th_l = reinterpret_cast<const int *>(stage + AG_OFF_THR)[t];
+                    excl_l = m.loop ? -1 : __float_as_int(pt.z);
                 }
             }
-#pragma unroll 1                                                                // one copy of the body: see aggr_target
+#pragma unroll 1
             for (int u = 0; u < AG_TPW; ++u) {
                 if (a + warp + u * AG_CONSUMERS >= b) break;                    // warp-uniform
-                const TargetResult tr = aggr_target<AGGR, ARG>(s_pts, s_rows, rows, px[u], py[u], th[u], excl[u], acc[u],
-                                                               m.r2, m.dim, m.phi_wrap, lane, list);
-                deg[u] += tr.nh;
-                acc[u] = tr.ac;
-                const int brow = tr.brow;
-                if (ARG && brow >= 0) barg[u] = node_of_row(d, brow);
+                const float px = __shfl_sync(0xffffffffu, px_l, u), py = __shfl_sync(0xffffffffu, py_l, u);
+                const int th = __shfl_sync(0xffffffffu, th_l, u), excl = __shfl_sync(0xffffffffu, excl_l, u);
+                const int nh = build_hit_list<AG_CH>(s_pts, rows, px, py, th, excl, mm, lane, list);
+                if (lane == u) deg_l += nh;
+                if (nh > 0) {
+                    float4 v4 = aggr_rows_q4<AGGR>(s_rows, list, nh, make_float4(IDENT, IDENT, IDENT, IDENT), lane);
+                    v4.x = fold_groups<AGGR>(v4.x); v4.y = fold_groups<AGGR>(v4.y);
+                    v4.z = fold_groups<AGGR>(v4.z); v4.w = fold_groups<AGGR>(v4.w);
+                    const float mine = grp == 0 ? v4.x : grp == 1 ? v4.y : grp == 2 ? v4.z : v4.w;
+                    if (AGGR == GM_AGGR_MAX) {
+                        if (u == 0) acc0 = fmaxf(acc0, mine); else if (u == 1) acc1 = fmaxf(acc1, mine);
+                        else if (u == 2) acc2 = fmaxf(acc2, mine); else acc3 = fmaxf(acc3, mine);
+                    } else {
+                        if (u == 0) acc0 += mine; else if (u == 1) acc1 += mine;
+                        else if (u == 2) acc2 += mine; else acc3 += mine;
+                    }
+                }
                 __syncwarp();                                   // the hit list is reused by the next target
             }
             __syncwarp();
@@ -357,16 +408,86 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
 #pragma unroll
                 for (int u = 0; u < AG_TPW; ++u) {
                     const int t = a + warp + u * AG_CONSUMERS;
+                    const int dg = __shfl_sync(0xffffffffu, deg_l, u);
                     if (t >= b) continue;
+                    const float acc = u == 0 ? acc0 : u == 1 ? acc1 : u == 2 ? acc2 : acc3;
+                    const size_t node = (size_t)(n0 + t);
+                    const float p = __ldg(P + node * H + ch);
+                    float o;
+                    if (dg == 0) o = 0.f;                                      // PyG: empty rows aggregate to 0
+                    else if (AGGR == GM_AGGR_MAX) o = p + acc;
+                    else if (AGGR == GM_AGGR_ADD) o = fmaf((float)dg, p, acc);
+                    else o = fmaf(acc, 1.f / (float)dg, p);
+                    out[node * H + ch] = o;
+                }
+            }
+        }
+    } else {
+        // ================================================================== consumers (lane = channel; training: arg-max)
+        // Per-slot state in registers (see the quarter-warp variant): lane u holds slot u's point / threshold / degree,
+        // the running max and arg-max of the four slots are eight scalars picked by a warp-uniform branch.
+        static_assert(AG_TPW == 4, "one scalar accumulator per target slot");
+        unsigned *list = reinterpret_cast<unsigned *>(gs + AG_LISTS) + warp * AG_LIST;
+        float px_l = 0.f, py_l = 0.f, acc0 = IDENT, acc1 = IDENT, acc2 = IDENT, acc3 = IDENT;
+        int th_l = 0, excl_l = -1, deg_l = 0, barg0 = -1, barg1 = -1, barg2 = -1, barg3 = -1;
+        for (uint32_t gc = 0;; ++gc) {
+            const int st = gc & 1;
+            const unsigned char *stage = gs + st * AG_STAGE_BYTES;
+            mbar_wait(full0 + 8u * st, (gc >> 1) & 1u);
+            const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + AG_OFF_DESC);
+            const int flags = d->flags;
+            if (flags & AG_END) break;
+            const int a = d->a, b = d->b, rows = d->rows, n0 = d->n0;
+            const float *s_rows = reinterpret_cast<const float *>(stage);
+            const float4 *s_pts = reinterpret_cast<const float4 *>(stage + AG_OFF_PTS);
+            if (flags & AG_FIRST) {
+                acc0 = acc1 = acc2 = acc3 = IDENT;
+                barg0 = barg1 = barg2 = barg3 = -1;
+                deg_l = 0;
+                const int t = a + warp + lane * AG_CONSUMERS;                   // lanes 0..3: slot = lane
+                if (lane < AG_TPW && t < b) {
+                    const float4 pt = reinterpret_cast<const float4 *>(stage + AG_OFF_TGT)[t];
+                    px_l = pt.x; py_l = pt.y;
+                    th_l = reinterpret_cast<const int *>(stage + AG_OFF_THR)[t];
+                    excl_l = m.loop ? -1 : __float_as_int(pt.z);
+                }
+            }
+#pragma unroll 1                                                                // one copy of the body: see aggr_target
+            for (int u = 0; u < AG_TPW; ++u) {
+                if (a + warp + u * AG_CONSUMERS >= b) break;                    // warp-uniform
+                const float px = __shfl_sync(0xffffffffu, px_l, u), py = __shfl_sync(0xffffffffu, py_l, u);
+                const int th = __shfl_sync(0xffffffffu, th_l, u), excl = __shfl_sync(0xffffffffu, excl_l, u);
+                const float ac = u == 0 ? acc0 : u == 1 ? acc1 : u == 2 ? acc2 : acc3;
+                const TargetResult tr = aggr_target<AGGR, ARG>(s_pts, s_rows, rows, px, py, th, excl, ac,
+                                                               m.r2, m.dim, m.phi_wrap, lane, list);
+                if (lane == u) deg_l += tr.nh;
+                const int brow = tr.brow;
+                const int bnode = (ARG && brow >= 0) ? node_of_row(d, brow) : -1;
+                if (u == 0) { acc0 = tr.ac; if (ARG && brow >= 0) barg0 = bnode; }
+                else if (u == 1) { acc1 = tr.ac; if (ARG && brow >= 0) barg1 = bnode; }
+                else if (u == 2) { acc2 = tr.ac; if (ARG && brow >= 0) barg2 = bnode; }
+                else { acc3 = tr.ac; if (ARG && brow >= 0) barg3 = bnode; }
+                __syncwarp();                                   // the hit list is reused by the next target
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty0 + 8u * st);       // this warp is done with the stage
+            if (flags & AG_LAST) {
+#pragma unroll
+                for (int u = 0; u < AG_TPW; ++u) {
+                    const int t = a + warp + u * AG_CONSUMERS;
+                    const int dg = __shfl_sync(0xffffffffu, deg_l, u);
+                    if (t >= b) continue;
+                    const float acc = u == 0 ? acc0 : u == 1 ? acc1 : u == 2 ? acc2 : acc3;
+                    const int barg = u == 0 ? barg0 : u == 1 ? barg1 : u == 2 ? barg2 : barg3;
                     const size_t node = (size_t)(n0 + t);
                     const float p = __ldg(P + node * H + lane);
                     float o;
-                    if (deg[u] == 0) o = 0.f;                                  // PyG: empty rows aggregate to 0
-                    else if (AGGR == GM_AGGR_MAX) o = p + acc[u];
-                    else if (AGGR == GM_AGGR_ADD) o = fmaf((float)deg[u], p, acc[u]);
-                    else o = fmaf(acc[u], 1.f / (float)deg[u], p);
+                    if (dg == 0) o = 0.f;                                      // PyG: empty rows aggregate to 0
+                    else if (AGGR == GM_AGGR_MAX) o = p + acc;
+                    else if (AGGR == GM_AGGR_ADD) o = fmaf((float)dg, p, acc);
+                    else o = fmaf(acc, 1.f / (float)dg, p);
                     out[node * H + lane] = o;
-                    if (ARG) arg[node * H + lane] = barg[u];
+                    if (ARG) arg[node * H + lane] = barg;
                     if (tail.partials) {
                         if (cnt == 0.f) shift = o;
                         cnt += 1.f;
@@ -580,12 +701,16 @@ __global__ void __launch_bounds__(RM_THREADS) k_row_moments(const float *__restr
 template <int AGGR>
 int launch_geo_aggr(const float *Y, const float *P, const GeoView &v, int N, float *out, int *arg,
                     const AggrTail &tail, cudaStream_t st) {
-    static int occ[2] = {0, 0};
-    const int which = arg ? 1 : 0;
+    static int occ[3] = {0, 0, 0};
+    const bool q4 = !arg && !tail.partials;              // inference: quarter-warp rows
+    const int which = arg ? 1 : (q4 ? 2 : 0);
     if (!occ[which]) {
         if (arg) {
             GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_aggr<AGGR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AG_TOTAL));
             occ[1] = resident_ctas(k_geo_aggr<AGGR, true>, AG_THREADS, AG_TOTAL, 3);
+        } else if (q4) {
+            GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_aggr<AGGR, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AG_TOTAL));
+            occ[2] = resident_ctas(k_geo_aggr<AGGR, false, true>, AG_THREADS, AG_TOTAL, 3);
         } else {
             GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_aggr<AGGR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AG_TOTAL));
             occ[0] = resident_ctas(k_geo_aggr<AGGR, false>, AG_THREADS, AG_TOTAL, 3);
@@ -598,6 +723,7 @@ int launch_geo_aggr(const float *Y, const float *P, const GeoView &v, int N, flo
     const bool split = tail.partials && (long long)(N + GEO_TPI - 1) / GEO_TPI >= 8LL * grid;
     const AggrTail in_kernel = split ? AggrTail{} : tail;
     if (arg) k_geo_aggr<AGGR, true><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, in_kernel);
+    else if (q4) k_geo_aggr<AGGR, false, true><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, in_kernel);
     else k_geo_aggr<AGGR, false><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, in_kernel);
     GM_LAUNCH_CHECK();
     if (split) {

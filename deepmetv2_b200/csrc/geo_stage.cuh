@@ -191,7 +191,7 @@ __device__ __forceinline__ void geo_produce(unsigned char *gs, uint32_t full0, u
 }
 
 // Hit list of one target against the staged chunk: BYTE OFFSETS (row * 128) of the rows whose point passes the edge
-// predicate of geo_layout.cuh, in staged order, padded with 8 x the identity row (row CH).  th = cap threshold of the
+// predicate of geo_layout.cuh, in staged order, padded with 16 x the identity row (row CH).  th = cap threshold of the
 // target, excl = local index to exclude (the target itself when loop == 0, -1 otherwise).  Returns the hit count.
 template <int CH>
 __device__ __forceinline__ int build_hit_list(const float4 *s_pts, int rows, float px, float py, int th, int excl,
@@ -216,7 +216,7 @@ __device__ __forceinline__ int build_hit_list(const float4 *s_pts, int rows, flo
             nh += __popc(mk);
         }
     }
-    if (lane < 8) list[nh + lane] = (unsigned)CH << 7;
+    if (lane < 16) list[nh + lane] = (unsigned)CH << 7;      // list capacity: CH + 16
     __syncwarp();
     return nh;
 }

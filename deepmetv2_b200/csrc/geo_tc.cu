@@ -37,7 +37,7 @@ namespace {
 #ifndef GT_NC_TF32
 #define GT_NC_TF32 8                                  // tf32 operand blocks are twice as large
 #endif
-constexpr int GT_LIST = GT_CH + 8;
+constexpr int GT_LIST = GT_CH + 16;                   // build_hit_list pads 16 entries
 constexpr int GT_BLK = 32;                            // edge columns per MMA block (MMA N)
 constexpr int GT_LBO = 192;                           // bytes between the 16-byte K chunks of an 8-row group: 4 rows x
                                                       // (4 | 8) chunks of a warp store land on distinct banks

@@ -5,7 +5,7 @@
 //   k_scatter_s       : S[j][c] = sum_{i: argmax_src(i,c) == j} d(conv)[i][c]  as a GATHER over the
 //                       transposed CSR (max-aggregation routes each (target,channel) gradient to one edge);
 //                       d(conv) = BatchNorm backward of G, evaluated on the fly for the matching entries only
-//   k_conv_bwd_node   : G += (W1-W2)^T d(conv) + W2^T S ; partial dW1 = dconv (x) x, dW2 = (S-dconv) (x) x ;
+//   k_conv_bwd_node2  : G += (W1-W2)^T d(conv) + W2^T S ; partial dW1 = dconv (x) x, dW2 = (S-dconv) (x) x ;
 //                       BatchNorm sums of the layer below
 //   k_encode_bwd      : BN_all backward on the fly -> encode_all / embed_continuous / embed_categorical / 3 tables
 //   k_reduce_partials : ONE launch: fixed-order sum of every stage's per-CTA partials into the gradient tensors
@@ -366,83 +366,6 @@ __global__ void __launch_bounds__(256) k_scatter_s(const float *__restrict__ G, 
 
 // ----------------------------------------------------------------------------------------- EdgeConv node-level backward
 // partial layout: dW1[32][32] @0, dW2[32][32] @1024, db[32] @2048
-__global__ void __launch_bounds__(NODE_TILE, 2)
-k_conv_bwd_node(const float *__restrict__ x, const float *__restrict__ raw, BnBwd bn, const float *__restrict__ S, int N,
-                const float *__restrict__ W, float *__restrict__ G, float *__restrict__ gpart, BnSumOut bo) {
-    extern __shared__ __align__(16) float smem[];
-    float *s_wd = smem;                  // W1 - W2, [c][k]
-    float *s_w2 = s_wd + H * H;
-    float *tA = s_w2 + H * H;            // d(conv)            then  G_new
-    float *tB = tA + NODE_TILE * GLD;    // x                  then  G_new * xhat(below)
-    float *tC = tB + NODE_TILE * GLD;    // S - d(conv)
-    float *s_coef = tC + NODE_TILE * GLD;   // [5][32]
-    float *s_mean = s_coef + 5 * H;      // BatchNorm below: mean, invstd
-    float *s_inv = s_mean + H;
-    const int t = threadIdx.x;
-    for (int i = t; i < H * H; i += NODE_TILE) {
-        const int c = i >> 5, k = i & 31;
-        const float a = W[c * CONV_IN + k], b = W[c * CONV_IN + H + k];
-        s_wd[i] = a - b; s_w2[i] = b;
-    }
-    bn_bwd_coeffs(bn, s_coef);
-    if (t < H) { s_mean[t] = bo.stat[t]; s_inv[t] = bo.stat[2 * H + t]; }
-    __syncthreads();
-    Outer<H, H> o1, o2; o1.zero(); o2.zero();
-    ColSum<H> cb, sg, sgx; cb.zero(); sg.zero(); sgx.zero();
-    const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
-    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        const int node0 = tile * NODE_TILE, rows = min(NODE_TILE, N - node0);
-        float g[H];
-        if (t < rows) {
-            const size_t n = (size_t)(node0 + t) * H;
-            float dc[H], s[H], tmp[H];
-            load_row32(G + n, g);
-            load_row32(raw + n, tmp);
-#pragma unroll
-            for (int k = 0; k < H; ++k) dc[k] = bn_bwd_one(s_coef, k, g[k], tmp[k]);
-            load_row32(S + n, s);
-            dense_t_smem<H, H>(s_wd, dc, tmp);
-#pragma unroll
-            for (int k = 0; k < H; ++k) g[k] += tmp[k];
-            dense_t_smem<H, H>(s_w2, s, tmp);
-#pragma unroll
-            for (int k = 0; k < H; ++k) g[k] += tmp[k];
-            store_row<H>(G + n, g);
-            store_row<H>(tA + t * GLD, dc);
-#pragma unroll
-            for (int k = 0; k < H; ++k) s[k] -= dc[k];
-            store_row<H>(tC + t * GLD, s);
-            load_row32(x + n, tmp);
-            store_row<H>(tB + t * GLD, tmp);
-        }
-        __syncthreads();
-        o1.accumulate(tA, GLD, tB, GLD, rows);
-        o2.accumulate(tC, GLD, tB, GLD, rows);
-        cb.accumulate(tA, GLD, rows);
-        __syncthreads();
-        if (t < rows) {   // BatchNorm sums of the layer below (bn_all for layer 0)
-            float rb[H];
-            load_row32(bo.raw + (size_t)(node0 + t) * H, rb);
-            store_row<H>(tA + t * GLD, g);
-#pragma unroll
-            for (int k = 0; k < H; ++k) rb[k] = g[k] * ((rb[k] - s_mean[k]) * s_inv[k]);
-            store_row<H>(tB + t * GLD, rb);
-        }
-        __syncthreads();
-        sg.accumulate(tA, GLD, rows);
-        sgx.accumulate(tB, GLD, rows);
-        __syncthreads();
-    }
-    float *dst = gpart + (size_t)blockIdx.x * GP_STRIDE;
-    o1.flush(tA, dst);
-    o2.flush(tA, dst + 1024);
-    cb.flush(tA, dst + 2048, H);
-    float *bp = bo.part + (size_t)blockIdx.x * 64;
-    sg.flush(tA, bp, H);
-    sgx.flush(tA, bp + H, H);
-    if (last_cta_done(bo.counter)) bn_sums_finalize(bo, tA);
-}
-
 // Same stage on the register-blocked tile product (common.cuh): 256 threads per 128-node tile.  Cooperative,
 // coalesced float4 loads build the tiles d(conv) = BatchNorm backward of G, S and x in shared memory; the two
 // 32x32 transposed products run as tile_gemm with the accumulators initialised from G (4 nodes x 4 channels per

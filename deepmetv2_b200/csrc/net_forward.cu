@@ -1,6 +1,6 @@
 // Forward of the GraphMETNetwork hot path (model/graph_met_network.py:47-69, model/net.py:45-47):
 //   k_build_lut   : the 168-entry categorical table ELU(Linear_24->16(cat[E_chrg,E_pdg,E_pv]))
-//   k_encode      : fused embeddings + continuous encoder + encode_all (+ BatchNorm moments)   [a3,a4]
+//   k_encode2     : fused embeddings + continuous encoder + encode_all (+ BatchNorm moments)   [a3,a4]
 //   k_node_prep   : emb_l = (resid +) BN(raw) ; Y = W2 emb_l ; P = (W1-W2) emb_l + b            [K4 + a5, node side]
 //   k_edge_aggr   : out_i = P_i + max_j Y_j over the CSR row (segmented, atomics-free) + BN moments [a5, edge side]
 //   k_edgeconv_simt: fp32 EdgeConv with the per-edge contraction W2 (x_j - x_i) spelled out (cross-check variant)
@@ -47,29 +47,6 @@ __global__ void __launch_bounds__(256) k_build_lut(GmParams p, float *__restrict
     lut[idx] = elu(acc);
 }
 
-// ------------------------------------------------------------------------------------------ moments
-// Moments of the valid rows of a [NODE_TILE][TILE_LD] smem tile, per channel, folded into the CTA's
-// running moments held by threads 0..31.  blockDim.x == NODE_TILE (4 warps).
-__device__ __forceinline__ void tile_moments(const float *tile, int rows, float (*red)[3][H], Moments &run) {
-    const int c = threadIdx.x & 31, q = threadIdx.x >> 5;
-    const int r0 = q * 32, r1 = min(rows, r0 + 32);
-    float n = (float)max(r1 - r0, 0), mean = 0.f, m2 = 0.f;
-    if (r1 > r0) {
-        float s = 0.f;
-        for (int r = r0; r < r1; ++r) s += tile[r * TILE_LD + c];
-        mean = s / n;
-        for (int r = r0; r < r1; ++r) { float d = tile[r * TILE_LD + c] - mean; m2 = fmaf(d, d, m2); }
-    }
-    red[q][0][c] = n; red[q][1][c] = mean; red[q][2][c] = m2;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-#pragma unroll
-        for (int g = 0; g < NODE_TILE / 32; ++g)
-            run = moments_combine(run, Moments{red[g][0][c], red[g][1][c], red[g][2][c]});
-    }
-    __syncthreads();
-}
-
 __device__ __forceinline__ void store_tile(const float *tile, float *__restrict__ out, int node0, int rows) {
     // coalesced float4 stores of a [rows][32] tile
     for (int idx = threadIdx.x; idx < rows * (H / 4); idx += blockDim.x) {
@@ -103,94 +80,6 @@ __device__ __forceinline__ int cat_combo(long long pdg, long long chg, long long
         iv = iv < 0 ? 0 : (iv > 7 ? 7 : iv);
     }
     return (int)((ic * 7 + ip) * 8 + iv);
-}
-
-__global__ void __launch_bounds__(NODE_TILE) k_encode(EncodeArgs a) {
-    __shared__ __align__(16) float s_cont_w[16 * 8];
-    __shared__ float s_cont_b[16];
-    __shared__ __align__(16) float s_enc_w[H * H];
-    __shared__ float s_enc_b[H];
-    __shared__ __align__(16) float s_lut[LUT_ROWS * 16];
-    __shared__ __align__(16) float s_x[NODE_TILE * 16];
-    __shared__ float s_tile[NODE_TILE * TILE_LD];
-    __shared__ float s_red[NODE_TILE / 8][3][H];   // tile_moments uses 4 slices, the last-CTA finalize all 16
-
-    const int t = threadIdx.x;
-    for (int i = t; i < 16 * 8; i += NODE_TILE) {
-        int o = i >> 3, k = i & 7;
-        s_cont_w[i] = k < a.CD ? a.cont_w[o * a.CD + k] : 0.f;
-    }
-    if (t < 16) s_cont_b[t] = a.cont_b[t];
-    for (int i = t; i < H * H; i += NODE_TILE) s_enc_w[i] = a.enc_w[i];
-    if (t < H) s_enc_b[t] = a.enc_b[t];
-    for (int i = t; i < LUT_ROWS * 16; i += NODE_TILE) s_lut[i] = a.lut[i];
-    __syncthreads();
-
-    Moments run{0.f, 0.f, 0.f};
-    int err = 0;
-    const int tiles = (a.N + NODE_TILE - 1) / NODE_TILE;
-    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        const int node0 = tile * NODE_TILE;
-        const int rows = min(NODE_TILE, a.N - node0);
-        float xc[8];
-        long long c0 = 0, c1 = 0, c2 = 0;
-        if (a.flat) {
-            const int S = a.x_cont_stride;
-            const float *src = a.x_cont + (size_t)node0 * S;
-            for (int i = t; i < rows * S; i += NODE_TILE) s_x[i] = src[i];
-            __syncthreads();
-            if (t < rows) {
-                const float *row = s_x + t * S;
-                const int cat_off = (int)(a.x_cat_f32 - a.x_cont);
-#pragma unroll
-                for (int k = 0; k < 8; ++k) xc[k] = k < a.CD ? row[k] : 0.f;
-                c0 = (long long)row[cat_off]; c1 = (long long)row[cat_off + 1]; c2 = (long long)row[cat_off + 2];
-            }
-        } else if (t < rows) {
-            const size_t n = a.perm ? (size_t)a.perm[node0 + t] : (size_t)(node0 + t);
-            const float *row = a.x_cont + n * a.x_cont_stride;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) xc[k] = k < a.CD ? row[k] : 0.f;
-            if (a.x_cat_i64) {
-                const long long *cr = a.x_cat_i64 + n * 3;
-                c0 = cr[0]; c1 = cr[1]; c2 = cr[2];
-            } else {
-                const float *cr = a.x_cat_f32 + n * a.x_cat_stride;
-                c0 = (long long)cr[0]; c1 = (long long)cr[1]; c2 = (long long)cr[2];
-            }
-        }
-        if (t < rows) {
-            float u[H];  // cat[emb_cat, emb_cont]  (model/graph_met_network.py:58)
-            const int combo = cat_combo(c0, c1, c2, &err);
-            const float4 *l4 = reinterpret_cast<const float4 *>(s_lut + combo * 16);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                float4 v = l4[k];
-                u[4 * k] = v.x; u[4 * k + 1] = v.y; u[4 * k + 2] = v.z; u[4 * k + 3] = v.w;
-            }
-            float h0[16];
-            dense_smem<8, 16>(s_cont_w, s_cont_b, xc, h0);
-#pragma unroll
-            for (int k = 0; k < 16; ++k) u[16 + k] = elu(h0[k]);
-            float z[H];
-            dense_smem<H, H>(s_enc_w, s_enc_b, u, z);
-#pragma unroll
-            for (int k = 0; k < H; ++k) s_tile[t * TILE_LD + k] = elu(z[k]);
-        }
-        __syncthreads();
-        store_tile(s_tile, a.enc_out, node0, rows);
-        if (a.partials) tile_moments(s_tile, rows, s_red, run);
-        else __syncthreads();
-    }
-    if (err) atomicOr(a.err_flags, GM_FLAG_CAT_OUT_OF_RANGE);
-    if (a.partials) {
-        if (t < 32) {
-            float *dst = a.partials + (size_t)blockIdx.x * MOM_STRIDE;
-            dst[t] = run.n; dst[H + t] = run.mean; dst[2 * H + t] = run.m2;
-        }
-        if (last_cta_done(a.counter))
-            bn_finalize_cta(a.partials, gridDim.x, a.bn, a.momentum, a.eps, a.stat, s_red);
-    }
 }
 
 // Encoder on the register-blocked tile product: 256 threads per 128-node tile.  Threads 0..127 build the node's
@@ -833,7 +722,6 @@ int edgeconv_direct(const float *x, const int *rowptr, const int *col, int N, co
 }
 
 int node_grid(int N) { return persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 4); }
-int encode_grid(int N) { return persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 4); }
 
 }  // namespace
 

@@ -106,3 +106,23 @@ def test_tc_geo_network_eval_step(prec, wtol):
     rel = ((w.cpu() - w_ref).abs() / w_ref.abs()).max().item()
     assert rel < wtol, rel
     assert abs(loss.item() - loss_ref.item()) < 10 * wtol * abs(loss_ref.item())
+
+
+@pytest.mark.parametrize("prec", ["bf16", "tf32"])
+def test_tc_geo_edge_set_with_phi_wrap(prec):
+    """The opt-in periodic phi grid through the tcgen05 path: neighbourhoods wrap across +-pi."""
+    b, etaphi = _events("dytt", [600, 450], 9)
+    ptr = b.ptr.long()
+    pos_d, ptr_d = etaphi.to(DEV), b.ptr.to(DEV).int()
+    g, ei = ops.build_graph(pos_d, 0.4, ptr_i32=ptr_d, loop=True, max_num_neighbors=255, phi_wrap=True,
+                            want_edge_index=True)
+    geo = ops.build_geo(pos_d, 0.4, ptr_d, loop=True, max_num_neighbors=255, phi_wrap=True)
+    N = etaphi.shape[0]
+    perm = geo.perm[:N].long()
+    x = _hash_features(ptr)
+    want = torch.zeros(N, 32, dtype=torch.float64)
+    eic = ei.cpu()
+    want.index_add_(0, eic[1], x[eic[0]].double())
+    W = torch.zeros(32, 64); W[:, :32] = torch.eye(32); W[:, 32:] = torch.eye(32)
+    got = ops.edgeconv_geo(x.to(DEV)[perm], geo, W.to(DEV), torch.zeros(32, device=DEV), aggr="add", precision=prec)
+    assert torch.equal(got.double().cpu(), want[perm.cpu()])
