@@ -253,31 +253,33 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
                     __syncwarp();
                     const uint32_t src = smem_u32(stage) + (uint32_t)(c4 * 16);
                     const uint32_t dstl = b_base + lane_off + (uint32_t)(r4 * 16);
-                    // one 8-column group per trip, software-pipelined: the rows of group k + 8 and the list entries of
-                    // group k + 16 are in flight while group k is subtracted, rounded and stored
+                    // the padded hits go into the block in runs bounded by the block end: the inner loop over 8-column
+                    // groups carries no block bookkeeping (two running pointers), the compiler unrolls it by two
                     auto lds4 = [](float4 &q, uint32_t a) {
                         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(q.x), "=f"(q.y), "=f"(q.z), "=f"(q.w) : "r"(a));
                     };
-                    float4 x0, x1;
-                    lds4(x0, src + list[r4]);
-                    lds4(x1, src + list[4 + r4]);
-                    unsigned o0 = list[8 + r4], o1 = list[12 + r4];                 // in bounds (GT_LIST); used only if valid
-                    for (int k = 0; k < nh; k += 8) {
-                        float4 y0 = x0, y1 = x1;
-                        if (k + 8 < nh) { lds4(y0, src + o0); lds4(y1, src + o1); } // warp-uniform
-                        if (k + 16 < nh) { o0 = list[k + 16 + r4]; o1 = list[k + 20 + r4]; }
-                        const uint32_t addr = dstl + (uint32_t)(buf * S::B_BYTES + (fill >> 3) * S::SBO);
-                        if constexpr (TF32) {
-                            gt_sts128(addr, tc5_to_tf32(x0.x - xi.x), tc5_to_tf32(x0.y - xi.y), tc5_to_tf32(x0.z - xi.z), tc5_to_tf32(x0.w - xi.w));
-                            gt_sts128(addr + 64, tc5_to_tf32(x1.x - xi.x), tc5_to_tf32(x1.y - xi.y), tc5_to_tf32(x1.z - xi.z), tc5_to_tf32(x1.w - xi.w));
-                        } else {
-                            gt_sts64(addr, tc5_pack_bf16(x0.x - xi.x, x0.y - xi.y), tc5_pack_bf16(x0.z - xi.z, x0.w - xi.w));
-                            gt_sts64(addr + 64, tc5_pack_bf16(x1.x - xi.x, x1.y - xi.y), tc5_pack_bf16(x1.z - xi.z, x1.w - xi.w));
+                    const int ngroups = (nh + 7) >> 3;
+                    const unsigned *lp = list + r4;
+                    int kg = 0;
+                    while (kg < ngroups) {                                          // warp-uniform
+                        const int ng = min(ngroups - kg, (GT_BLK - fill) >> 3);
+                        if (lane < ng) s_gslot[buf * 4 + (fill >> 3) + lane] = (unsigned char)u;
+                        uint32_t ad = dstl + (uint32_t)(buf * S::B_BYTES + (fill >> 3) * S::SBO);
+#pragma unroll 2
+                        for (int g = 0; g < ng; ++g, lp += 8, ad += S::SBO) {
+                            float4 x0, x1;
+                            lds4(x0, src + lp[0]);
+                            lds4(x1, src + lp[4]);
+                            if constexpr (TF32) {
+                                gt_sts128(ad, tc5_to_tf32(x0.x - xi.x), tc5_to_tf32(x0.y - xi.y), tc5_to_tf32(x0.z - xi.z), tc5_to_tf32(x0.w - xi.w));
+                                gt_sts128(ad + 64, tc5_to_tf32(x1.x - xi.x), tc5_to_tf32(x1.y - xi.y), tc5_to_tf32(x1.z - xi.z), tc5_to_tf32(x1.w - xi.w));
+                            } else {
+                                gt_sts64(ad, tc5_pack_bf16(x0.x - xi.x, x0.y - xi.y), tc5_pack_bf16(x0.z - xi.z, x0.w - xi.w));
+                                gt_sts64(ad + 64, tc5_pack_bf16(x1.x - xi.x, x1.y - xi.y), tc5_pack_bf16(x1.z - xi.z, x1.w - xi.w));
+                            }
                         }
-                        if (lane == 0) s_gslot[buf * 4 + (fill >> 3)] = (unsigned char)u;
-                        fill += 8;
+                        fill += 8 * ng; kg += ng;
                         if (fill == GT_BLK) flush();
-                        x0 = y0; x1 = y1;
                     }
                 }
                 __syncwarp();                                   // the hit list is reused by the next target
