@@ -566,88 +566,147 @@ __device__ __forceinline__ void issue_chunk3(const SegStage *seg, int k, const v
     }
 }
 
-__global__ void __launch_bounds__(GEO_THREADS)
+// Warp-specialised like the forward kernel: a producer warp walks the items and segments and streams the three row
+// arrays (chunk descriptor + TMA bulk copies, full / empty mbarriers, two stages), S2_CONSUMERS consumer warps walk the
+// staged rows on their own -- the only consumer-wide barriers are the two around the fold of a segment's accumulators
+// (the per-chunk CTA barriers of the first version were 3.1 stall cycles per issued instruction, ncu).
+constexpr int S2_CONSUMERS = GEO_WARPS;
+constexpr int S2_THREADS = (S2_CONSUMERS + 1) * 32;
+constexpr size_t S2_STAGE_BYTES = SC_STAGE_BYTES + 128;                         // + chunk descriptor
+constexpr size_t S2_ACC = SC_STAGES * S2_STAGE_BYTES;                           // [S2_CONSUMERS][32][32] f32
+constexpr size_t S2_COEF = S2_ACC + (size_t)S2_CONSUMERS * 32 * 32 * 4;         // [5][32] f32
+constexpr size_t S2_BAR = S2_COEF + 5 * 32 * 4;                                 // full[2], empty[2]
+constexpr size_t S2_TOTAL = S2_BAR + 16 * SC_STAGES;
+static_assert(S2_STAGE_BYTES % 128 == 0 && S2_BAR % 8 == 0, "scatter staging alignment");
+
+__global__ void __launch_bounds__(S2_THREADS)
 k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd bn, const int *__restrict__ arg,
               GeoView v, int N, float *__restrict__ S) {
     extern __shared__ __align__(128) unsigned char gs[];
-    float(*s_acc)[32][32] = reinterpret_cast<float(*)[32][32]>(gs + SC_ACC);
-    float *s_coef = reinterpret_cast<float *>(gs + SC_COEF);
-    int *s_item = reinterpret_cast<int *>(gs + SC_ITEM);
-    SegStage *seg = reinterpret_cast<SegStage *>(gs + SC_SEG);
-    const uint32_t bar0 = smem_u32(gs + SC_BAR);
+    float(*s_acc)[32][32] = reinterpret_cast<float(*)[32][32]>(gs + S2_ACC);
+    float *s_coef = reinterpret_cast<float *>(gs + S2_COEF);
+    const uint32_t full0 = smem_u32(gs + S2_BAR), empty0 = full0 + 8u * SC_STAGES;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     const GeoMeta m = *v.meta;
-    const CellGrid g = make_grid(v.bbox, m.r, m.dim, m.phi_wrap);
     if (tid == 0) {
-        for (int s = 0; s < SC_STAGES; ++s) mbar_init(bar0 + 8u * s, 1);
+        for (int s = 0; s < SC_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, S2_CONSUMERS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     bn_bwd_coeffs(bn, s_coef);
-    for (int i = lane; i < 32 * 32; i += 32) (&s_acc[warp][0][0])[i] = 0.f;
+    if (warp < S2_CONSUMERS)
+        for (int i = lane; i < 32 * 32; i += 32) (&s_acc[warp][0][0])[i] = 0.f;
     __syncthreads();
-    const float c_mean = s_coef[lane], c_inv = s_coef[H + lane], c_scale = s_coef[2 * H + lane];
-    const float c_1 = s_coef[3 * H + lane], c_2 = s_coef[4 * H + lane];
 
-    uint32_t phases = 0u;                                   // bit s = parity of pipeline stage s
     const int n_items = (N + GEO_TPI - 1) / GEO_TPI;
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const int n0 = item * GEO_TPI, icnt = min(GEO_TPI, N - n0);
-        if (warp == 0) item_segments(v, g, m.B, n0, icnt, lane, s_item);
-        __syncthreads();
-        unsigned heads = (unsigned)s_item[0];
-        while (heads) {
-            const int a = __ffs(heads) - 1;
-            heads &= heads - 1;
-            const int b = heads ? __ffs(heads) - 1 : icnt;
-            if (tid == 0) {
-                segment_runs(v, g, m.phi_wrap, s_item, a, b, seg);
-                const int nck = (seg->voff[seg->nr] + SC_CH - 1) / SC_CH;
-                for (int k = 0; k < min(nck, SC_STAGES); ++k)
-                    issue_chunk3(seg, k, arg, G, raw, smem_u32(gs + SC_ROWS + k * SC_STAGE_BYTES), bar0 + 8u * k);
-            }
-            __syncthreads();
-            const int C = seg->voff[seg->nr];
-            const int nchunks = (C + SC_CH - 1) / SC_CH;
-            const unsigned first = (unsigned)(n0 + a), span = (unsigned)(b - a);
-            for (int k = 0; k < nchunks; ++k) {
-                const int st = k & 1;
-                const int rows = min(SC_CH, C - k * SC_CH);
-                const int *s_arg = reinterpret_cast<const int *>(gs + SC_ROWS + st * SC_STAGE_BYTES);
-                const float *s_G = reinterpret_cast<const float *>(s_arg + SC_CH * 32);
-                const float *s_R = s_G + SC_CH * 32;
-                mbar_wait(bar0 + 8u * st, (phases >> st) & 1u);
-                phases ^= 1u << st;
-                // 4 staged rows per trip: their arg / G / raw loads are issued together (unconditionally: shared
-                // memory, no traffic to save), then the <= 4 read-modify-writes of the accumulator run in row order
-                for (int r = warp; r < rows; r += 4 * GEO_WARPS) {
-                    unsigned rel[4];
-                    float dv[4];
+    if (warp == S2_CONSUMERS) {
+        // ================================================================== producer
+        const CellGrid g = make_grid(v.bbox, m.r, m.dim, m.phi_wrap);
+        uint32_t gc = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int n0 = item * GEO_TPI, icnt = min(GEO_TPI, N - n0);
+            const bool valid = lane < icnt;
+            const float pw = valid ? __ldg(&v.pts[n0 + lane].w) : 0.f;
+            const int e = valid ? pts_event(pw) : -1;
+            const int cell = pts_cell(pw);
+            const int key = valid ? ((e << 5) | (cell / g.g1)) : -1;
+            const int prev = __shfl_up_sync(0xffffffffu, key, 1);
+            unsigned heads = __ballot_sync(0xffffffffu, valid && (lane == 0 || key != prev));
+            while (heads) {
+                const int a = __ffs(heads) - 1;
+                heads &= heads - 1;
+                const int b = heads ? __ffs(heads) - 1 : icnt;
+                const int ev = __shfl_sync(0xffffffffu, e, a);
+                const int ca = __shfl_sync(0xffffffffu, cell, a), cb = __shfl_sync(0xffffffffu, cell, b - 1);
+                const int ce = ca / g.g1;
+                int rlo[6], rhi[6], voff[7];
+                const int nr0 = nbhd_runs(g, v.cell_start + (size_t)ev * (CMAX + 1), ce, ca - ce * g.g1, cb - ce * g.g1,
+                                          m.phi_wrap, rlo, rhi);
+                int nr = 0, C = 0;
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int rr = min(r + u * GEO_WARPS, SC_CH - 1);
-                        rel[u] = (r + u * GEO_WARPS < rows) ? (unsigned)s_arg[rr * 32 + lane] - first : 0xffffffffu;
-                        const float xhat = (s_R[rr * 32 + lane] - c_mean) * c_inv;
-                        dv[u] = c_scale * (s_G[rr * 32 + lane] - c_1 - xhat * c_2);
+                for (int q = 0; q < 6; ++q)
+                    if (q < nr0 && rhi[q] > rlo[q]) { rlo[nr] = rlo[q]; voff[nr] = C; C += rhi[q] - rlo[q]; ++nr; }
+                voff[nr] = C;
+                const int nck = (C + SC_CH - 1) / SC_CH;
+                for (int k = 0; k < nck; ++k, ++gc) {
+                    const int st = gc & 1;
+                    mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u, 200);
+                    if (lane == 0) {
+                        unsigned char *stage = gs + st * S2_STAGE_BYTES;
+                        const uint32_t s_dst = smem_u32(stage), bar = full0 + 8u * st;
+                        const int c0 = k * SC_CH, c1 = min(C, c0 + SC_CH);
+                        ChunkDesc *d = reinterpret_cast<ChunkDesc *>(stage + SC_STAGE_BYTES);
+                        d->flags = (k == 0 ? AG_FIRST : 0) | (k == nck - 1 ? AG_LAST : 0);
+                        d->n0 = n0; d->a = a; d->b = b; d->rows = c1 - c0;
+                        mbar_expect_tx(bar, (uint32_t)(c1 - c0) * 384u);
+#pragma unroll
+                        for (int q = 0; q < 6; ++q) {
+                            if (q >= nr) break;
+                            const int lo = max(voff[q], c0), hi = min(voff[q + 1], c1);
+                            if (lo >= hi) continue;
+                            const size_t off = (size_t)(rlo[q] + (lo - voff[q])) * 128;
+                            const uint32_t n = (uint32_t)(hi - lo) * 128u, row = (uint32_t)(lo - c0) * 128u;
+                            bulk_g2s(s_dst + row, reinterpret_cast<const char *>(arg) + off, n, bar);
+                            bulk_g2s(s_dst + SC_CH * 128u + row, reinterpret_cast<const char *>(G) + off, n, bar);
+                            bulk_g2s(s_dst + 2u * SC_CH * 128u + row, reinterpret_cast<const char *>(raw) + off, n, bar);
+                        }
                     }
-#pragma unroll
-                    for (int u = 0; u < 4; ++u)
-                        if (rel[u] < span) s_acc[warp][a + rel[u]][lane] += dv[u];
+                    __syncwarp();
                 }
-                __syncthreads();                                           // stage st fully consumed
-                if (tid == 0 && k + SC_STAGES < nchunks)
-                    issue_chunk3(seg, k + SC_STAGES, arg, G, raw, smem_u32(gs + SC_ROWS + st * SC_STAGE_BYTES),
-                                 bar0 + 8u * st);
             }
-            // fold the warp accumulators of this segment's sources in warp order, write S, clear for the next use
-            for (int idx = tid; idx < (b - a) * 32; idx += GEO_THREADS) {
-                const int t = a + (idx >> 5), c = idx & 31;
-                float tot = 0.f;
+        }
+        const int st = gc & 1;                              // end-of-work descriptor (no copies)
+        mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u);
+        if (lane == 0) {
+            reinterpret_cast<ChunkDesc *>(gs + st * S2_STAGE_BYTES + SC_STAGE_BYTES)->flags = AG_END;
+            mbar_arrive(full0 + 8u * st);
+        }
+    } else {
+        // ================================================================== consumers
+        const float c_mean = s_coef[lane], c_inv = s_coef[H + lane], c_scale = s_coef[2 * H + lane];
+        const float c_1 = s_coef[3 * H + lane], c_2 = s_coef[4 * H + lane];
+        for (uint32_t gc = 0;; ++gc) {
+            const int st = gc & 1;
+            const unsigned char *stage = gs + st * S2_STAGE_BYTES;
+            mbar_wait(full0 + 8u * st, (gc >> 1) & 1u);
+            const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + SC_STAGE_BYTES);
+            const int flags = d->flags;
+            if (flags & AG_END) break;
+            const int a = d->a, b = d->b, rows = d->rows, n0 = d->n0;
+            const unsigned first = (unsigned)(n0 + a), span = (unsigned)(b - a);
+            const int *s_arg = reinterpret_cast<const int *>(stage);
+            const float *s_G = reinterpret_cast<const float *>(s_arg + SC_CH * 32);
+            const float *s_R = s_G + SC_CH * 32;
+            // 4 staged rows per trip: their arg / G / raw loads are issued together (unconditionally: shared memory,
+            // no traffic to save), then the <= 4 read-modify-writes of the accumulator run in row order
+            for (int r = warp; r < rows; r += 4 * S2_CONSUMERS) {
+                unsigned rel[4];
+                float dv[4];
 #pragma unroll
-                for (int w = 0; w < GEO_WARPS; ++w) { tot += s_acc[w][t][c]; s_acc[w][t][c] = 0.f; }
-                S[(size_t)(n0 + t) * H + c] = tot;
+                for (int u = 0; u < 4; ++u) {
+                    const int rr = min(r + u * S2_CONSUMERS, SC_CH - 1);
+                    rel[u] = (r + u * S2_CONSUMERS < rows) ? (unsigned)s_arg[rr * 32 + lane] - first : 0xffffffffu;
+                    const float xhat = (s_R[rr * 32 + lane] - c_mean) * c_inv;
+                    dv[u] = c_scale * (s_G[rr * 32 + lane] - c_1 - xhat * c_2);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (rel[u] < span) s_acc[warp][a + rel[u]][lane] += dv[u];
             }
-            __syncthreads();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty0 + 8u * st);       // this warp is done with the stage
+            if (flags & AG_LAST) {
+                // fold the warp accumulators of this segment's sources in warp order, write S, clear for the next use
+                asm volatile("bar.sync 1, %0;" ::"n"(S2_CONSUMERS * 32) : "memory");
+                for (int idx = tid; idx < (b - a) * 32; idx += S2_CONSUMERS * 32) {
+                    const int t = a + (idx >> 5), c = idx & 31;
+                    float tot = 0.f;
+#pragma unroll
+                    for (int w = 0; w < S2_CONSUMERS; ++w) { tot += s_acc[w][t][c]; s_acc[w][t][c] = 0.f; }
+                    S[(size_t)(n0 + t) * H + c] = tot;
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(S2_CONSUMERS * 32) : "memory");
+            }
         }
     }
 }
@@ -754,11 +813,11 @@ int geo_scatter_s(const float *G, const float *raw, const BnBwd &bn, const int *
     const GeoView v = view_of(geo_ws, N, B);
     static int occ = 0;
     if (!occ) {
-        GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SC_TOTAL));
-        occ = resident_ctas(k_geo_scatter, GEO_THREADS, SC_TOTAL, 3);
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S2_TOTAL));
+        occ = resident_ctas(k_geo_scatter, S2_THREADS, S2_TOTAL, 3);
     }
     const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, occ);
-    k_geo_scatter<<<grid, GEO_THREADS, SC_TOTAL, st>>>(G, raw, bn, arg, v, N, S);
+    k_geo_scatter<<<grid, S2_THREADS, S2_TOTAL, st>>>(G, raw, bn, arg, v, N, S);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
