@@ -21,7 +21,7 @@ namespace {
 #define GEO_SC_THREADS 128
 #endif
 #ifndef GEO_SC_CH
-#define GEO_SC_CH 64
+#define GEO_SC_CH 32
 #endif
 constexpr int GEO_THREADS = GEO_SC_THREADS;     // backward kernel: 4 warps
 constexpr int GEO_WARPS = GEO_THREADS / 32;
@@ -178,16 +178,6 @@ __global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, in
     }
 }
 
-// ------------------------------------------------------------------------------------------ staging machinery
-// A work item = GEO_TPI consecutive internal nodes.  It is cut into SEGMENTS of equal (event, eta-row); the
-// neighbourhood of a segment whose nodes sit in phi cells cpa..cpb is the <= 6 runs of nbhd_runs, flattened into
-// "virtual rows" 0..C-1 and staged AG_CH (forward) / SC_CH (backward) rows at a time.
-struct SegStage {
-    int nr;            // runs
-    int rlo[6];        // first internal node of run q
-    int voff[7];       // first virtual row of run q; voff[nr] = C
-};
-
 constexpr size_t AG_OFF_PTS = AgStage::OFF_PTS, AG_OFF_TGT = AgStage::OFF_TGT, AG_OFF_THR = AgStage::OFF_THR;
 constexpr size_t AG_OFF_DESC = AgStage::OFF_DESC, AG_STAGE_BYTES = AgStage::BYTES;
 constexpr size_t AG_LISTS = AG_STAGES * AG_STAGE_BYTES;                    // AG_CONSUMERS x AG_LIST x u32
@@ -195,40 +185,6 @@ constexpr size_t AG_BAR = AG_LISTS + (size_t)AG_CONSUMERS * AG_LIST * 4;   // fu
 constexpr size_t AG_TOTAL = AG_BAR + 16 * AG_STAGES;
 static_assert(AG_STAGE_BYTES % 128 == 0 && AG_LISTS % 8 == 0 && (AG_LIST * 4) % 16 == 0 && AG_LISTS % 16 == 0 && AG_BAR % 8 == 0, "staging alignment");
 static_assert(AG_STAGES * AG_STAGE_BYTES >= (size_t)(AG_THREADS / 8) * 3 * H * 4, "BatchNorm scratch aliases the stages");
-
-// backward kernel bookkeeping: heads, e[32], cell[32] + SegStage
-// warp 0: find the (event, eta-row) segments of the item's nodes
-__device__ __forceinline__ void item_segments(const GeoView &v, const CellGrid &g, int B, int n0, int cnt, int lane,
-                                              int *s_item) {
-    const int node = n0 + lane;
-    const bool valid = lane < cnt;
-    const float pw = valid ? __ldg(&v.pts[node].w) : 0.f;
-    const int e = valid ? pts_event(pw) : -1;
-    const int cell = pts_cell(pw);
-    const int key = valid ? ((e << 5) | (cell / g.g1)) : -1;
-    const int prev = __shfl_up_sync(0xffffffffu, key, 1);
-    const unsigned heads = __ballot_sync(0xffffffffu, valid && (lane == 0 || key != prev));
-    s_item[1 + lane] = e;
-    s_item[33 + lane] = cell;
-    if (lane == 0) s_item[0] = (int)heads;
-}
-
-// thread 0: runs of the segment [a, b) of the item
-__device__ __forceinline__ void segment_runs(const GeoView &v, const CellGrid &g, int phi_wrap, const int *s_item, int a,
-                                             int b, SegStage *seg) {
-    const int e = s_item[1 + a], ca = s_item[33 + a], cb = s_item[33 + b - 1];
-    const int ce = ca / g.g1;
-    int rlo[6], rhi[6];
-    const int nr = nbhd_runs(g, v.cell_start + (size_t)e * (CMAX + 1), ce, ca - ce * g.g1, cb - ce * g.g1, phi_wrap,
-                             rlo, rhi);
-    int off = 0, n = 0;
-    for (int q = 0; q < nr; ++q) {
-        if (rhi[q] <= rlo[q]) continue;
-        seg->rlo[n] = rlo[q]; seg->voff[n] = off; off += rhi[q] - rlo[q]; ++n;
-    }
-    seg->voff[n] = off;
-    seg->nr = n;
-}
 
 // One target against one staged chunk: hit list, then lane = channel walks the list 4 rows at a time out of shared
 // memory.  The caller must NOT unroll its target loop around this body: the consumer warps run decoupled, and four
@@ -540,31 +496,7 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
 // accumulators are folded in warp order and rows are walked in staged (= internal node) order: bit-deterministic.
 constexpr int SC_CH = GEO_SC_CH;               // staged target rows per pipeline stage
 constexpr int SC_STAGES = 2;
-constexpr size_t SC_ROWS = 0;                                                  // [stage][arg | G | raw][SC_CH][32] x 4 B
-constexpr size_t SC_STAGE_BYTES = (size_t)3 * SC_CH * 128;
-constexpr size_t SC_ACC = SC_ROWS + SC_STAGES * SC_STAGE_BYTES;                // [GEO_WARPS][32][32] f32
-constexpr size_t SC_COEF = SC_ACC + (size_t)GEO_WARPS * 32 * 32 * 4;           // [5][32] f32
-constexpr size_t SC_ITEM = SC_COEF + 5 * 32 * 4;
-constexpr size_t SC_SEG = SC_ITEM + 66 * 4;
-constexpr size_t SC_BAR = (SC_SEG + sizeof(SegStage) + 7) / 8 * 8;
-constexpr size_t SC_TOTAL = SC_BAR + 8 * SC_STAGES;
-
-// thread 0: TMA bulk copies of chunk k of the segment: three 128-byte row arrays
-__device__ __forceinline__ void issue_chunk3(const SegStage *seg, int k, const void *__restrict__ a0,
-                                             const void *__restrict__ a1, const void *__restrict__ a2, uint32_t s_dst,
-                                             uint32_t bar) {
-    const int c0 = k * SC_CH, c1 = min(seg->voff[seg->nr], c0 + SC_CH);
-    mbar_expect_tx(bar, (uint32_t)(c1 - c0) * 384u);
-    for (int q = 0; q < seg->nr; ++q) {
-        const int lo = max(seg->voff[q], c0), hi = min(seg->voff[q + 1], c1);
-        if (lo >= hi) continue;
-        const size_t off = (size_t)(seg->rlo[q] + (lo - seg->voff[q])) * 128;
-        const uint32_t n = (uint32_t)(hi - lo) * 128u, row = (uint32_t)(lo - c0) * 128u;
-        bulk_g2s(s_dst + row, reinterpret_cast<const char *>(a0) + off, n, bar);
-        bulk_g2s(s_dst + SC_CH * 128u + row, reinterpret_cast<const char *>(a1) + off, n, bar);
-        bulk_g2s(s_dst + 2u * SC_CH * 128u + row, reinterpret_cast<const char *>(a2) + off, n, bar);
-    }
-}
+constexpr size_t SC_STAGE_BYTES = (size_t)3 * SC_CH * 128;                   // [arg | G | raw][SC_CH][32] x 4 B
 
 // Warp-specialised like the forward kernel: a producer warp walks the items and segments and streams the three row
 // arrays (chunk descriptor + TMA bulk copies, full / empty mbarriers, two stages), S2_CONSUMERS consumer warps walk the
