@@ -30,6 +30,26 @@ inline int cuda_fail(cudaError_t e) {
         GM_CUDA_TRY(cudaGetLastError());   \
     } while (0)
 
+// Programmatic dependent launch (griddepcontrol): a kernel launched with GM_LAUNCH_PDL may begin -- block scheduling,
+// barrier / TMEM setup, staging of WEIGHTS into shared memory -- while its predecessor in the stream is still running;
+// it must execute pdl_wait() before it touches anything the predecessor wrote, and it lets its own successor start
+// with pdl_trigger() (always AFTER its pdl_wait(), so at most two kernels overlap and a prologue may read whatever
+// was complete two kernels back: parameters, never activations or statistics).  At DY/TT batch sizes a training step is
+// ~27 dependent launches of 15-70 us: the launch gaps and per-CTA prologues were ~10 % of it.  GM_PDL=0 disables.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&...args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#define GM_LAUNCH_PDL(kernel, grid, block, smem, st, ...)                                       \
+    GM_CUDA_TRY(::gm::launch_pdl(kernel, dim3(grid), dim3(block), smem, st, __VA_ARGS__))   /* then GM_LAUNCH_CHECK() */
+
 #define GM_TRY(expr)                 \
     do {                             \
         int _s = (expr);             \
@@ -71,6 +91,10 @@ inline int resident_ctas(K kernel, int threads, size_t smem, int fallback) {
 }
 
 // ----------------------------------------------------------------------------- device
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() { pdl_wait(); pdl_trigger(); }      // kernels without a prologue worth overlapping
+
 __device__ __forceinline__ float elu(float v) { return v > 0.f ? v : expm1f(v); }
 // derivative of ELU expressed through its OUTPUT a = elu(z): z>0 -> 1, else a + 1
 __device__ __forceinline__ float elu_grad_from_out(float a) { return a > 0.f ? 1.f : a + 1.f; }

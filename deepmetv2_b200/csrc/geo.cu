@@ -38,6 +38,7 @@ using AgStage = StageL<AG_CH, false>;
 __global__ void __launch_bounds__(256) k_geo_init(GeoMeta *m, float r, float r2, int dim, int phi_wrap, int loop, int cap_eff,
                                                   int N, int B, const int *__restrict__ ptr, int *__restrict__ ptr_copy,
                                                   int *__restrict__ sched, int *__restrict__ thr, int *stats) {
+    pdl_sync();
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
     if (gtid == 0) {
         *m = GeoMeta{r, r2, dim, phi_wrap, loop, cap_eff, N, B};
@@ -54,6 +55,7 @@ __global__ void __launch_bounds__(256) k_geo_init(GeoMeta *m, float r, float r2,
 __global__ void __launch_bounds__(256) k_cell_rank(const float4 *__restrict__ tmp, const int *__restrict__ ptr, int N,
                                                    int B, const int *__restrict__ cell_start,
                                                    float4 *__restrict__ pts, int *__restrict__ perm) {
+    pdl_sync();
     for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < N; s += gridDim.x * blockDim.x) {
         const int e = find_event(ptr, B, s);
         float4 t = tmp[s];
@@ -75,6 +77,7 @@ __global__ void __launch_bounds__(256) k_geo_cap_scan(const int *__restrict__ pt
                                                       const GeoMeta *__restrict__ meta, const int *__restrict__ bbox,
                                                       const int *__restrict__ cell_start, const float4 *__restrict__ pts,
                                                       int *__restrict__ list, int *__restrict__ count) {
+    pdl_sync();
     const GeoMeta m = *meta;
     const CellGrid g = make_grid(bbox, m.r, m.dim, m.phi_wrap);
     const int lane = threadIdx.x & 31;
@@ -108,6 +111,7 @@ __global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, in
                                                  const float4 *__restrict__ pts, int mask_words, int *__restrict__ thr,
                                                  const int *__restrict__ list, const int *__restrict__ count,
                                                  int *__restrict__ stats) {
+    pdl_sync();
     extern __shared__ unsigned int smask[];
     const GeoMeta m = *meta;
     const CellGrid g = make_grid(bbox, m.r, m.dim, m.phi_wrap);
@@ -297,6 +301,7 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
     }
     if (warp < AG_STAGES) reinterpret_cast<float *>(gs + warp * AG_STAGE_BYTES)[AG_CH * 32 + lane] = IDENT;
     __syncthreads();
+    pdl_sync();                                          // Y, P, the tickets: the previous kernels' outputs
 
     float cnt = 0.f, shift = 0.f, s1 = 0.f, s2 = 0.f;      // BatchNorm moments of this warp's outputs (lane = channel)
     if (warp == AG_CONSUMERS) {
@@ -525,6 +530,7 @@ k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd 
         for (int s = 0; s < SC_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, S2_CONSUMERS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    pdl_sync();                                          // the BatchNorm sums, G: the previous kernel's outputs
     bn_bwd_coeffs(bn, s_coef);
     if (warp < S2_CONSUMERS)
         for (int i = lane; i < 32 * 32; i += 32) (&s_acc[warp][0][0])[i] = 0.f;
@@ -651,6 +657,7 @@ k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd 
 // shifted sums per warp (shift = the warp's first row), Chan combination in warp / CTA order, last CTA finalises.
 constexpr int RM_THREADS = 256;
 __global__ void __launch_bounds__(RM_THREADS) k_row_moments(const float *__restrict__ x, int N, AggrTail tail) {
+    pdl_sync();
     __shared__ float s_red[RM_THREADS / 8][3][H];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int W = (gridDim.x * RM_THREADS) >> 5;
@@ -713,13 +720,13 @@ int launch_geo_aggr(const float *Y, const float *P, const GeoView &v, int N, flo
     // moments folded into the kernel is faster (c2: 72 vs 80 us).  Both are bit-reproducible.
     const bool split = tail.partials && (long long)(N + GEO_TPI - 1) / GEO_TPI >= 8LL * grid;
     const AggrTail in_kernel = split ? AggrTail{} : tail;
-    if (arg) k_geo_aggr<AGGR, true><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, in_kernel);
-    else if (q4) k_geo_aggr<AGGR, false, true><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, in_kernel);
-    else k_geo_aggr<AGGR, false><<<grid, AG_THREADS, AG_TOTAL, st>>>(Y, P, v, N, out, arg, in_kernel);
+    if (arg) GM_LAUNCH_PDL((k_geo_aggr<AGGR, true>), grid, AG_THREADS, AG_TOTAL, st, Y, P, v, N, out, arg, in_kernel);
+    else if (q4) GM_LAUNCH_PDL((k_geo_aggr<AGGR, false, true>), grid, AG_THREADS, AG_TOTAL, st, Y, P, v, N, out, arg, in_kernel);
+    else GM_LAUNCH_PDL((k_geo_aggr<AGGR, false>), grid, AG_THREADS, AG_TOTAL, st, Y, P, v, N, out, arg, in_kernel);
     GM_LAUNCH_CHECK();
     if (split) {
         const int mgrid = persistent_grid((N + 63) / 64, min(4, MAX_PARTIAL_CTAS / 148));
-        k_row_moments<<<mgrid, RM_THREADS, 0, st>>>(out, N, tail);
+        GM_LAUNCH_PDL(k_row_moments, mgrid, RM_THREADS, 0, st, out, N, tail);
         GM_LAUNCH_CHECK();
     }
     return GM_OK;
@@ -749,7 +756,7 @@ int geo_scatter_s(const float *G, const float *raw, const BnBwd &bn, const int *
         occ = resident_ctas(k_geo_scatter, S2_THREADS, S2_TOTAL, 3);
     }
     const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, occ);
-    k_geo_scatter<<<grid, S2_THREADS, S2_TOTAL, st>>>(G, raw, bn, arg, v, N, S);
+    GM_LAUNCH_PDL(k_geo_scatter, grid, S2_THREADS, S2_TOTAL, st, G, raw, bn, arg, v, N, S);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
@@ -776,11 +783,12 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
     const float rf = (float)r, r2 = (float)(r * r);          // r*r in double, then fp32
     const int cap_eff = loop ? max_num_neighbors : max_num_neighbors + 1;
     GM_TRY(bin_points(pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt, w.cell_start, w.tmp, w.stats, st));
-    k_geo_init<<<persistent_grid((N + 255) / 256, 4), 256, 0, st>>>(w.meta, rf, r2, dim, phi_wrap, loop, cap_eff, N, B, ptr, w.ptr,
-                                                                    w.sched, w.thr, w.stats);
+    GM_LAUNCH_PDL(k_geo_init, persistent_grid((N + 255) / 256, 4), 256, 0, st, w.meta, rf, r2, dim, phi_wrap, loop, cap_eff, N, B,
+                  ptr, w.ptr, w.sched, w.thr, w.stats);
     GM_LAUNCH_CHECK();
     if (N > 0) {
-        k_cell_rank<<<persistent_grid((N + 255) / 256, 8), 256, 0, st>>>(w.tmp, ptr, N, B, w.cell_start, w.pts, node_perm_out);
+        GM_LAUNCH_PDL(k_cell_rank, persistent_grid((N + 255) / 256, 8), 256, 0, st, w.tmp, ptr, N, B, w.cell_start, w.pts,
+                      node_perm_out);
         GM_LAUNCH_CHECK();
         const int mask_words = (max_event_nodes + 31) / 32 + 1;
         int threads = 256;
@@ -791,11 +799,11 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
             GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_cap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const int grid = persistent_grid(((long long)N * 32 + threads - 1) / threads, 2048 / threads);
         int *cap_list = reinterpret_cast<int *>(w.tmp);          // tmp is dead once k_cell_rank has run
-        k_geo_cap_scan<<<persistent_grid((N + 255) / 256, 8), 256, 0, st>>>(ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts,
-                                                                            cap_list, w.sched + 2);
+        GM_LAUNCH_PDL(k_geo_cap_scan, persistent_grid((N + 255) / 256, 8), 256, 0, st, ptr, N, B, w.meta, w.bbox, w.cell_start,
+                      w.pts, cap_list, w.sched + 2);
         GM_LAUNCH_CHECK();
-        k_geo_cap<<<grid, threads, smem, st>>>(ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts, mask_words, w.thr,
-                                               cap_list, w.sched + 2, w.stats);
+        GM_LAUNCH_PDL(k_geo_cap, grid, threads, smem, st, ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts, mask_words, w.thr,
+                      cap_list, w.sched + 2, w.stats);
         GM_LAUNCH_CHECK();
     }
     if (stats_out) GM_CUDA_TRY(cudaMemcpyAsync(stats_out, w.stats, 4 * sizeof(int), cudaMemcpyDeviceToDevice, st));

@@ -133,6 +133,7 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
     tc5_fence_before();
     __syncthreads();
     tc5_fence_after();
+    pdl_sync();                                          // X, P and the tickets are the previous kernels' outputs
     const uint32_t tmem_base = *reinterpret_cast<const uint32_t *>(gs + S::OFF_TMEM);
 
     if (warp == GT_CONSUMERS) {
@@ -339,7 +340,7 @@ int launch_geo_tc(const float *X, const float *P, const float *W, const GeoView 
         occ = max(occ, min((int)(227 * 1024 / (GtSmem<PREC>::TOTAL + 1024)), 512 / GtSmem<PREC>::TMEM_COLS));
     }
     const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, occ);
-    k_geo_edgeconv_tc<PREC, AGGR><<<grid, GtSmem<PREC>::THREADS, GtSmem<PREC>::TOTAL, st>>>(X, P, W, v, N, out);
+    GM_LAUNCH_PDL((k_geo_edgeconv_tc<PREC, AGGR>), grid, GtSmem<PREC>::THREADS, GtSmem<PREC>::TOTAL, st, X, P, W, v, N, out);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }

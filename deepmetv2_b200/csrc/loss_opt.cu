@@ -8,6 +8,10 @@ namespace gm {
 
 int g_last_cuda_error = 0;
 long long g_launch_count = 0;
+bool pdl_enabled() {
+    static const bool on = [] { const char *e = getenv("GM_PDL"); return !(e && e[0] == '0'); }();
+    return on;
+}
 
 namespace {
 struct TimerSlot {
@@ -70,6 +74,7 @@ __device__ __forceinline__ float block_sum(float v, float *sm) {
 __global__ void __launch_bounds__(RED_THREADS) k_met(const float *__restrict__ w, const float *__restrict__ pred,
                                                      int pstride, const int *__restrict__ ptr,
                                                      float *__restrict__ met) {
+    pdl_sync();
     __shared__ float sm[RED_THREADS / 32];
     const int e = blockIdx.x;
     const int lo = ptr[e], hi = ptr[e + 1];
@@ -91,6 +96,7 @@ __global__ void __launch_bounds__(RED_THREADS) k_met_grad(const float *__restric
                                                           int pstride, const int *__restrict__ ptr,
                                                           const float *__restrict__ truth, int tstride, int B,
                                                           float *__restrict__ met, float *__restrict__ gw) {
+    pdl_sync();
     __shared__ float sm[RED_THREADS / 32];
     __shared__ float s_g[2];
     const int e = blockIdx.x;
@@ -120,6 +126,7 @@ __global__ void __launch_bounds__(RED_THREADS) k_met_grad(const float *__restric
 
 __global__ void __launch_bounds__(RED_THREADS) k_loss(const float *__restrict__ met, const float *__restrict__ truth,
                                                       int tstride, int B, float *__restrict__ loss) {
+    pdl_sync();
     __shared__ float sm[RED_THREADS / 32];
     float acc = 0.f;
     for (int e = threadIdx.x; e < B; e += RED_THREADS) {
@@ -171,6 +178,7 @@ __global__ void __launch_bounds__(256) k_adamw(float *__restrict__ p, const floa
                                                float *__restrict__ m, float *__restrict__ v, int n, float lr,
                                                float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt,
                                                float gscale) {
+    pdl_wait();                                          // no early trigger: whatever follows may read weights up front
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float gi = g[i] * gscale;
         float pi = p[i] * (1.f - lr * wd);
@@ -325,11 +333,11 @@ int gm_met_loss(const float *w, const float *pred, int pred_stride, const float 
     if (pred_stride < 2 || truth_stride < 2) return GM_ERR_INVALID_ARGUMENT;
     cudaStream_t st = as_stream(stream);
     if (grad_w_out && N > 0)
-        k_met_grad<<<B, RED_THREADS, 0, st>>>(w, pred, pred_stride, ptr, truth, truth_stride, B, met_out, grad_w_out);
+        GM_LAUNCH_PDL(k_met_grad, B, RED_THREADS, 0, st, w, pred, pred_stride, ptr, truth, truth_stride, B, met_out, grad_w_out);
     else
-        k_met<<<B, RED_THREADS, 0, st>>>(w, pred, pred_stride, ptr, met_out);
+        GM_LAUNCH_PDL(k_met, B, RED_THREADS, 0, st, w, pred, pred_stride, ptr, met_out);
     GM_LAUNCH_CHECK();
-    k_loss<<<1, RED_THREADS, 0, st>>>(met_out, truth, truth_stride, B, loss_out);
+    GM_LAUNCH_PDL(k_loss, 1, RED_THREADS, 0, st, met_out, truth, truth_stride, B, loss_out);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
@@ -360,9 +368,8 @@ int gm_adamw_step(float *params, const float *grads, float *exp_avg, float *exp_
     if (n == 0) return GM_OK;
     const double bc1 = 1.0 - pow((double)beta1, (double)step);
     const double bc2 = 1.0 - pow((double)beta2, (double)step);
-    k_adamw<<<persistent_grid((n + 255) / 256, 8), 256, 0, as_stream(stream)>>>(
-        params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2),
-        grad_scale);
+    GM_LAUNCH_PDL(k_adamw, persistent_grid((n + 255) / 256, 8), 256, 0, as_stream(stream), params, grads, exp_avg, exp_avg_sq, n,
+                  lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }

@@ -154,6 +154,7 @@ struct Segs { int n; Seg s[MAX_SEGS]; };
 // thread (c = t%32, g = t/32): lanes read 32 consecutive outputs (coalesced), the 8 groups split the
 // CTA-partial axis (b = g, g+8, ...) and are folded in a fixed order => deterministic.
 __global__ void __launch_bounds__(256) k_reduce_partials(Segs segs) {
+    pdl_sync();
     __shared__ float sm[8][32];
     const Seg sg = segs.s[blockIdx.y];
     const int total = sg.rows * sg.cols;
@@ -225,6 +226,7 @@ k_head_bwd(const float *__restrict__ emb, const float *__restrict__ out, const f
     for (int i = t; i < 16 * H; i += NODE_TILE) s_w1[i] = w1[i];
     if (t < 16) { s_b1[t] = b1[t]; s_w2[t] = w2[t]; }
     if (t < H) { s_mean[t] = bo.stat[t]; s_inv[t] = bo.stat[2 * H + t]; }
+    pdl_sync();                                  // above: parameters and forward statistics (many kernels back)
     __syncthreads();
     Outer<16, H> oW1; oW1.zero();
     ColSum<GLD> cs; cs.zero();   // columns 0..15 = db1, 16..31 = dW2, 32 = db2
@@ -390,6 +392,7 @@ k_conv_bwd_node2(const float *__restrict__ x, const float *__restrict__ raw, BnB
         const float a = W[c * CONV_IN + k], b = W[c * CONV_IN + H + k];
         s_wd[i] = a - b; s_w2[i] = b;
     }
+    pdl_sync();                                  // weights above: parameters; the BatchNorm sums are the previous kernel's
     bn_bwd_coeffs(bn, s_coef);
     if (t < H) { s_mean[t] = bo.stat[t]; s_inv[t] = bo.stat[2 * H + t]; }
     __syncthreads();
@@ -511,6 +514,7 @@ __global__ void __launch_bounds__(NODE_TILE, 2) k_encode_bwd(EncBwdArgs a) {
     for (int i = t; i < LUT_ROWS * 16; i += NODE_TILE) s_lut[i] = a.lut[i];
     for (int i = t; i < 144; i += NODE_TILE)
         s_tab[i] = i < 24 ? a.e_chrg[i] : (i < 80 ? a.e_pdg[i - 24] : a.e_pv[i - 80]);
+    pdl_sync();                                  // above: parameters and the forward LUT; the BatchNorm sums are the previous kernel's
     bn_bwd_coeffs(a.bn, s_coef);
     __syncthreads();
 
@@ -692,8 +696,8 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
     // ---- head (stage 0); also produces the BatchNorm sums of the topmost BatchNorm (index depth)
     {
         TimedRegion tr(GM_TIMER_HEAD_BWD, st);
-        k_head_bwd<<<ngrid, NODE_TILE, 0, st>>>(f.emb[depth], out, grad_out, node_perm, N, p->out1_w, p->out1_b,
-                                                p->out2_w, apply_sigmoid, w.G, gpart(0), sum_out(depth));
+        GM_LAUNCH_PDL(k_head_bwd, ngrid, NODE_TILE, 0, st, f.emb[depth], out, grad_out, node_perm, N, p->out1_w, p->out1_b,
+                      p->out2_w, apply_sigmoid, w.G, gpart(0), sum_out(depth));
         GM_LAUNCH_CHECK();
     }
     add_seg(0, grads->out1_w, H, 0, 16, H, H);
@@ -719,8 +723,8 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
         }
         {
             TimedRegion tr(GM_TIMER_CONV_NODE_BWD, st);
-            k_conv_bwd_node2<<<ngrid, CB_THREADS, CONV_BWD_SMEM, st>>>(f.emb[l], f.conv[l], bn_in(l + 1), w.S, N,
-                                                                       p->conv_w[l], w.G, gpart(stage), sum_out(l));
+            GM_LAUNCH_PDL(k_conv_bwd_node2, ngrid, CB_THREADS, CONV_BWD_SMEM, st, f.emb[l], f.conv[l], bn_in(l + 1), w.S, N,
+                          p->conv_w[l], w.G, gpart(stage), sum_out(l));
             GM_LAUNCH_CHECK();
         }
         add_seg(stage, grads->conv_w[l], CONV_IN, 0, H, H, H);
@@ -740,7 +744,7 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
         GM_CUDA_TRY(cudaFuncSetAttribute(k_encode_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ENC_BWD_SMEM));
         {
             TimedRegion tr(GM_TIMER_ENCODE_BWD, st);
-            k_encode_bwd<<<ngrid, NODE_TILE, ENC_BWD_SMEM, st>>>(ea);
+            GM_LAUNCH_PDL(k_encode_bwd, ngrid, NODE_TILE, ENC_BWD_SMEM, st, ea);
             GM_LAUNCH_CHECK();
         }
         const int CD = p->continuous_dim;
@@ -759,7 +763,7 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
         for (int k = 0; k < segs.n; ++k) max_total = max(max_total, segs.s[k].rows * segs.s[k].cols);
         if (segs.n > 0) {
             dim3 grid((max_total + 31) / 32, segs.n);
-            k_reduce_partials<<<grid, 256, 0, st>>>(segs);
+            GM_LAUNCH_PDL(k_reduce_partials, grid, 256, 0, st, segs);
             GM_LAUNCH_CHECK();
         }
     }

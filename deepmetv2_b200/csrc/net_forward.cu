@@ -21,6 +21,7 @@ namespace {
 // ------------------------------------------------------------------------------------------ LUT
 __global__ void __launch_bounds__(256) k_build_lut(GmParams p, float *__restrict__ lut, int *__restrict__ counters,
                                                    float *__restrict__ bnstat, int training, float eps) {
+    pdl_sync();
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx < NUM_COUNTERS) counters[idx] = 0;
     if (!training && blockIdx.x == 0) {      // eval mode: BatchNorm is a fixed affine of the running statistics
@@ -106,6 +107,7 @@ __global__ void __launch_bounds__(ENC_THREADS, 3) k_encode2(EncodeArgs a) {
     if (t < 16) s_cont_b[t] = a.cont_b[t];
     for (int i = t; i < H * H; i += ENC_THREADS) s_encT[i] = a.enc_w[(i & 31) * H + (i >> 5)];
     if (t < H) s_enc_b[t] = a.enc_b[t];
+    pdl_sync();                                  // weights above: parameters; the LUT is the previous kernel's output
     for (int i = t; i < LUT_ROWS * 16; i += ENC_THREADS) s_lut[i] = a.lut[i];
     __syncthreads();
     const float4 b4 = reinterpret_cast<const float4 *>(s_enc_b)[og];
@@ -320,6 +322,7 @@ k_node_prep2(const float *__restrict__ raw, const float *__restrict__ resid, con
         s_wdT[i] = direct ? w1 : w1 - w2; s_w2T[i] = w2;
     }
     if (t < H) s_b[t] = bias[t];
+    pdl_sync();                                  // weights above: parameters; stat is the previous kernel's output
     if (stat && t < BNSTAT_STRIDE) s_stat[t] = stat[t];
     __syncthreads();
     const float4 b4 = reinterpret_cast<const float4 *>(s_b)[og];
@@ -631,6 +634,7 @@ __global__ void __launch_bounds__(NODE_TILE) k_head(const float *__restrict__ ra
     for (int i = t; i < 16 * H; i += NODE_TILE) s_w1[i] = w1[i];
     if (t < 16) { s_b1[t] = b1[t]; s_w2[t] = w2[t]; }
     if (t == 0) s_b2[0] = b2[0];
+    pdl_sync();                                  // weights above: parameters; stat is the previous kernel's output
     if (stat && t < BNSTAT_STRIDE) s_stat[t] = stat[t];
     __syncthreads();
     const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
@@ -791,7 +795,7 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
     const int depth = p->conv_depth;
     const int ngrid = node_grid(N);
 
-    k_build_lut<<<(LUT_ROWS * 16 + 255) / 256, 256, 0, st>>>(*p, w.lut, w.counters, w.bnstat, training, eps);
+    GM_LAUNCH_PDL(k_build_lut, (LUT_ROWS * 16 + 255) / 256, 256, 0, st, *p, w.lut, w.counters, w.bnstat, training, eps);
     GM_LAUNCH_CHECK();
 
     EncodeArgs ea{};
@@ -810,7 +814,7 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
     ea.err_flags = err_flags;
     {
         TimedRegion tr(GM_TIMER_ENCODE_FWD, st);
-        k_encode2<<<persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 3), ENC_THREADS, 0, st>>>(ea);
+        GM_LAUNCH_PDL(k_encode2, persistent_grid((N + NODE_TILE - 1) / NODE_TILE, 3), ENC_THREADS, 0, st, ea);
         GM_LAUNCH_CHECK();
     }
 
@@ -823,8 +827,8 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
         if (precision == GM_PREC_FP32) {
             {
                 TimedRegion tr(GM_TIMER_NODE_PREP, st);
-                k_node_prep2<<<ngrid, NP_THREADS, 0, st>>>(raw, resid, stat_in, p->conv_w[l], p->conv_b[l], N, w.emb[l],
-                                                           w.Y, w.P);
+                GM_LAUNCH_PDL(k_node_prep2, ngrid, NP_THREADS, 0, st, raw, resid, stat_in, p->conv_w[l], p->conv_b[l], N,
+                              w.emb[l], w.Y, w.P, 0);
                 GM_LAUNCH_CHECK();
             }
             AggrTail tail{};
@@ -835,8 +839,8 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
         } else if (geo_ws) {
             {
                 TimedRegion tr(GM_TIMER_NODE_PREP, st);
-                k_node_prep2<<<ngrid, NP_THREADS, 0, st>>>(raw, resid, stat_in, p->conv_w[l], p->conv_b[l], N, w.emb[l],
-                                                           nullptr, w.P, 1);
+                GM_LAUNCH_PDL(k_node_prep2, ngrid, NP_THREADS, 0, st, raw, resid, stat_in, p->conv_w[l], p->conv_b[l], N,
+                              w.emb[l], (float *)nullptr, w.P, 1);
                 GM_LAUNCH_CHECK();
             }
             TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
@@ -864,9 +868,9 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
         const float *raw = depth == 0 ? w.enc : w.conv[depth - 1];
         const float *resid = depth == 0 ? nullptr : w.emb[depth - 1];
         TimedRegion tr(GM_TIMER_HEAD_FWD, st);
-        k_head<<<ngrid, NODE_TILE, 0, st>>>(raw, resid, w.bnstat + (size_t)depth * BNSTAT_STRIDE, N, p->out1_w,
-                                            p->out1_b, p->out2_w, p->out2_b, apply_sigmoid, node_perm,
-                                            save_for_backward ? w.emb[depth] : nullptr, out);
+        GM_LAUNCH_PDL(k_head, ngrid, NODE_TILE, 0, st, raw, resid, w.bnstat + (size_t)depth * BNSTAT_STRIDE, N, p->out1_w,
+                      p->out1_b, p->out2_w, p->out2_b, apply_sigmoid, node_perm,
+                      save_for_backward ? w.emb[depth] : (float *)nullptr, out);
         GM_LAUNCH_CHECK();
     }
     return GM_OK;

@@ -47,6 +47,7 @@ size_t ws_layout(int N, int B, char *base, Workspace *w) {
 
 // ------------------------------------------------------------------------------------------
 __global__ void k_init(int *bbox, int *stats) {
+    pdl_sync();
     if (threadIdx.x == 0) {
         bbox[0] = 0x7fffffff; bbox[1] = (int)0x80000000;
         bbox[2] = 0x7fffffff; bbox[3] = (int)0x80000000;
@@ -55,6 +56,7 @@ __global__ void k_init(int *bbox, int *stats) {
 }
 
 __global__ void __launch_bounds__(256) k_bbox(const float *__restrict__ pos, int stride, int dim, int N, int *bbox) {
+    pdl_sync();
     int lo0 = 0x7fffffff, hi0 = (int)0x80000000, lo1 = lo0, hi1 = hi0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
         float a = pos[(size_t)i * stride];
@@ -81,6 +83,7 @@ __global__ void __launch_bounds__(256) k_cell_count(const float *__restrict__ po
                                                     const int *__restrict__ ptr, int N, int B, float r,
                                                     int phi_wrap, const int *__restrict__ bbox,
                                                     int *__restrict__ cell_cnt) {
+    pdl_sync();
     CellGrid g = make_grid(bbox, r, dim, phi_wrap);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
         int e = find_event(ptr, B, i);
@@ -94,6 +97,7 @@ __global__ void __launch_bounds__(256) k_cell_count(const float *__restrict__ po
 // one CTA per event: cell_start[e][c] = ptr[e] + exclusive_scan(cell_cnt[e][:]) ; CMAX = 1024 = blockDim
 __global__ void __launch_bounds__(CMAX) k_cell_scan(const int *__restrict__ ptr, const int *__restrict__ cell_cnt,
                                                    int *__restrict__ cell_start) {
+    pdl_sync();
     __shared__ int warp_tot[32];
     const int e = blockIdx.x, t = threadIdx.x, lane = t & 31, w = t >> 5;
     int v = cell_cnt[(size_t)e * CMAX + t];
@@ -118,6 +122,7 @@ __global__ void __launch_bounds__(256) k_cell_fill(const float *__restrict__ pos
                                                    int phi_wrap, const int *__restrict__ bbox,
                                                    int *__restrict__ cell_cnt, const int *__restrict__ cell_start,
                                                    float4 *__restrict__ sorted) {
+    pdl_sync();
     CellGrid g = make_grid(bbox, r, dim, phi_wrap);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
         int e = find_event(ptr, B, i);
@@ -330,6 +335,7 @@ __global__ void __launch_bounds__(256) k_fill(const int *__restrict__ ptr, int N
 
 __global__ void __launch_bounds__(256) k_prepare_etaphi(const float *__restrict__ x, int stride, int N,
                                                         float2 *__restrict__ out) {
+    pdl_sync();
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
         const float *row = x + (size_t)i * stride;
         out[i] = make_float2(row[3], atan2f(row[1], row[0]));
@@ -350,19 +356,19 @@ __global__ void __launch_bounds__(256) k_batch_to_ptr(const long long *__restric
 int run_common(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B, double r,
                int phi_wrap, const Workspace &w, cudaStream_t st) {
     const float rf = (float)r;
-    k_init<<<1, 32, 0, st>>>(w.bbox, w.stats);
+    GM_LAUNCH_PDL(k_init, 1, 32, 0, st, w.bbox, w.stats);
     GM_LAUNCH_CHECK();
     GM_CUDA_TRY(cudaMemsetAsync(w.cell_cnt, 0, (size_t)B * CMAX * sizeof(int), st));
     if (N == 0) return GM_OK;
     const int g = persistent_grid((N + 255) / 256, 8);
-    k_bbox<<<g, 256, 0, st>>>(pos, pos_stride, dim, N, w.bbox);
+    GM_LAUNCH_PDL(k_bbox, g, 256, 0, st, pos, pos_stride, dim, N, w.bbox);
     GM_LAUNCH_CHECK();
-    k_cell_count<<<g, 256, 0, st>>>(pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt);
+    GM_LAUNCH_PDL(k_cell_count, g, 256, 0, st, pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt);
     GM_LAUNCH_CHECK();
-    k_cell_scan<<<B, CMAX, 0, st>>>(ptr, w.cell_cnt, w.cell_start);
+    GM_LAUNCH_PDL(k_cell_scan, B, CMAX, 0, st, ptr, w.cell_cnt, w.cell_start);
     GM_LAUNCH_CHECK();
-    k_cell_fill<<<g, 256, 0, st>>>(pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt,
-                                   w.cell_start, w.sorted);
+    GM_LAUNCH_PDL(k_cell_fill, g, 256, 0, st, pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt, w.cell_start,
+                  w.sorted);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
@@ -458,8 +464,8 @@ int gm_radius_graph_fill(const float *pos, int pos_stride, int dim, const int *p
 int gm_prepare_etaphi(const float *x, int x_stride, int N, float *etaphi_out, void *stream) {
     if (N < 0 || (N > 0 && (!x || !etaphi_out)) || x_stride < 4) return GM_ERR_INVALID_ARGUMENT;
     if (N == 0) return GM_OK;
-    k_prepare_etaphi<<<persistent_grid((N + 255) / 256, 8), 256, 0, as_stream(stream)>>>(x, x_stride, N,
-                                                                                         (float2 *)etaphi_out);
+    GM_LAUNCH_PDL(k_prepare_etaphi, persistent_grid((N + 255) / 256, 8), 256, 0, as_stream(stream), x, x_stride, N,
+                  (float2 *)etaphi_out);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
