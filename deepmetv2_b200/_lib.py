@@ -61,6 +61,9 @@ SIGNATURES = {
     "gm_radius_graph_count": (_i, [_vp, _i, _i, _vp, _i, _i, _d, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _vp]),
     "gm_radius_graph_fill": (_i, [_vp, _i, _i, _vp, _i, _i, _d, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _ll, _vp,
                                   _vp, _vp]),
+    "gm_knn_graph_ws_bytes": (_sz, [_i, _i, _i]),
+    "gm_knn_graph_count": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _i, _vp, _sz, _vp, _vp]),
+    "gm_knn_graph_fill": (_i, [_i, _i, _i, _vp, _sz, _vp, _vp, _ll, _vp, _vp]),
     "gm_csr_ws_bytes": (_sz, [_i, _ll]),
     "gm_edge_index_to_csr": (_i, [_vp, _ll, _i, _vp, _sz, _vp, _vp, _vp]),
     "gm_csr_transpose": (_i, [_vp, _vp, _i, _ll, _vp, _sz, _vp, _vp, _vp, _vp]),

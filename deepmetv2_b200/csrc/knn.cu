@@ -1,0 +1,226 @@
+// k-nearest-neighbour graph per event in a D-dimensional (latent) space -- SURVEY.md §8 rows f4 / f1:
+//   knn_graph(emb, k=20, batch, loop=True)         /root/reference/model/graph_met_network.py:63 (sketched there)
+//   knn_graph(x, self.k, batch, loop=False, flow)  /root/reference/model/dynamic_reduction_network.py:86,95
+// [upstream torch_cluster.knn_graph] semantics restated in oracle/knn_bruteforce.c; this file is its CUDA form and is
+// bit-identical to it: dist = sum_d (x_j[d] - x_i[d])^2 accumulated in fp32 in dimension order with SEPARATE multiply
+// and add (no contraction), candidates scanned in ascending index, a candidate enters the list only when strictly
+// closer than the current worst entry => ties go to the lower index; the K best (K = k + !loop) come out ordered by
+// (distance, index), the self pair is dropped afterwards when loop == 0 (so a node with > k exact duplicates at lower
+// indices keeps k + 1 neighbours, as upstream's `row != col` mask does).
+//
+// Layout: one warp owns QPW queries whose coordinates sit in registers; the CTA streams the event's candidates
+// through shared memory in tiles (row stride DP + 4 floats: conflict-free 128-bit loads with lane = candidate); the
+// running top-K of a query is one (distance, index) pair per lane, kept sorted with ballot / shuffle insertion.
+#include "common.cuh"
+
+namespace gm {
+namespace {
+
+constexpr int KNN_WARPS = 8;
+constexpr int KNN_THREADS = KNN_WARPS * 32;
+constexpr int KNN_TILE = 128;      // candidates per shared-memory tile
+constexpr int KNN_MAX_K = 32;      // list entries per query = one per lane
+
+__device__ __forceinline__ int event_of(const int *__restrict__ ptr, int B, int i) {
+    int lo = 0, hi = B;            // last e with ptr[e] <= i
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(ptr + mid) <= i) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+template <int DP, int QPW>
+__global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restrict__ x, int stride, int dim,
+                                                            const int *__restrict__ ptr, int N, int B, int K, int loop,
+                                                            int *__restrict__ nbr, int *__restrict__ deg) {
+    constexpr int RS = DP + 4;                       // shared row stride (floats)
+    constexpr int QB = KNN_WARPS * QPW;              // queries per CTA
+    __shared__ __align__(16) float s_tile[KNN_TILE * RS];
+    pdl_sync();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (long long blk = blockIdx.x; blk * QB < N; blk += gridDim.x) {
+        const int q0 = (int)(blk * QB), q1 = min(N, q0 + QB);
+        // ---- this warp's queries: coordinates (zero-padded to DP), event, list
+        float q[QPW][DP];
+        int qi[QPW], qe[QPW];
+        float ld[QPW], worst[QPW];
+        int li[QPW];
+#pragma unroll
+        for (int u = 0; u < QPW; ++u) {
+            qi[u] = q0 + warp * QPW + u;
+            const bool live = qi[u] < N;
+            qe[u] = live ? event_of(ptr, B, qi[u]) : -1;
+#pragma unroll
+            for (int d = 0; d < DP; ++d) q[u][d] = (live && d < dim) ? __ldg(x + (size_t)qi[u] * stride + d) : 0.f;
+            ld[u] = INFINITY; li[u] = -1; worst[u] = INFINITY;
+        }
+        const int e_first = event_of(ptr, B, q0), e_last = event_of(ptr, B, q1 - 1);
+        for (int e = e_first; e <= e_last; ++e) {
+            const int c0 = __ldg(ptr + e), c1 = __ldg(ptr + e + 1);
+            for (int t0 = c0; t0 < c1; t0 += KNN_TILE) {
+                const int rows = min(KNN_TILE, c1 - t0);
+                __syncthreads();                     // previous tile fully consumed
+                for (int t = threadIdx.x; t < rows * DP; t += KNN_THREADS) {
+                    const int r = t / DP, d = t - r * DP;
+                    s_tile[r * RS + d] = d < dim ? x[(size_t)(t0 + r) * stride + d] : 0.f;
+                }
+                __syncthreads();
+                for (int j0 = 0; j0 < rows; j0 += 32) {
+                    const int j = j0 + lane;
+                    const bool valid = j < rows;
+                    const float4 *row = reinterpret_cast<const float4 *>(s_tile + (valid ? j : 0) * RS);
+                    float acc[QPW];
+#pragma unroll
+                    for (int u = 0; u < QPW; ++u) acc[u] = 0.f;
+#pragma unroll
+                    for (int d4 = 0; d4 < DP / 4; ++d4) {
+                        const float4 c = row[d4];
+#pragma unroll
+                        for (int u = 0; u < QPW; ++u) {
+                            float df;
+                            df = __fsub_rn(c.x, q[u][4 * d4 + 0]); acc[u] = __fadd_rn(acc[u], __fmul_rn(df, df));
+                            df = __fsub_rn(c.y, q[u][4 * d4 + 1]); acc[u] = __fadd_rn(acc[u], __fmul_rn(df, df));
+                            df = __fsub_rn(c.z, q[u][4 * d4 + 2]); acc[u] = __fadd_rn(acc[u], __fmul_rn(df, df));
+                            df = __fsub_rn(c.w, q[u][4 * d4 + 3]); acc[u] = __fadd_rn(acc[u], __fmul_rn(df, df));
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < QPW; ++u) {
+                        unsigned pass = __ballot_sync(0xffffffffu, valid && qe[u] == e && acc[u] < worst[u]);
+                        while (pass) {
+                            const int b = __ffs(pass) - 1;
+                            pass &= pass - 1;
+                            const float cd = __shfl_sync(0xffffffffu, acc[u], b);
+                            if (!(cd < worst[u])) continue;          // the worst entry moved since the ballot
+                            const int ci = t0 + j0 + b;
+                            const int pos = __popc(__ballot_sync(0xffffffffu, ld[u] <= cd));   // ties: earlier index first
+                            const float upd = __shfl_up_sync(0xffffffffu, ld[u], 1);
+                            const int upi = __shfl_up_sync(0xffffffffu, li[u], 1);
+                            if (lane > pos) { ld[u] = upd; li[u] = upi; }
+                            else if (lane == pos) { ld[u] = cd; li[u] = ci; }
+                            if (lane >= K) { ld[u] = INFINITY; li[u] = -1; }
+                            worst[u] = __shfl_sync(0xffffffffu, ld[u], K - 1);
+                        }
+                    }
+                }
+            }
+        }
+        // ---- write out: self dropped when !loop, survivors packed to the front in (distance, index) order
+#pragma unroll
+        for (int u = 0; u < QPW; ++u) {
+            if (qi[u] >= N) continue;
+            const bool keep = lane < K && li[u] >= 0 && (loop || li[u] != qi[u]);
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            const int rank = __popc(m & ((1u << lane) - 1u));
+            int *out = nbr + (size_t)qi[u] * K;
+            if (keep) out[rank] = li[u];
+            const int n = __popc(m);
+            if (lane >= n && lane < K) out[lane] = -1;
+            if (lane == 0) deg[qi[u]] = n;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) deg[N] = 0;
+}
+
+__global__ void __launch_bounds__(256) k_knn_fill(const int *__restrict__ nbr, const int *__restrict__ rowptr, int N, int K,
+                                                  int *__restrict__ col, long long capacity,
+                                                  long long *__restrict__ ei64) {
+    pdl_sync();
+    const long long total = (long long)N * K;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(t / K), s = (int)(t - (long long)i * K);
+        const int a = rowptr[i], n = rowptr[i + 1] - a;
+        if (s >= n) continue;
+        const long long p = (long long)a + s;
+        if (p >= capacity) continue;
+        const int j = nbr[t];
+        if (col) col[p] = j;
+        if (ei64) { ei64[p] = j; ei64[capacity + p] = i; }      // row 0 = source (neighbour), row 1 = target (query)
+    }
+}
+
+struct KnnWs {
+    int *nbr;       // [N, K]
+    int *tiles;     // scan tile totals
+};
+
+size_t knn_layout(int N, int K, char *base, KnnWs *w) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+    const size_t o_nbr = take((size_t)max(N, 1) * K * sizeof(int));
+    const size_t o_tiles = take(((size_t)(N + 1) / 1024 + 2) * sizeof(int));
+    if (w) { w->nbr = (int *)(base + o_nbr); w->tiles = (int *)(base + o_tiles); }
+    return off;
+}
+
+}  // namespace
+
+int exclusive_scan_inplace(int *data, int n, int *tile_totals, int *total_out, cudaStream_t st);
+
+namespace {
+
+template <int DP, int QPW>
+int launch_search(const float *x, int stride, int dim, const int *ptr, int N, int B, int K, int loop, int *nbr, int *deg,
+                  cudaStream_t st) {
+    const int qb = KNN_WARPS * QPW;
+    const int grid = persistent_grid(((long long)N + qb - 1) / qb, 16);
+    GM_LAUNCH_PDL((k_knn_search<DP, QPW>), grid, KNN_THREADS, 0, st, x, stride, dim, ptr, N, B, K, loop, nbr, deg);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+}  // namespace
+}  // namespace gm
+
+using namespace gm;
+
+extern "C" {
+
+size_t gm_knn_graph_ws_bytes(int N, int k, int loop) {
+    const int K = k + (loop ? 0 : 1);
+    return knn_layout(N < 0 ? 0 : N, K < 1 ? 1 : K, nullptr, nullptr);
+}
+
+int gm_knn_graph_count(const float *x, int x_stride, int dim, const int *ptr, int N, int B, int k, int loop, void *ws,
+                       size_t ws_bytes, int *rowptr_out, void *stream) {
+    if (N < 0 || B < 0 || !rowptr_out || !ws || (N > 0 && (!x || !ptr || B < 1))) return GM_ERR_INVALID_ARGUMENT;
+    const int K = k + (loop ? 0 : 1);
+    if (k < 1 || K > KNN_MAX_K || dim < 1 || dim > 64 || x_stride < dim) return GM_ERR_UNSUPPORTED;
+    if (ws_bytes < knn_layout(N, K, nullptr, nullptr)) return GM_ERR_CAPACITY;
+    cudaStream_t st = as_stream(stream);
+    if (N == 0) {
+        GM_CUDA_TRY(cudaMemsetAsync(rowptr_out, 0, sizeof(int), st));
+        return GM_OK;
+    }
+    KnnWs w;
+    knn_layout(N, K, (char *)ws, &w);
+    int rc;
+    if (dim <= 4) rc = launch_search<4, 4>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
+    else if (dim <= 8) rc = launch_search<8, 4>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
+    else if (dim <= 16) rc = launch_search<16, 2>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
+    else if (dim <= 32) rc = launch_search<32, 2>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
+    else rc = launch_search<64, 1>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
+    GM_TRY(rc);
+    GM_TRY(exclusive_scan_inplace(rowptr_out, N + 1, w.tiles, nullptr, st));
+    return GM_OK;
+}
+
+int gm_knn_graph_fill(int N, int k, int loop, const void *ws, size_t ws_bytes, const int *rowptr, int *col_out,
+                      long long col_capacity, int64_t *edge_index64_out, void *stream) {
+    if (N < 0 || !ws || !rowptr || col_capacity < 0) return GM_ERR_INVALID_ARGUMENT;
+    const int K = k + (loop ? 0 : 1);
+    if (k < 1 || K > KNN_MAX_K) return GM_ERR_UNSUPPORTED;
+    if (ws_bytes < knn_layout(N, K, nullptr, nullptr)) return GM_ERR_CAPACITY;
+    if (N == 0 || col_capacity == 0) return GM_OK;
+    KnnWs w;
+    knn_layout(N, K, (char *)ws, &w);
+    cudaStream_t st = as_stream(stream);
+    const int grid = persistent_grid(((long long)N * K + 255) / 256, 8);
+    GM_LAUNCH_PDL(k_knn_fill, grid, 256, 0, st, (const int *)w.nbr, rowptr, N, K, col_out, col_capacity,
+                  (long long *)edge_index64_out);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+}  // extern "C"

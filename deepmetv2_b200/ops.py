@@ -3,6 +3,7 @@ libgraphmet.so (CUDA, sm_100a) — same names, argument meaning and return types
 
 * ``radius_graph``  <- torch_cluster.radius_graph   (train.py:48, evaluate.py:88, plt_weight.py:122)
 * ``scatter_add``   <- torch_scatter.scatter_add     (model/net.py:8,55-56,79-80,132-133)
+* ``knn_graph``     <- torch_cluster.knn_graph      (model/graph_met_network.py:63, dynamic_reduction_network.py:86,95)
 * ``build_graph``   the same search without materialising the int64 ``edge_index`` (fused path)
 
 plus ``prepare_inputs`` (train.py:42-46 fused) and ``batch_to_ptr``.
@@ -195,6 +196,41 @@ def radius_graph(x, r, batch=None, loop=False, max_num_neighbors=32, flow="sourc
     if flow == "target_to_source":
         return ei.flip(0)
     return EdgeIndex.wrap(ei, g)
+
+
+def knn_graph(x, k, batch=None, loop=False, flow="source_to_target", ptr_i32=None):
+    """Drop-in for ``torch_cluster.knn_graph`` (model/graph_met_network.py:63 sketch, dynamic_reduction_network.py:86,95):
+    LongTensor[2,E]; per query i its ``k`` nearest nodes j of the same event (``k+1`` searched and the self pair dropped
+    when ``loop=False``), ordered by (distance, index); row 0 = j, row 1 = i for ``source_to_target``."""
+    assert flow in ("source_to_target", "target_to_source")
+    _lib.require_cuda(x, "x")
+    if x.dim() == 1:
+        x = x[:, None]
+    assert x.dtype == torch.float32 and x.stride(1) == 1
+    N, dim = x.shape
+    dev = x.device
+    if ptr_i32 is None:
+        if batch is None:
+            ptr_i32 = torch.tensor([0, N], dtype=torch.int32, device=dev)
+        else:
+            B = int(batch[-1].item()) + 1 if N > 0 else 0
+            ptr_i32 = batch_to_ptr(batch, B)
+    B = ptr_i32.numel() - 1
+    if dim > 64 or k + (0 if loop else 1) > 32:
+        raise NotImplementedError("knn_graph kernels cover dim <= 64 and k + (not loop) <= 32")
+    l = lib()
+    ws = torch.empty(l.gm_knn_graph_ws_bytes(N, int(k), int(bool(loop))), dtype=torch.uint8, device=dev)
+    rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+    check(l.gm_knn_graph_count(ptr(x), x.stride(0), dim, ptr(ptr_i32), N, B, int(k), int(bool(loop)), ptr(ws),
+                               ws.numel(), ptr(rowptr), stream()), "gm_knn_graph_count")
+    E = int(rowptr[-1].item())                        # one D2H sync, like upstream's `col != -1` mask
+    col = torch.empty(max(E, 1), dtype=torch.int32, device=dev)
+    ei = torch.empty(2, E, dtype=torch.int64, device=dev)
+    check(l.gm_knn_graph_fill(N, int(k), int(bool(loop)), ptr(ws), ws.numel(), ptr(rowptr), ptr(col), E, ptr(ei),
+                              stream()), "gm_knn_graph_fill")
+    if flow == "target_to_source":
+        return ei.flip(0)
+    return EdgeIndex.wrap(ei, GraphCSR(rowptr, col, N, E, -1, num_capped=1))     # a kNN graph is not symmetric
 
 
 def csr_from_edge_index(edge_index: torch.Tensor, num_nodes: int) -> GraphCSR:

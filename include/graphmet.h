@@ -154,6 +154,26 @@ int gm_edge_index_to_csr(const int64_t *edge_index, long long E, int N, void *ws
                          int *rowptr_out, int *col_out, void *stream);
 
 /* ---------------------------------------------------------------------------------
+ * f4 / f1. k-nearest-neighbour graph per event in a latent space (dim <= 64) — replaces
+ *     torch_cluster.knn_graph(x, k, batch, loop, flow) as sketched at
+ *     model/graph_met_network.py:63 (k=20, loop=True on the 32-d embedding) and used by
+ *     model/dynamic_reduction_network.py:86,95 (loop=False).
+ *     dist = sum_d (x_j[d]-x_i[d])^2 in fp32, dimension order, separate multiply/add; candidates
+ *     of the query's own event in ascending index; ties to the lower index; K = k + !loop best
+ *     per query ordered by (distance, index); self pair removed afterwards when !loop (so a
+ *     query keeps k+1 neighbours when self is not among its K best).  k + !loop <= 32.
+ *     Two-call protocol like the radius graph: _count searches, leaves the padded neighbour
+ *     table in ws and writes rowptr (rowptr[N] = E on the device); _fill packs col (int32,
+ *     CSR by target = query) and, optionally, int64 edge_index[2,capacity] (row 0 = source =
+ *     neighbour, row 1 = target = query: flow='source_to_target').
+ * --------------------------------------------------------------------------------- */
+size_t gm_knn_graph_ws_bytes(int N, int k, int loop);
+int gm_knn_graph_count(const float *x, int x_stride, int dim, const int *ptr, int N, int B, int k, int loop,
+                       void *ws, size_t ws_bytes, int *rowptr_out, void *stream);
+int gm_knn_graph_fill(int N, int k, int loop, const void *ws, size_t ws_bytes, const int *rowptr,
+                      int *col_out, long long col_capacity, int64_t *edge_index64_out, void *stream);
+
+/* ---------------------------------------------------------------------------------
  * Whole-network forward — replaces Net.forward / GraphMETNetwork.forward
  * (model/net.py:45-47, model/graph_met_network.py:47-69) given the CSR graph.
  *

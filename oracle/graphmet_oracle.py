@@ -111,6 +111,47 @@ def radius_graph(x, r, batch=None, loop=False, max_num_neighbors=32,
     return torch.stack([row, col], dim=0)
 
 
+_KNN_LIB = None
+
+
+def _knn_lib():
+    global _KNN_LIB
+    if _KNN_LIB is None:
+        so = os.path.join(_HERE, "_build", "libknn_oracle.so")
+        if not os.path.exists(so):
+            subprocess.check_call(["make", "-s", "-C", _HERE])
+        lib = ctypes.CDLL(so)
+        lib.oracle_knn_graph.restype = ctypes.c_longlong
+        lib.oracle_knn_graph.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                         ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+        _KNN_LIB = lib
+    return _KNN_LIB
+
+
+def knn_graph(x, k, batch=None, loop=False, flow="source_to_target"):
+    """[upstream torch_cluster.knn_graph] (graph_met_network.py:63 sketch; dynamic_reduction_network.py:86,95):
+    LongTensor[2,E], per query ordered by (distance, index); see knn_bruteforce.c."""
+    assert flow in ("source_to_target", "target_to_source")
+    xs = x.detach().cpu().to(torch.float32).contiguous()
+    if xs.dim() == 1:
+        xs = xs[:, None].contiguous()
+    N, dim = xs.shape
+    ptr = torch.tensor([0, N], dtype=torch.int64) if batch is None else batch_to_ptr(batch.detach().cpu())
+    K = k + (0 if loop else 1)
+    nbr = torch.full((max(N, 1), K), -1, dtype=torch.int64)
+    deg = torch.zeros(max(N, 1), dtype=torch.int64)
+    if N:
+        E = _knn_lib().oracle_knn_graph(xs.data_ptr(), dim, ptr.data_ptr(), ptr.numel() - 1, int(k), int(bool(loop)),
+                                        nbr.data_ptr(), deg.data_ptr())
+        assert E >= 0
+    nbr, deg = nbr[:N], deg[:N]
+    col = nbr[nbr >= 0]
+    row = torch.repeat_interleave(torch.arange(N, dtype=torch.int64), deg)
+    if flow == "source_to_target":
+        return torch.stack([col, row], dim=0)
+    return torch.stack([row, col], dim=0)
+
+
 def radius_graph_torch(x, r, batch=None, loop=False, max_num_neighbors=32):
     """Independent pure-torch O(n^2) cross-check of the C brute force (no cap handling
     beyond lowest-index truncation; fp32 non-fused d0*d0 + d1*d1)."""
