@@ -2,8 +2,8 @@
 //   knn_graph(emb, k=20, batch, loop=True)         /root/reference/model/graph_met_network.py:63 (sketched there)
 //   knn_graph(x, self.k, batch, loop=False, flow)  /root/reference/model/dynamic_reduction_network.py:86,95
 // [upstream torch_cluster.knn_graph] semantics restated in oracle/knn_bruteforce.c; this file is its CUDA form and is
-// bit-identical to it: dist = sum_d (x_j[d] - x_i[d])^2 accumulated in fp32 in dimension order with SEPARATE multiply
-// and add (no contraction), candidates scanned in ascending index, a candidate enters the list only when strictly
+// bit-identical to it: dist = sum_d (x_j[d] - x_i[d])^2 accumulated in fp32 in dimension order as fmaf(df, df, dist)
+// (what nvcc makes of upstream's `dist += df * df`), candidates scanned in ascending index, a candidate enters the list only when strictly
 // closer than the current worst entry => ties go to the lower index; the K best (K = k + !loop) come out ordered by
 // (distance, index), the self pair is dropped afterwards when loop == 0 (so a node with > k exact duplicates at lower
 // indices keeps k + 1 neighbours, as upstream's `row != col` mask does).
@@ -18,8 +18,14 @@ namespace {
 
 constexpr int KNN_WARPS = 8;
 constexpr int KNN_THREADS = KNN_WARPS * 32;
-constexpr int KNN_TILE = 128;      // candidates per shared-memory tile
+constexpr int KNN_TILE = 128;      // candidates per shared-memory tile (64 at DP = 64: two tiles stay under 48 KB)
 constexpr int KNN_MAX_K = 32;      // list entries per query = one per lane
+
+__device__ __forceinline__ void cp_async16(float *smem_dst, const float *gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __device__ __forceinline__ int event_of(const int *__restrict__ ptr, int B, int i) {
     int lo = 0, hi = B;            // last e with ptr[e] <= i
@@ -36,8 +42,25 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
                                                             int *__restrict__ nbr, int *__restrict__ deg) {
     constexpr int RS = DP + 4;                       // shared row stride (floats)
     constexpr int QB = KNN_WARPS * QPW;              // queries per CTA
-    __shared__ __align__(16) float s_tile[KNN_TILE * RS];
+    constexpr int TILE = DP >= 64 ? KNN_TILE / 2 : KNN_TILE;
+    __shared__ __align__(16) float s_tile[2][TILE * RS];     // tile t+1 lands (cp.async) while tile t is searched
     pdl_sync();
+    // 16-byte asynchronous copies when rows are whole float4s; otherwise element-wise with zero padding up to DP
+    const bool vec = dim == DP && (stride & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+    auto load_tile = [&](int buf, int t0, int rows) {
+        float *dst = s_tile[buf];
+        if (vec) {
+            for (int c = threadIdx.x; c < rows * (DP / 4); c += KNN_THREADS) {
+                const int r = c / (DP / 4), d4 = c - r * (DP / 4);
+                cp_async16(dst + r * RS + 4 * d4, x + (size_t)(t0 + r) * stride + 4 * d4);
+            }
+        } else {
+            for (int t = threadIdx.x; t < rows * DP; t += KNN_THREADS) {
+                const int r = t / DP, d = t - r * DP;
+                dst[r * RS + d] = d < dim ? x[(size_t)(t0 + r) * stride + d] : 0.f;
+            }
+        }
+    };
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (long long blk = blockIdx.x; blk * QB < N; blk += gridDim.x) {
         const int q0 = (int)(blk * QB), q1 = min(N, q0 + QB);
@@ -58,18 +81,19 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
         const int e_first = event_of(ptr, B, q0), e_last = event_of(ptr, B, q1 - 1);
         for (int e = e_first; e <= e_last; ++e) {
             const int c0 = __ldg(ptr + e), c1 = __ldg(ptr + e + 1);
-            for (int t0 = c0; t0 < c1; t0 += KNN_TILE) {
-                const int rows = min(KNN_TILE, c1 - t0);
-                __syncthreads();                     // previous tile fully consumed
-                for (int t = threadIdx.x; t < rows * DP; t += KNN_THREADS) {
-                    const int r = t / DP, d = t - r * DP;
-                    s_tile[r * RS + d] = d < dim ? x[(size_t)(t0 + r) * stride + d] : 0.f;
-                }
-                __syncthreads();
+            if (c0 >= c1) continue;
+            __syncthreads();                         // both buffers free (previous event / query block fully searched)
+            load_tile(0, c0, min(TILE, c1 - c0));
+            int buf = 0;
+            for (int t0 = c0; t0 < c1; t0 += TILE, buf ^= 1) {
+                const int rows = min(TILE, c1 - t0);
+                cp_async_wait_all();
+                __syncthreads();                     // tile `buf` visible to all; everyone is done with tile `buf ^ 1`
+                if (t0 + TILE < c1) load_tile(buf ^ 1, t0 + TILE, min(TILE, c1 - t0 - TILE));
                 for (int j0 = 0; j0 < rows; j0 += 32) {
                     const int j = j0 + lane;
                     const bool valid = j < rows;
-                    const float4 *row = reinterpret_cast<const float4 *>(s_tile + (valid ? j : 0) * RS);
+                    const float4 *row = reinterpret_cast<const float4 *>(s_tile[buf] + (valid ? j : 0) * RS);
                     float acc[QPW];
 #pragma unroll
                     for (int u = 0; u < QPW; ++u) acc[u] = 0.f;
@@ -79,10 +103,10 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
 #pragma unroll
                         for (int u = 0; u < QPW; ++u) {
                             float df;
-                            df = __fsub_rn(c.x, q[u][4 * d4 + 0]); acc[u] = __fadd_rn(acc[u], __fmul_rn(df, df));
-                            df = __fsub_rn(c.y, q[u][4 * d4 + 1]); acc[u] = __fadd_rn(acc[u], __fmul_rn(df, df));
-                            df = __fsub_rn(c.z, q[u][4 * d4 + 2]); acc[u] = __fadd_rn(acc[u], __fmul_rn(df, df));
-                            df = __fsub_rn(c.w, q[u][4 * d4 + 3]); acc[u] = __fadd_rn(acc[u], __fmul_rn(df, df));
+                            df = __fsub_rn(c.x, q[u][4 * d4 + 0]); acc[u] = __fmaf_rn(df, df, acc[u]);
+                            df = __fsub_rn(c.y, q[u][4 * d4 + 1]); acc[u] = __fmaf_rn(df, df, acc[u]);
+                            df = __fsub_rn(c.z, q[u][4 * d4 + 2]); acc[u] = __fmaf_rn(df, df, acc[u]);
+                            df = __fsub_rn(c.w, q[u][4 * d4 + 3]); acc[u] = __fmaf_rn(df, df, acc[u]);
                         }
                     }
 #pragma unroll
@@ -99,7 +123,7 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
                             const int upi = __shfl_up_sync(0xffffffffu, li[u], 1);
                             if (lane > pos) { ld[u] = upd; li[u] = upi; }
                             else if (lane == pos) { ld[u] = cd; li[u] = ci; }
-                            if (lane >= K) { ld[u] = INFINITY; li[u] = -1; }
+                            // (lanes >= K keep what falls off the end: never <= cd again, never written out)
                             worst[u] = __shfl_sync(0xffffffffu, ld[u], K - 1);
                         }
                     }

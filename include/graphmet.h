@@ -158,7 +158,7 @@ int gm_edge_index_to_csr(const int64_t *edge_index, long long E, int N, void *ws
  *     torch_cluster.knn_graph(x, k, batch, loop, flow) as sketched at
  *     model/graph_met_network.py:63 (k=20, loop=True on the 32-d embedding) and used by
  *     model/dynamic_reduction_network.py:86,95 (loop=False).
- *     dist = sum_d (x_j[d]-x_i[d])^2 in fp32, dimension order, separate multiply/add; candidates
+ *     dist = fmaf(df, df, dist) over d in order, df = x_j[d]-x_i[d], fp32; candidates
  *     of the query's own event in ascending index; ties to the lower index; K = k + !loop best
  *     per query ordered by (distance, index); self pair removed afterwards when !loop (so a
  *     query keeps k+1 neighbours when self is not among its K best).  k + !loop <= 32.

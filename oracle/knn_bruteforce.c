@@ -19,8 +19,9 @@
  *     among its K best (more than k exact duplicates at lower indices);
  *   - per query n_y of event e, candidates n_x scan [ptr[e], ptr[e+1]) in
  *     ascending order; dist = sum_d (x[n_x,d] - y[n_y,d])^2 in fp32, dimension
- *     order, here with separate multiply and add (built with
- *     -ffp-contract=off; the CUDA kernel uses __fmul_rn/__fadd_rn to match);
+ *     order; nvcc contracts upstream's `dist += df * df` to an FMA, so here
+ *     dist = fmaf(df, df, dist) explicitly (as radius_bruteforce.c does), and
+ *     the CUDA kernel uses __fsub_rn / __fmaf_rn to match;
  *   - a candidate replaces the current worst entry only when strictly closer,
  *     so ties go to the lower index; the K best leave ordered by (dist, index);
  *   - events with fewer than K nodes yield fewer neighbours (-1 entries are
@@ -55,8 +56,7 @@ long long oracle_knn_graph(const float *x, int dim, const int64_t *ptr, int B, i
                 float acc = 0.0f;
                 for (int d = 0; d < dim; ++d) {
                     const float df = cj[d] - qi[d];
-                    const float sq = df * df;
-                    acc = acc + sq;
+                    acc = fmaf(df, df, acc);
                 }
                 if (acc < bd[K - 1]) {
                     int s = K - 1;
