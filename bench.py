@@ -155,6 +155,9 @@ def run_cpu_arm(workload, steps, warmup):
 
 # ------------------------------------------------------------------------------------------------ main
 def main():
+    if os.environ.get("GM_BENCH_WATCHDOG"):       # debugging aid: dump every thread's stack and exit if the run stalls
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["GM_BENCH_WATCHDOG"]), exit=True)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=30)

@@ -26,7 +26,19 @@ namespace {
 
 constexpr int GLD = 36;                 // float4-aligned padded tile row (conflict-free LDS.128 row-per-thread)
 constexpr int GP_STRIDE = 2112;         // floats per CTA in the parameter-gradient partial buffer
-constexpr int MAX_BWD_CTAS = 148 * 2;
+// resident CTAs per SM the backward node kernels are compiled for (= their grid: one wave)
+#ifndef GM_BWD_OCC_HEAD
+#define GM_BWD_OCC_HEAD 4
+#endif
+#ifndef GM_BWD_OCC_ENC
+#define GM_BWD_OCC_ENC 2
+#endif
+#ifndef GM_BWD_OCC_CONV
+#define GM_BWD_OCC_CONV 3
+#endif
+constexpr int BWD_OCC_MAX = GM_BWD_OCC_HEAD > GM_BWD_OCC_CONV ? (GM_BWD_OCC_HEAD > GM_BWD_OCC_ENC ? GM_BWD_OCC_HEAD : GM_BWD_OCC_ENC)
+                                                             : (GM_BWD_OCC_CONV > GM_BWD_OCC_ENC ? GM_BWD_OCC_CONV : GM_BWD_OCC_ENC);
+constexpr int MAX_BWD_CTAS = 148 * BWD_OCC_MAX;
 constexpr int MAX_STAGES = GM_MAX_CONV_DEPTH + 2;   // head, conv layers, encoder
 
 struct BwdWs {
@@ -210,7 +222,7 @@ __device__ __forceinline__ void bn_sums_finalize(const BnSumOut &o, float *scrat
 
 // ----------------------------------------------------------------------------------------- head backward
 // partial layout: dW1[16][32] @0, db1[16] @512, dW2[16] @528, db2 @544
-__global__ void __launch_bounds__(NODE_TILE, 2)
+__global__ void __launch_bounds__(NODE_TILE, GM_BWD_OCC_HEAD)
 k_head_bwd(const float *__restrict__ emb, const float *__restrict__ out, const float *__restrict__ grad_out,
            const int *__restrict__ perm, int N, const float *__restrict__ w1, const float *__restrict__ b1,
            const float *__restrict__ w2, int apply_sigmoid, float *__restrict__ G, float *__restrict__ gpart,
@@ -374,7 +386,7 @@ __global__ void __launch_bounds__(256) k_scatter_s(const float *__restrict__ G, 
 // thread) and the new G leaves from registers as whole 128-byte rows; the parameter-gradient outer products and
 // the BatchNorm sums of the layer below read the same tiles.  [c][k] weights are K-major for the transposed product.
 constexpr int CB_THREADS = 256;
-__global__ void __launch_bounds__(CB_THREADS, 2)
+__global__ void __launch_bounds__(CB_THREADS, GM_BWD_OCC_CONV)
 k_conv_bwd_node2(const float *__restrict__ x, const float *__restrict__ raw, BnBwd bn, const float *__restrict__ S, int N,
                  const float *__restrict__ W, float *__restrict__ G, float *__restrict__ gpart, BnSumOut bo) {
     extern __shared__ __align__(16) float smem[];
@@ -493,7 +505,7 @@ struct EncBwdArgs {
     float *gpart;
 };
 
-__global__ void __launch_bounds__(NODE_TILE, 2) k_encode_bwd(EncBwdArgs a) {
+__global__ void __launch_bounds__(NODE_TILE, GM_BWD_OCC_ENC) k_encode_bwd(EncBwdArgs a) {
     extern __shared__ __align__(16) float smem[];
     float *s_enc_w = smem;                       // 1024
     float *s_cont_w = s_enc_w + H * H;           // 128  [16][8]
@@ -672,7 +684,9 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
     BwdWs w;
     bwd_ws_layout(N, (char *)bwd_ws, &w);
     const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
-    const int ngrid = persistent_grid(tiles, 2);
+    const int ngrid_head = persistent_grid(tiles, GM_BWD_OCC_HEAD);   // thread per node
+    const int ngrid_enc = persistent_grid(tiles, GM_BWD_OCC_ENC);
+    const int ngrid_conv = persistent_grid(tiles, GM_BWD_OCC_CONV);   // k_conv_bwd_node2 (tile products)
     const float inv_n = training ? 1.f / (float)N : 0.f;
     GM_CUDA_TRY(cudaMemsetAsync(w.counters, 0, NUM_COUNTERS * sizeof(int), st));
 
@@ -690,13 +704,14 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
 
     Segs segs{};
     auto add_seg = [&](int stage, float *dst, int dst_ld, int off, int rows, int src_ld, int cols) {
+        const int ngrid = stage == 0 ? ngrid_head : stage <= depth ? ngrid_conv : ngrid_enc;
         if (dst) segs.s[segs.n++] = Seg{gpart(stage), dst, dst_ld, off, rows, src_ld, cols, ngrid};
     };
 
     // ---- head (stage 0); also produces the BatchNorm sums of the topmost BatchNorm (index depth)
     {
         TimedRegion tr(GM_TIMER_HEAD_BWD, st);
-        GM_LAUNCH_PDL(k_head_bwd, ngrid, NODE_TILE, 0, st, f.emb[depth], out, grad_out, node_perm, N, p->out1_w, p->out1_b,
+        GM_LAUNCH_PDL(k_head_bwd, ngrid_head, NODE_TILE, 0, st, f.emb[depth], out, grad_out, node_perm, N, p->out1_w, p->out1_b,
                       p->out2_w, apply_sigmoid, w.G, gpart(0), sum_out(depth));
         GM_LAUNCH_CHECK();
     }
@@ -723,7 +738,7 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
         }
         {
             TimedRegion tr(GM_TIMER_CONV_NODE_BWD, st);
-            GM_LAUNCH_PDL(k_conv_bwd_node2, ngrid, CB_THREADS, CONV_BWD_SMEM, st, f.emb[l], f.conv[l], bn_in(l + 1), w.S, N,
+            GM_LAUNCH_PDL(k_conv_bwd_node2, ngrid_conv, CB_THREADS, CONV_BWD_SMEM, st, f.emb[l], f.conv[l], bn_in(l + 1), w.S, N,
                           p->conv_w[l], w.G, gpart(stage), sum_out(l));
             GM_LAUNCH_CHECK();
         }
@@ -744,7 +759,7 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
         GM_CUDA_TRY(cudaFuncSetAttribute(k_encode_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ENC_BWD_SMEM));
         {
             TimedRegion tr(GM_TIMER_ENCODE_BWD, st);
-            GM_LAUNCH_PDL(k_encode_bwd, ngrid, NODE_TILE, ENC_BWD_SMEM, st, ea);
+            GM_LAUNCH_PDL(k_encode_bwd, ngrid_enc, NODE_TILE, ENC_BWD_SMEM, st, ea);
             GM_LAUNCH_CHECK();
         }
         const int CD = p->continuous_dim;
