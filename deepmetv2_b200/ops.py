@@ -198,6 +198,29 @@ def radius_graph(x, r, batch=None, loop=False, max_num_neighbors=32, flow="sourc
     return EdgeIndex.wrap(ei, g)
 
 
+def build_knn(x: torch.Tensor, k: int, ptr_i32: torch.Tensor, loop: bool = False) -> GraphCSR:
+    """The k-NN search without materialising the int64 ``edge_index`` and WITHOUT a host sync: ``col`` is allocated at
+    its upper bound ``N * (k + !loop)`` and ``rowptr[N]`` (= E) stays on the device (``num_edges`` is the capacity).
+    What a per-layer dynamic graph (model/graph_met_network.py:63) wants: ``EdgeConv(...)(emb, build_knn(emb, 20, ptr, True))``."""
+    _lib.require_cuda(x, "x")
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    N, dim = x.shape
+    K = int(k) + (0 if loop else 1)
+    if dim > 64 or K > 32:
+        raise NotImplementedError("knn_graph kernels cover dim <= 64 and k + (not loop) <= 32")
+    dev = x.device
+    l = lib()
+    ws = torch.empty(l.gm_knn_graph_ws_bytes(N, int(k), int(bool(loop))), dtype=torch.uint8, device=dev)
+    rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+    cap = max(N * K, 1)
+    col = torch.empty(cap, dtype=torch.int32, device=dev)
+    check(l.gm_knn_graph_count(ptr(x), x.stride(0), dim, ptr(ptr_i32), N, ptr_i32.numel() - 1, int(k), int(bool(loop)),
+                               ptr(ws), ws.numel(), ptr(rowptr), stream()), "gm_knn_graph_count")
+    check(l.gm_knn_graph_fill(N, int(k), int(bool(loop)), ptr(ws), ws.numel(), ptr(rowptr), ptr(col), cap, None,
+                              stream()), "gm_knn_graph_fill")
+    return GraphCSR(rowptr, col, N, cap, -1, num_capped=1)
+
+
 def knn_graph(x, k, batch=None, loop=False, flow="source_to_target", ptr_i32=None):
     """Drop-in for ``torch_cluster.knn_graph`` (model/graph_met_network.py:63 sketch, dynamic_reduction_network.py:86,95):
     LongTensor[2,E]; per query i its ``k`` nearest nodes j of the same event (``k+1`` searched and the self pair dropped

@@ -83,3 +83,27 @@ def test_edgeconv_on_dynamic_knn_graph_matches_oracle(aggr):
         got = conv(emb.to(DEV), ei)
     err = (got.cpu() - want).abs().max().item() / want.abs().max().item()
     assert err < 1e-5, err
+
+
+def test_build_knn_is_sync_free_and_feeds_edgeconv():
+    """ops.build_knn: CSR at its upper-bound capacity, E left on the device; same rows as knn_graph; EdgeConv takes it."""
+    sizes = [300, 5, 0, 260]
+    batch = _batch(sizes)
+    ptr = torch.tensor([0, 300, 305, 305, 565], dtype=torch.int32, device=DEV)
+    torch.manual_seed(4)
+    emb = torch.randn(sum(sizes), 32)
+    for loop in (True, False):
+        want = O.knn_graph(emb, 8, batch, loop=loop)
+        g = ops.build_knn(emb.to(DEV), 8, ptr, loop=loop)
+        E = int(g.rowptr[-1])
+        assert E == want.shape[1] and g.col.numel() >= E
+        assert torch.equal(g.col[:E].long().cpu(), want[0])
+        deg = (g.rowptr[1:] - g.rowptr[:-1]).long().cpu()
+        assert torch.equal(torch.repeat_interleave(torch.arange(len(deg)), deg), want[1])
+    lin = torch.nn.Sequential(torch.nn.Linear(64, 32))
+    ref = O.EdgeConv(lin, "max")(emb, O.knn_graph(emb, 8, batch, loop=True)).detach()
+    conv = G.EdgeConv(torch.nn.Sequential(torch.nn.Linear(64, 32)), "max").to(DEV)
+    conv.nn.load_state_dict(lin.state_dict())
+    with torch.no_grad():
+        got = conv(emb.to(DEV), ops.build_knn(emb.to(DEV), 8, ptr, loop=True))
+    assert (got.cpu() - ref).abs().max().item() / ref.abs().max().item() < 1e-5
