@@ -154,6 +154,68 @@ def run_cpu_arm(workload, steps, warmup):
 
 
 # ------------------------------------------------------------------------------------------------ main
+def run_knn(args):
+    """Side line (row f4 / f1, not the headline metric): the k-NN graph of a c2-shaped batch in the 32-d embedding,
+    k = 20, loop = True (model/graph_met_network.py:63), with the oracle's C brute force timed beside it."""
+    import numpy as np
+    import torch
+    from deepmetv2_b200 import ops, synth
+    from deepmetv2_b200._lib import lib, ptr, stream, check
+    dev = torch.device("cuda", 0)
+    B, dim, k = 32, 32, 20
+    b = synth.make_batch(B, "dytt", seed=2000)
+    N = b.x.shape[0]
+    hx = torch.randn(N, dim, generator=torch.Generator().manual_seed(0)).pin_memory()
+    x, p = hx.to(dev), b.ptr.to(dev).int()
+    l = lib()
+    ws = torch.empty(l.gm_knn_graph_ws_bytes(N, k, 1), dtype=torch.uint8, device=dev)
+    rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+    col = torch.empty(N * k, dtype=torch.int32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step():
+        check(l.gm_knn_graph_count(ptr(x), dim, dim, ptr(p), N, B, k, 1, ptr(ws), ws.numel(), ptr(rowptr), stream()), "knn")
+        check(l.gm_knn_graph_fill(N, k, 1, ptr(ws), ws.numel(), ptr(rowptr), ptr(col), N * k, None, stream()), "knn")
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    l.gm_launch_count(1)
+    tot = 0.0
+    for _ in range(args.steps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); step(); e1.record(); torch.cuda.synchronize()
+        tot += e0.elapsed_time(e1)
+    launches = l.gm_launch_count(0)
+    ms = tot / args.steps
+    t0 = time.perf_counter()
+    for _ in range(args.steps):                       # host x -> H2D -> search -> int64 edge_index on the host
+        ei = ops.knn_graph(hx.to(dev, non_blocking=True), k, ptr_i32=p, loop=True).cpu()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    sizes = (b.ptr[1:] - b.ptr[:-1]).double()
+    flops = 3.0 * float((sizes * sizes).sum()) * dim
+    from oracle import graphmet_oracle as O           # CPU leg: 2 events of the batch, one core
+    n2 = int(b.ptr[2])
+    t0 = time.perf_counter()
+    O.knn_graph(hx[:n2], k, b.batch[:n2], loop=True)
+    cpu_s = time.perf_counter() - t0
+    print(json.dumps({
+        "metric": "k-NN graph events/sec", "value": B / ms * 1e3, "unit": "events/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "knn_graph(emb[N,32], k=20, loop=True) on 32 DY/TT-shaped events", "nodes": N,
+                   "l2": "flushed between timed iterations (256 MiB memset)"},
+        "gpu_launches": int(launches),
+        "roofline": {"kernel": "k_knn_search", "bound": "fp32 pipe (FSUB + FFMA per pair*dim)", "achieved": flops / ms / 1e9,
+                     "peak": 148 * 128 * 1.965 * 1.5 / 1e3, "unit": "TFLOP/s", "frac": flops / ms / 1e9 / (148 * 128 * 1.965 * 1.5 / 1e3),
+                     "traffic": 7189504, "note": "peak = 148 SMs x 128 lanes x 1.965 GHz x 3 flop per 2 instructions"},
+        "cpu_baseline": {"value": 2 / cpu_s, "unit": "events/s", "cores": 1, "kind": "port",
+                         "sample": "2 of the 32 events through oracle/knn_bruteforce.c"},
+        "e2e": {"value": B / e2e_s, "unit": "events/s", "h2d_bytes_per_step": N * dim * 4,
+                "d2h_bytes_per_step": int(ei.numel()) * 8, "api": "ops.knn_graph"},
+    }))
+
+
 def main():
     if os.environ.get("GM_BENCH_WATCHDOG"):       # debugging aid: dump every thread's stack and exit if the run stalls
         import faulthandler
@@ -163,13 +225,17 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["knn"])
     ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "bf16", "tf32x3"])
     ap.add_argument("--graph", default="implicit", choices=["implicit", "csr"],
                     help="implicit: cell-staged EdgeConv, no edge list (default; fp32 only). csr: explicit edge list")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.workload == "knn":                       # side line, single GPU; the headline workloads follow below
+        if int(os.environ.get("RANK", "0")) == 0:
+            run_knn(args)
+        return
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
