@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the GraphMETNetwork hot path on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c5|knn]
 
 A "step" is one pass of the hot path over one batch of synthetic events:
   c2 (default, BASELINE.json configs[1]): TRAINING step (radius graph + forward + loss + backward +
@@ -9,8 +9,10 @@ A "step" is one pass of the hot path over one batch of synthetic events:
   c3: high-pile-up INFERENCE (graph + forward + MET/loss) on 256 events of ~5k candidates.
   c5: training on 32 high-pile-up events per GPU (the data-parallel config).
 Multi-GPU: one process per GPU (torchrun), events sharded by rank (weak scaling: every rank gets its own
-batch of the same shape), the only collective is the NCCL all-reduce of the 26.6 KB flat gradient.
-Rank 0 prints ONE JSON line.
+batch of the same shape); the only collective is the exchange of the 26.6 KB flat gradient, fused with AdamW
+in one kernel over NVLink peer memory (csrc/comm.cu).  Rank 0 prints ONE JSON line.  With the default workload the
+line also carries "side": the other BASELINE configurations (c5 training at every N; c3 inference fp32 and bf16
+tcgen05 at N = 1) measured in the same run with the same timing rules, so that they are driver-visible.
 """
 from __future__ import annotations
 
@@ -36,6 +38,7 @@ WORKLOADS = {
     "c5": (32, "highpu", "train", "GraphMETNetwork training step, 32 high-pile-up events (~5k cands) per GPU"),
 }
 N_ROTATE = 4   # distinct pre-generated batches cycled through the steps
+L2_NOTE = "flushed between timed iterations (256 MiB memset)"
 
 
 def _peaks():
@@ -48,6 +51,15 @@ def _peaks():
                 "source": "measured (MEASURED_PEAKS.json)"}
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0,
             "source": "fallback (B200_PROFILING.md)"}
+
+
+def config_dict(workload: str, precision: str, graph: str, world: int) -> dict:
+    """The workload description BOTH arms print (the driver compares the two dicts): static facts only; what a run
+    measures about its batches (nodes, edges, degrees) goes under "workload_stats"."""
+    n_ev, shape, mode, human = WORKLOADS[workload]
+    return {"workload": human, "events_per_gpu": n_ev, "event_shape": shape, "mode": mode, "edge_precision": precision,
+            "graph": graph, "l2": L2_NOTE, "rotating_batches": N_ROTATE,
+            "parallelism": f"dp{world}" if world > 1 else "single"}
 
 
 class ClockSampler:
@@ -98,19 +110,56 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def make_batches(workload: str, rank: int):
+def make_batches(workload: str, rank: int, n_rotate: int = N_ROTATE):
     from deepmetv2_b200 import synth
     n_ev, shape, _, _ = WORKLOADS[workload]
     cfg = int(workload[1:])
-    return [synth.make_batch(n_ev, shape, seed=1000 * cfg + 100 * rank + i) for i in range(N_ROTATE)]
+    return [synth.make_batch(n_ev, shape, seed=1000 * cfg + 100 * rank + i) for i in range(n_rotate)]
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm
-def cpu_train_or_eval_step(model, opt, batch, mode):
-    """The reference path on host cores: train.py:40-55 / evaluate.py:81-100 restated (oracle)."""
+def ckdtree_radius_graph(etaphi, ptr, r=0.4, cap=255):
+    """The radius graph the way torch_cluster's CPU path finds it (a KD-tree per event; upstream: nanoflann) with
+    scipy.spatial.cKDTree as the closest available stand-in: pairs within r, both directions, self loops, sorted by
+    (target, source), lowest `cap` sources per target.  TIMING stand-in only: it compares d <= r in float64, so pairs
+    exactly on the boundary may differ from the fp32 strict '<' of the exactness oracle (radius_bruteforce.c)."""
+    import numpy as np
+    from scipy.spatial import cKDTree
+    pos = etaphi.numpy().astype(np.float64)
+    p = ptr.numpy()
+    src, dst = [], []
+    for e in range(len(p) - 1):
+        n = int(p[e + 1] - p[e])
+        if n == 0:
+            continue
+        pairs = cKDTree(pos[p[e]:p[e + 1]]).query_pairs(r, output_type="ndarray")
+        me = np.arange(n, dtype=np.int64)
+        src.append(np.concatenate([pairs[:, 0], pairs[:, 1], me]) + p[e])
+        dst.append(np.concatenate([pairs[:, 1], pairs[:, 0], me]) + p[e])
+    if not src:
+        return torch.empty(2, 0, dtype=torch.int64)
+    src, dst = np.concatenate(src), np.concatenate(dst)
+    order = np.lexsort((src, dst))
+    src, dst = src[order], dst[order]
+    deg = np.bincount(dst, minlength=pos.shape[0])
+    if deg.max() > cap:
+        start = np.cumsum(deg) - deg
+        keep = np.arange(dst.shape[0]) - start[dst] < cap
+        src, dst = src[keep], dst[keep]
+    return torch.from_numpy(np.stack([src, dst]).astype(np.int64))
+
+
+def cpu_train_or_eval_step(model, opt, batch, mode, graph="ckdtree"):
+    """The reference path on host cores: train.py:40-55 / evaluate.py:81-100 restated (oracle).
+    Returns (loss, E, seconds spent in the graph build)."""
     from oracle import graphmet_oracle as O
     x_cont, x_cat, etaphi = O.prepare_inputs(batch.x)
-    ei = O.radius_graph(etaphi, r=0.4, batch=batch.batch, loop=True, max_num_neighbors=255)
+    t0 = time.perf_counter()
+    if graph == "ckdtree":
+        ei = ckdtree_radius_graph(etaphi, batch.ptr, r=0.4, cap=255)
+    else:
+        ei = O.radius_graph(etaphi, r=0.4, batch=batch.batch, loop=True, max_num_neighbors=255)
+    t_graph = time.perf_counter() - t0
     if mode == "train":
         opt.zero_grad()
         w = model(x_cont, x_cat, ei, batch.batch)
@@ -120,7 +169,7 @@ def cpu_train_or_eval_step(model, opt, batch, mode):
     else:
         w = model(x_cont, x_cat, ei, batch.batch)       # evaluate.py keeps autograd enabled
         loss = O.loss_fn(w, batch.x, batch.y, batch.batch)
-    return float(loss.item()), ei.shape[1]
+    return float(loss.item()), ei.shape[1], t_graph
 
 
 def cpu_sample(batch, workload):
@@ -133,6 +182,9 @@ def cpu_sample(batch, workload):
 
 
 def run_cpu_arm(workload, steps, warmup):
+    """plain-PyTorch restatement of the PyG CPU path on all host cores, warm-up `warmup` steps,
+    MEDIAN of `steps` timed steps; graph build by a KD-tree per event (cKDTree, the stand-in for torch_cluster's
+    nanoflann CPU path) inside the timed step, with the O(n^2) one-core C brute force timed beside it."""
     from oracle import graphmet_oracle as O
     torch.set_num_threads(os.cpu_count() or 1)
     torch.manual_seed(0)
@@ -143,22 +195,48 @@ def run_cpu_arm(workload, steps, warmup):
     samples = [cpu_sample(b, workload) for b in make_batches(workload, 0)]
     for i in range(warmup):
         cpu_train_or_eval_step(model, opt, samples[i % N_ROTATE][0], mode)
-    t0 = time.perf_counter()
-    ev = 0
+    times, graph_times = [], []
     for i in range(steps):
-        s, n_ev = samples[i % N_ROTATE]
-        cpu_train_or_eval_step(model, opt, s, mode)
-        ev += n_ev
-    dt = time.perf_counter() - t0
-    return ev / dt, dt / max(steps, 1) * 1e3, samples[0][1], torch.get_num_threads()
+        s, _ = samples[i % N_ROTATE]
+        t0 = time.perf_counter()
+        _, _, tg = cpu_train_or_eval_step(model, opt, s, mode)
+        times.append(time.perf_counter() - t0)
+        graph_times.append(tg)
+    s0 = samples[0][0]
+    _, _, etaphi = O.prepare_inputs(s0.x)
+    t0 = time.perf_counter()
+    O.radius_graph(etaphi, r=0.4, batch=s0.batch, loop=True, max_num_neighbors=255)
+    brute_ms = (time.perf_counter() - t0) * 1e3
+    med = statistics.median(times)
+    n_s = samples[0][1]
+    return {"value": n_s / med, "ms_per_step": med * 1e3, "events_per_step": n_s, "threads": torch.get_num_threads(),
+            "graph_build_ms": {"ckdtree_per_event (inside the timed step)": statistics.median(graph_times) * 1e3,
+                               "bruteforce_c_one_core (the exactness oracle, timed once beside it)": brute_ms},
+            "timing": f"warm-up {warmup}, median of {steps} steps", "host_cpus": os.cpu_count()}
 
 
-# ------------------------------------------------------------------------------------------------ main
+# ------------------------------------------------------------------------------------------------ k-NN side line
+def smem_peak_gbps(l):
+    """Measured shared-memory read bandwidth of the whole chip (LDS.128 stream, gm_bench_smem_read), GB/s."""
+    ms = ctypes.c_float()
+    gb = ctypes.c_double()
+    if l.gm_bench_smem_read(200, ctypes.byref(ms), ctypes.byref(gb)) != 0 or ms.value <= 0:
+        return None
+    return gb.value / (ms.value * 1e-3)
+
+
+def fp32_peak_tflops(l):
+    """Measured FFMA stream peak of the whole chip (gm_bench_ffma), TFLOP/s."""
+    ms = ctypes.c_float()
+    gf = ctypes.c_double()
+    if l.gm_bench_ffma(200, ctypes.byref(ms), ctypes.byref(gf)) != 0 or ms.value <= 0:
+        return None
+    return gf.value / (ms.value * 1e-3) / 1e3
+
+
 def run_knn(args):
     """Side line (row f4 / f1, not the headline metric): the k-NN graph of a c2-shaped batch in the 32-d embedding,
     k = 20, loop = True (model/graph_met_network.py:63), with the oracle's C brute force timed beside it."""
-    import numpy as np
-    import torch
     from deepmetv2_b200 import ops, synth
     from deepmetv2_b200._lib import lib, ptr, stream, check
     dev = torch.device("cuda", 0)
@@ -199,16 +277,19 @@ def run_knn(args):
     t0 = time.perf_counter()
     O.knn_graph(hx[:n2], k, b.batch[:n2], loop=True)
     cpu_s = time.perf_counter() - t0
+    ffma = fp32_peak_tflops(l)                        # measured FFMA stream (2 flop / instruction)
+    # the search issues FSUB + FFMA per pair and dimension: 3 flop per 2 fp32-pipe instructions
+    peak = ffma * 0.75 if ffma else None
     print(json.dumps({
         "metric": "k-NN graph events/sec", "value": B / ms * 1e3, "unit": "events/s", "n_gpus": 1, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "knn_graph(emb[N,32], k=20, loop=True) on 32 DY/TT-shaped events", "nodes": N,
-                   "l2": "flushed between timed iterations (256 MiB memset)"},
+        "config": {"workload": "knn_graph(emb[N,32], k=20, loop=True) on 32 DY/TT-shaped events", "nodes": N, "l2": L2_NOTE},
         "gpu_launches": int(launches),
         "roofline": {"kernel": "k_knn_search", "bound": "fp32 pipe (FSUB + FFMA per pair*dim)", "achieved": flops / ms / 1e9,
-                     "peak": 148 * 128 * 1.965 * 1.5 / 1e3, "unit": "TFLOP/s", "frac": flops / ms / 1e9 / (148 * 128 * 1.965 * 1.5 / 1e3),
-                     "traffic": 7189504, "note": "peak = 148 SMs x 128 lanes x 1.965 GHz x 3 flop per 2 instructions"},
+                     "peak": peak, "unit": "TFLOP/s", "frac": (flops / ms / 1e9 / peak) if peak else None,
+                     "traffic": None,
+                     "note": "peak = 3/4 of the FFMA stream measured live by gm_bench_ffma (3 flop per 2 instructions)"},
         "cpu_baseline": {"value": 2 / cpu_s, "unit": "events/s", "cores": 1, "kind": "port",
                          "sample": "2 of the 32 events through oracle/knn_bruteforce.c"},
         "e2e": {"value": B / e2e_s, "unit": "events/s", "h2d_bytes_per_step": N * dim * 4,
@@ -216,196 +297,105 @@ def run_knn(args):
     }))
 
 
-def main():
-    if os.environ.get("GM_BENCH_WATCHDOG"):       # debugging aid: dump every thread's stack and exit if the run stalls
-        import faulthandler
-        faulthandler.dump_traceback_later(int(os.environ["GM_BENCH_WATCHDOG"]), exit=True)
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
-    ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["knn"])
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "bf16", "tf32x3"])
-    ap.add_argument("--graph", default="implicit", choices=["implicit", "csr"],
-                    help="implicit: cell-staged EdgeConv, no edge list (default; fp32 only). csr: explicit edge list")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    if args.workload == "knn":                       # side line, single GPU; the headline workloads follow below
-        if int(os.environ.get("RANK", "0")) == 0:
-            run_knn(args)
-        return
+# ------------------------------------------------------------------------------------------------ GPU arm
+class Arm:
+    """One workload on this rank: model, fused trainer, device-resident and pinned host batches."""
 
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    n_ev, shape, mode, human = WORKLOADS[args.workload]
-    metric = "training events/sec" if mode == "train" else "inference events/sec"
+    def __init__(self, workload, precision, graph, rank, world, dev, pg, n_rotate=N_ROTATE):
+        from deepmetv2_b200.model import net as gnet
+        from deepmetv2_b200.trainer import GraphMETTrainer
+        self.workload, self.precision, self.rank, self.world, self.dev = workload, precision, rank, world, dev
+        self.n_ev, _, self.mode, self.human = WORKLOADS[workload]
+        self.n_rotate = n_rotate
+        torch.manual_seed(0)
+        model = gnet.Net(8, 3).to(dev)
+        model.graphnet.edge_precision = precision
+        self.trainer = GraphMETTrainer(model, lr=1e-3, process_group=pg, graph=graph)
+        self.graph_mode = "implicit" if self.trainer._implicit(training=(self.mode == "train")) else "csr"
+        self.host = [b.pin_memory() for b in make_batches(workload, rank, n_rotate)]
+        self.devb = [b.to(dev) for b in self.host]
+        self.men = [int((b.ptr[1:] - b.ptr[:-1]).max()) for b in self.host]
+        for b, m in zip(self.host, self.men):
+            b.max_event_nodes = m
 
-    if args.impl == "reference":
-        # The reference's genuine PyG/torch_cluster implementation is unavailable on this box (packages
-        # absent); this arm times the oracle restatement of its CPU path on the host cores (kind "port").
-        if rank != 0:
-            return
-        value, ms, n_s, threads = run_cpu_arm(args.workload, args.steps, args.warmup)
-        sample = f"{n_s} of {n_ev} events of the {args.workload} batch per step"
-        print(json.dumps({
-            "impl": "reference", "metric": metric, "value": value, "unit": "events/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": human, "events_per_step": n_s},
-            "cpu_baseline": {"value": value, "unit": "events/s", "cores": threads, "kind": "port", "sample": sample},
-            "e2e": {"value": value, "unit": "events/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        }))
-        return
+    def step(self, i):
+        k = i % self.n_rotate
+        if self.mode == "train":
+            return self.trainer.train_step(self.devb[k], self.men[k])
+        return self.trainer.eval_step(self.devb[k], self.men[k])[1]
 
-    from deepmetv2_b200 import _lib
-    from deepmetv2_b200.model import net as gnet
-    from deepmetv2_b200.trainer import GraphMETTrainer
-
-    assert torch.cuda.is_available(), "bench.py --impl ours needs a CUDA device (no CPU fallback)"
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    pg = None
-    if world > 1:
-        torch.distributed.init_process_group("nccl", device_id=dev)
-        pg = torch.distributed.group.WORLD
-
-    def barrier():
-        if world > 1:
-            torch.distributed.barrier()
-        torch.cuda.synchronize()
-
-    l = _lib.lib()
-    torch.manual_seed(0)
-    model = gnet.Net(8, 3).to(dev)
-    model.graphnet.edge_precision = args.precision
-    trainer = GraphMETTrainer(model, lr=1e-3, process_group=pg, graph=args.graph)
-    graph_mode = "implicit" if trainer._implicit(training=(mode == "train")) else "csr"
-    host = [b.pin_memory() for b in make_batches(args.workload, rank)]
-    devb = [b.to(dev) for b in host]
-    men = [int((b.ptr[1:] - b.ptr[:-1]).max()) for b in host]
-    for b, m in zip(host, men):
-        b.max_event_nodes = m
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
-
-    def one_step(i):
-        k = i % N_ROTATE
-        if mode == "train":
-            return trainer.train_step(devb[k], men[k])
-        return trainer.eval_step(devb[k], men[k])[1]
-
-    def one_step_e2e(i):
-        k = i % N_ROTATE
-        if mode == "train":
-            return trainer.train_step_from_host(host[k], men[k])
-        x = host[k].x.to(dev, non_blocking=True); y = host[k].y.to(dev, non_blocking=True)
-        p = host[k].ptr.to(dev, non_blocking=True)
+    def step_e2e(self, i):
         from deepmetv2_b200.synth import EventBatch
-        _, loss, _ = trainer.eval_step(EventBatch(x, y, None, p), men[k])
+        k, dev = i % self.n_rotate, self.dev
+        if self.mode == "train":
+            return self.trainer.train_step_from_host(self.host[k], self.men[k])
+        x = self.host[k].x.to(dev, non_blocking=True); y = self.host[k].y.to(dev, non_blocking=True)
+        p = self.host[k].ptr.to(dev, non_blocking=True)
+        _, loss, _ = self.trainer.eval_step(EventBatch(x, y, None, p), self.men[k])
         return float(loss.item())
 
-    # ---------------- device-resident arm (value) ----------------
-    # nvidia-smi needs ~a second to come up and a step is ~1 ms: the sampler runs from before the warm-up to the end
-    # of the end-to-end arm, i.e. over the whole period the GPU is loaded by this benchmark (timed region included)
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-    for i in range(args.warmup):
-        one_step(i)
+    def graph_stats(self):
+        """(E, N) averages, max degree, #capped of the rotating batches from the explicit radius graph -- outside every
+        timed region; the implicit path never counts its edges."""
+        from deepmetv2_b200 import ops
+        Es, Ns, max_deg, capped = [], [], 0, 0
+        for k in range(self.n_rotate):
+            _, _, etaphi = ops.prepare_inputs(self.devb[k].x)
+            g = ops.build_graph(etaphi, 0.4, ptr_i32=self.devb[k].ptr, loop=True, max_num_neighbors=255)
+            Es.append(g.num_edges); Ns.append(self.devb[k].x.shape[0])
+            max_deg, capped = max(max_deg, g.max_degree), capped + g.num_capped
+            del g
+        torch.cuda.empty_cache()
+        return sum(Es) / len(Es), sum(Ns) / len(Ns), max_deg, capped
+
+
+def _max_over_ranks(v: float, dev, world: int) -> float:
+    t = torch.tensor([v], dtype=torch.float64, device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    return float(t.item())
+
+
+def measure_device(arm, l, steps, warmup, flush, barrier):
+    """W untimed warm-up steps, then K steps timed with CUDA events on the launching stream (L2 flushed before each,
+    outside the event pair), bracketed by barrier + synchronize; the total is the MAX over ranks."""
+    from deepmetv2_b200 import _lib
+    for i in range(warmup):
+        arm.step(i)
     barrier()
     l.gm_timing_enable(1)
-    for s in range(8):                   # clear the timer slots
+    for s in range(len(_lib.TIMERS)):        # clear the timer slots
         t_ms, t_n = ctypes.c_float(), ctypes.c_int()
         l.gm_timing_read(s, ctypes.byref(t_ms), ctypes.byref(t_n))
     l.gm_launch_count(1)
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     barrier()
     wall0 = time.perf_counter()
-    for i in range(args.steps):
-        flush.zero_()                    # L2 flush between timed iterations (outside the event pair)
+    for i in range(steps):
+        flush.zero_()
         ev[i][0].record()
-        one_step(i)
+        arm.step(i)
         ev[i][1].record()
     barrier()
     wall = time.perf_counter() - wall0
     launches = l.gm_launch_count(0)
     l.gm_timing_enable(0)
-    total_ms = sum(a.elapsed_time(b) for a, b in ev)
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-    total_ms = float(t.item())
-    value = n_ev * world * args.steps / (total_ms / 1e3)
-
+    total_ms = _max_over_ranks(sum(a.elapsed_time(b) for a, b in ev), arm.dev, arm.world)
     timers = {}
     for name, slot in _lib.TIMERS.items():
         t_ms, t_n = ctypes.c_float(), ctypes.c_int()
         l.gm_timing_read(slot, ctypes.byref(t_ms), ctypes.byref(t_n))
         if t_n.value:
             timers[name] = (t_ms.value, t_n.value)
+    return total_ms, timers, int(launches), wall
 
-    # graph statistics of the rotating batches (for the algorithmic flops / bytes), from the explicit radius graph
-    # — outside every timed region; the implicit path never counts its edges
-    from deepmetv2_b200 import ops
-    Es, Ns, max_deg, capped = [], [], 0, 0
-    for k in range(N_ROTATE):
-        _, _, etaphi = ops.prepare_inputs(devb[k].x)
-        g = ops.build_graph(etaphi, 0.4, ptr_i32=devb[k].ptr, loop=True, max_num_neighbors=255)
-        Es.append(g.num_edges); Ns.append(devb[k].x.shape[0])
-        max_deg, capped = max(max_deg, g.max_degree), capped + g.num_capped
-        del g
-    E_avg, N_avg = sum(Es) / len(Es), sum(Ns) / len(Ns)
-    torch.cuda.empty_cache()
 
-    # ---------------- end-to-end arm (host buffers, H2D + D2H inside the timed region) ----------------
-    for i in range(3):
-        one_step_e2e(i)
-    barrier()
-    e2e_t = 0.0
-    for i in range(args.steps):
-        flush.zero_()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        one_step_e2e(i)                  # ends with the loss on the host (stream sync inside)
-        e2e_t += time.perf_counter() - t0
-    t = torch.tensor([e2e_t], dtype=torch.float64, device=dev)
-    if world > 1:
-        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-    e2e_value = n_ev * world * args.steps / float(t.item())
-    # the same steps through the double-buffered feeder (row f3): H2D of batch k+1 overlaps the step on batch k; the
-    # loss of every step is still read back; no L2 flush inside this loop (inputs arrive from pinned host memory)
-    epoch = trainer.train_epoch_from_host if mode == "train" else trainer.eval_epoch_from_host
-    epoch([host[i % N_ROTATE] for i in range(3)])
-    barrier()
-    t0 = time.perf_counter()
-    epoch([host[i % N_ROTATE] for i in range(args.steps)])
-    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-    if world > 1:
-        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-    e2e_piped = n_ev * world * args.steps / float(t.item())
-    h2d = int(sum(b.x.numel() * 4 + b.y.numel() * 4 + b.ptr.numel() * 4 for b in host) / len(host))
-
-    if rank == 0 and len(sampler.lines) < 3:          # very short runs: keep the GPU busy until a few samples exist
-        t_end = time.perf_counter() + 3.0
-        i = 0
-        while len(sampler.lines) < 3 and time.perf_counter() < t_end:
-            one_step(i); i += 1
-            torch.cuda.synchronize()
-    clocks = sampler.stop() if rank == 0 else None
-    if rank != 0:
-        if world > 1:
-            torch.distributed.destroy_process_group()
-        return
-
-    peaks = _peaks()
-    training = mode == "train"
-    implicit = graph_mode == "implicit"
-    # ALGORITHMIC HBM bytes per launch of each kernel family (every tensor touched once).
-    #   csr graph: etaphi in, rowptr + col out (count + fill are two launches: half each)
-    #   implicit : etaphi in, points (16 B) + perm + thr out
+def kernel_table(arm, timers, total_ms, E_avg, N_avg, peaks):
+    """ALGORITHMIC HBM bytes per launch of each kernel family (every tensor touched once)."""
+    training, implicit = arm.mode == "train", arm.graph_mode == "implicit"
     alg_bytes = {
+        # csr graph: etaphi in, rowptr + col out (count + fill are two launches: half each);
+        # implicit: etaphi in, points (16 B) + perm + thr out
         "radius_graph": 32 * N_avg if implicit else (12 * N_avg + 4 * E_avg) / 2,
         "encode_fwd": 172 * N_avg,
         "node_prep": 640 * N_avg,                       # raw + resid in, emb + Y + P out
@@ -424,62 +414,227 @@ def main():
             d["hbm_GBps"] = alg_bytes[name] / (ms / n * 1e-3) / 1e9
             d["hbm_frac"] = d["hbm_GBps"] / peaks["hbm_gbs"]
         kernels[name] = d
+    return kernels, alg_bytes
 
-    # ncu DRAM traffic per launch (dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of
-    # this workload), committed under profiles/ and looked up here; null when no capture exists for the kernel
+
+def roofline_of(arm, timers, total_ms, alg_bytes, E_avg, peaks, smem_peak):
+    training, implicit = arm.mode == "train", arm.graph_mode == "implicit"
     traffic_db = {}
     tpath = os.path.join(REPO, "profiles", "ncu_traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath):     # dram__bytes_read.sum + dram__bytes_write.sum per launch of one `ncu --set full` capture
         with open(tpath) as f:
             traffic_db = json.load(f)
-
-    roofline = None
-    if args.precision in ("tf32", "bf16") and "edgeconv_fwd" in timers:
-        # the per-edge contraction on tcgen05: 4096 flop per edge per layer
+    if arm.precision in ("tf32", "bf16") and "edgeconv_fwd" in timers:
+        # the per-edge contraction on tcgen05: 4096 flop per edge per layer by the survey's contract;
+        # what the tensor core usefully does is W2 (x_j - x_i) = 2048 flop per edge (the x_i half is per node)
         ec_ms, ec_n = timers["edgeconv_fwd"]
         dur = ec_ms / ec_n * 1e-3
         achieved = 4096.0 * E_avg / dur / 1e12
         peak = peaks["bf16_tflops_sustained"]
-        roofline = {"kernel": ("k_geo_edgeconv_tc (" if implicit else "k_edgeconv_tc (") + args.precision + ")", "bound": "tensor", "achieved": achieved,
-                    "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                    "traffic": traffic_db.get(args.workload, {}).get(
-                        ("k_geo_edgeconv_tc (" if implicit else "k_edgeconv_tc (") + args.precision + ")"),
-                    "avg_launch_us": dur * 1e6, "launches_timed": ec_n,
-                    "algorithmic_flops_per_launch": 4096.0 * E_avg, "peak_source": peaks["source"],
-                    "share_of_step": ec_ms / total_ms}
-    elif timers:
-        # fp32 path: every kernel is HBM-bound by contract; report the family with the largest share of the step
-        dom = max((k for k in timers if k in alg_bytes), key=lambda k: timers[k][0])
-        ms, n = timers[dom]
-        dur = ms / n * 1e-3
-        achieved = alg_bytes[dom] / dur / 1e9
-        kname = {"edgeconv_fwd": "k_geo_aggr" if implicit else "k_edge_aggr",
-                 "scatter_s_bwd": "k_geo_scatter" if implicit else "k_scatter_s"}.get(dom, dom)
-        roofline = {"kernel": kname, "family": dom, "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
-                    "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                    "traffic": traffic_db.get(args.workload, {}).get(kname),
-                    "avg_launch_us": dur * 1e6, "launches_timed": n, "algorithmic_bytes_per_launch": alg_bytes[dom],
-                    "peak_source": peaks["source"] + " (burst copy figure: the kernel is timed alone by its own event pair)",
-                    "share_of_step": ms / total_ms}
-        if dom == "edgeconv_fwd":   # what physically feeds the kernel: neighbour rows out of L2 / shared memory
-            roofline["edge_rows_GBps"] = E_avg * 128.0 / dur / 1e9
+        kname = ("k_geo_edgeconv_tc (" if implicit else "k_edgeconv_tc (") + arm.precision + ")"
+        return {"kernel": kname, "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "frac": achieved / peak, "traffic": traffic_db.get(arm.workload, {}).get(kname),
+                "useful_mma_TFLOPs": 2048.0 * E_avg / dur / 1e12, "useful_mma_frac": 2048.0 * E_avg / dur / 1e12 / peak,
+                "avg_launch_us": dur * 1e6, "launches_timed": ec_n, "algorithmic_flops_per_launch": 4096.0 * E_avg,
+                "peak_source": peaks["source"] + " (sustained bf16 figure: the kernel is timed inside a long step)",
+                "share_of_step": ec_ms / total_ms}
+    if not timers:
+        return None
+    # fp32 path: every kernel is HBM-bound by contract; report the family with the largest share of the step
+    dom = max((k for k in timers if k in alg_bytes), key=lambda k: timers[k][0])
+    ms, n = timers[dom]
+    dur = ms / n * 1e-3
+    achieved = alg_bytes[dom] / dur / 1e9
+    kname = {"edgeconv_fwd": "k_geo_aggr" if implicit else "k_edge_aggr",
+             "scatter_s_bwd": "k_geo_scatter" if implicit else "k_scatter_s"}.get(dom, dom)
+    r = {"kernel": kname, "family": dom, "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
+         "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": traffic_db.get(arm.workload, {}).get(kname),
+         "avg_launch_us": dur * 1e6, "launches_timed": n, "algorithmic_bytes_per_launch": alg_bytes[dom],
+         "peak_source": peaks["source"] + " (burst copy figure: the kernel is timed alone by its own event pair)",
+         "share_of_step": ms / total_ms}
+    if dom == "edgeconv_fwd":   # what physically feeds the kernel: neighbour rows read out of shared memory
+        r["edge_rows_GBps"] = E_avg * 128.0 / dur / 1e9
+        if smem_peak:
+            r["smem_peak_GBps"] = smem_peak
+            r["smem_feed_frac"] = r["edge_rows_GBps"] / smem_peak
+            r["smem_peak_source"] = "measured live (gm_bench_smem_read: LDS.128 stream on every SM)"
+    return r
+
+
+def run_side(workload, precision, rank, world, dev, pg, l, steps, flush, barrier, peaks, smem_peak):
+    """One more BASELINE configuration in the same process, same timing rules (warm-up 3, L2 flush, CUDA events, max
+    over ranks); device-resident arm only."""
+    arm = Arm(workload, precision, "implicit", rank, world, dev, pg, n_rotate=2)
+    total_ms, timers, launches, _ = measure_device(arm, l, steps, 3, flush, barrier)
+    E_avg, N_avg, max_deg, capped = arm.graph_stats()
+    kernels, alg_bytes = kernel_table(arm, timers, total_ms, E_avg, N_avg, peaks)
+    out = {"metric": "training events/sec" if arm.mode == "train" else "inference events/sec",
+           "value": arm.n_ev * world * steps / (total_ms / 1e3), "unit": "events/s", "steps": steps, "warmup": 3,
+           "ms_per_step": total_ms / steps, "dtype": "f32" if precision == "fp32" else precision,
+           "config": config_dict(workload, precision, arm.graph_mode, world) | {"rotating_batches": 2},
+           "workload_stats": {"nodes_per_step": N_avg, "edges_per_step": E_avg, "max_degree": max_deg, "capped_nodes": capped},
+           "edges_per_sec": E_avg * world * steps / (total_ms / 1e3), "gpu_launches_per_step": launches / steps,
+           "roofline": roofline_of(arm, timers, total_ms, alg_bytes, E_avg, peaks, smem_peak),
+           "kernels": {k: {"avg_us": round(v["avg_us"], 2), "share_of_step": round(v["share_of_step"], 4),
+                           **({"hbm_frac": round(v["hbm_frac"], 4)} if "hbm_frac" in v else {})} for k, v in kernels.items()}}
+    arm.trainer.close()
+    del arm
+    torch.cuda.empty_cache()
+    return out
+
+
+def main():
+    if os.environ.get("GM_BENCH_WATCHDOG"):       # debugging aid: dump every thread's stack and exit if the run stalls
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["GM_BENCH_WATCHDOG"]), exit=True)
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["knn"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "bf16"])
+    ap.add_argument("--graph", default="implicit", choices=["implicit", "csr"],
+                    help="implicit: cell-staged EdgeConv, no edge list (default). csr: explicit edge list")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-side", action="store_true", help="skip the side lines (c5; c3 fp32 / bf16 at N = 1)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.workload == "knn":                       # side line, single GPU; the headline workloads follow below
+        if int(os.environ.get("RANK", "0")) == 0:
+            run_knn(args)
+        return
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    n_ev, shape, mode, human = WORKLOADS[args.workload]
+    metric = "training events/sec" if mode == "train" else "inference events/sec"
+
+    if args.impl == "reference":
+        # The reference's genuine PyG/torch_cluster implementation is unavailable on this box (packages
+        # absent); this arm times the oracle restatement of its CPU path on the host cores (kind "port").
+        if rank != 0:
+            return
+        cpu = run_cpu_arm(args.workload, args.steps, args.warmup)
+        sample = (f"{cpu['events_per_step']} of {n_ev} events of the {args.workload} batch per step; {cpu['timing']}; "
+                  "plain-PyTorch restatement of the PyG CPU path with a KD-tree radius graph (genuine PyG / torch_cluster "
+                  "unavailable on this box)")
+        print(json.dumps({
+            "impl": "reference", "metric": metric, "value": cpu["value"], "unit": "events/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cpu["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(args.workload, args.precision, args.graph, args.gpus),
+            "cpu_baseline": {"value": cpu["value"], "unit": "events/s", "cores": cpu["threads"], "kind": "port",
+                             "sample": sample, "graph_build_ms": cpu["graph_build_ms"], "host_cpus": cpu["host_cpus"]},
+            "e2e": {"value": cpu["value"], "unit": "events/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }))
+        return
+
+    from deepmetv2_b200 import _lib
+
+    assert torch.cuda.is_available(), "bench.py --impl ours needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    pg = None
+    if world > 1:
+        torch.distributed.init_process_group("nccl", device_id=dev)
+        pg = torch.distributed.group.WORLD
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    l = _lib.lib()
+    arm = Arm(args.workload, args.precision, args.graph, rank, world, dev, pg)
+    trainer = arm.trainer
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    # ---------------- device-resident arm (value) ----------------
+    # nvidia-smi needs ~a second to come up and a step is ~1 ms: the sampler runs from before the warm-up to the end
+    # of the end-to-end arm, i.e. over the whole period the GPU is loaded by this benchmark (timed region included)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    total_ms, timers, launches, wall = measure_device(arm, l, args.steps, args.warmup, flush, barrier)
+    value = n_ev * world * args.steps / (total_ms / 1e3)
+    E_avg, N_avg, max_deg, capped = arm.graph_stats()
+
+    # ---------------- end-to-end arm (host buffers, H2D + D2H inside the timed region) ----------------
+    for i in range(3):
+        arm.step_e2e(i)
+    barrier()
+    e2e_t = 0.0
+    for i in range(args.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        arm.step_e2e(i)                  # ends with the loss on the host (stream sync inside)
+        e2e_t += time.perf_counter() - t0
+    e2e_value = n_ev * world * args.steps / _max_over_ranks(e2e_t, dev, world)
+    # the same steps through the double-buffered feeder (row f3): H2D of batch k+1 overlaps the step on batch k; the
+    # loss of every step is still read back; no L2 flush inside this loop (inputs arrive from pinned host memory)
+    epoch = trainer.train_epoch_from_host if mode == "train" else trainer.eval_epoch_from_host
+    epoch([arm.host[i % N_ROTATE] for i in range(3)])
+    barrier()
+    t0 = time.perf_counter()
+    epoch([arm.host[i % N_ROTATE] for i in range(args.steps)])
+    e2e_piped = n_ev * world * args.steps / _max_over_ranks(time.perf_counter() - t0, dev, world)
+    h2d = int(sum(b.x.numel() * 4 + b.y.numel() * 4 + b.ptr.numel() * 4 for b in arm.host) / len(arm.host))
+    barrier()
+
+    peaks = _peaks()
+    smem_peak = smem_peak_gbps(l) if rank == 0 else None
+
+    # ---------------- side lines: the other BASELINE configurations, same run, same timing rules ----------------
+    side = {}
+    if args.workload == "c2" and not args.no_side:
+        ks = max(3, min(args.steps, 10))
+        side["c5"] = run_side("c5", "fp32", rank, world, dev, pg, l, ks, flush, barrier, peaks, smem_peak)
+        if world == 1:
+            ks3 = max(3, min(args.steps, 6))
+            side["c3_fp32"] = run_side("c3", "fp32", rank, world, dev, pg, l, ks3, flush, barrier, peaks, smem_peak)
+            side["c3_bf16"] = run_side("c3", "bf16", rank, world, dev, pg, l, ks3, flush, barrier, peaks, smem_peak)
+
+    # very short runs: keep THIS GPU busy until a few nvidia-smi samples exist.  Rank 0 only, so nothing here may
+    # involve a collective: inference steps (r01's version ran training steps, whose gradient all-reduce no other rank
+    # matched -- the N=2 driver run hung in NCCL for 600 s; see DESIGN.md section 5)
+    if rank == 0 and len(sampler.lines) < 3:
+        t_end = time.perf_counter() + 3.0
+        i = 0
+        while len(sampler.lines) < 3 and time.perf_counter() < t_end:
+            trainer.eval_step(arm.devb[i % N_ROTATE], arm.men[i % N_ROTATE]); i += 1
+            torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
+    barrier()                                          # every rank leaves the GPU phase together
+    trainer_fused = trainer.comm is not None
+    trainer.close()
+    if world > 1:
+        torch.distributed.destroy_process_group()
+    if rank != 0:
+        return
+
+    kernels, alg_bytes = kernel_table(arm, timers, total_ms, E_avg, N_avg, peaks)
+    roofline = roofline_of(arm, timers, total_ms, alg_bytes, E_avg, peaks, smem_peak)
 
     cpu = None
     if not args.no_cpu_baseline:
-        v, ms, n_s, threads = run_cpu_arm(args.workload, 2, 1)
-        cpu = {"value": v, "unit": "events/s", "cores": threads, "kind": "port",
-               "sample": f"2 steps of {n_s} of the {n_ev} events of the {args.workload} batch "
-                         f"(oracle restatement of the PyG CPU path; genuine PyG unavailable on this box)",
-               "ms_per_step": ms}
+        c = run_cpu_arm(args.workload, 10, 3)
+        cpu = {"value": c["value"], "unit": "events/s", "cores": c["threads"], "kind": "port",
+               "sample": f"{c['events_per_step']} of the {n_ev} events of the {args.workload} batch per step; {c['timing']} "
+                         f"(oracle restatement of the PyG CPU path, KD-tree radius graph; genuine PyG unavailable on this box)",
+               "ms_per_step": c["ms_per_step"], "graph_build_ms": c["graph_build_ms"], "host_cpus": c["host_cpus"]}
 
     out = {
         "metric": metric, "value": value, "unit": "events/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else args.precision, "data": "synthetic",
-        "config": {"workload": human, "events_per_gpu": n_ev, "nodes_per_step": N_avg, "edges_per_step": E_avg,
-                   "max_degree": max_deg, "capped_nodes": capped, "edge_precision": args.precision, "graph": graph_mode,
-                   "l2": "flushed between timed iterations (256 MiB memset)", "rotating_batches": N_ROTATE,
-                   "parallelism": f"dp{world}" if world > 1 else "single"},
+        "config": config_dict(args.workload, args.precision, args.graph, world),
+        "workload_stats": {"nodes_per_step": N_avg, "edges_per_step": E_avg, "max_degree": max_deg, "capped_nodes": capped,
+                           "graph_used": arm.graph_mode,
+                           "gradient_exchange": ("fused peer-memory all-reduce + AdamW (gm_allreduce_adamw_step)"
+                                                 if trainer_fused else "torch.distributed.all_reduce (NCCL)") if world > 1 else None},
         "edges_per_sec": E_avg * world * args.steps / (total_ms / 1e3),
         "wall_ms_per_step_incl_flush": wall / args.steps * 1e3,
         "gpu_launches": int(launches), "gpu_launches_per_step": launches / args.steps,
@@ -491,10 +646,9 @@ def main():
                 "pipelined_note": "same steps through feeder.HostFeeder (H2D of batch k+1 overlaps step k, the loss of "
                                   "every step read back one step late, no L2 flush inside the loop); reported beside, "
                                   "not instead of, value"},
+        "side": side or None,
     }
     print(json.dumps(out))
-    if world > 1:
-        torch.distributed.destroy_process_group()
 
 
 if __name__ == "__main__":

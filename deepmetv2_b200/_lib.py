@@ -55,6 +55,8 @@ SIGNATURES = {
     "gm_launch_count": (_ll, [_i]),
     "gm_timing_enable": (_i, [_i]),
     "gm_timing_read": (_i, [_i, _vp, _vp]),
+    "gm_bench_smem_read": (_i, [_i, _vp, _vp]),
+    "gm_bench_ffma": (_i, [_i, _vp, _vp]),
     "gm_prepare_etaphi": (_i, [_vp, _i, _i, _vp, _vp]),
     "gm_batch_to_ptr": (_i, [_vp, _i, _i, _vp, _vp]),
     "gm_radius_graph_ws_bytes": (_sz, [_i, _i]),
@@ -88,6 +90,13 @@ SIGNATURES = {
     "gm_index_stats": (_i, [_vp, _ll, _vp, _vp]),
     "gm_resolution": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "gm_adamw_step": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _f, _vp]),
+    "gm_met_loss_ex": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp, _vp]),
+    "gm_adamw_step_ex": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _f, _vp, _vp, _vp, _vp, _vp]),
+    "gm_comm_create": (_i, [_i, _i, _i, C.POINTER(_vp), _vp]),
+    "gm_comm_connect": (_i, [_vp, _vp]),
+    "gm_comm_destroy": (_i, [_vp]),
+    "gm_allreduce_adamw_step": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp,
+                                     _vp]),
 }
 
 _lib = None
@@ -134,8 +143,8 @@ def check(status: int, what: str = "libgraphmet") -> None:
         raise GraphMETLibraryError(f"{what}: {msg}")
 
 
-def stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+def stream(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
 
 
 def ptr(t: torch.Tensor | None) -> int | None:

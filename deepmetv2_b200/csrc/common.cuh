@@ -95,6 +95,23 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_sync() { pdl_wait(); pdl_trigger(); }      // kernels without a prologue worth overlapping
 
+// What the LAST kernel of a training step mirrors into pinned (device-mapped) host memory so the host can see device
+// error flags one step late without a copy or a sync: {step, GM_FLAG_* of the forward, flags of the graph build}.
+struct StepStatus {
+    const int *err_flags;     // device int[1] (gm_net_forward's err_flags) or NULL
+    const int *graph_stats;   // device int[4] (stats of the graph build; [3] = flags) or NULL
+    int *host;                // pinned host int[4] or NULL
+    int step;
+    __device__ __forceinline__ void publish() const {
+        if (!host) return;
+        volatile int *h = host;
+        h[1] = err_flags ? err_flags[0] : 0;
+        h[2] = graph_stats ? graph_stats[3] : 0;
+        __threadfence_system();
+        h[0] = step;
+    }
+};
+
 __device__ __forceinline__ float elu(float v) { return v > 0.f ? v : expm1f(v); }
 // derivative of ELU expressed through its OUTPUT a = elu(z): z>0 -> 1, else a + 1
 __device__ __forceinline__ float elu_grad_from_out(float a) { return a > 0.f ? 1.f : a + 1.f; }

@@ -90,11 +90,12 @@ __global__ void __launch_bounds__(RED_THREADS) k_met(const float *__restrict__ w
     if (threadIdx.x == 0) { met[2 * e] = sx; met[2 * e + 1] = sy; }
 }
 
-// MET + d loss / d w_n = ((METx+tx) px + (METy+ty) py) / B in one launch (training): the CTA of an event has everything d loss / d w needs once its own
+// MET + d loss / d w_n = ((METx+tx) px + (METy+ty) py) * grad_scale (1/B for loss_fn; 1 for the per-event SUM the
+// data-parallel step all-reduces before dividing by the GLOBAL event count) in one launch (training): the CTA of an event has everything d loss / d w needs once its own
 // MET is reduced; the second sweep over the event's rows hits L1/L2.  Same summation order as k_met.
 __global__ void __launch_bounds__(RED_THREADS) k_met_grad(const float *__restrict__ w, const float *__restrict__ pred,
                                                           int pstride, const int *__restrict__ ptr,
-                                                          const float *__restrict__ truth, int tstride, int B,
+                                                          const float *__restrict__ truth, int tstride, float grad_scale,
                                                           float *__restrict__ met, float *__restrict__ gw) {
     pdl_sync();
     __shared__ float sm[RED_THREADS / 32];
@@ -112,9 +113,8 @@ __global__ void __launch_bounds__(RED_THREADS) k_met_grad(const float *__restric
     sy = block_sum(sy, sm);
     if (threadIdx.x == 0) {
         met[2 * e] = sx; met[2 * e + 1] = sy;
-        const float inv_b = 1.0f / (float)B;
-        s_g[0] = (sx + truth[(size_t)e * tstride]) * inv_b;
-        s_g[1] = (sy + truth[(size_t)e * tstride + 1]) * inv_b;
+        s_g[0] = (sx + truth[(size_t)e * tstride]) * grad_scale;
+        s_g[1] = (sy + truth[(size_t)e * tstride + 1]) * grad_scale;
     }
     __syncthreads();
     const float gx = s_g[0], gy = s_g[1];
@@ -177,8 +177,10 @@ __global__ void __launch_bounds__(256) k_resolution(const float *__restrict__ me
 __global__ void __launch_bounds__(256) k_adamw(float *__restrict__ p, const float *__restrict__ g,
                                                float *__restrict__ m, float *__restrict__ v, int n, float lr,
                                                float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt,
-                                               float gscale) {
+                                               float gscale, const float *__restrict__ denom, StepStatus status) {
     pdl_wait();                                          // no early trigger: whatever follows may read weights up front
+    if (denom) gscale /= fmaxf(denom[0], 1.f);
+    if (blockIdx.x == 0 && threadIdx.x == 0) status.publish();
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float gi = g[i] * gscale;
         float pi = p[i] * (1.f - lr * wd);
@@ -328,12 +330,19 @@ const char *gm_status_string(int status) {
 
 int gm_met_loss(const float *w, const float *pred, int pred_stride, const float *truth, int truth_stride,
                 const int *ptr, int N, int B, float *met_out, float *loss_out, float *grad_w_out, void *stream) {
+    return gm_met_loss_ex(w, pred, pred_stride, truth, truth_stride, ptr, N, B, B > 0 ? 1.0f / (float)B : 0.f, met_out,
+                          loss_out, grad_w_out, stream);
+}
+
+int gm_met_loss_ex(const float *w, const float *pred, int pred_stride, const float *truth, int truth_stride,
+                   const int *ptr, int N, int B, float grad_scale, float *met_out, float *loss_out, float *grad_w_out,
+                   void *stream) {
     if (B <= 0 || N < 0 || !ptr || !truth || !met_out || !loss_out || (N > 0 && (!w || !pred)))
         return GM_ERR_INVALID_ARGUMENT;
     if (pred_stride < 2 || truth_stride < 2) return GM_ERR_INVALID_ARGUMENT;
     cudaStream_t st = as_stream(stream);
     if (grad_w_out && N > 0)
-        GM_LAUNCH_PDL(k_met_grad, B, RED_THREADS, 0, st, w, pred, pred_stride, ptr, truth, truth_stride, B, met_out, grad_w_out);
+        GM_LAUNCH_PDL(k_met_grad, B, RED_THREADS, 0, st, w, pred, pred_stride, ptr, truth, truth_stride, grad_scale, met_out, grad_w_out);
     else
         GM_LAUNCH_PDL(k_met, B, RED_THREADS, 0, st, w, pred, pred_stride, ptr, met_out);
     GM_LAUNCH_CHECK();
@@ -364,12 +373,21 @@ int gm_resolution(const float *met, const float *truth, int truth_stride, int tr
 
 int gm_adamw_step(float *params, const float *grads, float *exp_avg, float *exp_avg_sq, int n, float lr, float beta1,
                   float beta2, float eps, float weight_decay, int step, float grad_scale, void *stream) {
+    return gm_adamw_step_ex(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, grad_scale,
+                            nullptr, nullptr, nullptr, nullptr, stream);
+}
+
+int gm_adamw_step_ex(float *params, const float *grads, float *exp_avg, float *exp_avg_sq, int n, float lr, float beta1,
+                     float beta2, float eps, float weight_decay, int step, float grad_scale,
+                     const float *grad_denominator_dev, const int *err_flags_dev, const int *graph_stats_dev,
+                     int *status_host, void *stream) {
     if (n < 0 || step < 1 || (n > 0 && (!params || !grads || !exp_avg || !exp_avg_sq))) return GM_ERR_INVALID_ARGUMENT;
     if (n == 0) return GM_OK;
     const double bc1 = 1.0 - pow((double)beta1, (double)step);
     const double bc2 = 1.0 - pow((double)beta2, (double)step);
     GM_LAUNCH_PDL(k_adamw, persistent_grid((n + 255) / 256, 8), 256, 0, as_stream(stream), params, grads, exp_avg, exp_avg_sq, n,
-                  lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale);
+                  lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale, grad_denominator_dev,
+                  StepStatus{err_flags_dev, graph_stats_dev, status_host, step});
     GM_LAUNCH_CHECK();
     return GM_OK;
 }

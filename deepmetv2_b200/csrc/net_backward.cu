@@ -302,6 +302,9 @@ k_head_bwd(const float *__restrict__ emb, const float *__restrict__ out, const f
 // and the two halves are folded as (half 0) + (half 1) => fixed summation order.
 // Matching (target, channel) entries are sparse (32 per source on average): the G / raw loads are PREDICATED,
 // not branched, so all of a batch's loads are issued back to back (one more round trip, not one per match).
+// A user edge_index may list an edge (j -> i) more than once (e.g. the dz variant: torch.cat of two radius lists,
+// evaluate.py:91-96): the scatter-max of the forward routes a (target, channel) gradient to ONE edge, so repeated
+// entries of a (sorted) transposed row are skipped -- a duplicate is marked -1 when the row is loaded.
 __device__ __forceinline__ void scatter_consume(float2 &s, const int2 (&a)[8], const int (&i)[8], int j, int sub,
                                                 const float *s_coef, const float2 *__restrict__ G2,
                                                 const float2 *__restrict__ R2) {
@@ -345,6 +348,7 @@ __global__ void __launch_bounds__(256) k_scatter_s(const float *__restrict__ G, 
     if (j < N) {
         beg = __ldg(rowptr_t + j); end = __ldg(rowptr_t + j + 1);
         il = lane < end - beg ? __ldg(col_t + beg + lane) : -1;
+        if (lane > 0 && lane < end - beg && il == __ldg(col_t + beg + lane - 1)) il = -1;
     }
     while (j < N) {
         const int jn = j + stride;
@@ -353,25 +357,34 @@ __global__ void __launch_bounds__(256) k_scatter_s(const float *__restrict__ G, 
         float2 s = make_float2(0.f, 0.f);
         for (int e0 = beg; e0 < end; e0 += 32) {
             const int nb = min(32, end - e0);
-            if (e0 > beg) il = lane < nb ? __ldg(col_t + e0 + lane) : -1;
+            if (e0 > beg) {
+                il = lane < nb ? __ldg(col_t + e0 + lane) : -1;
+                if (lane < nb && il == __ldg(col_t + e0 + lane - 1)) il = -1;
+            }
             int ia[8], ib[8];
             int2 aa[8], ab[8];
 #pragma unroll
             for (int u = 0; u < 8; ++u) ia[u] = __shfl_sync(0xffffffffu, il, 2 * u + half);
 #pragma unroll
-            for (int u = 0; u < 8; ++u) aa[u] = (2 * u + half < nb) ? __ldg(arg2 + (size_t)ia[u] * (H / 2) + sub) : NONE;
+            for (int u = 0; u < 8; ++u) aa[u] = ia[u] >= 0 ? __ldg(arg2 + (size_t)ia[u] * (H / 2) + sub) : NONE;
             if (nb > 16) {
 #pragma unroll
                 for (int u = 0; u < 8; ++u) ib[u] = __shfl_sync(0xffffffffu, il, 16 + 2 * u + half);
 #pragma unroll
                 for (int u = 0; u < 8; ++u)
-                    ab[u] = (16 + 2 * u + half < nb) ? __ldg(arg2 + (size_t)ib[u] * (H / 2) + sub) : NONE;
+                    ab[u] = ib[u] >= 0 ? __ldg(arg2 + (size_t)ib[u] * (H / 2) + sub) : NONE;
             }
-            if (e0 == beg && jn < N) inext = lane < nend - nbeg ? __ldg(col_t + nbeg + lane) : -1;
+            if (e0 == beg && jn < N) {
+                inext = lane < nend - nbeg ? __ldg(col_t + nbeg + lane) : -1;
+                if (lane > 0 && lane < nend - nbeg && inext == __ldg(col_t + nbeg + lane - 1)) inext = -1;
+            }
             scatter_consume(s, aa, ia, j, sub, s_coef, G2, R2);
             if (nb > 16) scatter_consume(s, ab, ib, j, sub, s_coef, G2, R2);
         }
-        if (end == beg && jn < N) inext = lane < nend - nbeg ? __ldg(col_t + nbeg + lane) : -1;
+        if (end == beg && jn < N) {
+            inext = lane < nend - nbeg ? __ldg(col_t + nbeg + lane) : -1;
+            if (lane > 0 && lane < nend - nbeg && inext == __ldg(col_t + nbeg + lane - 1)) inext = -1;
+        }
         const float ox = __shfl_xor_sync(0xffffffffu, s.x, 16), oy = __shfl_xor_sync(0xffffffffu, s.y, 16);
         if (half == 0) reinterpret_cast<float2 *>(S)[(size_t)j * (H / 2) + sub] = make_float2(s.x + ox, s.y + oy);
         j = jn; beg = nbeg; end = nend; il = inext;

@@ -96,7 +96,7 @@ class _GraphMETFunction(torch.autograd.Function):
         depth = len(net.conv_continuous)
         l = lib()
         params = list(net.parameters())
-        flat = torch.zeros(sum(p.numel() for p in params), dtype=torch.float32, device=dev)
+        flat = torch.empty(sum(p.numel() for p in params), dtype=torch.float32, device=dev)   # every gradient is overwritten
         views, off = [], 0
         for p in params:
             views.append(flat[off:off + p.numel()].view_as(p))
@@ -111,7 +111,7 @@ class _GraphMETFunction(torch.autograd.Function):
         grad_out = grad_out.contiguous().float()
         check(l.gm_net_backward(C.byref(P), C.byref(G), ptr(ctx.x_cont), ctx.x_cont.stride(0), ptr(cat_i64),
                                 ptr(cat_f32), 0 if cat_f32 is None else cat_f32.stride(0), ptr(csr.rowptr),
-                                ptr(csr.col), ptr(rowptr_t), ptr(col_t), None, N, None, int(ctx.training),
+                                ptr(csr.col), ptr(rowptr_t), ptr(col_t), ptr(csr.capped_flag), N, None, int(ctx.training),
                                 int(ctx.apply_sigmoid), AGGR[net.aggr], float(net.bn_all.eps), ptr(ctx.ws),
                                 ctx.ws.numel(), ptr(bws), bws.numel(), ptr(ctx.out), ptr(grad_out), stream()),
               "gm_net_backward")

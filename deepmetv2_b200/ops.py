@@ -30,13 +30,16 @@ class GraphCSR:
     num_capped: int = 0
     rowptr_t: torch.Tensor | None = None
     col_t: torch.Tensor | None = None
+    capped_flag: torch.Tensor | None = None   # device int32[1] (#capped nodes) when the host never read it back
 
     @property
     def symmetric(self) -> bool:
-        return self.num_capped == 0
+        return self.num_capped == 0 and self.capped_flag is None
 
     def transposed(self):
-        """(rowptr_t, col_t): the graph by SOURCE. Equal to (rowptr, col) when no node was capped."""
+        """(rowptr_t, col_t): the graph by SOURCE. Equal to (rowptr, col) when no node was capped.  When the cap
+        count stayed on the device (``capped_flag``: the sync-free ``edge_capacity`` path) the transposed CSR is
+        built by kernels that are no-ops unless the flag is set, and the backward picks the right pair on the device."""
         if self.symmetric:
             return self.rowptr, self.col
         if self.rowptr_t is None:
@@ -46,7 +49,8 @@ class GraphCSR:
             self.rowptr_t = torch.empty(N + 1, dtype=torch.int32, device=self.col.device)
             self.col_t = torch.empty(max(E, 1), dtype=torch.int32, device=self.col.device)
             check(l.gm_csr_transpose(ptr(self.rowptr), ptr(self.col), N, E, ptr(ws), ws.numel(),
-                                     ptr(self.rowptr_t), ptr(self.col_t), None, stream()), "gm_csr_transpose")
+                                     ptr(self.rowptr_t), ptr(self.col_t), ptr(self.capped_flag), stream()),
+                  "gm_csr_transpose")
         return self.rowptr_t, self.col_t
 
 
@@ -127,6 +131,8 @@ def build_graph(pos: torch.Tensor, r: float, ptr_i32: torch.Tensor | None = None
           "gm_radius_graph_fill")
     g = GraphCSR(rowptr, col, N, E, max_deg, capped)
     g._stats = stats
+    if edge_capacity is not None:       # whether the cap bound is only known on the device: stats[2]
+        g.capped_flag = stats[2:3]
     return (g, ei) if want_edge_index else g
 
 

@@ -10,6 +10,14 @@ neighbourhoods staged in shared memory, so no edge list and no transposed graph 
 ``graph="csr"`` is the explicit path (count, scan, fill; E stays on the device; transposed CSR iff capped) and
 the only one that supports the tcgen05 ``edge_precision`` variants in TRAINING; in eval mode tf32 / bf16 run the
 per-edge contraction on the implicit graph too (``csrc/geo_tc.cu``).
+
+Data parallelism (``process_group=``): every rank steps on its own events; the per-event-SUM gradients are all-reduced
+and divided by the GLOBAL event count, so ranks may hold different numbers of events (a rank with none still joins
+with a zero gradient) and the update equals the gradient of the mean loss over all events of the step.  The exchange
+is fused with AdamW in one kernel over NVLink peer memory (``gm_allreduce_adamw_step``, ``csrc/comm.cu``); if CUDA IPC
+is unavailable it falls back to ``torch.distributed.all_reduce`` + ``gm_adamw_step_ex``.  BatchNorm uses rank-local
+batch statistics (DistributedDataParallel's default); the running statistics are rank-local too and
+:meth:`sync_bn_buffers` makes rank 0's authoritative before a checkpoint / evaluation (what DDP's buffer broadcast does).
 Parameters stay the module's ``nn.Parameter``s (re-pointed at one flat fp32 buffer), so
 ``state_dict()`` / checkpoints are unchanged; optimizer state converts to and from the
 ``torch.optim.AdamW`` layout the reference's checkpoints store (``optim_dict``).
@@ -28,7 +36,7 @@ from .synth import EventBatch
 class GraphMETTrainer:
     def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, r=0.4,
                  max_num_neighbors=255, loop=True, phi_wrap=False, process_group=None, device=None,
-                 graph="implicit"):
+                 graph="implicit", fused_allreduce=True):
         self.model = model
         self.net = model.graphnet if hasattr(model, "graphnet") else model
         self.apply_sigmoid = hasattr(model, "graphnet")       # Net applies the sigmoid, GraphMETNetwork does not
@@ -39,6 +47,7 @@ class GraphMETTrainer:
         self.graph = graph
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
+        self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
         self.step_count = 0
         params = list(self.net.parameters())
         dev = device or params[0].device
@@ -47,7 +56,9 @@ class GraphMETTrainer:
         self.device = dev
         n = sum(p.numel() for p in params)
         self.flat = torch.empty(n, dtype=torch.float32, device=dev)
-        self.flat_grad = torch.zeros(n, dtype=torch.float32, device=dev)
+        # [gradient | local events | local events * local loss]: the tail rides along in the all-reduce fallback
+        self._payload = torch.zeros(n + 2, dtype=torch.float32, device=dev)
+        self.flat_grad = self._payload[:n]
         self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
         self._views, self._gviews, off = [], [], 0
@@ -63,8 +74,96 @@ class GraphMETTrainer:
         self._cap_nodes = self._cap_events = self._cap_edges = -1
         self._cap_implicit = None
         self.flags = torch.zeros(1, dtype=torch.int32, device=dev)
-        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.stats = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)          # local mean loss of the last step
+        self.global_loss = torch.zeros((), dtype=torch.float32, device=dev)   # mean over ALL ranks' events (DP)
         self._host_loss = torch.zeros((), dtype=torch.float32).pin_memory()
+        # {step, forward error flags, graph-build flags} mirrored by the step's last kernel into pinned host memory
+        self._status = torch.zeros(4, dtype=torch.int32).pin_memory()
+        self._status_seen = 0
+        self.comm = None
+        if self.world > 1 and fused_allreduce:
+            self._connect_peers(n)
+
+    # ------------------------------------------------------------------------------------------ data parallelism
+    def _connect_peers(self, n: int):
+        """Exchange CUDA IPC handles of the per-rank exchange buffers (csrc/comm.cu).  Every rank must agree: if any
+        rank cannot create or map a buffer, all fall back to torch.distributed.all_reduce."""
+        import torch.distributed as dist
+        l = lib()
+        comm = C.c_void_p()
+        handle = (C.c_ubyte * 64)()
+        with torch.cuda.device(self.device):
+            ok = l.gm_comm_create(n, self.rank, self.world, C.byref(comm), handle) == _lib.GM_OK
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle) if ok else None, group=self.pg)
+            if ok and all(h is not None for h in handles):
+                ok = l.gm_comm_connect(comm, b"".join(handles)) == _lib.GM_OK
+            else:
+                ok = False
+            oks = [None] * self.world
+            dist.all_gather_object(oks, bool(ok), group=self.pg)     # also: nobody steps before everybody has mapped
+        if all(oks):
+            self.comm = comm
+        elif comm:
+            l.gm_comm_destroy(comm)
+
+    def close(self):
+        if self.comm is not None:
+            lib().gm_comm_destroy(self.comm)
+            self.comm = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:      # interpreter shutdown
+            pass
+
+    def sync_bn_buffers(self, src: int = 0):
+        """BatchNorm running statistics are rank-local during DP training; make rank ``src``'s authoritative (call before
+        saving a checkpoint or evaluating -- the buffer broadcast DistributedDataParallel does every forward)."""
+        if self.world == 1:
+            return
+        import torch.distributed as dist
+        for _, buf in self.net.named_buffers():
+            dist.broadcast(buf, src=dist.get_global_rank(self.pg, src), group=self.pg)
+
+    # ------------------------------------------------------------------------------------------ deferred errors
+    def _raise_pending(self):
+        """Device-side error flags of an EARLIER step (mirrored into pinned memory by that step's last kernel): raise
+        one step late, like a CUDA device assert, without a copy or a sync on the hot path."""
+        st = self._status
+        step = int(st[0])
+        if step == self._status_seen:
+            return
+        self._status_seen = step
+        fwd, graph = int(st[1]), int(st[2])
+        if fwd & _lib.FLAG_CAT_OUT_OF_RANGE:
+            self.flags.zero_()
+            raise IndexError("index out of range in self (embed_charge / embed_pdgid / embed_pv)")
+        if graph & _lib.FLAG_EVENT_TOO_LARGE:
+            raise _lib.GraphMETLibraryError("an event has more nodes than max_event_nodes promised: the radius graph "
+                                            f"of step {step} is wrong")
+
+    def check_errors(self):
+        """Synchronising check of the device error flags (use after eval_step, or at the end of an epoch)."""
+        flags = int(self.flags.item())
+        graph = int(self.stats[3].item()) if self._cap_nodes >= 0 else 0
+        if flags & _lib.FLAG_CAT_OUT_OF_RANGE:
+            self.flags.zero_()
+            raise IndexError("index out of range in self (embed_charge / embed_pdgid / embed_pv)")
+        if graph & _lib.FLAG_EVENT_TOO_LARGE:
+            raise _lib.GraphMETLibraryError("an event has more nodes than max_event_nodes promised")
+
+    def _check_batch(self, x, y, p):
+        if x.dtype != torch.float32 or x.dim() != 2 or x.shape[1] < 11 or x.stride(1) != 1:
+            raise ValueError("batch.x must be float32 [N, >=11] with unit column stride")
+        if y.dtype != torch.float32 or y.dim() != 2 or y.shape[1] < 2 or (y.shape[0] and y.stride(1) != 1):
+            raise ValueError("batch.y must be float32 [B, >=2] with unit column stride")
+        if p.dtype != torch.int32 or p.dim() != 1 or p.numel() != y.shape[0] + 1 or not p.is_contiguous():
+            raise ValueError("batch.ptr must be a contiguous int32 [B+1] tensor")
+        if x.device != self.device or y.device != self.device or p.device != self.device:
+            raise ValueError(f"batch tensors must live on {self.device}")
 
     # ------------------------------------------------------------------------------------------ buffers
     def _implicit(self, training: bool | None = None) -> bool:
@@ -85,7 +184,6 @@ class GraphMETTrainer:
         l, dev, depth = lib(), self.device, len(self.net.conv_continuous)
         u8 = lambda nbytes: torch.empty(int(nbytes), dtype=torch.uint8, device=dev)  # noqa: E731
         self.etaphi = torch.empty(N, 2, dtype=torch.float32, device=dev)
-        self.stats = torch.zeros(4, dtype=torch.int32, device=dev)
         if implicit:      # no edge list: O(N) state only
             self.geo_ws = u8(l.gm_geo_ws_bytes(N, B))
             self.perm = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
@@ -105,7 +203,7 @@ class GraphMETTrainer:
 
     # ------------------------------------------------------------------------------------------ pieces
     def _graph(self, x, ptr_i32, N, B, max_event_nodes, need_transpose):
-        l, st = lib(), stream()
+        l, st = lib(), stream(self.device)
         check(l.gm_prepare_etaphi(ptr(x), x.stride(0), N, ptr(self.etaphi), st), "gm_prepare_etaphi")
         if self._implicit():
             check(l.gm_geo_build(ptr(self.etaphi), 2, 2, ptr(ptr_i32), N, B, float(self.r), int(self.max_nn),
@@ -129,18 +227,18 @@ class GraphMETTrainer:
                                            x.stride(0), ptr(self.geo_ws), N, B, ptr(self.perm), int(training),
                                            int(save), int(self.apply_sigmoid), AGGR[net.aggr],
                                            PRECISION[net.edge_precision], float(net.bn_all.momentum), float(net.bn_all.eps), ptr(self.fwd_ws),
-                                           self.fwd_ws.numel(), ptr(self.weights), ptr(self.flags), stream()),
+                                           self.fwd_ws.numel(), ptr(self.weights), ptr(self.flags), stream(self.device)),
                   "gm_net_forward_geo")
             return
         check(lib().gm_net_forward(C.byref(self._P), ptr(x), x.stride(0), None, x.data_ptr() + 8 * 4, x.stride(0),
                                    ptr(self.rowptr), ptr(self.col), N, None, int(training), int(save),
                                    int(self.apply_sigmoid), AGGR[net.aggr], PRECISION[net.edge_precision],
                                    float(net.bn_all.momentum), float(net.bn_all.eps), ptr(self.fwd_ws),
-                                   self.fwd_ws.numel(), ptr(self.weights), ptr(self.flags), stream()),
+                                   self.fwd_ws.numel(), ptr(self.weights), ptr(self.flags), stream(self.device)),
               "gm_net_forward")
 
     def _backward(self, x, N, B):
-        net, l, st = self.net, lib(), stream()
+        net, l, st = self.net, lib(), stream(self.device)
         if self._implicit():
             check(l.gm_net_backward_geo(C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), None,
                                         x.data_ptr() + 32, x.stride(0), ptr(self.geo_ws), N, B, ptr(self.perm), 1,
@@ -166,26 +264,49 @@ class GraphMETTrainer:
     # ------------------------------------------------------------------------------------------ public
     def train_step(self, batch: EventBatch, max_event_nodes: int | None = None) -> torch.Tensor:
         """One optimisation step on a device-resident batch. Returns the loss as a 0-dim device tensor
-        (no sync). ``batch.x`` [N,11] f32, ``batch.y`` [B,>=2] f32, ``batch.ptr`` [B+1] i32."""
+        (no sync): the mean over this rank's events, or, with a process group, over ALL ranks' events.
+        ``batch.x`` [N,11] f32, ``batch.y`` [B,>=2] f32, ``batch.ptr`` [B+1] i32.  B == 0 is allowed (a rank whose
+        shard is empty still takes part in the gradient exchange, contributing zero)."""
+        self._raise_pending()
         x, y, p = batch.x, batch.y, batch.ptr
+        self._check_batch(x, y, p)
         N, B, men = self._sizes(batch, max_event_nodes)
         self.net.train()
-        self._reserve(N, B, men)
-        l, st = lib(), stream()
-        self._graph(x, p, N, B, men, need_transpose=True)
-        self._forward(x, N, B, training=True, save=True)
-        check(l.gm_met_loss(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
-                            ptr(self.met), ptr(self.loss), ptr(self.grad_w), st), "gm_met_loss")
-        self._backward(x, N, B)
-        scale = 1.0
-        if self.world > 1:
-            torch.distributed.all_reduce(self.flat_grad, group=self.pg)      # NCCL SUM over NVLink
-            scale = 1.0 / self.world
+        l, st = lib(), stream(self.device)
+        dp = self.world > 1
+        if N > 0 and B > 0:
+            self._reserve(N, B, men)
+            self._graph(x, p, N, B, men, need_transpose=True)
+            self._forward(x, N, B, training=True, save=True)
+            # DP: gradient of the per-event SUM; the optimiser kernel divides by the global event count
+            check(l.gm_met_loss_ex(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
+                                   1.0 if dp else 1.0 / B, ptr(self.met), ptr(self.loss), ptr(self.grad_w), st),
+                  "gm_met_loss")
+            self._backward(x, N, B)
+        else:                       # empty shard: nothing to differentiate, but the exchange below must still happen
+            self._payload.zero_()
+            self.loss.zero_()
+            B = 0
         self.step_count += 1
-        check(l.gm_adamw_step(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq),
-                              self.flat.numel(), self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay,
-                              self.step_count, scale, st), "gm_adamw_step")
-        return self.loss
+        hyper = (self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay, self.step_count)
+        mirrors = (ptr(self.flags), ptr(self.stats), ptr(self._status))
+        if not dp:
+            check(l.gm_adamw_step_ex(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq),
+                                     self.flat.numel(), *hyper, 1.0, None, *mirrors, st), "gm_adamw_step")
+            return self.loss
+        if self.comm is not None:   # ONE kernel: push to peers over NVLink, wait, rank-ordered sum, AdamW
+            check(l.gm_allreduce_adamw_step(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg),
+                                            ptr(self.exp_avg_sq), self.flat.numel(), *hyper, float(B), ptr(self.loss),
+                                            self.comm, ptr(self.global_loss), *mirrors, st), "gm_allreduce_adamw_step")
+            return self.global_loss
+        n = self.flat.numel()       # fallback: NCCL SUM all-reduce of [gradient | events | events * loss]
+        self._payload[n].fill_(float(B))
+        torch.mul(self.loss, float(B), out=self._payload[n + 1])
+        torch.distributed.all_reduce(self._payload, group=self.pg)
+        check(l.gm_adamw_step_ex(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq), n,
+                                 *hyper, 1.0, self._payload.data_ptr() + 4 * n, *mirrors, st), "gm_adamw_step")
+        torch.div(self._payload[n + 1], self._payload[n].clamp_min(1.0), out=self.global_loss)
+        return self.global_loss
 
     def train_step_from_host(self, host_batch: EventBatch, max_event_nodes: int | None = None) -> float:
         """End-to-end step from PINNED host buffers: H2D copies, the step, and the loss read back
@@ -198,7 +319,7 @@ class GraphMETTrainer:
             int((host_batch.ptr[1:] - host_batch.ptr[:-1]).max())       # host tensor: no device sync
         loss = self.train_step(EventBatch(x, y, None, p), men)
         self._host_loss.copy_(loss, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        torch.cuda.current_stream(self.device).synchronize()
         return float(self._host_loss)
 
     def _epoch_from_host(self, host_batches, depth, step):
@@ -238,13 +359,14 @@ class GraphMETTrainer:
     def eval_step(self, batch: EventBatch, max_event_nodes: int | None = None):
         """evaluate.py:81-100 fused: returns (weights[N] view, loss 0-dim, met[B,2]) on the device."""
         x, y, p = batch.x, batch.y, batch.ptr
+        self._check_batch(x, y, p)
         N, B, men = self._sizes(batch, max_event_nodes)
         self.net.eval()
         self._reserve(N, B, men)
         self._graph(x, p, N, B, men, need_transpose=False)
         self._forward(x, N, B, training=False, save=False)
         check(lib().gm_met_loss(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
-                                ptr(self.met), ptr(self.loss), None, stream()), "gm_met_loss")
+                                ptr(self.met), ptr(self.loss), None, stream(self.device)), "gm_met_loss")
         return self.weights[:N], self.loss, self.met[:B]
 
     def graph_stats(self):

@@ -83,6 +83,12 @@ long long gm_launch_count(int reset);  /* kernels this library launched since th
 int gm_timing_enable(int on);
 int gm_timing_read(int slot, float *total_ms_out, int *regions_out);
 
+/* Live peak measurements for roofline denominators that MEASURED_PEAKS.json does not carry (both SYNCHRONISE and
+ * allocate 4 bytes; measurement helpers, not part of the path): the chip-wide shared-memory read bandwidth (a
+ * conflict-free LDS.128 stream on every SM: what physically feeds the cell-staged EdgeConv) and the FFMA stream rate. */
+int gm_bench_smem_read(int iters, float *ms_out, double *gbytes_out);
+int gm_bench_ffma(int iters, float *ms_out, double *gflop_out);
+
 /* ---------------------------------------------------------------------------------
  * Parameters: the reference's 23 trainable tensors in construction order
  * (model/graph_met_network.py:15-45; state_dict names in comments) + BN buffers.
@@ -287,6 +293,14 @@ int gm_met_loss(const float *w, const float *pred, int pred_stride, const float 
                 int truth_stride, const int *ptr, int N, int B, float *met_out, float *loss_out,
                 float *grad_w_out, void *stream);
 
+/* gm_met_loss with an explicit scale on d loss / d w: grad_scale = 1/B reproduces loss_fn's mean (what gm_met_loss
+ * passes); grad_scale = 1 yields the gradient of the per-event SUM, which event-sharded data parallelism all-reduces
+ * and divides by the GLOBAL event count inside the optimiser kernel (ranks may hold different numbers of events).
+ * loss_out is the local mean in either case. */
+int gm_met_loss_ex(const float *w, const float *pred, int pred_stride, const float *truth,
+                   int truth_stride, const int *ptr, int N, int B, float grad_scale, float *met_out,
+                   float *loss_out, float *grad_w_out, void *stream);
+
 /* scatter_add(src, index) for a SORTED index given as ptr (model/net.py:55-56, :132-133). */
 int gm_segment_sum(const float *src, const int *ptr, int B, float *out, void *stream);
 /* torch_scatter.scatter_add for an arbitrary int64 index (atomicAdd; out must be pre-zeroed /
@@ -309,6 +323,47 @@ int gm_resolution(const float *met /*[B,2]*/, const float *truth, int truth_stri
 int gm_adamw_step(float *params, const float *grads, float *exp_avg, float *exp_avg_sq, int n,
                   float lr, float beta1, float beta2, float eps, float weight_decay,
                   int step, float grad_scale, void *stream);
+
+/* gm_adamw_step with (a) an optional DEVICE-side denominator: the gradient is multiplied by
+ * grad_scale / max(*grad_denominator_dev, 1) (the global event count that came out of an all-reduce), and (b) an
+ * optional status mirror: the kernel copies {step, err_flags_dev[0], graph_stats_dev[3]} into status_host (pinned,
+ * device-mapped host memory, int[4]) so the caller can raise on device-side error flags one step late without a
+ * copy or a synchronisation. */
+int gm_adamw_step_ex(float *params, const float *grads, float *exp_avg, float *exp_avg_sq, int n,
+                     float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                     float grad_scale, const float *grad_denominator_dev, const int *err_flags_dev,
+                     const int *graph_stats_dev, int *status_host, void *stream);
+
+/* ---------------------------------------------------------------------------------
+ * e. Event-sharded data parallelism: the ONE collective of the path -- the SUM all-reduce of the flat
+ *    gradient (26.6 KB for GraphMETNetwork) -- fused with the optimiser in ONE kernel over NVLink peer memory
+ *    (the reference is single-device, train.py:72; this replaces what DistributedDataParallel + optimizer.step()
+ *    would do around train.py:51-52).
+ *
+ *    Every rank owns an exchange buffer (allocated by gm_comm_create with cudaMalloc -- the only allocating call of
+ *    the library -- and exported as a 64-byte CUDA IPC handle); gm_comm_connect maps the peers' buffers.
+ *    gm_allreduce_adamw_step launches ONE kernel: every CTA stores its slice of
+ *        [ grads[0..n) | local_events | local_events * local_loss ]
+ *    into slot `rank` of EVERY rank's buffer (remote stores over NVLink / NVSwitch), publishes a per-(rank, CTA) flag
+ *    with release semantics, waits for the same slice from every peer, sums the world slices IN RANK ORDER (every
+ *    rank computes bit-identical sums, so parameters never diverge), divides by the global event count and applies
+ *    AdamW.  No NCCL kernel, no extra launch, no host synchronisation; slots are double-buffered by call parity.
+ *    Every rank must call it the same number of times with the same n.  comm == NULL: single process (scale =
+ *    1 / local_events).  Waits are bounded (a dead peer traps the kernel after ~20 s instead of hanging the GPU).
+ *    global_loss_out (optional, device float[1]): sum_r B_r * loss_r / sum_r B_r.
+ *    grads must be the gradient of the per-event SUM (gm_met_loss_ex with grad_scale = 1).
+ * --------------------------------------------------------------------------------- */
+typedef struct GmComm GmComm;
+#define GM_COMM_HANDLE_BYTES 64
+#define GM_COMM_MAX_WORLD 16
+int gm_comm_create(int n_floats, int rank, int world, GmComm **comm_out, void *ipc_handle_out);
+int gm_comm_connect(GmComm *comm, const void *all_handles /* world x GM_COMM_HANDLE_BYTES, rank order */);
+int gm_comm_destroy(GmComm *comm);
+int gm_allreduce_adamw_step(float *params, const float *grads, float *exp_avg, float *exp_avg_sq, int n,
+                            float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                            float local_events, const float *local_loss_dev, GmComm *comm,
+                            float *global_loss_out, const int *err_flags_dev, const int *graph_stats_dev,
+                            int *status_host, void *stream);
 
 #ifdef __cplusplus
 }
