@@ -194,14 +194,32 @@ def scatter_add(src, index, dim=-1, out=None, dim_size=None):
     return out.scatter_add_(dim, index, src)
 
 
+def round_operand(t: torch.Tensor, mode: str) -> torch.Tensor:
+    """What the tensor-core variants do to an MMA input: the value is formed in fp32, then rounded to bf16
+    (cvt.rn.bf16x2.f32: nearest even) or tf32 (cvt.rna.tf32.f32: nearest, ties away) -- returned in t's dtype so an
+    fp64 twin can carry the rounded value exactly."""
+    t32 = t.to(torch.float32)
+    if mode == "bf16":
+        return t32.to(torch.bfloat16).to(t.dtype)
+    if mode == "tf32":
+        bits = t32.contiguous().view(torch.int32)
+        return ((bits + 0x1000) & ~0x1FFF).view(torch.float32).to(t.dtype)
+    raise ValueError(mode)
+
+
 class EdgeConv(nn.Module):
-    """[upstream torch_geometric.nn.EdgeConv] op-for-op: gather, sub, cat, nn, scatter-aggr."""
+    """[upstream torch_geometric.nn.EdgeConv] op-for-op: gather, sub, cat, nn, scatter-aggr.
+
+    ``operand_rounding`` ("bf16" / "tf32", default None) turns the module into the arithmetic MODEL of the tcgen05
+    variants for error budgeting (tests only): msg = W1 x_i + b + round(W2) round(fp32(x_j - x_i)), products and sums
+    in the module's own dtype -- run it in float64 and the only error left is the operand rounding itself."""
 
     def __init__(self, nn, aggr="max"):  # noqa: A002 (the upstream argument is called `nn`)
         super().__init__()
         self.nn = nn
         self.aggr = aggr
         self.flow = "source_to_target"
+        self.operand_rounding = None
 
     def jittable(self):  # model/graph_met_network.py:38 calls .jittable()
         return self
@@ -210,7 +228,13 @@ class EdgeConv(nn.Module):
         j, i = edge_index[0], edge_index[1]
         x_i = x.index_select(0, i)
         x_j = x.index_select(0, j)
-        msg = self.nn(torch.cat([x_i, x_j - x_i], dim=-1))
+        if self.operand_rounding is None:
+            msg = self.nn(torch.cat([x_i, x_j - x_i], dim=-1))
+        else:
+            lin, H = self.nn[0], x.size(-1)
+            d = round_operand(x_j.float() - x_i.float(), self.operand_rounding).to(x.dtype)
+            w2 = round_operand(lin.weight[:, H:], self.operand_rounding)
+            msg = x_i @ lin.weight[:, :H].t() + lin.bias + d @ w2.t()
         N, C = x.size(0), msg.size(-1)
         idx = i.view(-1, 1).expand(-1, C)
         out = msg.new_zeros(N, C)

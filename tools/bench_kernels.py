@@ -8,3 +8,6 @@ for f in sys.argv[1:]:
     print(f"{f}: {d['value']:.0f} {d['unit']}  {d['ms_per_step']:.3f} ms/step  e2e {d['e2e']['value']:.0f}")
     ks = sorted(d.get("kernels", {}).items(), key=lambda kv: -kv[1]["avg_us"] * kv[1]["regions"])
     print("   " + "  ".join(f"{k}={v['avg_us']:.1f}" for k, v in ks))
+    for name, sd in (d.get("side") or {}).items():
+        r = sd.get("roofline") or {}
+        print(f"   side {name}: {sd['value']:.0f} {sd['unit']}  {sd['ms_per_step']:.3f} ms/step  roofline {r.get('kernel')} frac {r.get('frac')}")
