@@ -146,3 +146,99 @@ def global_max_pool(x, batch, size=None):
     size = int(batch.max()) + 1 if size is None else size
     out = x.new_zeros(size, x.size(1))
     return out.scatter_reduce(0, batch.view(-1, 1).expand(-1, x.size(1)), x, "amax", include_self=False)
+
+
+# --------------------------------------------------------------------------- the reference's own model, restated
+class DynamicReductionNetwork(nn.Module):
+    """dynamic_reduction_network.py:32-103 with the same attribute names (state_dict keys are the contract).
+
+    ``forward(data, hooks=None)``: ``hooks`` (tests only) may replace the DISCRETE stages so that a float stage can be
+    compared on identical graphs: ``hooks["graph"](stage, x, batch) -> edge_index`` and
+    ``hooks["cluster"](stage, edge_index, weight, n) -> cluster``; ``hooks["record"]`` (a dict) receives every
+    intermediate."""
+
+    def __init__(self, input_dim=5, hidden_dim=64, output_dim=1, k=16, aggr="add",
+                 norm=torch.tensor([1. / 500., 1. / 500., 1. / 54., 1 / 25., 1. / 1000.])):
+        super().__init__()
+        self.datanorm = nn.Parameter(norm)
+        self.k = k
+        start_width = 2 * hidden_dim
+        middle_width = 3 * hidden_dim // 2
+        self.inputnet = nn.Sequential(
+            nn.Linear(input_dim, hidden_dim // 2), nn.ELU(),
+            nn.Linear(hidden_dim // 2, hidden_dim), nn.ELU(),
+            nn.Linear(hidden_dim, hidden_dim), nn.ELU())
+
+        def convnn():
+            return nn.Sequential(nn.Linear(start_width, middle_width), nn.ELU(),
+                                 nn.Linear(middle_width, hidden_dim), nn.ELU(),
+                                 nn.BatchNorm1d(num_features=hidden_dim))
+        self.edgeconv1 = O.EdgeConv(nn=convnn(), aggr=aggr)
+        self.edgeconv2 = O.EdgeConv(nn=convnn(), aggr=aggr)
+        self.output = nn.Sequential(nn.Linear(hidden_dim, hidden_dim), nn.ELU(),
+                                    nn.Linear(hidden_dim, hidden_dim // 2), nn.ELU(),
+                                    nn.Linear(hidden_dim // 2, output_dim))
+
+    def forward(self, data, hooks=None):
+        hooks = hooks or {}
+        rec = hooks.get("record")
+
+        def note(name, v):
+            if rec is not None:
+                rec[name] = v.detach().clone() if torch.is_tensor(v) else v
+
+        def graph(stage, x, batch):
+            if "graph" in hooks:
+                return hooks["graph"](stage, x, batch)
+            return to_undirected(O.knn_graph(x, self.k, batch, loop=False, flow="source_to_target"), x.size(0))
+
+        def cluster_of(stage, ei, w, n):
+            if "cluster" in hooks:
+                return hooks["cluster"](stage, ei, w, n)
+            return graclus(ei, w, n)
+
+        x = self.datanorm * data.x                                   # :82
+        x = self.inputnet(x)                                         # :83
+        note("x0", x)
+        ei = graph(1, x, data.batch)                                 # :86
+        note("edge_index1", ei)
+        x = self.edgeconv1(x, ei)                                    # :87
+        note("x1", x)
+        weight = normalized_cut_2d(ei, x)                            # :89
+        note("weight1", weight)
+        cluster = cluster_of(1, ei, weight, x.size(0))               # :90
+        note("cluster1", cluster)
+        pooled = max_pool(cluster, types.SimpleNamespace(x=x, batch=data.batch, edge_index=ei))   # :92
+        x, batch = pooled.x, pooled.batch
+        note("x1p", x); note("batch1p", batch)
+        ei = graph(2, x, batch)                                      # :95
+        note("edge_index2", ei)
+        x = self.edgeconv2(x, ei)                                    # :96
+        note("x2", x)
+        weight = normalized_cut_2d(ei, x)                            # :98
+        note("weight2", weight)
+        cluster = cluster_of(2, ei, weight, x.size(0))               # :99
+        note("cluster2", cluster)
+        x, batch = max_pool_x(cluster, x, batch)                     # :100
+        x = global_max_pool(x, batch)                                # :102
+        note("pooled", x)
+        return self.output(x).squeeze(-1)                            # :104
+
+
+DRN_NORM = [1. / 2950.0, 1. / 2950.0, 1. / 2950.0, 1. / 5.265625, 1. / 143.875, 1. / 589., 1. / 1.2050781, 1. / 211., 1.,
+            1. / 7., 1.]
+
+
+class DRNNet(nn.Module):
+    """The commented-out wrapper at model/net.py:12-37."""
+
+    def __init__(self):
+        super().__init__()
+        self.drn = DynamicReductionNetwork(input_dim=11, hidden_dim=64, k=8, output_dim=2, aggr="max",
+                                           norm=torch.tensor(DRN_NORM))
+
+    def forward(self, data, hooks=None):
+        output = self.drn(data, hooks)
+        met = nn.Softplus()(output[:, 0]).unsqueeze(1)
+        metphi = math.pi * (2 * torch.sigmoid(output[:, 1]) - 1).unsqueeze(1)
+        return torch.cat((met, metphi), 1)
