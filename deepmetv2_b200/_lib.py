@@ -46,6 +46,22 @@ class GmParams(C.Structure):
                 ("continuous_dim", _i), ("conv_depth", _i)]
 
 
+class GmDrnConv(C.Structure):
+    _fields_ = [("w1", _vp), ("b1", _vp), ("w2", _vp), ("b2", _vp), ("bn_weight", _vp), ("bn_bias", _vp),
+                ("bn_running_mean", _vp), ("bn_running_var", _vp), ("bn_num_batches_tracked", _vp)]
+
+
+class GmDrnParams(C.Structure):
+    _fields_ = [("datanorm", _vp), ("in_w", _vp * 3), ("in_b", _vp * 3), ("conv", GmDrnConv * 2),
+                ("out_w", _vp * 3), ("out_b", _vp * 3), ("output_dim", _i), ("k", _i)]
+
+
+class GmDrnView(C.Structure):
+    _fields_ = [("x0", _vp), ("rowptr1", _vp), ("col1", _vp), ("row1", _vp), ("x1", _vp), ("weight1", _vp),
+                ("cluster1", _vp), ("partner1", _vp), ("x1p", _vp), ("ptr1p", _vp), ("rowptr2", _vp), ("col2", _vp),
+                ("row2", _vp), ("x2", _vp), ("pooled", _vp), ("edge_capacity", _ll)]
+
+
 # name -> (restype, argtypes); must list every symbol include/graphmet.h declares
 SIGNATURES = {
     "gm_version": (_i, []),
@@ -95,6 +111,14 @@ SIGNATURES = {
     "gm_comm_create": (_i, [_i, _i, _i, C.POINTER(_vp), _vp]),
     "gm_comm_connect": (_i, [_vp, _vp]),
     "gm_comm_destroy": (_i, [_vp]),
+    "gm_undirected_ws_bytes": (_sz, [_i, _ll]),
+    "gm_csr_to_undirected": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _sz, _vp, _vp, _vp, _ll, _vp, _vp]),
+    "gm_normalized_cut": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _ll, _vp, _vp]),
+    "gm_graclus": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "gm_cluster_max_pool": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _sz, _vp, _vp, _vp, _vp]),
+    "gm_drn_ws_bytes": (_sz, [_i, _i, _i]),
+    "gm_drn_forward": (_i, [C.POINTER(GmDrnParams), _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _f, _vp, _sz, _vp, _vp,
+                            C.POINTER(GmDrnView), _vp]),
     "gm_allreduce_adamw_step": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp,
                                      _vp]),
 }

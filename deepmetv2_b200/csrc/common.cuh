@@ -216,14 +216,15 @@ __device__ __forceinline__ void dense_t_smem(const float *__restrict__ W, const 
 //     nodes  ng, ng+32, ng+64, ng+96  (ng = t / (O/4))    x    outputs 4*og .. 4*og+3  (og = t % (O/4)),
 // so per k it issues 4 scalar LDS (x) + 1 LDS.128 (w) for 16 independent FMAs, and a warp's results are whole
 // contiguous output rows (coalesced float4 stores straight from registers).  acc[i][j] += x[ng+32i][k] * wT[k][4og+j].
-template <int K, int O, int LD>
+// PITCH (>= O, floats): row pitch of wT when the O outputs are a column block of a wider K-major matrix.
+template <int K, int O, int LD, int PITCH = O>
 __device__ __forceinline__ void tile_gemm(const float *__restrict__ sX, const float *__restrict__ wT, int ng, int og,
                                           float (&acc)[4][4]) {
     const float *x0 = sX + ng * LD;
     const float4 *w4 = reinterpret_cast<const float4 *>(wT) + og;
 #pragma unroll 8
     for (int k = 0; k < K; ++k) {
-        const float4 w = w4[k * (O / 4)];
+        const float4 w = w4[k * (PITCH / 4)];
         const float a0 = x0[k], a1 = x0[32 * LD + k], a2 = x0[64 * LD + k], a3 = x0[96 * LD + k];
         acc[0][0] = fmaf(a0, w.x, acc[0][0]); acc[0][1] = fmaf(a0, w.y, acc[0][1]);
         acc[0][2] = fmaf(a0, w.z, acc[0][2]); acc[0][3] = fmaf(a0, w.w, acc[0][3]);

@@ -1,0 +1,432 @@
+// Graph operators of the DynamicReductionNetwork variant -- CUDA forms of the upstream calls at
+// /root/reference/model/dynamic_reduction_network.py:86-102, restated on the CPU in oracle/drn_oracle.py:
+//   to_undirected(knn_graph(...))   -> gm_csr_to_undirected   (symmetrise + coalesce, sorted by (row, col))
+//   normalized_cut_2d               -> gm_normalized_cut
+//   graclus                         -> gm_graclus              (torch_cluster's CPU greedy matching, per event)
+//   max_pool / max_pool_x           -> gm_cluster_max_pool     (consecutive cluster ids + per-cluster max)
+// Every kernel takes the node count as min(N, *n_dev) when n_dev is given: the pooled graph's size only exists on the
+// device and the whole DRN forward runs without a host synchronisation.  Integer work: results are bit-exact.
+#include "common.cuh"
+
+namespace gm {
+
+int exclusive_scan_inplace(int *data, int n, int *tile_totals, int *total_out, cudaStream_t st);
+
+namespace {
+
+__device__ __forceinline__ int eff_n(int N, const int *n_dev) {
+    if (!n_dev) return N;
+    const int v = *n_dev;
+    return v < 0 ? 0 : (v < N ? v : N);
+}
+
+// directed input: either a CSR (rowptr, col) or the padded neighbour table of the k-NN search (nbr [N,K], deg [N])
+struct Directed {
+    const int *rowptr, *col, *nbr, *deg;
+    int K;
+    __device__ __forceinline__ int count(int i) const { return nbr ? deg[i] : rowptr[i + 1] - rowptr[i]; }
+    __device__ __forceinline__ int entry(int i, int s) const { return nbr ? nbr[(size_t)i * K + s] : col[rowptr[i] + s]; }
+};
+
+// rcnt[j] = number of rows that list j  (rcnt zeroed by the caller)
+__global__ void __launch_bounds__(256) k_und_count(Directed g, int N, const int *__restrict__ n_dev, int *__restrict__ rcnt) {
+    pdl_sync();
+    const int n = eff_n(N, n_dev);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int c = g.count(i);
+        for (int s = 0; s < c; ++s) {
+            const int j = g.entry(i, s);
+            if (j >= 0 && j < n) atomicAdd(rcnt + j, 1);
+        }
+    }
+}
+
+// capptr[i] = own(i) + rcnt[i]  (then scanned: row i of the scratch list holds own entries, then the reverse ones)
+__global__ void __launch_bounds__(256) k_und_cap(Directed g, int N, const int *__restrict__ n_dev, const int *__restrict__ rcnt,
+                                                 int *__restrict__ capptr) {
+    pdl_sync();
+    const int n = eff_n(N, n_dev);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= N; i += gridDim.x * blockDim.x)
+        capptr[i] = i < n ? g.count(i) + rcnt[i] : 0;
+}
+
+__global__ void __launch_bounds__(256) k_und_fill(Directed g, int N, const int *__restrict__ n_dev, int *__restrict__ rcnt,
+                                                  const int *__restrict__ capptr, int *__restrict__ tmp) {
+    pdl_sync();
+    const int n = eff_n(N, n_dev);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int c = g.count(i), base = capptr[i];
+        for (int s = 0; s < c; ++s) {
+            const int j = g.entry(i, s);
+            tmp[base + s] = j;
+            if (j >= 0 && j < n) {
+                const int slot = atomicSub(rcnt + j, 1) - 1;     // any order: the row is ranked afterwards
+                tmp[capptr[j] + g.count(j) + slot] = i;
+            }
+        }
+    }
+}
+
+// warp per node: flag every entry that repeats an earlier one of the row (or is out of range); degU = #distinct
+__global__ void __launch_bounds__(256) k_und_dedupe(int N, const int *__restrict__ n_dev, const int *__restrict__ capptr,
+                                                    const int *__restrict__ tmp, unsigned char *__restrict__ dupf,
+                                                    int *__restrict__ rowptr_out) {
+    pdl_sync();
+    const int n = eff_n(N, n_dev);
+    const int lane = threadIdx.x & 31;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i <= N; i += warps) {
+        if (i >= n) {
+            if (lane == 0) rowptr_out[i] = 0;
+            continue;
+        }
+        const int a = capptr[i], len = capptr[i + 1] - a;
+        int distinct = 0;
+        for (int t = lane; t < len; t += 32) {
+            const int v = tmp[a + t];
+            bool dup = v < 0 || v >= n;
+            for (int s = 0; s < t; ++s) dup |= tmp[a + s] == v;
+            dupf[a + t] = dup ? 1 : 0;
+            distinct += dup ? 0 : 1;
+        }
+        distinct = warp_sum_int(distinct);
+        if (lane == 0) rowptr_out[i] = distinct;
+    }
+}
+
+// warp per node: rank of every distinct entry among the row's distinct entries -> sorted, coalesced row
+__global__ void __launch_bounds__(256) k_und_emit(int N, const int *__restrict__ n_dev, const int *__restrict__ capptr,
+                                                  const int *__restrict__ tmp, const unsigned char *__restrict__ dupf,
+                                                  const int *__restrict__ rowptr_out, int *__restrict__ col_out,
+                                                  int *__restrict__ row_out, long long capacity,
+                                                  long long *__restrict__ ei64) {
+    pdl_sync();
+    const int n = eff_n(N, n_dev);
+    const int lane = threadIdx.x & 31;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += warps) {
+        const int a = capptr[i], len = capptr[i + 1] - a, o = rowptr_out[i];
+        for (int t = lane; t < len; t += 32) {
+            if (dupf[a + t]) continue;
+            const int v = tmp[a + t];
+            int rank = 0;
+            for (int s = 0; s < len; ++s) rank += (!dupf[a + s] && tmp[a + s] < v) ? 1 : 0;
+            const long long p = (long long)o + rank;
+            if (p >= capacity) continue;
+            if (col_out) col_out[p] = v;
+            if (row_out) row_out[p] = i;
+            if (ei64) { ei64[p] = i; ei64[capacity + p] = v; }
+        }
+    }
+}
+
+struct UndWs {
+    int *rcnt, *capptr, *tmp, *tiles;
+    unsigned char *dupf;
+};
+size_t und_layout(int N, long long Ed, char *base, UndWs *w) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+    const size_t nodes = (size_t)(N > 0 ? N : 1) + 1, ent = (size_t)(Ed > 0 ? Ed : 1) * 2;
+    const size_t o_r = take(nodes * 4), o_c = take(nodes * 4), o_t = take(ent * 4), o_d = take(ent),
+                 o_s = take((nodes / 1024 + 2) * 4);
+    if (w) {
+        w->rcnt = (int *)(base + o_r); w->capptr = (int *)(base + o_c); w->tmp = (int *)(base + o_t);
+        w->dupf = (unsigned char *)(base + o_d); w->tiles = (int *)(base + o_s);
+    }
+    return off;
+}
+
+// ------------------------------------------------------------------------------------------ normalized cut
+// 8 lanes per edge: ||x[row] - x[col]||_2 * (1/deg[row] + 1/deg[col]);  E = rowptr[N] on the device
+__global__ void __launch_bounds__(256) k_normalized_cut(const float *__restrict__ x, int stride, int dim,
+                                                        const int *__restrict__ rowptr, const int *__restrict__ col,
+                                                        const int *__restrict__ row, int N, long long capacity,
+                                                        float *__restrict__ w_out) {
+    pdl_sync();
+    long long E = rowptr[N];
+    if (E > capacity) E = capacity;
+    const int sub = threadIdx.x & 7;
+    const long long groups = ((long long)gridDim.x * blockDim.x) >> 3;
+    const long long Epad = (E + 3) / 4 * 4;      // whole warps stay converged for the shuffles
+    for (long long p = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3; p < Epad; p += groups) {
+        const bool live = p < E;
+        const int r = live ? row[p] : 0, c = live ? col[p] : 0;
+        const float4 *xr = reinterpret_cast<const float4 *>(x + (size_t)r * stride);
+        const float4 *xc = reinterpret_cast<const float4 *>(x + (size_t)c * stride);
+        float acc = 0.f;
+        for (int d4 = sub; d4 < dim / 4; d4 += 8) {
+            const float4 a = xr[d4], b = xc[d4];
+            float d;
+            d = a.x - b.x; acc = fmaf(d, d, acc);
+            d = a.y - b.y; acc = fmaf(d, d, acc);
+            d = a.z - b.z; acc = fmaf(d, d, acc);
+            d = a.w - b.w; acc = fmaf(d, d, acc);
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        if (live && sub == 0) {
+            const float dr = 1.0f / (float)(rowptr[r + 1] - rowptr[r]);
+            const float dc = 1.0f / (float)(rowptr[c + 1] - rowptr[c]);
+            w_out[p] = sqrtf(acc) * (dr + dc);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ graclus
+// One warp per event (the matching is sequential in visiting order by definition; events are independent
+// components).  The matched state lives in shared memory; the rows of the next 32 visited nodes are staged into
+// shared memory with independent loads, so the sequential phase never waits on L2.
+constexpr int GR_BUF = 2048;      // staged row entries per block of 32 visited nodes
+
+__global__ void __launch_bounds__(32) k_graclus(const int *__restrict__ rowptr, const int *__restrict__ col,
+                                                const float *__restrict__ weight, const int *__restrict__ ptr, int B,
+                                                const int *__restrict__ visit, int state_cap, int *__restrict__ cluster,
+                                                int *__restrict__ partner) {
+    extern __shared__ int s_gr[];
+    int *s_col = s_gr;
+    float *s_w = reinterpret_cast<float *>(s_gr + GR_BUF);
+    int *s_state = s_gr + 2 * GR_BUF;       // [state_cap] cluster id or -1
+    pdl_sync();
+    const int lane = threadIdx.x;
+    for (int e = blockIdx.x; e < B; e += gridDim.x) {
+        const int base = ptr[e], n = ptr[e + 1] - base;
+        if (n <= 0) continue;
+        const bool in_smem = n <= state_cap;
+        volatile int *g_state = cluster + base;                     // slow path: the output array is the state
+        for (int l = lane; l < n; l += 32) {
+            if (in_smem) s_state[l] = -1; else g_state[l] = -1;
+        }
+        __syncwarp();
+        for (int n0 = 0; n0 < n; n0 += 32) {
+            const int pos = n0 + lane;
+            const int u_l = pos < n ? (visit ? visit[base + pos] : base + pos) : -1;
+            const int ra = u_l >= 0 ? rowptr[u_l] : 0;
+            const int len_l = u_l >= 0 ? rowptr[u_l + 1] - ra : 0;
+            int total;
+            const int off_l = warp_excl_scan_int(len_l, lane, total);
+            const bool staged = total <= GR_BUF;
+            const int cnt = min(32, n - n0);
+            if (staged) {
+                for (int q = 0; q < cnt; ++q) {
+                    const int a = __shfl_sync(0xffffffffu, ra, q), l = __shfl_sync(0xffffffffu, len_l, q),
+                              o = __shfl_sync(0xffffffffu, off_l, q);
+                    for (int t = lane; t < l; t += 32) {
+                        s_col[o + t] = col[a + t];
+                        s_w[o + t] = weight ? weight[a + t] : 0.f;
+                    }
+                }
+            }
+            __syncwarp();
+            for (int q = 0; q < cnt; ++q) {
+                const int u = __shfl_sync(0xffffffffu, u_l, q);
+                const int su = in_smem ? s_state[u - base] : g_state[u - base];
+                if (su >= 0) continue;                               // warp-uniform
+                const int a = __shfl_sync(0xffffffffu, ra, q), l = __shfl_sync(0xffffffffu, len_l, q),
+                          o = __shfl_sync(0xffffffffu, off_l, q);
+                float bw = -1.f;
+                int bt = -1, bv = u;
+                for (int t0 = 0; t0 < l; t0 += 32) {
+                    const int t = t0 + lane;
+                    if (t < l) {
+                        const int v = staged ? s_col[o + t] : col[a + t];
+                        const float w = staged ? s_w[o + t] : (weight ? weight[a + t] : 0.f);
+                        const int lv = v - base;
+                        bool ok = v != u && lv >= 0 && lv < n && w >= 0.f;
+                        if (ok) ok = (in_smem ? s_state[lv] : g_state[lv]) < 0;
+                        // weighted: largest weight, ties to the later entry; unweighted: the first unmatched entry
+                        if (ok && (weight ? (w >= bw) : (bt < 0))) { bw = w; bt = t; bv = v; }
+                    }
+                }
+#pragma unroll
+                for (int s = 16; s > 0; s >>= 1) {
+                    const float ow = __shfl_xor_sync(0xffffffffu, bw, s);
+                    const int ot = __shfl_xor_sync(0xffffffffu, bt, s), ov = __shfl_xor_sync(0xffffffffu, bv, s);
+                    bool take;
+                    if (weight) take = ot >= 0 && (bt < 0 || ow > bw || (ow == bw && ot > bt));
+                    else take = ot >= 0 && (bt < 0 || ot < bt);
+                    if (take) { bw = ow; bt = ot; bv = ov; }
+                }
+                const int vmax = bt >= 0 ? bv : u;
+                const int c = min(u, vmax);
+                if (lane == 0) {
+                    if (in_smem) { s_state[u - base] = c; s_state[vmax - base] = c; }
+                    else { g_state[u - base] = c; g_state[vmax - base] = c; }
+                    cluster[u] = c; cluster[vmax] = c;
+                    if (partner) {
+                        if (vmax == u) partner[u] = -1;
+                        else { partner[u] = vmax; partner[vmax] = u; }
+                    }
+                }
+                __syncwarp();
+            }
+            __syncwarp();
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ pooling
+__global__ void __launch_bounds__(256) k_pool_flags(const int *__restrict__ cluster, int N, const int *__restrict__ n_dev,
+                                                    int *__restrict__ scan) {
+    pdl_sync();
+    const int n = eff_n(N, n_dev);
+    for (int u = blockIdx.x * blockDim.x + threadIdx.x; u <= N; u += gridDim.x * blockDim.x)
+        scan[u] = (u < n && cluster[u] == u) ? 1 : 0;
+}
+
+// 16 lanes per node (float4 each at dim 64): x_out[newid] = max(x[u], x[partner])
+__global__ void __launch_bounds__(256) k_pool_apply(const float *__restrict__ x, int dim, const int *__restrict__ cluster,
+                                                    const int *__restrict__ partner, const int *__restrict__ ptr, int N, int B,
+                                                    const int *__restrict__ n_dev, const int *__restrict__ scan,
+                                                    float *__restrict__ x_out, int *__restrict__ ptr_out,
+                                                    int *__restrict__ newid_out) {
+    pdl_sync();
+    const int n = eff_n(N, n_dev);
+    const int q = dim / 4;
+    const long long total = (long long)n * q;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const int u = (int)(t / q), d4 = (int)(t - (long long)u * q);
+        const int cu = cluster[u];
+        if (d4 == 0 && newid_out) newid_out[u] = scan[cu];
+        if (cu != u) continue;
+        float4 a = reinterpret_cast<const float4 *>(x + (size_t)u * dim)[d4];
+        const int v = partner[u];
+        if (v >= 0) {
+            const float4 b = reinterpret_cast<const float4 *>(x + (size_t)v * dim)[d4];
+            a.x = fmaxf(a.x, b.x); a.y = fmaxf(a.y, b.y); a.z = fmaxf(a.z, b.z); a.w = fmaxf(a.w, b.w);
+        }
+        reinterpret_cast<float4 *>(x_out + (size_t)scan[u] * dim)[d4] = a;
+    }
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e <= B; e += gridDim.x * blockDim.x) {
+        const int s = min(ptr[e], n);
+        ptr_out[e] = scan[s];
+    }
+}
+
+}  // namespace
+
+// internal entry points shared with drn_net.cu
+int drn_to_undirected(const int *rowptr, const int *col, const int *nbr, const int *deg, int K, int N, const int *n_dev,
+                      void *ws, size_t ws_bytes, int *rowptr_out, int *col_out, int *row_out, long long capacity,
+                      long long *ei64, cudaStream_t st) {
+    const long long Ed = nbr ? (long long)N * K : (capacity + 1) / 2;     // CSR input: capacity >= 2 x directed edges
+    UndWs w;
+    if (ws_bytes < und_layout(N, Ed, nullptr, nullptr)) return GM_ERR_CAPACITY;
+    und_layout(N, Ed, (char *)ws, &w);
+    Directed g{rowptr, col, nbr, deg, K};
+    GM_CUDA_TRY(cudaMemsetAsync(w.rcnt, 0, ((size_t)N + 1) * sizeof(int), st));
+    const int gn = persistent_grid(((long long)N + 256) / 256, 8);
+    const int gw = persistent_grid(((long long)N * 32 + 255) / 256 + 1, 8);
+    GM_LAUNCH_PDL(k_und_count, gn, 256, 0, st, g, N, n_dev, w.rcnt);
+    GM_LAUNCH_CHECK();
+    GM_LAUNCH_PDL(k_und_cap, gn, 256, 0, st, g, N, n_dev, (const int *)w.rcnt, w.capptr);
+    GM_LAUNCH_CHECK();
+    GM_TRY(exclusive_scan_inplace(w.capptr, N + 1, w.tiles, nullptr, st));
+    GM_LAUNCH_PDL(k_und_fill, gn, 256, 0, st, g, N, n_dev, w.rcnt, (const int *)w.capptr, w.tmp);
+    GM_LAUNCH_CHECK();
+    GM_LAUNCH_PDL(k_und_dedupe, gw, 256, 0, st, N, n_dev, (const int *)w.capptr, (const int *)w.tmp, w.dupf, rowptr_out);
+    GM_LAUNCH_CHECK();
+    GM_TRY(exclusive_scan_inplace(rowptr_out, N + 1, w.tiles, nullptr, st));
+    GM_LAUNCH_PDL(k_und_emit, gw, 256, 0, st, N, n_dev, (const int *)w.capptr, (const int *)w.tmp,
+                  (const unsigned char *)w.dupf, (const int *)rowptr_out, col_out, row_out, capacity, ei64);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+int drn_normalized_cut(const float *x, int stride, int dim, const int *rowptr, const int *col, const int *row, int N,
+                       long long capacity, float *w_out, cudaStream_t st) {
+    const int g = persistent_grid((capacity * 8 + 255) / 256, 8);
+    GM_LAUNCH_PDL(k_normalized_cut, g, 256, 0, st, x, stride, dim, rowptr, col, row, N, capacity, w_out);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+int drn_graclus(const int *rowptr, const int *col, const float *weight, const int *ptr, int N, int B, int men,
+                const int *visit, int *cluster, int *partner, cudaStream_t st) {
+    (void)N;
+    int cap = men > 0 ? men : 1;
+    const int max_cap = (200 * 1024 - 2 * GR_BUF * 4) / 4;
+    if (cap > max_cap) cap = max_cap;            // larger events run with the state in global memory
+    const size_t smem = (size_t)(2 * GR_BUF + cap) * 4;
+    static bool attr_set = false;
+    if (!attr_set) {
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_graclus, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+    }
+    GM_LAUNCH_PDL(k_graclus, B, 32, smem, st, rowptr, col, weight, ptr, B, visit, cap, cluster, partner);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+int drn_max_pool(const float *x, int dim, const int *cluster, const int *partner, const int *ptr, int N, int B,
+                 const int *n_dev, int *scan, int *tiles, float *x_out, int *ptr_out, int *newid_out, cudaStream_t st) {
+    const int gn = persistent_grid(((long long)N + 256) / 256, 8);
+    GM_LAUNCH_PDL(k_pool_flags, gn, 256, 0, st, cluster, N, n_dev, scan);
+    GM_LAUNCH_CHECK();
+    GM_TRY(exclusive_scan_inplace(scan, N + 1, tiles, nullptr, st));
+    const int ga = persistent_grid(((long long)N * (dim / 4) + 255) / 256 + 1, 8);
+    GM_LAUNCH_PDL(k_pool_apply, ga, 256, 0, st, x, dim, cluster, partner, ptr, N, B, n_dev, (const int *)scan, x_out,
+                  ptr_out, newid_out);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+}  // namespace gm
+
+using namespace gm;
+
+extern "C" {
+
+size_t gm_undirected_ws_bytes(int N, long long E_directed_capacity) {
+    return und_layout(N < 0 ? 0 : N, E_directed_capacity, nullptr, nullptr);
+}
+
+int gm_csr_to_undirected(const int *rowptr, const int *col, const int *nbr, const int *deg, int K, int N,
+                         const int *n_dev, void *ws, size_t ws_bytes, int *rowptr_out, int *col_out, int *row_out,
+                         long long capacity, int64_t *edge_index64_out, void *stream) {
+    if (N < 0 || !ws || !rowptr_out || capacity < 0) return GM_ERR_INVALID_ARGUMENT;
+    const bool table = nbr != nullptr;
+    if (N > 0 && (table ? (!deg || K < 1) : (!rowptr || !col))) return GM_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = as_stream(stream);
+    if (N == 0) {
+        GM_CUDA_TRY(cudaMemsetAsync(rowptr_out, 0, sizeof(int), st));
+        return GM_OK;
+    }
+    return drn_to_undirected(rowptr, col, nbr, deg, K, N, n_dev, ws, ws_bytes, rowptr_out, col_out, row_out, capacity,
+                             (long long *)edge_index64_out, st);
+}
+
+int gm_normalized_cut(const float *x, int x_stride, int dim, const int *rowptr, const int *col, const int *row,
+                      int N, long long capacity, float *weight_out, void *stream) {
+    if (N < 0 || capacity < 0 || (N > 0 && (!x || !rowptr || !col || !row || !weight_out))) return GM_ERR_INVALID_ARGUMENT;
+    if (dim < 4 || (dim & 3) || (x_stride & 3) || (reinterpret_cast<uintptr_t>(x) & 15)) return GM_ERR_UNSUPPORTED;
+    if (N == 0 || capacity == 0) return GM_OK;
+    return drn_normalized_cut(x, x_stride, dim, rowptr, col, row, N, capacity, weight_out, as_stream(stream));
+}
+
+int gm_graclus(const int *rowptr, const int *col, const float *weight, const int *ptr, int N, int B,
+               int max_event_nodes, const int *visit, int *cluster_out, int *partner_out, void *stream) {
+    if (N < 0 || B < 0 || (N > 0 && (!rowptr || !col || !ptr || !cluster_out || B < 1))) return GM_ERR_INVALID_ARGUMENT;
+    if (N == 0) return GM_OK;
+    return drn_graclus(rowptr, col, weight, ptr, N, B, max_event_nodes, visit, cluster_out, partner_out, as_stream(stream));
+}
+
+int gm_cluster_max_pool(const float *x, int dim, const int *cluster, const int *partner, const int *ptr, int N,
+                        int B, const int *n_dev, void *scan_ws, size_t scan_ws_bytes, float *x_out, int *ptr_out,
+                        int *newid_out, void *stream) {
+    if (N < 0 || B < 0 || !scan_ws || !ptr_out || (N > 0 && (!x || !cluster || !partner || !ptr || !x_out)))
+        return GM_ERR_INVALID_ARGUMENT;
+    if (dim < 4 || (dim & 3)) return GM_ERR_UNSUPPORTED;
+    UndWs w;
+    if (scan_ws_bytes < und_layout(N, 0, nullptr, nullptr)) return GM_ERR_CAPACITY;
+    und_layout(N, 0, (char *)scan_ws, &w);
+    cudaStream_t st = as_stream(stream);
+    if (N == 0) {
+        GM_CUDA_TRY(cudaMemsetAsync(ptr_out, 0, ((size_t)B + 1) * sizeof(int), st));
+        return GM_OK;
+    }
+    return drn_max_pool(x, dim, cluster, partner, ptr, N, B, n_dev, w.capptr, w.tiles, x_out, ptr_out, newid_out, st);
+}
+
+}  // extern "C"

@@ -1,0 +1,559 @@
+// DynamicReductionNetwork forward on B200 -- /root/reference/model/dynamic_reduction_network.py:81-104
+// with the wrapper of /root/reference/model/net.py:12-37.  The graph operators live in drn_graph.cu / knn.cu; this file has
+// the float stages:
+//   k_drn_node     datanorm * x -> inputnet (11->32->64->64, ELU) -> x0, and the per-node half of the edge MLP's first layer:
+//                  Linear(128->96)(cat[x_i, x_j - x_i]) = A_i + B_j with A = (W1a - W1b) x + b1, B = W1b x  (one [N,192] row)
+//   k_drn_edge     per edge (j -> i): h1 = ELU(A_i + B_j) [96]; h2 = ELU(W2 h1 + b2) [64] -- the NON-separable contraction,
+//                  128-edge tiles against the K-major W2 held in shared memory; per-tile BatchNorm moments over the edge
+//                  rows; per-target running max AND min (BatchNorm is a per-channel affine map, so
+//                  max_j BN(h_j) = BN(max_j h_j) for a non-negative scale and BN(min_j h_j) otherwise)
+//   k_drn_bn       merges the tile moments in a fixed order (train) or reads the running statistics (eval)
+//   k_drn_apply    x_out[i] = BN(max or min), rows that straddle tiles folded from the per-tile head / tail partials
+//   k_drn_head     global max pool per event + output MLP (64->64->32->OD) + softplus / pi(2 sigmoid - 1)
+// No atomics on floats, every reduction in a fixed order: the forward is bit-deterministic run to run.
+#include "common.cuh"
+
+namespace gm {
+
+int knn_search_table(const float *x, int stride, int dim, const int *ptr, int N, int B, int K, int loop, int *nbr, int *deg,
+                     const int *n_dev, cudaStream_t st);
+int drn_to_undirected(const int *rowptr, const int *col, const int *nbr, const int *deg, int K, int N, const int *n_dev,
+                      void *ws, size_t ws_bytes, int *rowptr_out, int *col_out, int *row_out, long long capacity,
+                      long long *ei64, cudaStream_t st);
+int drn_normalized_cut(const float *x, int stride, int dim, const int *rowptr, const int *col, const int *row, int N,
+                       long long capacity, float *w_out, cudaStream_t st);
+int drn_graclus(const int *rowptr, const int *col, const float *weight, const int *ptr, int N, int B, int men,
+                const int *visit, int *cluster, int *partner, cudaStream_t st);
+int drn_max_pool(const float *x, int dim, const int *cluster, const int *partner, const int *ptr, int N, int B,
+                 const int *n_dev, int *scan, int *tiles, float *x_out, int *ptr_out, int *newid_out, cudaStream_t st);
+
+namespace {
+
+constexpr int DH = GM_DRN_HIDDEN;     // 64
+constexpr int DM = GM_DRN_MIDDLE;     // 96
+constexpr int DI = GM_DRN_INPUT;      // 11
+constexpr int AB_W = 2 * DM;          // 192: [A | B] row per node
+constexpr int DT = 128;               // nodes / edges per tile
+constexpr int DTHREADS = 512;
+
+__device__ __forceinline__ int eff_n(int N, const int *n_dev) {
+    if (!n_dev) return N;
+    const int v = *n_dev;
+    return v < 0 ? 0 : (v < N ? v : N);
+}
+
+// global row-major W [O][K] (row pitch ldw) -> shared K-major wT [k * pitch + o0 + o]
+__device__ __forceinline__ void stage_kmajor(const float *__restrict__ W, int O, int K, int ldw, float *__restrict__ wT,
+                                             int pitch, int o0) {
+    for (int t = threadIdx.x; t < O * K; t += blockDim.x) {
+        const int o = t / K, k = t - o * K;
+        wT[k * pitch + o0 + o] = W[(size_t)o * ldw + k];
+    }
+}
+
+struct NodeParams {
+    const float *norm, *w1, *b1, *w2, *b2, *w3, *b3;    // inputnet (INPUTNET only)
+    const float *cw1, *cb1;                             // edge MLP first layer [96,128], [96]
+};
+
+// shared-memory plan (floats)
+constexpr int LD_IN = 13, LD_A = 33, LD_B = 68;
+constexpr int NS_WAB = DH * AB_W, NS_BAB = AB_W, NS_C = DT * LD_B;
+constexpr int NS_W1 = DI * 32, NS_W2 = 32 * DH, NS_W3 = DH * DH, NS_IN = DT * LD_IN, NS_A = DT * LD_A, NS_B = DT * LD_B;
+constexpr size_t NODE_SMEM_BASE = (size_t)(NS_WAB + NS_BAB + NS_C) * 4;
+constexpr size_t NODE_SMEM_FULL = NODE_SMEM_BASE + (size_t)(NS_W1 + 32 + NS_W2 + DH + NS_W3 + DH + 16 + NS_IN + NS_A + NS_B) * 4;
+
+template <bool INPUTNET>
+__global__ void __launch_bounds__(DTHREADS, 1) k_drn_node(const float *__restrict__ x, int x_stride, int N,
+                                                          const int *__restrict__ n_dev, NodeParams p,
+                                                          float *__restrict__ x0_out, float *__restrict__ ab_out) {
+    extern __shared__ __align__(16) float s_node[];
+    float *sWab = s_node, *sbab = sWab + NS_WAB, *sC = sbab + NS_BAB;
+    float *sW1 = sC + NS_C, *sb1 = sW1 + NS_W1, *sW2 = sb1 + 32, *sb2 = sW2 + NS_W2, *sW3 = sb2 + DH, *sb3 = sW3 + NS_W3,
+          *sNorm = sb3 + DH, *sIn = sNorm + 16, *sA = sIn + NS_IN, *sB = sA + NS_A;
+    const int tid = threadIdx.x;
+    // ---- prologue: parameters only (overlaps the predecessor under programmatic dependent launch)
+    for (int t = tid; t < DM * DH; t += DTHREADS) {       // [A | B] weights: (W1a - W1b | W1b), K-major, pitch 192
+        const int o = t / DH, k = t - o * DH;
+        const float wa = p.cw1[(size_t)o * 2 * DH + k], wb = p.cw1[(size_t)o * 2 * DH + DH + k];
+        sWab[k * AB_W + o] = wa - wb;
+        sWab[k * AB_W + DM + o] = wb;
+    }
+    for (int t = tid; t < AB_W; t += DTHREADS) sbab[t] = t < DM ? p.cb1[t] : 0.f;
+    if constexpr (INPUTNET) {
+        stage_kmajor(p.w1, 32, DI, DI, sW1, 32, 0);
+        stage_kmajor(p.w2, DH, 32, 32, sW2, DH, 0);
+        stage_kmajor(p.w3, DH, DH, DH, sW3, DH, 0);
+        if (tid < 32) sb1[tid] = p.b1[tid];
+        if (tid < DH) { sb2[tid] = p.b2[tid]; sb3[tid] = p.b3[tid]; }
+        if (tid < DI) sNorm[tid] = p.norm[tid];
+    }
+    pdl_sync();
+    const int n = eff_n(N, n_dev);
+    const int ng = tid >> 4, og = tid & 15;               // tile product mapping for 64 outputs
+    for (int n0 = blockIdx.x * DT; n0 < n; n0 += gridDim.x * DT) {
+        const int rows = min(DT, n - n0);
+        __syncthreads();                                   // previous tile fully consumed (and the prologue visible)
+        if constexpr (INPUTNET) {
+            for (int t = tid; t < DT * DI; t += DTHREADS) {
+                const int r = t / DI, k = t - r * DI;
+                sIn[r * LD_IN + k] = r < rows ? x[(size_t)(n0 + r) * x_stride + k] * sNorm[k] : 0.f;
+            }
+            __syncthreads();
+            {   // 11 -> 32: thread = (node, 8 outputs)
+                const int node = tid & (DT - 1), o0 = (tid >> 7) * 8;
+                float acc[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] = sb1[o0 + j];
+#pragma unroll
+                for (int k = 0; k < DI; ++k) {
+                    const float v = sIn[node * LD_IN + k];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[j] = fmaf(v, sW1[k * 32 + o0 + j], acc[j]);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sA[node * LD_A + o0 + j] = elu(acc[j]);
+            }
+            __syncthreads();
+            {   // 32 -> 64
+                float acc[4][4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = sb2[4 * og + j];
+                tile_gemm<32, DH, LD_A>(sA, sW2, ng, og, acc);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    *reinterpret_cast<float4 *>(sB + (ng + 32 * i) * LD_B + 4 * og) =
+                        make_float4(elu(acc[i][0]), elu(acc[i][1]), elu(acc[i][2]), elu(acc[i][3]));
+            }
+            __syncthreads();
+            {   // 64 -> 64: x0
+                float acc[4][4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = sb3[4 * og + j];
+                tile_gemm<DH, DH, LD_B>(sB, sW3, ng, og, acc);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int r = ng + 32 * i;
+                    const float4 v = make_float4(elu(acc[i][0]), elu(acc[i][1]), elu(acc[i][2]), elu(acc[i][3]));
+                    *reinterpret_cast<float4 *>(sC + r * LD_B + 4 * og) = v;
+                    if (r < rows) *reinterpret_cast<float4 *>(x0_out + (size_t)(n0 + r) * DH + 4 * og) = v;
+                }
+            }
+        } else {
+            for (int t = tid; t < DT * (DH / 4); t += DTHREADS) {
+                const int r = t >> 4, q = t & 15;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < rows) v = reinterpret_cast<const float4 *>(x + (size_t)(n0 + r) * x_stride)[q];
+                *reinterpret_cast<float4 *>(sC + r * LD_B + 4 * q) = v;
+            }
+        }
+        __syncthreads();
+        // [A | B] = x0 . (W1a - W1b | W1b)^T + (b1 | 0): three 64-column blocks of the 192-wide row
+#pragma unroll 1
+        for (int cb = 0; cb < 3; ++cb) {
+            float acc[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = sbab[DH * cb + 4 * og + j];
+            tile_gemm<DH, DH, LD_B, AB_W>(sC, sWab + DH * cb, ng, og, acc);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = ng + 32 * i;
+                if (r < rows)
+                    *reinterpret_cast<float4 *>(ab_out + (size_t)(n0 + r) * AB_W + DH * cb + 4 * og) =
+                        make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ per-edge MLP
+struct EdgeOut {
+    float *mx, *mn;     // [N,64]  per-target max / min of h2 for rows that lie inside one tile
+    float *bmx, *bmn;   // [2][tiles_cap][64]: 0 = head (the row started in an earlier tile), 1 = tail (continues in the next)
+    float *tmom;        // [tiles_cap][2][64]: per-tile (mean, M2) of h2 over the tile's edge rows
+};
+constexpr int LD_H1 = 100, LD_H2 = 68;
+constexpr int ES_W2 = DM * DH, ES_H = DT * LD_H1, ES_MOM = 8 * DH * 2;
+constexpr size_t EDGE_SMEM = (size_t)(ES_W2 + DH + ES_H + ES_MOM) * 4 + (size_t)(2 * DT + DT + 2 + 8) * 4;
+
+template <bool STATS>
+__global__ void __launch_bounds__(DTHREADS, 2) k_drn_edge(const float *__restrict__ ab, const int *__restrict__ rowptr,
+                                                          const int *__restrict__ row, const int *__restrict__ col, int N,
+                                                          long long capacity, const float *__restrict__ w2,
+                                                          const float *__restrict__ b2, EdgeOut o, int tiles_cap) {
+    extern __shared__ __align__(16) float s_edge[];
+    float *sW2 = s_edge, *sb2 = sW2 + ES_W2, *sH = sb2 + DH, *sMom = sH + ES_H;
+    int *sTgt = reinterpret_cast<int *>(sMom + ES_MOM), *sSrc = sTgt + DT, *sSeg = sSrc + DT, *sCnt = sSeg + DT + 2;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    stage_kmajor(w2, DH, DM, DM, sW2, DH, 0);
+    if (tid < DH) sb2[tid] = b2[tid];
+    pdl_sync();
+    long long E = rowptr[N];
+    if (E > capacity) E = capacity;
+    const int ntiles = (int)((E + DT - 1) / DT);
+    const int ng = tid >> 4, og = tid & 15;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long e0 = (long long)tile * DT;
+        const int ne = (int)min((long long)DT, E - e0);
+        __syncthreads();
+        if (tid < DT) {
+            sTgt[tid] = tid < ne ? row[e0 + tid] : -1;
+            sSrc[tid] = tid < ne ? col[e0 + tid] : -1;
+        }
+        __syncthreads();
+        // h1 = ELU(A_i + B_j): 24 float4 per edge row
+        for (int it = tid; it < DT * (DM / 4); it += DTHREADS) {
+            const int e = it / (DM / 4), q = it - e * (DM / 4);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (e < ne) {
+                const float4 a = reinterpret_cast<const float4 *>(ab + (size_t)sTgt[e] * AB_W)[q];
+                const float4 b = reinterpret_cast<const float4 *>(ab + (size_t)sSrc[e] * AB_W + DM)[q];
+                v = make_float4(elu(a.x + b.x), elu(a.y + b.y), elu(a.z + b.z), elu(a.w + b.w));
+            }
+            *reinterpret_cast<float4 *>(sH + e * LD_H1 + 4 * q) = v;
+        }
+        __syncthreads();
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = sb2[4 * og + j];
+        tile_gemm<DM, DH, LD_H1>(sH, sW2, ng, og, acc);
+        __syncthreads();                                  // h1 fully consumed: the h2 tile reuses its storage
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<float4 *>(sH + (ng + 32 * i) * LD_H2 + 4 * og) =
+                make_float4(elu(acc[i][0]), elu(acc[i][1]), elu(acc[i][2]), elu(acc[i][3]));
+        if (tid < DT) {                                   // segment starts (rows of one target are consecutive)
+            const bool start = tid < ne && (tid == 0 || sTgt[tid] != sTgt[tid - 1]);
+            const unsigned m = __ballot_sync(0xffffffffu, start);
+            if (lane == 0) sCnt[warp] = __popc(m);
+            sSrc[tid] = start ? (int)__popc(m & ((1u << lane) - 1u)) : -1;     // sSrc is free now: rank inside the warp
+        }
+        __syncthreads();
+        if (tid < DT && sSrc[tid] >= 0) {
+            int prefix = 0;
+            for (int w = 0; w < warp; ++w) prefix += sCnt[w];
+            sSeg[prefix + sSrc[tid]] = tid;
+        }
+        const int nseg = sCnt[0] + sCnt[1] + sCnt[2] + sCnt[3];
+        if (tid == 0) sSeg[nseg] = ne;
+        if constexpr (STATS) {                            // per-tile BatchNorm moments, two-pass per 8-row slice
+            const int c = tid & (DH - 1), part = tid >> 6;
+            float s = 0.f;
+            int cnt = 0;
+            for (int r = part; r < ne; r += 8) { s += sH[r * LD_H2 + c]; ++cnt; }
+            const float mean = cnt ? s / (float)cnt : 0.f;
+            float m2 = 0.f;
+            for (int r = part; r < ne; r += 8) { const float d = sH[r * LD_H2 + c] - mean; m2 = fmaf(d, d, m2); }
+            sMom[(part * DH + c) * 2] = mean;
+            sMom[(part * DH + c) * 2 + 1] = m2;
+        }
+        __syncthreads();
+        if constexpr (STATS) {
+            if (tid < DH) {
+                Moments m{0.f, 0.f, 0.f};
+                for (int part = 0; part < 8; ++part) {
+                    const int cnt = part < ne ? (ne - part + 7) / 8 : 0;
+                    m = moments_combine(m, Moments{(float)cnt, sMom[(part * DH + tid) * 2], sMom[(part * DH + tid) * 2 + 1]});
+                }
+                o.tmom[((size_t)tile * 2) * DH + tid] = m.mean;
+                o.tmom[((size_t)tile * 2 + 1) * DH + tid] = m.m2;
+            }
+        }
+        for (int p = tid; p < nseg * DH; p += DTHREADS) {
+            const int s = p >> 6, c = p & (DH - 1);
+            const int r0 = sSeg[s], r1 = sSeg[s + 1];
+            float vmax = -INFINITY, vmin = INFINITY;
+            for (int r = r0; r < r1; ++r) {
+                const float v = sH[r * LD_H2 + c];
+                vmax = fmaxf(vmax, v);
+                vmin = fminf(vmin, v);
+            }
+            const int i = sTgt[r0];
+            const long long a = rowptr[i], b = rowptr[i + 1];
+            if (a < e0) {
+                o.bmx[((size_t)tile) * DH + c] = vmax;
+                o.bmn[((size_t)tile) * DH + c] = vmin;
+            } else if (b > e0 + DT) {
+                o.bmx[((size_t)tiles_cap + tile) * DH + c] = vmax;
+                o.bmn[((size_t)tiles_cap + tile) * DH + c] = vmin;
+            } else {
+                o.mx[(size_t)i * DH + c] = vmax;
+                o.mn[(size_t)i * DH + c] = vmin;
+            }
+        }
+    }
+}
+
+// bnss [4][64] = mean, invstd, gamma, beta of the BatchNorm1d over the edge rows
+__global__ void __launch_bounds__(1024) k_drn_bn(const int *__restrict__ rowptr, int N, long long capacity,
+                                                 const float *__restrict__ tmom, int training, float momentum, float eps,
+                                                 const float *__restrict__ gamma, const float *__restrict__ beta,
+                                                 float *__restrict__ running_mean, float *__restrict__ running_var,
+                                                 long long *__restrict__ nbt, float *__restrict__ bnss) {
+    __shared__ float s_m[16][DH][3];
+    pdl_sync();
+    const int tid = threadIdx.x, c = tid & (DH - 1), part = tid >> 6;
+    long long E = rowptr[N];
+    if (E > capacity) E = capacity;
+    if (training) {
+        const int ntiles = (int)((E + DT - 1) / DT);
+        Moments m{0.f, 0.f, 0.f};
+        for (int t = part; t < ntiles; t += 16) {
+            const int ne = (int)min((long long)DT, E - (long long)t * DT);
+            m = moments_combine(m, Moments{(float)ne, tmom[((size_t)t * 2) * DH + c], tmom[((size_t)t * 2 + 1) * DH + c]});
+        }
+        s_m[part][c][0] = m.n; s_m[part][c][1] = m.mean; s_m[part][c][2] = m.m2;
+    }
+    __syncthreads();
+    if (tid >= DH) return;
+    float mean, invstd;
+    if (training && E > 0) {
+        Moments m{0.f, 0.f, 0.f};
+        for (int q = 0; q < 16; ++q) m = moments_combine(m, Moments{s_m[q][c][0], s_m[q][c][1], s_m[q][c][2]});
+        mean = m.mean;
+        const float var = m.m2 / m.n;
+        invstd = 1.f / sqrtf(var + eps);
+        const float unbiased = m.n > 1.f ? m.m2 / (m.n - 1.f) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+        if (c == 0 && nbt) nbt[0] += 1;
+    } else {
+        mean = running_mean[c];
+        invstd = 1.f / sqrtf(running_var[c] + eps);
+    }
+    bnss[c] = mean; bnss[DH + c] = invstd; bnss[2 * DH + c] = gamma[c]; bnss[3 * DH + c] = beta[c];
+}
+
+__global__ void __launch_bounds__(256) k_drn_apply(const int *__restrict__ rowptr, int N, const int *__restrict__ n_dev,
+                                                   EdgeOut o, int tiles_cap, const float *__restrict__ bnss,
+                                                   float *__restrict__ x_out) {
+    pdl_sync();
+    const int n = eff_n(N, n_dev);
+    const long long total = (long long)n * DH;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(t >> 6), c = (int)(t & (DH - 1));
+        const int a = rowptr[i], b = rowptr[i + 1];
+        float out = 0.f;                                  // no incoming edge: scatter-max leaves 0
+        if (b > a) {
+            const int t0 = a >> 7, t1 = (b - 1) >> 7;
+            float vmax, vmin;
+            if (t0 == t1) {
+                vmax = o.mx[(size_t)i * DH + c];
+                vmin = o.mn[(size_t)i * DH + c];
+            } else {
+                vmax = o.bmx[((size_t)tiles_cap + t0) * DH + c];
+                vmin = o.bmn[((size_t)tiles_cap + t0) * DH + c];
+                for (int q = t0 + 1; q <= t1; ++q) {
+                    vmax = fmaxf(vmax, o.bmx[(size_t)q * DH + c]);
+                    vmin = fminf(vmin, o.bmn[(size_t)q * DH + c]);
+                }
+            }
+            const float g = bnss[2 * DH + c];
+            const float v = g >= 0.f ? vmax : vmin;       // BatchNorm is monotone per channel: max commutes up to the sign
+            out = (v - bnss[c]) * bnss[DH + c] * g + bnss[3 * DH + c];
+        }
+        x_out[t] = out;
+    }
+}
+
+// CTA per event: global max pool over the event's (pooled) nodes, then the output MLP and the wrapper's activations
+struct HeadParams {
+    const float *w1, *b1, *w2, *b2, *w3, *b3;
+    int od;
+};
+__global__ void __launch_bounds__(256) k_drn_head(const float *__restrict__ x, const int *__restrict__ ptr, int B, HeadParams p,
+                                                  float *__restrict__ pooled, float *__restrict__ out,
+                                                  float *__restrict__ net_out) {
+    __shared__ float s_part[4][DH], s_p[DH], s_h1[DH], s_h2[DH / 2], s_o[8];
+    pdl_sync();
+    const int tid = threadIdx.x, c = tid & (DH - 1), part = tid >> 6;
+    for (int e = blockIdx.x; e < B; e += gridDim.x) {
+        const int a = ptr[e], b = ptr[e + 1];
+        float m = -INFINITY;
+        for (int r = a + part; r < b; r += 4) m = fmaxf(m, x[(size_t)r * DH + c]);
+        s_part[part][c] = m;
+        __syncthreads();
+        if (tid < DH) {
+            float v = fmaxf(fmaxf(s_part[0][tid], s_part[1][tid]), fmaxf(s_part[2][tid], s_part[3][tid]));
+            if (b <= a) v = 0.f;
+            s_p[tid] = v;
+            if (pooled) pooled[(size_t)e * DH + tid] = v;
+        }
+        __syncthreads();
+        if (tid < DH) {
+            float acc = p.b1[tid];
+            for (int k = 0; k < DH; ++k) acc = fmaf(p.w1[tid * DH + k], s_p[k], acc);
+            s_h1[tid] = elu(acc);
+        }
+        __syncthreads();
+        if (tid < DH / 2) {
+            float acc = p.b2[tid];
+            for (int k = 0; k < DH; ++k) acc = fmaf(p.w2[tid * DH + k], s_h1[k], acc);
+            s_h2[tid] = elu(acc);
+        }
+        __syncthreads();
+        if (tid < p.od) {
+            float acc = p.b3[tid];
+            for (int k = 0; k < DH / 2; ++k) acc = fmaf(p.w3[tid * (DH / 2) + k], s_h2[k], acc);
+            s_o[tid] = acc;
+            out[(size_t)e * p.od + tid] = acc;
+        }
+        __syncthreads();
+        if (net_out && tid == 0 && p.od == 2) {           // model/net.py:31-36
+            const float o0 = s_o[0], o1 = s_o[1];
+            net_out[2 * e] = o0 > 20.f ? o0 : log1pf(expf(o0));
+            net_out[2 * e + 1] = 3.14159265358979323846f * (2.f * sigmoidf(o1) - 1.f);
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------ workspace
+struct DrnWs {
+    float *x0, *ab, *mx, *mn, *bmx, *bmn, *tmom, *bnss, *x1, *weight1, *x1p, *x2, *pooled;
+    int *nbr, *deg, *rowptr1, *col1, *row1, *cluster1, *partner1, *scan, *scan_tiles, *ptr1p, *rowptr2, *col2, *row2;
+    char *und;
+    size_t und_bytes;
+    long long ecap;
+    int tiles_cap;
+};
+
+size_t drn_layout(int N, int B, int k, char *base, DrnWs *w) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return base ? base + o : (char *)nullptr; };
+    const size_t n = (size_t)(N > 0 ? N : 1), K = (size_t)k + 1;
+    DrnWs t{};
+    t.ecap = (long long)(2 * n * K);
+    t.tiles_cap = (int)(t.ecap / DT + 2);
+    t.x0 = (float *)take(n * DH * 4);
+    t.ab = (float *)take(n * AB_W * 4);
+    t.mx = (float *)take(n * DH * 4);
+    t.mn = (float *)take(n * DH * 4);
+    t.bmx = (float *)take((size_t)2 * t.tiles_cap * DH * 4);
+    t.bmn = (float *)take((size_t)2 * t.tiles_cap * DH * 4);
+    t.tmom = (float *)take((size_t)2 * t.tiles_cap * DH * 4);
+    t.bnss = (float *)take(2 * 4 * DH * 4);
+    t.x1 = (float *)take(n * DH * 4);
+    t.weight1 = (float *)take((size_t)t.ecap * 4);
+    t.x1p = (float *)take(n * DH * 4);
+    t.x2 = (float *)take(n * DH * 4);
+    t.pooled = (float *)take((size_t)(B > 0 ? B : 1) * DH * 4);
+    t.nbr = (int *)take(n * K * 4);
+    t.deg = (int *)take((n + 1) * 4);
+    t.rowptr1 = (int *)take((n + 1) * 4);
+    t.col1 = (int *)take((size_t)t.ecap * 4);
+    t.row1 = (int *)take((size_t)t.ecap * 4);
+    t.cluster1 = (int *)take(n * 4);
+    t.partner1 = (int *)take(n * 4);
+    t.scan = (int *)take((n + 1) * 4);
+    t.scan_tiles = (int *)take(((n + 1) / 1024 + 2) * 4);
+    t.ptr1p = (int *)take((size_t)(B + 2) * 4);
+    t.rowptr2 = (int *)take((n + 1) * 4);
+    t.col2 = (int *)take((size_t)t.ecap * 4);
+    t.row2 = (int *)take((size_t)t.ecap * 4);
+    t.und_bytes = gm_undirected_ws_bytes((int)n, (long long)(n * K));
+    t.und = take(t.und_bytes);
+    if (w) *w = t;
+    return off;
+}
+
+int edge_stage(const DrnWs &w, const GmDrnConv &cv, const int *rowptr, const int *col, const int *row, int N, const int *n_dev,
+               int training, float momentum, float eps, float *bnss, float *x_out, cudaStream_t st) {
+    EdgeOut o{w.mx, w.mn, w.bmx, w.bmn, w.tmom};
+    static bool attr = false;
+    if (!attr) {
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_drn_edge<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EDGE_SMEM));
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_drn_edge<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EDGE_SMEM));
+        attr = true;
+    }
+    const int grid = persistent_grid(w.tiles_cap, 2);
+    if (training) {
+        GM_LAUNCH_PDL(k_drn_edge<true>, grid, DTHREADS, EDGE_SMEM, st, (const float *)w.ab, rowptr, row, col, N, w.ecap,
+                      (const float *)cv.w2, (const float *)cv.b2, o, w.tiles_cap);
+    } else {
+        GM_LAUNCH_PDL(k_drn_edge<false>, grid, DTHREADS, EDGE_SMEM, st, (const float *)w.ab, rowptr, row, col, N, w.ecap,
+                      (const float *)cv.w2, (const float *)cv.b2, o, w.tiles_cap);
+    }
+    GM_LAUNCH_CHECK();
+    GM_LAUNCH_PDL(k_drn_bn, 1, 1024, 0, st, rowptr, N, w.ecap, (const float *)w.tmom, training, momentum, eps,
+                  (const float *)cv.bn_weight, (const float *)cv.bn_bias, cv.bn_running_mean, cv.bn_running_var,
+                  (long long *)cv.bn_num_batches_tracked, bnss);
+    GM_LAUNCH_CHECK();
+    GM_LAUNCH_PDL(k_drn_apply, persistent_grid(((long long)N * DH + 255) / 256, 8), 256, 0, st, rowptr, N, n_dev, o,
+                  w.tiles_cap, (const float *)bnss, x_out);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+}  // namespace
+}  // namespace gm
+
+using namespace gm;
+
+extern "C" {
+
+size_t gm_drn_ws_bytes(int N, int B, int k) { return drn_layout(N < 0 ? 0 : N, B < 0 ? 0 : B, k < 1 ? 1 : k, nullptr, nullptr); }
+
+int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int *ptr, int N, int B,
+                   int max_event_nodes, int training, int precision, float momentum, float eps, void *ws,
+                   size_t ws_bytes, float *out, float *net_out, GmDrnView *view_out, void *stream) {
+    if (!p || !ws || N < 1 || B < 1 || !x || !ptr || !out || x_stride < DI) return GM_ERR_INVALID_ARGUMENT;
+    if (p->k < 1 || p->k + 1 > 32 || p->output_dim < 1 || p->output_dim > 8) return GM_ERR_UNSUPPORTED;
+    if (precision != GM_PREC_FP32) return GM_ERR_UNSUPPORTED;
+    if (net_out && p->output_dim != 2) return GM_ERR_INVALID_ARGUMENT;
+    if (ws_bytes < drn_layout(N, B, p->k, nullptr, nullptr)) return GM_ERR_CAPACITY;
+    cudaStream_t st = as_stream(stream);
+    DrnWs w;
+    drn_layout(N, B, p->k, (char *)ws, &w);
+    const int K = p->k + 1;
+    static bool attr = false;
+    if (!attr) {
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_drn_node<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NODE_SMEM_FULL));
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_drn_node<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NODE_SMEM_BASE));
+        attr = true;
+    }
+    const int node_grid = persistent_grid(((long long)N + DT - 1) / DT, 1);
+    // ---- stage 1 (:82-92)
+    NodeParams np{p->datanorm, p->in_w[0], p->in_b[0], p->in_w[1], p->in_b[1], p->in_w[2], p->in_b[2], p->conv[0].w1, p->conv[0].b1};
+    GM_LAUNCH_PDL(k_drn_node<true>, node_grid, DTHREADS, NODE_SMEM_FULL, st, x, x_stride, N, (const int *)nullptr, np, w.x0, w.ab);
+    GM_LAUNCH_CHECK();
+    GM_TRY(knn_search_table(w.x0, DH, DH, ptr, N, B, K, 0, w.nbr, w.deg, nullptr, st));
+    GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, nullptr, w.und, w.und_bytes, w.rowptr1, w.col1, w.row1,
+                             w.ecap, nullptr, st));
+    GM_TRY(edge_stage(w, p->conv[0], w.rowptr1, w.col1, w.row1, N, nullptr, training, momentum, eps, w.bnss, w.x1, st));
+    GM_TRY(drn_normalized_cut(w.x1, DH, DH, w.rowptr1, w.col1, w.row1, N, w.ecap, w.weight1, st));
+    GM_TRY(drn_graclus(w.rowptr1, w.col1, w.weight1, ptr, N, B, max_event_nodes, nullptr, w.cluster1, w.partner1, st));
+    GM_TRY(drn_max_pool(w.x1, DH, w.cluster1, w.partner1, ptr, N, B, nullptr, w.scan, w.scan_tiles, w.x1p, w.ptr1p, nullptr, st));
+    // ---- stage 2 (:95-96) on the M = ptr1p[B] pooled nodes; M never leaves the device
+    const int *m_dev = w.ptr1p + B;
+    NodeParams np2{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, p->conv[1].w1, p->conv[1].b1};
+    GM_LAUNCH_PDL(k_drn_node<false>, node_grid, DTHREADS, NODE_SMEM_BASE, st, (const float *)w.x1p, DH, N, m_dev, np2,
+                  (float *)nullptr, w.ab);
+    GM_LAUNCH_CHECK();
+    GM_TRY(knn_search_table(w.x1p, DH, DH, w.ptr1p, N, B, K, 0, w.nbr, w.deg, m_dev, st));
+    GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, m_dev, w.und, w.und_bytes, w.rowptr2, w.col2, w.row2,
+                             w.ecap, nullptr, st));
+    GM_TRY(edge_stage(w, p->conv[1], w.rowptr2, w.col2, w.row2, N, m_dev, training, momentum, eps, w.bnss + 4 * DH, w.x2, st));
+    // ---- :98-104: the second clustering cannot change a global maximum; pool per event and run the output MLP
+    HeadParams hp{p->out_w[0], p->out_b[0], p->out_w[1], p->out_b[1], p->out_w[2], p->out_b[2], p->output_dim};
+    GM_LAUNCH_PDL(k_drn_head, B, 256, 0, st, (const float *)w.x2, (const int *)w.ptr1p, B, hp, w.pooled, out, net_out);
+    GM_LAUNCH_CHECK();
+    if (view_out) {
+        GmDrnView v{};
+        v.x0 = w.x0; v.rowptr1 = w.rowptr1; v.col1 = w.col1; v.row1 = w.row1; v.x1 = w.x1; v.weight1 = w.weight1;
+        v.cluster1 = w.cluster1; v.partner1 = w.partner1; v.x1p = w.x1p; v.ptr1p = w.ptr1p; v.rowptr2 = w.rowptr2;
+        v.col2 = w.col2; v.row2 = w.row2; v.x2 = w.x2; v.pooled = w.pooled; v.edge_capacity = w.ecap;
+        *view_out = v;
+    }
+    return GM_OK;
+}
+
+}  // extern "C"

@@ -38,13 +38,16 @@ __device__ __forceinline__ int event_of(const int *__restrict__ ptr, int B, int 
 
 template <int DP, int QPW>
 __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restrict__ x, int stride, int dim,
-                                                            const int *__restrict__ ptr, int N, int B, int K, int loop,
-                                                            int *__restrict__ nbr, int *__restrict__ deg) {
+                                                            const int *__restrict__ ptr, int Ncap, int B, int K, int loop,
+                                                            int *__restrict__ nbr, int *__restrict__ deg,
+                                                            const int *__restrict__ n_dev) {
     constexpr int RS = DP + 4;                       // shared row stride (floats)
     constexpr int QB = KNN_WARPS * QPW;              // queries per CTA
     constexpr int TILE = DP >= 64 ? KNN_TILE / 2 : KNN_TILE;
     __shared__ __align__(16) float s_tile[2][TILE * RS];     // tile t+1 lands (cp.async) while tile t is searched
     pdl_sync();
+    // n_dev (optional): the node count lives on the device (pooled DRN graph); rows beyond it get degree 0
+    const int N = n_dev ? max(0, min(Ncap, *n_dev)) : Ncap;
     // 16-byte asynchronous copies when rows are whole float4s; otherwise element-wise with zero padding up to DP
     const bool vec = dim == DP && (stride & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
     auto load_tile = [&](int buf, int t0, int rows) {
@@ -144,7 +147,7 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
             if (lane == 0) deg[qi[u]] = n;
         }
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) deg[N] = 0;
+    for (int i = N + blockIdx.x * KNN_THREADS + threadIdx.x; i <= Ncap; i += gridDim.x * KNN_THREADS) deg[i] = 0;
 }
 
 __global__ void __launch_bounds__(256) k_knn_fill(const int *__restrict__ nbr, const int *__restrict__ rowptr, int N, int K,
@@ -186,15 +189,26 @@ namespace {
 
 template <int DP, int QPW>
 int launch_search(const float *x, int stride, int dim, const int *ptr, int N, int B, int K, int loop, int *nbr, int *deg,
-                  cudaStream_t st) {
+                  const int *n_dev, cudaStream_t st) {
     const int qb = KNN_WARPS * QPW;
     const int grid = persistent_grid(((long long)N + qb - 1) / qb, 16);
-    GM_LAUNCH_PDL((k_knn_search<DP, QPW>), grid, KNN_THREADS, 0, st, x, stride, dim, ptr, N, B, K, loop, nbr, deg);
+    GM_LAUNCH_PDL((k_knn_search<DP, QPW>), grid, KNN_THREADS, 0, st, x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
 
 }  // namespace
+
+// the search alone (padded neighbour table nbr [N,K] + deg [N+1], no scan): what the fused DRN forward consumes
+int knn_search_table(const float *x, int stride, int dim, const int *ptr, int N, int B, int K, int loop, int *nbr, int *deg,
+                     const int *n_dev, cudaStream_t st) {
+    if (dim <= 4) return launch_search<4, 4>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
+    if (dim <= 8) return launch_search<8, 4>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
+    if (dim <= 16) return launch_search<16, 2>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
+    if (dim <= 32) return launch_search<32, 2>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
+    return launch_search<64, 1>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
+}
+
 }  // namespace gm
 
 using namespace gm;
@@ -219,13 +233,7 @@ int gm_knn_graph_count(const float *x, int x_stride, int dim, const int *ptr, in
     }
     KnnWs w;
     knn_layout(N, K, (char *)ws, &w);
-    int rc;
-    if (dim <= 4) rc = launch_search<4, 4>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
-    else if (dim <= 8) rc = launch_search<8, 4>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
-    else if (dim <= 16) rc = launch_search<16, 2>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
-    else if (dim <= 32) rc = launch_search<32, 2>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
-    else rc = launch_search<64, 1>(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, st);
-    GM_TRY(rc);
+    GM_TRY(knn_search_table(x, x_stride, dim, ptr, N, B, K, loop, w.nbr, rowptr_out, nullptr, st));
     GM_TRY(exclusive_scan_inplace(rowptr_out, N + 1, w.tiles, nullptr, st));
     return GM_OK;
 }

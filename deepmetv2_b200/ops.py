@@ -310,3 +310,86 @@ def scatter_add(src, index, dim=-1, out=None, dim_size=None):
         out = torch.zeros(dim_size, dtype=torch.float32, device=src.device)
     check(l.gm_scatter_add(ptr(src), ptr(index), src.numel(), ptr(out), dim_size, stream()), "gm_scatter_add")
     return out
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# DynamicReductionNetwork graph operators (row f1): drop-ins for the upstream calls at
+# model/dynamic_reduction_network.py:27-30,86-100
+# ----------------------------------------------------------------------------------------------------------------------
+def to_undirected(edge_index: torch.Tensor, num_nodes: int | None = None):
+    """Drop-in for ``torch_geometric.utils.to_undirected``: both directions of every edge, sorted by (row, col),
+    duplicates removed.  LongTensor[2,E'] carrying its int32 CSR (``._gm_csr``, plus ``._gm_row``)."""
+    _lib.require_cuda(edge_index, "edge_index")
+    if num_nodes is None:
+        num_nodes = int(edge_index.max().item()) + 1 if edge_index.numel() else 0
+    csr = csr_from_edge_index(edge_index, num_nodes)
+    N, dev = num_nodes, edge_index.device
+    E = edge_index.shape[1]
+    l = lib()
+    ws = torch.empty(l.gm_undirected_ws_bytes(N, max(E, 1)), dtype=torch.uint8, device=dev)
+    cap = max(2 * E, 1)
+    rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+    col = torch.empty(cap, dtype=torch.int32, device=dev)
+    row = torch.empty(cap, dtype=torch.int32, device=dev)
+    ei = torch.empty(2, cap, dtype=torch.int64, device=dev)
+    check(l.gm_csr_to_undirected(ptr(csr.rowptr), ptr(csr.col), None, None, 0, N, None, ptr(ws), ws.numel(), ptr(rowptr),
+                                 ptr(col), ptr(row), cap, ptr(ei), stream()), "gm_csr_to_undirected")
+    Eu = int(rowptr[-1].item()) if N else 0       # one D2H sync, like upstream's unique()
+    out = EdgeIndex.wrap(ei[:, :Eu].contiguous(), GraphCSR(rowptr, col[:max(Eu, 1)], N, Eu, -1, 0))
+    out._gm_row = row[:max(Eu, 1)]
+    return out
+
+
+def normalized_cut_2d(edge_index: torch.Tensor, pos: torch.Tensor) -> torch.Tensor:
+    """model/dynamic_reduction_network.py:27-30 (``torch.norm(pos[row] - pos[col])`` then upstream ``normalized_cut``).
+    ``edge_index`` must come from :func:`to_undirected` (sorted by row; in-degree == row length)."""
+    _lib.require_cuda(pos, "pos")
+    csr, row = getattr(edge_index, "_gm_csr", None), getattr(edge_index, "_gm_row", None)
+    if csr is None or row is None:
+        raise NotImplementedError("normalized_cut_2d takes the edge_index returned by ops.to_undirected")
+    pos = pos.contiguous().float()
+    E = csr.num_edges
+    w = torch.empty(max(E, 1), dtype=torch.float32, device=pos.device)
+    check(lib().gm_normalized_cut(ptr(pos), pos.stride(0), pos.shape[1], ptr(csr.rowptr), ptr(csr.col), ptr(row),
+                                  csr.num_nodes, E, ptr(w), stream()), "gm_normalized_cut")
+    return w[:E]
+
+
+def graclus(edge_index: torch.Tensor, weight: torch.Tensor | None = None, num_nodes: int | None = None,
+            ptr_i32: torch.Tensor | None = None, node_perm: torch.Tensor | None = None, return_partner: bool = False):
+    """Drop-in for ``torch_cluster.graclus`` (the CPU algorithm, deterministic visiting order): LongTensor[num_nodes] of
+    cluster ids.  ``ptr_i32`` (event boundaries) lets events be matched in parallel (they are independent components);
+    ``node_perm`` = visiting order grouped by event (upstream draws a random permutation; default ascending index)."""
+    csr = getattr(edge_index, "_gm_csr", None)
+    if csr is None:
+        raise NotImplementedError("graclus takes the edge_index returned by ops.to_undirected")
+    N = csr.num_nodes if num_nodes is None else num_nodes
+    dev = edge_index.device
+    if ptr_i32 is None:
+        ptr_i32 = torch.tensor([0, N], dtype=torch.int32, device=dev)
+    men = int((ptr_i32[1:] - ptr_i32[:-1]).max().item())
+    cluster = torch.empty(N, dtype=torch.int32, device=dev)
+    partner = torch.empty(N, dtype=torch.int32, device=dev)
+    visit = None if node_perm is None else node_perm.to(torch.int32).contiguous()
+    wt = None if weight is None else weight.contiguous().float()
+    check(lib().gm_graclus(ptr(csr.rowptr), ptr(csr.col), ptr(wt), ptr(ptr_i32), N, ptr_i32.numel() - 1, men, ptr(visit),
+                           ptr(cluster), ptr(partner), stream()), "gm_graclus")
+    return (cluster.long(), partner) if return_partner else cluster.long()
+
+
+def cluster_max_pool(x: torch.Tensor, cluster: torch.Tensor, partner: torch.Tensor, ptr_i32: torch.Tensor):
+    """``torch_geometric.nn.max_pool_x`` for the clusters of :func:`graclus` (size <= 2): returns (x_pooled [M,D],
+    ptr_pooled [B+1] int32, consecutive cluster id per node [N] int32).  One D2H sync for M."""
+    _lib.require_cuda(x, "x")
+    x = x.contiguous().float()
+    N, D = x.shape
+    B = ptr_i32.numel() - 1
+    l, dev = lib(), x.device
+    ws = torch.empty(l.gm_undirected_ws_bytes(N, 0), dtype=torch.uint8, device=dev)
+    xo = torch.empty(N, D, dtype=torch.float32, device=dev)
+    po = torch.empty(B + 1, dtype=torch.int32, device=dev)
+    newid = torch.empty(N, dtype=torch.int32, device=dev)
+    check(l.gm_cluster_max_pool(ptr(x), D, ptr(cluster.to(torch.int32).contiguous()), ptr(partner), ptr(ptr_i32), N, B, None,
+                                ptr(ws), ws.numel(), ptr(xo), ptr(po), ptr(newid), stream()), "gm_cluster_max_pool")
+    M = int(po[-1].item())
+    return xo[:M], po, newid

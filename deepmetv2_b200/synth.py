@@ -23,6 +23,8 @@ SHAPES = {
     "dytt": (1700.0, 250.0, 800, 3000, (2, 6)),
     "highpu": (5000.0, 500.0, 3000, 7000, (4, 6)),
     "tiny": (40.0, 10.0, 8, 80, (1, 2)),
+    # Z -> nu nu (BASELINE config 4, the DRN variant): DY-like pile-up multiplicity, fewer hard jets (recoil only)
+    "znunu": (1700.0, 250.0, 800, 3000, (1, 3)),
 }
 
 _PDG_VALUES = np.array([211, -211, 130, 22, 11, -11, 13, -13, 1, 2], dtype=np.float32)

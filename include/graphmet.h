@@ -365,6 +365,88 @@ int gm_allreduce_adamw_step(float *params, const float *grads, float *exp_avg, f
                             float *global_loss_out, const int *err_flags_dev, const int *graph_stats_dev,
                             int *status_host, void *stream);
 
+/* ---------------------------------------------------------------------------------
+ * f1. DynamicReductionNetwork variant (model/dynamic_reduction_network.py:32-103; wrapper sketched at
+ *     model/net.py:12-37: input_dim 11, hidden 64, k 8, output_dim 2, aggr 'max').
+ *
+ * Graph operators (drop-ins for the upstream calls at dynamic_reduction_network.py:86-102), all on int32 CSR by
+ * row with ascending columns; n_dev (optional device int) overrides N with min(N, *n_dev) so a pooled graph
+ * whose size only exists on the device needs no host synchronisation.
+ *
+ *   gm_csr_to_undirected  <- torch_geometric.utils.to_undirected (:86,95): rows i of (rowptr, col) list the
+ *       sources j of directed edges j -> i; the result holds every pair in both directions, sorted by (row, col),
+ *       duplicates removed.  rowptr_out [N+1] (rowptr_out[N] = E on the device), col_out / row_out [capacity]
+ *       (COO row of every entry), optional int64 edge_index[2,capacity] (row 0 = row, row 1 = col); capacity >= 2 x the
+ *       number of directed edges, ws >= gm_undirected_ws_bytes(N, directed edges).
+ *       Also accepts the padded neighbour table of gm_knn_graph_count instead of a CSR: nbr [N,K], deg [N].
+ *   gm_normalized_cut     <- normalized_cut_2d (:27-30) + torch_geometric.utils.normalized_cut:
+ *       w_e = ||x[row] - x[col]||_2 * (1/deg[row] + 1/deg[col]).
+ *   gm_graclus            <- torch_cluster.graclus (:90,99), the CPU algorithm: per event, nodes visited in `visit`
+ *       order (NULL = ascending index; upstream draws a random permutation), an unmatched node takes its
+ *       unmatched neighbour of largest weight >= 0 (ties: the later entry of the row); cluster id = the smaller
+ *       index of the pair.  cluster_out [N]; partner_out [N] (optional): the other member or -1.
+ *   gm_cluster_max_pool   <- torch_geometric.nn.max_pool / max_pool_x (:92,100) for clusters of <= 2 nodes given
+ *       as (cluster, partner): consecutive cluster ids in ascending order of the cluster's smallest member,
+ *       x_out[c] = max over members, ptr_out [B+1] = pooled event boundaries (ptr_out[B] = M on the device),
+ *       newid_out [N] (optional) = consecutive cluster id per input node.  scan_ws: gm_undirected_ws_bytes(N, 0).
+ * --------------------------------------------------------------------------------- */
+size_t gm_undirected_ws_bytes(int N, long long E_directed_capacity);
+int gm_csr_to_undirected(const int *rowptr, const int *col, const int *nbr, const int *deg, int K, int N,
+                         const int *n_dev, void *ws, size_t ws_bytes, int *rowptr_out, int *col_out, int *row_out,
+                         long long capacity, int64_t *edge_index64_out, void *stream);
+int gm_normalized_cut(const float *x, int x_stride, int dim, const int *rowptr, const int *col, const int *row,
+                      int N, long long capacity, float *weight_out, void *stream);
+int gm_graclus(const int *rowptr, const int *col, const float *weight, const int *ptr, int N, int B,
+               int max_event_nodes, const int *visit, int *cluster_out, int *partner_out, void *stream);
+int gm_cluster_max_pool(const float *x, int dim, const int *cluster, const int *partner, const int *ptr, int N,
+                        int B, const int *n_dev, void *scan_ws, size_t scan_ws_bytes, float *x_out, int *ptr_out,
+                        int *newid_out, void *stream);
+
+#define GM_DRN_HIDDEN 64
+#define GM_DRN_MIDDLE 96
+#define GM_DRN_INPUT 11
+typedef struct GmDrnConv {
+    float *w1, *b1;              /* [96,128],[96]  drn.edgeconvL.nn.0.{weight,bias}: acts on cat[x_i, x_j - x_i] */
+    float *w2, *b2;              /* [64,96],[64]   drn.edgeconvL.nn.2.{weight,bias} */
+    float *bn_weight, *bn_bias;  /* [64]           drn.edgeconvL.nn.4.{weight,bias}: BatchNorm1d over the E edge rows */
+    float *bn_running_mean, *bn_running_var;       /* [64] */
+    int64_t *bn_num_batches_tracked;               /* [1] or NULL */
+} GmDrnConv;
+typedef struct GmDrnParams {
+    float *datanorm;             /* [11]  drn.datanorm */
+    float *in_w[3], *in_b[3];    /* drn.inputnet.{0,2,4}: [32,11],[64,32],[64,64] + biases */
+    GmDrnConv conv[2];           /* drn.edgeconv1 / drn.edgeconv2 */
+    float *out_w[3], *out_b[3];  /* drn.output.{0,2,4}: [64,64],[32,64],[output_dim,32] + biases */
+    int output_dim;              /* <= 8 (2 for the wrapper) */
+    int k;                       /* neighbours per node (8) */
+} GmDrnParams;
+/* Device pointers into the workspace of the last gm_drn_forward (for stage-wise parity tests and the backward). */
+typedef struct GmDrnView {
+    float *x0;                   /* [N,64]   inputnet output */
+    int *rowptr1, *col1, *row1;  /* undirected kNN graph of stage 1 (rowptr1[N] = E1) */
+    float *x1;                   /* [N,64]   edgeconv1 output */
+    float *weight1;              /* [E1]     normalized cut */
+    int *cluster1, *partner1;    /* [N] */
+    float *x1p;                  /* [M,64]   pooled */
+    int *ptr1p;                  /* [B+1]    pooled event boundaries (ptr1p[B] = M) */
+    int *rowptr2, *col2, *row2;  /* stage 2 graph over the M pooled nodes (rowptr2[N] = E2) */
+    float *x2;                   /* [M,64]   edgeconv2 output */
+    float *pooled;               /* [B,64]   global max pool */
+    long long edge_capacity;     /* capacity of col / row / weight arrays */
+} GmDrnView;
+size_t gm_drn_ws_bytes(int N, int B, int k);
+/* Whole forward, no host synchronisation: datanorm, inputnet, then twice (kNN graph in the 64-d latent space ->
+ * to_undirected -> EdgeConv(Linear 128->96, ELU, Linear 96->64, ELU, BatchNorm over edges; max) -> [stage 1 only:
+ * normalized cut -> graclus -> max_pool]), global max pool, output MLP.  The second normalized_cut / graclus /
+ * max_pool_x (:98-100) does not influence the output (global_max_pool of per-cluster maxima is the per-event
+ * maximum) and is not run.  training: 1 = BatchNorm batch statistics over the E edge rows + running-stat update.
+ * out [B, output_dim] = drn(data); net_out (optional, [B,2], output_dim == 2): softplus(out[:,0]),
+ * pi * (2 sigmoid(out[:,1]) - 1) (model/net.py:31-36).  precision: GM_PREC_FP32 or GM_PREC_BF16 / GM_PREC_TF32
+ * (the 96 -> 64 per-edge contraction on tcgen05). */
+int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int *ptr, int N, int B,
+                   int max_event_nodes, int training, int precision, float momentum, float eps, void *ws,
+                   size_t ws_bytes, float *out, float *net_out, GmDrnView *view_out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
