@@ -26,7 +26,8 @@ MAX_CONV_DEPTH = 4
 AGGR = {"max": 0, "add": 1, "mean": 2}
 PRECISION = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3, "fp32_direct": 4}
 TIMERS = {"radius_graph": 0, "encode_fwd": 1, "edgeconv_fwd": 2, "head_fwd": 3, "scatter_s_bwd": 4,
-          "conv_node_bwd": 5, "encode_bwd": 6, "bn": 7, "node_prep": 8, "head_bwd": 9}
+          "conv_node_bwd": 5, "encode_bwd": 6, "bn": 7, "node_prep": 8, "head_bwd": 9,
+          "drn_node": 10, "drn_knn": 11, "drn_graph": 12, "drn_edge": 13, "drn_pool": 14}
 
 _vp, _i, _ll, _f, _d, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double, C.c_size_t
 
@@ -73,6 +74,7 @@ SIGNATURES = {
     "gm_timing_read": (_i, [_i, _vp, _vp]),
     "gm_bench_smem_read": (_i, [_i, _vp, _vp]),
     "gm_bench_ffma": (_i, [_i, _vp, _vp]),
+    "gm_bench_ffma2": (_i, [_i, _vp, _vp]),
     "gm_prepare_etaphi": (_i, [_vp, _i, _i, _vp, _vp]),
     "gm_batch_to_ptr": (_i, [_vp, _i, _i, _vp, _vp]),
     "gm_radius_graph_ws_bytes": (_sz, [_i, _i]),

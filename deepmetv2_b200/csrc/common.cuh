@@ -112,6 +112,24 @@ struct StepStatus {
     }
 };
 
+// Packed fp32x2 arithmetic (sm_100: FFMA2 / FADD2 -- one instruction, two IEEE round-to-nearest results, bit-identical
+// to the scalar fmaf / subtraction on each half).
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;"
+        : "=l"(d)
+        : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)),
+          "l"(*reinterpret_cast<unsigned long long *>(&c)));
+    return *reinterpret_cast<float2 *>(&d);
+}
+__device__ __forceinline__ float2 fsub2(float2 a, float2 b) {
+    unsigned long long d;
+    asm("sub.rn.f32x2 %0, %1, %2;"
+        : "=l"(d)
+        : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)));
+    return *reinterpret_cast<float2 *>(&d);
+}
+
 __device__ __forceinline__ float elu(float v) { return v > 0.f ? v : expm1f(v); }
 // derivative of ELU expressed through its OUTPUT a = elu(z): z>0 -> 1, else a + 1
 __device__ __forceinline__ float elu_grad_from_out(float a) { return a > 0.f ? 1.f : a + 1.f; }

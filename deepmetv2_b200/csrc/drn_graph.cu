@@ -175,94 +175,155 @@ __global__ void __launch_bounds__(256) k_normalized_cut(const float *__restrict_
 }
 
 // ------------------------------------------------------------------------------------------ graclus
-// One warp per event (the matching is sequential in visiting order by definition; events are independent
-// components).  The matched state lives in shared memory; the rows of the next 32 visited nodes are staged into
-// shared memory with independent loads, so the sequential phase never waits on L2.
-constexpr int GR_BUF = 2048;      // staged row entries per block of 32 visited nodes
+// One warp per event (the matching is sequential in visiting order by definition; events are independent components).
+// Per block of 32 visited nodes: (1) the block's rows are staged into shared memory with independent loads (the loads
+// of the NEXT block are issued before the current block is committed, so their latency is hidden); (2) every lane
+// picks the best unmatched neighbour of ITS node from the state at block start -- the sequential answer unless that
+// neighbour gets matched by an earlier node of the same block (matching OTHER neighbours only removes candidates that
+// were not the maximum); (3) a short commit loop walks the 32 nodes in order and re-evaluates just those.
+constexpr int GR_BUF = 768;       // staged row entries per block of 32 visited nodes (per buffer)
+constexpr int GR_TRIPS = 6;       // register-held prefetch: 32 * 4 * GR_TRIPS entries
+
+struct GrBlock {                   // lane-held description of a block of 32 visited nodes
+    int u, ra, len, off, total;
+};
+
+__device__ __forceinline__ GrBlock gr_describe(const int *__restrict__ rowptr, const int *__restrict__ visit, int base, int n,
+                                               int n0, int lane) {
+    GrBlock b;
+    const int pos = n0 + lane;
+    b.u = pos < n ? (visit ? visit[base + pos] : base + pos) : -1;
+    b.ra = b.u >= 0 ? rowptr[b.u] : 0;
+    b.len = b.u >= 0 ? rowptr[b.u + 1] - b.ra : 0;
+    b.off = warp_excl_scan_int(b.len, lane, b.total);
+    return b;
+}
+
+// entry t of the block -> global position in col / weight (search over the scanned row lengths)
+__device__ __forceinline__ int gr_source(const GrBlock &b, int t) {
+    int lo = 0;                                            // last q with off[q] <= t
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+        const int probe = __shfl_sync(0xffffffffu, b.off, lo + step);
+        if (probe <= t) lo += step;
+    }
+    const int a = __shfl_sync(0xffffffffu, b.ra, lo), o = __shfl_sync(0xffffffffu, b.off, lo);
+    return a + t - o;
+}
+
+// best admissible entry of row [o, o + l) of the staged (or global) lists for node u: returns the neighbour or u
+__device__ __forceinline__ int gr_choose(const int *__restrict__ cols, const float *__restrict__ ws, bool weighted, int o, int l,
+                                         int u, int base, int n, const int *__restrict__ state) {
+    unsigned bkey = 0u;
+    int bv = u;
+    for (int t = 0; t < l; ++t) {
+        const int v = cols[o + t];
+        const int lv = v - base;
+        if (v == u || lv < 0 || lv >= n) continue;
+        unsigned key;
+        if (weighted) {
+            const float w = ws[o + t];
+            if (!(w >= 0.f)) continue;
+            key = __float_as_uint(w + 0.f) + 1u;           // weights >= 0 order like unsigned integers
+        } else {
+            key = 1u;
+        }
+        if (state[lv] >= 0) continue;
+        // weighted: largest weight, ties to the LATER entry; unweighted: the first unmatched entry
+        if (weighted ? key >= bkey : bkey == 0u) { bkey = key; bv = v; }
+    }
+    return bv;
+}
 
 __global__ void __launch_bounds__(32) k_graclus(const int *__restrict__ rowptr, const int *__restrict__ col,
                                                 const float *__restrict__ weight, const int *__restrict__ ptr, int B,
                                                 const int *__restrict__ visit, int state_cap, int *__restrict__ cluster,
                                                 int *__restrict__ partner) {
     extern __shared__ int s_gr[];
-    int *s_col = s_gr;
-    float *s_w = reinterpret_cast<float *>(s_gr + GR_BUF);
-    int *s_state = s_gr + 2 * GR_BUF;       // [state_cap] cluster id or -1
+    int *s_col = s_gr;                                     // [GR_BUF]
+    float *s_w = reinterpret_cast<float *>(s_gr + GR_BUF); // [GR_BUF]
+    int *s_state = s_gr + 2 * GR_BUF;                      // [state_cap] cluster id or -1
     pdl_sync();
     const int lane = threadIdx.x;
+    const bool weighted = weight != nullptr;
     for (int e = blockIdx.x; e < B; e += gridDim.x) {
         const int base = ptr[e], n = ptr[e + 1] - base;
         if (n <= 0) continue;
-        const bool in_smem = n <= state_cap;
-        volatile int *g_state = cluster + base;                     // slow path: the output array is the state
+        // the matched state: shared memory when the event fits, else the output array itself (slow, still exact)
+        int *state = n <= state_cap ? s_state : cluster + base;
+        for (int l = lane; l < n; l += 32) state[l] = -1;
+        __syncwarp();
+        GrBlock cur = gr_describe(rowptr, visit, base, n, 0, lane);
+        int pc[4 * GR_TRIPS];
+        float pw[4 * GR_TRIPS];
+        auto prefetch = [&](const GrBlock &b) {            // independent loads into registers
+            if (b.total > GR_BUF || b.total > 128 * GR_TRIPS) return;
+#pragma unroll
+            for (int i = 0; i < 4 * GR_TRIPS; ++i) {
+                const int t = 32 * i + lane;
+                if (32 * i < b.total) {                    // warp-uniform
+                    // ascending visiting order: the rows of 32 consecutive nodes are one contiguous range of the CSR
+                    const int src = visit ? gr_source(b, t) : __shfl_sync(0xffffffffu, b.ra, 0) + t;
+                    const bool live = t < b.total;
+                    pc[i] = live ? col[src] : 0;
+                    pw[i] = (live && weighted) ? weight[src] : 0.f;
+                }
+            }
+        };
+        prefetch(cur);
+        for (int n0 = 0; n0 < n; n0 += 32) {
+            const int cnt = min(32, n - n0);
+            const bool staged = cur.total <= GR_BUF && cur.total <= 128 * GR_TRIPS;
+            if (staged) {
+#pragma unroll
+                for (int i = 0; i < 4 * GR_TRIPS; ++i) {
+                    const int t = 32 * i + lane;
+                    if (t < cur.total) { s_col[t] = pc[i]; s_w[t] = pw[i]; }
+                }
+            }
+            __syncwarp();
+            const int *cols = staged ? s_col : col;
+            const float *ws = staged ? s_w : weight;
+            const int row_o = staged ? cur.off : cur.ra;
+            // (2) speculative choice from the state at block start, every lane for its own node
+            int vsel = cur.u;
+            if (cur.u >= 0 && state[cur.u - base] < 0)
+                vsel = gr_choose(cols, ws, weighted, row_o, cur.len, cur.u, base, n, state);
+            // next block: describe it and put its loads in flight before the sequential part
+            GrBlock nxt = cur;
+            if (n0 + 32 < n) {
+                nxt = gr_describe(rowptr, visit, base, n, n0 + 32, lane);
+                prefetch(nxt);
+            }
+            // (3) commit in visiting order
+            for (int q = 0; q < cnt; ++q) {
+                const int u = __shfl_sync(0xffffffffu, cur.u, q);
+                int v = __shfl_sync(0xffffffffu, vsel, q);
+                if (state[u - base] >= 0) continue;                               // matched earlier in this block
+                if (v != u && state[v - base] >= 0) {                             // the chosen neighbour was taken: redo
+                    const int o = __shfl_sync(0xffffffffu, row_o, q), l = __shfl_sync(0xffffffffu, cur.len, q);
+                    v = gr_choose(cols, ws, weighted, o, l, u, base, n, state);   // every lane computes the same answer
+                }
+                const int c = min(u, v);
+                if (lane == 0) { state[u - base] = c; state[v - base] = c; }      // shared memory only: no global store
+                __syncwarp();                                                     // sits between two dependent steps
+            }
+            __syncwarp();
+            cur = nxt;
+        }
+        // write-out: cluster ids, and the partner derived from them (the non-representative member names both)
         for (int l = lane; l < n; l += 32) {
-            if (in_smem) s_state[l] = -1; else g_state[l] = -1;
+            if (state != cluster + base) cluster[base + l] = state[l];
+            if (partner) partner[base + l] = -1;
         }
         __syncwarp();
-        for (int n0 = 0; n0 < n; n0 += 32) {
-            const int pos = n0 + lane;
-            const int u_l = pos < n ? (visit ? visit[base + pos] : base + pos) : -1;
-            const int ra = u_l >= 0 ? rowptr[u_l] : 0;
-            const int len_l = u_l >= 0 ? rowptr[u_l + 1] - ra : 0;
-            int total;
-            const int off_l = warp_excl_scan_int(len_l, lane, total);
-            const bool staged = total <= GR_BUF;
-            const int cnt = min(32, n - n0);
-            if (staged) {
-                for (int q = 0; q < cnt; ++q) {
-                    const int a = __shfl_sync(0xffffffffu, ra, q), l = __shfl_sync(0xffffffffu, len_l, q),
-                              o = __shfl_sync(0xffffffffu, off_l, q);
-                    for (int t = lane; t < l; t += 32) {
-                        s_col[o + t] = col[a + t];
-                        s_w[o + t] = weight ? weight[a + t] : 0.f;
-                    }
-                }
+        if (partner) {
+            for (int l = lane; l < n; l += 32) {
+                const int c = state[l];
+                if (c != base + l) { partner[base + l] = c; partner[c] = base + l; }
             }
-            __syncwarp();
-            for (int q = 0; q < cnt; ++q) {
-                const int u = __shfl_sync(0xffffffffu, u_l, q);
-                const int su = in_smem ? s_state[u - base] : g_state[u - base];
-                if (su >= 0) continue;                               // warp-uniform
-                const int a = __shfl_sync(0xffffffffu, ra, q), l = __shfl_sync(0xffffffffu, len_l, q),
-                          o = __shfl_sync(0xffffffffu, off_l, q);
-                float bw = -1.f;
-                int bt = -1, bv = u;
-                for (int t0 = 0; t0 < l; t0 += 32) {
-                    const int t = t0 + lane;
-                    if (t < l) {
-                        const int v = staged ? s_col[o + t] : col[a + t];
-                        const float w = staged ? s_w[o + t] : (weight ? weight[a + t] : 0.f);
-                        const int lv = v - base;
-                        bool ok = v != u && lv >= 0 && lv < n && w >= 0.f;
-                        if (ok) ok = (in_smem ? s_state[lv] : g_state[lv]) < 0;
-                        // weighted: largest weight, ties to the later entry; unweighted: the first unmatched entry
-                        if (ok && (weight ? (w >= bw) : (bt < 0))) { bw = w; bt = t; bv = v; }
-                    }
-                }
-#pragma unroll
-                for (int s = 16; s > 0; s >>= 1) {
-                    const float ow = __shfl_xor_sync(0xffffffffu, bw, s);
-                    const int ot = __shfl_xor_sync(0xffffffffu, bt, s), ov = __shfl_xor_sync(0xffffffffu, bv, s);
-                    bool take;
-                    if (weight) take = ot >= 0 && (bt < 0 || ow > bw || (ow == bw && ot > bt));
-                    else take = ot >= 0 && (bt < 0 || ot < bt);
-                    if (take) { bw = ow; bt = ot; bv = ov; }
-                }
-                const int vmax = bt >= 0 ? bv : u;
-                const int c = min(u, vmax);
-                if (lane == 0) {
-                    if (in_smem) { s_state[u - base] = c; s_state[vmax - base] = c; }
-                    else { g_state[u - base] = c; g_state[vmax - base] = c; }
-                    cluster[u] = c; cluster[vmax] = c;
-                    if (partner) {
-                        if (vmax == u) partner[u] = -1;
-                        else { partner[u] = vmax; partner[vmax] = u; }
-                    }
-                }
-                __syncwarp();
-            }
-            __syncwarp();
         }
+        __syncwarp();
     }
 }
 

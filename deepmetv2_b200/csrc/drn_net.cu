@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(DTHREADS, 1) k_drn_node(const float *__restric
 struct EdgeOut {
     float *mx, *mn;     // [N,64]  per-target max / min of h2 for rows that lie inside one tile
     float *bmx, *bmn;   // [2][tiles_cap][64]: 0 = head (the row started in an earlier tile), 1 = tail (continues in the next)
-    float *tmom;        // [tiles_cap][2][64]: per-tile (mean, M2) of h2 over the tile's edge rows
+    float *tmom;        // [grid][3][64]: per-CTA (n, mean, M2) of h2 over the edge rows of the CTA's tiles
 };
 constexpr int LD_H1 = 100, LD_H2 = 68;
 constexpr int ES_W2 = DM * DH, ES_H = DT * LD_H1, ES_MOM = 8 * DH * 2;
@@ -198,6 +198,7 @@ __global__ void __launch_bounds__(DTHREADS, 2) k_drn_edge(const float *__restric
     if (E > capacity) E = capacity;
     const int ntiles = (int)((E + DT - 1) / DT);
     const int ng = tid >> 4, og = tid & 15;
+    Moments cta_m{0.f, 0.f, 0.f};                         // threads < 64: channel tid over this CTA's tiles, fixed order
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const long long e0 = (long long)tile * DT;
         const int ne = (int)min((long long)DT, E - e0);
@@ -263,8 +264,7 @@ __global__ void __launch_bounds__(DTHREADS, 2) k_drn_edge(const float *__restric
                     const int cnt = part < ne ? (ne - part + 7) / 8 : 0;
                     m = moments_combine(m, Moments{(float)cnt, sMom[(part * DH + tid) * 2], sMom[(part * DH + tid) * 2 + 1]});
                 }
-                o.tmom[((size_t)tile * 2) * DH + tid] = m.mean;
-                o.tmom[((size_t)tile * 2 + 1) * DH + tid] = m.m2;
+                cta_m = moments_combine(cta_m, m);
             }
         }
         for (int p = tid; p < nseg * DH; p += DTHREADS) {
@@ -290,12 +290,20 @@ __global__ void __launch_bounds__(DTHREADS, 2) k_drn_edge(const float *__restric
             }
         }
     }
+    if constexpr (STATS) {
+        if (tid < DH) {
+            o.tmom[((size_t)blockIdx.x * 3) * DH + tid] = cta_m.n;
+            o.tmom[((size_t)blockIdx.x * 3 + 1) * DH + tid] = cta_m.mean;
+            o.tmom[((size_t)blockIdx.x * 3 + 2) * DH + tid] = cta_m.m2;
+        }
+    }
 }
 
-// bnss [4][64] = mean, invstd, gamma, beta of the BatchNorm1d over the edge rows
+// bnss [4][64] = mean, invstd, gamma, beta of the BatchNorm1d over the edge rows.  Training: the per-CTA Chan moments
+// of k_drn_edge (ncta of them) are merged in a fixed two-level order (deterministic).
 __global__ void __launch_bounds__(1024) k_drn_bn(const int *__restrict__ rowptr, int N, long long capacity,
-                                                 const float *__restrict__ tmom, int training, float momentum, float eps,
-                                                 const float *__restrict__ gamma, const float *__restrict__ beta,
+                                                 const float *__restrict__ tmom, int ncta, int training, float momentum,
+                                                 float eps, const float *__restrict__ gamma, const float *__restrict__ beta,
                                                  float *__restrict__ running_mean, float *__restrict__ running_var,
                                                  long long *__restrict__ nbt, float *__restrict__ bnss) {
     __shared__ float s_m[16][DH][3];
@@ -303,19 +311,18 @@ __global__ void __launch_bounds__(1024) k_drn_bn(const int *__restrict__ rowptr,
     const int tid = threadIdx.x, c = tid & (DH - 1), part = tid >> 6;
     long long E = rowptr[N];
     if (E > capacity) E = capacity;
-    if (training) {
-        const int ntiles = (int)((E + DT - 1) / DT);
+    const bool batch_stats = training && E > 0;
+    if (batch_stats) {
         Moments m{0.f, 0.f, 0.f};
-        for (int t = part; t < ntiles; t += 16) {
-            const int ne = (int)min((long long)DT, E - (long long)t * DT);
-            m = moments_combine(m, Moments{(float)ne, tmom[((size_t)t * 2) * DH + c], tmom[((size_t)t * 2 + 1) * DH + c]});
-        }
+        for (int t = part; t < ncta; t += 16)
+            m = moments_combine(m, Moments{tmom[((size_t)t * 3) * DH + c], tmom[((size_t)t * 3 + 1) * DH + c],
+                                           tmom[((size_t)t * 3 + 2) * DH + c]});
         s_m[part][c][0] = m.n; s_m[part][c][1] = m.mean; s_m[part][c][2] = m.m2;
     }
     __syncthreads();
     if (tid >= DH) return;
     float mean, invstd;
-    if (training && E > 0) {
+    if (batch_stats) {
         Moments m{0.f, 0.f, 0.f};
         for (int q = 0; q < 16; ++q) m = moments_combine(m, Moments{s_m[q][c][0], s_m[q][c][1], s_m[q][c][2]});
         mean = m.mean;
@@ -369,20 +376,24 @@ struct HeadParams {
     const float *w1, *b1, *w2, *b2, *w3, *b3;
     int od;
 };
-__global__ void __launch_bounds__(256) k_drn_head(const float *__restrict__ x, const int *__restrict__ ptr, int B, HeadParams p,
+constexpr int HEAD_PARTS = 16;
+__global__ void __launch_bounds__(HEAD_PARTS * DH) k_drn_head(const float *__restrict__ x, const int *__restrict__ ptr, int B, HeadParams p,
                                                   float *__restrict__ pooled, float *__restrict__ out,
                                                   float *__restrict__ net_out) {
-    __shared__ float s_part[4][DH], s_p[DH], s_h1[DH], s_h2[DH / 2], s_o[8];
+    __shared__ float s_part[HEAD_PARTS][DH], s_p[DH], s_h1[DH], s_h2[DH / 2], s_o[8];
     pdl_sync();
     const int tid = threadIdx.x, c = tid & (DH - 1), part = tid >> 6;
     for (int e = blockIdx.x; e < B; e += gridDim.x) {
         const int a = ptr[e], b = ptr[e + 1];
         float m = -INFINITY;
-        for (int r = a + part; r < b; r += 4) m = fmaxf(m, x[(size_t)r * DH + c]);
+#pragma unroll 4
+        for (int r = a + part; r < b; r += HEAD_PARTS) m = fmaxf(m, x[(size_t)r * DH + c]);
         s_part[part][c] = m;
         __syncthreads();
         if (tid < DH) {
-            float v = fmaxf(fmaxf(s_part[0][tid], s_part[1][tid]), fmaxf(s_part[2][tid], s_part[3][tid]));
+            float v = s_part[0][tid];
+#pragma unroll
+            for (int q = 1; q < HEAD_PARTS; ++q) v = fmaxf(v, s_part[q][tid]);
             if (b <= a) v = 0.f;
             s_p[tid] = v;
             if (pooled) pooled[(size_t)e * DH + tid] = v;
@@ -417,6 +428,7 @@ __global__ void __launch_bounds__(256) k_drn_head(const float *__restrict__ x, c
 }
 
 // ------------------------------------------------------------------------------------------ workspace
+constexpr int MAX_EDGE_CTAS = 148 * 4;
 struct DrnWs {
     float *x0, *ab, *mx, *mn, *bmx, *bmn, *tmom, *bnss, *x1, *weight1, *x1p, *x2, *pooled;
     int *nbr, *deg, *rowptr1, *col1, *row1, *cluster1, *partner1, *scan, *scan_tiles, *ptr1p, *rowptr2, *col2, *row2;
@@ -439,7 +451,7 @@ size_t drn_layout(int N, int B, int k, char *base, DrnWs *w) {
     t.mn = (float *)take(n * DH * 4);
     t.bmx = (float *)take((size_t)2 * t.tiles_cap * DH * 4);
     t.bmn = (float *)take((size_t)2 * t.tiles_cap * DH * 4);
-    t.tmom = (float *)take((size_t)2 * t.tiles_cap * DH * 4);
+    t.tmom = (float *)take((size_t)3 * MAX_EDGE_CTAS * DH * 4);
     t.bnss = (float *)take(2 * 4 * DH * 4);
     t.x1 = (float *)take(n * DH * 4);
     t.weight1 = (float *)take((size_t)t.ecap * 4);
@@ -474,7 +486,10 @@ int edge_stage(const DrnWs &w, const GmDrnConv &cv, const int *rowptr, const int
         GM_CUDA_TRY(cudaFuncSetAttribute(k_drn_edge<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EDGE_SMEM));
         attr = true;
     }
-    const int grid = persistent_grid(w.tiles_cap, 2);
+    int grid = persistent_grid(w.tiles_cap, 2);
+    if (grid > MAX_EDGE_CTAS) grid = MAX_EDGE_CTAS;
+    {
+    TimedRegion tr(GM_TIMER_DRN_EDGE, st);
     if (training) {
         GM_LAUNCH_PDL(k_drn_edge<true>, grid, DTHREADS, EDGE_SMEM, st, (const float *)w.ab, rowptr, row, col, N, w.ecap,
                       (const float *)cv.w2, (const float *)cv.b2, o, w.tiles_cap);
@@ -483,7 +498,9 @@ int edge_stage(const DrnWs &w, const GmDrnConv &cv, const int *rowptr, const int
                       (const float *)cv.w2, (const float *)cv.b2, o, w.tiles_cap);
     }
     GM_LAUNCH_CHECK();
-    GM_LAUNCH_PDL(k_drn_bn, 1, 1024, 0, st, rowptr, N, w.ecap, (const float *)w.tmom, training, momentum, eps,
+    }
+    TimedRegion tr2(GM_TIMER_DRN_POOL, st);
+    GM_LAUNCH_PDL(k_drn_bn, 1, 1024, 0, st, rowptr, N, w.ecap, (const float *)w.tmom, grid, training, momentum, eps,
                   (const float *)cv.bn_weight, (const float *)cv.bn_bias, cv.bn_running_mean, cv.bn_running_var,
                   (long long *)cv.bn_num_batches_tracked, bnss);
     GM_LAUNCH_CHECK();
@@ -523,29 +540,53 @@ int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int
     const int node_grid = persistent_grid(((long long)N + DT - 1) / DT, 1);
     // ---- stage 1 (:82-92)
     NodeParams np{p->datanorm, p->in_w[0], p->in_b[0], p->in_w[1], p->in_b[1], p->in_w[2], p->in_b[2], p->conv[0].w1, p->conv[0].b1};
-    GM_LAUNCH_PDL(k_drn_node<true>, node_grid, DTHREADS, NODE_SMEM_FULL, st, x, x_stride, N, (const int *)nullptr, np, w.x0, w.ab);
-    GM_LAUNCH_CHECK();
-    GM_TRY(knn_search_table(w.x0, DH, DH, ptr, N, B, K, 0, w.nbr, w.deg, nullptr, st));
-    GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, nullptr, w.und, w.und_bytes, w.rowptr1, w.col1, w.row1,
-                             w.ecap, nullptr, st));
+    {
+        TimedRegion tr(GM_TIMER_DRN_NODE, st);
+        GM_LAUNCH_PDL(k_drn_node<true>, node_grid, DTHREADS, NODE_SMEM_FULL, st, x, x_stride, N, (const int *)nullptr, np, w.x0, w.ab);
+        GM_LAUNCH_CHECK();
+    }
+    {
+        TimedRegion tr(GM_TIMER_DRN_KNN, st);
+        GM_TRY(knn_search_table(w.x0, DH, DH, ptr, N, B, K, 0, w.nbr, w.deg, nullptr, st));
+    }
+    {
+        TimedRegion tr(GM_TIMER_DRN_GRAPH, st);
+        GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, nullptr, w.und, w.und_bytes, w.rowptr1, w.col1, w.row1,
+                                 w.ecap, nullptr, st));
+    }
     GM_TRY(edge_stage(w, p->conv[0], w.rowptr1, w.col1, w.row1, N, nullptr, training, momentum, eps, w.bnss, w.x1, st));
-    GM_TRY(drn_normalized_cut(w.x1, DH, DH, w.rowptr1, w.col1, w.row1, N, w.ecap, w.weight1, st));
-    GM_TRY(drn_graclus(w.rowptr1, w.col1, w.weight1, ptr, N, B, max_event_nodes, nullptr, w.cluster1, w.partner1, st));
-    GM_TRY(drn_max_pool(w.x1, DH, w.cluster1, w.partner1, ptr, N, B, nullptr, w.scan, w.scan_tiles, w.x1p, w.ptr1p, nullptr, st));
+    {
+        TimedRegion tr(GM_TIMER_DRN_POOL, st);
+        GM_TRY(drn_normalized_cut(w.x1, DH, DH, w.rowptr1, w.col1, w.row1, N, w.ecap, w.weight1, st));
+        GM_TRY(drn_graclus(w.rowptr1, w.col1, w.weight1, ptr, N, B, max_event_nodes, nullptr, w.cluster1, w.partner1, st));
+        GM_TRY(drn_max_pool(w.x1, DH, w.cluster1, w.partner1, ptr, N, B, nullptr, w.scan, w.scan_tiles, w.x1p, w.ptr1p, nullptr, st));
+    }
     // ---- stage 2 (:95-96) on the M = ptr1p[B] pooled nodes; M never leaves the device
     const int *m_dev = w.ptr1p + B;
     NodeParams np2{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, p->conv[1].w1, p->conv[1].b1};
-    GM_LAUNCH_PDL(k_drn_node<false>, node_grid, DTHREADS, NODE_SMEM_BASE, st, (const float *)w.x1p, DH, N, m_dev, np2,
-                  (float *)nullptr, w.ab);
-    GM_LAUNCH_CHECK();
-    GM_TRY(knn_search_table(w.x1p, DH, DH, w.ptr1p, N, B, K, 0, w.nbr, w.deg, m_dev, st));
-    GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, m_dev, w.und, w.und_bytes, w.rowptr2, w.col2, w.row2,
-                             w.ecap, nullptr, st));
+    {
+        TimedRegion tr(GM_TIMER_DRN_NODE, st);
+        GM_LAUNCH_PDL(k_drn_node<false>, node_grid, DTHREADS, NODE_SMEM_BASE, st, (const float *)w.x1p, DH, N, m_dev, np2,
+                      (float *)nullptr, w.ab);
+        GM_LAUNCH_CHECK();
+    }
+    {
+        TimedRegion tr(GM_TIMER_DRN_KNN, st);
+        GM_TRY(knn_search_table(w.x1p, DH, DH, w.ptr1p, N, B, K, 0, w.nbr, w.deg, m_dev, st));
+    }
+    {
+        TimedRegion tr(GM_TIMER_DRN_GRAPH, st);
+        GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, m_dev, w.und, w.und_bytes, w.rowptr2, w.col2, w.row2,
+                                 w.ecap, nullptr, st));
+    }
     GM_TRY(edge_stage(w, p->conv[1], w.rowptr2, w.col2, w.row2, N, m_dev, training, momentum, eps, w.bnss + 4 * DH, w.x2, st));
     // ---- :98-104: the second clustering cannot change a global maximum; pool per event and run the output MLP
     HeadParams hp{p->out_w[0], p->out_b[0], p->out_w[1], p->out_b[1], p->out_w[2], p->out_b[2], p->output_dim};
-    GM_LAUNCH_PDL(k_drn_head, B, 256, 0, st, (const float *)w.x2, (const int *)w.ptr1p, B, hp, w.pooled, out, net_out);
-    GM_LAUNCH_CHECK();
+    {
+        TimedRegion tr(GM_TIMER_DRN_POOL, st);
+        GM_LAUNCH_PDL(k_drn_head, B, HEAD_PARTS * DH, 0, st, (const float *)w.x2, (const int *)w.ptr1p, B, hp, w.pooled, out, net_out);
+        GM_LAUNCH_CHECK();
+    }
     if (view_out) {
         GmDrnView v{};
         v.x0 = w.x0; v.rowptr1 = w.rowptr1; v.col1 = w.col1; v.row1 = w.row1; v.x1 = w.x1; v.weight1 = w.weight1;

@@ -36,7 +36,7 @@ __device__ __forceinline__ int event_of(const int *__restrict__ ptr, int B, int 
     return lo;
 }
 
-template <int DP, int QPW>
+template <int DP, int QPW, int CPL>
 __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restrict__ x, int stride, int dim,
                                                             const int *__restrict__ ptr, int Ncap, int B, int K, int loop,
                                                             int *__restrict__ nbr, int *__restrict__ deg,
@@ -93,41 +93,54 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
                 cp_async_wait_all();
                 __syncthreads();                     // tile `buf` visible to all; everyone is done with tile `buf ^ 1`
                 if (t0 + TILE < c1) load_tile(buf ^ 1, t0 + TILE, min(TILE, c1 - t0 - TILE));
-                for (int j0 = 0; j0 < rows; j0 += 32) {
-                    const int j = j0 + lane;
-                    const bool valid = j < rows;
-                    const float4 *row = reinterpret_cast<const float4 *>(s_tile[buf] + (valid ? j : 0) * RS);
-                    float acc[QPW];
+                // CPL candidates per lane and step: CPL independent fmaf chains per query hide the FFMA latency at the
+                // low occupancy the D = 64 variant runs at (query coordinates fill the register file)
+                for (int j0 = 0; j0 < rows; j0 += 32 * CPL) {
+                    float acc[CPL][QPW];
+                    bool valid[CPL];
+                    const float4 *row[CPL];
 #pragma unroll
-                    for (int u = 0; u < QPW; ++u) acc[u] = 0.f;
+                    for (int g = 0; g < CPL; ++g) {
+                        const int j = j0 + 32 * g + lane;
+                        valid[g] = j < rows;
+                        row[g] = reinterpret_cast<const float4 *>(s_tile[buf] + (valid[g] ? j : 0) * RS);
+#pragma unroll
+                        for (int u = 0; u < QPW; ++u) acc[g][u] = 0.f;
+                    }
 #pragma unroll
                     for (int d4 = 0; d4 < DP / 4; ++d4) {
-                        const float4 c = row[d4];
 #pragma unroll
-                        for (int u = 0; u < QPW; ++u) {
-                            float df;
-                            df = __fsub_rn(c.x, q[u][4 * d4 + 0]); acc[u] = __fmaf_rn(df, df, acc[u]);
-                            df = __fsub_rn(c.y, q[u][4 * d4 + 1]); acc[u] = __fmaf_rn(df, df, acc[u]);
-                            df = __fsub_rn(c.z, q[u][4 * d4 + 2]); acc[u] = __fmaf_rn(df, df, acc[u]);
-                            df = __fsub_rn(c.w, q[u][4 * d4 + 3]); acc[u] = __fmaf_rn(df, df, acc[u]);
+                        for (int g = 0; g < CPL; ++g) {
+                            const float4 c = row[g][d4];
+#pragma unroll
+                            for (int u = 0; u < QPW; ++u) {
+                                float df;
+                                df = __fsub_rn(c.x, q[u][4 * d4 + 0]); acc[g][u] = __fmaf_rn(df, df, acc[g][u]);
+                                df = __fsub_rn(c.y, q[u][4 * d4 + 1]); acc[g][u] = __fmaf_rn(df, df, acc[g][u]);
+                                df = __fsub_rn(c.z, q[u][4 * d4 + 2]); acc[g][u] = __fmaf_rn(df, df, acc[g][u]);
+                                df = __fsub_rn(c.w, q[u][4 * d4 + 3]); acc[g][u] = __fmaf_rn(df, df, acc[g][u]);
+                            }
                         }
                     }
 #pragma unroll
-                    for (int u = 0; u < QPW; ++u) {
-                        unsigned pass = __ballot_sync(0xffffffffu, valid && qe[u] == e && acc[u] < worst[u]);
-                        while (pass) {
-                            const int b = __ffs(pass) - 1;
-                            pass &= pass - 1;
-                            const float cd = __shfl_sync(0xffffffffu, acc[u], b);
-                            if (!(cd < worst[u])) continue;          // the worst entry moved since the ballot
-                            const int ci = t0 + j0 + b;
-                            const int pos = __popc(__ballot_sync(0xffffffffu, ld[u] <= cd));   // ties: earlier index first
-                            const float upd = __shfl_up_sync(0xffffffffu, ld[u], 1);
-                            const int upi = __shfl_up_sync(0xffffffffu, li[u], 1);
-                            if (lane > pos) { ld[u] = upd; li[u] = upi; }
-                            else if (lane == pos) { ld[u] = cd; li[u] = ci; }
-                            // (lanes >= K keep what falls off the end: never <= cd again, never written out)
-                            worst[u] = __shfl_sync(0xffffffffu, ld[u], K - 1);
+                    for (int g = 0; g < CPL; ++g) {          // ascending candidate index: group 0 before group 1
+#pragma unroll
+                        for (int u = 0; u < QPW; ++u) {
+                            unsigned pass = __ballot_sync(0xffffffffu, valid[g] && qe[u] == e && acc[g][u] < worst[u]);
+                            while (pass) {
+                                const int b = __ffs(pass) - 1;
+                                pass &= pass - 1;
+                                const float cd = __shfl_sync(0xffffffffu, acc[g][u], b);
+                                if (!(cd < worst[u])) continue;          // the worst entry moved since the ballot
+                                const int ci = t0 + j0 + 32 * g + b;
+                                const int pos = __popc(__ballot_sync(0xffffffffu, ld[u] <= cd));   // ties: earlier index first
+                                const float upd = __shfl_up_sync(0xffffffffu, ld[u], 1);
+                                const int upi = __shfl_up_sync(0xffffffffu, li[u], 1);
+                                if (lane > pos) { ld[u] = upd; li[u] = upi; }
+                                else if (lane == pos) { ld[u] = cd; li[u] = ci; }
+                                // (lanes >= K keep what falls off the end: never <= cd again, never written out)
+                                worst[u] = __shfl_sync(0xffffffffu, ld[u], K - 1);
+                            }
                         }
                     }
                 }
@@ -187,12 +200,12 @@ int exclusive_scan_inplace(int *data, int n, int *tile_totals, int *total_out, c
 
 namespace {
 
-template <int DP, int QPW>
+template <int DP, int QPW, int CPL = 1>
 int launch_search(const float *x, int stride, int dim, const int *ptr, int N, int B, int K, int loop, int *nbr, int *deg,
                   const int *n_dev, cudaStream_t st) {
     const int qb = KNN_WARPS * QPW;
     const int grid = persistent_grid(((long long)N + qb - 1) / qb, 16);
-    GM_LAUNCH_PDL((k_knn_search<DP, QPW>), grid, KNN_THREADS, 0, st, x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev);
+    GM_LAUNCH_PDL((k_knn_search<DP, QPW, CPL>), grid, KNN_THREADS, 0, st, x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
@@ -206,7 +219,7 @@ int knn_search_table(const float *x, int stride, int dim, const int *ptr, int N,
     if (dim <= 8) return launch_search<8, 4>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
     if (dim <= 16) return launch_search<16, 2>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
     if (dim <= 32) return launch_search<32, 2>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
-    return launch_search<64, 1>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
+    return launch_search<64, 1, 1>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
 }
 
 }  // namespace gm

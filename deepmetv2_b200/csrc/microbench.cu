@@ -42,6 +42,23 @@ __global__ void __launch_bounds__(MB_THREADS, 2) k_ffma(int iters, float a, floa
     if (s == -1.f) sink[0] = s;
 }
 
+__global__ void __launch_bounds__(MB_THREADS, 2) k_ffma2(int iters, float a, float b, float *sink) {
+    float2 acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = make_float2((float)(threadIdx.x + k), (float)k);
+    const float2 a2 = make_float2(a, a), b2 = make_float2(b, b);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] = ffma2(acc[k], a2, b2);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += acc[k].x + acc[k].y;
+    if (s == -1.f) sink[0] = s;
+}
+
 template <typename F>
 int timed(F &&launch, float *ms_out) {
     cudaEvent_t e0, e1;
@@ -85,6 +102,18 @@ int gm_bench_ffma(int iters, float *ms_out, double *gflop_out) {
     const int rc = timed([&] { k_ffma<<<grid, MB_THREADS>>>(iters * 16, 0.999f, 0.001f, sink); }, ms_out);
     cudaFree(sink);
     *gflop_out = (double)grid * MB_THREADS * (double)iters * 16.0 * 128.0 * 2.0 / 1e9;
+    return rc;
+}
+
+/* the packed form: fma.rn.f32x2 (FFMA2), 4 flop per instruction and lane */
+int gm_bench_ffma2(int iters, float *ms_out, double *gflop_out) {
+    if (iters < 1 || !ms_out || !gflop_out) return GM_ERR_INVALID_ARGUMENT;
+    const int grid = num_sms() * 2;
+    float *sink = nullptr;
+    GM_CUDA_TRY(cudaMalloc(&sink, sizeof(float)));
+    const int rc = timed([&] { k_ffma2<<<grid, MB_THREADS>>>(iters * 16, 0.999f, 0.001f, sink); }, ms_out);
+    cudaFree(sink);
+    *gflop_out = (double)grid * MB_THREADS * (double)iters * 16.0 * 64.0 * 4.0 / 1e9;
     return rc;
 }
 

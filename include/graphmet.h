@@ -79,7 +79,12 @@ long long gm_launch_count(int reset);  /* kernels this library launched since th
 #define GM_TIMER_BN 7
 #define GM_TIMER_NODE_PREP 8
 #define GM_TIMER_HEAD_BWD 9
-#define GM_NUM_TIMERS 10
+#define GM_TIMER_DRN_NODE 10      /* DRN: inputnet + per-node half of the edge MLP */
+#define GM_TIMER_DRN_KNN 11       /* DRN: k-NN search in the 64-d latent space */
+#define GM_TIMER_DRN_GRAPH 12     /* DRN: to_undirected */
+#define GM_TIMER_DRN_EDGE 13      /* DRN: the per-edge 96->64 contraction kernel alone */
+#define GM_TIMER_DRN_POOL 14      /* DRN: BatchNorm merge + apply, normalized cut, graclus, max pool, head */
+#define GM_NUM_TIMERS 15
 int gm_timing_enable(int on);
 int gm_timing_read(int slot, float *total_ms_out, int *regions_out);
 
@@ -88,6 +93,7 @@ int gm_timing_read(int slot, float *total_ms_out, int *regions_out);
  * conflict-free LDS.128 stream on every SM: what physically feeds the cell-staged EdgeConv) and the FFMA stream rate. */
 int gm_bench_smem_read(int iters, float *ms_out, double *gbytes_out);
 int gm_bench_ffma(int iters, float *ms_out, double *gflop_out);
+int gm_bench_ffma2(int iters, float *ms_out, double *gflop_out);   /* packed fma.rn.f32x2 (FFMA2) stream */
 
 /* ---------------------------------------------------------------------------------
  * Parameters: the reference's 23 trainable tensors in construction order
