@@ -746,6 +746,15 @@ int geo_edge_aggr(int aggr, const float *Y, const float *P, const void *geo_ws, 
     return GM_ERR_INVALID_ARGUMENT;
 }
 
+// BatchNorm moments of a finished [N,32] layer output as a separate static-schedule pass (bit-reproducible): what the
+// tcgen05 EdgeConv (geo_tc.cu, ticket-scheduled, no in-kernel moments) uses in training
+int geo_row_moments(const float *out, int N, const AggrTail &tail, cudaStream_t st) {
+    const int mgrid = persistent_grid((N + 63) / 64, min(4, MAX_PARTIAL_CTAS / 148));
+    GM_LAUNCH_PDL(k_row_moments, mgrid, RM_THREADS, 0, st, out, N, tail);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
 int geo_scatter_s(const float *G, const float *raw, const BnBwd &bn, const int *arg, const void *geo_ws, int N, int B,
                   float *S, cudaStream_t st) {
     if (!geo_ws || B < 1) return GM_ERR_INVALID_ARGUMENT;

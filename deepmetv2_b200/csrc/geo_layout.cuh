@@ -72,9 +72,11 @@ struct AggrTail;
 struct BnBwd;
 int geo_edge_aggr(int aggr, const float *Y, const float *P, const void *geo_ws, int N, int B, float *out, int *arg,
                   const AggrTail &tail, cudaStream_t st);
-// implemented in geo_tc.cu: the same layer as a per-edge tcgen05 contraction (tf32 / bf16), forward without arg-max
+int geo_row_moments(const float *out, int N, const AggrTail &tail, cudaStream_t st);
+// implemented in geo_tc.cu: the same layer as a per-edge tcgen05 contraction (tf32 / bf16); arg (optional, max only) =
+// arg-max source node per (target, channel) for the backward
 int geo_edgeconv_tc(int aggr, int precision, const float *X, const float *P, const float *W, const void *geo_ws, int N,
-                    int B, float *out, cudaStream_t st);
+                    int B, float *out, int *arg, cudaStream_t st);
 int geo_scatter_s(const float *G, const float *raw, const BnBwd &bn, const int *arg, const void *geo_ws, int N, int B,
                   float *S, cudaStream_t st);
 

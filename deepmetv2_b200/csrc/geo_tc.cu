@@ -66,7 +66,9 @@ struct GtSmem {
     static constexpr size_t OFF_SLOT = OFF_ACC + (size_t)GT_CONSUMERS * GT_TPW * 128;  // [warp][slot] (eta, phi, thr, excl)
     static constexpr size_t OFF_DEG = OFF_SLOT + (size_t)GT_CONSUMERS * GT_TPW * 16;   // [warp][slot] i32
     static constexpr size_t OFF_GSLOT = OFF_DEG + (size_t)GT_CONSUMERS * GT_TPW * 4;   // [warp][2][4] u8: slot of a group
-    static constexpr size_t OFF_BAR = (OFF_GSLOT + (size_t)GT_CONSUMERS * 8 + 7) / 8 * 8;     // full[2] empty[2] mma[warp]
+    static constexpr size_t OFF_CNODE = (OFF_GSLOT + (size_t)GT_CONSUMERS * 8 + 15) / 16 * 16;  // [warp][2][32] i32: source node of a column (arg-max variant)
+    static constexpr size_t OFF_ARG = OFF_CNODE + (size_t)GT_CONSUMERS * 2 * GT_BLK * 4;        // [warp][slot][32] i32: running arg-max
+    static constexpr size_t OFF_BAR = (OFF_ARG + (size_t)GT_CONSUMERS * GT_TPW * 128 + 7) / 8 * 8;     // full[2] empty[2] mma[warp]
     static constexpr size_t OFF_TMEM = OFF_BAR + (size_t)(2 * GT_STAGES + GT_CONSUMERS) * 8;
     static constexpr size_t TOTAL = OFF_TMEM + 16;
     static_assert(OFF_A % 128 == 0 && OFF_B % 16 == 0 && OFF_XI % 16 == 0 && OFF_SLOT % 16 == 0, "operand alignment");
@@ -93,10 +95,13 @@ __device__ __forceinline__ void gt_sts128(uint32_t addr, uint32_t a, uint32_t b,
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
-template <int PREC, int AGGR>
+// ARG (max only): also the arg-max SOURCE node per (target, channel), so that tf32 / bf16 TRAINING runs on the implicit
+// graph: the source node of every operand column is recorded when the column is filled (the stage may be gone by the
+// time the block comes back from the tensor core) and the epilogue keeps the first maximum in column order.
+template <int PREC, int AGGR, bool ARG = false>
 __global__ void __launch_bounds__(GtSmem<PREC>::THREADS, 1)
 k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, const float *__restrict__ W, GeoView v,
-                  int N, float *__restrict__ out) {
+                  int N, float *__restrict__ out, int *__restrict__ arg) {
     using S = GtSmem<PREC>;
     using C = GtCfg<PREC>;
     constexpr bool TF32 = PREC == GM_PREC_TF32;
@@ -148,6 +153,8 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
         float4 *s_slot = reinterpret_cast<float4 *>(gs + S::OFF_SLOT) + w * GT_TPW;
         int *s_deg = reinterpret_cast<int *>(gs + S::OFF_DEG) + w * GT_TPW;
         unsigned char *s_gslot = gs + S::OFF_GSLOT + w * 8;
+        int *s_cnode = reinterpret_cast<int *>(gs + S::OFF_CNODE) + w * 2 * GT_BLK;
+        int *s_arg = reinterpret_cast<int *>(gs + S::OFF_ARG) + w * GT_TPW * 32;
         const uint32_t b_base = smem_u32(gs + S::OFF_B) + (uint32_t)(w * 2 * S::B_BYTES);
         const uint32_t mbar = mma0 + 8u * w;
         const uint32_t d_tmem = tmem_base + (uint32_t)(w * GT_BLK);                 // all 128 lanes, this warp's columns
@@ -168,13 +175,18 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
             tc5_ld32(ld_tmem, r);
             const unsigned slots = *reinterpret_cast<const unsigned *>(s_gslot + pending * 4);
             float run = IDENT;                                                      // groups of one slot are merged in registers
+            int runcol = 0;
 #pragma unroll
             for (int g = 0; g < GT_BLK / 8; ++g) {
                 if (g * 8 < nv_pending) {                                           // warp-uniform
                     float t[8];
 #pragma unroll
                     for (int c = 0; c < 8; ++c) t[c] = __uint_as_float(r[8 * g + c]);
-                    if (AGGR == GM_AGGR_MAX)
+                    if constexpr (ARG) {
+#pragma unroll
+                        for (int c = 0; c < 8; ++c)
+                            if (t[c] > run) { run = t[c]; runcol = 8 * g + c; }     // strict: the first maximum wins
+                    } else if (AGGR == GM_AGGR_MAX)
                         run = fmaxf(fmaxf(fmaxf(run, t[0]), fmaxf(t[1], t[2])), fmaxf(fmaxf(t[3], t[4]), fmaxf(t[5], fmaxf(t[6], t[7]))));
                     else
                         run += ((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]));
@@ -182,7 +194,11 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
                     const bool close = (g + 1) * 8 >= nv_pending || g == GT_BLK / 8 - 1 || ((slots >> (8 * g + 8)) & 0xffu) != sg;
                     if (close) {                                                    // warp-uniform
                         float *dst = s_acc + (int)sg * 32 + lane;
-                        *dst = AGGR == GM_AGGR_MAX ? fmaxf(*dst, run) : *dst + run;
+                        if constexpr (ARG) {
+                            if (run > *dst) { *dst = run; s_arg[(int)sg * 32 + lane] = s_cnode[pending * GT_BLK + runcol]; }
+                        } else {
+                            *dst = AGGR == GM_AGGR_MAX ? fmaxf(*dst, run) : *dst + run;
+                        }
                         run = IDENT;
                     }
                 }
@@ -233,6 +249,7 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
                 for (int u = 0; u < GT_TPW; ++u) {
                     const int t = a + w + u * GT_CONSUMERS;
                     s_acc[u * 32 + lane] = IDENT;
+                    if constexpr (ARG) s_arg[u * 32 + lane] = -1;
                     if (t < b) s_xi[u * 32 + lane] = s_trows[t * 32 + lane];
                 }
                 __syncwarp();
@@ -266,11 +283,18 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
                         const int ng = min(ngroups - kg, (GT_BLK - fill) >> 3);
                         if (lane < ng) s_gslot[buf * 4 + (fill >> 3) + lane] = (unsigned char)u;
                         uint32_t ad = dstl + (uint32_t)(buf * S::B_BYTES + (fill >> 3) * S::SBO);
+                        int *cn = s_cnode + buf * GT_BLK + fill + r4;
 #pragma unroll 2
-                        for (int g = 0; g < ng; ++g, lp += 8, ad += S::SBO) {
+                        for (int g = 0; g < ng; ++g, lp += 8, ad += S::SBO, cn += 8) {
                             float4 x0, x1;
                             lds4(x0, src + lp[0]);
                             lds4(x1, src + lp[4]);
+                            if constexpr (ARG) {
+                                if (c4 == 0) {                                      // one lane per staged row: column -> node
+                                    cn[0] = node_of_row(d, (int)(lp[0] >> 7));
+                                    cn[4] = node_of_row(d, (int)(lp[4] >> 7));
+                                }
+                            }
                             if constexpr (TF32) {
                                 gt_sts128(ad, tc5_to_tf32(x0.x - xi.x), tc5_to_tf32(x0.y - xi.y), tc5_to_tf32(x0.z - xi.z), tc5_to_tf32(x0.w - xi.w));
                                 gt_sts128(ad + 64, tc5_to_tf32(x1.x - xi.x), tc5_to_tf32(x1.y - xi.y), tc5_to_tf32(x1.z - xi.z), tc5_to_tf32(x1.w - xi.w));
@@ -309,6 +333,7 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
                     else if (AGGR == GM_AGGR_ADD) o = fmaf((float)deg, p[u], acc);
                     else o = fmaf(acc, 1.f / (float)deg, p[u]);
                     out[(size_t)(n0 + t) * H + lane] = o;
+                    if constexpr (ARG) arg[(size_t)(n0 + t) * H + lane] = deg == 0 ? -1 : s_arg[u * 32 + lane];
                 }
                 __syncwarp();
             }
@@ -326,32 +351,37 @@ k_geo_edgeconv_tc(const float *__restrict__ X, const float *__restrict__ P, cons
     }
 }
 
-template <int PREC, int AGGR>
-int launch_geo_tc(const float *X, const float *P, const float *W, const GeoView &v, int N, float *out, cudaStream_t st) {
+template <int PREC, int AGGR, bool ARG = false>
+int launch_geo_tc(const float *X, const float *P, const float *W, const GeoView &v, int N, float *out, int *arg,
+                  cudaStream_t st) {
     static int occ = 0;
     if (!occ) {
-        GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_edgeconv_tc<PREC, AGGR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_edgeconv_tc<PREC, AGGR, ARG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)GtSmem<PREC>::TOTAL));
-        GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_edgeconv_tc<PREC, AGGR>, cudaFuncAttributePreferredSharedMemoryCarveout,
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_edgeconv_tc<PREC, AGGR, ARG>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                          (int)cudaSharedmemCarveoutMaxShared));
-        occ = min(resident_ctas(k_geo_edgeconv_tc<PREC, AGGR>, GtSmem<PREC>::THREADS, GtSmem<PREC>::TOTAL, 1), 512 / GtSmem<PREC>::TMEM_COLS);
+        occ = min(resident_ctas(k_geo_edgeconv_tc<PREC, AGGR, ARG>, GtSmem<PREC>::THREADS, GtSmem<PREC>::TOTAL, 1), 512 / GtSmem<PREC>::TMEM_COLS);
         // work is taken from a ticket counter, so a CTA that is not resident at once only finds the queue empty:
         // size the grid by what shared memory allows even if the occupancy query is pessimistic
         occ = max(occ, min((int)(227 * 1024 / (GtSmem<PREC>::TOTAL + 1024)), 512 / GtSmem<PREC>::TMEM_COLS));
     }
     const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, occ);
-    GM_LAUNCH_PDL((k_geo_edgeconv_tc<PREC, AGGR>), grid, GtSmem<PREC>::THREADS, GtSmem<PREC>::TOTAL, st, X, P, W, v, N, out);
+    GM_LAUNCH_PDL((k_geo_edgeconv_tc<PREC, AGGR, ARG>), grid, GtSmem<PREC>::THREADS, GtSmem<PREC>::TOTAL, st, X, P, W, v, N, out, arg);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
 
 template <int PREC>
 int dispatch_geo_tc(int aggr, const float *X, const float *P, const float *W, const GeoView &v, int N, float *out,
-                    cudaStream_t st) {
+                    int *arg, cudaStream_t st) {
+    if (arg) {
+        if (aggr != GM_AGGR_MAX) return GM_ERR_UNSUPPORTED;
+        return launch_geo_tc<PREC, GM_AGGR_MAX, true>(X, P, W, v, N, out, arg, st);
+    }
     switch (aggr) {
-        case GM_AGGR_MAX: return launch_geo_tc<PREC, GM_AGGR_MAX>(X, P, W, v, N, out, st);
-        case GM_AGGR_ADD: return launch_geo_tc<PREC, GM_AGGR_ADD>(X, P, W, v, N, out, st);
-        case GM_AGGR_MEAN: return launch_geo_tc<PREC, GM_AGGR_MEAN>(X, P, W, v, N, out, st);
+        case GM_AGGR_MAX: return launch_geo_tc<PREC, GM_AGGR_MAX>(X, P, W, v, N, out, nullptr, st);
+        case GM_AGGR_ADD: return launch_geo_tc<PREC, GM_AGGR_ADD>(X, P, W, v, N, out, nullptr, st);
+        case GM_AGGR_MEAN: return launch_geo_tc<PREC, GM_AGGR_MEAN>(X, P, W, v, N, out, nullptr, st);
     }
     return GM_ERR_INVALID_ARGUMENT;
 }
@@ -359,12 +389,13 @@ int dispatch_geo_tc(int aggr, const float *X, const float *P, const float *W, co
 }  // namespace
 
 // X: layer input [N,32] in internal order; P = W1 x + b [N,32]; W: the EdgeConv weight [32,64] (W2 = columns 32..63)
+// arg (optional, max only): [N,32] arg-max source node per (target, channel), internal order
 int geo_edgeconv_tc(int aggr, int precision, const float *X, const float *P, const float *W, const void *geo_ws, int N,
-                    int B, float *out, cudaStream_t st) {
+                    int B, float *out, int *arg, cudaStream_t st) {
     if (!geo_ws || B < 1) return GM_ERR_INVALID_ARGUMENT;
     const GeoView v = view_of(geo_ws, N, B);
-    if (precision == GM_PREC_TF32) return dispatch_geo_tc<GM_PREC_TF32>(aggr, X, P, W, v, N, out, st);
-    if (precision == GM_PREC_BF16) return dispatch_geo_tc<GM_PREC_BF16>(aggr, X, P, W, v, N, out, st);
+    if (precision == GM_PREC_TF32) return dispatch_geo_tc<GM_PREC_TF32>(aggr, X, P, W, v, N, out, arg, st);
+    if (precision == GM_PREC_BF16) return dispatch_geo_tc<GM_PREC_BF16>(aggr, X, P, W, v, N, out, arg, st);
     return GM_ERR_UNSUPPORTED;
 }
 

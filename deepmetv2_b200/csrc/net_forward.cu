@@ -783,9 +783,9 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
     if (N < 0 || !ws || !err_flags) return GM_ERR_INVALID_ARGUMENT;
     if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || (!rowptr && !geo_ws) || !out)) return GM_ERR_INVALID_ARGUMENT;
     if (geo_ws && !node_perm) return GM_ERR_UNSUPPORTED;
-    // per-edge tcgen05 on the implicit graph: forward only (no arg-max, no BatchNorm partials)
+    // per-edge tcgen05 on the implicit graph: tf32 / bf16; training (arg-max + BatchNorm moments) for aggr = max
     if (geo_ws && precision != GM_PREC_FP32 &&
-        ((precision != GM_PREC_TF32 && precision != GM_PREC_BF16) || training || save_for_backward))
+        ((precision != GM_PREC_TF32 && precision != GM_PREC_BF16) || (save_for_backward && aggr != GM_AGGR_MAX)))
         return GM_ERR_UNSUPPORTED;
     if (ws_bytes < net_ws_layout(N, p->conv_depth, save_for_backward, nullptr, nullptr)) return GM_ERR_CAPACITY;
     if (N == 0) return GM_OK;
@@ -844,7 +844,9 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
                 GM_LAUNCH_CHECK();
             }
             TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
-            GM_TRY(geo_edgeconv_tc(aggr, precision, w.emb[l], w.P, p->conv_w[l], geo_ws, N, B, w.conv[l], st));
+            GM_TRY(geo_edgeconv_tc(aggr, precision, w.emb[l], w.P, p->conv_w[l], geo_ws, N, B, w.conv[l], arg, st));
+            if (training)      // the tensor-core kernel is ticket-scheduled: moments as a static, bit-reproducible pass
+                GM_TRY(geo_row_moments(w.conv[l], N, AggrTail{w.partials, w.counters + 1 + l, p->conv_bn[l], momentum, eps, stat_out}, st));
         } else {
             {
                 TimedRegion tr(GM_TIMER_NODE_PREP, st);
@@ -907,15 +909,15 @@ int gm_edgeconv_forward_geo(const float *x, const void *geo_ws, int N, int B, co
     cudaStream_t st = as_stream(stream);
     float *Y = (float *)ws;
     float *P = (float *)((char *)ws + gm_edgeconv_ws_bytes(N) / 2);
-    if (precision != GM_PREC_FP32) {                    // per-edge tcgen05 contraction: forward only
-        if (arg_out || (precision != GM_PREC_TF32 && precision != GM_PREC_BF16)) return GM_ERR_UNSUPPORTED;
+    if (precision != GM_PREC_FP32) {                    // per-edge tcgen05 contraction (arg-max for aggr = max)
+        if ((arg_out && aggr != GM_AGGR_MAX) || (precision != GM_PREC_TF32 && precision != GM_PREC_BF16)) return GM_ERR_UNSUPPORTED;
         {
             TimedRegion tr(GM_TIMER_NODE_PREP, st);
             k_node_prep2<<<node_grid(N), NP_THREADS, 0, st>>>(x, nullptr, nullptr, W, b, N, nullptr, nullptr, P, 1);
             GM_LAUNCH_CHECK();
         }
         TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
-        return geo_edgeconv_tc(aggr, precision, x, P, W, geo_ws, N, B, out, st);
+        return geo_edgeconv_tc(aggr, precision, x, P, W, geo_ws, N, B, out, arg_out, st);
     }
     {
         TimedRegion tr(GM_TIMER_NODE_PREP, st);

@@ -180,7 +180,7 @@ def edgeconv_geo(x_internal: torch.Tensor, geo: GeoGraph, weight: torch.Tensor, 
                  want_arg: bool = False, precision: str = "fp32"):
     """EdgeConv(Linear(64, 32), aggr) over the implicit graph; ``x_internal`` [N,32] is in internal node order
     (``x[geo.perm]``) and so are the outputs.  ``precision`` "tf32" / "bf16" runs the per-edge contraction on
-    tcgen05 (forward only: no ``want_arg``)."""
+    tcgen05 (``want_arg`` with ``aggr="max"`` only)."""
     _lib.require_cuda(x_internal, "x")
     x = x_internal.contiguous().float()
     N = x.shape[0]

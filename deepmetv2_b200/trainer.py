@@ -7,9 +7,10 @@ evaluate.py:81-100 of the reference as ONE call).
 The radius graph is, by default, kept IMPLICIT (``graph="implicit"``, ``gm_geo_build``): points are cell-binned,
 the network runs in cell-sorted node order and the EdgeConv kernels re-evaluate the edge predicate on cell
 neighbourhoods staged in shared memory, so no edge list and no transposed graph are ever written.
-``graph="csr"`` is the explicit path (count, scan, fill; E stays on the device; transposed CSR iff capped) and
-the only one that supports the tcgen05 ``edge_precision`` variants in TRAINING; in eval mode tf32 / bf16 run the
-per-edge contraction on the implicit graph too (``csrc/geo_tc.cu``).
+``graph="csr"`` is the explicit path (count, scan, fill; E stays on the device; transposed CSR iff capped).  The
+tcgen05 ``edge_precision`` variants (tf32 / bf16) run the per-edge contraction on the implicit graph too
+(``csrc/geo_tc.cu``), in eval mode and -- for ``aggr="max"``, with the arg-max sources recorded for the backward --
+in training.
 
 Data parallelism (``process_group=``): every rank steps on its own events; the per-event-SUM gradients are all-reduced
 and divided by the GLOBAL event count, so ranks may hold different numbers of events (a rank with none still joins
@@ -167,12 +168,14 @@ class GraphMETTrainer:
 
     # ------------------------------------------------------------------------------------------ buffers
     def _implicit(self, training: bool | None = None) -> bool:
-        """fp32: always; tf32 / bf16 (per-edge tcgen05 on the implicit graph, csrc/geo_tc.cu): forward only."""
+        """fp32: always; tf32 / bf16 (per-edge tcgen05 on the implicit graph, csrc/geo_tc.cu): eval, and training with
+        max aggregation (the kernel records the arg-max sources the backward routes gradients through)."""
         if training is None:
             training = self.net.training
         if self.graph != "implicit":
             return False
-        return self.net.edge_precision == "fp32" or (self.net.edge_precision in ("tf32", "bf16") and not training)
+        return self.net.edge_precision == "fp32" or \
+            (self.net.edge_precision in ("tf32", "bf16") and (not training or self.net.aggr == "max"))
 
     def _reserve(self, N: int, B: int, max_event_nodes: int):
         implicit = self._implicit()

@@ -254,9 +254,11 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
  * gm_net_forward_geo / gm_net_backward_geo / gm_edgeconv_forward_geo are gm_net_forward / gm_net_backward /
  * gm_edgeconv_forward with (geo_ws, B, node_perm) in place of the CSR: the EdgeConv layers stage each cell
  * neighbourhood once into shared memory (TMA bulk copies) and evaluate that predicate there; the backward
- * needs no transposed graph.  precision: GM_PREC_FP32 (factored fp32: forward, backward, arg-max) or, forward
- * only (training == 0, save_for_backward == 0, arg_out == NULL), GM_PREC_TF32 / GM_PREC_BF16: the per-edge
- * contraction on tcgen05, every consumer warp driving its own TMEM pipeline (csrc/geo_tc.cu).  geo_ws (gm_geo_ws_bytes(N, B)) must stay
+ * needs no transposed graph.  precision: GM_PREC_FP32 (factored fp32: forward, backward, arg-max) or GM_PREC_TF32 /
+ * GM_PREC_BF16: the per-edge contraction on tcgen05, every consumer warp driving its own TMEM pipeline
+ * (csrc/geo_tc.cu); with aggr = max it also records the arg-max sources (save_for_backward / arg_out), so a
+ * training step runs on the implicit graph in these precisions too (the backward is the fp32 one, routed through
+ * the recorded sources).  geo_ws (gm_geo_ws_bytes(N, B)) must stay
  * untouched between the build and the last forward / backward that uses it.
  * stats_out (optional, int[4]): {-1 (E is not counted), max degree seen among cap candidates, #capped, flags}.
  * x of gm_edgeconv_forward_geo, and arg_out, are in INTERNAL node order.
