@@ -298,6 +298,10 @@ def run_knn(args):
 
 
 def run_drn(args):
+    print(json.dumps(drn_line(args)))
+
+
+def drn_line(args):
     """Side line for BASELINE config 4 / row f1: the DynamicReductionNetwork variant (model/dynamic_reduction_network.py with
     the wrapper of model/net.py:12-37) on 32 synthetic Z->nunu-shaped events, train-mode forward (BatchNorm batch statistics
     over the edge rows + running-stat update; the backward is not built).  Roofline on the per-edge 96->64 contraction."""
@@ -371,7 +375,7 @@ def run_drn(args):
     cpu_s = statistics.median(ts)
     kern = {k: {"avg_us": v[0] / max(v[1], 1) * 1e3, "regions_per_step": v[1] / args.steps,
                 "share_of_step": v[0] / args.steps / ms_step} for k, v in timers.items()}
-    print(json.dumps({
+    return ({
         "metric": "DRN forward events/sec", "value": B / ms_step * 1e3, "unit": "events/s", "n_gpus": 1, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if not tensor else args.precision, "data": "synthetic",
@@ -390,7 +394,7 @@ def run_drn(args):
                                    "a Python loop), warm-up 1, median of 3"},
         "e2e": {"value": B / e2e_s, "unit": "events/s", "h2d_bytes_per_step": int(Nn * 44 + (B + 1) * 4),
                 "d2h_bytes_per_step": B * 8, "api": "DRNNet.forward"},
-    }))
+    })
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
@@ -696,6 +700,10 @@ def main():
             ks3 = max(3, min(args.steps, 6))
             side["c3_fp32"] = run_side("c3", "fp32", rank, world, dev, pg, l, ks3, flush, barrier, peaks, smem_peak)
             side["c3_bf16"] = run_side("c3", "bf16", rank, world, dev, pg, l, ks3, flush, barrier, peaks, smem_peak)
+            # tf32 / bf16 TRAINING on the implicit graph (arg-max variant of the tcgen05 kernel) and BASELINE config 4
+            side["c5_bf16"] = run_side("c5", "bf16", rank, world, dev, pg, l, ks, flush, barrier, peaks, smem_peak)
+            l.gm_timing_enable(0)
+            side["c4_drn"] = drn_line(argparse.Namespace(steps=ks, warmup=3, precision="fp32"))
 
     # very short runs: keep THIS GPU busy until a few nvidia-smi samples exist.  Rank 0 only, so nothing here may
     # involve a collective: inference steps (r01's version ran training steps, whose gradient all-reduce no other rank

@@ -107,6 +107,7 @@ SIGNATURES = {
     "gm_scatter_add": (_i, [_vp, _vp, _ll, _vp, _ll, _vp]),
     "gm_index_stats": (_i, [_vp, _ll, _vp, _vp]),
     "gm_resolution": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    "gm_resolution_summary": (_i, [_vp, _ll, _vp, _i, _i, _f, _i, _vp, _vp]),
     "gm_adamw_step": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _f, _vp]),
     "gm_met_loss_ex": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp, _vp]),
     "gm_adamw_step_ex": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _f, _vp, _vp, _vp, _vp, _vp]),

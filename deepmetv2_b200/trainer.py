@@ -34,6 +34,31 @@ from ._lib import AGGR, PRECISION, check, lib, ptr, stream
 from .synth import EventBatch
 
 
+class FusedAdamW(torch.optim.Optimizer):
+    """``torch.optim.AdamW``-shaped handle on the trainer's fused optimiser (train.py:75-76): hyper-parameters live in
+    ``param_groups[0]`` exactly as in torch, so ``torch.optim.lr_scheduler.ReduceLROnPlateau(trainer.optimizer, factor=0.5,
+    patience=500, threshold=0.05)`` / ``scheduler.step(loss)`` (train.py:58,76) work unchanged -- the fused step kernel
+    reads ``lr`` / ``betas`` / ``eps`` / ``weight_decay`` from the group on every step.  ``step()`` is a no-op (the update
+    is the last kernel of ``GraphMETTrainer.train_step``); ``state_dict()`` / ``load_state_dict()`` use torch's AdamW
+    layout (what the reference stores as ``optim_dict``)."""
+
+    def __init__(self, trainer, params, lr, betas, eps, weight_decay):
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=False))
+        self._trainer = trainer
+
+    def step(self, closure=None):          # the fused kernel already applied the update
+        return None if closure is None else closure()
+
+    def zero_grad(self, set_to_none: bool = True):   # gradients are overwritten by every backward
+        return None
+
+    def state_dict(self):
+        return self._trainer.optimizer_state_dict()
+
+    def load_state_dict(self, sd):
+        self._trainer.load_optimizer_state_dict(sd)
+
+
 class GraphMETTrainer:
     def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, r=0.4,
                  max_num_neighbors=255, loop=True, phi_wrap=False, process_group=None, device=None,
@@ -41,7 +66,6 @@ class GraphMETTrainer:
         self.model = model
         self.net = model.graphnet if hasattr(model, "graphnet") else model
         self.apply_sigmoid = hasattr(model, "graphnet")       # Net applies the sigmoid, GraphMETNetwork does not
-        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
         self.r, self.max_nn, self.loop, self.phi_wrap = r, max_num_neighbors, loop, phi_wrap
         if graph not in ("implicit", "csr"):
             raise ValueError("graph must be 'implicit' or 'csr'")
@@ -72,6 +96,7 @@ class GraphMETTrainer:
             off += k
         self._P = self.net._param_struct()
         self._G = self.net._param_struct(grad_views=self._gviews)
+        self.optimizer = FusedAdamW(self, params, lr, tuple(betas), eps, weight_decay)
         self._cap_nodes = self._cap_events = self._cap_edges = -1
         self._cap_implicit = None
         self.flags = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -85,6 +110,17 @@ class GraphMETTrainer:
         self.comm = None
         if self.world > 1 and fused_allreduce:
             self._connect_peers(n)
+
+    # hyper-parameters: one source of truth, the optimizer's param group (so LR schedulers act on the fused step)
+    def _hp(self, key):
+        return self.optimizer.param_groups[0][key]
+
+    lr = property(lambda self: self._hp("lr"), lambda self, v: self.optimizer.param_groups[0].__setitem__("lr", v))
+    betas = property(lambda self: tuple(self._hp("betas")),
+                     lambda self, v: self.optimizer.param_groups[0].__setitem__("betas", tuple(v)))
+    eps = property(lambda self: self._hp("eps"), lambda self, v: self.optimizer.param_groups[0].__setitem__("eps", v))
+    weight_decay = property(lambda self: self._hp("weight_decay"),
+                            lambda self, v: self.optimizer.param_groups[0].__setitem__("weight_decay", v))
 
     # ------------------------------------------------------------------------------------------ data parallelism
     def _connect_peers(self, n: int):
@@ -291,7 +327,8 @@ class GraphMETTrainer:
             self.loss.zero_()
             B = 0
         self.step_count += 1
-        hyper = (self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay, self.step_count)
+        hyper = (float(self.lr), float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay),
+                 self.step_count)
         mirrors = (ptr(self.flags), ptr(self.stats), ptr(self._status))
         if not dp:
             check(l.gm_adamw_step_ex(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq),

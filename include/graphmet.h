@@ -323,6 +323,15 @@ int gm_index_stats(const int64_t *index, long long n, int64_t *stats_out, void *
 int gm_resolution(const float *met /*[B,2]*/, const float *truth, int truth_stride, int truth_cols,
                   int B, float *out, float *qt_out, void *stream);
 
+/* f4. The per-epoch summary of evaluate.py:110-156 on the device: events are digitized by qT into n_bins bins of
+ *     bin_width (np.digitize over np.arange(0, 400, 10): n_bins = 39, bin_width = 10) and, per MET flavour k and bin,
+ *     out[k][0..4][bin] = (q84 - q16)/2 of u_perp, the same of u_perp / mean(R), of u_par, of u_par / mean(R), and
+ *     mean(R) -- np.quantile's default linear interpolation; out is [K,5,n_bins+1] with the last column 0 (the
+ *     layout of the reference's np.histogram(qT_hist, bins=40, range=(0,400), weights=...)[0]); empty bins are NaN.
+ *     vals [K,3,ld]: u_perp, u_par, R of all M events of the epoch (gm_resolution's layout with row pitch ld). */
+int gm_resolution_summary(const float *vals, long long ld, const float *qt, int M, int K, float bin_width, int n_bins,
+                          float *out, void *stream);
+
 /* ---------------------------------------------------------------------------------
  * a9. Optimiser — replaces torch.optim.AdamW.step (train.py:52,75): one fused kernel over a
  *     flat fp32 buffer. grad_scale multiplies the gradient first (1/world_size after a SUM

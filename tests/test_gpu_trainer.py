@@ -132,3 +132,31 @@ def test_trainer_capped_graph(graph):
     gref = torch.cat([p.grad.flatten() for p in ref.parameters()])
     err = (tr.flat_grad.cpu() - gref).abs().max() / gref.abs().max()
     assert err < 1e-3, err
+
+
+def test_lr_scheduler_drives_the_fused_step():
+    """train.py:58,76: ReduceLROnPlateau on the trainer's optimizer handle changes what the fused AdamW kernel applies."""
+    torch.manual_seed(0)
+    b = synth.make_batch(2, "dytt", seed=5, sizes=[200, 180]).to(DEV)
+    def run(schedule):
+        m = gnet.Net(8, 3)
+        torch.manual_seed(1)
+        for p in m.parameters():
+            torch.nn.init.normal_(p, std=0.1) if p.dim() > 1 else None
+        m.to(DEV)
+        tr = GraphMETTrainer(m, lr=1e-3)
+        sched = torch.optim.lr_scheduler.ReduceLROnPlateau(tr.optimizer, factor=0.5, patience=0, threshold=0.05)
+        before = tr.flat.clone()
+        if schedule:
+            sched.step(1.0); sched.step(1.0)          # no improvement with patience 0: lr halves
+            assert abs(tr.lr - 5e-4) < 1e-12
+        tr.train_step(b)
+        torch.cuda.synchronize()
+        return (tr.flat - before).abs().max().item(), tr
+    d_full, _ = run(False)
+    d_half, tr = run(True)
+    assert abs(d_half / d_full - 0.5) < 0.02            # the first AdamW step moves every weight by ~lr
+    sd = tr.optimizer.state_dict()
+    assert sd["param_groups"][0]["lr"] == tr.lr and len(sd["state"]) == 23
+    ref_opt = torch.optim.AdamW([torch.nn.Parameter(torch.zeros_like(v)) for v in tr._views], lr=1e-3)
+    ref_opt.load_state_dict(sd)                          # torch's own AdamW accepts the layout
