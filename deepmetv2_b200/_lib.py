@@ -95,6 +95,11 @@ SIGNATURES = {
     "gm_net_bwd_ws_bytes": (_sz, [_i, _i]),
     "gm_net_backward": (_i, [C.POINTER(GmParams), C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp,
                              _i, _vp, _i, _i, _i, _f, _vp, _sz, _vp, _sz, _vp, _vp, _vp]),
+    "gm_net_knn_ws_bytes": (_sz, [_i, _i, _i]),
+    "gm_net_forward_knn": (_i, [C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _f, _vp, _sz,
+                                _vp, _sz, _vp, _vp, _vp]),
+    "gm_net_backward_knn": (_i, [C.POINTER(GmParams), C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz,
+                                 _vp, _sz, _vp, _sz, _vp, _vp, _vp]),
     "gm_geo_ws_bytes": (_sz, [_i, _i]),
     "gm_geo_build": (_i, [_vp, _i, _i, _vp, _i, _i, _d, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _vp]),
     "gm_net_forward_geo": (_i, [C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _f, _f,

@@ -681,11 +681,11 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
                              const int *col, const int *rowptr_t, const int *col_t, const int *use_transposed_flag,
                              const void *geo_ws, int B, int N, const int *node_perm, int training, int apply_sigmoid,
                              int aggr, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
-                             const float *out, const float *grad_out, void *stream) {
+                             const float *out, const float *grad_out, void *stream, const KnnLayers *kl = nullptr) {
     GM_TRY(check_params(p));
     if (!grads || N < 0 || !fwd_ws || !bwd_ws) return GM_ERR_INVALID_ARGUMENT;
     if (aggr != GM_AGGR_MAX) return GM_ERR_UNSUPPORTED;
-    if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || (!geo_ws && (!rowptr_t || !col_t)) || !out || !grad_out))
+    if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || (!geo_ws && !kl && (!rowptr_t || !col_t)) || !out || !grad_out))
         return GM_ERR_INVALID_ARGUMENT;
     const int depth = p->conv_depth;
     if (fwd_ws_bytes < net_ws_layout(N, depth, 1, nullptr, nullptr)) return GM_ERR_CAPACITY;
@@ -744,8 +744,10 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
             } else {
                 static int occ = 0;
                 if (!occ) occ = resident_ctas(k_scatter_s, 256, 0, 3);
+                // per-layer k-NN graphs are asymmetric: always the layer's own transposed CSR
                 k_scatter_s<<<persistent_grid(((long long)N * 32 + 255) / 256, occ), 256, 0, st>>>(
-                    w.G, f.conv[l], bn_in(l + 1), f.arg[l], rowptr, col, rowptr_t, col_t, use_transposed_flag, N, w.S);
+                    w.G, f.conv[l], bn_in(l + 1), f.arg[l], kl ? kl->rowptr[l] : rowptr, kl ? kl->col[l] : col,
+                    kl ? kl->rowptr_t[l] : rowptr_t, kl ? kl->col_t[l] : col_t, kl ? nullptr : use_transposed_flag, N, w.S);
                 GM_LAUNCH_CHECK();
             }
         }
@@ -810,6 +812,20 @@ int gm_net_backward(const GmParams *p, const GmParams *grads, const float *x_con
     return net_backward_impl(p, grads, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, rowptr, col, rowptr_t,
                              col_t, use_transposed_flag, nullptr, 0, N, node_perm, training, apply_sigmoid, aggr, fwd_ws,
                              fwd_ws_bytes, bwd_ws, bwd_ws_bytes, out, grad_out, stream);
+}
+
+int gm_net_backward_knn(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
+                        const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride, int N, int k, int training,
+                        int apply_sigmoid, int aggr, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws,
+                        size_t bwd_ws_bytes, const void *knn_ws, size_t knn_ws_bytes, const float *out,
+                        const float *grad_out, void *stream) {
+    if (!knn_ws || !p) return GM_ERR_INVALID_ARGUMENT;
+    if (knn_ws_bytes < knn_layers_layout(N, p->conv_depth, k, nullptr, nullptr)) return GM_ERR_CAPACITY;
+    KnnLayers kl;
+    knn_layers_layout(N, p->conv_depth, k, (char *)knn_ws, &kl);
+    return net_backward_impl(p, grads, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, nullptr, nullptr,
+                             nullptr, nullptr, nullptr, nullptr, 0, N, nullptr, training, apply_sigmoid, aggr, fwd_ws,
+                             fwd_ws_bytes, bwd_ws, bwd_ws_bytes, out, grad_out, stream, &kl);
 }
 
 int gm_net_backward_geo(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,

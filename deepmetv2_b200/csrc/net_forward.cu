@@ -778,10 +778,16 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
                             const float *x_cat_f32, int x_cat_stride, const int *rowptr, const int *col,
                             const void *geo_ws, int B, int N, const int *node_perm, int training,
                             int save_for_backward, int apply_sigmoid, int aggr, int precision, float momentum,
-                            float eps, void *ws, size_t ws_bytes, float *out, int *err_flags, void *stream) {
+                            float eps, void *ws, size_t ws_bytes, float *out, int *err_flags, void *stream,
+                            const int *knn_ptr = nullptr, int knn_k = 0, void *knn_ws = nullptr) {
     GM_TRY(check_params(p));
+    KnnLayers kl{};
+    if (knn_ptr) {        // per-layer dynamic k-NN graph in the embedding space (fp32, caller node order)
+        if (knn_k < 1 || knn_k > 32 || !knn_ws || B < 1 || node_perm || precision != GM_PREC_FP32 || geo_ws) return GM_ERR_UNSUPPORTED;
+        knn_layers_layout(N, p->conv_depth, knn_k, (char *)knn_ws, &kl);
+    }
     if (N < 0 || !ws || !err_flags) return GM_ERR_INVALID_ARGUMENT;
-    if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || (!rowptr && !geo_ws) || !out)) return GM_ERR_INVALID_ARGUMENT;
+    if (N > 0 && (!x_cont || (!x_cat_i64 && !x_cat_f32) || (!rowptr && !geo_ws && !knn_ptr) || !out)) return GM_ERR_INVALID_ARGUMENT;
     if (geo_ws && !node_perm) return GM_ERR_UNSUPPORTED;
     // per-edge tcgen05 on the implicit graph: tf32 / bf16; training (arg-max + BatchNorm moments) for aggr = max
     if (geo_ws && precision != GM_PREC_FP32 &&
@@ -833,8 +839,17 @@ static int net_forward_impl(const GmParams *p, const float *x_cont, int x_cont_s
             }
             AggrTail tail{};
             if (training) tail = AggrTail{w.partials, w.counters + 1 + l, p->conv_bn[l], momentum, eps, stat_out};
+            if (knn_ptr) {   // knn_graph(emb_l, k, batch, loop=True): the layer's own graph, kept for the backward
+                TimedRegion trg(GM_TIMER_RADIUS_GRAPH, st);
+                GM_TRY(gm_knn_graph_count(w.emb[l], H, H, knn_ptr, N, B, knn_k, 1, kl.knn_ws, kl.knn_bytes, kl.rowptr[l], stream));
+                GM_TRY(gm_knn_graph_fill(N, knn_k, 1, kl.knn_ws, kl.knn_bytes, kl.rowptr[l], kl.col[l], kl.ecap, nullptr, stream));
+                if (save_for_backward)
+                    GM_TRY(gm_csr_transpose(kl.rowptr[l], kl.col[l], N, kl.ecap, kl.csr_ws, kl.csr_bytes, kl.rowptr_t[l],
+                                            kl.col_t[l], nullptr, stream));
+            }
             TimedRegion tr(GM_TIMER_EDGECONV_FWD, st);
             if (geo_ws) GM_TRY(geo_edge_aggr(aggr, w.Y, w.P, geo_ws, N, B, w.conv[l], arg, tail, st));
+            else if (knn_ptr) GM_TRY(edge_aggr(aggr, w.Y, w.P, kl.rowptr[l], kl.col[l], N, w.conv[l], arg, tail, st));
             else GM_TRY(edge_aggr(aggr, w.Y, w.P, rowptr, col, N, w.conv[l], arg, tail, st));
         } else if (geo_ws) {
             {
@@ -899,6 +914,21 @@ int gm_net_forward_geo(const GmParams *p, const float *x_cont, int x_cont_stride
     return net_forward_impl(p, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, nullptr, nullptr, geo_ws, B, N,
                             node_perm, training, save_for_backward, apply_sigmoid, aggr, precision, momentum, eps,
                             ws, ws_bytes, out, err_flags, stream);
+}
+
+size_t gm_net_knn_ws_bytes(int N, int conv_depth, int k) {
+    return knn_layers_layout(N < 0 ? 0 : N, conv_depth, k < 1 ? 1 : k, nullptr, nullptr);
+}
+
+int gm_net_forward_knn(const GmParams *p, const float *x_cont, int x_cont_stride, const int64_t *x_cat_i64,
+                       const float *x_cat_f32, int x_cat_stride, const int *ptr, int N, int B, int k, int training,
+                       int save_for_backward, int apply_sigmoid, int aggr, float momentum, float eps, void *ws,
+                       size_t ws_bytes, void *knn_ws, size_t knn_ws_bytes, float *out, int *err_flags, void *stream) {
+    if (!ptr || B < 1 || !knn_ws || !p) return GM_ERR_INVALID_ARGUMENT;
+    if (knn_ws_bytes < knn_layers_layout(N, p->conv_depth, k, nullptr, nullptr)) return GM_ERR_CAPACITY;
+    return net_forward_impl(p, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, nullptr, nullptr, nullptr, B, N,
+                            nullptr, training, save_for_backward, apply_sigmoid, aggr, GM_PREC_FP32, momentum, eps, ws,
+                            ws_bytes, out, err_flags, stream, ptr, k, knn_ws);
 }
 
 int gm_edgeconv_forward_geo(const float *x, const void *geo_ws, int N, int B, const float *W, const float *b, int aggr,

@@ -116,6 +116,34 @@ __device__ __forceinline__ void bn_finalize_cta(const float *__restrict__ partia
     __syncthreads();
 }
 
+// Per-layer DYNAMIC k-NN graphs (row f4: model/graph_met_network.py:63, knn_graph(emb, k, batch, loop=True) rebuilt from
+// every layer's input embedding): CSR by target and, for the backward, its transpose, kept per layer.
+struct KnnLayers {
+    int *rowptr[GM_MAX_CONV_DEPTH], *col[GM_MAX_CONV_DEPTH], *rowptr_t[GM_MAX_CONV_DEPTH], *col_t[GM_MAX_CONV_DEPTH];
+    char *knn_ws, *csr_ws;
+    size_t knn_bytes, csr_bytes;
+    long long ecap;
+};
+inline size_t knn_layers_layout(int N, int depth, int k, char *base, KnnLayers *w) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return base ? base + o : (char *)nullptr; };
+    const size_t n = (size_t)(N > 0 ? N : 1);
+    KnnLayers t{};
+    t.ecap = (long long)n * k;
+    for (int l = 0; l < depth; ++l) {
+        t.rowptr[l] = (int *)take((n + 1) * 4);
+        t.col[l] = (int *)take((size_t)t.ecap * 4);
+        t.rowptr_t[l] = (int *)take((n + 1) * 4);
+        t.col_t[l] = (int *)take((size_t)t.ecap * 4);
+    }
+    t.knn_bytes = gm_knn_graph_ws_bytes((int)n, k, 1);
+    t.knn_ws = take(t.knn_bytes);
+    t.csr_bytes = gm_csr_ws_bytes((int)n, t.ecap);
+    t.csr_ws = take(t.csr_bytes);
+    if (w) *w = t;
+    return off;
+}
+
 struct AggrTail {   // BatchNorm epilogue of the EdgeConv output (train mode); partials == NULL otherwise
     float *partials; int *counter; GmBatchNorm bn; float momentum, eps; float *stat;
 };

@@ -62,14 +62,15 @@ class FusedAdamW(torch.optim.Optimizer):
 class GraphMETTrainer:
     def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, r=0.4,
                  max_num_neighbors=255, loop=True, phi_wrap=False, process_group=None, device=None,
-                 graph="implicit", fused_allreduce=True):
+                 graph="implicit", fused_allreduce=True, knn_k=20):
         self.model = model
         self.net = model.graphnet if hasattr(model, "graphnet") else model
         self.apply_sigmoid = hasattr(model, "graphnet")       # Net applies the sigmoid, GraphMETNetwork does not
         self.r, self.max_nn, self.loop, self.phi_wrap = r, max_num_neighbors, loop, phi_wrap
-        if graph not in ("implicit", "csr"):
-            raise ValueError("graph must be 'implicit' or 'csr'")
-        self.graph = graph
+        if graph not in ("implicit", "csr", "knn"):
+            raise ValueError("graph must be 'implicit', 'csr' or 'knn'")
+        self.graph = graph        # "knn": the per-layer dynamic graph of model/graph_met_network.py:63 (row f4)
+        self.knn_k = int(knn_k)
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.rank = torch.distributed.get_rank(process_group) if process_group is not None else 0
@@ -215,7 +216,8 @@ class GraphMETTrainer:
 
     def _reserve(self, N: int, B: int, max_event_nodes: int):
         implicit = self._implicit()
-        E = 0 if implicit else N * min(self.max_nn + (0 if self.loop else 1), max(max_event_nodes, 1))
+        knn = self.graph == "knn"
+        E = 0 if (implicit or knn) else N * min(self.max_nn + (0 if self.loop else 1), max(max_event_nodes, 1))
         if N <= self._cap_nodes and B <= self._cap_events and E <= self._cap_edges and \
                 implicit == self._cap_implicit:
             return
@@ -226,6 +228,8 @@ class GraphMETTrainer:
         if implicit:      # no edge list: O(N) state only
             self.geo_ws = u8(l.gm_geo_ws_bytes(N, B))
             self.perm = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
+        elif knn:         # per-layer k-NN CSR + transposes
+            self.knn_ws = u8(l.gm_net_knn_ws_bytes(N, depth, self.knn_k))
         else:
             self.rg_ws = u8(l.gm_radius_graph_ws_bytes(N, B))
             self.rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
@@ -242,6 +246,9 @@ class GraphMETTrainer:
 
     # ------------------------------------------------------------------------------------------ pieces
     def _graph(self, x, ptr_i32, N, B, max_event_nodes, need_transpose):
+        if self.graph == "knn":      # the graphs are built layer by layer inside the forward
+            self._knn_ptr, self._knn_B = ptr_i32, B
+            return
         l, st = lib(), stream(self.device)
         check(l.gm_prepare_etaphi(ptr(x), x.stride(0), N, ptr(self.etaphi), st), "gm_prepare_etaphi")
         if self._implicit():
@@ -261,6 +268,16 @@ class GraphMETTrainer:
 
     def _forward(self, x, N, B, training, save):
         net = self.net
+        if self.graph == "knn":
+            if net.edge_precision != "fp32":
+                raise NotImplementedError("graph='knn' runs the fp32 EdgeConv")
+            check(lib().gm_net_forward_knn(C.byref(self._P), ptr(x), x.stride(0), None, x.data_ptr() + 8 * 4, x.stride(0),
+                                           ptr(self._knn_ptr), N, B, self.knn_k, int(training), int(save),
+                                           int(self.apply_sigmoid), AGGR[net.aggr], float(net.bn_all.momentum),
+                                           float(net.bn_all.eps), ptr(self.fwd_ws), self.fwd_ws.numel(), ptr(self.knn_ws),
+                                           self.knn_ws.numel(), ptr(self.weights), ptr(self.flags), stream(self.device)),
+                  "gm_net_forward_knn")
+            return
         if self._implicit():
             check(lib().gm_net_forward_geo(C.byref(self._P), ptr(x), x.stride(0), None, x.data_ptr() + 8 * 4,
                                            x.stride(0), ptr(self.geo_ws), N, B, ptr(self.perm), int(training),
@@ -278,6 +295,13 @@ class GraphMETTrainer:
 
     def _backward(self, x, N, B):
         net, l, st = self.net, lib(), stream(self.device)
+        if self.graph == "knn":
+            check(l.gm_net_backward_knn(C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), None, x.data_ptr() + 32,
+                                        x.stride(0), N, self.knn_k, 1, int(self.apply_sigmoid), AGGR[net.aggr],
+                                        ptr(self.fwd_ws), self.fwd_ws.numel(), ptr(self.bwd_ws), self.bwd_ws.numel(),
+                                        ptr(self.knn_ws), self.knn_ws.numel(), ptr(self.weights), ptr(self.grad_w), st),
+                  "gm_net_backward_knn")
+            return
         if self._implicit():
             check(l.gm_net_backward_geo(C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), None,
                                         x.data_ptr() + 32, x.stride(0), ptr(self.geo_ws), N, B, ptr(self.perm), 1,
@@ -313,6 +337,7 @@ class GraphMETTrainer:
         self.net.train()
         l, st = lib(), stream(self.device)
         dp = self.world > 1
+        self._last_N = N
         if N > 0 and B > 0:
             self._reserve(N, B, men)
             self._graph(x, p, N, B, men, need_transpose=True)
@@ -408,6 +433,18 @@ class GraphMETTrainer:
         check(lib().gm_met_loss(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
                                 ptr(self.met), ptr(self.loss), None, stream(self.device)), "gm_met_loss")
         return self.weights[:N], self.loss, self.met[:B]
+
+    def knn_layer_graph(self, layer: int):
+        """(rowptr [N+1], col [E]) int32 of the k-NN graph EdgeConv layer ``layer`` used in the last step (graph="knn";
+        synchronises; tests / inspection).  Mirrors knn_layers_layout in csrc/net_layout.cuh."""
+        N, k = self._last_N, self.knn_k
+        al = lambda v: (v + 255) // 256 * 256  # noqa: E731
+        per_layer = 2 * (al((N + 1) * 4) + al(N * k * 4))
+        off = layer * per_layer
+        rowptr = self.knn_ws[off:off + (N + 1) * 4].view(torch.int32).clone()
+        off += al((N + 1) * 4)
+        E = int(rowptr[-1])
+        return rowptr, self.knn_ws[off:off + E * 4].view(torch.int32).clone()
 
     def graph_stats(self):
         """(E, max degree before the cap, #capped nodes, flags) of the last batch — synchronises.  On the

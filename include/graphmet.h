@@ -283,6 +283,26 @@ int gm_edgeconv_forward_geo(const float *x, const void *geo_ws, int N, int B, co
                             int aggr, int precision, void *ws, size_t ws_bytes, float *out, int *arg_out,
                             void *stream);
 
+/* ---------------------------------------------------------------------------------
+ * f4. The per-layer DYNAMIC graph sketched at model/graph_met_network.py:63:
+ *     emb = emb + BN(EdgeConv(emb, knn_graph(emb, k=20, batch=batch, loop=True)))
+ * gm_net_forward_knn / gm_net_backward_knn are gm_net_forward / gm_net_backward with every EdgeConv layer rebuilding
+ * its graph from its own input embedding (32-d k-NN per event, csrc/knn.cu; bit-identical to torch_cluster's
+ * semantics as restated in oracle/knn_bruteforce.c).  The layer graphs (CSR by target and, when save_for_backward,
+ * their transposes -- a k-NN graph is asymmetric) stay in knn_ws (gm_net_knn_ws_bytes(N, conv_depth, k)) between the
+ * forward and the backward.  fp32, aggr = max for the backward, nodes in the caller's order, k <= 32.
+ * --------------------------------------------------------------------------------- */
+size_t gm_net_knn_ws_bytes(int N, int conv_depth, int k);
+int gm_net_forward_knn(const GmParams *p, const float *x_cont, int x_cont_stride, const int64_t *x_cat_i64,
+                       const float *x_cat_f32, int x_cat_stride, const int *ptr, int N, int B, int k, int training,
+                       int save_for_backward, int apply_sigmoid, int aggr, float momentum, float eps, void *ws,
+                       size_t ws_bytes, void *knn_ws, size_t knn_ws_bytes, float *out, int *err_flags, void *stream);
+int gm_net_backward_knn(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
+                        const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride, int N, int k, int training,
+                        int apply_sigmoid, int aggr, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws,
+                        size_t bwd_ws_bytes, const void *knn_ws, size_t knn_ws_bytes, const float *out,
+                        const float *grad_out, void *stream);
+
 /* CSR (by target) -> CSR of the transposed graph (by source), targets ascending per row.
  * ws: gm_csr_ws_bytes(N, E). Needed by the backward only when GM_FLAG_DEGREE_CAPPED was raised;
  * with only_if_flag the kernels are no-ops unless *only_if_flag != 0 (E is then a capacity). */

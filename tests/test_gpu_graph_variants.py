@@ -75,3 +75,53 @@ def test_dynamic_knn_network_forward_matches_oracle():
     assert same > 0.999, same
     err = (out.cpu() - out_ref).abs().max().item() / out_ref.abs().max().item()
     assert err < 1e-3, err
+
+
+def test_knn_trainer_step_matches_oracle_autograd():
+    """Row f4: the per-layer dynamic k-NN EdgeConv inside the fused trainer (graph="knn"), forward AND backward over the
+    asymmetric k-NN CSR.  The oracle runs graph_met_network.py:57-65 with the commented line switched on, on the graphs
+    our step used (a k-NN search is not differentiable, so the graphs are constants of the autograd graph); those graphs
+    are themselves checked against the oracle's search on the oracle's embeddings (identical up to fp near-ties)."""
+    from deepmetv2_b200.trainer import GraphMETTrainer
+    torch.manual_seed(2)
+    b = synth.make_batch(3, "dytt", seed=79, sizes=[400, 15, 330])      # one event smaller than k
+    x_cont, x_cat, _ = O.prepare_inputs(b.x)
+    ref = O.Net(8, 3).train()
+    ours = gnet.Net(8, 3); ours.load_state_dict(ref.state_dict()); ours.to(DEV)
+    tr = GraphMETTrainer(ours, lr=0.0, weight_decay=0.0, graph="knn", knn_k=20)
+    loss = tr.train_step(b.to(DEV))
+    torch.cuda.synchronize()
+    graphs = []
+    for l in range(2):
+        rowptr, col = tr.knn_layer_graph(l)
+        rowptr, col = rowptr.cpu().long(), col.cpu().long()
+        tgt = torch.repeat_interleave(torch.arange(rowptr.numel() - 1), rowptr[1:] - rowptr[:-1])
+        graphs.append(torch.stack([col, tgt], 0))
+
+    gn = ref.graphnet
+    emb_cont = gn.embed_continuous(x_cont)
+    pdg = torch.abs(x_cat[:, 0])
+    for i, k in enumerate(gn.pdgs):
+        pdg = torch.where(pdg == k, torch.full_like(pdg, i), pdg)
+    emb_cat = gn.embed_categorical(torch.cat([gn.embed_charge(x_cat[:, 1] + 1), gn.embed_pdgid(pdg), gn.embed_pv(x_cat[:, 2])], 1))
+    emb = gn.bn_all(gn.encode_all(torch.cat([emb_cat, emb_cont], 1)))
+    for l, conv in enumerate(gn.conv_continuous):
+        ei_ref = O.knn_graph(emb.detach(), 20, b.batch, loop=True)
+        assert ei_ref.shape == graphs[l].shape
+        assert (ei_ref == graphs[l]).all(0).float().mean().item() > 0.995, l
+        emb = emb + conv[1](conv[0](emb, graphs[l]))
+    w_ref = torch.sigmoid(gn.output(emb).squeeze(-1))
+    loss_ref = O.loss_fn(w_ref, b.x, b.y, b.batch)
+    loss_ref.backward()
+    assert abs(loss.item() - loss_ref.item()) < 1e-3 * abs(loss_ref.item())
+    grads = {k: g for (k, _), g in zip(ours.graphnet.named_parameters(), tr._gviews)}
+    named = dict(ref.graphnet.named_parameters())
+    for k, p in named.items():
+        scale = p.grad.abs().max().clamp_min(1e-12)
+        if k.endswith("nn.0.bias"):       # feeds a train-mode BatchNorm: the true gradient is 0
+            scale = named[k.replace("nn.0.bias", "nn.0.weight")].grad.abs().max()
+        err = float((grads[k].cpu() - p.grad).abs().max() / scale)
+        assert err < 1e-3, (k, err)
+    # eval step through the same graph mode
+    w, l2, _ = tr.eval_step(b.to(DEV))
+    assert torch.isfinite(w).all() and torch.isfinite(l2)
