@@ -11,7 +11,8 @@
 //   k_drn_apply    x_out[i] = BN(max or min), rows that straddle tiles folded from the per-tile head / tail partials
 //   k_drn_head     global max pool per event + output MLP (64->64->32->OD) + softplus / pi(2 sigmoid - 1)
 // No atomics on floats, every reduction in a fixed order: the forward is bit-deterministic run to run.
-#include "common.cuh"
+#include "geo_stage.cuh"
+#include "tc_ptx.cuh"
 
 namespace gm {
 
@@ -182,6 +183,75 @@ constexpr int LD_H1 = 100, LD_H2 = 68;
 constexpr int ES_W2 = DM * DH, ES_H = DT * LD_H1, ES_MOM = 8 * DH * 2;
 constexpr size_t EDGE_SMEM = (size_t)(ES_W2 + DH + ES_H + ES_MOM) * 4 + (size_t)(2 * DT + DT + 2 + 8) * 4;
 
+// Shared tail of the per-edge kernels: the finished h2 tile ([128][LD_H2] fp32 in shared memory, rows = edges in CSR
+// order) -> per-tile BatchNorm moments folded into the CTA's running moments, and per-target max / min written to the
+// row's slot (inside the tile) or the tile's head / tail partial (rows that straddle tiles).
+template <bool STATS, int NT>
+__device__ __forceinline__ void edge_tile_reduce(const float *sH, const int *sTgt, int *sSrc, int *sSeg, int *sCnt, float *sMom,
+                                                 int ne, long long e0, int tile, const int *__restrict__ rowptr,
+                                                 const EdgeOut &o, int tiles_cap, Moments &cta_m) {
+    constexpr int PARTS = NT / DH;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < DT) {                                       // segment starts (rows of one target are consecutive)
+        const bool start = tid < ne && (tid == 0 || sTgt[tid] != sTgt[tid - 1]);
+        const unsigned m = __ballot_sync(0xffffffffu, start);
+        if (lane == 0) sCnt[warp] = __popc(m);
+        sSrc[tid] = start ? (int)__popc(m & ((1u << lane) - 1u)) : -1;         // sSrc is free now: rank inside the warp
+    }
+    __syncthreads();
+    if (tid < DT && sSrc[tid] >= 0) {
+        int prefix = 0;
+        for (int w = 0; w < warp; ++w) prefix += sCnt[w];
+        sSeg[prefix + sSrc[tid]] = tid;
+    }
+    const int nseg = sCnt[0] + sCnt[1] + sCnt[2] + sCnt[3];
+    if (tid == 0) sSeg[nseg] = ne;
+    if constexpr (STATS) {                                // per-tile BatchNorm moments, two-pass per row slice
+        const int c = tid & (DH - 1), part = tid >> 6;
+        float s = 0.f;
+        int cnt = 0;
+        for (int r = part; r < ne; r += PARTS) { s += sH[r * LD_H2 + c]; ++cnt; }
+        const float mean = cnt ? s / (float)cnt : 0.f;
+        float m2 = 0.f;
+        for (int r = part; r < ne; r += PARTS) { const float d = sH[r * LD_H2 + c] - mean; m2 = fmaf(d, d, m2); }
+        sMom[(part * DH + c) * 2] = mean;
+        sMom[(part * DH + c) * 2 + 1] = m2;
+    }
+    __syncthreads();
+    if constexpr (STATS) {
+        if (tid < DH) {
+            Moments m{0.f, 0.f, 0.f};
+            for (int part = 0; part < PARTS; ++part) {
+                const int cnt = part < ne ? (ne - part + PARTS - 1) / PARTS : 0;
+                m = moments_combine(m, Moments{(float)cnt, sMom[(part * DH + tid) * 2], sMom[(part * DH + tid) * 2 + 1]});
+            }
+            cta_m = moments_combine(cta_m, m);
+        }
+    }
+    for (int p = tid; p < nseg * DH; p += NT) {
+        const int s = p >> 6, c = p & (DH - 1);
+        const int r0 = sSeg[s], r1 = sSeg[s + 1];
+        float vmax = -INFINITY, vmin = INFINITY;
+        for (int r = r0; r < r1; ++r) {
+            const float v = sH[r * LD_H2 + c];
+            vmax = fmaxf(vmax, v);
+            vmin = fminf(vmin, v);
+        }
+        const int i = sTgt[r0];
+        const long long a = rowptr[i], b = rowptr[i + 1];
+        if (a < e0) {
+            o.bmx[((size_t)tile) * DH + c] = vmax;
+            o.bmn[((size_t)tile) * DH + c] = vmin;
+        } else if (b > e0 + DT) {
+            o.bmx[((size_t)tiles_cap + tile) * DH + c] = vmax;
+            o.bmn[((size_t)tiles_cap + tile) * DH + c] = vmin;
+        } else {
+            o.mx[(size_t)i * DH + c] = vmax;
+            o.mn[(size_t)i * DH + c] = vmin;
+        }
+    }
+}
+
 template <bool STATS>
 __global__ void __launch_bounds__(DTHREADS, 2) k_drn_edge(const float *__restrict__ ab, const int *__restrict__ rowptr,
                                                           const int *__restrict__ row, const int *__restrict__ col, int N,
@@ -190,7 +260,7 @@ __global__ void __launch_bounds__(DTHREADS, 2) k_drn_edge(const float *__restric
     extern __shared__ __align__(16) float s_edge[];
     float *sW2 = s_edge, *sb2 = sW2 + ES_W2, *sH = sb2 + DH, *sMom = sH + ES_H;
     int *sTgt = reinterpret_cast<int *>(sMom + ES_MOM), *sSrc = sTgt + DT, *sSeg = sSrc + DT, *sCnt = sSeg + DT + 2;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     stage_kmajor(w2, DH, DM, DM, sW2, DH, 0);
     if (tid < DH) sb2[tid] = b2[tid];
     pdl_sync();
@@ -231,64 +301,7 @@ __global__ void __launch_bounds__(DTHREADS, 2) k_drn_edge(const float *__restric
         for (int i = 0; i < 4; ++i)
             *reinterpret_cast<float4 *>(sH + (ng + 32 * i) * LD_H2 + 4 * og) =
                 make_float4(elu(acc[i][0]), elu(acc[i][1]), elu(acc[i][2]), elu(acc[i][3]));
-        if (tid < DT) {                                   // segment starts (rows of one target are consecutive)
-            const bool start = tid < ne && (tid == 0 || sTgt[tid] != sTgt[tid - 1]);
-            const unsigned m = __ballot_sync(0xffffffffu, start);
-            if (lane == 0) sCnt[warp] = __popc(m);
-            sSrc[tid] = start ? (int)__popc(m & ((1u << lane) - 1u)) : -1;     // sSrc is free now: rank inside the warp
-        }
-        __syncthreads();
-        if (tid < DT && sSrc[tid] >= 0) {
-            int prefix = 0;
-            for (int w = 0; w < warp; ++w) prefix += sCnt[w];
-            sSeg[prefix + sSrc[tid]] = tid;
-        }
-        const int nseg = sCnt[0] + sCnt[1] + sCnt[2] + sCnt[3];
-        if (tid == 0) sSeg[nseg] = ne;
-        if constexpr (STATS) {                            // per-tile BatchNorm moments, two-pass per 8-row slice
-            const int c = tid & (DH - 1), part = tid >> 6;
-            float s = 0.f;
-            int cnt = 0;
-            for (int r = part; r < ne; r += 8) { s += sH[r * LD_H2 + c]; ++cnt; }
-            const float mean = cnt ? s / (float)cnt : 0.f;
-            float m2 = 0.f;
-            for (int r = part; r < ne; r += 8) { const float d = sH[r * LD_H2 + c] - mean; m2 = fmaf(d, d, m2); }
-            sMom[(part * DH + c) * 2] = mean;
-            sMom[(part * DH + c) * 2 + 1] = m2;
-        }
-        __syncthreads();
-        if constexpr (STATS) {
-            if (tid < DH) {
-                Moments m{0.f, 0.f, 0.f};
-                for (int part = 0; part < 8; ++part) {
-                    const int cnt = part < ne ? (ne - part + 7) / 8 : 0;
-                    m = moments_combine(m, Moments{(float)cnt, sMom[(part * DH + tid) * 2], sMom[(part * DH + tid) * 2 + 1]});
-                }
-                cta_m = moments_combine(cta_m, m);
-            }
-        }
-        for (int p = tid; p < nseg * DH; p += DTHREADS) {
-            const int s = p >> 6, c = p & (DH - 1);
-            const int r0 = sSeg[s], r1 = sSeg[s + 1];
-            float vmax = -INFINITY, vmin = INFINITY;
-            for (int r = r0; r < r1; ++r) {
-                const float v = sH[r * LD_H2 + c];
-                vmax = fmaxf(vmax, v);
-                vmin = fminf(vmin, v);
-            }
-            const int i = sTgt[r0];
-            const long long a = rowptr[i], b = rowptr[i + 1];
-            if (a < e0) {
-                o.bmx[((size_t)tile) * DH + c] = vmax;
-                o.bmn[((size_t)tile) * DH + c] = vmin;
-            } else if (b > e0 + DT) {
-                o.bmx[((size_t)tiles_cap + tile) * DH + c] = vmax;
-                o.bmn[((size_t)tiles_cap + tile) * DH + c] = vmin;
-            } else {
-                o.mx[(size_t)i * DH + c] = vmax;
-                o.mn[(size_t)i * DH + c] = vmin;
-            }
-        }
+        edge_tile_reduce<STATS, DTHREADS>(sH, sTgt, sSrc, sSeg, sCnt, sMom, ne, e0, tile, rowptr, o, tiles_cap, cta_m);
     }
     if constexpr (STATS) {
         if (tid < DH) {
@@ -297,6 +310,138 @@ __global__ void __launch_bounds__(DTHREADS, 2) k_drn_edge(const float *__restric
             o.tmom[((size_t)blockIdx.x * 3 + 2) * DH + tid] = cta_m.m2;
         }
     }
+}
+
+// ------------------------------------------------------------------------------------------ per-edge MLP on tcgen05
+// The same tile as k_drn_edge with the 96 -> 64 contraction on the 5th-generation tensor cores (bf16 operands, fp32
+// accumulation in TMEM): this is the NON-separable edge MLP, the case a per-edge tensor-core contraction exists for.
+//   A = h1 tile   [128 edges x 96] bf16, built by all threads (gather A_i + B_j, ELU, round) straight into the canonical
+//       K-major no-swizzle layout (8-row x 16-byte core matrices; LBO 128 B between K chunks, SBO 1536 B between row groups)
+//   B = W2        [64 x 96] bf16, staged once per CTA in the same layout
+//   D = A . B^T   [128 lanes x 64 columns] fp32 in TMEM: 6 tcgen05.mma (M 128, N 64, K 16) issued by one thread, one commit
+//   epilogue      8 warps: tcgen05.ld 32x32b.x32 (lane = edge row, 32 channel columns), + b2, ELU -> the fp32 h2 tile in
+//                 shared memory, then the shared segmented max / min + BatchNorm-moment tail.
+constexpr int TC_THREADS = 256;
+constexpr int TC_LBO = 128, TC_SBO = (DM / 8) * TC_LBO;               // 12 K chunks of 8 bf16
+constexpr int TC_B_BYTES = (DH / 8) * TC_SBO;      // (the A operand: (DT / 8) * TC_SBO = 24 KB)
+// the fp32 h2 tile reuses the A operand's storage (the tensor core is done with A when the epilogue starts)
+constexpr size_t TC_OFF_B = 0, TC_OFF_A = TC_B_BYTES, TC_OFF_H2 = TC_OFF_A, TC_OFF_MOM = TC_OFF_H2 + (size_t)DT * LD_H2 * 4,
+                 TC_OFF_B2 = TC_OFF_MOM + (size_t)ES_MOM * 4, TC_OFF_INT = TC_OFF_B2 + DH * 4,
+                 TC_OFF_BAR = (TC_OFF_INT + (size_t)(3 * DT + 2 + 8) * 4 + 7) / 8 * 8, TC_SMEM = TC_OFF_BAR + 16;
+
+__device__ __forceinline__ uint64_t drn_smem_desc(uint32_t addr) {
+    uint64_t d = (uint64_t)((addr >> 4) & 0x3FFF);
+    d |= (uint64_t)(TC_LBO >> 4) << 16;
+    d |= (uint64_t)(TC_SBO >> 4) << 32;
+    d |= 1ull << 46;                                                  // descriptor version (sm_100); SWIZZLE_NONE
+    return d;
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(TC_THREADS, 4) k_drn_edge_tc(const float *__restrict__ ab, const int *__restrict__ rowptr,
+                                                               const int *__restrict__ row, const int *__restrict__ col, int N,
+                                                               long long capacity, const float *__restrict__ w2,
+                                                               const float *__restrict__ b2, EdgeOut o, int tiles_cap) {
+    extern __shared__ __align__(128) unsigned char s_tc[];
+    float *sH2 = reinterpret_cast<float *>(s_tc + TC_OFF_H2), *sMom = reinterpret_cast<float *>(s_tc + TC_OFF_MOM),
+          *sb2 = reinterpret_cast<float *>(s_tc + TC_OFF_B2);
+    int *sTgt = reinterpret_cast<int *>(s_tc + TC_OFF_INT), *sSrc = sTgt + DT, *sSeg = sSrc + DT, *sCnt = sSeg + DT + 2;
+    const uint32_t a_base = smem_u32(s_tc + TC_OFF_A), b_base = smem_u32(s_tc + TC_OFF_B), bar = smem_u32(s_tc + TC_OFF_BAR);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // ---- one-time setup: barrier, TMEM (64 fp32 columns), W2 as the bf16 B operand, b2
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tc5_alloc(smem_u32(s_tc + TC_OFF_BAR + 8), 64);
+    for (int t = tid; t < DH * (DM / 8); t += TC_THREADS) {
+        const int n = t / (DM / 8), q = t - n * (DM / 8);
+        const float4 w0 = *reinterpret_cast<const float4 *>(w2 + (size_t)n * DM + 8 * q);
+        const float4 w1 = *reinterpret_cast<const float4 *>(w2 + (size_t)n * DM + 8 * q + 4);
+        const uint32_t addr = b_base + (uint32_t)((n >> 3) * TC_SBO + q * TC_LBO + (n & 7) * 16);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(tc5_pack_bf16(w0.x, w0.y)),
+                     "r"(tc5_pack_bf16(w0.z, w0.w)), "r"(tc5_pack_bf16(w1.x, w1.y)), "r"(tc5_pack_bf16(w1.z, w1.w)) : "memory");
+    }
+    if (tid < DH) sb2[tid] = b2[tid];
+    tc5_fence_async_smem();
+    tc5_fence_before();
+    __syncthreads();
+    tc5_fence_after();
+    pdl_sync();
+    const uint32_t tmem = *reinterpret_cast<const uint32_t *>(s_tc + TC_OFF_BAR + 8);
+    // instruction descriptor: fp32 accumulate, bf16 A and B, both K-major, N = 64, M = 128
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(DH >> 3) << 17) | ((uint32_t)(DT >> 4) << 24);
+    const uint64_t adesc0 = drn_smem_desc(a_base), bdesc0 = drn_smem_desc(b_base);
+    long long E = rowptr[N];
+    if (E > capacity) E = capacity;
+    const int ntiles = (int)((E + DT - 1) / DT);
+    Moments cta_m{0.f, 0.f, 0.f};
+    uint32_t parity = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long e0 = (long long)tile * DT;
+        const int ne = (int)min((long long)DT, E - e0);
+        if (tid < DT) {
+            sTgt[tid] = tid < ne ? row[e0 + tid] : -1;
+            sSrc[tid] = tid < ne ? col[e0 + tid] : -1;
+        }
+        __syncthreads();
+        // A operand: h1 = ELU(A_i + B_j) rounded to bf16, 8 values (one 16-byte K chunk of one row) per item
+        for (int it = tid; it < DT * (DM / 8); it += TC_THREADS) {
+            const int e = it / (DM / 8), q = it - e * (DM / 8);
+            uint32_t p0 = 0, p1 = 0, p2 = 0, p3 = 0;
+            if (e < ne) {
+                const float4 *pa = reinterpret_cast<const float4 *>(ab + (size_t)sTgt[e] * AB_W + 8 * q);
+                const float4 *pb = reinterpret_cast<const float4 *>(ab + (size_t)sSrc[e] * AB_W + DM + 8 * q);
+                const float4 a0 = pa[0], a1 = pa[1], c0 = pb[0], c1 = pb[1];
+                p0 = tc5_pack_bf16(elu_fast(a0.x + c0.x), elu_fast(a0.y + c0.y));
+                p1 = tc5_pack_bf16(elu_fast(a0.z + c0.z), elu_fast(a0.w + c0.w));
+                p2 = tc5_pack_bf16(elu_fast(a1.x + c1.x), elu_fast(a1.y + c1.y));
+                p3 = tc5_pack_bf16(elu_fast(a1.z + c1.z), elu_fast(a1.w + c1.w));
+            }
+            const uint32_t addr = a_base + (uint32_t)((e >> 3) * TC_SBO + q * TC_LBO + (e & 7) * 16);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(p0), "r"(p1), "r"(p2), "r"(p3) : "memory");
+        }
+        tc5_fence_async_smem();                           // generic-proxy stores -> visible to the tensor core's async proxy
+        tc5_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            tc5_fence_after();
+#pragma unroll
+            for (int ks = 0; ks < DM / 16; ++ks)
+                tc5_mma<false>(tmem, adesc0 + (uint64_t)((ks * 2 * TC_LBO) >> 4), bdesc0 + (uint64_t)((ks * 2 * TC_LBO) >> 4), idesc,
+                               ks > 0 ? 1u : 0u);
+            tc5_commit(bar);
+        }
+        mbar_wait(bar, parity, 32);
+        parity ^= 1u;
+        tc5_fence_after();
+        {   // epilogue: warp w reads lane quarter (w & 3), channel columns 32 * (w >> 2) .. + 31
+            const int quarter = warp & 3, cb = warp >> 2;
+            uint32_t r[32];
+            tc5_ld32(tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(cb * 32), r);
+            float *dst = sH2 + (quarter * 32 + lane) * LD_H2 + cb * 32;
+#pragma unroll
+            for (int c = 0; c < 32; c += 4)
+                *reinterpret_cast<float4 *>(dst + c) =
+                    make_float4(elu_fast(__uint_as_float(r[c]) + sb2[cb * 32 + c]), elu_fast(__uint_as_float(r[c + 1]) + sb2[cb * 32 + c + 1]),
+                                elu_fast(__uint_as_float(r[c + 2]) + sb2[cb * 32 + c + 2]), elu_fast(__uint_as_float(r[c + 3]) + sb2[cb * 32 + c + 3]));
+        }
+        tc5_fence_before();
+        __syncthreads();                                  // h2 complete; TMEM and the A tile are free for the next tile
+        edge_tile_reduce<STATS, TC_THREADS>(sH2, sTgt, sSrc, sSeg, sCnt, sMom, ne, e0, tile, rowptr, o, tiles_cap, cta_m);
+        __syncthreads();
+    }
+    if constexpr (STATS) {
+        if (tid < DH) {
+            o.tmom[((size_t)blockIdx.x * 3) * DH + tid] = cta_m.n;
+            o.tmom[((size_t)blockIdx.x * 3 + 1) * DH + tid] = cta_m.mean;
+            o.tmom[((size_t)blockIdx.x * 3 + 2) * DH + tid] = cta_m.m2;
+        }
+    }
+    tc5_fence_before();
+    __syncthreads();
+    tc5_fence_after();
+    if (warp == 0) tc5_dealloc(tmem, 64);
 }
 
 // bnss [4][64] = mean, invstd, gamma, beta of the BatchNorm1d over the edge rows.  Training: the per-CTA Chan moments
@@ -478,19 +623,29 @@ size_t drn_layout(int N, int B, int k, char *base, DrnWs *w) {
 }
 
 int edge_stage(const DrnWs &w, const GmDrnConv &cv, const int *rowptr, const int *col, const int *row, int N, const int *n_dev,
-               int training, float momentum, float eps, float *bnss, float *x_out, cudaStream_t st) {
+               int training, int precision, float momentum, float eps, float *bnss, float *x_out, cudaStream_t st) {
     EdgeOut o{w.mx, w.mn, w.bmx, w.bmn, w.tmom};
     static bool attr = false;
     if (!attr) {
         GM_CUDA_TRY(cudaFuncSetAttribute(k_drn_edge<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EDGE_SMEM));
         GM_CUDA_TRY(cudaFuncSetAttribute(k_drn_edge<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EDGE_SMEM));
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_drn_edge_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM));
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_drn_edge_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM));
         attr = true;
     }
-    int grid = persistent_grid(w.tiles_cap, 2);
+    const bool tc = precision == GM_PREC_BF16;
+    int grid = persistent_grid(w.tiles_cap, tc ? 4 : 2);
     if (grid > MAX_EDGE_CTAS) grid = MAX_EDGE_CTAS;
     {
     TimedRegion tr(GM_TIMER_DRN_EDGE, st);
-    if (training) {
+    if (tc) {
+        if (training)
+            GM_LAUNCH_PDL(k_drn_edge_tc<true>, grid, TC_THREADS, TC_SMEM, st, (const float *)w.ab, rowptr, row, col, N, w.ecap,
+                          (const float *)cv.w2, (const float *)cv.b2, o, w.tiles_cap);
+        else
+            GM_LAUNCH_PDL(k_drn_edge_tc<false>, grid, TC_THREADS, TC_SMEM, st, (const float *)w.ab, rowptr, row, col, N, w.ecap,
+                          (const float *)cv.w2, (const float *)cv.b2, o, w.tiles_cap);
+    } else if (training) {
         GM_LAUNCH_PDL(k_drn_edge<true>, grid, DTHREADS, EDGE_SMEM, st, (const float *)w.ab, rowptr, row, col, N, w.ecap,
                       (const float *)cv.w2, (const float *)cv.b2, o, w.tiles_cap);
     } else {
@@ -524,7 +679,7 @@ int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int
                    size_t ws_bytes, float *out, float *net_out, GmDrnView *view_out, void *stream) {
     if (!p || !ws || N < 1 || B < 1 || !x || !ptr || !out || x_stride < DI) return GM_ERR_INVALID_ARGUMENT;
     if (p->k < 1 || p->k + 1 > 32 || p->output_dim < 1 || p->output_dim > 8) return GM_ERR_UNSUPPORTED;
-    if (precision != GM_PREC_FP32) return GM_ERR_UNSUPPORTED;
+    if (precision != GM_PREC_FP32 && precision != GM_PREC_BF16) return GM_ERR_UNSUPPORTED;   // tf32: not built for the DRN
     if (net_out && p->output_dim != 2) return GM_ERR_INVALID_ARGUMENT;
     if (ws_bytes < drn_layout(N, B, p->k, nullptr, nullptr)) return GM_ERR_CAPACITY;
     cudaStream_t st = as_stream(stream);
@@ -554,7 +709,7 @@ int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int
         GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, nullptr, w.und, w.und_bytes, w.rowptr1, w.col1, w.row1,
                                  w.ecap, nullptr, st));
     }
-    GM_TRY(edge_stage(w, p->conv[0], w.rowptr1, w.col1, w.row1, N, nullptr, training, momentum, eps, w.bnss, w.x1, st));
+    GM_TRY(edge_stage(w, p->conv[0], w.rowptr1, w.col1, w.row1, N, nullptr, training, precision, momentum, eps, w.bnss, w.x1, st));
     {
         TimedRegion tr(GM_TIMER_DRN_POOL, st);
         GM_TRY(drn_normalized_cut(w.x1, DH, DH, w.rowptr1, w.col1, w.row1, N, w.ecap, w.weight1, st));
@@ -579,7 +734,7 @@ int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int
         GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, m_dev, w.und, w.und_bytes, w.rowptr2, w.col2, w.row2,
                                  w.ecap, nullptr, st));
     }
-    GM_TRY(edge_stage(w, p->conv[1], w.rowptr2, w.col2, w.row2, N, m_dev, training, momentum, eps, w.bnss + 4 * DH, w.x2, st));
+    GM_TRY(edge_stage(w, p->conv[1], w.rowptr2, w.col2, w.row2, N, m_dev, training, precision, momentum, eps, w.bnss + 4 * DH, w.x2, st));
     // ---- :98-104: the second clustering cannot change a global maximum; pool per event and run the output MLP
     HeadParams hp{p->out_w[0], p->out_b[0], p->out_w[1], p->out_b[1], p->out_w[2], p->out_b[2], p->output_dim};
     {
