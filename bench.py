@@ -583,7 +583,22 @@ def run_side(workload, precision, rank, world, dev, pg, l, steps, flush, barrier
     return out
 
 
+_REAL_STDOUT = None
+
+
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's "NCCL version ..." banner at
+    communicator creation): everything incidental goes to stderr, the JSON line to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+        sys.stdout = _REAL_STDOUT
+
+
 def main():
+    _claim_stdout()
     if os.environ.get("GM_BENCH_WATCHDOG"):       # debugging aid: dump every thread's stack and exit if the run stalls
         import faulthandler
         faulthandler.dump_traceback_later(int(os.environ["GM_BENCH_WATCHDOG"]), exit=True)
