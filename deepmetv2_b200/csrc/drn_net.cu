@@ -486,14 +486,14 @@ __global__ void __launch_bounds__(1024) k_drn_bn(const int *__restrict__ rowptr,
 
 __global__ void __launch_bounds__(256) k_drn_apply(const int *__restrict__ rowptr, int N, const int *__restrict__ n_dev,
                                                    EdgeOut o, int tiles_cap, const float *__restrict__ bnss,
-                                                   float *__restrict__ x_out) {
+                                                   float *__restrict__ x_out, float *__restrict__ vsel_out) {
     pdl_sync();
     const int n = eff_n(N, n_dev);
     const long long total = (long long)n * DH;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
         const int i = (int)(t >> 6), c = (int)(t & (DH - 1));
         const int a = rowptr[i], b = rowptr[i + 1];
-        float out = 0.f;                                  // no incoming edge: scatter-max leaves 0
+        float out = 0.f, vs = 0.f;                        // no incoming edge: scatter-max leaves 0
         if (b > a) {
             const int t0 = a >> 7, t1 = (b - 1) >> 7;
             float vmax, vmin;
@@ -511,8 +511,10 @@ __global__ void __launch_bounds__(256) k_drn_apply(const int *__restrict__ rowpt
             const float g = bnss[2 * DH + c];
             const float v = g >= 0.f ? vmax : vmin;       // BatchNorm is monotone per channel: max commutes up to the sign
             out = (v - bnss[c]) * bnss[DH + c] * g + bnss[3 * DH + c];
+            vs = v;
         }
         x_out[t] = out;
+        if (vsel_out) vsel_out[t] = vs;                   // the selected (max or min) h2: the backward finds its edge by equality
     }
 }
 
@@ -575,7 +577,7 @@ __global__ void __launch_bounds__(HEAD_PARTS * DH) k_drn_head(const float *__res
 // ------------------------------------------------------------------------------------------ workspace
 constexpr int MAX_EDGE_CTAS = 148 * 4;
 struct DrnWs {
-    float *x0, *ab, *mx, *mn, *bmx, *bmn, *tmom, *bnss, *x1, *weight1, *x1p, *x2, *pooled;
+    float *x0, *ab, *mx, *mn, *bmx, *bmn, *tmom, *bnss, *x1, *weight1, *x1p, *x2, *pooled, *vsel1, *vsel2;
     int *nbr, *deg, *rowptr1, *col1, *row1, *cluster1, *partner1, *scan, *scan_tiles, *ptr1p, *rowptr2, *col2, *row2;
     char *und;
     size_t und_bytes;
@@ -603,6 +605,8 @@ size_t drn_layout(int N, int B, int k, char *base, DrnWs *w) {
     t.x1p = (float *)take(n * DH * 4);
     t.x2 = (float *)take(n * DH * 4);
     t.pooled = (float *)take((size_t)(B > 0 ? B : 1) * DH * 4);
+    t.vsel1 = (float *)take(n * DH * 4);
+    t.vsel2 = (float *)take(n * DH * 4);
     t.nbr = (int *)take(n * K * 4);
     t.deg = (int *)take((n + 1) * 4);
     t.rowptr1 = (int *)take((n + 1) * 4);
@@ -623,7 +627,8 @@ size_t drn_layout(int N, int B, int k, char *base, DrnWs *w) {
 }
 
 int edge_stage(const DrnWs &w, const GmDrnConv &cv, const int *rowptr, const int *col, const int *row, int N, const int *n_dev,
-               int training, int precision, float momentum, float eps, float *bnss, float *x_out, cudaStream_t st) {
+               int training, int precision, float momentum, float eps, float *bnss, float *x_out, float *vsel_out,
+               cudaStream_t st) {
     EdgeOut o{w.mx, w.mn, w.bmx, w.bmn, w.tmom};
     static bool attr = false;
     if (!attr) {
@@ -660,7 +665,7 @@ int edge_stage(const DrnWs &w, const GmDrnConv &cv, const int *rowptr, const int
                   (long long *)cv.bn_num_batches_tracked, bnss);
     GM_LAUNCH_CHECK();
     GM_LAUNCH_PDL(k_drn_apply, persistent_grid(((long long)N * DH + 255) / 256, 8), 256, 0, st, rowptr, N, n_dev, o,
-                  w.tiles_cap, (const float *)bnss, x_out);
+                  w.tiles_cap, (const float *)bnss, x_out, vsel_out);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
@@ -709,7 +714,7 @@ int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int
         GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, nullptr, w.und, w.und_bytes, w.rowptr1, w.col1, w.row1,
                                  w.ecap, nullptr, st));
     }
-    GM_TRY(edge_stage(w, p->conv[0], w.rowptr1, w.col1, w.row1, N, nullptr, training, precision, momentum, eps, w.bnss, w.x1, st));
+    GM_TRY(edge_stage(w, p->conv[0], w.rowptr1, w.col1, w.row1, N, nullptr, training, precision, momentum, eps, w.bnss, w.x1, w.vsel1, st));
     {
         TimedRegion tr(GM_TIMER_DRN_POOL, st);
         GM_TRY(drn_normalized_cut(w.x1, DH, DH, w.rowptr1, w.col1, w.row1, N, w.ecap, w.weight1, st));
@@ -734,7 +739,7 @@ int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int
         GM_TRY(drn_to_undirected(nullptr, nullptr, w.nbr, w.deg, K, N, m_dev, w.und, w.und_bytes, w.rowptr2, w.col2, w.row2,
                                  w.ecap, nullptr, st));
     }
-    GM_TRY(edge_stage(w, p->conv[1], w.rowptr2, w.col2, w.row2, N, m_dev, training, precision, momentum, eps, w.bnss + 4 * DH, w.x2, st));
+    GM_TRY(edge_stage(w, p->conv[1], w.rowptr2, w.col2, w.row2, N, m_dev, training, precision, momentum, eps, w.bnss + 4 * DH, w.x2, w.vsel2, st));
     // ---- :98-104: the second clustering cannot change a global maximum; pool per event and run the output MLP
     HeadParams hp{p->out_w[0], p->out_b[0], p->out_w[1], p->out_b[1], p->out_w[2], p->out_b[2], p->output_dim};
     {

@@ -28,7 +28,14 @@ constexpr int GEO_WARPS = GEO_THREADS / 32;
 constexpr int AG_CONSUMERS = 8;      // forward kernel: 8 consumer warps (AG_TPW targets of the item each) ...
 constexpr int AG_THREADS = (AG_CONSUMERS + 1) * 32;   // ... + 1 producer warp (segments, descriptors, TMA)
 constexpr int AG_TPW = GEO_TPI / AG_CONSUMERS;
-constexpr int AG_CH = 224;           // staged neighbourhood rows per pipeline stage (2 stages x 3 CTAs fit one SM)
+#ifndef GEO_AG_CH
+#define GEO_AG_CH 224
+#endif
+#ifndef GEO_AG_STAGES
+#define GEO_AG_STAGES 2
+#endif
+constexpr int AG_CH = GEO_AG_CH;     // staged neighbourhood rows per pipeline stage (224 x 2 stages x 3 CTAs fit one SM)
+constexpr int AGF_STAGES = GEO_AG_STAGES;   // ring depth of the forward kernel (how far the producer warp runs ahead)
 constexpr int AG_LIST = AG_CH + 16;  // per-warp hit list (uint32 byte offsets of staged rows), padded by 16 identity entries
 using AgStage = StageL<AG_CH, false>;
 
@@ -184,11 +191,11 @@ __global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, in
 
 constexpr size_t AG_OFF_PTS = AgStage::OFF_PTS, AG_OFF_TGT = AgStage::OFF_TGT, AG_OFF_THR = AgStage::OFF_THR;
 constexpr size_t AG_OFF_DESC = AgStage::OFF_DESC, AG_STAGE_BYTES = AgStage::BYTES;
-constexpr size_t AG_LISTS = AG_STAGES * AG_STAGE_BYTES;                    // AG_CONSUMERS x AG_LIST x u32
+constexpr size_t AG_LISTS = AGF_STAGES * AG_STAGE_BYTES;                   // AG_CONSUMERS x AG_LIST x u32
 constexpr size_t AG_BAR = AG_LISTS + (size_t)AG_CONSUMERS * AG_LIST * 4;   // full[AG_STAGES], empty[AG_STAGES]
-constexpr size_t AG_TOTAL = AG_BAR + 16 * AG_STAGES;
+constexpr size_t AG_TOTAL = AG_BAR + 16 * AGF_STAGES;
 static_assert(AG_STAGE_BYTES % 128 == 0 && AG_LISTS % 8 == 0 && (AG_LIST * 4) % 16 == 0 && AG_LISTS % 16 == 0 && AG_BAR % 8 == 0, "staging alignment");
-static_assert(AG_STAGES * AG_STAGE_BYTES >= (size_t)(AG_THREADS / 8) * 3 * H * 4, "BatchNorm scratch aliases the stages");
+static_assert(AGF_STAGES * AG_STAGE_BYTES >= (size_t)(AG_THREADS / 8) * 3 * H * 4, "BatchNorm scratch aliases the stages");
 
 // One target against one staged chunk: hit list, then lane = channel walks the list 4 rows at a time out of shared
 // memory.  The caller must NOT unroll its target loop around this body: the consumer warps run decoupled, and four
@@ -289,24 +296,24 @@ __global__ void __launch_bounds__(AG_THREADS, 3)
 k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, int N, float *__restrict__ out,
            int *__restrict__ arg, AggrTail tail) {
     extern __shared__ __align__(128) unsigned char gs[];
-    const uint32_t full0 = smem_u32(gs + AG_BAR), empty0 = full0 + 8u * AG_STAGES;
+    const uint32_t full0 = smem_u32(gs + AG_BAR), empty0 = full0 + 8u * AGF_STAGES;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     const GeoMeta m = *v.meta;
     const float IDENT = AGGR == GM_AGGR_MAX ? -INFINITY : 0.f;
     const bool dynamic = tail.partials == nullptr;
     if (tid == 0) {
-        for (int s = 0; s < AG_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, AG_CONSUMERS); }
+        for (int s = 0; s < AGF_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, AG_CONSUMERS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp < AG_STAGES) reinterpret_cast<float *>(gs + warp * AG_STAGE_BYTES)[AG_CH * 32 + lane] = IDENT;
+    if (warp < AGF_STAGES) reinterpret_cast<float *>(gs + warp * AG_STAGE_BYTES)[AG_CH * 32 + lane] = IDENT;
     __syncthreads();
     pdl_sync();                                          // Y, P, the tickets: the previous kernels' outputs
 
     float cnt = 0.f, shift = 0.f, s1 = 0.f, s2 = 0.f;      // BatchNorm moments of this warp's outputs (lane = channel)
     if (warp == AG_CONSUMERS) {
         // ================================================================== producer
-        geo_produce<AgStage, false>(gs, full0, empty0, v, m, Y, N, dynamic, lane);
+        geo_produce<AgStage, false, AGF_STAGES>(gs, full0, empty0, v, m, Y, N, dynamic, lane);
     } else if constexpr (Q4) {
         // ================================================================== consumers, quarter-warp rows (inference)
         // Per-slot state lives in REGISTERS, not in a dynamically indexed (= local-memory) array: lane u holds the
@@ -321,9 +328,9 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
         GeoMeta mm;
         mm.r2 = m.r2; mm.dim = m.dim; mm.phi_wrap = m.phi_wrap;
         for (uint32_t gc = 0;; ++gc) {
-            const int st = gc & 1;
+            const int st = gc % AGF_STAGES;
             const unsigned char *stage = gs + st * AG_STAGE_BYTES;
-            mbar_wait(full0 + 8u * st, (gc >> 1) & 1u);
+            mbar_wait(full0 + 8u * st, (gc / AGF_STAGES) & 1u);
             const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + AG_OFF_DESC);
             const int flags = d->flags;
             if (flags & AG_END) break;
@@ -392,9 +399,9 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
         float px_l = 0.f, py_l = 0.f, acc0 = IDENT, acc1 = IDENT, acc2 = IDENT, acc3 = IDENT;
         int th_l = 0, excl_l = -1, deg_l = 0, barg0 = -1, barg1 = -1, barg2 = -1, barg3 = -1;
         for (uint32_t gc = 0;; ++gc) {
-            const int st = gc & 1;
+            const int st = gc % AGF_STAGES;
             const unsigned char *stage = gs + st * AG_STAGE_BYTES;
-            mbar_wait(full0 + 8u * st, (gc >> 1) & 1u);
+            mbar_wait(full0 + 8u * st, (gc / AGF_STAGES) & 1u);
             const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + AG_OFF_DESC);
             const int flags = d->flags;
             if (flags & AG_END) break;

@@ -57,7 +57,7 @@ extern "C" {
 #define GM_PREC_FP32 0      /* fp32 CUDA cores, factored form P_i + aggr_j Y_j (parity mode, default) */
 #define GM_PREC_TF32 1      /* tcgen05 kind::tf32 */
 #define GM_PREC_BF16 2      /* tcgen05 kind::f16 (bf16 operands, fp32 accumulate in TMEM) */
-#define GM_PREC_TF32X3 3    /* reserved: tcgen05 3xTF32 split (returns GM_ERR_UNSUPPORTED) */
+
 #define GM_PREC_FP32_DIRECT 4 /* fp32 CUDA cores, per-edge contraction W2 (x_j - x_i) spelled out (cross-check) */
 
 int gm_version(void);

@@ -7,7 +7,7 @@ NV="/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c+
 SRC=${3:-geo}
 $NV $2 -c $SRC.cu -o build/${SRC}_$1.o
 OBJS=""
-for f in radius_graph net_forward net_backward edgeconv_tc loss_opt geo geo_tc knn; do
+for f in radius_graph net_forward net_backward edgeconv_tc loss_opt geo geo_tc knn comm microbench drn_graph drn_net metrics; do
   if [ "$f" == "$SRC" ]; then OBJS="$OBJS build/${SRC}_$1.o"; else OBJS="$OBJS build/$f.o"; fi
 done
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o variants/libgraphmet_$1.so $OBJS -lcudart
