@@ -60,7 +60,7 @@ class GmDrnParams(C.Structure):
 class GmDrnView(C.Structure):
     _fields_ = [("x0", _vp), ("rowptr1", _vp), ("col1", _vp), ("row1", _vp), ("x1", _vp), ("weight1", _vp),
                 ("cluster1", _vp), ("partner1", _vp), ("x1p", _vp), ("ptr1p", _vp), ("rowptr2", _vp), ("col2", _vp),
-                ("row2", _vp), ("x2", _vp), ("pooled", _vp), ("edge_capacity", _ll)]
+                ("row2", _vp), ("x2", _vp), ("pooled", _vp), ("edge_capacity", _ll), ("asel1", _vp), ("asel2", _vp)]
 
 
 # name -> (restype, argtypes); must list every symbol include/graphmet.h declares
@@ -127,6 +127,8 @@ SIGNATURES = {
     "gm_drn_ws_bytes": (_sz, [_i, _i, _i]),
     "gm_drn_forward": (_i, [C.POINTER(GmDrnParams), _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _f, _vp, _sz, _vp, _vp,
                             C.POINTER(GmDrnView), _vp]),
+    "gm_drn_bwd_ws_bytes": (_sz, [_i, _i, _i]),
+    "gm_drn_backward": (_i, [C.POINTER(GmDrnParams), C.POINTER(GmDrnParams), _vp, _i, _vp, _i, _i, _vp, _sz, _vp, _sz, _vp, _vp]),
     "gm_allreduce_adamw_step": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp,
                                      _vp]),
 }

@@ -470,6 +470,7 @@ typedef struct GmDrnView {
     float *x2;                   /* [M,64]   edgeconv2 output */
     float *pooled;               /* [B,64]   global max pool */
     long long edge_capacity;     /* capacity of col / row / weight arrays */
+    int *asel1, *asel2;          /* [N,64] (training): source node each EdgeConv's max selected per (node, channel), -1 = no edge */
 } GmDrnView;
 size_t gm_drn_ws_bytes(int N, int B, int k);
 /* Whole forward, no host synchronisation: datanorm, inputnet, then twice (kNN graph in the 64-d latent space ->
@@ -483,6 +484,18 @@ size_t gm_drn_ws_bytes(int N, int B, int k);
 int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int *ptr, int N, int B,
                    int max_event_nodes, int training, int precision, float momentum, float eps, void *ws,
                    size_t ws_bytes, float *out, float *net_out, GmDrnView *view_out, void *stream);
+
+/* Backward of gm_drn_forward (training = 1, GM_PREC_FP32): grad_out [B, output_dim] = dL/d out.  Every tensor of `grads`
+ * (a GmDrnParams whose pointers name the gradient buffers; the BatchNorm running buffers, output_dim and k are ignored;
+ * a NULL pointer skips that tensor) is OVERWRITTEN: datanorm, inputnet, both edge MLPs incl. their BatchNorm weight /
+ * bias, the output MLP -- 31 tensors.  fwd_ws must be the untouched workspace of the forward on the same inputs.
+ * k-NN search, graclus and the pooling indices are constants of the differentiation (as in the reference, where
+ * they are integer tensors); max aggregation / max pooling route each gradient to the selected element; BatchNorm
+ * over the edge rows is differentiated with batch statistics.  Deterministic (no float atomics). */
+size_t gm_drn_bwd_ws_bytes(int N, int B, int k);
+int gm_drn_backward(const GmDrnParams *p, const GmDrnParams *grads, const float *x, int x_stride, const int *ptr, int N,
+                    int B, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
+                    const float *grad_out, void *stream);
 
 #ifdef __cplusplus
 }

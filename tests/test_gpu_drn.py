@@ -217,8 +217,9 @@ def test_drn_bf16_tcgen05_edge_mlp(mode):
     ours.edge_precision = "bf16"
     ref.train(mode == "train"); ours.train(mode == "train")
     x, batch = torch.from_numpy(z["x"]), torch.from_numpy(z["batch"])
-    out = ours(types.SimpleNamespace(x=x.to(DEV), batch=batch.to(DEV)))
-    out_again = ours(types.SimpleNamespace(x=x.to(DEV), batch=batch.to(DEV))) if mode == "eval" else out
+    with torch.no_grad():        # the tcgen05 variant is forward-only (the backward differentiates the fp32 forward)
+        out = ours(types.SimpleNamespace(x=x.to(DEV), batch=batch.to(DEV)))
+        out_again = ours(types.SimpleNamespace(x=x.to(DEV), batch=batch.to(DEV))) if mode == "eval" else out
     assert torch.equal(out, out_again)
     it = {k: v.cpu() for k, v in ours.intermediates().items()}
     N = x.shape[0]
@@ -238,3 +239,101 @@ def test_drn_bf16_tcgen05_edge_mlp(mode):
         close(it["x2"], _edgeconv_bf16_model(ref.edgeconv2, xp, ei2), 5e-3, "x2 vs bf16 model")
         close(out, ref.output(D.global_max_pool(it["x2"], bp)).squeeze(-1), 1e-5, "out")
     print(f"\n[DRN bf16 tcgen05, {mode}] x1 vs operand-rounding model {e_model:.2e} | vs fp32 oracle {e_fp32:.2e}")
+
+
+def _drn_case(name):
+    """(state_dict, x, batch, datanorm): the fixtures of the reference's own file, or a 980-node batch with a datanorm
+    that keeps the continuous features visible."""
+    if name in ("tiny", "small"):
+        z, sd = load_case(name)
+        return sd, torch.from_numpy(z["x"]), torch.from_numpy(z["batch"]), torch.tensor(D.DRN_NORM)
+    torch.manual_seed(77)
+    norm = torch.tensor([1 / 3., 1 / 3., 1 / 3., 1 / 2., 2., 1., 3., 1 / 211., 1., 1 / 7., 1.])
+    m = D.DynamicReductionNetwork(input_dim=11, hidden_dim=64, k=8, output_dim=2, aggr="max", norm=norm)
+    with torch.no_grad():
+        for ec in (m.edgeconv1, m.edgeconv2):
+            bn = ec.nn[4]
+            bn.weight.uniform_(-1.5, 1.5); bn.bias.uniform_(-0.5, 0.5)
+    b = synth.make_batch(3, "dytt", seed=91, sizes=[300, 420, 260])
+    return {k: v.clone() for k, v in m.state_dict().items()}, b.x, b.batch, norm
+
+
+def _edgeconv_selected(ec, x, ei, arg):
+    """The oracle's EdgeConv with the max taken at GIVEN edges: out[i, c] = msg[edge(i <- arg[i, c]), c].  Which of two
+    (nearly) equal messages is the maximum is an integer decision of the forward, like the graph itself; the oracle
+    differentiates through the decisions our forward took."""
+    j, i = ei[0], ei[1]
+    n = x.shape[0]
+    msg = ec.nn(torch.cat([x[i], x[j] - x[i]], 1))
+    key = i * n + j
+    order = torch.argsort(key)
+    deg = torch.bincount(i, minlength=n)
+    q = torch.arange(n)[:, None] * n + arg.long().clamp_min(0)
+    pos = torch.searchsorted(key[order], q.reshape(-1)).clamp_max(key.numel() - 1)
+    eidx = order[pos].view(n, 64)
+    assert bool(((key[eidx] == q) | (deg == 0)[:, None]).all()), "a selected source is not an edge of the graph"
+    out = msg.gather(0, eidx)
+    return torch.where((deg > 0)[:, None], out, torch.zeros_like(out))
+
+
+@pytest.mark.parametrize("name", ["tiny", "small", "synthetic"])
+def test_drn_backward_matches_oracle_autograd(name):
+    """gm_drn_backward: all 31 gradients (datanorm, inputnet, both edge MLPs with their BatchNorm-over-edges, output MLP)
+    against torch autograd through the oracle, run on the graphs, clusters, pooling winners and arg-max edges our forward
+    used (integer decisions of the forward are constants of the differentiation, in the reference too; with the wrapper's
+    normalisation -- px / 2950 ... -- candidates that share (pdgId, charge, fromPV) have latent rows that agree to ~1e-4,
+    and a maximum between two of them is now and then decided below the fp32 rounding difference of two correct
+    forwards: the oracle therefore takes the decisions from our forward and is checked to reproduce its values).
+    Bound: 1e-3 of each tensor's max-abs gradient."""
+    sd, x, batch, norm = _drn_case(name)
+    ref = D.DynamicReductionNetwork(input_dim=11, hidden_dim=64, k=8, output_dim=2, aggr="max", norm=norm.clone())
+    ref.load_state_dict(sd)
+    ours = drn.DynamicReductionNetwork(input_dim=11, hidden_dim=64, k=8, output_dim=2, aggr="max", norm=norm.clone())
+    ours.load_state_dict(sd, strict=True)
+    ours.to(DEV)
+    ref.train(); ours.train()
+    B = int(batch.max()) + 1
+    R = torch.randn(B, 2, generator=torch.Generator().manual_seed(7))
+    out = ours(types.SimpleNamespace(x=x.to(DEV), batch=batch.to(DEV)))
+    (out * R.to(DEV)).sum().backward()
+    torch.cuda.synchronize()
+    it = {k: v.cpu() for k, v in ours.intermediates().items()}
+    ei1, ei2 = csr_to_ei(it["rowptr1"], it["col1"]), csr_to_ei(it["rowptr2"], it["col2"])
+    # The oracle, stage by stage on our graphs / clusters.  max_pool picks, per (cluster, channel), the larger of two
+    # members: where the two values agree to the last few ulps (both edge maxima sit on the saturated branch of the
+    # ELU) the CPU and the GPU forward can order them differently, so the winner -- like the graph and the clusters, an
+    # integer decision of the forward -- is taken from OUR forward and the oracle differentiates through that gather.
+    arg1, arg2 = it["asel1"], it["asel2"]
+    x0 = ref.inputnet(ref.datanorm * x)
+    x1 = _edgeconv_selected(ref.edgeconv1, x0, ei1, arg1)
+    close(x1, ref.edgeconv1(x0, ei1), 1e-5, "selected edges attain the maximum")
+    cl = it["cluster1"].long()
+    newid, _ = D.consecutive_cluster(cl)
+    M = int(newid.max()) + 1
+    lo = torch.full((M,), x.shape[0], dtype=torch.long).scatter_reduce(0, newid, torch.arange(x.shape[0]), "amin")
+    hi = torch.zeros(M, dtype=torch.long).scatter_reduce(0, newid, torch.arange(x.shape[0]), "amax")
+    ours_x1 = it["x1"]
+    win = torch.where(ours_x1[lo] >= ours_x1[hi], lo[:, None].expand(-1, 64), hi[:, None].expand(-1, 64))
+    xp = x1.gather(0, win)
+    bp = batch[lo]
+    assert torch.equal(ours_x1.gather(0, win), it["x1p"])
+    x2 = _edgeconv_selected(ref.edgeconv2, xp, ei2, arg2)
+    close(x2, ref.edgeconv2(xp, ei2), 1e-5, "selected edges attain the maximum")
+    out_ref = ref.output(D.global_max_pool(x2, bp)).squeeze(-1)
+    close(out, out_ref, 1e-4, "train-mode output")
+    (out_ref * R).sum().backward()
+    named = dict(ours.named_parameters())
+    worst = ("", 0.0)
+    for k, p in ref.named_parameters():
+        g, gr = named[k].grad, p.grad
+        assert g is not None, k
+        err = close(g, gr, 1e-3, "grad " + k)
+        worst = max(worst, (k, err), key=lambda t: t[1])
+    print(f"\n[DRN backward, {name}] worst gradient error {worst[1]:.2e} of max-abs ({worst[0]})")
+    # a second backward on the same inputs: bit-identical gradients (no float atomics anywhere)
+    g1 = {k: v.grad.clone() for k, v in named.items()}
+    ours.zero_grad()
+    sd_bn = {k: v.clone() for k, v in ours.state_dict().items()}
+    out2 = ours(types.SimpleNamespace(x=x.to(DEV), batch=batch.to(DEV)))
+    (out2 * R.to(DEV)).sum().backward()
+    assert all(torch.equal(named[k].grad, g1[k]) for k in g1)
