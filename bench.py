@@ -303,24 +303,36 @@ def run_drn(args):
 
 def drn_line(args):
     """Side line for BASELINE config 4 / row f1: the DynamicReductionNetwork variant (model/dynamic_reduction_network.py with
-    the wrapper of model/net.py:12-37) on 32 synthetic Z->nunu-shaped events, train-mode forward (BatchNorm batch statistics
-    over the edge rows + running-stat update; the backward is not built).  Roofline on the per-edge 96->64 contraction."""
+    the wrapper of model/net.py:12-37) on 32 synthetic Z->nunu-shaped events.  fp32: a full TRAINING step (forward with
+    BatchNorm over the edge rows, fused wrapper + MET loss, backward of all 31 tensors, flat AdamW) through DRNTrainer;
+    bf16: the tcgen05 edge MLP, train-mode forward only (the backward differentiates the fp32 forward)."""
     import types
     from deepmetv2_b200 import synth
     from deepmetv2_b200._lib import lib, TIMERS
     from deepmetv2_b200.model import dynamic_reduction_network as drn
+    from deepmetv2_b200.trainer import DRNTrainer
     dev = torch.device("cuda", 0)
     B = 32
     l = lib()
     torch.manual_seed(0)
     net = drn.DRNNet().to(dev).train()
     net.drn.edge_precision = args.precision
+    training = args.precision == "fp32"
     host = [synth.make_batch(B, "znunu", seed=4000 + i).pin_memory() for i in range(N_ROTATE)]
     devb = [b.to(dev) for b in host]
     men = [int((b.ptr[1:] - b.ptr[:-1]).max()) for b in host]
+    trainer = DRNTrainer(net, lr=1e-3) if training else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step(i):
+        k = i % N_ROTATE
+        if training:
+            return trainer.train_step(devb[k], men[k])
+        with torch.no_grad():
+            return net(devb[k], men[k])
+
     for i in range(max(args.warmup, 3)):
-        net(devb[i % N_ROTATE], men[i % N_ROTATE])
+        step(i)
     torch.cuda.synchronize()
     l.gm_timing_enable(1)
     l.gm_launch_count(1)
@@ -328,72 +340,93 @@ def drn_line(args):
     for i in range(args.steps):
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(); net(devb[i % N_ROTATE], men[i % N_ROTATE]); e1.record(); torch.cuda.synchronize()
+        e0.record(); step(i); e1.record(); torch.cuda.synchronize()
         tot += e0.elapsed_time(e1)
     launches = l.gm_launch_count(0)
     timers = {}
-    for name in ("drn_node", "drn_knn", "drn_graph", "drn_edge", "drn_pool"):
+    for name in ("drn_node", "drn_knn", "drn_graph", "drn_edge", "drn_pool", "drn_edge_bwd", "drn_bwd"):
         ms, n = ctypes.c_float(), ctypes.c_int()
         l.gm_timing_read(TIMERS[name], ctypes.byref(ms), ctypes.byref(n))
-        timers[name] = (ms.value, n.value)
+        if n.value:
+            timers[name] = (ms.value, n.value)
     l.gm_timing_enable(0)
     ms_step = tot / args.steps
     # edges of both stages (outside the timed region)
     E1 = E2 = Nn = M = 0
     for k in range(N_ROTATE):
-        net(devb[k], men[k])
+        with torch.no_grad():
+            net(devb[k], men[k])
         it = net.drn.intermediates()
         E1 += int(it["rowptr1"][-1]); E2 += int(it["rowptr2"][-1]); Nn += devb[k].x.shape[0]; M += int(it["ptr1p"][-1])
     E1, E2, Nn, M = E1 / N_ROTATE, E2 / N_ROTATE, Nn / N_ROTATE, M / N_ROTATE
-    edge_ms, edge_n = timers["drn_edge"]
-    edge_us = edge_ms / max(edge_n, 1) * 1e3
-    flop_per_launch = (E1 + E2) / 2 * 2.0 * 96 * 64
     tensor = args.precision != "fp32"
+    dom = "drn_edge_bwd" if training else "drn_edge"
+    edge_ms, edge_n = timers[dom]
+    edge_us = edge_ms / max(edge_n, 1) * 1e3
+    # per-edge tile products: forward 96x64; backward = forward recompute + dW2 + W2^T dz2 (3 x 96x64)
+    flop_per_launch = (E1 + E2) / 2 * 2.0 * 96 * 64 * (3 if training else 1)
     if tensor:
         pk = _peaks()
-        peak, peak_src, unit_bound = pk["bf16_tflops_sustained"] * (0.5 if args.precision == "tf32" else 1.0), pk["source"], "tensor"
+        peak, peak_src, unit_bound = pk["bf16_tflops_sustained"], pk["source"], "tensor"
     else:
         peak, peak_src, unit_bound = fp32_peak_tflops(l), "FFMA stream measured live by gm_bench_ffma", "fp32 pipe"
     ach = flop_per_launch / (edge_us * 1e-6) / 1e12
-    # e2e: pinned host x / ptr -> H2D -> forward -> [B,2] D2H
+    # e2e: pinned host x / y / ptr -> H2D -> step -> loss (training) or [B,2] (inference) back on the host
     t0 = time.perf_counter()
     for i in range(args.steps):
         hb = host[i % N_ROTATE]
-        d = types.SimpleNamespace(x=hb.x.to(dev, non_blocking=True), ptr=hb.ptr.to(dev, non_blocking=True))
-        o = net(d, men[i % N_ROTATE]).cpu()
+        if training:
+            trainer.train_step_from_host(hb, men[i % N_ROTATE])
+        else:
+            d = types.SimpleNamespace(x=hb.x.to(dev, non_blocking=True), ptr=hb.ptr.to(dev, non_blocking=True))
+            with torch.no_grad():
+                net(d, men[i % N_ROTATE]).cpu()
     e2e_s = (time.perf_counter() - t0) / args.steps
-    # CPU leg: the oracle port on 4 events, all host threads, warm-up 1 + median of 3
+    # CPU leg: the oracle port on 4 events, all host threads, warm-up 1 + median of 3 (training: + loss + autograd)
     from oracle import drn_oracle as D
     ref = D.DRNNet().train()
     n4 = int(host[0].ptr[4])
     cd = lambda: types.SimpleNamespace(x=host[0].x[:n4].clone(), batch=host[0].batch[:n4].clone())  # noqa: E731
-    with torch.no_grad():
-        ref(cd())
-        ts = []
-        for _ in range(3):
-            t0 = time.perf_counter(); ref(cd()); ts.append(time.perf_counter() - t0)
+
+    def cpu_step():
+        if not training:
+            with torch.no_grad():
+                return ref(cd())
+        ref.zero_grad()
+        o = ref(cd())
+        yy = host[0].y[:4]
+        loss = 0.5 * ((o[:, 0] * torch.cos(o[:, 1]) - yy[:, 0]) ** 2 + (o[:, 0] * torch.sin(o[:, 1]) - yy[:, 1]) ** 2).mean()
+        loss.backward()
+    cpu_step()
+    ts = []
+    for _ in range(3):
+        t0 = time.perf_counter(); cpu_step(); ts.append(time.perf_counter() - t0)
     cpu_s = statistics.median(ts)
     kern = {k: {"avg_us": v[0] / max(v[1], 1) * 1e3, "regions_per_step": v[1] / args.steps,
                 "share_of_step": v[0] / args.steps / ms_step} for k, v in timers.items()}
+    mode = "train" if training else "train-forward"
     return ({
-        "metric": "DRN forward events/sec", "value": B / ms_step * 1e3, "unit": "events/s", "n_gpus": 1, "steps": args.steps,
+        "metric": "DRN training events/sec" if training else "DRN forward events/sec", "value": B / ms_step * 1e3,
+        "unit": "events/s", "n_gpus": 1, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if not tensor else args.precision, "data": "synthetic",
-        "config": {"workload": "DynamicReductionNetwork variant (knn_graph + pooling), train-mode forward, 32 synthetic "
-                               "Z->nunu-shaped events", "events_per_gpu": B, "event_shape": "znunu", "mode": "train-forward",
+        "config": {"workload": "DynamicReductionNetwork variant (knn_graph + pooling) " +
+                               ("training step" if training else "train-mode forward") + ", 32 synthetic Z->nunu-shaped events",
+                   "events_per_gpu": B, "event_shape": "znunu", "mode": mode,
                    "edge_precision": args.precision, "l2": L2_NOTE, "rotating_batches": N_ROTATE},
         "workload_stats": {"nodes_per_step": Nn, "pooled_nodes": M, "edges_stage1": E1, "edges_stage2": E2},
         "gpu_launches": int(launches), "gpu_launches_per_step": launches / args.steps,
-        "roofline": {"kernel": "k_drn_edge", "bound": unit_bound, "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+        "roofline": {"kernel": "k_drn_edge_bwd" if training else ("k_drn_edge_tc" if tensor else "k_drn_edge"),
+                     "bound": unit_bound, "achieved": ach, "peak": peak, "unit": "TFLOP/s",
                      "frac": ach / peak if peak else None, "traffic": None, "avg_launch_us": edge_us,
                      "flop_per_launch": flop_per_launch, "peak_source": peak_src,
-                     "share_of_step": kern["drn_edge"]["share_of_step"]},
+                     "share_of_step": kern[dom]["share_of_step"]},
         "kernels": kern,
         "cpu_baseline": {"value": 4 / cpu_s, "unit": "events/s", "cores": torch.get_num_threads(), "kind": "port",
                          "sample": "4 of the 32 events through oracle/drn_oracle.py (k-NN by oracle/knn_bruteforce.c, graclus in "
-                                   "a Python loop), warm-up 1, median of 3"},
-        "e2e": {"value": B / e2e_s, "unit": "events/s", "h2d_bytes_per_step": int(Nn * 44 + (B + 1) * 4),
-                "d2h_bytes_per_step": B * 8, "api": "DRNNet.forward"},
+                                   "a Python loop" + (", loss + autograd backward" if training else "") + "), warm-up 1, median of 3"},
+        "e2e": {"value": B / e2e_s, "unit": "events/s", "h2d_bytes_per_step": int(Nn * 44 + (B + 1) * 4 + B * 44),
+                "d2h_bytes_per_step": 4 if training else B * 8, "api": "DRNTrainer.train_step_from_host" if training else "DRNNet.forward"},
     })
 
 

@@ -27,7 +27,7 @@ AGGR = {"max": 0, "add": 1, "mean": 2}
 PRECISION = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3, "fp32_direct": 4}
 TIMERS = {"radius_graph": 0, "encode_fwd": 1, "edgeconv_fwd": 2, "head_fwd": 3, "scatter_s_bwd": 4,
           "conv_node_bwd": 5, "encode_bwd": 6, "bn": 7, "node_prep": 8, "head_bwd": 9,
-          "drn_node": 10, "drn_knn": 11, "drn_graph": 12, "drn_edge": 13, "drn_pool": 14}
+          "drn_node": 10, "drn_knn": 11, "drn_graph": 12, "drn_edge": 13, "drn_pool": 14, "drn_edge_bwd": 15, "drn_bwd": 16}
 
 _vp, _i, _ll, _f, _d, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double, C.c_size_t
 
@@ -127,6 +127,7 @@ SIGNATURES = {
     "gm_drn_ws_bytes": (_sz, [_i, _i, _i]),
     "gm_drn_forward": (_i, [C.POINTER(GmDrnParams), _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _f, _vp, _sz, _vp, _vp,
                             C.POINTER(GmDrnView), _vp]),
+    "gm_drn_met_loss": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "gm_drn_bwd_ws_bytes": (_sz, [_i, _i, _i]),
     "gm_drn_backward": (_i, [C.POINTER(GmDrnParams), C.POINTER(GmDrnParams), _vp, _i, _vp, _i, _i, _vp, _sz, _vp, _sz, _vp, _vp]),
     "gm_allreduce_adamw_step": (_i, [_vp, _vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp,

@@ -782,30 +782,41 @@ __global__ void __launch_bounds__(256) k_drn_head_bwd(const float *__restrict__ 
     }
 }
 
-// S_c = sum_i g[i,c], T_c = sum_i g[i,c] * hat_sel(i,c) over the nodes that have edges (g = d x_out); also d gamma, d beta
-__global__ void __launch_bounds__(1024) k_drn_bn_sums(const float *__restrict__ g, const float *__restrict__ vsel,
-                                                      const int *__restrict__ rowptr, int N, const int *__restrict__ n_dev,
-                                                      const float *__restrict__ bnss, float *__restrict__ sums,
-                                                      float *__restrict__ dgamma, float *__restrict__ dbeta) {
-    __shared__ double s_s[16][DH], s_t[16][DH];
+// S_c = sum_i g[i,c], T_c = sum_i g[i,c] * hat_sel(i,c) over the nodes that have edges (g = d x_out); also d gamma, d beta.
+// Two launches: per-CTA partials over an interleaved node range (fixed order inside a CTA), then their sum in CTA order.
+constexpr int BS_PARTS = 16;
+__global__ void __launch_bounds__(BS_PARTS * DH) k_drn_bn_sums(const float *__restrict__ g, const float *__restrict__ vsel,
+                                                               const int *__restrict__ rowptr, int N, const int *__restrict__ n_dev,
+                                                               const float *__restrict__ bnss, double *__restrict__ partial) {
+    __shared__ double s_s[BS_PARTS][DH], s_t[BS_PARTS][DH];
     pdl_sync();
     const int n = eff_n(N, n_dev), tid = threadIdx.x, c = tid & (DH - 1), part = tid >> 6;
     const float mean = bnss[c], invstd = bnss[DH + c];
     double S = 0.0, T = 0.0;
-    for (int i = part; i < n; i += 16) {
+    for (int i = blockIdx.x * BS_PARTS + part; i < n; i += gridDim.x * BS_PARTS) {
         if (rowptr[i + 1] <= rowptr[i]) continue;
         const float gi = g[(size_t)i * DH + c];
         S += (double)gi;
-        T += (double)gi * (double)((vsel[(size_t)i * DH + c] - mean) * invstd);
+        T += (double)(gi * ((vsel[(size_t)i * DH + c] - mean) * invstd));
     }
     s_s[part][c] = S; s_t[part][c] = T;
     __syncthreads();
     if (tid < DH) {
         double a = 0.0, b = 0.0;
-        for (int q = 0; q < 16; ++q) { a += s_s[q][tid]; b += s_t[q][tid]; }
-        sums[tid] = (float)a; sums[DH + tid] = (float)b;
-        dbeta[tid] = (float)a; dgamma[tid] = (float)b;
+        for (int q = 0; q < BS_PARTS; ++q) { a += s_s[q][tid]; b += s_t[q][tid]; }
+        partial[((size_t)blockIdx.x * 2) * DH + tid] = a;
+        partial[((size_t)blockIdx.x * 2 + 1) * DH + tid] = b;
     }
+}
+__global__ void __launch_bounds__(2 * DH) k_drn_bn_sums_fin(const double *__restrict__ partial, int nparts, float *__restrict__ sums,
+                                                            float *__restrict__ dgamma, float *__restrict__ dbeta) {
+    pdl_sync();
+    const int tid = threadIdx.x;                       // 0..63: S, 64..127: T
+    double acc = 0.0;
+    for (int q = 0; q < nparts; ++q) acc += partial[(size_t)q * 2 * DH + tid];
+    sums[tid] = (float)acc;
+    if (tid < DH) { if (dbeta) dbeta[tid] = (float)acc; }
+    else if (dgamma) dgamma[tid - DH] = (float)acc;
 }
 
 // position of the reverse entry: mirror[p] = index of (col -> row) for entry p = (row -> col) of a symmetric sorted CSR
@@ -1382,6 +1393,40 @@ int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int
 namespace gm {
 namespace {
 
+// The wrapper of model/net.py:31-36 fused with a regression loss on the MET vector it parametrises:
+//   met = softplus(out0), phi = pi (2 sigmoid(out1) - 1), loss = 0.5 mean_e[(met cos phi - t0)^2 + (met sin phi - t1)^2]
+// (the reference keeps no loss for this variant; this is the Cartesian MSE against genMET px, py = truth columns 0, 1).
+// One CTA: B events, fixed-order block reduction; also d loss / d out [B,2] so the backward needs no extra pass.
+__global__ void __launch_bounds__(256) k_drn_met_loss(const float *__restrict__ out, const float *__restrict__ truth,
+                                                      int truth_stride, int B, float grad_scale, float *__restrict__ net_out,
+                                                      float *__restrict__ loss_out, float *__restrict__ dout) {
+    __shared__ double s_red[256];
+    pdl_sync();
+    double acc = 0.0;
+    for (int e = threadIdx.x; e < B; e += 256) {
+        const float o0 = out[2 * e], o1 = out[2 * e + 1];
+        const float met = o0 > 20.f ? o0 : log1pf(expf(o0));
+        const float sg = sigmoidf(o1), phi = 3.14159265358979323846f * (2.f * sg - 1.f);
+        float sp, cp;
+        sincosf(phi, &sp, &cp);
+        const float rx = met * cp - truth[(size_t)e * truth_stride], ry = met * sp - truth[(size_t)e * truth_stride + 1];
+        acc += 0.5 * ((double)rx * rx + (double)ry * ry);
+        if (net_out) { net_out[2 * e] = met; net_out[2 * e + 1] = phi; }
+        if (dout) {
+            const float dmet = (rx * cp + ry * sp) * grad_scale, dphi = met * (ry * cp - rx * sp) * grad_scale;
+            dout[2 * e] = dmet * sigmoidf(o0);                                   // d softplus
+            dout[2 * e + 1] = dphi * 2.f * 3.14159265358979323846f * sg * (1.f - sg);
+        }
+    }
+    s_red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) s_red[threadIdx.x] += s_red[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) loss_out[0] = (float)(s_red[0] / (double)B);
+}
+
 // ------------------------------------------------------------------------------------------ backward: host side
 struct DrnBwdWs {
     float *dz1, *dab, *gA, *gB, *sums, *part, *psum;
@@ -1427,19 +1472,29 @@ int copy_seg(const float *src, float *dst, int n, cudaStream_t st) {
 int edge_stage_bwd(const DrnWs &f, const DrnBwdWs &w, const GmDrnConv &cv, const GmDrnConv &gcv, const float *x_in,
                    const float *vsel, const int *asel, const float *bnss, const int *rowptr, const int *col, const int *row, int N,
                    const int *n_dev, const float *gout, float *gin, cudaStream_t st) {
-    GM_LAUNCH_PDL(k_drn_bn_sums, 1, 1024, 0, st, gout, vsel, rowptr, N, n_dev, bnss, w.sums, gcv.bn_weight, gcv.bn_bias);
+    const int node_grid = persistent_grid(((long long)N + DT - 1) / DT, 1);
+    {
+    TimedRegion tr0(GM_TIMER_DRN_BWD, st);
+    const int sgrid = persistent_grid(((long long)N + BS_PARTS - 1) / BS_PARTS, 1);
+    GM_LAUNCH_PDL(k_drn_bn_sums, sgrid, BS_PARTS * DH, 0, st, gout, vsel, rowptr, N, n_dev, bnss, (double *)w.part);
+    GM_LAUNCH_CHECK();
+    GM_LAUNCH_PDL(k_drn_bn_sums_fin, 1, 2 * DH, 0, st, (const double *)w.part, sgrid, w.sums, gcv.bn_weight, gcv.bn_bias);
     GM_LAUNCH_CHECK();
     // [A | B] of this stage again (the forward keeps one buffer for both stages)
     NodeParams np{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, cv.w1, cv.b1};
-    const int node_grid = persistent_grid(((long long)N + DT - 1) / DT, 1);
     GM_LAUNCH_PDL(k_drn_node<false>, node_grid, DTHREADS, NODE_SMEM_BASE, st, x_in, DH, N, n_dev, np, (float *)nullptr, f.ab);
     GM_LAUNCH_CHECK();
     GM_LAUNCH_PDL(k_drn_mirror, persistent_grid((f.ecap + 255) / 256, 8), 256, 0, st, rowptr, col, row, N, f.ecap, w.mirror);
     GM_LAUNCH_CHECK();
+    }
     const int eg = persistent_grid(f.tiles_cap, 1);
+    {
+    TimedRegion tre(GM_TIMER_DRN_EDGE_BWD, st);
     GM_LAUNCH_PDL(k_drn_edge_bwd, eg, DTHREADS, EB_SMEM, st, (const float *)f.ab, rowptr, row, col, N, f.ecap,
                   (const float *)cv.w2, (const float *)cv.b2, bnss, (const float *)w.sums, asel, gout, w.dz1, w.part);
     GM_LAUNCH_CHECK();
+    }
+    TimedRegion trr(GM_TIMER_DRN_BWD, st);
     GM_TRY(sum_rows(w.part, eg, EB_PART, w.psum, st));
     GM_TRY(copy_seg(w.psum, gcv.w2, DH * DM, st));
     GM_TRY(copy_seg(w.psum + DH * DM, gcv.b2, DH, st));
@@ -1526,6 +1581,15 @@ int gm_drn_backward(const GmDrnParams *p, const GmDrnParams *grads, const float 
         GM_TRY(copy_seg(w.psum + o1 + 32 * DI, grads->in_b[0], 32, st));
         GM_TRY(copy_seg(w.psum + o1 + 32 * DI + 32, grads->datanorm, DI, st));
     }
+    return GM_OK;
+}
+
+int gm_drn_met_loss(const float *out, const float *truth, int truth_stride, int B, float *net_out, float *loss_out,
+                    float *grad_out, void *stream) {
+    if (B < 1 || !out || !truth || !loss_out || truth_stride < 2) return GM_ERR_INVALID_ARGUMENT;
+    GM_LAUNCH_PDL(k_drn_met_loss, 1, 256, 0, as_stream(stream), out, truth, truth_stride, B, 1.f / (float)B, net_out, loss_out,
+                  grad_out);
+    GM_LAUNCH_CHECK();
     return GM_OK;
 }
 

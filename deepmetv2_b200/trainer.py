@@ -478,3 +478,116 @@ class GraphMETTrainer:
                 self.exp_avg_sq[off:off + k].copy_(st["exp_avg_sq"].reshape(-1))
                 self.step_count = int(st["step"])
             off += k
+
+
+class DRNTrainer:
+    """Fused, sync-free training step for the DynamicReductionNetwork variant (BASELINE config 4, row f1):
+    forward (``gm_drn_forward``, train-mode BatchNorm over the edge rows) -> wrapper activations + Cartesian MET loss
+    (``gm_drn_met_loss``) -> backward (``gm_drn_backward``, all 31 gradients into one flat buffer) -> fused flat AdamW
+    (``gm_adamw_step``).  Parameters stay the module's ``nn.Parameter``s (re-pointed at a flat fp32 buffer);
+    ``trainer.optimizer`` is the same torch-Optimizer-shaped handle as GraphMETTrainer's."""
+
+    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01):
+        self.model = model
+        self.net = model.drn if hasattr(model, "drn") else model
+        params = list(self.net.parameters())
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise _lib.GraphMETLibraryError("DRNTrainer needs the model on a CUDA device (no CPU fallback)")
+        if self.net.output_dim != 2:
+            raise NotImplementedError("the fused loss is the (MET, MET phi) regression of model/net.py:12-37: output_dim = 2")
+        self.device = dev
+        n = sum(p.numel() for p in params)
+        self.flat = torch.empty(n, dtype=torch.float32, device=dev)
+        self.flat_grad = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
+        self._views, gviews, off = [], {}, 0
+        for (name, p) in self.net.named_parameters():
+            k = p.numel()
+            self.flat[off:off + k].copy_(p.data.reshape(-1))
+            p.data = self.flat[off:off + k].view_as(p)
+            self._views.append(p.data)
+            gviews[name] = self.flat_grad[off:off + k].view_as(p)
+            off += k
+        self._gviews = gviews
+        self._P = self.net._param_struct()
+        self._G = self.net._param_struct(grad_views=gviews)
+        self.optimizer = FusedAdamW(self, params, lr, tuple(betas), eps, weight_decay)
+        self.step_count = 0
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self._host_loss = torch.zeros((), dtype=torch.float32).pin_memory()
+        self._cap = (-1, -1)
+
+    lr = property(lambda self: self.optimizer.param_groups[0]["lr"])
+
+    def optimizer_state_dict(self):
+        return GraphMETTrainer.optimizer_state_dict(self)
+
+    def load_optimizer_state_dict(self, sd):
+        g = sd["param_groups"][0]
+        self.optimizer.param_groups[0].update(lr=g["lr"], betas=tuple(g["betas"]), eps=g["eps"], weight_decay=g["weight_decay"])
+        off = 0
+        for i, v in enumerate(self._views):
+            k, st = v.numel(), sd["state"].get(i)
+            if st is not None:
+                self.exp_avg[off:off + k].copy_(st["exp_avg"].reshape(-1))
+                self.exp_avg_sq[off:off + k].copy_(st["exp_avg_sq"].reshape(-1))
+                self.step_count = int(st["step"])
+            off += k
+
+    betas = property(lambda self: tuple(self.optimizer.param_groups[0]["betas"]))
+    eps = property(lambda self: self.optimizer.param_groups[0]["eps"])
+    weight_decay = property(lambda self: self.optimizer.param_groups[0]["weight_decay"])
+
+    def _reserve(self, N, B):
+        if N <= self._cap[0] and B <= self._cap[1]:
+            return
+        N, B = max(N, self._cap[0]), max(B, self._cap[1])
+        l, dev, k = lib(), self.device, int(self.net.k)
+        self.fwd_ws = torch.empty(l.gm_drn_ws_bytes(N, B, k), dtype=torch.uint8, device=dev)
+        self.bwd_ws = torch.empty(l.gm_drn_bwd_ws_bytes(N, B, k), dtype=torch.uint8, device=dev)
+        self.out = torch.empty(B, 2, dtype=torch.float32, device=dev)
+        self.net_out = torch.empty(B, 2, dtype=torch.float32, device=dev)
+        self.dout = torch.empty(B, 2, dtype=torch.float32, device=dev)
+        self._cap = (N, B)
+
+    def train_step(self, batch: EventBatch, max_event_nodes: int | None = None) -> torch.Tensor:
+        """One optimisation step on a device-resident batch (x [N,11], y [B,>=2], ptr [B+1] i32); returns the loss as a
+        0-dim device tensor (no sync)."""
+        x, y, p = batch.x, batch.y, batch.ptr
+        N, B = x.shape[0], y.shape[0]
+        men = max_event_nodes if max_event_nodes is not None else getattr(batch, "max_event_nodes", None)
+        if men is None:
+            men = int((p[1:] - p[:-1]).max().item())
+        self.net.train()
+        self._reserve(N, B)
+        l, st, net = lib(), stream(self.device), self.net
+        bn = net.edgeconv1.nn[4]
+        # the workspaces are allocated at their capacity: the layout is a function of (N, B), so pass exact sizes
+        fws = l.gm_drn_ws_bytes(N, B, int(net.k))
+        bws = l.gm_drn_bwd_ws_bytes(N, B, int(net.k))
+        check(l.gm_drn_forward(C.byref(self._P), ptr(x), x.stride(0), ptr(p), N, B, int(men), 1, PRECISION["fp32"],
+                               float(bn.momentum if bn.momentum is not None else 0.1), float(bn.eps), ptr(self.fwd_ws), fws,
+                               ptr(self.out), None, None, st), "gm_drn_forward")
+        check(l.gm_drn_met_loss(ptr(self.out), ptr(y), y.stride(0), B, ptr(self.net_out), ptr(self.loss), ptr(self.dout), st),
+              "gm_drn_met_loss")
+        check(l.gm_drn_backward(C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), ptr(p), N, B, ptr(self.fwd_ws), fws,
+                                ptr(self.bwd_ws), bws, ptr(self.dout), st), "gm_drn_backward")
+        self.step_count += 1
+        g = self.optimizer.param_groups[0]
+        check(l.gm_adamw_step(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq), self.flat.numel(),
+                              float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
+                              float(g["weight_decay"]), self.step_count, 1.0, st), "gm_adamw_step")
+        return self.loss
+
+    def train_step_from_host(self, host_batch: EventBatch, max_event_nodes: int | None = None) -> float:
+        dev = self.device
+        x = host_batch.x.to(dev, non_blocking=True)
+        y = host_batch.y.to(dev, non_blocking=True)
+        p = host_batch.ptr.to(dev, non_blocking=True)
+        men = max_event_nodes if max_event_nodes is not None else int((host_batch.ptr[1:] - host_batch.ptr[:-1]).max())
+        loss = self.train_step(EventBatch(x, y, None, p), men)
+        self._host_loss.copy_(loss, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        return float(self._host_loss)

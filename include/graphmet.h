@@ -84,7 +84,9 @@ long long gm_launch_count(int reset);  /* kernels this library launched since th
 #define GM_TIMER_DRN_GRAPH 12     /* DRN: to_undirected */
 #define GM_TIMER_DRN_EDGE 13      /* DRN: the per-edge 96->64 contraction kernel alone */
 #define GM_TIMER_DRN_POOL 14      /* DRN: BatchNorm merge + apply, normalized cut, graclus, max pool, head */
-#define GM_NUM_TIMERS 15
+#define GM_TIMER_DRN_EDGE_BWD 15  /* DRN backward: the per-edge kernel (recompute + BatchNorm / max backward + dW2 + W2^T dz2) */
+#define GM_TIMER_DRN_BWD 16       /* DRN backward: everything else (head, sums, mirror, gather, node side, pool, inputnet, reductions) */
+#define GM_NUM_TIMERS 17
 int gm_timing_enable(int on);
 int gm_timing_read(int slot, float *total_ms_out, int *regions_out);
 
@@ -492,6 +494,12 @@ int gm_drn_forward(const GmDrnParams *p, const float *x, int x_stride, const int
  * k-NN search, graclus and the pooling indices are constants of the differentiation (as in the reference, where
  * they are integer tensors); max aggregation / max pooling route each gradient to the selected element; BatchNorm
  * over the edge rows is differentiated with batch statistics.  Deterministic (no float atomics). */
+/* The wrapper's activations (model/net.py:31-36) fused with a Cartesian MSE on the regressed MET vector:
+ * met = softplus(out0), phi = pi (2 sigmoid(out1) - 1), loss = 0.5 mean_e[(met cos phi - t0)^2 + (met sin phi - t1)^2],
+ * t = truth[:, 0:2] (genMET px, py).  The reference keeps no loss for this variant (the wrapper is commented out); this
+ * one closes the training step.  out [B,2]; net_out (optional) [B,2] = (met, phi); grad_out (optional) [B,2] = dL/d out. */
+int gm_drn_met_loss(const float *out, const float *truth, int truth_stride, int B, float *net_out, float *loss_out,
+                    float *grad_out, void *stream);
 size_t gm_drn_bwd_ws_bytes(int N, int B, int k);
 int gm_drn_backward(const GmDrnParams *p, const GmDrnParams *grads, const float *x, int x_stride, const int *ptr, int N,
                     int B, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,

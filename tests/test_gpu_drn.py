@@ -337,3 +337,42 @@ def test_drn_backward_matches_oracle_autograd(name):
     out2 = ours(types.SimpleNamespace(x=x.to(DEV), batch=batch.to(DEV)))
     (out2 * R.to(DEV)).sum().backward()
     assert all(torch.equal(named[k].grad, g1[k]) for k in g1)
+
+
+def test_drn_trainer_step_matches_torch_adamw_on_oracle_gradients():
+    """DRNTrainer.train_step = forward + fused wrapper / MET loss + backward + flat AdamW: the loss equals the wrapper's
+    formula on the oracle side, and after one step every parameter equals torch.optim.AdamW applied to the gradients of
+    that loss taken through our own autograd node (itself checked against the oracle above)."""
+    import math
+    from deepmetv2_b200.trainer import DRNTrainer
+    torch.manual_seed(5)
+    b = synth.make_batch(4, "znunu", seed=93, sizes=[220, 180, 1, 260])
+    net_a, net_b = drn.DRNNet(), drn.DRNNet()
+    net_b.load_state_dict(net_a.state_dict())
+    net_a.to(DEV); net_b.to(DEV)
+    g = b.to(DEV)
+    # reference route: our autograd node + torch ops for the wrapper and the loss + torch AdamW
+    net_b.train()
+    o = net_b(g)                                             # (met, phi)
+    px, py = o[:, 0] * torch.cos(o[:, 1]), o[:, 0] * torch.sin(o[:, 1])
+    loss_b = 0.5 * ((px - g.y[:, 0]) ** 2 + (py - g.y[:, 1]) ** 2).mean()
+    loss_b.backward()
+    # fused route
+    before = {k: v.detach().clone() for k, v in net_a.named_parameters()}
+    tr = DRNTrainer(net_a, lr=1e-3)
+    loss_a = tr.train_step(g)
+    torch.cuda.synchronize()
+    assert abs(loss_a.item() - loss_b.item()) <= 1e-5 * abs(loss_b.item())
+    for k, pb in net_b.drn.named_parameters():
+        close(tr._gviews[k], pb.grad, 1e-4, "fused-loss gradient " + k)
+    # the update: torch.optim.AdamW fed with the fused step's own gradient (AdamW's first step is lr * sign(g): comparing
+    # two routes' updates directly would amplify rounding noise of near-zero gradient entries to +-lr)
+    clones = {k: torch.nn.Parameter(v.clone()) for k, v in before.items()}
+    for k, q in clones.items():
+        q.grad = tr._gviews[k.replace("drn.", "", 1)].clone()
+    torch.optim.AdamW(list(clones.values()), lr=1e-3).step()
+    for k, pa in net_a.named_parameters():
+        assert torch.allclose(pa, clones[k], rtol=1e-6, atol=1e-7), k
+    for (k, ba), (_, bb) in zip(net_a.named_buffers(), net_b.named_buffers()):
+        assert torch.allclose(ba.float(), bb.float(), rtol=1e-6, atol=1e-7), k
+    assert math.isfinite(tr.train_step_from_host(b.pin_memory()))
