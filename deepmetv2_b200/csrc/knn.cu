@@ -18,7 +18,10 @@ namespace {
 
 constexpr int KNN_WARPS = 8;
 constexpr int KNN_THREADS = KNN_WARPS * 32;
-constexpr int KNN_TILE = 128;      // candidates per shared-memory tile (64 at DP = 64: two tiles stay under 48 KB)
+#ifndef KNN_TILE_ROWS
+#define KNN_TILE_ROWS 128
+#endif
+constexpr int KNN_TILE = KNN_TILE_ROWS;   // candidates per shared-memory tile (dynamic shared memory: 2 x TILE x (DP + 4) floats)
 constexpr int KNN_MAX_K = 32;      // list entries per query = one per lane
 
 __device__ __forceinline__ void cp_async16(float *smem_dst, const float *gmem_src) {
@@ -43,8 +46,9 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
                                                             const int *__restrict__ n_dev) {
     constexpr int RS = DP + 4;                       // shared row stride (floats)
     constexpr int QB = KNN_WARPS * QPW;              // queries per CTA
-    constexpr int TILE = DP >= 64 ? KNN_TILE / 2 : KNN_TILE;
-    __shared__ __align__(16) float s_tile[2][TILE * RS];     // tile t+1 lands (cp.async) while tile t is searched
+    constexpr int TILE = KNN_TILE;
+    extern __shared__ __align__(16) float s_tile_raw[];      // [2][TILE * RS]: tile t+1 lands (cp.async) while tile t is searched
+    float *const s_tile[2] = {s_tile_raw, s_tile_raw + TILE * RS};
     pdl_sync();
     // n_dev (optional): the node count lives on the device (pooled DRN graph); rows beyond it get degree 0
     const int N = n_dev ? max(0, min(Ncap, *n_dev)) : Ncap;
@@ -114,11 +118,22 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
                             const float4 c = row[g][d4];
 #pragma unroll
                             for (int u = 0; u < QPW; ++u) {
+#ifndef KNN_SCALAR_SUB
+                                // the two subtractions of a dimension pair as ONE packed FADD2 (bit-identical halves);
+                                // the fmaf chain stays scalar and in dimension order
+                                const float2 d01 = fsub2(make_float2(c.x, c.y), make_float2(q[u][4 * d4 + 0], q[u][4 * d4 + 1]));
+                                const float2 d23 = fsub2(make_float2(c.z, c.w), make_float2(q[u][4 * d4 + 2], q[u][4 * d4 + 3]));
+                                acc[g][u] = __fmaf_rn(d01.x, d01.x, acc[g][u]);
+                                acc[g][u] = __fmaf_rn(d01.y, d01.y, acc[g][u]);
+                                acc[g][u] = __fmaf_rn(d23.x, d23.x, acc[g][u]);
+                                acc[g][u] = __fmaf_rn(d23.y, d23.y, acc[g][u]);
+#else
                                 float df;
                                 df = __fsub_rn(c.x, q[u][4 * d4 + 0]); acc[g][u] = __fmaf_rn(df, df, acc[g][u]);
                                 df = __fsub_rn(c.y, q[u][4 * d4 + 1]); acc[g][u] = __fmaf_rn(df, df, acc[g][u]);
                                 df = __fsub_rn(c.z, q[u][4 * d4 + 2]); acc[g][u] = __fmaf_rn(df, df, acc[g][u]);
                                 df = __fsub_rn(c.w, q[u][4 * d4 + 3]); acc[g][u] = __fmaf_rn(df, df, acc[g][u]);
+#endif
                             }
                         }
                     }
@@ -205,7 +220,14 @@ int launch_search(const float *x, int stride, int dim, const int *ptr, int N, in
                   const int *n_dev, cudaStream_t st) {
     const int qb = KNN_WARPS * QPW;
     const int grid = persistent_grid(((long long)N + qb - 1) / qb, 16);
-    GM_LAUNCH_PDL((k_knn_search<DP, QPW, CPL>), grid, KNN_THREADS, 0, st, x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev);
+    constexpr size_t smem = (size_t)2 * KNN_TILE * (DP + 4) * sizeof(float);
+    static bool attr = false;
+    if (!attr) {
+        if (smem > 48 * 1024)
+            GM_CUDA_TRY(cudaFuncSetAttribute(k_knn_search<DP, QPW, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = true;
+    }
+    GM_LAUNCH_PDL((k_knn_search<DP, QPW, CPL>), grid, KNN_THREADS, smem, st, x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }
