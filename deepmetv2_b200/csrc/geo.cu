@@ -325,6 +325,7 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
         const int grp = lane >> 3, c4 = lane & 7, ch = 4 * c4 + grp;
         float px_l = 0.f, py_l = 0.f, acc0 = IDENT, acc1 = IDENT, acc2 = IDENT, acc3 = IDENT;
         int th_l = 0, excl_l = -1, deg_l = 0;
+        float qp0 = 0.f, qp1 = 0.f, qp2 = 0.f, qp3 = 0.f;
         GeoMeta mm;
         mm.r2 = m.r2; mm.dim = m.dim; mm.phi_wrap = m.phi_wrap;
         for (uint32_t gc = 0;; ++gc) {
@@ -340,6 +341,10 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
             if (flags & AG_FIRST) {
                 acc0 = acc1 = acc2 = acc3 = IDENT;
                 deg_l = 0;
+                qp0 = (a + warp < b) ? __ldg(P + (size_t)(n0 + a + warp) * H + ch) : 0.f;      // in flight for the whole segment
+                qp1 = (a + warp + AG_CONSUMERS < b) ? __ldg(P + (size_t)(n0 + a + warp + AG_CONSUMERS) * H + ch) : 0.f;
+                qp2 = (a + warp + 2 * AG_CONSUMERS < b) ? __ldg(P + (size_t)(n0 + a + warp + 2 * AG_CONSUMERS) * H + ch) : 0.f;
+                qp3 = (a + warp + 3 * AG_CONSUMERS < b) ? __ldg(P + (size_t)(n0 + a + warp + 3 * AG_CONSUMERS) * H + ch) : 0.f;
                 const int t = a + warp + lane * AG_CONSUMERS;                   // lanes 0..3: slot = lane
                 if (lane < AG_TPW && t < b) {
                     const float4 pt = reinterpret_cast<const float4 *>(stage + AG_OFF_TGT)[t];
@@ -380,7 +385,7 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
                     if (t >= b) continue;
                     const float acc = u == 0 ? acc0 : u == 1 ? acc1 : u == 2 ? acc2 : acc3;
                     const size_t node = (size_t)(n0 + t);
-                    const float p = __ldg(P + node * H + ch);
+                    const float p = u == 0 ? qp0 : u == 1 ? qp1 : u == 2 ? qp2 : qp3;
                     float o;
                     if (dg == 0) o = 0.f;                                      // PyG: empty rows aggregate to 0
                     else if (AGGR == GM_AGGR_MAX) o = p + acc;
