@@ -291,8 +291,11 @@ __device__ __forceinline__ float fold_groups(float v) {             // over the 
 // full[s] (1 arrival + TMA bytes) / empty[s] (AG_CONSUMERS arrivals) mbarriers; no CTA-wide barrier in the main loop.
 // Items are scheduled statically (item = blockIdx + k * gridDim) when BatchNorm partials are produced, so the per-CTA
 // moments are bit-reproducible; without them (eval) the producer takes tickets from a self-resetting counter.
+#ifndef GEO_AG_MINB
+#define GEO_AG_MINB 3
+#endif
 template <int AGGR, bool ARG, bool Q4 = false>
-__global__ void __launch_bounds__(AG_THREADS, 3)
+__global__ void __launch_bounds__(AG_THREADS, GEO_AG_MINB)
 k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, int N, float *__restrict__ out,
            int *__restrict__ arg, AggrTail tail) {
     extern __shared__ __align__(128) unsigned char gs[];

@@ -18,6 +18,15 @@ namespace {
 
 constexpr int KNN_WARPS = 8;
 constexpr int KNN_THREADS = KNN_WARPS * 32;
+#ifndef KNN_QPW64
+#define KNN_QPW64 5
+#endif
+#ifndef KNN_QPW32
+#define KNN_QPW32 2
+#endif
+#ifndef QSMEM_ENABLED
+#define QSMEM_ENABLED 1
+#endif
 #ifndef KNN_TILE_ROWS
 #define KNN_TILE_ROWS 128
 #endif
@@ -46,9 +55,16 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
                                                             const int *__restrict__ n_dev) {
     constexpr int RS = DP + 4;                       // shared row stride (floats)
     constexpr int QB = KNN_WARPS * QPW;              // queries per CTA
-    constexpr int TILE = KNN_TILE;
+    constexpr int TILE = DP >= 64 ? (KNN_TILE * 3) / 4 : KNN_TILE;     // 96 rows at 64-d: 4 resident CTAs per SM
     extern __shared__ __align__(16) float s_tile_raw[];      // [2][TILE * RS]: tile t+1 lands (cp.async) while tile t is searched
     float *const s_tile[2] = {s_tile_raw, s_tile_raw + TILE * RS};
+    // QS: the warp's QPW queries live in SHARED memory and are read with broadcast LDS.128 (one 16-byte wavefront),
+    // the candidate row is read once per 4 dimensions (a 512-byte, 4-wavefront LDS.128) and shared by all QPW
+    // queries.  With one query per warp and its coordinates in registers the search was bound by the shared-memory
+    // pipe (64 cycles of candidate rows per 32 FP cycles); with 8 queries per warp it is FP-bound.
+    constexpr bool QS = QSMEM_ENABLED && QPW >= 4 && DP >= 32;
+    float *const s_q = s_tile_raw + 2 * TILE * RS;          // [KNN_WARPS * QPW][DP] (QS only)
+    const uint32_t sq_addr = (uint32_t)__cvta_generic_to_shared(s_q + (threadIdx.x >> 5) * QPW * DP);
     pdl_sync();
     // n_dev (optional): the node count lives on the device (pooled DRN graph); rows beyond it get degree 0
     const int N = n_dev ? max(0, min(Ncap, *n_dev)) : Ncap;
@@ -72,7 +88,7 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
     for (long long blk = blockIdx.x; blk * QB < N; blk += gridDim.x) {
         const int q0 = (int)(blk * QB), q1 = min(N, q0 + QB);
         // ---- this warp's queries: coordinates (zero-padded to DP), event, list
-        float q[QPW][DP];
+        float q[QPW][QS ? 1 : DP];
         int qi[QPW], qe[QPW];
         float ld[QPW], worst[QPW];
         int li[QPW];
@@ -81,8 +97,15 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
             qi[u] = q0 + warp * QPW + u;
             const bool live = qi[u] < N;
             qe[u] = live ? event_of(ptr, B, qi[u]) : -1;
+            if constexpr (QS) {
+                __syncwarp();
+                for (int d = lane; d < DP; d += 32)
+                    s_q[(warp * QPW + u) * DP + d] = (live && d < dim) ? __ldg(x + (size_t)qi[u] * stride + d) : 0.f;
+                __syncwarp();
+            } else {
 #pragma unroll
-            for (int d = 0; d < DP; ++d) q[u][d] = (live && d < dim) ? __ldg(x + (size_t)qi[u] * stride + d) : 0.f;
+                for (int d = 0; d < DP; ++d) q[u][d] = (live && d < dim) ? __ldg(x + (size_t)qi[u] * stride + d) : 0.f;
+            }
             ld[u] = INFINITY; li[u] = -1; worst[u] = INFINITY;
         }
         const int e_first = event_of(ptr, B, q0), e_last = event_of(ptr, B, q1 - 1);
@@ -118,6 +141,19 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn_search(const float *__restr
                             const float4 c = row[g][d4];
 #pragma unroll
                             for (int u = 0; u < QPW; ++u) {
+                                if constexpr (QS) {
+                                    float4 qv;                              // volatile: keep the loop-invariant load IN the loop
+                                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                                 : "=f"(qv.x), "=f"(qv.y), "=f"(qv.z), "=f"(qv.w)
+                                                 : "r"(sq_addr + (uint32_t)(u * DP * 4 + 16 * d4)));
+                                    const float2 d01 = fsub2(make_float2(c.x, c.y), make_float2(qv.x, qv.y));
+                                    const float2 d23 = fsub2(make_float2(c.z, c.w), make_float2(qv.z, qv.w));
+                                    acc[g][u] = __fmaf_rn(d01.x, d01.x, acc[g][u]);
+                                    acc[g][u] = __fmaf_rn(d01.y, d01.y, acc[g][u]);
+                                    acc[g][u] = __fmaf_rn(d23.x, d23.x, acc[g][u]);
+                                    acc[g][u] = __fmaf_rn(d23.y, d23.y, acc[g][u]);
+                                    continue;
+                                }
 #ifndef KNN_SCALAR_SUB
                                 // the two subtractions of a dimension pair as ONE packed FADD2 (bit-identical halves);
                                 // the fmaf chain stays scalar and in dimension order
@@ -220,7 +256,8 @@ int launch_search(const float *x, int stride, int dim, const int *ptr, int N, in
                   const int *n_dev, cudaStream_t st) {
     const int qb = KNN_WARPS * QPW;
     const int grid = persistent_grid(((long long)N + qb - 1) / qb, 16);
-    constexpr size_t smem = (size_t)2 * KNN_TILE * (DP + 4) * sizeof(float);
+    constexpr int TILE = DP >= 64 ? (KNN_TILE * 3) / 4 : KNN_TILE;
+    constexpr size_t smem = (size_t)(2 * TILE * (DP + 4) + KNN_WARPS * QPW * DP) * sizeof(float);
     static bool attr = false;
     if (!attr) {
         if (smem > 48 * 1024)
@@ -240,8 +277,8 @@ int knn_search_table(const float *x, int stride, int dim, const int *ptr, int N,
     if (dim <= 4) return launch_search<4, 4>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
     if (dim <= 8) return launch_search<8, 4>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
     if (dim <= 16) return launch_search<16, 2>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
-    if (dim <= 32) return launch_search<32, 2>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
-    return launch_search<64, 1, 1>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
+    if (dim <= 32) return launch_search<32, KNN_QPW32>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
+    return launch_search<64, KNN_QPW64, 1>(x, stride, dim, ptr, N, B, K, loop, nbr, deg, n_dev, st);
 }
 
 }  // namespace gm
