@@ -303,9 +303,9 @@ def run_drn(args):
 
 def drn_line(args):
     """Side line for BASELINE config 4 / row f1: the DynamicReductionNetwork variant (model/dynamic_reduction_network.py with
-    the wrapper of model/net.py:12-37) on 32 synthetic Z->nunu-shaped events.  fp32: a full TRAINING step (forward with
-    BatchNorm over the edge rows, fused wrapper + MET loss, backward of all 31 tensors, flat AdamW) through DRNTrainer;
-    bf16: the tcgen05 edge MLP, train-mode forward only (the backward differentiates the fp32 forward)."""
+    the wrapper of model/net.py:12-37) on 32 synthetic Z->nunu-shaped events: a full TRAINING step (forward with
+    BatchNorm over the edge rows, fused wrapper + MET loss, backward of all 31 tensors, flat AdamW) through DRNTrainer.
+    --precision bf16: the forward's edge MLP on tcgen05, the backward in fp32 (straight-through)."""
     import types
     from deepmetv2_b200 import synth
     from deepmetv2_b200._lib import lib, TIMERS
@@ -317,7 +317,7 @@ def drn_line(args):
     torch.manual_seed(0)
     net = drn.DRNNet().to(dev).train()
     net.drn.edge_precision = args.precision
-    training = args.precision == "fp32"
+    training = True
     host = [synth.make_batch(B, "znunu", seed=4000 + i).pin_memory() for i in range(N_ROTATE)]
     devb = [b.to(dev) for b in host]
     men = [int((b.ptr[1:] - b.ptr[:-1]).max()) for b in host]
@@ -365,11 +365,7 @@ def drn_line(args):
     edge_us = edge_ms / max(edge_n, 1) * 1e3
     # per-edge tile products: forward 96x64; backward = forward recompute + dW2 + W2^T dz2 (3 x 96x64)
     flop_per_launch = (E1 + E2) / 2 * 2.0 * 96 * 64 * (3 if training else 1)
-    if tensor:
-        pk = _peaks()
-        peak, peak_src, unit_bound = pk["bf16_tflops_sustained"], pk["source"], "tensor"
-    else:
-        peak, peak_src, unit_bound = fp32_peak_tflops(l), "FFMA stream measured live by gm_bench_ffma", "fp32 pipe"
+    peak, peak_src, unit_bound = fp32_peak_tflops(l), "FFMA stream measured live by gm_bench_ffma", "fp32 pipe"
     ach = flop_per_launch / (edge_us * 1e-6) / 1e12
     # e2e: pinned host x / y / ptr -> H2D -> step -> loss (training) or [B,2] (inference) back on the host
     t0 = time.perf_counter()

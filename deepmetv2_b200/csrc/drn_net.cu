@@ -357,8 +357,9 @@ __global__ void __launch_bounds__(TC_THREADS, 4) k_drn_edge_tc(const float *__re
     if (warp == 0) tc5_alloc(smem_u32(s_tc + TC_OFF_BAR + 8), 64);
     for (int t = tid; t < DH * (DM / 8); t += TC_THREADS) {
         const int n = t / (DM / 8), q = t - n * (DM / 8);
-        const float4 w0 = *reinterpret_cast<const float4 *>(w2 + (size_t)n * DM + 8 * q);
-        const float4 w1 = *reinterpret_cast<const float4 *>(w2 + (size_t)n * DM + 8 * q + 4);
+        const float *wp = w2 + (size_t)n * DM + 8 * q;   // scalar loads: parameters may sit at any 4-byte offset of a flat buffer
+        const float4 w0 = make_float4(wp[0], wp[1], wp[2], wp[3]);
+        const float4 w1 = make_float4(wp[4], wp[5], wp[6], wp[7]);
         const uint32_t addr = b_base + (uint32_t)((n >> 3) * TC_SBO + q * TC_LBO + (n & 7) * 16);
         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(tc5_pack_bf16(w0.x, w0.y)),
                      "r"(tc5_pack_bf16(w0.z, w0.w)), "r"(tc5_pack_bf16(w1.x, w1.y)), "r"(tc5_pack_bf16(w1.z, w1.w)) : "memory");

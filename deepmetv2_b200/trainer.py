@@ -485,7 +485,10 @@ class DRNTrainer:
     forward (``gm_drn_forward``, train-mode BatchNorm over the edge rows) -> wrapper activations + Cartesian MET loss
     (``gm_drn_met_loss``) -> backward (``gm_drn_backward``, all 31 gradients into one flat buffer) -> fused flat AdamW
     (``gm_adamw_step``).  Parameters stay the module's ``nn.Parameter``s (re-pointed at a flat fp32 buffer);
-    ``trainer.optimizer`` is the same torch-Optimizer-shaped handle as GraphMETTrainer's."""
+    ``trainer.optimizer`` is the same torch-Optimizer-shaped handle as GraphMETTrainer's.
+    ``net.edge_precision = "bf16"`` runs the FORWARD's 96 -> 64 edge contraction on tcgen05 (``k_drn_edge_tc``); the
+    backward stays fp32 and routes through the arg-max sources that forward recorded (the bf16 rounding is treated as
+    the identity: a straight-through estimate, reported under a looser tolerance)."""
 
     def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01):
         self.model = model
@@ -567,7 +570,7 @@ class DRNTrainer:
         # the workspaces are allocated at their capacity: the layout is a function of (N, B), so pass exact sizes
         fws = l.gm_drn_ws_bytes(N, B, int(net.k))
         bws = l.gm_drn_bwd_ws_bytes(N, B, int(net.k))
-        check(l.gm_drn_forward(C.byref(self._P), ptr(x), x.stride(0), ptr(p), N, B, int(men), 1, PRECISION["fp32"],
+        check(l.gm_drn_forward(C.byref(self._P), ptr(x), x.stride(0), ptr(p), N, B, int(men), 1, PRECISION[net.edge_precision],
                                float(bn.momentum if bn.momentum is not None else 0.1), float(bn.eps), ptr(self.fwd_ws), fws,
                                ptr(self.out), None, None, st), "gm_drn_forward")
         check(l.gm_drn_met_loss(ptr(self.out), ptr(y), y.stride(0), B, ptr(self.net_out), ptr(self.loss), ptr(self.dout), st),
