@@ -127,6 +127,8 @@ SIGNATURES = {
     "gm_drn_ws_bytes": (_sz, [_i, _i, _i]),
     "gm_drn_forward": (_i, [C.POINTER(GmDrnParams), _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _f, _vp, _sz, _vp, _vp,
                             C.POINTER(GmDrnView), _vp]),
+    "gm_exchange_post": (_i, [_vp, _i, _f, _vp, _vp, _vp]),
+    "gm_exchange_apply_adamw": (_i, [_vp, _vp, _vp, _i, _f, _f, _f, _f, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gm_drn_met_loss": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "gm_drn_bwd_ws_bytes": (_sz, [_i, _i, _i]),
     "gm_drn_backward": (_i, [C.POINTER(GmDrnParams), C.POINTER(GmDrnParams), _vp, _i, _vp, _i, _i, _vp, _sz, _vp, _sz, _vp, _vp]),

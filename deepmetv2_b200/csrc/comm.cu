@@ -124,6 +124,61 @@ k_exchange_adamw(float *__restrict__ p, const float *__restrict__ g, float *__re
     }
 }
 
+// The same exchange as TWO kernels, so that the wait for the peers can be moved behind work of the NEXT step that does
+// not depend on the updated weights (its radius-graph build): k_exchange_post ends step s (push + flags, never waits),
+// k_exchange_apply runs in step s + 1 right before the forward (wait, rank-ordered sum, AdamW).  Same slots, flags,
+// parity and summation order as the fused kernel: the parameters are bit-identical either way.
+__global__ void __launch_bounds__(CM_THREADS)
+k_exchange_post(const float *__restrict__ g, int n, float local_events, const float *__restrict__ local_loss, CommView c) {
+    pdl_wait();
+    const int t = threadIdx.x, i = blockIdx.x * CM_THREADS + t;
+    const int W = c.world, par = (int)(c.seq & 1u);
+    if (i < c.np) {
+        float mine = 0.f;
+        if (i < n) mine = g[i];
+        else if (i == n) mine = local_events;
+        else if (i == n + 1) mine = local_events > 0.f ? local_events * local_loss[0] : 0.f;
+        const size_t off = ((size_t)par * W + c.rank) * c.np + i;
+        for (int r = 0; r < W; ++r) c.slots[(c.rank + r) % W][off] = mine;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (t < W) st_release_sys(c.flags[t] + (size_t)c.rank * CM_MAX_CTAS + blockIdx.x, c.seq);
+}
+
+__global__ void __launch_bounds__(CM_THREADS)
+k_exchange_apply(float *__restrict__ p, float *__restrict__ m, float *__restrict__ v, int n, float lr, float b1, float b2,
+                 float eps, float wd, float bc1, float bc2_sqrt, CommView c, float *__restrict__ global_loss, StepStatus status) {
+    pdl_wait();
+    const int t = threadIdx.x, i = blockIdx.x * CM_THREADS + t;
+    const int W = c.world, par = (int)(c.seq & 1u);
+    const int tail = n / CM_THREADS;
+    if (blockIdx.x == 0 && t == 0) status.publish();
+    const unsigned *my_flags = c.flags[c.rank];
+    if (t < W) wait_flag(my_flags + (size_t)t * CM_MAX_CTAS + blockIdx.x, c.seq);
+    else if (t >= 32 && t < 32 + W && (int)blockIdx.x != tail) wait_flag(my_flags + (size_t)(t - 32) * CM_MAX_CTAS + tail, c.seq);
+    __syncthreads();
+    const float *mine_slots = c.slots[c.rank] + (size_t)par * W * c.np;
+    float events = 0.f;
+    for (int r = 0; r < W; ++r) events += ld_relaxed_sys(mine_slots + (size_t)r * c.np + n);
+    const float inv_events = 1.f / fmaxf(events, 1.f);
+    if (i < n) {
+        float gi = 0.f;
+        for (int r = 0; r < W; ++r) gi += ld_relaxed_sys(mine_slots + (size_t)r * c.np + i);
+        gi *= inv_events;
+        float pi = p[i] * (1.f - lr * wd);
+        const float mi = b1 * m[i] + (1.f - b1) * gi;
+        const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+        const float denom = sqrtf(vi) / bc2_sqrt + eps;
+        pi -= (lr / bc1) * (mi / denom);
+        p[i] = pi; m[i] = mi; v[i] = vi;
+    } else if (i == n + 1 && global_loss) {
+        float ls = 0.f;
+        for (int r = 0; r < W; ++r) ls += ld_relaxed_sys(mine_slots + (size_t)r * c.np + i);
+        global_loss[0] = ls * inv_events;
+    }
+}
+
 // comm == NULL: the same arithmetic without peers
 __global__ void __launch_bounds__(CM_THREADS)
 k_local_adamw(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m, float *__restrict__ v, int n,
@@ -233,6 +288,42 @@ int gm_allreduce_adamw_step(float *params, const float *grads, float *exp_avg, f
     GM_LAUNCH_PDL(k_exchange_adamw, (comm->np + CM_THREADS - 1) / CM_THREADS, CM_THREADS, 0, st, params, grads, exp_avg,
                   exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), local_events,
                   local_loss_dev, v, global_loss_out, status);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+static CommView view_of(GmComm *comm, unsigned seq) {
+    CommView v{};
+    v.rank = comm->rank; v.world = comm->world; v.np = comm->np;
+    v.seq = seq;
+    for (int r = 0; r < comm->world; ++r) {
+        v.slots[r] = reinterpret_cast<float *>(comm->peer[r]);
+        v.flags[r] = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(comm->peer[r]) + slots_bytes(comm->np, comm->world));
+    }
+    return v;
+}
+
+int gm_exchange_post(const float *grads, int n, float local_events, const float *local_loss_dev, GmComm *comm, void *stream) {
+    if (n < 1 || !grads || !local_loss_dev || local_events < 0.f || !comm || comm->world < 2) return GM_ERR_INVALID_ARGUMENT;
+    if (!comm->connected || comm->n != n) return GM_ERR_INVALID_ARGUMENT;
+    const CommView v = view_of(comm, ++comm->seq);
+    GM_LAUNCH_PDL(k_exchange_post, (comm->np + CM_THREADS - 1) / CM_THREADS, CM_THREADS, 0, as_stream(stream), grads, n,
+                  local_events, local_loss_dev, v);
+    GM_LAUNCH_CHECK();
+    return GM_OK;
+}
+
+int gm_exchange_apply_adamw(float *params, float *exp_avg, float *exp_avg_sq, int n, float lr, float beta1, float beta2,
+                            float eps, float weight_decay, int step, GmComm *comm, float *global_loss_out,
+                            const int *err_flags_dev, const int *graph_stats_dev, int *status_host, void *stream) {
+    if (n < 1 || step < 1 || !params || !exp_avg || !exp_avg_sq || !comm || comm->world < 2) return GM_ERR_INVALID_ARGUMENT;
+    if (!comm->connected || comm->n != n || comm->seq == 0) return GM_ERR_INVALID_ARGUMENT;
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    const StepStatus status{err_flags_dev, graph_stats_dev, status_host, step};
+    const CommView v = view_of(comm, comm->seq);          // the exchange the last gm_exchange_post opened
+    GM_LAUNCH_PDL(k_exchange_apply, (comm->np + CM_THREADS - 1) / CM_THREADS, CM_THREADS, 0, as_stream(stream), params, exp_avg,
+                  exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), v, global_loss_out, status);
     GM_LAUNCH_CHECK();
     return GM_OK;
 }

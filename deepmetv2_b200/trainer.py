@@ -62,7 +62,7 @@ class FusedAdamW(torch.optim.Optimizer):
 class GraphMETTrainer:
     def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, r=0.4,
                  max_num_neighbors=255, loop=True, phi_wrap=False, process_group=None, device=None,
-                 graph="implicit", fused_allreduce=True, knn_k=20):
+                 graph="implicit", fused_allreduce=True, knn_k=20, overlap_exchange=True):
         self.model = model
         self.net = model.graphnet if hasattr(model, "graphnet") else model
         self.apply_sigmoid = hasattr(model, "graphnet")       # Net applies the sigmoid, GraphMETNetwork does not
@@ -109,6 +109,11 @@ class GraphMETTrainer:
         self._status = torch.zeros(4, dtype=torch.int32).pin_memory()
         self._status_seen = 0
         self.comm = None
+        # overlap_exchange (peer-memory exchange only): a step ENDS by pushing its gradient to the peers and the wait +
+        # AdamW run at the start of the next step, behind that step's radius-graph build (which does not read the
+        # weights), so rank skew up to one graph build is hidden.  flush() applies a pending update at once.
+        self.overlap_exchange = bool(overlap_exchange)
+        self._pending = None
         if self.world > 1 and fused_allreduce:
             self._connect_peers(n)
 
@@ -146,8 +151,18 @@ class GraphMETTrainer:
         elif comm:
             l.gm_comm_destroy(comm)
 
+    def flush(self):
+        """Apply the gradient exchange of the last step if it is still pending (``overlap_exchange``): parameters,
+        optimizer state and ``global_loss`` are up to date afterwards.  Every rank must call it at the same point."""
+        if self._pending is not None:
+            hyper, self._pending = self._pending, None
+            check(lib().gm_exchange_apply_adamw(ptr(self.flat), ptr(self.exp_avg), ptr(self.exp_avg_sq), self.flat.numel(),
+                                                *hyper, self.comm, ptr(self.global_loss), ptr(self.flags), ptr(self.stats),
+                                                ptr(self._status), stream(self.device)), "gm_exchange_apply_adamw")
+
     def close(self):
         if self.comm is not None:
+            self.flush()
             lib().gm_comm_destroy(self.comm)
             self.comm = None
 
@@ -162,6 +177,7 @@ class GraphMETTrainer:
         saving a checkpoint or evaluating -- the buffer broadcast DistributedDataParallel does every forward)."""
         if self.world == 1:
             return
+        self.flush()
         import torch.distributed as dist
         for _, buf in self.net.named_buffers():
             dist.broadcast(buf, src=dist.get_global_rank(self.pg, src), group=self.pg)
@@ -341,6 +357,7 @@ class GraphMETTrainer:
         if N > 0 and B > 0:
             self._reserve(N, B, men)
             self._graph(x, p, N, B, men, need_transpose=True)
+            self.flush()            # the previous step's update, behind this step's (weight-independent) graph build
             self._forward(x, N, B, training=True, save=True)
             # DP: gradient of the per-event SUM; the optimiser kernel divides by the global event count
             check(l.gm_met_loss_ex(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
@@ -348,6 +365,7 @@ class GraphMETTrainer:
                   "gm_met_loss")
             self._backward(x, N, B)
         else:                       # empty shard: nothing to differentiate, but the exchange below must still happen
+            self.flush()
             self._payload.zero_()
             self.loss.zero_()
             B = 0
@@ -359,6 +377,12 @@ class GraphMETTrainer:
             check(l.gm_adamw_step_ex(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq),
                                      self.flat.numel(), *hyper, 1.0, None, *mirrors, st), "gm_adamw_step")
             return self.loss
+        if self.comm is not None and self.overlap_exchange:
+            # push now, wait + AdamW at the start of the next step (or in flush()); global_loss lags by that much
+            check(l.gm_exchange_post(ptr(self.flat_grad), self.flat.numel(), float(B), ptr(self.loss), self.comm, st),
+                  "gm_exchange_post")
+            self._pending = hyper
+            return self.global_loss
         if self.comm is not None:   # ONE kernel: push to peers over NVLink, wait, rank-ordered sum, AdamW
             check(l.gm_allreduce_adamw_step(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg),
                                             ptr(self.exp_avg_sq), self.flat.numel(), *hyper, float(B), ptr(self.loss),
@@ -383,6 +407,7 @@ class GraphMETTrainer:
         men = max_event_nodes if max_event_nodes is not None else \
             int((host_batch.ptr[1:] - host_batch.ptr[:-1]).max())       # host tensor: no device sync
         loss = self.train_step(EventBatch(x, y, None, p), men)
+        self.flush()                # the caller reads this step's (global) loss: no deferral on this path
         self._host_loss.copy_(loss, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return float(self._host_loss)
@@ -397,6 +422,7 @@ class GraphMETTrainer:
         losses, pending = [], None
         for k, b in enumerate(HostFeeder(host_batches, self.device, depth=depth)):
             loss = step(b)
+            self.flush()            # every step's loss is read back: apply the exchange before the copy is enqueued
             slot, ev = self._loss_ring[k & 1]
             slot.copy_(loss, non_blocking=True)
             ev.record()
@@ -423,6 +449,7 @@ class GraphMETTrainer:
     @torch.no_grad()
     def eval_step(self, batch: EventBatch, max_event_nodes: int | None = None):
         """evaluate.py:81-100 fused: returns (weights[N] view, loss 0-dim, met[B,2]) on the device."""
+        self.flush()
         x, y, p = batch.x, batch.y, batch.ptr
         self._check_batch(x, y, p)
         N, B, men = self._sizes(batch, max_event_nodes)
@@ -454,6 +481,8 @@ class GraphMETTrainer:
     # ------------------------------------------------------------------------------------------ optimizer state
     def optimizer_state_dict(self):
         """State in torch.optim.AdamW's layout (what the reference stores as ``optim_dict``)."""
+        if getattr(self, "_pending", None) is not None:
+            self.flush()
         state, off = {}, 0
         for i, v in enumerate(self._views):
             k = v.numel()

@@ -505,6 +505,16 @@ int gm_drn_backward(const GmDrnParams *p, const GmDrnParams *grads, const float 
                     int B, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
                     const float *grad_out, void *stream);
 
+/* The same exchange as two calls, for callers that put weight-independent work of the NEXT step (its graph build)
+ * between them: gm_exchange_post ends step s (pushes this rank's payload to every peer and raises the flags; never
+ * waits), gm_exchange_apply_adamw (waits for the peers' payloads of that exchange, rank-ordered sum, global-event-count
+ * scaling, AdamW) runs before the next forward.  Every post must be followed by exactly one apply on every rank;
+ * parameters end up bit-identical to gm_allreduce_adamw_step. */
+int gm_exchange_post(const float *grads, int n, float local_events, const float *local_loss_dev, GmComm *comm, void *stream);
+int gm_exchange_apply_adamw(float *params, float *exp_avg, float *exp_avg_sq, int n, float lr, float beta1, float beta2,
+                            float eps, float weight_decay, int step, GmComm *comm, float *global_loss_out,
+                            const int *err_flags_dev, const int *graph_stats_dev, int *status_host, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,7 +26,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, fused, out_dir):
+def _worker(rank, world, port, mode, out_dir):
     import torch.distributed as dist
     from deepmetv2_b200 import dp, synth
     from deepmetv2_b200.model import net as gnet
@@ -40,7 +40,9 @@ def _worker(rank, world, port, fused, out_dir):
     try:
         torch.manual_seed(0)
         model = gnet.Net(8, 3).to(dev)
-        tr = GraphMETTrainer(model, lr=1e-3, process_group=dist.group.WORLD, fused_allreduce=fused)
+        fused = mode != "nccl"
+        tr = GraphMETTrainer(model, lr=1e-3, process_group=dist.group.WORLD, fused_allreduce=fused,
+                             overlap_exchange=(mode == "overlap"))
         assert (tr.comm is not None) == fused, "CUDA IPC peer mapping failed on this box"
         full = synth.make_batch(5, "dytt", seed=90, sizes=[230, 180, 260, 150, 205])
         shards = [(0, 3), (3, 5)]                               # 3 + 2 events: different B per rank
@@ -53,6 +55,9 @@ def _worker(rank, world, port, fused, out_dir):
                 b = dp.slice_batch(full, 0, 5) if rank == 0 else dp.slice_batch(full, 5, 5)
             g = EventBatch(b.x.to(dev), b.y.to(dev), None, b.ptr.to(dev).int())
             loss = tr.train_step(g, max_event_nodes=300)
+            if mode == "overlap":
+                assert tr._pending is not None          # the update of this step waits for the next step / flush()
+            tr.flush()
             torch.cuda.synchronize()
             record[f"loss{step}"] = loss.item()
             record[f"flat{step}"] = tr.flat.cpu().clone()
@@ -67,8 +72,10 @@ def _worker(rank, world, port, fused, out_dir):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("fused", [True, False])
-def test_two_rank_training_is_replica_exact_and_globally_weighted(tmp_path, fused):
+@pytest.mark.parametrize("mode", ["overlap", "fused", "nccl"])
+def test_two_rank_training_is_replica_exact_and_globally_weighted(tmp_path, mode):
+    """overlap: gm_exchange_post at the end of a step, gm_exchange_apply_adamw behind the next step's graph build (here:
+    in flush()); fused: both in one kernel; nccl: torch.distributed.all_reduce + gm_adamw_step_ex."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
@@ -76,7 +83,7 @@ def test_two_rank_training_is_replica_exact_and_globally_weighted(tmp_path, fuse
     from deepmetv2_b200.model import net as gnet
     from deepmetv2_b200.synth import EventBatch
     from deepmetv2_b200.trainer import GraphMETTrainer
-    mp.spawn(_worker, args=(2, _free_port(), fused, str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), mode, str(tmp_path)), nprocs=2, join=True)
     r0 = torch.load(tmp_path / "rank0.pt", weights_only=False)
     r1 = torch.load(tmp_path / "rank1.pt", weights_only=False)
     for step in range(3):
@@ -100,3 +107,43 @@ def test_two_rank_training_is_replica_exact_and_globally_weighted(tmp_path, fuse
     assert (got - want).abs().max().item() <= 1e-5 * want.abs().max().item()
     want_loss = (counts[0] * losses[0] + counts[1] * losses[1]) / sum(counts)
     assert abs(r0["loss0"] - want_loss) <= 1e-6 * abs(want_loss)
+
+
+def _worker_overlap_steps(rank, world, port, overlap, out_dir):
+    """Several back-to-back steps WITHOUT flushing in between (the deferred update runs inside the next step)."""
+    import torch.distributed as dist
+    from deepmetv2_b200 import synth
+    from deepmetv2_b200.model import net as gnet
+    from deepmetv2_b200.trainer import GraphMETTrainer
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        torch.manual_seed(0)
+        model = gnet.Net(8, 3).to(dev)
+        tr = GraphMETTrainer(model, lr=1e-3, process_group=dist.group.WORLD, overlap_exchange=overlap)
+        batches = [synth.make_batch(3, "dytt", seed=200 + 10 * rank + i, sizes=[220, 260, 180]).to(dev) for i in range(3)]
+        for step in range(6):
+            tr.train_step(batches[step % 3], max_event_nodes=300)
+        tr.flush()
+        torch.cuda.synchronize()
+        torch.save({"flat": tr.flat.cpu().clone(), "loss": tr.global_loss.item()}, os.path.join(out_dir, f"o{int(overlap)}_rank{rank}.pt"))
+        dist.barrier()
+        tr.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_deferred_exchange_equals_fused_exchange_after_six_steps(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    for overlap in (True, False):
+        mp.spawn(_worker_overlap_steps, args=(2, _free_port(), overlap, str(tmp_path)), nprocs=2, join=True)
+    a0, a1 = (torch.load(tmp_path / f"o1_rank{r}.pt", weights_only=False) for r in (0, 1))
+    b0 = torch.load(tmp_path / "o0_rank0.pt", weights_only=False)
+    assert torch.equal(a0["flat"], a1["flat"])                    # replicas identical
+    assert torch.equal(a0["flat"], b0["flat"])                    # and bit-identical to the one-kernel exchange
+    assert a0["loss"] == b0["loss"]
