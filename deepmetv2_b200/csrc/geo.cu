@@ -806,9 +806,10 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
     TimedRegion tr(GM_TIMER_RADIUS_GRAPH, st);
     const float rf = (float)r, r2 = (float)(r * r);          // r*r in double, then fp32
     const int cap_eff = loop ? max_num_neighbors : max_num_neighbors + 1;
-    GM_TRY(bin_points(pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt, w.cell_start, w.tmp, w.stats, st));
+    int *stats = stats_out ? stats_out : w.stats;             // the kernels count straight into the caller's words
+    GM_TRY(bin_points(pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt, w.cell_start, w.tmp, stats, st));
     GM_LAUNCH_PDL(k_geo_init, persistent_grid((N + 255) / 256, 4), 256, 0, st, w.meta, rf, r2, dim, phi_wrap, loop, cap_eff, N, B,
-                  ptr, w.ptr, w.sched, w.thr, w.stats);
+                  ptr, w.ptr, w.sched, w.thr, stats);
     GM_LAUNCH_CHECK();
     if (N > 0) {
         GM_LAUNCH_PDL(k_cell_rank, persistent_grid((N + 255) / 256, 8), 256, 0, st, w.tmp, ptr, N, B, w.cell_start, w.pts,
@@ -827,10 +828,9 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
                       w.pts, cap_list, w.sched + 2);
         GM_LAUNCH_CHECK();
         GM_LAUNCH_PDL(k_geo_cap, grid, threads, smem, st, ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts, mask_words, w.thr,
-                      cap_list, w.sched + 2, w.stats);
+                      cap_list, w.sched + 2, stats);
         GM_LAUNCH_CHECK();
     }
-    if (stats_out) GM_CUDA_TRY(cudaMemcpyAsync(stats_out, w.stats, 4 * sizeof(int), cudaMemcpyDeviceToDevice, st));
     return GM_OK;
 }
 

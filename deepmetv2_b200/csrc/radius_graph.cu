@@ -46,13 +46,16 @@ size_t ws_layout(int N, int B, char *base, Workspace *w) {
 }
 
 // ------------------------------------------------------------------------------------------
-__global__ void k_init(int *bbox, int *stats) {
+// bbox / stats reset and the cell histogram cleared in one launch (a memset node here would also break the
+// programmatic-dependent-launch chain of the kernels that follow)
+__global__ void __launch_bounds__(256) k_init(int *bbox, int *stats, int4 *__restrict__ cell_cnt4, int n4) {
     pdl_sync();
-    if (threadIdx.x == 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
         bbox[0] = 0x7fffffff; bbox[1] = (int)0x80000000;
         bbox[2] = 0x7fffffff; bbox[3] = (int)0x80000000;
         stats[0] = 0; stats[1] = 0; stats[2] = 0; stats[3] = 0;
     }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) cell_cnt4[i] = make_int4(0, 0, 0, 0);
 }
 
 __global__ void __launch_bounds__(256) k_bbox(const float *__restrict__ pos, int stride, int dim, int N, int *bbox) {
@@ -356,9 +359,10 @@ __global__ void __launch_bounds__(256) k_batch_to_ptr(const long long *__restric
 int run_common(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B, double r,
                int phi_wrap, const Workspace &w, cudaStream_t st) {
     const float rf = (float)r;
-    GM_LAUNCH_PDL(k_init, 1, 32, 0, st, w.bbox, w.stats);
+    const int n4 = B * (CMAX / 4);                            // cell_cnt is 256-byte aligned in both workspaces, CMAX % 4 == 0
+    GM_LAUNCH_PDL(k_init, persistent_grid((n4 + 255) / 256 > 0 ? (n4 + 255) / 256 : 1, 8), 256, 0, st, w.bbox, w.stats,
+                  reinterpret_cast<int4 *>(w.cell_cnt), n4);
     GM_LAUNCH_CHECK();
-    GM_CUDA_TRY(cudaMemsetAsync(w.cell_cnt, 0, (size_t)B * CMAX * sizeof(int), st));
     if (N == 0) return GM_OK;
     const int g = persistent_grid((N + 255) / 256, 8);
     GM_LAUNCH_PDL(k_bbox, g, 256, 0, st, pos, pos_stride, dim, N, w.bbox);
