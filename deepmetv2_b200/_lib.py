@@ -81,6 +81,7 @@ SIGNATURES = {
     "gm_radius_graph_count": (_i, [_vp, _i, _i, _vp, _i, _i, _d, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _vp]),
     "gm_radius_graph_fill": (_i, [_vp, _i, _i, _vp, _i, _i, _d, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _ll, _vp,
                                   _vp, _vp]),
+    "gm_radius_graph_static": (_i, [_vp, _i, _i, _vp, _i, _i, _d, _i, _i, _i, _i, _vp, _vp, _ll, _vp, _vp]),
     "gm_knn_graph_ws_bytes": (_sz, [_i, _i, _i]),
     "gm_knn_graph_count": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _i, _vp, _sz, _vp, _vp]),
     "gm_knn_graph_fill": (_i, [_i, _i, _i, _vp, _sz, _vp, _vp, _ll, _vp, _vp]),

@@ -11,6 +11,8 @@
 // max_num_neighbors cap keeps the LOWEST indices, exactly like the reference's sequential scan,
 // without any sort and independent of the (atomic, hence arbitrary) order inside a cell.
 #include "geo_layout.cuh"
+#include <cstdio>
+#include <mutex>
 
 namespace gm {
 namespace {
@@ -394,6 +396,34 @@ int bin_points(const float *pos, int pos_stride, int dim, const int *ptr, int N,
     return run_common(pos, pos_stride, dim, ptr, N, B, (double)r, phi_wrap, w, st);
 }
 
+// ------------------------------------------------------------------------------------------
+// Scratch of gm_radius_graph_static: lives in the library's image on every GPU that loads it (until exit), so the
+// entry point never allocates.  Shared by ALL calls: two calls that overlap on the GPU race on it.
+constexpr int STATIC_MAX_NODES = GM_STATIC_MAX_NODES, STATIC_MAX_EVENTS = GM_STATIC_MAX_EVENTS;
+constexpr size_t STATIC_SCRATCH_BYTES = 1600u * 1024u;       // >= ws_layout(STATIC_MAX_NODES, STATIC_MAX_EVENTS) = 1,573,888
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static std::mutex g_static_mu;
+static void *g_static_ptr[STATIC_MAX_DEVICES];               // device address of g_static_scratch, per device
+
+// In host code `g_static_scratch` is only a handle: the device address comes from cudaGetSymbolAddress, looked up once
+// per device with that device current.
+static int static_scratch(void **out) {
+    int dev = -1;
+    GM_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= STATIC_MAX_DEVICES) return GM_ERR_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void *p = nullptr;
+        GM_CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) return GM_ERR_CUDA;
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return GM_OK;
+}
+
 int exclusive_scan_inplace(int *data, int n, int *tile_totals, int *total_out, cudaStream_t st) {
     if (n <= 0) return GM_OK;
     int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
@@ -460,6 +490,55 @@ int gm_radius_graph_fill(const float *pos, int pos_stride, int dim, const int *p
     k_fill<<<g, threads, smem, st>>>(ptr, N, B, rf, r2, dim, max_num_neighbors, loop, phi_wrap, mask_words, w.bbox,
                                      w.cell_start, w.sorted, rowptr, col_out, col_capacity,
                                      (long long *)edge_index64_out, w.stats);
+    GM_LAUNCH_CHECK();
+    if (stats_out) GM_CUDA_TRY(cudaMemcpyAsync(stats_out, w.stats, 4 * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    return GM_OK;
+}
+
+// The two-call protocol above in ONE call that allocates nothing: the workspace is g_static_scratch.  Same kernels, same
+// launch shapes, same results as gm_radius_graph_count + gm_radius_graph_fill.  k_init clears what must start at zero
+// (bbox, counters, cell histogram), so the previous call's contents do not matter.
+int gm_radius_graph_static(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B, double r,
+                           int max_num_neighbors, int loop, int phi_wrap, int max_event_nodes, int *rowptr_out,
+                           int *col_out, long long col_capacity, int *stats_out, void *stream) {
+    if (N > STATIC_MAX_NODES || B > STATIC_MAX_EVENTS) {
+        fprintf(stderr, "gm_radius_graph_static: N=%d / B=%d beyond the static scratch (GM_STATIC_MAX_NODES=%d, "
+                        "GM_STATIC_MAX_EVENTS=%d); use gm_radius_graph_count/_fill with a caller workspace\n",
+                N, B, STATIC_MAX_NODES, STATIC_MAX_EVENTS);
+        return GM_ERR_CAPACITY;
+    }
+    void *ws = nullptr;
+    if (N >= 0 && B >= 0 && ws_layout(N, B, nullptr, nullptr) > STATIC_SCRATCH_BYTES) return GM_ERR_CAPACITY;
+    GM_TRY(static_scratch(&ws));
+    GM_TRY(check_args(pos, dim, ptr, N, B, r, max_num_neighbors, ws, STATIC_SCRATCH_BYTES));
+    if (!rowptr_out || (!col_out && col_capacity > 0) || col_capacity < 0 || max_event_nodes < 0)
+        return GM_ERR_INVALID_ARGUMENT;
+    cudaStream_t st = as_stream(stream);
+    Workspace w;
+    ws_layout(N, B, (char *)ws, &w);
+    GM_TRY(run_common(pos, pos_stride, dim, ptr, N, B, r, phi_wrap, w, st));
+    if (N == 0) {
+        GM_CUDA_TRY(cudaMemsetAsync(rowptr_out, 0, sizeof(int), st));
+        if (stats_out) GM_CUDA_TRY(cudaMemcpyAsync(stats_out, w.stats, 4 * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        return GM_OK;
+    }
+    const float rf = (float)r, r2 = (float)(r * r);
+    const int gd = persistent_grid(((long long)N * 32 + 255) / 256, 8);
+    k_degree<<<gd, 256, 0, st>>>(ptr, N, B, rf, r2, dim, max_num_neighbors, loop, phi_wrap, w.bbox, w.cell_start,
+                                 w.sorted, rowptr_out, w.stats);
+    GM_LAUNCH_CHECK();
+    GM_TRY(exclusive_scan_inplace(rowptr_out, N + 1, w.scan_tot, w.stats + 0, st));
+    const int mask_words = (max_event_nodes + 31) / 32 + 1;
+    int threads = 256;
+    while (threads > 32 && (size_t)(threads / 32) * mask_words * 4 > 200 * 1024) threads >>= 1;
+    const size_t smem = (size_t)(threads / 32) * mask_words * 4;
+    if (smem > 200 * 1024) return GM_ERR_UNSUPPORTED;
+    if (smem > 48 * 1024)
+        GM_CUDA_TRY(cudaFuncSetAttribute(k_fill, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int gf = persistent_grid(((long long)N * 32 + threads - 1) / threads, 2048 / threads);
+    k_fill<<<gf, threads, smem, st>>>(ptr, N, B, rf, r2, dim, max_num_neighbors, loop, phi_wrap, mask_words, w.bbox,
+                                      w.cell_start, w.sorted, rowptr_out, col_out, col_capacity, (long long *)nullptr,
+                                      w.stats);
     GM_LAUNCH_CHECK();
     if (stats_out) GM_CUDA_TRY(cudaMemcpyAsync(stats_out, w.stats, 4 * sizeof(int), cudaMemcpyDeviceToDevice, st));
     return GM_OK;

@@ -161,6 +161,23 @@ int gm_radius_graph_fill(const float *pos, int pos_stride, int dim, const int *p
                          int64_t *edge_index64_out /* [2, col_capacity] or NULL */,
                          int *stats_out, void *stream);
 
+/* gm_radius_graph_count + gm_radius_graph_fill in ONE call that allocates nothing. NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it). The workspace is a file-scope static __device__ array of
+ * 1,638,400 bytes inside the library (every GPU that loads the library holds it until exit), which bounds the call to
+ * N <= GM_STATIC_MAX_NODES and B <= GM_STATIC_MAX_EVENTS; larger sizes return GM_ERR_CAPACITY (and say so on
+ * stderr). No cudaMalloc / cudaFree / allocating routine is called; the caller passes every input and output.
+ * Results are bit-identical to the two-call protocol: rowptr_out [N+1], col_out [col_capacity] (edges beyond the
+ * capacity are dropped and GM_FLAG_EDGE_OVERFLOW is set in stats[3]; E is rowptr_out[N] / stats[0]).
+ * ALL calls on a device share the one array and it keeps the last call's contents (the call itself clears what must
+ * start at zero): calls that overlap on the GPU (different streams, concurrent threads) RACE — serialise them. */
+#define GM_STATIC_MAX_NODES 65536
+#define GM_STATIC_MAX_EVENTS 64
+int gm_radius_graph_static(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B,
+                           double r, int max_num_neighbors, int loop, int phi_wrap,
+                           int max_event_nodes, int *rowptr_out, int *col_out, long long col_capacity,
+                           int *stats_out, void *stream);
+
 /* Any int64 edge_index[2,E] (e.g. one not produced by this library) -> CSR by target.
  * Device counting sort, sources ascending per row (stable). Needs ws of gm_csr_ws_bytes. */
 size_t gm_csr_ws_bytes(int N, long long E);
