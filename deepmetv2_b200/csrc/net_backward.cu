@@ -110,6 +110,25 @@ struct Outer {
             acc[14] = fmaf(a.w, v.z, acc[14]); acc[15] = fmaf(a.w, v.w, acc[15]);
         }
     }
+    // one-barrier form of flush: every row group parks its block in stage[g][O][I] (GROUPS*O*I floats); after a barrier
+    // fold_staged sums the groups in the same order as flush (bit-identical)
+    __device__ __forceinline__ void stage(float *stage) const {
+        const int t = threadIdx.x;
+        if (t >= GROUPS * BLK) return;
+        const int g = t / BLK, b = t - g * BLK, bo = b / BI, bi = b - bo * BI;
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+            *reinterpret_cast<float4 *>(stage + g * (O * I) + (4 * bo + a) * I + 4 * bi) =
+                make_float4(acc[4 * a], acc[4 * a + 1], acc[4 * a + 2], acc[4 * a + 3]);
+    }
+    static __device__ __forceinline__ void fold_staged(const float *stage, float *__restrict__ dst) {
+        for (int i = threadIdx.x; i < O * I; i += NT) {
+            float s = 0.f;
+#pragma unroll
+            for (int g = 0; g < GROUPS; ++g) s += stage[g * (O * I) + i];
+            dst[i] = s;
+        }
+    }
     // fold the row groups in order, write the [O][I] CTA partial; scratch >= O*I floats of smem
     __device__ __forceinline__ void flush(float *scratch, float *__restrict__ dst) {
         const int t = threadIdx.x;
@@ -143,6 +162,17 @@ struct ColSum {
         const int g = t / NC, c = t - g * NC;
         const int r0 = g * ROWS_PER, r1 = min(rows, r0 + ROWS_PER);
         for (int r = r0; r < r1; ++r) acc += T[r * ld + c];
+    }
+    __device__ __forceinline__ void stage(float *stage) const {      // stage[g][NC]; see Outer::stage
+        if (threadIdx.x < GROUPS * NC) stage[threadIdx.x] = acc;
+    }
+    static __device__ __forceinline__ void fold_staged(const float *stage, float *__restrict__ dst, int ncols_out) {
+        if ((int)threadIdx.x < ncols_out) {
+            float s = 0.f;
+#pragma unroll
+            for (int g = 0; g < GROUPS; ++g) s += stage[g * NC + threadIdx.x];
+            dst[threadIdx.x] = s;
+        }
     }
     __device__ __forceinline__ void flush(float *scratch, float *__restrict__ dst, int ncols_out) {
         const int t = threadIdx.x;
@@ -285,12 +315,15 @@ k_head_bwd(const float *__restrict__ emb, const float *__restrict__ out, const f
         sgx.accumulate(tB, GLD, rows);
         __syncthreads();
     }
+    // accumulators parked in the dead tiles, one barrier, fixed-order folds
+    oW1.stage(tA); cs.stage(tB); sg.stage(tB + 128); sgx.stage(tB + 256);
+    __syncthreads();
     float *dst = gpart + (size_t)blockIdx.x * GP_STRIDE;
-    oW1.flush(scratch, dst);
-    cs.flush(scratch, dst + 512, 33);
+    oW1.fold_staged(tA, dst);
+    cs.fold_staged(tB, dst + 512, 33);
     float *bp = bo.part + (size_t)blockIdx.x * 64;
-    sg.flush(scratch, bp, H);
-    sgx.flush(scratch, bp + H, H);
+    sg.fold_staged(tB + 128, bp, H);
+    sgx.fold_staged(tB + 256, bp + H, H);
     if (last_cta_done(bo.counter)) bn_sums_finalize(bo, scratch);
 }
 
@@ -492,13 +525,17 @@ k_conv_bwd_node2(const float *__restrict__ x, const float *__restrict__ raw, BnB
         sgx.accumulate(tB, GLD, rows);
         __syncthreads();
     }
+    // all accumulators parked in the dead tiles (tA | tB | tC contiguous), one barrier, fixed-order folds
+    float *st1 = tA, *st2 = st1 + 4 * 1024, *stc = st2 + 4 * 1024;
+    o1.stage(st1); o2.stage(st2); cb.stage(stc); sg.stage(stc + 256); sgx.stage(stc + 512);
+    __syncthreads();
     float *dst = gpart + (size_t)blockIdx.x * GP_STRIDE;
-    o1.flush(tA, dst);
-    o2.flush(tA, dst + 1024);
-    cb.flush(tA, dst + 2048, H);
+    o1.fold_staged(st1, dst);
+    o2.fold_staged(st2, dst + 1024);
+    cb.fold_staged(stc, dst + 2048, H);
     float *bp = bo.part + (size_t)blockIdx.x * 64;
-    sg.flush(tA, bp, H);
-    sgx.flush(tA, bp + H, H);
+    sg.fold_staged(stc + 256, bp, H);
+    sgx.fold_staged(stc + 512, bp + H, H);
     if (last_cta_done(bo.counter)) bn_sums_finalize(bo, tA);
 }
 
@@ -518,145 +555,200 @@ struct EncBwdArgs {
     float *gpart;
 };
 
-__global__ void __launch_bounds__(NODE_TILE, GM_BWD_OCC_ENC) k_encode_bwd(EncBwdArgs a) {
+// 256 threads per 128-node tile.  Per tile, four barrier intervals:
+//   A  every thread: coalesced float4 loads of enc / G -> dz = BN'(G)·ELU'(enc) into tA; threads < 128: one node each,
+//      rebuild u = [LUT row | ELU(W_c x + b)] into tB (x_c and the three table indices stay in registers)
+//      [threads >= 112 meanwhile fold the PREVIOUS tile's d(table values) (tD) into the embedding-table accumulators]
+//   B  du = dz·W_enc as a register-blocked tile product (4 nodes x 4 inputs per thread), times ELU'(u) read back from
+//      tB; dW_enc += dzᵀu, db_enc += Σ dz
+//   B' tA <- [d cat-pre | d cont-pre] from the product's registers, tB <- [x_c | the node's 24 table values]
+//   C  dW_c, db_c, dW_k, db_k outer products / column sums; d(table values) = d cat-pre · W_k, (node, half) per thread -> tD
+constexpr int EB_THREADS = 256;
+constexpr int TD_LD = 28;                // d(table values) row: 24 floats + the node's packed table indices
+__global__ void __launch_bounds__(EB_THREADS, GM_BWD_OCC_ENC) k_encode_bwd(EncBwdArgs a) {
     extern __shared__ __align__(16) float smem[];
-    float *s_enc_w = smem;                       // 1024
-    float *s_cont_w = s_enc_w + H * H;           // 128  [16][8]
+    float *s_enc_w = smem;                       // 1024  [o][i]: K-major for du = dz·W
+    float *s_cont_w = s_enc_w + H * H;           // 128   [16][8]
     float *s_cont_b = s_cont_w + 128;            // 16
-    float *s_cat_w = s_cont_b + 16;              // 384  [16][24]
+    float *s_cat_w = s_cont_b + 16;              // 384   [16][24]: K-major for dv = dpk·W_k
     float *s_lut = s_cat_w + 384;                // 2688
-    float *s_tab = s_lut + LUT_ROWS * 16;        // 144  [18][8]
+    float *s_tab = s_lut + LUT_ROWS * 16;        // 144   [18][8]
     float *tA = s_tab + 144;                     // NODE_TILE*GLD
     float *tB = tA + NODE_TILE * GLD;            // NODE_TILE*GLD
-    float *scratch = tB + NODE_TILE * GLD;       // 1024
-    int *s_idx = reinterpret_cast<int *>(scratch + 1024);  // NODE_TILE
-    float *s_coef = reinterpret_cast<float *>(s_idx + NODE_TILE);   // 160
-    const int t = threadIdx.x;
-    for (int i = t; i < H * H; i += NODE_TILE) s_enc_w[i] = a.enc_w[i];
-    for (int i = t; i < 128; i += NODE_TILE) { int o = i >> 3, k = i & 7; s_cont_w[i] = k < a.CD ? a.cont_w[o * a.CD + k] : 0.f; }
+    float *tD = tB + NODE_TILE * GLD;            // NODE_TILE*TD_LD
+    float *scratch = tD + NODE_TILE * TD_LD;     // 1024
+    float *s_coef = scratch + 1024;              // 160
+    const int t = threadIdx.x, ng = t >> 3, og = t & 7;
+    for (int i = t; i < H * H; i += EB_THREADS) s_enc_w[i] = a.enc_w[i];
+    if (t < 128) { int o = t >> 3, k = t & 7; s_cont_w[t] = k < a.CD ? a.cont_w[o * a.CD + k] : 0.f; }
     if (t < 16) s_cont_b[t] = a.cont_b[t];
-    for (int i = t; i < 384; i += NODE_TILE) s_cat_w[i] = a.cat_w[i];
-    for (int i = t; i < LUT_ROWS * 16; i += NODE_TILE) s_lut[i] = a.lut[i];
-    for (int i = t; i < 144; i += NODE_TILE)
-        s_tab[i] = i < 24 ? a.e_chrg[i] : (i < 80 ? a.e_pdg[i - 24] : a.e_pv[i - 80]);
+    for (int i = t; i < 384; i += EB_THREADS) s_cat_w[i] = a.cat_w[i];
+    for (int i = t; i < LUT_ROWS * 16; i += EB_THREADS) s_lut[i] = a.lut[i];
+    if (t < 144) s_tab[t] = t < 24 ? a.e_chrg[t] : (t < 80 ? a.e_pdg[t - 24] : a.e_pv[t - 80]);
     pdl_sync();                                  // above: parameters and the forward LUT; the BatchNorm sums are the previous kernel's
     bn_bwd_coeffs(a.bn, s_coef);
     __syncthreads();
 
-    Outer<H, H> oA; oA.zero();
-    Outer<16, 8> oC; oC.zero();
-    Outer<16, 24> oK; oK.zero();
-    ColSum<H> cA; cA.zero();
-    ColSum<16> cC; cC.zero();
-    ColSum<16> cK; cK.zero();
-    float tab_acc[2] = {0.f, 0.f};
+    Outer<H, H, EB_THREADS> oA; oA.zero();
+    Outer<16, 8, EB_THREADS> oC; oC.zero();
+    Outer<16, 24, EB_THREADS> oK; oK.zero();
+    ColSum<H, EB_THREADS> cA; cA.zero();
+    ColSum<16, EB_THREADS> cC; cC.zero();
+    ColSum<16, EB_THREADS> cK; cK.zero();
+    float tab_acc = 0.f;
+    // embedding-table accumulator of this thread: row r of the stacked 18-row table, column k
+    const int tid = t - (EB_THREADS - 144);
+    const int tr = tid >> 3, tk = tid & 7;
+    const int tshift = tr < 3 ? 0 : (tr < 10 ? 8 : 16);
+    const int twant = tr < 3 ? tr : (tr < 10 ? tr - 3 : tr - 10);
+    const int tcol = tshift + tk;
+    int prev_rows = 0;
 
     const int tiles = (a.N + NODE_TILE - 1) / NODE_TILE;
     for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const int node0 = tile * NODE_TILE, rows = min(NODE_TILE, a.N - node0);
-        float xc[8], du[H], hact[16], ecat[16];
-        int ic = 0, ip = 0, iv = 0;
-        if (t < rows) {
-            const size_t n = node0 + t;
-            const size_t src = a.perm ? (size_t)a.perm[n] : n;
-            const float *row = a.x_cont + src * a.x_cont_stride;
+        // ---- A
+        {
+            const float4 *E4 = reinterpret_cast<const float4 *>(a.enc) + (size_t)node0 * (H / 4);
+            const float4 *G4 = reinterpret_cast<const float4 *>(a.G) + (size_t)node0 * (H / 4);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) xc[k] = k < a.CD ? row[k] : 0.f;
-            long long c0, c1, c2;
-            if (a.x_cat_i64) { const long long *cr = a.x_cat_i64 + src * 3; c0 = cr[0]; c1 = cr[1]; c2 = cr[2]; }
-            else { const float *cr = a.x_cat_f32 + src * a.x_cat_stride; c0 = (long long)cr[0]; c1 = (long long)cr[1]; c2 = (long long)cr[2]; }
-            long long lc = c1 + 1, lp = pdg_remap(c0), lv = c2;   // clamp exactly like the forward
-            ic = (int)(lc < 0 ? 0 : (lc > 2 ? 2 : lc));
-            ip = (int)(lp < 0 ? 0 : (lp > 6 ? 6 : lp));
-            iv = (int)(lv < 0 ? 0 : (lv > 7 ? 7 : lv));
-            const int combo = (ic * 7 + ip) * 8 + iv;
-            float u[H], dz[H], a0[H], h0[16];
+            for (int it = 0; it < NODE_TILE * (H / 4) / EB_THREADS; ++it) {
+                const int idx = it * EB_THREADS + t, r = idx >> 3, c4 = (idx & 7) * 4;
+                float4 dz = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < rows) {
+                    const float4 e = E4[idx], g = G4[idx];
+                    dz.x = bn_bwd_one(s_coef, c4 + 0, g.x, e.x) * elu_grad_from_out(e.x);
+                    dz.y = bn_bwd_one(s_coef, c4 + 1, g.y, e.y) * elu_grad_from_out(e.y);
+                    dz.z = bn_bwd_one(s_coef, c4 + 2, g.z, e.z) * elu_grad_from_out(e.z);
+                    dz.w = bn_bwd_one(s_coef, c4 + 3, g.w, e.w) * elu_grad_from_out(e.w);
+                }
+                *reinterpret_cast<float4 *>(tA + r * GLD + c4) = dz;
+            }
+        }
+        float xc[8];
+        int packed = 0;
+        if (t < NODE_TILE) {
+            float u[H];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) { ecat[k] = s_lut[combo * 16 + k]; u[k] = ecat[k]; }
-            dense_smem<8, 16>(s_cont_w, s_cont_b, xc, h0);
+            for (int k = 0; k < H; ++k) u[k] = 0.f;
 #pragma unroll
-            for (int k = 0; k < 16; ++k) { hact[k] = elu(h0[k]); u[16 + k] = hact[k]; }
-            load_row32(a.enc + n * H, a0);
-            load_row32(a.G + n * H, dz);
+            for (int k = 0; k < 8; ++k) xc[k] = 0.f;
+            if (t < rows) {
+                const size_t n = node0 + t;
+                const size_t src = a.perm ? (size_t)a.perm[n] : n;
+                const float *row = a.x_cont + src * a.x_cont_stride;
 #pragma unroll
-            for (int k = 0; k < H; ++k) dz[k] = bn_bwd_one(s_coef, k, dz[k], a0[k]) * elu_grad_from_out(a0[k]);
-            store_row<H>(tA + t * GLD, dz);
+                for (int k = 0; k < 8; ++k) xc[k] = k < a.CD ? row[k] : 0.f;
+                long long c0, c1, c2;
+                if (a.x_cat_i64) { const long long *cr = a.x_cat_i64 + src * 3; c0 = cr[0]; c1 = cr[1]; c2 = cr[2]; }
+                else { const float *cr = a.x_cat_f32 + src * a.x_cat_stride; c0 = (long long)cr[0]; c1 = (long long)cr[1]; c2 = (long long)cr[2]; }
+                const long long lc = c1 + 1, lp = pdg_remap(c0), lv = c2;   // clamp exactly like the forward
+                const int ic = (int)(lc < 0 ? 0 : (lc > 2 ? 2 : lc));
+                const int ip = (int)(lp < 0 ? 0 : (lp > 6 ? 6 : lp));
+                const int iv = (int)(lv < 0 ? 0 : (lv > 7 ? 7 : lv));
+                packed = ic | (ip << 8) | (iv << 16);
+                const int combo = (ic * 7 + ip) * 8 + iv;
+                float h0[16];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) u[k] = s_lut[combo * 16 + k];
+                dense_smem<8, 16>(s_cont_w, s_cont_b, xc, h0);
+#pragma unroll
+                for (int k = 0; k < 16; ++k) u[16 + k] = elu(h0[k]);
+            }
             store_row<H>(tB + t * GLD, u);
-            dense_t_smem<H, H>(s_enc_w, dz, du);
+        }
+        if (tid >= 0) {                          // the previous tile's table gradients (tD is not touched before interval C)
+#pragma unroll 4
+            for (int rr = 0; rr < prev_rows; ++rr)
+                if (((__float_as_int(tD[rr * TD_LD + 24]) >> tshift) & 0xff) == twant) tab_acc += tD[rr * TD_LD + tcol];
         }
         __syncthreads();
+        // ---- B
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+        tile_gemm<H, H, GLD>(tA, s_enc_w, ng, og, acc);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float4 uv = *reinterpret_cast<const float4 *>(tB + (ng + 32 * i) * GLD + 4 * og);
+            acc[i][0] *= elu_grad_from_out(uv.x); acc[i][1] *= elu_grad_from_out(uv.y);
+            acc[i][2] *= elu_grad_from_out(uv.z); acc[i][3] *= elu_grad_from_out(uv.w);
+        }
         oA.accumulate(tA, GLD, tB, GLD, rows);
         cA.accumulate(tA, GLD, rows);
         __syncthreads();
-        float dpk[16];
-        if (t < rows) {
-            float dh0[16];
+        // ---- B'
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                dh0[k] = du[16 + k] * elu_grad_from_out(hact[k]);
-                dpk[k] = du[k] * elu_grad_from_out(ecat[k]);
-            }
-            store_row<16>(tA + t * GLD, dh0);
-            store_row<8>(tB + t * GLD, xc);
-        }
-        __syncthreads();
-        oC.accumulate(tA, GLD, tB, GLD, rows);
-        cC.accumulate(tA, GLD, rows);
-        __syncthreads();
-        if (t < rows) {
-            float v[24];
+        for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<float4 *>(tA + (ng + 32 * i) * GLD + 4 * og) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        if (t < NODE_TILE) {
+            const int ic = packed & 0xff, ip = (packed >> 8) & 0xff, iv = (packed >> 16) & 0xff;
+            float v[H];
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                v[k] = s_tab[ic * 8 + k]; v[8 + k] = s_tab[24 + ip * 8 + k]; v[16 + k] = s_tab[80 + iv * 8 + k];
+                v[k] = xc[k];
+                v[8 + k] = s_tab[ic * 8 + k]; v[16 + k] = s_tab[24 + ip * 8 + k]; v[24 + k] = s_tab[80 + iv * 8 + k];
             }
-            store_row<16>(tA + t * GLD, dpk);
-            store_row<24>(tB + t * GLD, v);
+            store_row<H>(tB + t * GLD, v);
         }
         __syncthreads();
-        oK.accumulate(tA, GLD, tB, GLD, rows);
+        // ---- C: tA = [d cat-pre (16) | d cont-pre (16)], tB = [x_c (8) | table values (24)]
+        oC.accumulate(tA + 16, GLD, tB, GLD, rows);
+        cC.accumulate(tA + 16, GLD, rows);
+        oK.accumulate(tA, GLD, tB + 8, GLD, rows);
         cK.accumulate(tA, GLD, rows);
-        __syncthreads();
-        if (t < rows) {
-            float dv[24];
-            dense_t_smem<24, 16>(s_cat_w, dpk, dv);
-            store_row<24>(tB + t * GLD, dv);
-            s_idx[t] = ic | (ip << 8) | (iv << 16);
-        }
-        __syncthreads();
-        // embedding-table gradients: accumulator (row r of the stacked 18-row table, column k)
+        {
+            const int n = t >> 1, hf = t & 1;
+            float dv[12];
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            const int id = t + q * NODE_TILE;
-            if (id < 144) {
-                const int r = id >> 3, k = id & 7;
-                const int shift = r < 3 ? 0 : (r < 10 ? 8 : 16);
-                const int want = r < 3 ? r : (r < 10 ? r - 3 : r - 10);
-                const int colo = (r < 3 ? 0 : (r < 10 ? 8 : 16)) + k;
-                float acc = tab_acc[q];
-                for (int rr = 0; rr < rows; ++rr)
-                    if (((s_idx[rr] >> shift) & 0xff) == want) acc += tB[rr * GLD + colo];
-                tab_acc[q] = acc;
+            for (int j = 0; j < 12; ++j) dv[j] = 0.f;
+            const float *dp = tA + n * GLD;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const float d = dp[k];
+                const float4 *w4 = reinterpret_cast<const float4 *>(s_cat_w + k * 24 + 12 * hf);
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    const float4 w = w4[q];
+                    dv[4 * q + 0] = fmaf(d, w.x, dv[4 * q + 0]); dv[4 * q + 1] = fmaf(d, w.y, dv[4 * q + 1]);
+                    dv[4 * q + 2] = fmaf(d, w.z, dv[4 * q + 2]); dv[4 * q + 3] = fmaf(d, w.w, dv[4 * q + 3]);
+                }
             }
+            float4 *d4 = reinterpret_cast<float4 *>(tD + n * TD_LD + 12 * hf);
+#pragma unroll
+            for (int q = 0; q < 3; ++q) d4[q] = make_float4(dv[4 * q], dv[4 * q + 1], dv[4 * q + 2], dv[4 * q + 3]);
+            if (t < NODE_TILE) tD[t * TD_LD + 24] = __int_as_float(packed);
         }
+        prev_rows = rows;
         __syncthreads();
     }
-    float *dst = a.gpart + (size_t)blockIdx.x * GP_STRIDE;
-    oA.flush(scratch, dst);
-    cA.flush(scratch, dst + 1024, H);
-    oC.flush(scratch, dst + 1056);
-    cC.flush(scratch, dst + 1184, 16);
-    oK.flush(scratch, dst + 1200);
-    cK.flush(scratch, dst + 1584, 16);
-#pragma unroll
-    for (int q = 0; q < 2; ++q) {
-        const int id = t + q * NODE_TILE;
-        if (id < 144) dst[1600 + id] = tab_acc[q];
+    if (tid >= 0) {
+#pragma unroll 4
+        for (int rr = 0; rr < prev_rows; ++rr)
+            if (((__float_as_int(tD[rr * TD_LD + 24]) >> tshift) & 0xff) == twant) tab_acc += tD[rr * TD_LD + tcol];
     }
+    __syncthreads();
+    // every accumulator parked in the (now dead) tiles, one barrier, one fixed-order fold: tA | tB | tD are contiguous
+    static_assert(2 * NODE_TILE * GLD + NODE_TILE * TD_LD >= 4 * 1024 + 32 * 128 + 10 * 384 + 3 * 256, "staging pool");
+    float *st_oA = tA, *st_oC = st_oA + 4 * 1024, *st_oK = st_oC + 32 * 128, *st_cA = st_oK + 10 * 384,
+          *st_cC = st_cA + 256, *st_cK = st_cC + 256;
+    oA.stage(st_oA); oC.stage(st_oC); oK.stage(st_oK); cA.stage(st_cA); cC.stage(st_cC); cK.stage(st_cK);
+    __syncthreads();
+    float *dst = a.gpart + (size_t)blockIdx.x * GP_STRIDE;
+    oA.fold_staged(st_oA, dst);
+    cA.fold_staged(st_cA, dst + 1024, H);
+    oC.fold_staged(st_oC, dst + 1056);
+    cC.fold_staged(st_cC, dst + 1184, 16);
+    oK.fold_staged(st_oK, dst + 1200);
+    cK.fold_staged(st_cK, dst + 1584, 16);
+    if (tid >= 0) dst[1600 + tid] = tab_acc;
 }
 
 constexpr size_t CONV_BWD_SMEM = (size_t)(2 * H * H + 3 * NODE_TILE * GLD + 5 * H + 2 * H) * 4;
 constexpr size_t ENC_BWD_SMEM =
-    (size_t)(H * H + 128 + 16 + 384 + LUT_ROWS * 16 + 144 + 2 * NODE_TILE * GLD + 1024 + NODE_TILE + 5 * H) * 4;
+    (size_t)(H * H + 128 + 16 + 384 + LUT_ROWS * 16 + 144 + 2 * NODE_TILE * GLD + NODE_TILE * TD_LD + 1024 + 5 * H) * 4;
 
 }  // namespace
 
@@ -774,7 +866,7 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
         GM_CUDA_TRY(cudaFuncSetAttribute(k_encode_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ENC_BWD_SMEM));
         {
             TimedRegion tr(GM_TIMER_ENCODE_BWD, st);
-            GM_LAUNCH_PDL(k_encode_bwd, ngrid_enc, NODE_TILE, ENC_BWD_SMEM, st, ea);
+            GM_LAUNCH_PDL(k_encode_bwd, ngrid_enc, EB_THREADS, ENC_BWD_SMEM, st, ea);
             GM_LAUNCH_CHECK();
         }
         const int CD = p->continuous_dim;
