@@ -215,6 +215,7 @@ __device__ __forceinline__ TargetResult aggr_target(const float4 *s_pts, const f
     const uint32_t col = smem_u32(s_rows + lane);                          // this lane's channel of staged row 0
     auto lds = [](uint32_t a) { float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; };
     unsigned boff = 0xffffffffu;                                           // byte offset of the arg-max row
+    int bk = -1;                                                           // first group of 8 hits that holds the new maximum
     for (int k8 = 0; k8 < nh; k8 += 8) {
         const uint4 ra = *reinterpret_cast<const uint4 *>(list + k8);
         const uint4 rb = *reinterpret_cast<const uint4 *>(list + k8 + 4);
@@ -223,19 +224,32 @@ __device__ __forceinline__ TargetResult aggr_target(const float4 *s_pts, const f
         const float v4 = lds(col + rb.x), v5 = lds(col + rb.y);
         const float v6 = lds(col + rb.z), v7 = lds(col + rb.w);
         if (AGGR == GM_AGGR_MAX && ARG) {
-            if (v0 > ac) { ac = v0; boff = ra.x; }
-            if (v1 > ac) { ac = v1; boff = ra.y; }
-            if (v2 > ac) { ac = v2; boff = ra.z; }
-            if (v3 > ac) { ac = v3; boff = ra.w; }
-            if (v4 > ac) { ac = v4; boff = rb.x; }
-            if (v5 > ac) { ac = v5; boff = rb.y; }
-            if (v6 > ac) { ac = v6; boff = rb.z; }
-            if (v7 > ac) { ac = v7; boff = rb.w; }
+            // the arg-max is tracked per GROUP (3 instructions per 8 hits instead of per hit) and resolved to a row
+            // once per (target, chunk) below: strict > keeps the FIRST group that attains the maximum
+            const float m8 = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), fmaxf(fmaxf(v4, v5), fmaxf(v6, v7)));
+            if (m8 > ac) { ac = m8; bk = k8; }
         } else if (AGGR == GM_AGGR_MAX) {
             ac = fmaxf(fmaxf(fmaxf(ac, v0), fmaxf(v1, v2)), fmaxf(fmaxf(v3, v4), fmaxf(v5, fmaxf(v6, v7))));
         } else {
             ac += v0; ac += v1; ac += v2; ac += v3; ac += v4; ac += v5; ac += v6; ac += v7;
         }
+    }
+    if (AGGR == GM_AGGR_MAX && ARG && bk >= 0) {
+        // first hit of that group whose value IS the maximum (fmaxf returns one of its inputs), in list = row order
+        const uint4 ra = *reinterpret_cast<const uint4 *>(list + bk);
+        const uint4 rb = *reinterpret_cast<const uint4 *>(list + bk + 4);
+        const float v0 = lds(col + ra.x), v1 = lds(col + ra.y);
+        const float v2 = lds(col + ra.z), v3 = lds(col + ra.w);
+        const float v4 = lds(col + rb.x), v5 = lds(col + rb.y);
+        const float v6 = lds(col + rb.z);
+        boff = rb.w;
+        if (v6 == ac) boff = rb.z;
+        if (v5 == ac) boff = rb.y;
+        if (v4 == ac) boff = rb.x;
+        if (v3 == ac) boff = ra.w;
+        if (v2 == ac) boff = ra.z;
+        if (v1 == ac) boff = ra.y;
+        if (v0 == ac) boff = ra.x;
     }
     return TargetResult{ac, boff == 0xffffffffu ? -1 : (int)(boff >> 7), nh};
 }
