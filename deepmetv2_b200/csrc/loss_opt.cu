@@ -70,16 +70,19 @@ __device__ __forceinline__ float block_sum(float v, float *sm) {
     return r;  // valid in thread 0
 }
 
+// 1024 threads per event: at ~1.7k candidates per event the launch is one or two dependent load batches per thread
+// (32 CTAs of 256 threads took 7 batches)
+constexpr int MET_THREADS = 1024;
 // one CTA per event: fixed thread-strided order + fixed tree => deterministic MET
-__global__ void __launch_bounds__(RED_THREADS) k_met(const float *__restrict__ w, const float *__restrict__ pred,
+__global__ void __launch_bounds__(MET_THREADS) k_met(const float *__restrict__ w, const float *__restrict__ pred,
                                                      int pstride, const int *__restrict__ ptr,
                                                      float *__restrict__ met) {
     pdl_sync();
-    __shared__ float sm[RED_THREADS / 32];
+    __shared__ float sm[MET_THREADS / 32];
     const int e = blockIdx.x;
     const int lo = ptr[e], hi = ptr[e + 1];
     float sx = 0.f, sy = 0.f;
-    for (int n = lo + threadIdx.x; n < hi; n += RED_THREADS) {
+    for (int n = lo + threadIdx.x; n < hi; n += MET_THREADS) {
         const float wn = w[n];
         const float *row = pred + (size_t)n * pstride;
         sx = fmaf(wn, row[0], sx);
@@ -93,17 +96,17 @@ __global__ void __launch_bounds__(RED_THREADS) k_met(const float *__restrict__ w
 // MET + d loss / d w_n = ((METx+tx) px + (METy+ty) py) * grad_scale (1/B for loss_fn; 1 for the per-event SUM the
 // data-parallel step all-reduces before dividing by the GLOBAL event count) in one launch (training): the CTA of an event has everything d loss / d w needs once its own
 // MET is reduced; the second sweep over the event's rows hits L1/L2.  Same summation order as k_met.
-__global__ void __launch_bounds__(RED_THREADS) k_met_grad(const float *__restrict__ w, const float *__restrict__ pred,
+__global__ void __launch_bounds__(MET_THREADS) k_met_grad(const float *__restrict__ w, const float *__restrict__ pred,
                                                           int pstride, const int *__restrict__ ptr,
                                                           const float *__restrict__ truth, int tstride, float grad_scale,
                                                           float *__restrict__ met, float *__restrict__ gw) {
     pdl_sync();
-    __shared__ float sm[RED_THREADS / 32];
+    __shared__ float sm[MET_THREADS / 32];
     __shared__ float s_g[2];
     const int e = blockIdx.x;
     const int lo = ptr[e], hi = ptr[e + 1];
     float sx = 0.f, sy = 0.f;
-    for (int n = lo + threadIdx.x; n < hi; n += RED_THREADS) {
+    for (int n = lo + threadIdx.x; n < hi; n += MET_THREADS) {
         const float wn = w[n];
         const float *row = pred + (size_t)n * pstride;
         sx = fmaf(wn, row[0], sx);
@@ -118,7 +121,7 @@ __global__ void __launch_bounds__(RED_THREADS) k_met_grad(const float *__restric
     }
     __syncthreads();
     const float gx = s_g[0], gy = s_g[1];
-    for (int n = lo + threadIdx.x; n < hi; n += RED_THREADS) {
+    for (int n = lo + threadIdx.x; n < hi; n += MET_THREADS) {
         const float *row = pred + (size_t)n * pstride;
         gw[n] = fmaf(gx, row[0], gy * row[1]);
     }
@@ -342,9 +345,9 @@ int gm_met_loss_ex(const float *w, const float *pred, int pred_stride, const flo
     if (pred_stride < 2 || truth_stride < 2) return GM_ERR_INVALID_ARGUMENT;
     cudaStream_t st = as_stream(stream);
     if (grad_w_out && N > 0)
-        GM_LAUNCH_PDL(k_met_grad, B, RED_THREADS, 0, st, w, pred, pred_stride, ptr, truth, truth_stride, grad_scale, met_out, grad_w_out);
+        GM_LAUNCH_PDL(k_met_grad, B, MET_THREADS, 0, st, w, pred, pred_stride, ptr, truth, truth_stride, grad_scale, met_out, grad_w_out);
     else
-        GM_LAUNCH_PDL(k_met, B, RED_THREADS, 0, st, w, pred, pred_stride, ptr, met_out);
+        GM_LAUNCH_PDL(k_met, B, MET_THREADS, 0, st, w, pred, pred_stride, ptr, met_out);
     GM_LAUNCH_CHECK();
     GM_LAUNCH_PDL(k_loss, 1, RED_THREADS, 0, st, met_out, truth, truth_stride, B, loss_out);
     GM_LAUNCH_CHECK();

@@ -193,11 +193,13 @@ constexpr int MAX_SEGS = 4 + 3 * GM_MAX_CONV_DEPTH + 9;
 struct Segs { int n; Seg s[MAX_SEGS]; };
 
 // dst[r*dst_ld + c] = sum_b part[b][off + r*src_ld + c].  grid = (chunks of 32 outputs, segments);
-// thread (c = t%32, g = t/32): lanes read 32 consecutive outputs (coalesced), the 8 groups split the
-// CTA-partial axis (b = g, g+8, ...) and are folded in a fixed order => deterministic.
-__global__ void __launch_bounds__(256) k_reduce_partials(Segs segs) {
+// thread (c = t%32, g = t/32): lanes read 32 consecutive outputs (coalesced), the RP_GROUPS groups split the
+// CTA-partial axis (b = g, g+RP_GROUPS, ...) and are folded in a fixed order => deterministic.  32 groups: the launch is
+// bound by the latency of each thread's dependent batches of loads (444 partials / 8 groups = 14 batches of 4 before).
+constexpr int RP_GROUPS = 32;
+__global__ void __launch_bounds__(RP_GROUPS * 32) k_reduce_partials(Segs segs) {
     pdl_sync();
-    __shared__ float sm[8][32];
+    __shared__ float sm[RP_GROUPS][32];
     const Seg sg = segs.s[blockIdx.y];
     const int total = sg.rows * sg.cols;
     const int i = blockIdx.x * 32 + (threadIdx.x & 31);
@@ -208,15 +210,15 @@ __global__ void __launch_bounds__(256) k_reduce_partials(Segs segs) {
     if (i < total) {
         r = i / sg.cols; c = i - r * sg.cols;
         const float *p = sg.part + sg.off + r * sg.src_ld + c;
-#pragma unroll 4
-        for (int b = g; b < sg.nblk; b += 8) acc += p[(size_t)b * GP_STRIDE];
+#pragma unroll 8
+        for (int b = g; b < sg.nblk; b += RP_GROUPS) acc += p[(size_t)b * GP_STRIDE];
     }
     sm[g][threadIdx.x & 31] = acc;
     __syncthreads();
     if (g == 0 && i < total) {
         float t = 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) t += sm[k][threadIdx.x];
+        for (int k = 0; k < RP_GROUPS; ++k) t += sm[k][threadIdx.x];
         sg.dst[r * sg.dst_ld + c] = t;
     }
 }
@@ -885,7 +887,7 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
         for (int k = 0; k < segs.n; ++k) max_total = max(max_total, segs.s[k].rows * segs.s[k].cols);
         if (segs.n > 0) {
             dim3 grid((max_total + 31) / 32, segs.n);
-            GM_LAUNCH_PDL(k_reduce_partials, grid, 256, 0, st, segs);
+            GM_LAUNCH_PDL(k_reduce_partials, grid, RP_GROUPS * 32, 0, st, segs);
             GM_LAUNCH_CHECK();
         }
     }
