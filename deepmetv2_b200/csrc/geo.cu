@@ -40,50 +40,120 @@ constexpr int AG_LIST = AG_CH + 16;  // per-warp hit list (uint32 byte offsets o
 using AgStage = StageL<AG_CH, false>;
 
 // ------------------------------------------------------------------------------------------ build
-// meta, ticket counters, the workspace's copy of ptr and the "not capped" default of thr in ONE launch (was a kernel,
-// a memcpy node and two memset nodes: at DY/TT sizes the build is launch-latency bound)
-__global__ void __launch_bounds__(256) k_geo_init(GeoMeta *m, float r, float r2, int dim, int phi_wrap, int loop, int cap_eff,
-                                                  int N, int B, const int *__restrict__ ptr, int *__restrict__ ptr_copy,
-                                                  int *__restrict__ sched, int *__restrict__ thr, int *stats) {
+// Binning of ONE event per CTA (events of up to GEO_BIN_EVENT_MAX nodes): cell histogram in shared memory, scan,
+// counting-sort scatter, re-ranking inside the cells by original index (the internal order must be reproducible:
+// see k_cell_rank) and the cap pre-filter -- what k_cell_count / k_cell_scan / k_cell_fill / k_cell_rank do in four
+// launches with global atomics.  At DY/TT sizes the graph build is a chain of latency-bound launches; this is one.
+constexpr int BE_THREADS = 1024;
+constexpr int GEO_BIN_EVENT_MAX = 16384, GEO_BIN_EVENT_MIN_B = 128;
+__device__ __forceinline__ int cell_of(const CellGrid &g, const float *__restrict__ pos, int stride, int dim, size_t i,
+                                       float &a, float &b) {
+    a = pos[i * stride];
+    b = dim >= 2 ? pos[i * stride + 1] : 0.f;
+    return cell_coord(a, g.min0, g.inv0, g.g0) * g.g1 + cell_coord(b, g.min1, g.inv1, g.g1);
+}
+__global__ void __launch_bounds__(BE_THREADS) k_bin_event(const float *__restrict__ pos, int stride, int dim,
+                                                          const int *__restrict__ ptr, float r, int phi_wrap, int cap_eff,
+                                                          const int *__restrict__ bbox, int *__restrict__ cell_start,
+                                                          float4 *__restrict__ tmp, float4 *__restrict__ pts,
+                                                          int *__restrict__ perm, int *__restrict__ list,
+                                                          int *__restrict__ count) {
+    __shared__ int s_cnt[CMAX];          // histogram, then the scatter cursor
+    __shared__ int s_start[CMAX + 1];    // event-local exclusive starts
+    __shared__ int s_wtot[32];
     pdl_sync();
-    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
-    if (gtid == 0) {
-        *m = GeoMeta{r, r2, dim, phi_wrap, loop, cap_eff, N, B};
-        stats[0] = -1;                                   // E is never counted on this path
-        sched[0] = 0; sched[1] = 0; sched[2] = 0; sched[3] = 0;
+    const CellGrid g = make_grid(bbox, r, dim, phi_wrap);
+    const int e = blockIdx.x, t = threadIdx.x, lane = t & 31, wp = t >> 5;
+    const int lo = ptr[e], n = ptr[e + 1] - lo;
+    s_cnt[t] = 0;
+    __syncthreads();
+    for (int i = t; i < n; i += BE_THREADS) {
+        float a, b;
+        atomicAdd(&s_cnt[cell_of(g, pos, stride, dim, (size_t)(lo + i), a, b)], 1);
     }
-    for (int i = gtid; i <= B; i += gsize) ptr_copy[i] = ptr[i];
-    for (int i = gtid; i < N; i += gsize) thr[i] = 0x7f7f7f7f;      // "not capped"
+    __syncthreads();
+    {   // exclusive scan of the 1024 counts (thread = cell)
+        const int v = s_cnt[t];
+        int tot;
+        const int ex = warp_excl_scan_int(v, lane, tot);
+        if (lane == 31) s_wtot[wp] = tot;
+        __syncthreads();
+        if (wp == 0) {
+            int dummy;
+            const int wex = warp_excl_scan_int(s_wtot[lane], lane, dummy);
+            s_wtot[lane] = wex;
+        }
+        __syncthreads();
+        const int st = s_wtot[wp] + ex;
+        s_start[t] = st;
+        if (t == CMAX - 1) s_start[CMAX] = st + v;
+        cell_start[(size_t)e * (CMAX + 1) + t] = lo + st;
+        if (t == CMAX - 1) cell_start[(size_t)e * (CMAX + 1) + CMAX] = lo + st + v;
+        s_cnt[t] = 0;                                        // now the cursor
+    }
+    __syncthreads();
+    for (int i = t; i < n; i += BE_THREADS) {
+        float a, b;
+        const int c = cell_of(g, pos, stride, dim, (size_t)(lo + i), a, b);
+        const int k = atomicAdd(&s_cnt[c], 1);               // arbitrary order inside the cell: fixed by the ranking below
+        tmp[lo + s_start[c] + k] = make_float4(a, b, __int_as_float(i), __int_as_float(c));
+    }
+    __syncthreads();                                         // this CTA's global writes are visible to this CTA
+    for (int s0 = t & ~31; s0 < n; s0 += BE_THREADS) {       // warp-aligned: the ballot below
+        const int s = s0 + lane;
+        bool dense = false;
+        if (s < n) {
+            float4 p = __ldcg(&tmp[lo + s]);
+            const int idx = __float_as_int(p.z), cell = __float_as_int(p.w);
+            const int c0 = s_start[cell], c1 = s_start[cell + 1];
+            int rank = 0;
+            for (int k = c0; k < c1; ++k) rank += __float_as_int(__ldcg(&tmp[lo + k].z)) < idx;
+            p.w = __int_as_float(cell | (e << 10));
+            pts[lo + c0 + rank] = p;
+            perm[lo + c0 + rank] = lo + idx;
+            // population of the 3x3 neighbourhood (nbhd_runs with cpa = cpb = cp, on the shared starts)
+            const int ce = cell / g.g1, cp = cell - ce * g.g1;
+            int C = 0;
+#pragma unroll
+            for (int de = -1; de <= 1; ++de) {
+                const int ce2 = ce + de;
+                if (ce2 < 0 || ce2 >= g.g0) continue;
+                const int *row = s_start + ce2 * g.g1;
+                int l = cp - 1, h = cp + 1;
+                if (phi_wrap) {
+                    if (g.g1 >= 3 && 3 < g.g1) {
+                        if (l < 0) { C += row[g.g1] - row[g.g1 - 1]; l = 0; }
+                        else if (h >= g.g1) { C += row[1] - row[0]; h = g.g1 - 1; }
+                    } else { l = 0; h = g.g1 - 1; }
+                }
+                l = l < 0 ? 0 : l;
+                h = h >= g.g1 ? g.g1 - 1 : h;
+                C += row[h + 1] - row[l];
+            }
+            dense = C > cap_eff;
+        }
+        const unsigned mk = __ballot_sync(0xffffffffu, dense);
+        if (mk) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(count, __popc(mk));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (dense) list[base + __popc(mk & ((1u << lane) - 1u))] = lo + s;
+        }
+    }
 }
 
 // The counting-sort scatter (k_cell_fill) places the points of a cell in atomic (arbitrary) order.  Internal order
 // must be reproducible run to run (it fixes every summation order downstream), so each point is re-ranked inside its
 // cell by original index: thread per slot, O(cell population) compares against L1/L2-resident neighbours.
+// Same launch, cap pre-filter: only a target whose 3x3 neighbourhood holds more than `cap` points can be capped at
+// all -- a property of its CELL, hence of the slot (ranking permutes inside a cell).  Those slots (a few percent outside
+// jet cores) are appended to a list for the warp-per-target kernel below; the order of the list is arbitrary and
+// irrelevant (thr[s] depends on s alone).
 __global__ void __launch_bounds__(256) k_cell_rank(const float4 *__restrict__ tmp, const int *__restrict__ ptr, int N,
                                                    int B, const int *__restrict__ cell_start,
-                                                   float4 *__restrict__ pts, int *__restrict__ perm) {
-    pdl_sync();
-    for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < N; s += gridDim.x * blockDim.x) {
-        const int e = find_event(ptr, B, s);
-        float4 t = tmp[s];
-        const int idx = __float_as_int(t.z), cell = __float_as_int(t.w);
-        const int *cs = cell_start + (size_t)e * (CMAX + 1);
-        const int lo = __ldg(cs + cell), hi = __ldg(cs + cell + 1);
-        int rank = 0;
-        for (int k = lo; k < hi; ++k) rank += __float_as_int(tmp[k].z) < idx;
-        t.w = __int_as_float(cell | (e << 10));
-        pts[lo + rank] = t;
-        perm[lo + rank] = __ldg(ptr + e) + idx;
-    }
-}
-
-// Cap pre-filter, thread per node: only a target whose 3x3 neighbourhood holds more than `cap` points can be capped
-// at all.  Those (a few percent outside jet cores) are appended to a list for the warp-per-target kernel below; the
-// order of the list is arbitrary and irrelevant (thr[s] depends on s alone).
-__global__ void __launch_bounds__(256) k_geo_cap_scan(const int *__restrict__ ptr, int N, int B,
-                                                      const GeoMeta *__restrict__ meta, const int *__restrict__ bbox,
-                                                      const int *__restrict__ cell_start, const float4 *__restrict__ pts,
-                                                      int *__restrict__ list, int *__restrict__ count) {
+                                                   float4 *__restrict__ pts, int *__restrict__ perm,
+                                                   const GeoMeta *__restrict__ meta, const int *__restrict__ bbox,
+                                                   int *__restrict__ list, int *__restrict__ count) {
     pdl_sync();
     const GeoMeta m = *meta;
     const CellGrid g = make_grid(bbox, m.r, m.dim, m.phi_wrap);
@@ -92,11 +162,19 @@ __global__ void __launch_bounds__(256) k_geo_cap_scan(const int *__restrict__ pt
         const int s = s0 + lane;
         bool dense = false;
         if (s < N) {
-            const float pw = __ldg(&pts[s].w);
-            const int e = pts_event(pw), cell = pts_cell(pw);
+            const int e = find_event(ptr, B, s);
+            float4 t = tmp[s];
+            const int idx = __float_as_int(t.z), cell = __float_as_int(t.w);
+            const int *cs = cell_start + (size_t)e * (CMAX + 1);
+            const int lo = __ldg(cs + cell), hi = __ldg(cs + cell + 1);
+            int rank = 0;
+            for (int k = lo; k < hi; ++k) rank += __float_as_int(tmp[k].z) < idx;
+            t.w = __int_as_float(cell | (e << 10));
+            pts[lo + rank] = t;
+            perm[lo + rank] = __ldg(ptr + e) + idx;
             const int ce = cell / g.g1, cp = cell - ce * g.g1;
             int rlo[6], rhi[6];
-            const int nr = nbhd_runs(g, cell_start + (size_t)e * (CMAX + 1), ce, cp, cp, m.phi_wrap, rlo, rhi);
+            const int nr = nbhd_runs(g, cs, ce, cp, cp, m.phi_wrap, rlo, rhi);
             int C = 0;
             for (int q = 0; q < nr; ++q) C += rhi[q] - rlo[q];
             dense = C > m.cap_eff;
@@ -821,14 +899,13 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
     const float rf = (float)r, r2 = (float)(r * r);          // r*r in double, then fp32
     const int cap_eff = loop ? max_num_neighbors : max_num_neighbors + 1;
     int *stats = stats_out ? stats_out : w.stats;             // the kernels count straight into the caller's words
-    GM_TRY(bin_points(pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt, w.cell_start, w.tmp, stats, st));
-    GM_LAUNCH_PDL(k_geo_init, persistent_grid((N + 255) / 256, 4), 256, 0, st, w.meta, rf, r2, dim, phi_wrap, loop, cap_eff, N, B,
-                  ptr, w.ptr, w.sched, w.thr, stats);
-    GM_LAUNCH_CHECK();
+    const GeoInit gi{w.meta, GeoMeta{rf, r2, dim, phi_wrap, loop, cap_eff, N, B}, w.ptr, w.sched, w.thr};
+    // enough events of ordinary size to fill the GPU with one CTA each: k_bin_event (256 x 5k-candidate events: build
+    // 278 -> 259 us); otherwise the four grid-wide kernels of bin_points (32 events: 32 CTAs are slower, 76 -> 94 us)
+    const bool per_event = N > 0 && B >= GEO_BIN_EVENT_MIN_B && max_event_nodes > 0 && max_event_nodes <= GEO_BIN_EVENT_MAX;
+    GM_TRY(bin_points(pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt, w.cell_start, w.tmp, stats, st, &gi,
+                      per_event));
     if (N > 0) {
-        GM_LAUNCH_PDL(k_cell_rank, persistent_grid((N + 255) / 256, 8), 256, 0, st, w.tmp, ptr, N, B, w.cell_start, w.pts,
-                      node_perm_out);
-        GM_LAUNCH_CHECK();
         const int mask_words = (max_event_nodes + 31) / 32 + 1;
         int threads = 256;
         while (threads > 32 && (size_t)(threads / 32) * mask_words * 4 > 200 * 1024) threads >>= 1;
@@ -837,10 +914,14 @@ int gm_geo_build(const float *pos, int pos_stride, int dim, const int *ptr, int 
         if (smem > 48 * 1024)
             GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_cap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const int grid = persistent_grid(((long long)N * 32 + threads - 1) / threads, 2048 / threads);
-        int *cap_list = reinterpret_cast<int *>(w.tmp);          // tmp is dead once k_cell_rank has run
-        GM_LAUNCH_PDL(k_geo_cap_scan, persistent_grid((N + 255) / 256, 8), 256, 0, st, ptr, N, B, w.meta, w.bbox, w.cell_start,
-                      w.pts, cap_list, w.sched + 2);
+        if (per_event)
+            GM_LAUNCH_PDL(k_bin_event, B, BE_THREADS, 0, st, pos, pos_stride, dim, ptr, rf, phi_wrap, cap_eff, w.bbox,
+                          w.cell_start, w.tmp, w.pts, node_perm_out, w.cap_list, w.sched + 2);
+        else
+            GM_LAUNCH_PDL(k_cell_rank, persistent_grid((N + 255) / 256, 8), 256, 0, st, w.tmp, ptr, N, B, w.cell_start, w.pts,
+                          node_perm_out, w.meta, w.bbox, w.cap_list, w.sched + 2);
         GM_LAUNCH_CHECK();
+        int *cap_list = w.cap_list;
         GM_LAUNCH_PDL(k_geo_cap, grid, threads, smem, st, ptr, N, B, w.meta, w.bbox, w.cell_start, w.pts, mask_words, w.thr,
                       cap_list, w.sched + 2, stats);
         GM_LAUNCH_CHECK();

@@ -28,6 +28,7 @@ struct GeoWs {
     float4 *tmp;          // [N] points grouped by (event, cell), arbitrary order inside a cell
     float4 *pts;          // [N] (eta, phi, local original index bits, event << 10 | cell) in internal order
     int *thr;             // [N] internal order
+    int *cap_list;        // [N] slots whose 3x3 neighbourhood can exceed the cap (first sched[2] entries)
     int *stats;           // [4] E (-1: not counted), max degree seen in dense cells, #capped, flags
     int *sched;           // [4] ticket / finished-CTA counters of the dynamically scheduled (eval) forward kernel,
                           //     [2] = length of the cap-candidate list
@@ -59,13 +60,34 @@ inline size_t geo_ws_layout(int N, int B, char *base, GeoWs *w) {
     t.tmp = (float4 *)take(nodes * sizeof(float4));
     t.pts = (float4 *)take(nodes * sizeof(float4));
     t.thr = (int *)take(nodes * sizeof(int));
+    t.cap_list = (int *)take(nodes * sizeof(int));
     if (w) *w = t;
     return off;
 }
 
-// implemented in radius_graph.cu: bbox -> cell histogram -> per-event scan -> scatter of (eta, phi, idx, cell)
+// What gm_geo_build has to reset per build (meta, ticket counters, its copy of ptr, the "not capped" default of thr):
+// rides along in the first kernel of bin_points (one launch less on a latency-bound chain).  meta == nullptr: nothing.
+struct GeoInit {
+    GeoMeta *meta;
+    GeoMeta value;
+    int *ptr_copy, *sched, *thr;
+};
+__device__ __forceinline__ void geo_init_body(const GeoInit &gi, const int *__restrict__ ptr, int *stats) {
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+    if (gtid == 0) {
+        *gi.meta = gi.value;
+        stats[0] = -1;                                   // E is never counted on this path
+        gi.sched[0] = 0; gi.sched[1] = 0; gi.sched[2] = 0; gi.sched[3] = 0;
+    }
+    for (int i = gtid; i <= gi.value.B; i += gsize) gi.ptr_copy[i] = ptr[i];
+    for (int i = gtid; i < gi.value.N; i += gsize) gi.thr[i] = 0x7f7f7f7f;      // "not capped"
+}
+
+// implemented in radius_graph.cu: bbox -> cell histogram -> per-event scan -> scatter of (eta, phi, idx, cell);
+// prologue_only: reset + bbox only (the caller bins the cells itself)
 int bin_points(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B, float r, int phi_wrap,
-               int *bbox, int *cell_cnt, int *cell_start, float4 *sorted, int *stats, cudaStream_t st);
+               int *bbox, int *cell_cnt, int *cell_start, float4 *sorted, int *stats, cudaStream_t st,
+               const GeoInit *geo_init = nullptr, bool prologue_only = false);
 
 // implemented in geo.cu, used by net_forward.cu / net_backward.cu
 struct AggrTail;

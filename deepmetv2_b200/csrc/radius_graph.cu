@@ -50,13 +50,15 @@ size_t ws_layout(int N, int B, char *base, Workspace *w) {
 // ------------------------------------------------------------------------------------------
 // bbox / stats reset and the cell histogram cleared in one launch (a memset node here would also break the
 // programmatic-dependent-launch chain of the kernels that follow)
-__global__ void __launch_bounds__(256) k_init(int *bbox, int *stats, int4 *__restrict__ cell_cnt4, int n4) {
+__global__ void __launch_bounds__(256) k_init(int *bbox, int *stats, int4 *__restrict__ cell_cnt4, int n4, GeoInit gi,
+                                              const int *__restrict__ ptr) {
     pdl_sync();
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         bbox[0] = 0x7fffffff; bbox[1] = (int)0x80000000;
         bbox[2] = 0x7fffffff; bbox[3] = (int)0x80000000;
         stats[0] = 0; stats[1] = 0; stats[2] = 0; stats[3] = 0;
     }
+    if (gi.meta) geo_init_body(gi, ptr, stats);          // gm_geo_build's per-build reset rides along (thread 0 of CTA 0 again)
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) cell_cnt4[i] = make_int4(0, 0, 0, 0);
 }
 
@@ -359,16 +361,21 @@ __global__ void __launch_bounds__(256) k_batch_to_ptr(const long long *__restric
 }
 
 int run_common(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B, double r,
-               int phi_wrap, const Workspace &w, cudaStream_t st) {
+               int phi_wrap, const Workspace &w, cudaStream_t st, const GeoInit *geo_init = nullptr,
+               bool prologue_only = false) {
     const float rf = (float)r;
     const int n4 = B * (CMAX / 4);                            // cell_cnt is 256-byte aligned in both workspaces, CMAX % 4 == 0
-    GM_LAUNCH_PDL(k_init, persistent_grid((n4 + 255) / 256 > 0 ? (n4 + 255) / 256 : 1, 8), 256, 0, st, w.bbox, w.stats,
-                  reinterpret_cast<int4 *>(w.cell_cnt), n4);
+    GeoInit gi{};
+    if (geo_init) gi = *geo_init;
+    const int init_work = (n4 > N ? n4 : N) + 255;
+    GM_LAUNCH_PDL(k_init, persistent_grid(init_work / 256 > 0 ? init_work / 256 : 1, 8), 256, 0, st, w.bbox, w.stats,
+                  reinterpret_cast<int4 *>(w.cell_cnt), n4, gi, ptr);
     GM_LAUNCH_CHECK();
     if (N == 0) return GM_OK;
     const int g = persistent_grid((N + 255) / 256, 8);
     GM_LAUNCH_PDL(k_bbox, g, 256, 0, st, pos, pos_stride, dim, N, w.bbox);
     GM_LAUNCH_CHECK();
+    if (prologue_only) return GM_OK;                          // the caller bins the cells itself (geo: one CTA per event)
     GM_LAUNCH_PDL(k_cell_count, g, 256, 0, st, pos, pos_stride, dim, ptr, N, B, rf, phi_wrap, w.bbox, w.cell_cnt);
     GM_LAUNCH_CHECK();
     GM_LAUNCH_PDL(k_cell_scan, B, CMAX, 0, st, ptr, w.cell_cnt, w.cell_start);
@@ -391,9 +398,10 @@ int check_args(const float *pos, int dim, const int *ptr, int N, int B, double r
 }  // namespace
 
 int bin_points(const float *pos, int pos_stride, int dim, const int *ptr, int N, int B, float r, int phi_wrap,
-               int *bbox, int *cell_cnt, int *cell_start, float4 *sorted, int *stats, cudaStream_t st) {
+               int *bbox, int *cell_cnt, int *cell_start, float4 *sorted, int *stats, cudaStream_t st,
+               const GeoInit *geo_init, bool prologue_only) {
     Workspace w{bbox, cell_cnt, cell_start, sorted, nullptr, stats};
-    return run_common(pos, pos_stride, dim, ptr, N, B, (double)r, phi_wrap, w, st);
+    return run_common(pos, pos_stride, dim, ptr, N, B, (double)r, phi_wrap, w, st, geo_init, prologue_only);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -64,6 +64,21 @@ def test_implicit_graph_equals_explicit_edge_list_on_synthetic_events():
             _check_edge_set(etaphi, b.ptr, 0.4, loop, 255, phi_wrap=True)
 
 
+def test_implicit_graph_per_event_binning_path():
+    """>= 128 events of ordinary size take the one-CTA-per-event binning kernel (k_bin_event) instead of the four
+    grid-wide launches: same edge set, with empty / one-node events, duplicates, a binding cap and phi wrap."""
+    gen = torch.Generator().manual_seed(21)
+    sizes = [int(v) for v in torch.randint(30, 220, (150,), generator=gen)]
+    sizes[3], sizes[77], sizes[149] = 0, 1, 2
+    b = synth.make_batch(len(sizes), "dytt", seed=9, sizes=sizes)
+    _, _, etaphi = O.prepare_inputs(b.x)
+    etaphi[40:60] = etaphi[40:41]                                      # exact duplicates inside event 0
+    for loop in (True, False):
+        _check_edge_set(etaphi, b.ptr, 0.4, loop, 255)
+        g, _ = _check_edge_set(etaphi, b.ptr, 0.8, loop, 8, phi_wrap=True)
+        assert g.num_capped > 0
+
+
 def test_implicit_graph_cap_duplicates_and_dense_cells():
     gen = torch.Generator().manual_seed(11)
     # two dense blobs (degrees far above the cap), duplicates, and a sparse halo, in 3 events
