@@ -47,6 +47,13 @@ class GmParams(C.Structure):
                 ("continuous_dim", _i), ("conv_depth", _i)]
 
 
+class GmAdamW(C.Structure):
+    _fields_ = [("params", _vp), ("grads", _vp), ("exp_avg", _vp), ("exp_avg_sq", _vp), ("n", _i),
+                ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
+                ("weight_decay", C.c_float), ("step", _i), ("grad_scale", C.c_float),
+                ("err_flags_dev", _vp), ("graph_stats_dev", _vp), ("status_host", _vp)]
+
+
 class GmDrnConv(C.Structure):
     _fields_ = [("w1", _vp), ("b1", _vp), ("w2", _vp), ("b2", _vp), ("bn_weight", _vp), ("bn_bias", _vp),
                 ("bn_running_mean", _vp), ("bn_running_var", _vp), ("bn_num_batches_tracked", _vp)]
@@ -107,6 +114,8 @@ SIGNATURES = {
                                 _vp, _sz, _vp, _vp, _vp]),
     "gm_net_backward_geo": (_i, [C.POINTER(GmParams), C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _i, _i, _vp,
                                  _i, _i, _i, _vp, _sz, _vp, _sz, _vp, _vp, _vp]),
+    "gm_net_backward_geo_adamw": (_i, [C.POINTER(GmParams), C.POINTER(GmParams), _vp, _i, _vp, _vp, _i, _vp, _i, _i, _vp,
+                                       _i, _i, _i, _vp, _sz, _vp, _sz, _vp, _vp, C.POINTER(GmAdamW), _vp]),
     "gm_edgeconv_forward_geo": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _i, _vp, _sz, _vp, _vp, _vp]),
     "gm_met_loss": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "gm_segment_sum": (_i, [_vp, _vp, _i, _vp, _vp]),

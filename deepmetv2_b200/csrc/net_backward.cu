@@ -197,29 +197,62 @@ struct Segs { int n; Seg s[MAX_SEGS]; };
 // CTA-partial axis (b = g, g+RP_GROUPS, ...) and are folded in a fixed order => deterministic.  32 groups: the launch is
 // bound by the latency of each thread's dependent batches of loads (444 partials / 8 groups = 14 batches of 4 before).
 constexpr int RP_GROUPS = 32;
-__global__ void __launch_bounds__(RP_GROUPS * 32) k_reduce_partials(Segs segs) {
-    pdl_sync();
+// Optional tail: the LAST CTA to finish (ticket) applies AdamW to the flat parameter buffer the gradient tensors are views
+// of -- gm_adamw_step_ex's arithmetic, one launch less at the end of a single-GPU training step.  params == NULL: none.
+struct AdamTail {
+    float *params; const float *grads; float *m, *v;
+    int n;
+    float lr, b1, b2, eps, wd, bc1, bc2_sqrt, gscale;
+    StepStatus status;
+    int *ticket;
+};
+__global__ void __launch_bounds__(RP_GROUPS * 32) k_reduce_partials(Segs segs, AdamTail tail) {
+    if (tail.params) pdl_wait(); else pdl_sync();        // with the tail: no early trigger (what follows may read weights up front)
     __shared__ float sm[RP_GROUPS][32];
+    __shared__ int s_last;
     const Seg sg = segs.s[blockIdx.y];
     const int total = sg.rows * sg.cols;
     const int i = blockIdx.x * 32 + (threadIdx.x & 31);
-    if (!sg.dst || blockIdx.x * 32 >= total) return;
-    const int g = threadIdx.x >> 5;
-    float acc = 0.f;
-    int r = 0, c = 0;
-    if (i < total) {
-        r = i / sg.cols; c = i - r * sg.cols;
-        const float *p = sg.part + sg.off + r * sg.src_ld + c;
+    if (sg.dst && (int)blockIdx.x * 32 < total) {         // CTA-uniform
+        const int g = threadIdx.x >> 5;
+        float acc = 0.f;
+        int r = 0, c = 0;
+        if (i < total) {
+            r = i / sg.cols; c = i - r * sg.cols;
+            const float *p = sg.part + sg.off + r * sg.src_ld + c;
 #pragma unroll 8
-        for (int b = g; b < sg.nblk; b += RP_GROUPS) acc += p[(size_t)b * GP_STRIDE];
-    }
-    sm[g][threadIdx.x & 31] = acc;
-    __syncthreads();
-    if (g == 0 && i < total) {
-        float t = 0.f;
+            for (int b = g; b < sg.nblk; b += RP_GROUPS) acc += p[(size_t)b * GP_STRIDE];
+        }
+        sm[g][threadIdx.x & 31] = acc;
+        __syncthreads();
+        if (g == 0 && i < total) {
+            float t = 0.f;
 #pragma unroll
-        for (int k = 0; k < RP_GROUPS; ++k) t += sm[k][threadIdx.x];
-        sg.dst[r * sg.dst_ld + c] = t;
+            for (int k = 0; k < RP_GROUPS; ++k) t += sm[k][threadIdx.x];
+            sg.dst[r * sg.dst_ld + c] = t;
+        }
+    }
+    if (!tail.params) return;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int n_ctas = (int)(gridDim.x * gridDim.y);
+        const int last = atomicAdd(tail.ticket, 1) == n_ctas - 1;
+        if (last) *tail.ticket = 0;
+        s_last = last;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (threadIdx.x == 0) tail.status.publish();
+    for (int k = threadIdx.x; k < tail.n; k += RP_GROUPS * 32) {
+        const float gi = __ldcg(tail.grads + k) * tail.gscale;
+        float pi = tail.params[k] * (1.f - tail.lr * tail.wd);
+        const float mi = tail.b1 * tail.m[k] + (1.f - tail.b1) * gi;
+        const float vi = tail.b2 * tail.v[k] + (1.f - tail.b2) * gi * gi;
+        const float denom = sqrtf(vi) / tail.bc2_sqrt + tail.eps;
+        pi -= (tail.lr / tail.bc1) * (mi / denom);
+        tail.params[k] = pi; tail.m[k] = mi; tail.v[k] = vi;
     }
 }
 
@@ -775,7 +808,8 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
                              const int *col, const int *rowptr_t, const int *col_t, const int *use_transposed_flag,
                              const void *geo_ws, int B, int N, const int *node_perm, int training, int apply_sigmoid,
                              int aggr, const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
-                             const float *out, const float *grad_out, void *stream, const KnnLayers *kl = nullptr) {
+                             const float *out, const float *grad_out, void *stream, const KnnLayers *kl = nullptr,
+                             const GmAdamW *opt = nullptr) {
     GM_TRY(check_params(p));
     if (!grads || N < 0 || !fwd_ws || !bwd_ws) return GM_ERR_INVALID_ARGUMENT;
     if (aggr != GM_AGGR_MAX) return GM_ERR_UNSUPPORTED;
@@ -795,7 +829,9 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
     const int ngrid_enc = persistent_grid(tiles, GM_BWD_OCC_ENC);
     const int ngrid_conv = persistent_grid(tiles, GM_BWD_OCC_CONV);   // k_conv_bwd_node2 (tile products)
     const float inv_n = training ? 1.f / (float)N : 0.f;
-    GM_CUDA_TRY(cudaMemsetAsync(w.counters, 0, NUM_COUNTERS * sizeof(int), st));
+    // the tickets reset themselves; the memset (a node that breaks the dependent-launch chain) only guards a workspace
+    // used for the first time -- gm_net_backward_geo_adamw's contract makes the caller hand over zeroed tickets instead
+    if (!opt) GM_CUDA_TRY(cudaMemsetAsync(w.counters, 0, NUM_COUNTERS * sizeof(int), st));
 
     auto gpart = [&](int stage) { return w.gpart + (size_t)stage * MAX_BWD_CTAS * GP_STRIDE; };
     // BatchNorm index b: 0 = bn_all (raw = enc), l+1 = conv_bn[l] (raw = conv[l])
@@ -887,7 +923,16 @@ static int net_backward_impl(const GmParams *p, const GmParams *grads, const flo
         for (int k = 0; k < segs.n; ++k) max_total = max(max_total, segs.s[k].rows * segs.s[k].cols);
         if (segs.n > 0) {
             dim3 grid((max_total + 31) / 32, segs.n);
-            GM_LAUNCH_PDL(k_reduce_partials, grid, RP_GROUPS * 32, 0, st, segs);
+            AdamTail tail{};
+            if (opt) {
+                const double bc1 = 1.0 - pow((double)opt->beta1, (double)opt->step);
+                const double bc2 = 1.0 - pow((double)opt->beta2, (double)opt->step);
+                tail = AdamTail{opt->params, opt->grads, opt->exp_avg, opt->exp_avg_sq, opt->n, opt->lr, opt->beta1, opt->beta2,
+                                opt->eps, opt->weight_decay, (float)bc1, (float)sqrt(bc2), opt->grad_scale,
+                                StepStatus{opt->err_flags_dev, opt->graph_stats_dev, opt->status_host, opt->step},
+                                w.counters + NUM_COUNTERS - 1};
+            }
+            GM_LAUNCH_PDL(k_reduce_partials, grid, RP_GROUPS * 32, 0, st, segs, tail);
             GM_LAUNCH_CHECK();
         }
     }
@@ -931,6 +976,19 @@ int gm_net_backward_geo(const GmParams *p, const GmParams *grads, const float *x
     return net_backward_impl(p, grads, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, nullptr, nullptr,
                              nullptr, nullptr, nullptr, geo_ws, B, N, node_perm, training, apply_sigmoid, aggr, fwd_ws,
                              fwd_ws_bytes, bwd_ws, bwd_ws_bytes, out, grad_out, stream);
+}
+
+int gm_net_backward_geo_adamw(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
+                              const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride, const void *geo_ws, int N,
+                              int B, const int *node_perm, int training, int apply_sigmoid, int aggr, const void *fwd_ws,
+                              size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes, const float *out,
+                              const float *grad_out, const GmAdamW *opt, void *stream) {
+    if (!geo_ws || B < 1 || !node_perm || N < 1) return GM_ERR_INVALID_ARGUMENT;
+    if (!opt || opt->n < 1 || opt->step < 1 || !opt->params || !opt->grads || !opt->exp_avg || !opt->exp_avg_sq)
+        return GM_ERR_INVALID_ARGUMENT;
+    return net_backward_impl(p, grads, x_cont, x_cont_stride, x_cat_i64, x_cat_f32, x_cat_stride, nullptr, nullptr,
+                             nullptr, nullptr, nullptr, geo_ws, B, N, node_perm, training, apply_sigmoid, aggr, fwd_ws,
+                             fwd_ws_bytes, bwd_ws, bwd_ws_bytes, out, grad_out, stream, nullptr, opt);
 }
 
 }  // extern "C"

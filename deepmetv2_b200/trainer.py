@@ -26,12 +26,15 @@ Parameters stay the module's ``nn.Parameter``s (re-pointed at one flat fp32 buff
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
 from . import _lib
-from ._lib import AGGR, PRECISION, check, lib, ptr, stream
+from ._lib import AGGR, PRECISION, GmAdamW, check, lib, ptr, stream
 from .synth import EventBatch
+
+_FUSED_ADAMW = os.environ.get("GM_FUSED_ADAMW", "1") != "0"     # 0: separate gm_net_backward_geo + gm_adamw_step_ex launches
 
 
 class FusedAdamW(torch.optim.Optimizer):
@@ -255,6 +258,7 @@ class GraphMETTrainer:
             self.csr_ws = u8(l.gm_csr_ws_bytes(N, E))
         self.fwd_ws = u8(l.gm_net_ws_bytes(N, depth, 1))
         self.bwd_ws = u8(l.gm_net_bwd_ws_bytes(N, depth))
+        self.bwd_ws[:256].zero_()           # "last CTA" tickets: gm_net_backward_geo_adamw wants them zero on first use
         self.weights = torch.empty(N, dtype=torch.float32, device=dev)
         self.grad_w = torch.empty(N, dtype=torch.float32, device=dev)
         self.met = torch.empty(B, 2, dtype=torch.float32, device=dev)
@@ -363,6 +367,19 @@ class GraphMETTrainer:
             check(l.gm_met_loss_ex(ptr(self.weights), ptr(x), x.stride(0), ptr(y), y.stride(0), ptr(p), N, B,
                                    1.0 if dp else 1.0 / B, ptr(self.met), ptr(self.loss), ptr(self.grad_w), st),
                   "gm_met_loss")
+            if not dp and self.graph != "knn" and self._implicit() and _FUSED_ADAMW:
+                # single GPU: loss.backward() + optimizer.step() as ONE call, AdamW in the last kernel of the backward
+                self.step_count += 1
+                opt = GmAdamW(ptr(self.flat), ptr(self.flat_grad), ptr(self.exp_avg), ptr(self.exp_avg_sq),
+                              self.flat.numel(), float(self.lr), float(self.betas[0]), float(self.betas[1]),
+                              float(self.eps), float(self.weight_decay), self.step_count, 1.0, ptr(self.flags),
+                              ptr(self.stats), ptr(self._status))
+                check(l.gm_net_backward_geo_adamw(
+                    C.byref(self._P), C.byref(self._G), ptr(x), x.stride(0), None, x.data_ptr() + 32, x.stride(0),
+                    ptr(self.geo_ws), N, B, ptr(self.perm), 1, int(self.apply_sigmoid), AGGR[self.net.aggr],
+                    ptr(self.fwd_ws), self.fwd_ws.numel(), ptr(self.bwd_ws), self.bwd_ws.numel(), ptr(self.weights),
+                    ptr(self.grad_w), C.byref(opt), st), "gm_net_backward_geo_adamw")
+                return self.loss
             self._backward(x, N, B)
         else:                       # empty shard: nothing to differentiate, but the exchange below must still happen
             self.flush()

@@ -390,6 +390,28 @@ int gm_adamw_step_ex(float *params, const float *grads, float *exp_avg, float *e
                      float grad_scale, const float *grad_denominator_dev, const int *err_flags_dev,
                      const int *graph_stats_dev, int *status_host, void *stream);
 
+/* gm_net_backward_geo with the optimiser in its last kernel (single GPU; train.py:51-52 loss.backward() +
+ * optimizer.step() as ONE call): the gradient tensors of `grads` must be views that tile opt->grads (the flat
+ * gradient buffer, n floats) in the order of opt->params; the last CTA of the final reduction applies
+ * gm_adamw_step_ex's update (bit-identical to calling it afterwards) and publishes the status mirror.
+ * Contract that saves a memset node per step: the first 64 bytes of bwd_ws (the "last CTA" tickets) must be ZERO
+ * the first time a workspace is used; the kernels leave them at zero.  N >= 1. */
+typedef struct {
+    float *params; const float *grads; float *exp_avg, *exp_avg_sq;
+    int n;
+    float lr, beta1, beta2, eps, weight_decay;
+    int step;                       /* 1-based step count AFTER this update */
+    float grad_scale;
+    const int *err_flags_dev, *graph_stats_dev;   /* optional status mirror, see gm_adamw_step_ex */
+    int *status_host;
+} GmAdamW;
+int gm_net_backward_geo_adamw(const GmParams *p, const GmParams *grads, const float *x_cont, int x_cont_stride,
+                              const int64_t *x_cat_i64, const float *x_cat_f32, int x_cat_stride,
+                              const void *geo_ws, int N, int B, const int *node_perm,
+                              int training, int apply_sigmoid, int aggr,
+                              const void *fwd_ws, size_t fwd_ws_bytes, void *bwd_ws, size_t bwd_ws_bytes,
+                              const float *out, const float *grad_out, const GmAdamW *opt, void *stream);
+
 /* ---------------------------------------------------------------------------------
  * e. Event-sharded data parallelism: the ONE collective of the path -- the SUM all-reduce of the flat
  *    gradient (26.6 KB for GraphMETNetwork) -- fused with the optimiser in ONE kernel over NVLink peer memory
