@@ -20,8 +20,12 @@ namespace {
 #ifndef GEO_SC_THREADS
 #define GEO_SC_THREADS 128
 #endif
+// 128-row stages (115 KB per CTA: ONE CTA of 5 warps per SM).  Timed alone (own CUDA-event pair) the kernel is slower
+// than with 32-row stages and 5 CTAs per SM (c2 31 vs 27 us) -- but inside the dependent-launch chain of a step the lean
+// footprint leaves room for the next kernel's CTAs to be resident and through their prologue: the STEP is 3 % faster
+// (c2 0.456 -> 0.442 ms, c5 1.104 -> 1.076 ms; 32 / 48 / 64 / 96 / 192 / 256 rows and 3-4 stages measured).
 #ifndef GEO_SC_CH
-#define GEO_SC_CH 32
+#define GEO_SC_CH 128
 #endif
 constexpr int GEO_THREADS = GEO_SC_THREADS;     // backward kernel: 4 warps
 constexpr int GEO_WARPS = GEO_THREADS / 32;
@@ -607,7 +611,10 @@ k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, 
 // No distance test, no cap threshold, no transposed graph: arg == j already says the edge exists.  The four warp
 // accumulators are folded in warp order and rows are walked in staged (= internal node) order: bit-deterministic.
 constexpr int SC_CH = GEO_SC_CH;               // staged target rows per pipeline stage
-constexpr int SC_STAGES = 2;
+#ifndef GEO_SC_STAGES
+#define GEO_SC_STAGES 2
+#endif
+constexpr int SC_STAGES = GEO_SC_STAGES;
 constexpr size_t SC_STAGE_BYTES = (size_t)3 * SC_CH * 128;                   // [arg | G | raw][SC_CH][32] x 4 B
 
 // Warp-specialised like the forward kernel: a producer warp walks the items and segments and streams the three row
@@ -674,8 +681,8 @@ k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd 
                 voff[nr] = C;
                 const int nck = (C + SC_CH - 1) / SC_CH;
                 for (int k = 0; k < nck; ++k, ++gc) {
-                    const int st = gc & 1;
-                    mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u, 200);
+                    const int st = gc % SC_STAGES;
+                    mbar_wait(empty0 + 8u * st, ((gc / SC_STAGES) & 1u) ^ 1u, 200);
                     if (lane == 0) {
                         unsigned char *stage = gs + st * S2_STAGE_BYTES;
                         const uint32_t s_dst = smem_u32(stage), bar = full0 + 8u * st;
@@ -700,8 +707,8 @@ k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd 
                 }
             }
         }
-        const int st = gc & 1;                              // end-of-work descriptor (no copies)
-        mbar_wait(empty0 + 8u * st, ((gc >> 1) & 1u) ^ 1u);
+        const int st = gc % SC_STAGES;                      // end-of-work descriptor (no copies)
+        mbar_wait(empty0 + 8u * st, ((gc / SC_STAGES) & 1u) ^ 1u);
         if (lane == 0) {
             reinterpret_cast<ChunkDesc *>(gs + st * S2_STAGE_BYTES + SC_STAGE_BYTES)->flags = AG_END;
             mbar_arrive(full0 + 8u * st);
@@ -711,9 +718,9 @@ k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd 
         const float c_mean = s_coef[lane], c_inv = s_coef[H + lane], c_scale = s_coef[2 * H + lane];
         const float c_1 = s_coef[3 * H + lane], c_2 = s_coef[4 * H + lane];
         for (uint32_t gc = 0;; ++gc) {
-            const int st = gc & 1;
+            const int st = gc % SC_STAGES;
             const unsigned char *stage = gs + st * S2_STAGE_BYTES;
-            mbar_wait(full0 + 8u * st, (gc >> 1) & 1u);
+            mbar_wait(full0 + 8u * st, (gc / SC_STAGES) & 1u);
             const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + SC_STAGE_BYTES);
             const int flags = d->flags;
             if (flags & AG_END) break;
