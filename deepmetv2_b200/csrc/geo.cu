@@ -32,16 +32,24 @@ constexpr int GEO_WARPS = GEO_THREADS / 32;
 constexpr int AG_CONSUMERS = 8;      // forward kernel: 8 consumer warps (AG_TPW targets of the item each) ...
 constexpr int AG_THREADS = (AG_CONSUMERS + 1) * 32;   // ... + 1 producer warp (segments, descriptors, TMA)
 constexpr int AG_TPW = GEO_TPI / AG_CONSUMERS;
+// Two tunings of the forward aggregation kernel (geo_aggr.inc), picked per launch by the mean event size:
+//   ag_big   : 224-row stages x 2, compiled for 3 CTAs per SM (27 warps) -- 5k-candidate events: dense hit lists want warps
+//   ag_small : 320-row stages x 2, compiled for 2 CTAs per SM (112 registers) -- DY/TT-sized events: a segment's whole
+//              neighbourhood fits one chunk and the arg-max body no longer sits at its register cap
+// Measured on whole steps (timers off): c2 0.442 -> 0.435 ms with ag_small, c5 1.076 -> 1.088 ms (hence the switch).
 #ifndef GEO_AG_CH
 #define GEO_AG_CH 224
 #endif
 #ifndef GEO_AG_STAGES
 #define GEO_AG_STAGES 2
 #endif
-constexpr int AG_CH = GEO_AG_CH;     // staged neighbourhood rows per pipeline stage (224 x 2 stages x 3 CTAs fit one SM)
-constexpr int AGF_STAGES = GEO_AG_STAGES;   // ring depth of the forward kernel (how far the producer warp runs ahead)
-constexpr int AG_LIST = AG_CH + 16;  // per-warp hit list (uint32 byte offsets of staged rows), padded by 16 identity entries
-using AgStage = StageL<AG_CH, false>;
+#ifndef GEO_AG_MINB
+#define GEO_AG_MINB 3
+#endif
+#ifndef GEO_AG_SMALL_EVENT
+#define GEO_AG_SMALL_EVENT 3000   // mean nodes per event below which ag_small runs (training kernel)
+#endif
+
 
 // ------------------------------------------------------------------------------------------ build
 // Binning of ONE event per CTA (events of up to GEO_BIN_EVENT_MAX nodes): cell histogram in shared memory, scan,
@@ -271,335 +279,16 @@ __global__ void __launch_bounds__(256) k_geo_cap(const int *__restrict__ ptr, in
     }
 }
 
-constexpr size_t AG_OFF_PTS = AgStage::OFF_PTS, AG_OFF_TGT = AgStage::OFF_TGT, AG_OFF_THR = AgStage::OFF_THR;
-constexpr size_t AG_OFF_DESC = AgStage::OFF_DESC, AG_STAGE_BYTES = AgStage::BYTES;
-constexpr size_t AG_LISTS = AGF_STAGES * AG_STAGE_BYTES;                   // AG_CONSUMERS x AG_LIST x u32
-constexpr size_t AG_BAR = AG_LISTS + (size_t)AG_CONSUMERS * AG_LIST * 4;   // full[AG_STAGES], empty[AG_STAGES]
-constexpr size_t AG_TOTAL = AG_BAR + 16 * AGF_STAGES;
-static_assert(AG_STAGE_BYTES % 128 == 0 && AG_LISTS % 8 == 0 && (AG_LIST * 4) % 16 == 0 && AG_LISTS % 16 == 0 && AG_BAR % 8 == 0, "staging alignment");
-static_assert(AGF_STAGES * AG_STAGE_BYTES >= (size_t)(AG_THREADS / 8) * 3 * H * 4, "BatchNorm scratch aliases the stages");
-
-// One target against one staged chunk: hit list, then lane = channel walks the list 4 rows at a time out of shared
-// memory.  The caller must NOT unroll its target loop around this body: the consumer warps run decoupled, and four
-// copies (one per target slot) thrash the instruction cache (ncu: stall_no_instruction 0.2 -> 3.7 per issue); a
-// __noinline__ call, on the other hand, confines ptxas to the scratch registers and serialises the row loads.
-struct TargetResult {
-    float ac;
-    int brow, nh;
-};
-template <int AGGR, bool ARG>
-__device__ __forceinline__ TargetResult aggr_target(const float4 *s_pts, const float *s_rows, int rows, float px, float py,
-                                                 int th, int excl, float ac, float r2, int dim, int phi_wrap, int lane,
-                                                 unsigned *list) {
-    GeoMeta m;
-    m.r2 = r2; m.dim = dim; m.phi_wrap = phi_wrap;
-    const int nh = build_hit_list<AG_CH>(s_pts, rows, px, py, th, excl, m, lane, list);
-    const uint32_t col = smem_u32(s_rows + lane);                          // this lane's channel of staged row 0
-    auto lds = [](uint32_t a) { float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; };
-    unsigned boff = 0xffffffffu;                                           // byte offset of the arg-max row
-    int bk = -1;                                                           // first group of 8 hits that holds the new maximum
-    for (int k8 = 0; k8 < nh; k8 += 8) {
-        const uint4 ra = *reinterpret_cast<const uint4 *>(list + k8);
-        const uint4 rb = *reinterpret_cast<const uint4 *>(list + k8 + 4);
-        const float v0 = lds(col + ra.x), v1 = lds(col + ra.y);
-        const float v2 = lds(col + ra.z), v3 = lds(col + ra.w);
-        const float v4 = lds(col + rb.x), v5 = lds(col + rb.y);
-        const float v6 = lds(col + rb.z), v7 = lds(col + rb.w);
-        if (AGGR == GM_AGGR_MAX && ARG) {
-            // the arg-max is tracked per GROUP (3 instructions per 8 hits instead of per hit) and resolved to a row
-            // once per (target, chunk) below: strict > keeps the FIRST group that attains the maximum
-            const float m8 = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), fmaxf(fmaxf(v4, v5), fmaxf(v6, v7)));
-            if (m8 > ac) { ac = m8; bk = k8; }
-        } else if (AGGR == GM_AGGR_MAX) {
-            ac = fmaxf(fmaxf(fmaxf(ac, v0), fmaxf(v1, v2)), fmaxf(fmaxf(v3, v4), fmaxf(v5, fmaxf(v6, v7))));
-        } else {
-            ac += v0; ac += v1; ac += v2; ac += v3; ac += v4; ac += v5; ac += v6; ac += v7;
-        }
-    }
-    if (AGGR == GM_AGGR_MAX && ARG && bk >= 0) {
-        // first hit of that group whose value IS the maximum (fmaxf returns one of its inputs), in list = row order
-        const uint4 ra = *reinterpret_cast<const uint4 *>(list + bk);
-        const uint4 rb = *reinterpret_cast<const uint4 *>(list + bk + 4);
-        const float v0 = lds(col + ra.x), v1 = lds(col + ra.y);
-        const float v2 = lds(col + ra.z), v3 = lds(col + ra.w);
-        const float v4 = lds(col + rb.x), v5 = lds(col + rb.y);
-        const float v6 = lds(col + rb.z);
-        boff = rb.w;
-        if (v6 == ac) boff = rb.z;
-        if (v5 == ac) boff = rb.y;
-        if (v4 == ac) boff = rb.x;
-        if (v3 == ac) boff = ra.w;
-        if (v2 == ac) boff = ra.z;
-        if (v1 == ac) boff = ra.y;
-        if (v0 == ac) boff = ra.x;
-    }
-    return TargetResult{ac, boff == 0xffffffffu ? -1 : (int)(boff >> 7), nh};
-}
-
-// The same reduction with QUARTER-WARP rows (inference: no arg-max, no BatchNorm moments): 8 lanes read one staged row
-// as LDS.128, lane = 4 channels, the 4 lane groups take 4 consecutive list entries each, so one trip covers 16 hits
-// with 1 list load + 4 row loads + 8 three-input max instead of 16 row loads + 16 max.  Every lane group keeps its own
-// partial over the chunks of a segment; the groups are folded once per target (2 shuffles per channel).
-template <int AGGR>
-__device__ __forceinline__ float4 aggr_rows_q4(const float *s_rows, const unsigned *list, int nh, float4 ac, int lane) {
-    const uint32_t base = smem_u32(s_rows) + (uint32_t)((lane & 7) * 16);
-    const unsigned *mine = list + 4 * (lane >> 3);
-    auto lds4 = [](uint32_t a) {
-        float4 q;
-        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(q.x), "=f"(q.y), "=f"(q.z), "=f"(q.w) : "r"(a));
-        return q;
-    };
-    for (int k = 0; k < nh; k += 16) {
-        const uint4 o = *reinterpret_cast<const uint4 *>(mine + k);
-        const float4 r0 = lds4(base + o.x), r1 = lds4(base + o.y), r2 = lds4(base + o.z), r3 = lds4(base + o.w);
-        if (AGGR == GM_AGGR_MAX) {
-            ac.x = fmaxf(fmaxf(fmaxf(ac.x, r0.x), r1.x), fmaxf(r2.x, r3.x));
-            ac.y = fmaxf(fmaxf(fmaxf(ac.y, r0.y), r1.y), fmaxf(r2.y, r3.y));
-            ac.z = fmaxf(fmaxf(fmaxf(ac.z, r0.z), r1.z), fmaxf(r2.z, r3.z));
-            ac.w = fmaxf(fmaxf(fmaxf(ac.w, r0.w), r1.w), fmaxf(r2.w, r3.w));
-        } else {
-            ac.x += (r0.x + r1.x) + (r2.x + r3.x);
-            ac.y += (r0.y + r1.y) + (r2.y + r3.y);
-            ac.z += (r0.z + r1.z) + (r2.z + r3.z);
-            ac.w += (r0.w + r1.w) + (r2.w + r3.w);
-        }
-    }
-    return ac;
-}
-template <int AGGR>
-__device__ __forceinline__ float fold_groups(float v) {             // over the 4 lane groups (lanes l, l^8, l^16, l^24)
-    const float a = __shfl_xor_sync(0xffffffffu, v, 8);
-    v = AGGR == GM_AGGR_MAX ? fmaxf(v, a) : v + a;
-    const float b = __shfl_xor_sync(0xffffffffu, v, 16);
-    return AGGR == GM_AGGR_MAX ? fmaxf(v, b) : v + b;
-}
-
-// ------------------------------------------------------------------------------------------ forward: aggregate
-// out_i = P_i + max_{j in N(i)} Y_j (add / mean alike), warp-specialised.
-//   producer warp : walks the CTA's items, cuts them into segments, computes the neighbourhood runs and streams the
-//                   neighbourhood (points + Y rows) through a 2-stage ring with TMA bulk copies, AG_CH rows at a time;
-//                   every chunk carries its descriptor and the item's target points / cap thresholds, so consumers never
-//                   touch global memory until they write a finished row.  It runs ahead across segment and item
-//                   boundaries: the pipeline never drains while the CTA has work.
-//   consumer warps: a warp owns AG_TPW targets of the item and keeps their running max / arg-max in REGISTERS.  Per
-//                   (target, chunk): lanes test 32 candidate points at a time and compact the hits (ballot + popc) into
-//                   a per-warp list, then lane = channel walks the list 4 rows at a time out of shared memory.
-// full[s] (1 arrival + TMA bytes) / empty[s] (AG_CONSUMERS arrivals) mbarriers; no CTA-wide barrier in the main loop.
-// Items are scheduled statically (item = blockIdx + k * gridDim) when BatchNorm partials are produced, so the per-CTA
-// moments are bit-reproducible; without them (eval) the producer takes tickets from a self-resetting counter.
-#ifndef GEO_AG_MINB
-#define GEO_AG_MINB 3
-#endif
-template <int AGGR, bool ARG, bool Q4 = false>
-__global__ void __launch_bounds__(AG_THREADS, GEO_AG_MINB)
-k_geo_aggr(const float *__restrict__ Y, const float *__restrict__ P, GeoView v, int N, float *__restrict__ out,
-           int *__restrict__ arg, AggrTail tail) {
-    extern __shared__ __align__(128) unsigned char gs[];
-    const uint32_t full0 = smem_u32(gs + AG_BAR), empty0 = full0 + 8u * AGF_STAGES;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
-    const GeoMeta m = *v.meta;
-    const float IDENT = AGGR == GM_AGGR_MAX ? -INFINITY : 0.f;
-    const bool dynamic = tail.partials == nullptr;
-    if (tid == 0) {
-        for (int s = 0; s < AGF_STAGES; ++s) { mbar_init(full0 + 8u * s, 1); mbar_init(empty0 + 8u * s, AG_CONSUMERS); }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp < AGF_STAGES) reinterpret_cast<float *>(gs + warp * AG_STAGE_BYTES)[AG_CH * 32 + lane] = IDENT;
-    __syncthreads();
-    pdl_sync();                                          // Y, P, the tickets: the previous kernels' outputs
-
-    float cnt = 0.f, shift = 0.f, s1 = 0.f, s2 = 0.f;      // BatchNorm moments of this warp's outputs (lane = channel)
-    if (warp == AG_CONSUMERS) {
-        // ================================================================== producer
-        geo_produce<AgStage, false, AGF_STAGES>(gs, full0, empty0, v, m, Y, N, dynamic, lane);
-    } else if constexpr (Q4) {
-        // ================================================================== consumers, quarter-warp rows (inference)
-        // Per-slot state lives in REGISTERS, not in a dynamically indexed (= local-memory) array: lane u holds the
-        // point / cap threshold / degree of target slot u (fetched with one shuffle each), and the four running
-        // accumulators are four scalars selected by a warp-uniform branch.  After a (target, chunk) the four lane
-        // groups are folded and lane (g, c4) keeps channel 4 * c4 + g.
-        static_assert(AG_TPW == 4, "one scalar accumulator per target slot");
-        unsigned *list = reinterpret_cast<unsigned *>(gs + AG_LISTS) + warp * AG_LIST;
-        const int grp = lane >> 3, c4 = lane & 7, ch = 4 * c4 + grp;
-        float px_l = 0.f, py_l = 0.f, acc0 = IDENT, acc1 = IDENT, acc2 = IDENT, acc3 = IDENT;
-        int th_l = 0, excl_l = -1, deg_l = 0;
-        float qp0 = 0.f, qp1 = 0.f, qp2 = 0.f, qp3 = 0.f;
-        GeoMeta mm;
-        mm.r2 = m.r2; mm.dim = m.dim; mm.phi_wrap = m.phi_wrap;
-        for (uint32_t gc = 0;; ++gc) {
-            const int st = gc % AGF_STAGES;
-            const unsigned char *stage = gs + st * AG_STAGE_BYTES;
-            mbar_wait(full0 + 8u * st, (gc / AGF_STAGES) & 1u);
-            const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + AG_OFF_DESC);
-            const int flags = d->flags;
-            if (flags & AG_END) break;
-            const int a = d->a, b = d->b, rows = d->rows, n0 = d->n0;
-            const float *s_rows = reinterpret_cast<const float *>(stage);
-            const float4 *s_pts = reinterpret_cast<const float4 *>(stage + AG_OFF_PTS);
-            if (flags & AG_FIRST) {
-                acc0 = acc1 = acc2 = acc3 = IDENT;
-                deg_l = 0;
-                qp0 = (a + warp < b) ? __ldg(P + (size_t)(n0 + a + warp) * H + ch) : 0.f;      // in flight for the whole segment
-                qp1 = (a + warp + AG_CONSUMERS < b) ? __ldg(P + (size_t)(n0 + a + warp + AG_CONSUMERS) * H + ch) : 0.f;
-                qp2 = (a + warp + 2 * AG_CONSUMERS < b) ? __ldg(P + (size_t)(n0 + a + warp + 2 * AG_CONSUMERS) * H + ch) : 0.f;
-                qp3 = (a + warp + 3 * AG_CONSUMERS < b) ? __ldg(P + (size_t)(n0 + a + warp + 3 * AG_CONSUMERS) * H + ch) : 0.f;
-                const int t = a + warp + lane * AG_CONSUMERS;                   // lanes 0..3: slot = lane
-                if (lane < AG_TPW && t < b) {
-                    const float4 pt = reinterpret_cast<const float4 *>(stage + AG_OFF_TGT)[t];
-                    px_l = pt.x; py_l = pt.y;
-                    th_l = reinterpret_cast<const int *>(stage + AG_OFF_THR)[t];
-                    excl_l = m.loop ? -1 : __float_as_int(pt.z);
-                }
-            }
-#pragma unroll 1
-            for (int u = 0; u < AG_TPW; ++u) {
-                if (a + warp + u * AG_CONSUMERS >= b) break;                    // warp-uniform
-                const float px = __shfl_sync(0xffffffffu, px_l, u), py = __shfl_sync(0xffffffffu, py_l, u);
-                const int th = __shfl_sync(0xffffffffu, th_l, u), excl = __shfl_sync(0xffffffffu, excl_l, u);
-                const int nh = build_hit_list<AG_CH>(s_pts, rows, px, py, th, excl, mm, lane, list);
-                if (lane == u) deg_l += nh;
-                if (nh > 0) {
-                    float4 v4 = aggr_rows_q4<AGGR>(s_rows, list, nh, make_float4(IDENT, IDENT, IDENT, IDENT), lane);
-                    v4.x = fold_groups<AGGR>(v4.x); v4.y = fold_groups<AGGR>(v4.y);
-                    v4.z = fold_groups<AGGR>(v4.z); v4.w = fold_groups<AGGR>(v4.w);
-                    const float mine = grp == 0 ? v4.x : grp == 1 ? v4.y : grp == 2 ? v4.z : v4.w;
-                    if (AGGR == GM_AGGR_MAX) {
-                        if (u == 0) acc0 = fmaxf(acc0, mine); else if (u == 1) acc1 = fmaxf(acc1, mine);
-                        else if (u == 2) acc2 = fmaxf(acc2, mine); else acc3 = fmaxf(acc3, mine);
-                    } else {
-                        if (u == 0) acc0 += mine; else if (u == 1) acc1 += mine;
-                        else if (u == 2) acc2 += mine; else acc3 += mine;
-                    }
-                }
-                __syncwarp();                                   // the hit list is reused by the next target
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(empty0 + 8u * st);       // this warp is done with the stage
-            if (flags & AG_LAST) {
-#pragma unroll
-                for (int u = 0; u < AG_TPW; ++u) {
-                    const int t = a + warp + u * AG_CONSUMERS;
-                    const int dg = __shfl_sync(0xffffffffu, deg_l, u);
-                    if (t >= b) continue;
-                    const float acc = u == 0 ? acc0 : u == 1 ? acc1 : u == 2 ? acc2 : acc3;
-                    const size_t node = (size_t)(n0 + t);
-                    const float p = u == 0 ? qp0 : u == 1 ? qp1 : u == 2 ? qp2 : qp3;
-                    float o;
-                    if (dg == 0) o = 0.f;                                      // PyG: empty rows aggregate to 0
-                    else if (AGGR == GM_AGGR_MAX) o = p + acc;
-                    else if (AGGR == GM_AGGR_ADD) o = fmaf((float)dg, p, acc);
-                    else o = fmaf(acc, 1.f / (float)dg, p);
-                    out[node * H + ch] = o;
-                }
-            }
-        }
-    } else {
-        // ================================================================== consumers (lane = channel; training: arg-max)
-        // Per-slot state in registers (see the quarter-warp variant): lane u holds slot u's point / threshold / degree,
-        // the running max and arg-max of the four slots are eight scalars picked by a warp-uniform branch.
-        static_assert(AG_TPW == 4, "one scalar accumulator per target slot");
-        unsigned *list = reinterpret_cast<unsigned *>(gs + AG_LISTS) + warp * AG_LIST;
-        float px_l = 0.f, py_l = 0.f, acc0 = IDENT, acc1 = IDENT, acc2 = IDENT, acc3 = IDENT;
-        int th_l = 0, excl_l = -1, deg_l = 0, barg0 = -1, barg1 = -1, barg2 = -1, barg3 = -1;
-        for (uint32_t gc = 0;; ++gc) {
-            const int st = gc % AGF_STAGES;
-            const unsigned char *stage = gs + st * AG_STAGE_BYTES;
-            mbar_wait(full0 + 8u * st, (gc / AGF_STAGES) & 1u);
-            const ChunkDesc *d = reinterpret_cast<const ChunkDesc *>(stage + AG_OFF_DESC);
-            const int flags = d->flags;
-            if (flags & AG_END) break;
-            const int a = d->a, b = d->b, rows = d->rows, n0 = d->n0;
-            const float *s_rows = reinterpret_cast<const float *>(stage);
-            const float4 *s_pts = reinterpret_cast<const float4 *>(stage + AG_OFF_PTS);
-            if (flags & AG_FIRST) {
-                acc0 = acc1 = acc2 = acc3 = IDENT;
-                barg0 = barg1 = barg2 = barg3 = -1;
-                deg_l = 0;
-                const int t = a + warp + lane * AG_CONSUMERS;                   // lanes 0..3: slot = lane
-                if (lane < AG_TPW && t < b) {
-                    const float4 pt = reinterpret_cast<const float4 *>(stage + AG_OFF_TGT)[t];
-                    px_l = pt.x; py_l = pt.y;
-                    th_l = reinterpret_cast<const int *>(stage + AG_OFF_THR)[t];
-                    excl_l = m.loop ? -1 : __float_as_int(pt.z);
-                }
-            }
-#pragma unroll 1                                                                // one copy of the body: see aggr_target
-            for (int u = 0; u < AG_TPW; ++u) {
-                if (a + warp + u * AG_CONSUMERS >= b) break;                    // warp-uniform
-                const float px = __shfl_sync(0xffffffffu, px_l, u), py = __shfl_sync(0xffffffffu, py_l, u);
-                const int th = __shfl_sync(0xffffffffu, th_l, u), excl = __shfl_sync(0xffffffffu, excl_l, u);
-                const float ac = u == 0 ? acc0 : u == 1 ? acc1 : u == 2 ? acc2 : acc3;
-                const TargetResult tr = aggr_target<AGGR, ARG>(s_pts, s_rows, rows, px, py, th, excl, ac,
-                                                               m.r2, m.dim, m.phi_wrap, lane, list);
-                if (lane == u) deg_l += tr.nh;
-                const int brow = tr.brow;
-                const int bnode = (ARG && brow >= 0) ? node_of_row(d, brow) : -1;
-                if (u == 0) { acc0 = tr.ac; if (ARG && brow >= 0) barg0 = bnode; }
-                else if (u == 1) { acc1 = tr.ac; if (ARG && brow >= 0) barg1 = bnode; }
-                else if (u == 2) { acc2 = tr.ac; if (ARG && brow >= 0) barg2 = bnode; }
-                else { acc3 = tr.ac; if (ARG && brow >= 0) barg3 = bnode; }
-                __syncwarp();                                   // the hit list is reused by the next target
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(empty0 + 8u * st);       // this warp is done with the stage
-            if (flags & AG_LAST) {
-#pragma unroll
-                for (int u = 0; u < AG_TPW; ++u) {
-                    const int t = a + warp + u * AG_CONSUMERS;
-                    const int dg = __shfl_sync(0xffffffffu, deg_l, u);
-                    if (t >= b) continue;
-                    const float acc = u == 0 ? acc0 : u == 1 ? acc1 : u == 2 ? acc2 : acc3;
-                    const int barg = u == 0 ? barg0 : u == 1 ? barg1 : u == 2 ? barg2 : barg3;
-                    const size_t node = (size_t)(n0 + t);
-                    const float p = __ldg(P + node * H + lane);
-                    float o;
-                    if (dg == 0) o = 0.f;                                      // PyG: empty rows aggregate to 0
-                    else if (AGGR == GM_AGGR_MAX) o = p + acc;
-                    else if (AGGR == GM_AGGR_ADD) o = fmaf((float)dg, p, acc);
-                    else o = fmaf(acc, 1.f / (float)dg, p);
-                    out[node * H + lane] = o;
-                    if (ARG) arg[node * H + lane] = barg;
-                    if (tail.partials) {
-                        if (cnt == 0.f) shift = o;
-                        cnt += 1.f;
-                        const float dd = o - shift;
-                        s1 += dd;
-                        s2 = fmaf(dd, dd, s2);
-                    }
-                }
-            }
-        }
-    }
-    if (dynamic) {                                              // last CTA out re-arms the ticket counter
-        __syncthreads();
-        if (tid == 0) {
-            __threadfence();
-            if (atomicAdd(v.sched + 1, 1) == (int)gridDim.x - 1) { v.sched[0] = 0; v.sched[1] = 0; __threadfence(); }
-        }
-    }
-    if (tail.partials) {
-        float(*s_red)[3][H] = reinterpret_cast<float(*)[3][H]>(gs);      // aliases the (now idle) pipeline stages
-        __syncthreads();
-        if (warp < AG_CONSUMERS) {
-            const float rn = cnt > 0.f ? 1.f / cnt : 0.f;
-            s_red[warp][0][lane] = cnt;
-            s_red[warp][1][lane] = fmaf(s1, rn, shift);
-            s_red[warp][2][lane] = fmaxf(s2 - s1 * s1 * rn, 0.f);
-        }
-        __syncthreads();
-        if (warp == 0) {
-            Moments tot{0.f, 0.f, 0.f};
-#pragma unroll
-            for (int k = 0; k < AG_CONSUMERS; ++k)
-                tot = moments_combine(tot, Moments{s_red[k][0][lane], s_red[k][1][lane], s_red[k][2][lane]});
-            float *dst = tail.partials + (size_t)blockIdx.x * MOM_STRIDE;
-            dst[lane] = tot.n; dst[H + lane] = tot.mean; dst[2 * H + lane] = tot.m2;
-        }
-        if (last_cta_done(tail.counter))
-            bn_finalize_cta(tail.partials, gridDim.x, tail.bn, tail.momentum, tail.eps, tail.stat, s_red);
-    }
-}
+namespace ag_big {
+#include "geo_aggr.inc"
+}  // namespace ag_big
+#undef GEO_AG_CH
+#undef GEO_AG_MINB
+#define GEO_AG_CH 320
+#define GEO_AG_MINB 2
+namespace ag_small {
+#include "geo_aggr.inc"
+}  // namespace ag_small
 
 // ------------------------------------------------------------------------------------------ backward: route to sources
 // S[j][c] = sum over targets i with arg(i,c) == j of d conv_i[c]   (max-aggregation sends each (target, channel)
@@ -810,33 +499,36 @@ __global__ void __launch_bounds__(RM_THREADS) k_row_moments(const float *__restr
 }
 
 // ------------------------------------------------------------------------------------------ launchers
+// One launch of k_geo_aggr<AGGR, ARG, Q4> of tuning namespace NS (a macro: the two namespaces hold same-named templates)
+#define GEO_AGGR_LAUNCH(NS, ARG, Q4, SLOT)                                                                              \
+    do {                                                                                                                \
+        if (!occ[SLOT]) {                                                                                               \
+            GM_CUDA_TRY(cudaFuncSetAttribute(NS::k_geo_aggr<AGGR, ARG, Q4>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                             (int)NS::AG_TOTAL));                                                       \
+            occ[SLOT] = resident_ctas(NS::k_geo_aggr<AGGR, ARG, Q4>, AG_THREADS, NS::AG_TOTAL, 3);                      \
+        }                                                                                                               \
+        grid = persistent_grid(n_items, min(occ[SLOT], MAX_PARTIAL_CTAS / 148));                                        \
+        split = tail.partials && (long long)n_items >= 8LL * grid;                                                      \
+        const AggrTail in_kernel = split ? AggrTail{} : tail;                                                           \
+        GM_LAUNCH_PDL((NS::k_geo_aggr<AGGR, ARG, Q4>), grid, AG_THREADS, NS::AG_TOTAL, st, Y, P, v, N, out, arg, in_kernel); \
+    } while (0)
+
 template <int AGGR>
-int launch_geo_aggr(const float *Y, const float *P, const GeoView &v, int N, float *out, int *arg,
+int launch_geo_aggr(const float *Y, const float *P, const GeoView &v, int N, int B, float *out, int *arg,
                     const AggrTail &tail, cudaStream_t st) {
-    static int occ[3] = {0, 0, 0};
+    static int occ[4] = {0, 0, 0, 0};
     const bool q4 = !arg && !tail.partials;              // inference: quarter-warp rows
-    const int which = arg ? 1 : (q4 ? 2 : 0);
-    if (!occ[which]) {
-        if (arg) {
-            GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_aggr<AGGR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AG_TOTAL));
-            occ[1] = resident_ctas(k_geo_aggr<AGGR, true>, AG_THREADS, AG_TOTAL, 3);
-        } else if (q4) {
-            GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_aggr<AGGR, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AG_TOTAL));
-            occ[2] = resident_ctas(k_geo_aggr<AGGR, false, true>, AG_THREADS, AG_TOTAL, 3);
-        } else {
-            GM_CUDA_TRY(cudaFuncSetAttribute(k_geo_aggr<AGGR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AG_TOTAL));
-            occ[0] = resident_ctas(k_geo_aggr<AGGR, false>, AG_THREADS, AG_TOTAL, 3);
-        }
-    }
-    const int grid = persistent_grid((N + GEO_TPI - 1) / GEO_TPI, min(occ[which], MAX_PARTIAL_CTAS / 148));
+    const int n_items = (N + GEO_TPI - 1) / GEO_TPI;
+    int grid = 1;
     // Train mode, two ways to the BatchNorm moments: with >= 8 items per CTA the ticket schedule wins more than the
     // extra (L2-resident) pass of k_row_moments costs (c5: 233 -> 212 us); below that the static schedule with the
     // moments folded into the kernel is faster (c2: 72 vs 80 us).  Both are bit-reproducible.
-    const bool split = tail.partials && (long long)(N + GEO_TPI - 1) / GEO_TPI >= 8LL * grid;
-    const AggrTail in_kernel = split ? AggrTail{} : tail;
-    if (arg) GM_LAUNCH_PDL((k_geo_aggr<AGGR, true>), grid, AG_THREADS, AG_TOTAL, st, Y, P, v, N, out, arg, in_kernel);
-    else if (q4) GM_LAUNCH_PDL((k_geo_aggr<AGGR, false, true>), grid, AG_THREADS, AG_TOTAL, st, Y, P, v, N, out, arg, in_kernel);
-    else GM_LAUNCH_PDL((k_geo_aggr<AGGR, false>), grid, AG_THREADS, AG_TOTAL, st, Y, P, v, N, out, arg, in_kernel);
+    bool split = false;
+    if (arg && AGGR == GM_AGGR_MAX && (long long)N < (long long)GEO_AG_SMALL_EVENT * B)
+        GEO_AGGR_LAUNCH(ag_small, true, false, 3);       // training on DY/TT-sized events
+    else if (arg) GEO_AGGR_LAUNCH(ag_big, true, false, 1);
+    else if (q4) GEO_AGGR_LAUNCH(ag_big, false, true, 2);
+    else GEO_AGGR_LAUNCH(ag_big, false, false, 0);
     GM_LAUNCH_CHECK();
     if (split) {
         const int mgrid = persistent_grid((N + 63) / 64, min(4, MAX_PARTIAL_CTAS / 148));
@@ -853,9 +545,9 @@ int geo_edge_aggr(int aggr, const float *Y, const float *P, const void *geo_ws, 
     if (!geo_ws || B < 1) return GM_ERR_INVALID_ARGUMENT;
     const GeoView v = view_of(geo_ws, N, B);
     switch (aggr) {
-        case GM_AGGR_MAX: return launch_geo_aggr<GM_AGGR_MAX>(Y, P, v, N, out, arg, tail, st);
-        case GM_AGGR_ADD: return launch_geo_aggr<GM_AGGR_ADD>(Y, P, v, N, out, arg, tail, st);
-        case GM_AGGR_MEAN: return launch_geo_aggr<GM_AGGR_MEAN>(Y, P, v, N, out, arg, tail, st);
+        case GM_AGGR_MAX: return launch_geo_aggr<GM_AGGR_MAX>(Y, P, v, N, B, out, arg, tail, st);
+        case GM_AGGR_ADD: return launch_geo_aggr<GM_AGGR_ADD>(Y, P, v, N, B, out, arg, tail, st);
+        case GM_AGGR_MEAN: return launch_geo_aggr<GM_AGGR_MEAN>(Y, P, v, N, B, out, arg, tail, st);
     }
     return GM_ERR_INVALID_ARGUMENT;
 }
