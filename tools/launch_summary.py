@@ -2,7 +2,7 @@
 (the kernels between the last two occurrences of a marker kernel) with per-kernel device time and share."""
 import collections, csv, sys
 
-def main(path, marker="adamw"):
+def main(path, marker="k_reduce_partials"):   # the last kernel of a single-GPU training step (AdamW rides in it)
     with open(path) as f:
         lines = [l for l in f if not l.startswith("==")]
     rows = list(csv.DictReader(lines))
