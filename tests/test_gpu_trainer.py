@@ -160,3 +160,22 @@ def test_lr_scheduler_drives_the_fused_step():
     assert sd["param_groups"][0]["lr"] == tr.lr and len(sd["state"]) == 23
     ref_opt = torch.optim.AdamW([torch.nn.Parameter(torch.zeros_like(v)) for v in tr._views], lr=1e-3)
     ref_opt.load_state_dict(sd)                          # torch's own AdamW accepts the layout
+
+
+def test_optimiser_in_the_backward_equals_the_two_call_form(monkeypatch):
+    """gm_net_backward_geo_adamw (AdamW applied by the last CTA of the backward's final reduction) must leave the
+    parameters, the optimiser state and the status mirror BIT-identical to gm_net_backward_geo + gm_adamw_step_ex."""
+    from deepmetv2_b200 import trainer as T
+    batches = [synth.make_batch(6, "dytt", seed=70 + i).to(DEV) for i in range(3)]
+    states = []
+    for fused in (True, False):
+        monkeypatch.setattr(T, "_FUSED_ADAMW", fused)
+        torch.manual_seed(5)
+        tr = GraphMETTrainer(gnet.Net(8, 3).to(DEV), lr=2e-3, weight_decay=0.01)
+        losses = [tr.train_step(b).clone() for b in batches for _ in range(2)]
+        torch.cuda.synchronize()
+        states.append((tr.flat.clone(), tr.exp_avg.clone(), tr.exp_avg_sq.clone(), torch.stack(losses), tr.step_count))
+        tr.close()
+    for a, b in zip(states[0][:4], states[1][:4]):
+        assert torch.equal(a, b)
+    assert states[0][4] == states[1][4] == 6
