@@ -240,6 +240,7 @@ __global__ void __launch_bounds__(32) k_graclus(const int *__restrict__ rowptr, 
                                                 const int *__restrict__ visit, int state_cap, int *__restrict__ cluster,
                                                 int *__restrict__ partner) {
     extern __shared__ int s_gr[];
+    __shared__ unsigned s_hit[32];
     int *s_col = s_gr;                                     // [GR_BUF]
     float *s_w = reinterpret_cast<float *>(s_gr + GR_BUF); // [GR_BUF]
     int *s_state = s_gr + 2 * GR_BUF;                      // [state_cap] cluster id or -1
@@ -295,8 +296,48 @@ __global__ void __launch_bounds__(32) k_graclus(const int *__restrict__ rowptr, 
                 nxt = gr_describe(rowptr, visit, base, n, n0 + 32, lane);
                 prefetch(nxt);
             }
-            // (3) commit in visiting order
-            for (int q = 0; q < cnt; ++q) {
+            // (3a) commit in visiting order, first WITHOUT touching the state: a speculative choice stands unless an
+            // earlier node of this block took one of its two ends.  Lane q knows which lanes could (hitU: their choice
+            // is my node; hitV: their choice or their node is my choice); walking q = 0 .. cnt-1 with the running mask
+            // of committed lanes is one shuffle per node instead of two state loads, a store and a warp barrier.  The
+            // walk stops at the first node whose chosen neighbour was taken (it has to choose again from the real
+            // state); everything before it is written out in parallel and (3b) continues from there.
+            int q0 = 0;
+            if (!visit && state == s_state) {
+                const int u = cur.u;
+                const bool act = u >= 0 && state[u - base] < 0;
+                const bool pair = act && vsel != u;
+                const int vj = pair ? vsel - base - n0 : -1;               // my choice as a lane of this block, if it is one
+                s_hit[lane] = 0u;
+                __syncwarp();
+                if (pair && vj >= 0 && vj < 32) atomicOr(&s_hit[vj], 1u << lane);
+                __syncwarp();
+                const unsigned hitU = s_hit[lane];
+                unsigned hitV = 0u;
+                const unsigned pairs = __ballot_sync(0xffffffffu, pair);
+                if (pair) {
+                    hitV = __match_any_sync(pairs, vsel) & ~(1u << lane);     // same choice
+                    if (vj >= 0 && vj < 32) hitV |= 1u << vj;                 // my choice is a node of this block
+                }
+                unsigned done = 0u;
+                int stop = cnt;
+                for (int q = 0; q < cnt; ++q) {
+                    int code = 0;                                             // 0 nothing, 1 commit, 2 must choose again
+                    if (act && !(hitU & done)) code = (pair && (hitV & done)) ? 2 : 1;
+                    code = __shfl_sync(0xffffffffu, code, q);
+                    if (code == 2) { stop = q; break; }
+                    if (code == 1) done |= 1u << q;
+                }
+                if (done & (1u << lane)) {
+                    const int c = min(u, vsel);
+                    state[u - base] = c;
+                    state[vsel - base] = c;
+                }
+                __syncwarp();
+                q0 = stop;
+            }
+            // (3b) the rest of the block against the real state
+            for (int q = q0; q < cnt; ++q) {
                 const int u = __shfl_sync(0xffffffffu, cur.u, q);
                 int v = __shfl_sync(0xffffffffu, vsel, q);
                 if (state[u - base] >= 0) continue;                               // matched earlier in this block
