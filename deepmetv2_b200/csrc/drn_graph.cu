@@ -182,7 +182,10 @@ __global__ void __launch_bounds__(256) k_normalized_cut(const float *__restrict_
 // neighbour gets matched by an earlier node of the same block (matching OTHER neighbours only removes candidates that
 // were not the maximum); (3) a short commit loop walks the 32 nodes in order and re-evaluates just those.
 constexpr int GR_BUF = 768;       // staged row entries per block of 32 visited nodes (per buffer)
-constexpr int GR_TRIPS = 6;       // register-held prefetch: 32 * 4 * GR_TRIPS entries
+__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+                 : "memory");
+}
 
 struct GrBlock {                   // lane-held description of a block of 32 visited nodes
     int u, ra, len, off, total;
@@ -241,9 +244,9 @@ __global__ void __launch_bounds__(32) k_graclus(const int *__restrict__ rowptr, 
                                                 int *__restrict__ partner) {
     extern __shared__ int s_gr[];
     __shared__ unsigned s_hit[32];
-    int *s_col = s_gr;                                     // [GR_BUF]
-    float *s_w = reinterpret_cast<float *>(s_gr + GR_BUF); // [GR_BUF]
-    int *s_state = s_gr + 2 * GR_BUF;                      // [state_cap] cluster id or -1
+    int *s_col = s_gr;                                         // [2][GR_BUF]
+    float *s_w = reinterpret_cast<float *>(s_gr + 2 * GR_BUF); // [2][GR_BUF]
+    int *s_state = s_gr + 4 * GR_BUF;                          // [state_cap] cluster id or -1
     pdl_sync();
     const int lane = threadIdx.x;
     const bool weighted = weight != nullptr;
@@ -255,36 +258,33 @@ __global__ void __launch_bounds__(32) k_graclus(const int *__restrict__ rowptr, 
         for (int l = lane; l < n; l += 32) state[l] = -1;
         __syncwarp();
         GrBlock cur = gr_describe(rowptr, visit, base, n, 0, lane);
-        int pc[4 * GR_TRIPS];
-        float pw[4 * GR_TRIPS];
-        auto prefetch = [&](const GrBlock &b) {            // independent loads into registers
-            if (b.total > GR_BUF || b.total > 128 * GR_TRIPS) return;
-#pragma unroll
-            for (int i = 0; i < 4 * GR_TRIPS; ++i) {
-                const int t = 32 * i + lane;
-                if (32 * i < b.total) {                    // warp-uniform
+        // The rows of the NEXT block travel global -> shared memory as 4-byte cp.async copies into the other half of a
+        // double buffer while the current block is chosen and committed.  (Register-held prefetches completed one by
+        // one: ncu showed a full memory round trip on each of a block's ~11 load pairs, 45 % of the kernel.)
+        auto stage_async = [&](const GrBlock &b, int half) {
+            if (b.total <= GR_BUF) {
+                const int first = __shfl_sync(0xffffffffu, b.ra, 0);
+                for (int t0 = 0; t0 < b.total; t0 += 32) {             // warp-uniform trip count (gr_source shuffles)
+                    const int t = t0 + lane;
                     // ascending visiting order: the rows of 32 consecutive nodes are one contiguous range of the CSR
-                    const int src = visit ? gr_source(b, t) : __shfl_sync(0xffffffffu, b.ra, 0) + t;
-                    const bool live = t < b.total;
-                    pc[i] = live ? col[src] : 0;
-                    pw[i] = (live && weighted) ? weight[src] : 0.f;
+                    const int src = visit ? gr_source(b, min(t, b.total - 1)) : first + t;
+                    if (t < b.total) {
+                        cp_async4(s_col + half * GR_BUF + t, col + src);
+                        if (weighted) cp_async4(s_w + half * GR_BUF + t, weight + src);
+                    }
                 }
             }
+            asm volatile("cp.async.commit_group;" ::: "memory");
         };
-        prefetch(cur);
+        int half = 0;
+        stage_async(cur, half);
         for (int n0 = 0; n0 < n; n0 += 32) {
             const int cnt = min(32, n - n0);
-            const bool staged = cur.total <= GR_BUF && cur.total <= 128 * GR_TRIPS;
-            if (staged) {
-#pragma unroll
-                for (int i = 0; i < 4 * GR_TRIPS; ++i) {
-                    const int t = 32 * i + lane;
-                    if (t < cur.total) { s_col[t] = pc[i]; s_w[t] = pw[i]; }
-                }
-            }
+            const bool staged = cur.total <= GR_BUF;
+            asm volatile("cp.async.wait_all;" ::: "memory");
             __syncwarp();
-            const int *cols = staged ? s_col : col;
-            const float *ws = staged ? s_w : weight;
+            const int *cols = staged ? s_col + half * GR_BUF : col;
+            const float *ws = staged ? s_w + half * GR_BUF : weight;
             const int row_o = staged ? cur.off : cur.ra;
             // (2) speculative choice from the state at block start, every lane for its own node
             int vsel = cur.u;
@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(32) k_graclus(const int *__restrict__ rowptr, 
             GrBlock nxt = cur;
             if (n0 + 32 < n) {
                 nxt = gr_describe(rowptr, visit, base, n, n0 + 32, lane);
-                prefetch(nxt);
+                stage_async(nxt, half ^ 1);
             }
             // (3a) commit in visiting order, first WITHOUT touching the state: a speculative choice stands unless an
             // earlier node of this block took one of its two ends.  Lane q knows which lanes could (hitU: their choice
@@ -351,6 +351,7 @@ __global__ void __launch_bounds__(32) k_graclus(const int *__restrict__ rowptr, 
             }
             __syncwarp();
             cur = nxt;
+            half ^= 1;
         }
         // write-out: cluster ids, and the partner derived from them (the non-representative member names both)
         for (int l = lane; l < n; l += 32) {
@@ -448,9 +449,9 @@ int drn_graclus(const int *rowptr, const int *col, const float *weight, const in
                 const int *visit, int *cluster, int *partner, cudaStream_t st) {
     (void)N;
     int cap = men > 0 ? men : 1;
-    const int max_cap = (200 * 1024 - 2 * GR_BUF * 4) / 4;
+    const int max_cap = (200 * 1024 - 4 * GR_BUF * 4) / 4;
     if (cap > max_cap) cap = max_cap;            // larger events run with the state in global memory
-    const size_t smem = (size_t)(2 * GR_BUF + cap) * 4;
+    const size_t smem = (size_t)(4 * GR_BUF + cap) * 4;
     static bool attr_set = false;
     if (!attr_set) {
         GM_CUDA_TRY(cudaFuncSetAttribute(k_graclus, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
