@@ -114,4 +114,35 @@ __device__ __forceinline__ int nbhd_runs(const CellGrid &g, const int *__restric
     return n;
 }
 
+// nbhd_runs for the staging producers: ALWAYS six slots (eta-row ce-1: wrap run, main run; ce: ...; ce+1: ...), an
+// absent run is empty (lo == hi == 0), so the slots are statically indexed (registers, not a local-memory array) and
+// the twelve cell_start loads are unconditional and independent of each other: one memory round trip per segment
+// instead of up to twelve (the producer warp is what the consumers of a DY/TT-sized step wait for).  Same runs in
+// the same order as nbhd_runs once the empty slots are dropped.
+__device__ __forceinline__ void nbhd_runs6(const CellGrid &g, const int *__restrict__ cs, int ce, int cpa, int cpb,
+                                           int phi_wrap, int (&rlo)[6], int (&rhi)[6]) {
+#pragma unroll
+    for (int de = -1; de <= 1; ++de) {
+        const int ce2 = ce + de;
+        const bool ok = ce2 >= 0 && ce2 < g.g0;
+        const int *row = cs + (ok ? ce2 : ce) * g.g1;
+        int lo = cpa - 1, hi = cpb + 1, wl = -1;
+        if (phi_wrap) {
+            if (g.g1 >= 3 && hi - lo + 1 < g.g1) {
+                if (lo < 0) { wl = g.g1 - 1; lo = 0; }
+                else if (hi >= g.g1) { wl = 0; hi = g.g1 - 1; }
+            } else {
+                lo = 0; hi = g.g1 - 1;
+            }
+        }
+        lo = lo < 0 ? 0 : lo;
+        hi = hi >= g.g1 ? g.g1 - 1 : hi;
+        const int wc = wl < 0 ? 0 : wl;
+        const int w0 = __ldg(row + wc), w1 = __ldg(row + wc + 1), m0 = __ldg(row + lo), m1 = __ldg(row + hi + 1);
+        const int s = 2 * (de + 1);
+        rlo[s] = (ok && wl >= 0) ? w0 : 0; rhi[s] = (ok && wl >= 0) ? w1 : 0;
+        rlo[s + 1] = ok ? m0 : 0;          rhi[s + 1] = ok ? m1 : 0;
+    }
+}
+
 }  // namespace gm

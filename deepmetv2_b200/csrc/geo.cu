@@ -361,13 +361,12 @@ k_geo_scatter(const float *__restrict__ G, const float *__restrict__ raw, BnBwd 
                 const int ca = __shfl_sync(0xffffffffu, cell, a), cb = __shfl_sync(0xffffffffu, cell, b - 1);
                 const int ce = ca / g.g1;
                 int rlo[6], rhi[6], voff[7];
-                const int nr0 = nbhd_runs(g, v.cell_start + (size_t)ev * (CMAX + 1), ce, ca - ce * g.g1, cb - ce * g.g1,
-                                          m.phi_wrap, rlo, rhi);
-                int nr = 0, C = 0;
+                nbhd_runs6(g, v.cell_start + (size_t)ev * (CMAX + 1), ce, ca - ce * g.g1, cb - ce * g.g1, m.phi_wrap, rlo, rhi);
+                constexpr int nr = 6;                          // empty slots stay (zero rows): static indexing, no local memory
+                int C = 0;
 #pragma unroll
-                for (int q = 0; q < 6; ++q)
-                    if (q < nr0 && rhi[q] > rlo[q]) { rlo[nr] = rlo[q]; voff[nr] = C; C += rhi[q] - rlo[q]; ++nr; }
-                voff[nr] = C;
+                for (int q = 0; q < 6; ++q) { voff[q] = C; C += rhi[q] - rlo[q]; }
+                voff[6] = C;
                 const int nck = (C + SC_CH - 1) / SC_CH;
                 for (int k = 0; k < nck; ++k, ++gc) {
                     const int st = gc % SC_STAGES;
