@@ -329,10 +329,26 @@ k_node_prep2(const float *__restrict__ raw, const float *__restrict__ resid, con
     const int tiles = (N + NODE_TILE - 1) / NODE_TILE;
     for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const int node0 = tile * NODE_TILE, rows = min(NODE_TILE, N - node0);
-        for (int idx = t; idx < rows * (H / 4); idx += NP_THREADS) {
-            const int r = idx >> 3, c4 = (idx & 7) * 4;
+        // all loads of the tile first (8 x 16 bytes per thread in flight), then the arithmetic: ONE memory round trip per
+        // tile -- the rolled loop issued a load pair per trip and waited for it (four round trips)
+        constexpr int NP_IT = NODE_TILE * (H / 4) / NP_THREADS;
+        float4 rv[NP_IT], qv[NP_IT];
+#pragma unroll
+        for (int it = 0; it < NP_IT; ++it) {
+            const int idx = it * NP_THREADS + t, r = idx >> 3;
             const size_t g = (size_t)(node0 + r) * (H / 4) + (idx & 7);
-            float4 v = reinterpret_cast<const float4 *>(raw)[g];
+            rv[it] = qv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (r < rows) {
+                rv[it] = reinterpret_cast<const float4 *>(raw)[g];
+                if (resid) qv[it] = reinterpret_cast<const float4 *>(resid)[g];
+            }
+        }
+#pragma unroll
+        for (int it = 0; it < NP_IT; ++it) {
+            const int idx = it * NP_THREADS + t, r = idx >> 3, c4 = (idx & 7) * 4;
+            if (r >= rows) continue;
+            const size_t g = (size_t)(node0 + r) * (H / 4) + (idx & 7);
+            float4 v = rv[it];
             if (stat) {
                 v.x = fmaf(v.x - s_stat[c4 + 0], s_stat[H + c4 + 0], s_stat[3 * H + c4 + 0]);
                 v.y = fmaf(v.y - s_stat[c4 + 1], s_stat[H + c4 + 1], s_stat[3 * H + c4 + 1]);
@@ -340,7 +356,7 @@ k_node_prep2(const float *__restrict__ raw, const float *__restrict__ resid, con
                 v.w = fmaf(v.w - s_stat[c4 + 3], s_stat[H + c4 + 3], s_stat[3 * H + c4 + 3]);
             }
             if (resid) {
-                const float4 q = reinterpret_cast<const float4 *>(resid)[g];
+                const float4 q = qv[it];
                 v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
             }
             if (emb_out) reinterpret_cast<float4 *>(emb_out)[g] = v;
