@@ -354,7 +354,8 @@ class GraphMETTrainer:
         x, y, p = batch.x, batch.y, batch.ptr
         self._check_batch(x, y, p)
         N, B, men = self._sizes(batch, max_event_nodes)
-        self.net.train()
+        if not self.net.training:      # nn.Module.train() walks the module tree: not once per step
+            self.net.train()
         l, st = lib(), stream(self.device)
         dp = self.world > 1
         self._last_N = N
@@ -470,7 +471,8 @@ class GraphMETTrainer:
         x, y, p = batch.x, batch.y, batch.ptr
         self._check_batch(x, y, p)
         N, B, men = self._sizes(batch, max_event_nodes)
-        self.net.eval()
+        if self.net.training:
+            self.net.eval()
         self._reserve(N, B, men)
         self._graph(x, p, N, B, men, need_transpose=False)
         self._forward(x, N, B, training=False, save=False)
@@ -609,7 +611,8 @@ class DRNTrainer:
         men = max_event_nodes if max_event_nodes is not None else getattr(batch, "max_event_nodes", None)
         if men is None:
             men = int((p[1:] - p[:-1]).max().item())
-        self.net.train()
+        if not self.net.training:
+            self.net.train()
         self._reserve(N, B)
         l, st, net = lib(), stream(self.device), self.net
         bn = net.edgeconv1.nn[4]
