@@ -284,8 +284,14 @@ namespace ag_big {
 }  // namespace ag_big
 #undef GEO_AG_CH
 #undef GEO_AG_MINB
-#define GEO_AG_CH 320
-#define GEO_AG_MINB 2
+#ifndef GEO_AG_SMALL_CH
+#define GEO_AG_SMALL_CH 320
+#endif
+#ifndef GEO_AG_SMALL_MINB
+#define GEO_AG_SMALL_MINB 2
+#endif
+#define GEO_AG_CH GEO_AG_SMALL_CH
+#define GEO_AG_MINB GEO_AG_SMALL_MINB
 namespace ag_small {
 #include "geo_aggr.inc"
 }  // namespace ag_small
