@@ -57,3 +57,30 @@ def test_no_cpu_fallback():
     with pytest.raises(RuntimeError):
         m(torch.zeros(4, 8), torch.zeros(4, 3, dtype=torch.long), torch.zeros(2, 0, dtype=torch.long),
           torch.zeros(4, dtype=torch.long))
+
+
+def test_ctypes_structs_match_the_c_header_field_by_field(tmp_path):
+    """Every ctypes.Structure of the binding against the C compiler's view of include/graphmet.h: sizeof and the
+    offset of every field (a drifted field order or type would hand the kernels garbage pointers)."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no C compiler")
+    structs = {n: c for n, c in vars(_lib).items()
+               if isinstance(c, type) and issubclass(c, ctypes.Structure) and n.startswith("Gm")}
+    assert {"GmBatchNorm", "GmParams", "GmAdamW", "GmDrnConv", "GmDrnParams", "GmDrnView"} <= set(structs)
+    lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{_lib.HEADER}"', 'int main(void) {']
+    for n, c in structs.items():
+        lines.append(f'  printf("{n} %zu\\n", sizeof({n}));')
+        for f in c._fields_:
+            lines.append(f'  printf("{n}.{f[0]} %zu\\n", offsetof({n}, {f[0]}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c99", "-o", str(exe), str(src)], check=True)
+    want = dict(l.split() for l in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for n, c in structs.items():
+        assert ctypes.sizeof(c) == int(want[n]), n
+        for f in c._fields_:
+            assert getattr(c, f[0]).offset == int(want[f"{n}.{f[0]}"]), f"{n}.{f[0]}"
