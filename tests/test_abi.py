@@ -84,3 +84,29 @@ def test_ctypes_structs_match_the_c_header_field_by_field(tmp_path):
         assert ctypes.sizeof(c) == int(want[n]), n
         for f in c._fields_:
             assert getattr(c, f[0]).offset == int(want[f"{n}.{f[0]}"]), f"{n}.{f[0]}"
+
+
+def test_ctypes_signatures_match_the_header_prototypes():
+    """Argument count and scalar / pointer kind of every entry point: _lib.SIGNATURES against the prototypes of
+    include/graphmet.h (an argument dropped on one side shifts every pointer after it)."""
+    src = re.sub(r"/\*.*?\*/", " ", open(_lib.HEADER).read(), flags=re.S)
+    protos = dict((m.group(2), (m.group(1).strip(), m.group(3)))
+                  for m in re.finditer(r"^([A-Za-z_][\w \*]*?)\b(gm_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", src, flags=re.M))
+
+    def kind(decl):
+        decl = decl.strip()
+        if "*" in decl:
+            return "ptr"
+        base = re.sub(r"\b(const|unsigned|signed)\b", "", decl).split()
+        t = " ".join(base[:-1]) if len(base) > 1 else base[0]
+        return {"int": "int", "float": "float", "double": "double", "size_t": "size_t", "long long": "ll",
+                "int64_t": "ll"}[t]
+
+    ckind = {ctypes.c_int: "int", ctypes.c_float: "float", ctypes.c_double: "double", ctypes.c_size_t: "size_t",
+             ctypes.c_longlong: "ll", ctypes.c_void_p: "ptr", ctypes.c_char_p: "ptr"}
+    assert sorted(protos) == sorted(_lib.SIGNATURES)
+    for name, (ret, params) in protos.items():
+        params = params.strip()
+        want = [] if params in ("", "void") else [kind(p) for p in params.split(",")]
+        got = [ckind.get(a, "ptr") for a in _lib.SIGNATURES[name][1]]      # POINTER(struct) -> ptr
+        assert got == want, f"{name}: binding {got} vs header {want}"
