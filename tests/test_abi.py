@@ -110,3 +110,7 @@ def test_ctypes_signatures_match_the_header_prototypes():
         want = [] if params in ("", "void") else [kind(p) for p in params.split(",")]
         got = [ckind.get(a, "ptr") for a in _lib.SIGNATURES[name][1]]      # POINTER(struct) -> ptr
         assert got == want, f"{name}: binding {got} vs header {want}"
+        rk = "ptr" if "*" in ret else {"int": "int", "size_t": "size_t", "long long": "ll", "float": "float",
+                                       "double": "double", "void": "void"}[re.sub(r"\bconst\b", "", ret).strip()]
+        res = _lib.SIGNATURES[name][0]
+        assert ("void" if res is None else ckind.get(res, "ptr")) == rk, f"{name}: return type"
