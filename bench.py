@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the GraphMETNetwork hot path on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c5|knn]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c4|c5|knn]
 
 A "step" is one pass of the hot path over one batch of synthetic events:
   c2 (default, BASELINE.json configs[1]): TRAINING step (radius graph + forward + loss + backward +
@@ -13,6 +13,11 @@ batch of the same shape); the only collective is the exchange of the 26.6 KB fla
 in one kernel over NVLink peer memory (csrc/comm.cu).  Rank 0 prints ONE JSON line.  With the default workload the
 line also carries "side": the other BASELINE configurations (c5 training at every N; c3 inference fp32 and bf16
 tcgen05 at N = 1) measured in the same run with the same timing rules, so that they are driver-visible.
+
+Timing: W warm-up steps, then K steps timed with CUDA events on the launching stream (L2 flushed before every step,
+outside the event pair), max over ranks -> value / ms_per_step / gpu_launches, with the library's per-kernel timers OFF
+(production behaviour); then the same K steps once more with one CUDA-event pair per kernel family -> kernels / roofline
+/ instrumented_ms_per_step (the event records between kernels break the dependent-launch chain: that pass is slower).
 """
 from __future__ import annotations
 
